@@ -1,0 +1,166 @@
+/*
+ * prestogpu.h — C ABI of the B200-native hash-aggregation / hash-join path.
+ *
+ * This is the drop-in boundary.  Every entry point is what a
+ * JNI binding of the reference's operator interfaces would call; the
+ * reference interface each one replaces is cited as file:line relative to
+ * /root/reference/core/trino-main/src/main/java/io/trino/ (OP = operator/).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, no C++/torch types.
+ *  - every function returns int32 status (PG_OK == 0); out-params are last.
+ *  - a pg_col describes one Trino Block: values + optional 1-byte-per-row
+ *    null mask (boolean[] valueIsNull) + optional int32 offsets (n+1) for
+ *    variable width blocks.  `mem` says where the pointers live.
+ *  - handles are not thread-safe; one CUDA stream per context.
+ *  - input columns are copied/consumed before the call returns; nothing is
+ *    retained that points into caller memory (unless mem == PG_MEM_DEVICE
+ *    and the call documents that it keeps a reference).
+ */
+#ifndef PRESTOGPU_H
+#define PRESTOGPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PG_API __attribute__((visibility("default")))
+
+/* ---- status codes (SURVEY §8b "Error conventions") ---- */
+enum {
+    PG_OK = 0,
+    PG_NEED_MEMORY = 1,              /* Work.process()==false analogue: nothing consumed      */
+    PG_E_INSUFFICIENT_RESOURCES = 2, /* GENERIC_INSUFFICIENT_RESOURCES (OP/BigintGroupByHash.java:265-267) */
+    PG_E_NUMERIC_OVERFLOW = 3,       /* NUMERIC_VALUE_OUT_OF_RANGE (type/BigintOperators.java:47-55)     */
+    PG_E_INVALID_ARGUMENT = 4,       /* checkArgument / IllegalArgumentException             */
+    PG_E_CUDA = 5,
+    PG_E_NCCL = 6,
+    PG_E_INTERNAL = 7,
+    PG_E_ILLEGAL_STATE = 8           /* checkState / IllegalStateException                    */
+};
+
+/* ---- column element types (spi/type/ *.java) ---- */
+enum {
+    PG_BIGINT = 1,        /* LongArrayBlock, int64                                   */
+    PG_INTEGER = 2,       /* IntArrayBlock, int32                                    */
+    PG_DATE = 3,          /* IntArrayBlock, int32 days                               */
+    PG_DOUBLE = 4,        /* LongArrayBlock holding doubleToLongBits                 */
+    PG_SHORT_DECIMAL = 5, /* LongArrayBlock, unscaled int64 (p <= 18)                */
+    PG_LONG_DECIMAL = 6,  /* Int128ArrayBlock, 2 x int64 sign-magnitude (p > 18)     */
+    PG_VARCHAR = 7,       /* VariableWidthBlock: bytes + int32 offsets[n+1]          */
+    PG_VARBINARY = 8,     /* same layout as VARCHAR (intermediate states)            */
+    PG_BOOLEAN = 9        /* ByteArrayBlock, 1 byte                                  */
+};
+
+enum { PG_MEM_HOST = 0, PG_MEM_DEVICE = 1 };
+
+typedef struct pg_col {
+    int32_t type;           /* PG_BIGINT ...                                         */
+    int32_t mem;            /* PG_MEM_HOST | PG_MEM_DEVICE                           */
+    int64_t n;              /* positionCount                                         */
+    const void* values;     /* element array (bytes for VARCHAR/VARBINARY)           */
+    const uint8_t* nulls;   /* 1 byte per row, non-zero == null; NULL == no nulls    */
+    const int32_t* offsets; /* VARCHAR/VARBINARY only: n+1 offsets into values       */
+    int32_t precision;      /* decimals                                              */
+    int32_t scale;
+} pg_col;
+
+/* mutable twin used for outputs: caller allocates, callee fills */
+typedef struct pg_col_out {
+    int32_t type;
+    int32_t mem;
+    int64_t capacity;       /* rows the buffers can hold                             */
+    void* values;
+    uint8_t* nulls;         /* may be NULL if the caller does not want null flags    */
+    int32_t* offsets;       /* VARCHAR/VARBINARY: capacity+1                         */
+    int64_t values_capacity_bytes; /* VARCHAR/VARBINARY byte capacity                */
+} pg_col_out;
+
+typedef struct pg_ctx pg_ctx;
+
+/* ---- context ---- */
+PG_API int32_t pg_ctx_create(int32_t device, pg_ctx** out);
+PG_API int32_t pg_ctx_destroy(pg_ctx* ctx);
+/* message of the last failing call on this context (thread-unsafe, like the handle) */
+PG_API const char* pg_last_error(pg_ctx* ctx);
+/* use an external stream (e.g. torch's current stream) for all work of this context */
+PG_API int32_t pg_ctx_set_stream(pg_ctx* ctx, void* cuda_stream);
+PG_API int32_t pg_ctx_synchronize(pg_ctx* ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches)  */
+PG_API int64_t pg_ctx_launch_count(pg_ctx* ctx);
+PG_API const char* pg_version(void);
+
+/* =====================================================================================
+ * GroupByHash  —  replaces OP/GroupByHash.java:31-88, OP/BigintGroupByHash.java:43-425,
+ * OP/MultiChannelGroupByHash.java:55-853.
+ * Exactly one BIGINT key -> the bigint table (16-byte slots, key in slot); anything else ->
+ * the multi-channel table (8-byte slots + packed key rows).  Dispatch mirrors
+ * GroupByHash.createGroupByHash (OP/GroupByHash.java:45-59).
+ * Group ids are dense and assigned in first-seen row order, like the reference.
+ * ===================================================================================== */
+typedef struct pg_groupby pg_groupby;
+
+PG_API int32_t pg_groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys,
+                                 int32_t has_hash_channel, int64_t expected_size, pg_groupby** out);
+PG_API int32_t pg_groupby_destroy(pg_groupby* gb);
+/* getGroupIds(Page) (OP/GroupByHash.java:75): out_ids[n] int32 (host or device, `ids_mem`),
+ * *out_group_count = GroupByIdBlock.groupCount.  hash_col = precomputed $hashvalue channel or NULL. */
+PG_API int32_t pg_groupby_get_group_ids(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n,
+                                        int32_t* out_ids, int32_t ids_mem, int64_t* out_group_count);
+/* addPage(Page) (OP/GroupByHash.java:73) */
+PG_API int32_t pg_groupby_add_page(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n);
+/* contains(position, page, hashChannels[, rawHash]) for every row of the page (OP/GroupByHash.java:77-83) */
+PG_API int32_t pg_groupby_contains(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n,
+                                   uint8_t* out, int32_t out_mem);
+/* appendValuesTo(groupId, pageBuilder, 0) for groupId in [first, first+n) (OP/GroupByHash.java:71);
+ * out_hash (int64[n], may be NULL) receives the raw-hash channel / getRawHash(groupId) (:85). */
+PG_API int32_t pg_groupby_export_keys(pg_groupby* gb, int64_t first, int64_t n, pg_col_out* out_keys,
+                                      int64_t* out_hash, int32_t hash_mem);
+/* bytes needed for variable-width key `key` over all groups (to size pg_col_out.values) */
+PG_API int32_t pg_groupby_varwidth_bytes(pg_groupby* gb, int32_t key, int64_t* out_bytes);
+/* getGroupCount / getCapacity / getHashCollisions / getEstimatedSize (OP/GroupByHash.java:61-87).
+ * capacity is the reference's logical capacity schedule (arraySize(expected,0.75) doubled while
+ * groupCount >= maxFill); device_bytes is what the table really holds in HBM. */
+PG_API int32_t pg_groupby_stats(pg_groupby* gb, int64_t* group_count, int64_t* capacity,
+                                int64_t* collisions, int64_t* device_bytes);
+
+/* =====================================================================================
+ * GroupedAccumulator — replaces OP/aggregation/GroupedAccumulator.java:22-39 as generated by
+ * OP/aggregation/AccumulatorCompiler.java:261-330,487-566 for count/sum/avg/min/max.
+ *
+ * Intermediate (partial -> final) column layouts, per aggregate:
+ *   COUNT, COUNT_COL      : [BIGINT count]                                   (CountAggregation.java:33-55)
+ *   SUM(BIGINT|INTEGER)   : [BIGINT count, BIGINT sum]                       (LongSumAggregation.java:34-64)
+ *   SUM(DOUBLE)           : [BIGINT count, DOUBLE sum]                       (DoubleSumAggregation.java:33-63)
+ *   AVG(DOUBLE|BIGINT)    : [DOUBLE sum, BIGINT count]                       (AverageAggregations.java:34-80)
+ *   SUM(DECIMAL)          : [VARBINARY 24 B = overflow int64 | lo | hi], NULL if untouched
+ *                           (state/LongDecimalWithOverflowStateSerializer.java:38-66)
+ *   AVG(DECIMAL)          : [VARBINARY 32 B = count | overflow | lo | hi]
+ *                           (state/LongDecimalWithOverflowAndLongStateSerializer.java:38-68)
+ *   MIN, MAX              : [value type, nullable]                           (NullableLongStateSerializer.java:33-42)
+ * ===================================================================================== */
+enum { PG_AGG_COUNT = 1, PG_AGG_COUNT_COL = 2, PG_AGG_SUM = 3, PG_AGG_AVG = 4, PG_AGG_MIN = 5, PG_AGG_MAX = 6 };
+
+typedef struct pg_agg pg_agg;
+PG_API int32_t pg_agg_create(pg_ctx* ctx, int32_t kind, int32_t in_type, pg_agg** out);
+PG_API int32_t pg_agg_destroy(pg_agg* agg);
+/* addInput(GroupByIdBlock, Page): ids int32[n] (`ids_mem`), arg NULL for COUNT, mask NULL or BOOLEAN */
+PG_API int32_t pg_agg_add_input(pg_agg* agg, const int32_t* ids, int32_t ids_mem, int64_t group_count,
+                                const pg_col* arg, const pg_col* mask, int64_t n);
+/* addIntermediate(GroupByIdBlock, Block): `state` = the columns listed in the table above */
+PG_API int32_t pg_agg_add_intermediate(pg_agg* agg, const int32_t* ids, int32_t ids_mem, int64_t group_count,
+                                       const pg_col* state, int64_t n);
+PG_API int32_t pg_agg_n_intermediate(pg_agg* agg, int32_t* out);
+/* evaluateFinal / evaluateIntermediate for groupId in [first, first+n).  Returns
+ * PG_E_NUMERIC_OVERFLOW and *error_group where the reference's output function throws. */
+PG_API int32_t pg_agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t final_step,
+                               pg_col_out* out, int64_t* error_group);
+PG_API int32_t pg_agg_device_bytes(pg_agg* agg, int64_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,12 @@
+"""presto-1_b200 — B200-native hash-aggregation / hash-join operator path behind the reference's operator API.
+
+The package directory name contains a hyphen (it follows the reference repo's name); import it with
+`importlib.import_module("presto-1_b200")` or through the `presto_b200` shim at the repository root.
+"""
+from . import _native as native
+from ._native import (AGG_AVG, AGG_COUNT, AGG_COUNT_COL, AGG_MAX, AGG_MIN, AGG_SUM, BIGINT, BOOLEAN, DATE, DOUBLE, INTEGER,
+                      LONG_DECIMAL, SHORT_DECIMAL, VARBINARY, VARCHAR, PrestoGpuError)
+from .blocks import Block, OutBlock, Page
+from .context import GpuContext, default_context
+from .groupby import GroupByHash, GroupByIdBlock
+from .accumulators import GroupedAccumulator, final_type, intermediate_types

@@ -1,0 +1,54 @@
+"""GpuContext: one pg_ctx (device + stream).  Creation fails loudly without a CUDA device (no CPU fallback)."""
+import ctypes as C
+
+from . import _native as N
+
+
+class GpuContext:
+    def __init__(self, device=0, use_torch_stream=True):
+        self._h = C.c_void_p()
+        rc = N.lib().pg_ctx_create(device, C.byref(self._h))
+        if rc != N.PG_OK:
+            raise N.PrestoGpuError(rc, "pg_ctx_create(device=%d) failed: no usable CUDA device (there is no CPU fallback)" % device)
+        self.device = device
+        if use_torch_stream:
+            try:
+                import torch
+                if torch.cuda.is_available():
+                    torch.cuda.set_device(device)
+                    self.set_stream(torch.cuda.current_stream(device).cuda_stream)
+            except ImportError:
+                pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    def set_stream(self, cuda_stream):
+        N.check(self._h, N.lib().pg_ctx_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def synchronize(self):
+        N.check(self._h, N.lib().pg_ctx_synchronize(self._h))
+
+    def launch_count(self):
+        return int(N.lib().pg_ctx_launch_count(self._h))
+
+    def close(self):
+        if self._h:
+            N.lib().pg_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default = {}
+
+
+def default_context(device=0):
+    if device not in _default:
+        _default[device] = GpuContext(device)
+    return _default[device]

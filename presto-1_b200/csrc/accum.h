@@ -1,0 +1,85 @@
+// accum.h — grouped accumulators (replaces the classes AccumulatorCompiler.java:261-330,487-566 generates for
+// count/sum/avg/min/max and their state classes under MAIN/operator/aggregation/state/).
+//
+// HBM layout: one state array per aggregate, `words` u64 words per group (array of structs):
+//   COUNT, COUNT_COL               [cnt]
+//   SUM(bigint|integer)            [cnt, lo, hi]           128-bit two's complement running sum
+//   SUM(double), AVG(double|bigint)[cnt, sum(double bits)]
+//   SUM/AVG(decimal)               [cnt, w0, w1, w2]       192-bit two's complement running sum; converted to the
+//                                                          reference's (overflow, sign-magnitude 127 bit) state on output
+//   MIN/MAX (64-bit types)         [cnt, key]              key = value, or the Double.compare order key for doubles
+//   MIN/MAX (long decimal)         [cnt, hi, lo]           two's complement, resolved in two passes (hi, then lo)
+// Multi-word sums are updated with one atomicAdd per word plus carry propagation; integer addition commutes, so the
+// final state is independent of the order in which rows arrive.
+#pragma once
+#include "context.h"
+
+namespace pg {
+
+enum OpClass : int32_t {
+    OP_COUNT = 0,    // cnt += 1
+    OP_SUM_I64 = 1,  // cnt, 128-bit sum
+    OP_SUM_F64 = 2,  // cnt, double sum
+    OP_SUM_DEC = 3,  // cnt, 192-bit sum
+    OP_MIN64 = 4,
+    OP_MAX64 = 5,
+    OP_MIN128 = 6,
+    OP_MAX128 = 7,
+};
+
+static const int MAX_AGGS = 16;
+
+struct AggOp {
+    int32_t op;         // OpClass
+    int32_t in_type;    // PG_* of the argument (0 for count(*))
+    int32_t words;      // u64 words per group in the global state
+    int32_t skip_null;  // 1: rows whose argument is null do not contribute (everything but count(*))
+    int32_t priv_off;   // first word inside the block-private table (PRIVATE mode)
+    int32_t convert_i2d;  // avg(bigint): accumulate (double)value
+    DCol arg;
+    DCol mask;          // optional BOOLEAN mask column (values==nullptr: no mask)
+    unsigned long long* state;  // global state base
+};
+
+struct AggProgram {
+    int32_t naggs;
+    int32_t priv_words;  // total private words per group
+    AggOp ops[MAX_AGGS];
+};
+
+static inline int state_words(int op) {
+    switch (op) {
+        case OP_COUNT: return 1;
+        case OP_SUM_I64: return 3;
+        case OP_SUM_F64: return 2;
+        case OP_SUM_DEC: return 4;
+        case OP_MIN64: case OP_MAX64: return 2;
+        default: return 3;
+    }
+}
+
+// launch the grouped accumulation of `prog` over n rows with group ids `gids` (device int32)
+void accumulate(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count);
+// (re)initialise state words of groups [first, first+count): zeros, min/max identities
+void init_state(pg_ctx* ctx, int op, unsigned long long* state, int64_t first, int64_t count);
+
+}  // namespace pg
+
+struct pg_agg {
+    pg_ctx* ctx = nullptr;
+    int32_t kind = 0;      // PG_AGG_*
+    int32_t in_type = 0;
+    int32_t op = 0;        // OpClass
+    int32_t words = 0;
+    int64_t capacity = 0;  // groups the state array holds (initialised)
+    pg::DevBuf state;
+};
+
+namespace pg {
+void agg_create(pg_ctx* ctx, int32_t kind, int32_t in_type, pg_agg** out);
+void agg_ensure_capacity(pg_agg* agg, int64_t group_count);
+AggOp agg_make_op(pg_agg* agg, const DCol* arg, const DCol* mask);
+// evaluate groups [first, first+n) into device buffers described by `st` (already begun)
+void agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, int64_t* error_group, bool do_sync);
+int agg_n_intermediate(const pg_agg* agg);
+}  // namespace pg

@@ -1,0 +1,110 @@
+// context.cu — context lifetime, column import (host Blocks -> device-resident column buffers).
+#include "context.h"
+
+namespace pg {
+
+int64_t col_value_bytes(pg_ctx* ctx, const pg_col& c, int64_t n) {
+    if (!type_is_var(c.type)) return n * type_width(c.type);
+    if (n == 0) return 0;
+    PG_CHECK_ARG(c.offsets != nullptr, "variable width column without offsets");
+    int32_t last = 0, first = 0;
+    if (c.mem == PG_MEM_DEVICE) {
+        copy_async(ctx, ctx->h_scalar, c.offsets + n, 4, cudaMemcpyDeviceToHost);
+        copy_async(ctx, (char*)ctx->h_scalar + 8, c.offsets, 4, cudaMemcpyDeviceToHost);
+        sync(ctx);
+        memcpy(&last, ctx->h_scalar, 4);
+        memcpy(&first, (char*)ctx->h_scalar + 8, 4);
+    } else {
+        last = c.offsets[n]; first = c.offsets[0];
+    }
+    (void)first;
+    return last;  // offsets index into `values` from its start
+}
+
+void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
+    PG_CHECK_ARG(type_valid(c.type), "unknown column type %d", c.type);
+    PG_CHECK_ARG(n >= 0, "negative row count");
+    PG_CHECK_ARG(n == 0 || c.values != nullptr || type_is_var(c.type), "column without values");
+    out.n = n;
+    out.d.type = c.type; out.d.pad = 0;
+    out.value_bytes = col_value_bytes(ctx, c, n);
+    if (c.mem == PG_MEM_DEVICE) {
+        out.d.values = c.values; out.d.nulls = c.nulls; out.d.offsets = c.offsets;
+        return;
+    }
+    PG_CHECK_ARG(c.mem == PG_MEM_HOST, "bad mem kind %d", c.mem);
+    out.values.alloc(ctx, out.value_bytes > 0 ? out.value_bytes : 8);
+    copy_async(ctx, out.values.p, c.values, out.value_bytes, cudaMemcpyHostToDevice);
+    out.d.values = out.values.p;
+    out.d.nulls = nullptr; out.d.offsets = nullptr;
+    if (c.nulls) {
+        out.nulls.alloc(ctx, n > 0 ? n : 1);
+        copy_async(ctx, out.nulls.p, c.nulls, n, cudaMemcpyHostToDevice);
+        out.d.nulls = out.nulls.as<uint8_t>();
+    }
+    if (type_is_var(c.type)) {
+        out.offsets.alloc(ctx, (n + 1) * 4);
+        if (c.offsets) copy_async(ctx, out.offsets.p, c.offsets, (n + 1) * 4, cudaMemcpyHostToDevice);
+        else memset_async(ctx, out.offsets.p, 0, (n + 1) * 4);
+        out.d.offsets = out.offsets.as<int32_t>();
+    }
+}
+
+}  // namespace pg
+
+using namespace pg;
+
+extern "C" {
+
+int32_t pg_ctx_create(int32_t device, pg_ctx** out) {
+    if (!out) return PG_E_INVALID_ARGUMENT;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) { cudaGetLastError(); return PG_E_CUDA; }   // no CPU fallback: fail loudly
+    if (device < 0 || device >= count) return PG_E_INVALID_ARGUMENT;
+    pg_ctx* ctx = new pg_ctx();
+    ctx->device = device;
+    int32_t rc = guard(ctx, [&] {
+        cudaDeviceProp prop;
+        PG_CUDA(cudaGetDeviceProperties(&prop, device));
+        ctx->sm_count = prop.multiProcessorCount;
+        PG_CUDA(cudaMallocHost((void**)&ctx->h_scalar, 64 * sizeof(int64_t)));
+        // keep freed blocks cached in the default pool: per-page scratch is reused, not returned to the OS
+        cudaMemPool_t pool;
+        PG_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        uint64_t thresh = UINT64_MAX;
+        PG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+    });
+    if (rc != PG_OK) { delete ctx; return rc; }
+    *out = ctx;
+    return PG_OK;
+}
+
+int32_t pg_ctx_destroy(pg_ctx* ctx) {
+    if (!ctx) return PG_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
+    delete ctx;
+    return PG_OK;
+}
+
+const char* pg_last_error(pg_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int32_t pg_ctx_set_stream(pg_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    ctx->stream = (cudaStream_t)cuda_stream;
+    return PG_OK;
+}
+
+int32_t pg_ctx_synchronize(pg_ctx* ctx) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    return guard(ctx, [&] { sync(ctx); });
+}
+
+int64_t pg_ctx_launch_count(pg_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+const char* pg_version(void) { return "prestogpu 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,197 @@
+// context.h — pg_ctx: one device, one stream, stream-ordered device memory, error text, launch counter.
+#pragma once
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <exception>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+struct pg_ctx {
+    int device = 0;
+    cudaStream_t stream = 0;   // legacy default stream unless pg_ctx_set_stream() is called
+    int64_t launches = 0;      // kernels launched through PG_LAUNCH
+    int sm_count = 148;
+    std::string err;
+    // pinned host bounce buffer for small read-backs (flags, counters)
+    int64_t* h_scalar = nullptr;  // 64 x int64, pinned
+};
+
+namespace pg {
+
+struct Error : public std::exception {
+    int32_t code;
+    std::string msg;
+    Error(int32_t c, std::string m) : code(c), msg(std::move(m)) {}
+    const char* what() const noexcept override { return msg.c_str(); }
+};
+
+[[noreturn]] static inline void fail(int32_t code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    throw Error(code, buf);
+}
+
+#define PG_CUDA(expr)                                                                            \
+    do {                                                                                         \
+        cudaError_t _e = (expr);                                                                 \
+        if (_e != cudaSuccess) ::pg::fail(PG_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+#define PG_CHECK_ARG(cond, ...) do { if (!(cond)) ::pg::fail(PG_E_INVALID_ARGUMENT, __VA_ARGS__); } while (0)
+#define PG_CHECK_STATE(cond, ...) do { if (!(cond)) ::pg::fail(PG_E_ILLEGAL_STATE, __VA_ARGS__); } while (0)
+
+// kernel<<<grid, block, smem, ctx->stream>>>(...) with launch counting and error check
+#define PG_LAUNCH(ctx, kernel, grid, block, smem, ...)                                           \
+    do {                                                                                         \
+        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                         \
+        (ctx)->launches++;                                                                       \
+        PG_CUDA(cudaGetLastError());                                                             \
+    } while (0)
+
+// Wraps the body of every extern "C" entry point.
+template <typename F>
+static inline int32_t guard(pg_ctx* ctx, F&& f) {
+    try {
+        if (ctx) PG_CUDA(cudaSetDevice(ctx->device));
+        f();
+        return PG_OK;
+    } catch (const Error& e) {
+        if (ctx) ctx->err = e.msg;
+        return e.code;
+    } catch (const std::exception& e) {
+        if (ctx) ctx->err = e.what();
+        return PG_E_INTERNAL;
+    }
+}
+
+// Stream-ordered device buffer (cudaMallocAsync on the context stream).
+struct DevBuf {
+    pg_ctx* ctx = nullptr;
+    void* p = nullptr;
+    int64_t bytes = 0;
+    DevBuf() {}
+    DevBuf(pg_ctx* c, int64_t nbytes) { alloc(c, nbytes); }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept { ctx = o.ctx; p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        if (this != &o) { release(); ctx = o.ctx; p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+        return *this;
+    }
+    ~DevBuf() { release(); }
+    void alloc(pg_ctx* c, int64_t nbytes) {
+        release();
+        ctx = c; bytes = nbytes;
+        if (nbytes > 0) {
+            cudaError_t e = cudaMallocAsync(&p, (size_t)nbytes, c->stream);
+            if (e != cudaSuccess) {
+                p = nullptr; bytes = 0; cudaGetLastError();
+                fail(PG_E_INSUFFICIENT_RESOURCES, "device allocation of %lld bytes failed: %s", (long long)nbytes, cudaGetErrorString(e));
+            }
+        }
+    }
+    void release() {
+        if (p) { cudaFreeAsync(p, ctx->stream); p = nullptr; bytes = 0; }
+    }
+    // grow to at least nbytes keeping the first keep_bytes
+    void grow(pg_ctx* c, int64_t nbytes, int64_t keep_bytes) {
+        if (nbytes <= bytes) return;
+        DevBuf n(c, nbytes);
+        if (p && keep_bytes > 0) PG_CUDA(cudaMemcpyAsync(n.p, p, (size_t)keep_bytes, cudaMemcpyDeviceToDevice, c->stream));
+        *this = std::move(n);
+    }
+    template <typename T> T* as() const { return (T*)p; }
+};
+
+static inline void memset_async(pg_ctx* ctx, void* p, int v, int64_t bytes) {
+    if (bytes > 0) PG_CUDA(cudaMemsetAsync(p, v, (size_t)bytes, ctx->stream));
+}
+static inline void copy_async(pg_ctx* ctx, void* dst, const void* src, int64_t bytes, cudaMemcpyKind kind) {
+    if (bytes > 0) PG_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, kind, ctx->stream));
+}
+static inline void sync(pg_ctx* ctx) { PG_CUDA(cudaStreamSynchronize(ctx->stream)); }
+
+// read back up to 64 int64 scalars from device memory (synchronises the stream)
+static inline void read_scalars(pg_ctx* ctx, const void* d, int n, int64_t* out) {
+    copy_async(ctx, ctx->h_scalar, d, (int64_t)n * 8, cudaMemcpyDeviceToHost);
+    sync(ctx);
+    for (int i = 0; i < n; i++) out[i] = ctx->h_scalar[i];
+}
+
+// A pg_col imported for the duration of one call: host columns are staged to the device, device columns
+// are used in place.
+struct ColImport {
+    DCol d;
+    DevBuf values, nulls, offsets;
+    int64_t n = 0;
+    int64_t value_bytes = 0;
+};
+void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out);
+// bytes of the value buffer of column c with n rows (reads the last offset for variable width columns)
+int64_t col_value_bytes(pg_ctx* ctx, const pg_col& c, int64_t n);
+
+// Output column staging: kernels always write device memory; host outputs are copied back in finish().
+struct OutStage {
+    pg_ctx* ctx = nullptr;
+    pg_col_out* o = nullptr;
+    void* d_values = nullptr;
+    uint8_t* d_nulls = nullptr;
+    int32_t* d_offsets = nullptr;
+    DevBuf bv, bn, bo;
+    int64_t n = 0;
+    void begin(pg_ctx* c, pg_col_out* out, int64_t rows, int64_t value_bytes) {
+        ctx = c; o = out; n = rows;
+        PG_CHECK_ARG(out != nullptr, "missing output column");
+        PG_CHECK_ARG(out->capacity >= rows, "output column capacity %lld < %lld rows", (long long)out->capacity, (long long)rows);
+        bool var = type_is_var(out->type);
+        if (var) PG_CHECK_ARG(out->offsets != nullptr && out->values_capacity_bytes >= value_bytes,
+                              "variable width output needs offsets and %lld value bytes", (long long)value_bytes);
+        if (out->mem == PG_MEM_DEVICE) {
+            d_values = out->values; d_nulls = out->nulls; d_offsets = out->offsets;
+        } else {
+            bv.alloc(c, value_bytes > 0 ? value_bytes : 8); d_values = bv.p;
+            if (out->nulls) { bn.alloc(c, rows > 0 ? rows : 1); d_nulls = bn.as<uint8_t>(); }
+            if (var) { bo.alloc(c, (rows + 1) * 4); d_offsets = bo.as<int32_t>(); }
+        }
+    }
+    void finish(int64_t value_bytes) {
+        if (o->mem == PG_MEM_DEVICE) return;
+        copy_async(ctx, o->values, d_values, value_bytes, cudaMemcpyDeviceToHost);
+        if (o->nulls) copy_async(ctx, o->nulls, d_nulls, n, cudaMemcpyDeviceToHost);
+        if (type_is_var(o->type)) copy_async(ctx, o->offsets, d_offsets, (n + 1) * 4, cudaMemcpyDeviceToHost);
+    }
+};
+
+// int32/int64/uint8 result vectors that may live on the host or the device
+template <typename T>
+struct OutVec {
+    pg_ctx* ctx = nullptr;
+    T* user = nullptr;
+    int32_t mem = PG_MEM_DEVICE;
+    T* d = nullptr;
+    DevBuf tmp;
+    int64_t n = 0;
+    void begin(pg_ctx* c, T* out, int32_t out_mem, int64_t count) {
+        ctx = c; user = out; mem = out_mem; n = count;
+        if (!out) { d = nullptr; return; }
+        if (out_mem == PG_MEM_DEVICE) d = out;
+        else { tmp.alloc(c, (count > 0 ? count : 1) * (int64_t)sizeof(T)); d = tmp.as<T>(); }
+    }
+    void finish(int64_t count = -1) {
+        if (user && mem != PG_MEM_DEVICE) copy_async(ctx, user, d, (count < 0 ? n : count) * (int64_t)sizeof(T), cudaMemcpyDeviceToHost);
+    }
+};
+
+static inline int grid_for(pg_ctx* ctx, int64_t n, int block, int per_thread = 1, int max_waves = 8) {
+    int64_t g = (n + (int64_t)block * per_thread - 1) / ((int64_t)block * per_thread);
+    int64_t cap = (int64_t)ctx->sm_count * max_waves * (2048 / block);
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+}  // namespace pg

@@ -1,0 +1,859 @@
+// groupby.cu — GroupByHash kernels and host logic.  See groupby.h for the HBM layout.
+#include "groupby.h"
+
+namespace pg {
+
+static const int GB_THREADS = 256;
+
+// ------------------------------------------------------------------ key helpers (multi-channel mode)
+PG_D int64_t keys_row_hash(const KeyCols& kc, int nkeys, int64_t i) {
+    uint64_t h = 0;  // INITIAL_HASH_VALUE (HashGenerationOptimizer.java:98)
+    for (int k = 0; k < nkeys; k++) h = 31 * h + (uint64_t)dcol_type_hash(kc.c[k], i);
+    return (int64_t)h;
+}
+
+PG_D bool double_not_distinct(int64_t a, int64_t b) {  // SPI/type/DoubleType.java:181-192
+    if (bits_is_nan(a) && bits_is_nan(b)) return true;
+    return __longlong_as_double(a) == __longlong_as_double(b);
+}
+
+// IS NOT DISTINCT FROM between input rows i and j (same page)
+PG_D bool keys_equal_rows(const KeyCols& kc, const KeyLayout& L, int64_t i, int64_t j) {
+    for (int k = 0; k < L.nkeys; k++) {
+        const DCol& c = kc.c[k];
+        bool ni = dcol_is_null(c, i), nj = dcol_is_null(c, j);
+        if (ni || nj) { if (ni != nj) return false; continue; }
+        switch (c.type) {
+            case PG_VARCHAR: case PG_VARBINARY: {
+                int32_t oi = c.offsets[i], li = c.offsets[i + 1] - oi, oj = c.offsets[j], lj = c.offsets[j + 1] - oj;
+                if (li != lj) return false;
+                const uint8_t* b = (const uint8_t*)c.values;
+                for (int32_t t = 0; t < li; t++) if (b[oi + t] != b[oj + t]) return false;
+                break;
+            }
+            case PG_LONG_DECIMAL: {
+                const int64_t* p = (const int64_t*)c.values;
+                if (p[2 * i] != p[2 * j] || p[2 * i + 1] != p[2 * j + 1]) return false;
+                break;
+            }
+            case PG_DOUBLE:
+                if (!double_not_distinct(dcol_long(c, i), dcol_long(c, j))) return false;
+                break;
+            default:
+                if (dcol_long(c, i) != dcol_long(c, j)) return false;
+        }
+    }
+    return true;
+}
+
+// IS NOT DISTINCT FROM between input row i and the stored key row of group g
+PG_D bool keys_equal_store(const KeyCols& kc, const KeyLayout& L, int64_t i, const uint64_t* key_rows, const uint8_t* arena,
+                           int64_t g) {
+    const uint64_t* row = key_rows + g * L.row_words;
+    uint64_t nullbits = row[0];
+    for (int k = 0; k < L.nkeys; k++) {
+        const DCol& c = kc.c[k];
+        bool ni = dcol_is_null(c, i), ng = (nullbits >> k) & 1;
+        if (ni || ng) { if (ni != ng) return false; continue; }
+        const uint64_t* w = row + L.word_off[k];
+        switch (c.type) {
+            case PG_VARCHAR: case PG_VARBINARY: {
+                int32_t oi = c.offsets[i], li = c.offsets[i + 1] - oi;
+                int64_t og = (int64_t)(w[0] >> 24); int32_t lg = (int32_t)(w[0] & 0xFFFFFF);
+                if (li != lg) return false;
+                const uint8_t* b = (const uint8_t*)c.values;
+                for (int32_t t = 0; t < li; t++) if (b[oi + t] != arena[og + t]) return false;
+                break;
+            }
+            case PG_LONG_DECIMAL: {
+                const uint64_t* p = (const uint64_t*)c.values;
+                if (p[2 * i] != w[0] || p[2 * i + 1] != w[1]) return false;
+                break;
+            }
+            case PG_DOUBLE:
+                if (!double_not_distinct(dcol_long(c, i), (int64_t)w[0])) return false;
+                break;
+            default:
+                if (dcol_long(c, i) != (int64_t)w[0]) return false;
+        }
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ table init / rebuild
+__global__ void gb_init_slots_kernel(Slot* slots, int64_t nslots, unsigned long long empty) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < nslots; i += stride) {
+        // one 16-byte store per slot
+        int4 v;
+        v.x = (int)(empty & 0xffffffffu); v.y = (int)(empty >> 32); v.z = -1; v.w = 0x7fffffff;
+        ((int4*)slots)[i] = v;
+    }
+}
+
+// re-insert every assigned group into a fresh table (BigintGroupByHash.tryRehash :287-303 walks valuesByGroupId
+// the same way; MultiChannelGroupByHash.tryRehash :384-404 walks the old slots)
+__global__ void gb_rebuild_bigint_kernel(Slot* slots, int64_t mask, const int64_t* values_by_group, int64_t groups,
+                                         const Slot* old_special) {
+    const int32_t magic_gid = old_special[0].gid, null_gid = old_special[1].gid;
+    int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; g < groups; g += stride) {
+        if (g == null_gid || g == magic_gid) continue;
+        unsigned long long key = (unsigned long long)values_by_group[g];
+        int64_t p = (int64_t)(fmix64(key) & (uint64_t)mask);
+        while (true) {
+            unsigned long long old = atomicCAS(&slots[p].word, EMPTY_KEY, key);
+            if (old == EMPTY_KEY) { slots[p].gid = (int32_t)g; break; }
+            p = (p + 1) & mask;
+        }
+    }
+}
+__global__ void gb_rebuild_multi_kernel(Slot* slots, int64_t mask, const int64_t* hash_by_group, int64_t groups) {
+    int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; g < groups; g += stride) {
+        uint64_t f = fmix64((uint64_t)hash_by_group[g]);
+        unsigned long long word = (f & 0xFFFFFFFF00000000ULL) | (unsigned long long)(uint32_t)g;
+        int64_t p = (int64_t)(f & (uint64_t)mask);
+        while (true) {
+            unsigned long long old = atomicCAS(&slots[p].word, EMPTY_WORD, word);
+            if (old == EMPTY_WORD) { slots[p].gid = (int32_t)g; break; }
+            p = (p + 1) & mask;
+        }
+    }
+}
+// carry the two special slots (magic key, null group) of bigint mode across a rebuild; pending ones are reset
+__global__ void gb_copy_special_kernel(Slot* dst, int64_t dst_cap, const Slot* src, int64_t src_cap) {
+    int t = threadIdx.x;
+    if (t < 2) {
+        Slot s = src[src_cap + t];
+        if (s.gid < 0) s.first_row = 0x7fffffff;
+        dst[dst_cap + t] = s;
+    }
+}
+
+// ------------------------------------------------------------------ K1: insert
+// Each row finds or claims its slot; pending slots get first_row = min(row).  row_slot[row] = slot index.
+// A block stops claiming when it has used its quota (the host then rebuilds a larger table and redoes the chunk).
+struct InsertArgs {
+    Slot* slots;
+    int64_t cap;
+    int64_t mask;
+    int32_t* row_slot;
+    GbMeta* meta;
+    int64_t n;
+    int64_t quota;   // max new slots per block
+    const uint64_t* key_rows;
+    const uint8_t* arena;
+};
+
+template <bool BIGINT>
+__global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, KeyCols kc, KeyLayout L, DCol hash_col, int has_hash) {
+    __shared__ int s_inserted;
+    __shared__ int s_stop;
+    if (threadIdx.x == 0) { s_inserted = 0; s_stop = 0; }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int iter = 0;
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < a.n; base += stride, iter++) {
+        // warp-uniform stop test (no block barrier inside the loop: warps of a block run independently)
+        int stop = 0;
+        if (lane == 0) {
+            stop = *((volatile int*)&s_stop);
+            if (!stop && (iter & 7) == 7) stop = *((volatile int32_t*)&a.meta->abort);
+        }
+        stop = __shfl_sync(0xffffffffu, stop, 0);
+        if (stop) break;
+        int64_t row = base + threadIdx.x;
+        bool valid = row < a.n;
+        bool claimed = false;
+        if (valid) {
+            int64_t s;
+            if (BIGINT) {
+                const DCol& c = kc.c[0];
+                if (dcol_is_null(c, row)) s = a.cap + 1;
+                else {
+                    unsigned long long key = (unsigned long long)((const int64_t*)c.values)[row];
+                    if (key == EMPTY_KEY) s = a.cap;
+                    else {
+                        int64_t p = (int64_t)(fmix64(key) & (uint64_t)a.mask);
+                        while (true) {
+                            unsigned long long k = *((volatile unsigned long long*)&a.slots[p].word);
+                            if (k == key) break;
+                            if (k == EMPTY_KEY) {
+                                unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_KEY, key);
+                                if (old == EMPTY_KEY) { claimed = true; break; }
+                                if (old == key) break;
+                            }
+                            p = (p + 1) & a.mask;
+                        }
+                        s = p;
+                    }
+                }
+            } else {
+                int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
+                uint64_t f = fmix64((uint64_t)raw);
+                uint32_t tag = (uint32_t)(f >> 32);
+                unsigned long long mine = ((unsigned long long)tag << 32) | (unsigned long long)(REF_PENDING | (uint32_t)row);
+                int64_t p = (int64_t)(f & (uint64_t)a.mask);
+                while (true) {
+                    unsigned long long w = *((volatile unsigned long long*)&a.slots[p].word);
+                    if (w == EMPTY_WORD) {
+                        unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_WORD, mine);
+                        if (old == EMPTY_WORD) { claimed = true; break; }
+                        w = old;
+                    }
+                    if ((uint32_t)(w >> 32) == tag) {
+                        uint32_t ref = (uint32_t)w;
+                        bool eq = (ref & REF_PENDING) ? keys_equal_rows(kc, L, row, (int64_t)(ref & ~REF_PENDING))
+                                                      : keys_equal_store(kc, L, row, a.key_rows, a.arena, (int64_t)ref);
+                        if (eq) break;
+                    }
+                    p = (p + 1) & a.mask;
+                }
+                s = p;
+            }
+            if (*((volatile int32_t*)&a.slots[s].gid) < 0) atomicMin(&a.slots[s].first_row, (int32_t)row);
+            a.row_slot[row] = (int32_t)s;
+        }
+        unsigned b = __ballot_sync(0xffffffffu, claimed);
+        if (lane == 0 && b) {
+            int before = atomicAdd(&s_inserted, __popc(b));
+            if ((int64_t)before + __popc(b) >= a.quota) *((volatile int*)&s_stop) = 1;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (s_inserted) atomicAdd((unsigned long long*)&a.meta->inserted, (unsigned long long)s_inserted);
+        // stopping before the last row means the chunk is incomplete
+        if (s_stop) a.meta->abort = 1;   // (a block that stops on its very last row also reports abort: harmless redo)
+    }
+}
+
+// ------------------------------------------------------------------ K2: first-seen group-id assignment
+// A row is the representative of a new group iff its slot is still pending and it is the slot's first_row.
+PG_D bool row_is_new_group(const Slot* slots, const int32_t* row_slot, int64_t row, int32_t* slot_out) {
+    int32_t s = row_slot[row];
+    *slot_out = s;
+    const Slot& sl = slots[s];
+    return sl.gid < 0 && sl.first_row == (int32_t)row;
+}
+PG_D int64_t row_var_bytes(const KeyCols& kc, const KeyLayout& L, int64_t row) {
+    int64_t b = 0;
+    for (int k = 0; k < L.nkeys; k++) {
+        const DCol& c = kc.c[k];
+        if ((c.type == PG_VARCHAR || c.type == PG_VARBINARY) && !dcol_is_null(c, row)) b += c.offsets[row + 1] - c.offsets[row];
+    }
+    return b;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) gb_count_new_kernel(const Slot* slots, const int32_t* row_slot, int64_t n,
+                                                                    KeyCols kc, KeyLayout L, int has_var, Pair64* tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 acc{0, 0};
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t row = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (row < n) {
+            int32_t s;
+            if (row_is_new_group(slots, row_slot, row, &s)) {
+                acc.a += 1;
+                if (has_var) acc.b += row_var_bytes(kc, L, row);
+            }
+        }
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+struct AssignArgs {
+    Slot* slots;
+    int64_t cap;
+    const int32_t* row_slot;
+    int64_t n;
+    const Pair64* tile_prefix;   // exclusive prefix per tile
+    const GbMeta* meta;          // group_count / arena_bytes before this chunk
+    int64_t* values_by_group;    // bigint mode
+    uint64_t* key_rows;          // multi mode
+    int64_t* hash_by_group;
+    uint8_t* arena;
+};
+
+template <bool BIGINT>
+__global__ void __launch_bounds__(SCAN_THREADS) gb_assign_kernel(AssignArgs a, KeyCols kc, KeyLayout L, DCol hash_col, int has_hash,
+                                                                 int has_var) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 run = a.tile_prefix[blockIdx.x];
+    run.a += a.meta->group_count;
+    run.b += a.meta->arena_bytes;
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t row = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        int32_t s = 0;
+        Pair64 v{0, 0};
+        if (row < a.n && row_is_new_group(a.slots, a.row_slot, row, &s)) {
+            v.a = 1;
+            if (has_var) v.b = row_var_bytes(kc, L, row);
+        }
+        Pair64 total;
+        Pair64 ex = block_exclusive_scan(v, smem, &total);
+        if (v.a) {
+            int64_t gid = run.a + ex.a;
+            if (BIGINT) {
+                int64_t key = 0;
+                if (s == a.cap) key = (int64_t)EMPTY_KEY;
+                else if (s < a.cap) key = ((const int64_t*)kc.c[0].values)[row];
+                a.values_by_group[gid] = key;
+            } else {
+                uint64_t* out = a.key_rows + gid * L.row_words;
+                int64_t boff = run.b + ex.b;
+                uint64_t nullbits = 0;
+                for (int k = 0; k < L.nkeys; k++) {
+                    const DCol& c = kc.c[k];
+                    uint64_t* w = out + L.word_off[k];
+                    if (dcol_is_null(c, row)) {
+                        nullbits |= 1ULL << k;
+                        w[0] = 0;
+                        if (c.type == PG_LONG_DECIMAL) w[1] = 0;
+                        if (c.type == PG_VARCHAR || c.type == PG_VARBINARY) w[0] = (uint64_t)boff << 24;
+                        continue;
+                    }
+                    switch (c.type) {
+                        case PG_VARCHAR: case PG_VARBINARY: {
+                            int32_t o = c.offsets[row], len = c.offsets[row + 1] - o;
+                            const uint8_t* b = (const uint8_t*)c.values;
+                            for (int32_t t = 0; t < len; t++) a.arena[boff + t] = b[o + t];
+                            w[0] = ((uint64_t)boff << 24) | (uint64_t)(uint32_t)len;
+                            boff += len;
+                            break;
+                        }
+                        case PG_LONG_DECIMAL: {
+                            const uint64_t* p = (const uint64_t*)c.values;
+                            w[0] = p[2 * row]; w[1] = p[2 * row + 1];
+                            break;
+                        }
+                        default: w[0] = (uint64_t)dcol_long(c, row);
+                    }
+                }
+                out[0] = nullbits;
+                int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
+                a.hash_by_group[gid] = raw;
+                unsigned long long tagw = a.slots[s].word & 0xFFFFFFFF00000000ULL;
+                a.slots[s].word = tagw | (unsigned long long)(uint32_t)gid;
+            }
+            a.slots[s].gid = (int32_t)gid;
+        }
+        run = run + total;
+    }
+}
+
+__global__ void gb_commit_kernel(GbMeta* meta) {
+    meta->group_count += meta->chunk_total.a;
+    meta->arena_bytes += meta->chunk_total.b;
+}
+
+// K3: per-row group id (GroupByIdBlock)
+__global__ void gb_lookup_ids_kernel(const Slot* slots, const int32_t* row_slot, int64_t n, int32_t* out_ids) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out_ids[i] = slots[row_slot[i]].gid;
+}
+
+// ------------------------------------------------------------------ contains (read-only probe)
+template <bool BIGINT>
+__global__ void gb_contains_kernel(const Slot* slots, int64_t cap, int64_t mask, const uint64_t* key_rows, const uint8_t* arena,
+                                   KeyCols kc, KeyLayout L, DCol hash_col, int has_hash, int64_t n, uint8_t* out) {
+    int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; row < n; row += stride) {
+        bool found = false;
+        if (BIGINT) {
+            const DCol& c = kc.c[0];
+            if (dcol_is_null(c, row)) found = slots[cap + 1].gid >= 0;
+            else {
+                unsigned long long key = (unsigned long long)((const int64_t*)c.values)[row];
+                if (key == EMPTY_KEY) found = slots[cap].gid >= 0;
+                else {
+                    int64_t p = (int64_t)(fmix64(key) & (uint64_t)mask);
+                    while (true) {
+                        unsigned long long k = slots[p].word;
+                        if (k == key) { found = slots[p].gid >= 0; break; }
+                        if (k == EMPTY_KEY) break;
+                        p = (p + 1) & mask;
+                    }
+                }
+            }
+        } else {
+            int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
+            uint64_t f = fmix64((uint64_t)raw);
+            uint32_t tag = (uint32_t)(f >> 32);
+            int64_t p = (int64_t)(f & (uint64_t)mask);
+            while (true) {
+                unsigned long long w = slots[p].word;
+                if (w == EMPTY_WORD) break;
+                uint32_t ref = (uint32_t)w;
+                if ((uint32_t)(w >> 32) == tag && !(ref & REF_PENDING) && keys_equal_store(kc, L, row, key_rows, arena, (int64_t)ref)) {
+                    found = true; break;
+                }
+                p = (p + 1) & mask;
+            }
+        }
+        out[row] = found ? 1 : 0;
+    }
+}
+
+// ------------------------------------------------------------------ export (appendValuesTo / getRawHash)
+__global__ void gb_export_bigint_kernel(const int64_t* values_by_group, const Slot* special, int64_t first, int64_t n,
+                                        int64_t* out_values, uint8_t* out_nulls, int64_t* out_hash) {
+    const int32_t null_gid = special[1].gid;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        int64_t g = first + i;
+        bool isnull = g == null_gid;
+        int64_t v = isnull ? 0 : values_by_group[g];
+        if (out_values) out_values[i] = v;
+        if (out_nulls) out_nulls[i] = isnull ? 1 : 0;
+        if (out_hash) out_hash[i] = isnull ? 0 : long_type_hash(v);   // BigintGroupByHash.getRawHash :200-203
+    }
+}
+
+__global__ void gb_export_fixed_kernel(const uint64_t* key_rows, KeyLayout L, int k, int64_t first, int64_t n, void* out_values,
+                                       uint8_t* out_nulls) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int type = L.types[k];
+    for (; i < n; i += stride) {
+        const uint64_t* row = key_rows + (first + i) * L.row_words;
+        const uint64_t* w = row + L.word_off[k];
+        if (out_nulls) out_nulls[i] = (row[0] >> k) & 1;
+        switch (type) {
+            case PG_INTEGER: case PG_DATE: ((int32_t*)out_values)[i] = (int32_t)w[0]; break;
+            case PG_BOOLEAN: ((uint8_t*)out_values)[i] = (uint8_t)w[0]; break;
+            case PG_LONG_DECIMAL: ((uint64_t*)out_values)[2 * i] = w[0]; ((uint64_t*)out_values)[2 * i + 1] = w[1]; break;
+            default: ((uint64_t*)out_values)[i] = w[0];
+        }
+    }
+}
+__global__ void gb_export_hash_kernel(const int64_t* hash_by_group, int64_t first, int64_t n, int64_t* out_hash) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out_hash[i] = hash_by_group[first + i];
+}
+
+PG_D int64_t group_var_len(const uint64_t* key_rows, const KeyLayout& L, int k, int64_t g) {
+    const uint64_t* row = key_rows + g * L.row_words;
+    if ((row[0] >> k) & 1) return 0;
+    return (int64_t)(row[L.word_off[k]] & 0xFFFFFF);
+}
+__global__ void __launch_bounds__(SCAN_THREADS) gb_export_var_count_kernel(const uint64_t* key_rows, KeyLayout L, int k, int64_t first,
+                                                                           int64_t n, Pair64* tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 acc{0, 0};
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (i < n) acc.a += group_var_len(key_rows, L, k, first + i);
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) gb_export_var_kernel(const uint64_t* key_rows, const uint8_t* arena, KeyLayout L, int k,
+                                                                     int64_t first, int64_t n, const Pair64* tile_prefix,
+                                                                     uint8_t* out_bytes, int32_t* out_offsets, uint8_t* out_nulls) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 run = tile_prefix[blockIdx.x];
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        Pair64 v{0, 0};
+        if (i < n) v.a = group_var_len(key_rows, L, k, first + i);
+        Pair64 total;
+        Pair64 ex = block_exclusive_scan(v, smem, &total);
+        if (i < n) {
+            const uint64_t* row = key_rows + (first + i) * L.row_words;
+            int64_t src = (int64_t)(row[L.word_off[k]] >> 24);
+            int64_t dst = run.a + ex.a;
+            out_offsets[i] = (int32_t)dst;
+            if (i == n - 1) out_offsets[n] = (int32_t)(dst + v.a);
+            if (out_nulls) out_nulls[i] = (row[0] >> k) & 1;
+            for (int64_t t = 0; t < v.a; t++) out_bytes[dst + t] = arena[src + t];
+        }
+        run = run + total;
+    }
+}
+__global__ void gb_sum_var_bytes_kernel(const uint64_t* key_rows, KeyLayout L, int k, int64_t groups, unsigned long long* out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned long long acc = 0;
+    for (; i < groups; i += stride) acc += (unsigned long long)group_var_len(key_rows, L, k, i);
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
+// ------------------------------------------------------------------ host logic
+static const int64_t MIN_PHYS_CAP = 1LL << 20;
+
+static void alloc_table(pg_groupby* gb, int64_t cap, DevBuf& slots) {
+    pg_ctx* ctx = gb->ctx;
+    slots.alloc(ctx, (cap + 2) * (int64_t)sizeof(Slot));
+    int grid = grid_for(ctx, cap + 2, 256, 4);
+    PG_LAUNCH(ctx, gb_init_slots_kernel, grid, 256, 0, slots.as<Slot>(), cap + 2, gb->bigint_mode ? EMPTY_KEY : EMPTY_WORD);
+}
+
+static void ensure_group_storage(pg_groupby* gb) {
+    pg_ctx* ctx = gb->ctx;
+    int64_t need = gb->max_fill + 2 + 256 * 1024;   // slack: blocks may overshoot their quota by one iteration
+    if (gb->bigint_mode) gb->values_by_group.grow(ctx, need * 8, gb->groups * 8);
+    else {
+        gb->key_rows.grow(ctx, need * gb->layout.row_words * 8, gb->groups * gb->layout.row_words * 8);
+        gb->hash_by_group.grow(ctx, need * 8, gb->groups * 8);
+    }
+}
+
+// replace the table by one with new_cap slots, re-inserting the assigned groups (pending claims are dropped)
+static void rebuild_table(pg_groupby* gb, int64_t new_cap) {
+    pg_ctx* ctx = gb->ctx;
+    if (new_cap > (1LL << 30)) fail(PG_E_INSUFFICIENT_RESOURCES, "Size of hash table cannot exceed 1 billion entries");
+    DevBuf fresh;
+    alloc_table(gb, new_cap, fresh);
+    if (gb->slots.p) {
+        if (gb->groups > 0) {
+            int grid = grid_for(ctx, gb->groups, 256);
+            if (gb->bigint_mode)
+                PG_LAUNCH(ctx, gb_rebuild_bigint_kernel, grid, 256, 0, fresh.as<Slot>(), new_cap - 1, gb->values_by_group.as<int64_t>(),
+                          gb->groups, gb->slots.as<Slot>() + gb->cap);
+            else
+                PG_LAUNCH(ctx, gb_rebuild_multi_kernel, grid, 256, 0, fresh.as<Slot>(), new_cap - 1, gb->hash_by_group.as<int64_t>(),
+                          gb->groups);
+        }
+        PG_LAUNCH(ctx, gb_copy_special_kernel, 1, 32, 0, fresh.as<Slot>(), new_cap, gb->slots.as<Slot>(), gb->cap);
+        gb->rehashes++;
+    }
+    gb->slots = std::move(fresh);
+    gb->cap = new_cap;
+    gb->max_fill = max_fill_075(new_cap);
+    gb->occupied = gb->groups;   // special slots are not counted against the fill
+    ensure_group_storage(gb);
+}
+
+void groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys, int32_t has_hash_channel, int64_t expected,
+                    pg_groupby** out) {
+    PG_CHECK_ARG(out != nullptr && key_types != nullptr, "null argument");
+    PG_CHECK_ARG(nkeys >= 1 && nkeys <= MAX_KEYS, "between 1 and %d group-by channels are supported, got %d", MAX_KEYS, nkeys);
+    PG_CHECK_ARG(expected > 0, "expectedSize must be greater than zero");   // BigintGroupByHash.java:82
+    for (int k = 0; k < nkeys; k++) PG_CHECK_ARG(type_valid(key_types[k]), "unknown key type %d", key_types[k]);
+    pg_groupby* gb = new pg_groupby();
+    try {
+        gb->ctx = ctx;
+        gb->bigint_mode = (nkeys == 1 && key_types[0] == PG_BIGINT);   // GroupByHash.createGroupByHash :45-59
+        gb->has_hash_channel = has_hash_channel != 0;
+        gb->expected = expected;
+        KeyLayout& L = gb->layout;
+        memset(&L, 0, sizeof(L));
+        L.nkeys = nkeys;
+        int w = 1;
+        for (int k = 0; k < nkeys; k++) {
+            L.types[k] = key_types[k];
+            L.word_off[k] = w;
+            w += key_types[k] == PG_LONG_DECIMAL ? 2 : 1;
+            if (type_is_var(key_types[k])) gb->has_var = true;
+        }
+        L.row_words = w;
+        gb->ref_capacity = array_size_075(expected);
+        gb->meta.alloc(ctx, sizeof(GbMeta));
+        memset_async(ctx, gb->meta.p, 0, sizeof(GbMeta));
+        int64_t cap = gb->ref_capacity < MIN_PHYS_CAP ? MIN_PHYS_CAP : gb->ref_capacity;
+        rebuild_table(gb, cap);
+        if (gb->has_var) gb->arena.alloc(ctx, 1 << 20);
+    } catch (...) {
+        delete gb;
+        throw;
+    }
+    *out = gb;
+}
+
+int64_t groupby_device_bytes(const pg_groupby* gb) {
+    return gb->slots.bytes + gb->values_by_group.bytes + gb->key_rows.bytes + gb->hash_by_group.bytes + gb->arena.bytes +
+           gb->row_slot.bytes + gb->tile_sums.bytes + gb->meta.bytes;
+}
+
+static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_col, int64_t n, int32_t* d_out_ids) {
+    pg_ctx* ctx = gb->ctx;
+    if (n <= 0) return;
+    const KeyLayout& L = gb->layout;
+    DCol hc; memset(&hc, 0, sizeof(hc));
+    int has_hash = 0;
+    if (!gb->bigint_mode && hash_col) { hc = *hash_col; has_hash = 1; }
+    gb->row_slot.grow(ctx, n * 4, 0);
+    int64_t ntiles = num_tiles(n);
+    gb->tile_sums.grow(ctx, ntiles * (int64_t)sizeof(Pair64), 0);
+    GbMeta* meta = gb->meta.as<GbMeta>();
+
+    // ---- K1 with quota / rebuild loop
+    const int grid = grid_for(ctx, n, GB_THREADS);
+    while (true) {
+        int64_t room = gb->max_fill - gb->occupied;
+        int64_t quota;
+        if (room >= n) quota = INT64_MAX / 2;
+        else {
+            quota = room / grid - GB_THREADS;
+            if (quota < 32) { rebuild_table(gb, gb->cap * 2); continue; }
+        }
+        memset_async(ctx, &meta->inserted, 0, 8);
+        memset_async(ctx, &meta->abort, 0, 4);
+        InsertArgs a;
+        a.slots = gb->slots.as<Slot>(); a.cap = gb->cap; a.mask = gb->cap - 1; a.row_slot = gb->row_slot.as<int32_t>();
+        a.meta = meta; a.n = n; a.quota = quota; a.key_rows = gb->key_rows.as<uint64_t>(); a.arena = gb->arena.as<uint8_t>();
+        if (gb->bigint_mode) PG_LAUNCH(ctx, gb_insert_kernel<true>, grid, GB_THREADS, 0, a, kc, L, hc, has_hash);
+        else PG_LAUNCH(ctx, gb_insert_kernel<false>, grid, GB_THREADS, 0, a, kc, L, hc, has_hash);
+        // one read-back: {inserted, abort}
+        copy_async(ctx, ctx->h_scalar, &meta->inserted, 8, cudaMemcpyDeviceToHost);
+        copy_async(ctx, ctx->h_scalar + 1, &meta->abort, 4, cudaMemcpyDeviceToHost);
+        sync(ctx);
+        int64_t inserted = ctx->h_scalar[0];
+        int32_t aborted; memcpy(&aborted, ctx->h_scalar + 1, 4);
+        gb->occupied += inserted;
+        if (!aborted) break;
+        rebuild_table(gb, gb->cap * 2);   // drops this chunk's pending claims; the chunk is redone
+    }
+
+    // ---- K2: flag new groups, scan, assign ids in first-seen order
+    PG_LAUNCH(ctx, gb_count_new_kernel, (int)ntiles, SCAN_THREADS, 0, gb->slots.as<Slot>(), gb->row_slot.as<int32_t>(), n, kc, L,
+              gb->has_var ? 1 : 0, gb->tile_sums.as<Pair64>());
+    scan_tile_totals(ctx, gb->tile_sums.as<Pair64>(), ntiles, &meta->chunk_total);
+    if (gb->has_var) {
+        int64_t tot[2];
+        read_scalars(ctx, &meta->chunk_total, 2, tot);
+        int64_t need = gb->arena_used + tot[1];
+        if (need > gb->arena.bytes) gb->arena.grow(ctx, need * 2, gb->arena_used);
+        gb->arena_used = need;
+    }
+    AssignArgs as;
+    as.slots = gb->slots.as<Slot>(); as.cap = gb->cap; as.row_slot = gb->row_slot.as<int32_t>(); as.n = n;
+    as.tile_prefix = gb->tile_sums.as<Pair64>(); as.meta = meta; as.values_by_group = gb->values_by_group.as<int64_t>();
+    as.key_rows = gb->key_rows.as<uint64_t>(); as.hash_by_group = gb->hash_by_group.as<int64_t>(); as.arena = gb->arena.as<uint8_t>();
+    if (gb->bigint_mode) PG_LAUNCH(ctx, gb_assign_kernel<true>, (int)ntiles, SCAN_THREADS, 0, as, kc, L, hc, has_hash, 0);
+    else PG_LAUNCH(ctx, gb_assign_kernel<false>, (int)ntiles, SCAN_THREADS, 0, as, kc, L, hc, has_hash, gb->has_var ? 1 : 0);
+    PG_LAUNCH(ctx, gb_commit_kernel, 1, 1, 0, meta);
+
+    // ---- K3
+    if (d_out_ids) {
+        int g3 = grid_for(ctx, n, 256, 4);
+        PG_LAUNCH(ctx, gb_lookup_ids_kernel, g3, 256, 0, gb->slots.as<Slot>(), gb->row_slot.as<int32_t>(), n, d_out_ids);
+    }
+    int64_t gc;
+    read_scalars(ctx, &meta->group_count, 1, &gc);
+    gb->groups = gc;
+}
+
+static KeyCols offset_keys(const KeyCols& kc, const KeyLayout& L, int64_t off) {
+    KeyCols r = kc;
+    for (int k = 0; k < L.nkeys; k++) {
+        DCol& c = r.c[k];
+        if (c.nulls) c.nulls += off;
+        if (type_is_var(c.type)) c.offsets += off;
+        else c.values = (const char*)c.values + off * type_width(c.type);
+    }
+    return r;
+}
+
+void groupby_process(pg_groupby* gb, const KeyCols& keys, const DCol* hash_col, int64_t n, int32_t* d_out_ids) {
+    pg_ctx* ctx = gb->ctx;
+    for (int64_t off = 0; off < n; off += MAX_CHUNK_ROWS) {
+        int64_t m = n - off < MAX_CHUNK_ROWS ? n - off : MAX_CHUNK_ROWS;
+        KeyCols kc = offset_keys(keys, gb->layout, off);
+        DCol hc;
+        if (hash_col) { hc = *hash_col; hc.values = (const int64_t*)hc.values + off; }
+        process_chunk(gb, kc, hash_col ? &hc : nullptr, m, d_out_ids ? d_out_ids + off : nullptr);
+    }
+    (void)ctx;
+    // the reference's logical capacity schedule (needRehash/tryRehash, BigintGroupByHash.java:262-334)
+    while (gb->groups >= max_fill_075(gb->ref_capacity) && gb->ref_capacity < (1LL << 30)) gb->ref_capacity *= 2;
+}
+
+}  // namespace pg
+
+// ------------------------------------------------------------------ C ABI
+using namespace pg;
+
+namespace {
+struct ImportedKeys {
+    std::vector<ColImport> cols;
+    ColImport hash;
+    KeyCols kc;
+    DCol hc;
+    bool has_hash = false;
+};
+void import_keys(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n, ImportedKeys& out) {
+    PG_CHECK_ARG(keys != nullptr, "null key columns");
+    const KeyLayout& L = gb->layout;
+    out.cols.resize(L.nkeys);
+    memset(&out.kc, 0, sizeof(out.kc));
+    for (int k = 0; k < L.nkeys; k++) {
+        PG_CHECK_ARG(keys[k].type == L.types[k], "key channel %d has type %d, expected %d", k, keys[k].type, L.types[k]);
+        PG_CHECK_ARG(keys[k].n == n, "key channel %d has %lld rows, expected %lld", k, (long long)keys[k].n, (long long)n);
+        import_col(gb->ctx, keys[k], n, out.cols[k]);
+        out.kc.c[k] = out.cols[k].d;
+    }
+    out.has_hash = false;
+    if (hash_col && gb->has_hash_channel) {
+        PG_CHECK_ARG(hash_col->type == PG_BIGINT && hash_col->n == n, "hash channel must be BIGINT with %lld rows", (long long)n);
+        import_col(gb->ctx, *hash_col, n, out.hash);
+        out.hc = out.hash.d;
+        out.has_hash = true;
+    } else {
+        PG_CHECK_ARG(!gb->has_hash_channel || gb->bigint_mode, "this GroupByHash was created with a precomputed hash channel");
+    }
+}
+}  // namespace
+
+extern "C" {
+
+int32_t pg_groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys, int32_t has_hash_channel, int64_t expected_size,
+                          pg_groupby** out) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    return guard(ctx, [&] { groupby_create(ctx, key_types, nkeys, has_hash_channel, expected_size, out); });
+}
+
+int32_t pg_groupby_destroy(pg_groupby* gb) {
+    if (!gb) return PG_OK;
+    pg_ctx* ctx = gb->ctx;
+    return guard(ctx, [&] { delete gb; });
+}
+
+int32_t pg_groupby_get_group_ids(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n, int32_t* out_ids,
+                                 int32_t ids_mem, int64_t* out_group_count) {
+    if (!gb) return PG_E_INVALID_ARGUMENT;
+    return guard(gb->ctx, [&] {
+        PG_CHECK_ARG(n >= 0 && (out_ids != nullptr || n == 0), "bad arguments");
+        ImportedKeys ik;
+        import_keys(gb, keys, hash_col, n, ik);
+        OutVec<int32_t> ids;
+        ids.begin(gb->ctx, out_ids, ids_mem, n);
+        groupby_process(gb, ik.kc, ik.has_hash ? &ik.hc : nullptr, n, ids.d);
+        ids.finish();
+        sync(gb->ctx);
+        if (out_group_count) *out_group_count = gb->groups;
+    });
+}
+
+int32_t pg_groupby_add_page(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n) {
+    if (!gb) return PG_E_INVALID_ARGUMENT;
+    return guard(gb->ctx, [&] {
+        PG_CHECK_ARG(n >= 0, "bad arguments");
+        ImportedKeys ik;
+        import_keys(gb, keys, hash_col, n, ik);
+        groupby_process(gb, ik.kc, ik.has_hash ? &ik.hc : nullptr, n, nullptr);
+        sync(gb->ctx);
+    });
+}
+
+int32_t pg_groupby_contains(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n, uint8_t* out, int32_t out_mem) {
+    if (!gb) return PG_E_INVALID_ARGUMENT;
+    return guard(gb->ctx, [&] {
+        PG_CHECK_ARG(n >= 0 && (out != nullptr || n == 0), "bad arguments");
+        if (n == 0) return;
+        pg_ctx* ctx = gb->ctx;
+        ImportedKeys ik;
+        import_keys(gb, keys, hash_col, n, ik);
+        OutVec<uint8_t> o;
+        o.begin(ctx, out, out_mem, n);
+        DCol hc; memset(&hc, 0, sizeof(hc));
+        if (ik.has_hash) hc = ik.hc;
+        int grid = grid_for(ctx, n, 256);
+        if (gb->bigint_mode)
+            PG_LAUNCH(ctx, gb_contains_kernel<true>, grid, 256, 0, gb->slots.as<Slot>(), gb->cap, gb->cap - 1, gb->key_rows.as<uint64_t>(),
+                      gb->arena.as<uint8_t>(), ik.kc, gb->layout, hc, ik.has_hash ? 1 : 0, n, o.d);
+        else
+            PG_LAUNCH(ctx, gb_contains_kernel<false>, grid, 256, 0, gb->slots.as<Slot>(), gb->cap, gb->cap - 1, gb->key_rows.as<uint64_t>(),
+                      gb->arena.as<uint8_t>(), ik.kc, gb->layout, hc, ik.has_hash ? 1 : 0, n, o.d);
+        o.finish();
+        sync(ctx);
+    });
+}
+
+int32_t pg_groupby_varwidth_bytes(pg_groupby* gb, int32_t key, int64_t* out_bytes) {
+    if (!gb || !out_bytes) return PG_E_INVALID_ARGUMENT;
+    return guard(gb->ctx, [&] {
+        pg_ctx* ctx = gb->ctx;
+        PG_CHECK_ARG(key >= 0 && key < gb->layout.nkeys, "bad key channel");
+        *out_bytes = 0;
+        if (!type_is_var(gb->layout.types[key]) || gb->groups == 0) return;
+        DevBuf acc(ctx, 8);
+        memset_async(ctx, acc.p, 0, 8);
+        PG_LAUNCH(ctx, gb_sum_var_bytes_kernel, grid_for(ctx, gb->groups, 256), 256, 0, gb->key_rows.as<uint64_t>(), gb->layout, key,
+                  gb->groups, acc.as<unsigned long long>());
+        read_scalars(ctx, acc.p, 1, out_bytes);
+    });
+}
+
+int32_t pg_groupby_export_keys(pg_groupby* gb, int64_t first, int64_t n, pg_col_out* out_keys, int64_t* out_hash, int32_t hash_mem) {
+    if (!gb) return PG_E_INVALID_ARGUMENT;
+    return guard(gb->ctx, [&] {
+        pg_ctx* ctx = gb->ctx;
+        PG_CHECK_ARG(first >= 0 && n >= 0 && first + n <= gb->groups, "group range [%lld, %lld) outside [0, %lld)", (long long)first,
+                     (long long)(first + n), (long long)gb->groups);
+        if (n == 0) return;
+        const KeyLayout& L = gb->layout;
+        OutVec<int64_t> oh;
+        oh.begin(ctx, out_hash, hash_mem, n);
+        int grid = grid_for(ctx, n, 256);
+        std::vector<OutStage> st(out_keys ? L.nkeys : 0);
+        std::vector<int64_t> vbytes(L.nkeys, 0);
+        if (gb->bigint_mode) {
+            int64_t* dv = nullptr; uint8_t* dn = nullptr;
+            if (out_keys) {
+                PG_CHECK_ARG(out_keys[0].type == PG_BIGINT, "output key type mismatch");
+                st[0].begin(ctx, &out_keys[0], n, n * 8);
+                dv = (int64_t*)st[0].d_values; dn = st[0].d_nulls; vbytes[0] = n * 8;
+            }
+            PG_LAUNCH(ctx, gb_export_bigint_kernel, grid, 256, 0, gb->values_by_group.as<int64_t>(), gb->slots.as<Slot>() + gb->cap, first,
+                      n, dv, dn, oh.d);
+        } else {
+            if (oh.d) PG_LAUNCH(ctx, gb_export_hash_kernel, grid, 256, 0, gb->hash_by_group.as<int64_t>(), first, n, oh.d);
+            for (int k = 0; out_keys && k < L.nkeys; k++) {
+                PG_CHECK_ARG(out_keys[k].type == L.types[k], "output key %d type mismatch", k);
+                if (!type_is_var(L.types[k])) {
+                    vbytes[k] = n * type_width(L.types[k]);
+                    st[k].begin(ctx, &out_keys[k], n, vbytes[k]);
+                    PG_LAUNCH(ctx, gb_export_fixed_kernel, grid, 256, 0, gb->key_rows.as<uint64_t>(), L, k, first, n, st[k].d_values,
+                              st[k].d_nulls);
+                } else {
+                    int64_t ntiles = num_tiles(n);
+                    DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+                    Pair64* d_total = tiles.as<Pair64>() + ntiles;
+                    PG_LAUNCH(ctx, gb_export_var_count_kernel, (int)ntiles, SCAN_THREADS, 0, gb->key_rows.as<uint64_t>(), L, k, first, n,
+                              tiles.as<Pair64>());
+                    scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, d_total);
+                    int64_t tot[2];
+                    read_scalars(ctx, d_total, 2, tot);
+                    vbytes[k] = tot[0];
+                    st[k].begin(ctx, &out_keys[k], n, vbytes[k]);
+                    PG_LAUNCH(ctx, gb_export_var_kernel, (int)ntiles, SCAN_THREADS, 0, gb->key_rows.as<uint64_t>(), gb->arena.as<uint8_t>(), L,
+                              k, first, n, tiles.as<Pair64>(), (uint8_t*)st[k].d_values, st[k].d_offsets, st[k].d_nulls);
+                }
+            }
+        }
+        for (size_t k = 0; k < st.size(); k++) st[k].finish(vbytes[k]);
+        oh.finish();
+        sync(ctx);
+    });
+}
+
+int32_t pg_groupby_stats(pg_groupby* gb, int64_t* group_count, int64_t* capacity, int64_t* collisions, int64_t* device_bytes) {
+    if (!gb) return PG_E_INVALID_ARGUMENT;
+    if (group_count) *group_count = gb->groups;
+    if (capacity) *capacity = gb->ref_capacity;
+    if (collisions) *collisions = 0;   // probe-length statistics are not collected on the device path
+    if (device_bytes) *device_bytes = groupby_device_bytes(gb);
+    return PG_OK;
+}
+
+}  // extern "C"

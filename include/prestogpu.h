@@ -160,6 +160,77 @@ PG_API int32_t pg_agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t fi
                                pg_col_out* out, int64_t* error_group);
 PG_API int32_t pg_agg_device_bytes(pg_agg* agg, int64_t* out);
 
+/* =====================================================================================
+ * Join build + LookupSource — replaces OP/HashBuilderOperator.java:308-350,428-496 (addInput/finish),
+ * OP/PagesIndex.java:209-240,489-533, OP/PagesHash.java:53-125 (build) and :152-222 (lookup),
+ * OP/ArrayPositionLinks.java:44-100, OP/JoinHash.java:81-125, OP/LookupSource.java:23-50,
+ * OP/JoinProbe.java:87-117 and the emit loop of OP/LookupJoinOperator.java:299-378.
+ * ===================================================================================== */
+enum { PG_JOIN_INNER = 0, PG_JOIN_PROBE_OUTER = 1 };
+
+typedef struct pg_joinbuild pg_joinbuild;
+typedef struct pg_lookup pg_lookup;
+
+/* HashBuilderOperatorFactory(types, outputChannels, hashChannels, preComputedHashChannel, expectedPositions)
+ * (OP/HashBuilderOperator.java:54-152).  hash_channel = index of the precomputed $hashvalue BIGINT channel or -1. */
+PG_API int32_t pg_joinbuild_create(pg_ctx* ctx, const int32_t* types, int32_t ncols, const int32_t* join_channels, int32_t njoin,
+                                   int32_t hash_channel, int64_t expected_rows, pg_joinbuild** out);
+PG_API int32_t pg_joinbuild_destroy(pg_joinbuild* b);
+/* HashBuilderOperator.addInput -> PagesIndex.addPage: the page's columns are copied into device-resident build columns */
+PG_API int32_t pg_joinbuild_add_page(pg_joinbuild* b, const pg_col* cols, int64_t n);
+/* HashBuilderOperator.finish -> buildLookupSource: builds the hash table; the builder's storage moves into the lookup */
+PG_API int32_t pg_joinbuild_finish(pg_joinbuild* b, pg_lookup** out);
+PG_API int32_t pg_lookup_destroy(pg_lookup* ls);
+/* getJoinPositionCount / PagesHash hashSize / getInMemorySizeInBytes / positionLinks.isPresent() */
+PG_API int32_t pg_lookup_stats(pg_lookup* ls, int64_t* rows, int64_t* hash_size, int64_t* device_bytes, int32_t* has_duplicates);
+/* One probe page through JoinProbe + LookupJoinOperator.processProbe: emits (probe position, build position) pairs in the
+ * reference's order (probe order; within a probe row the build rows newest first = positionLinks chain order).
+ * build position -1 = appendNullForBuild (PROBE_OUTER).  Probe rows with a null join key never match.
+ * If the output exceeds `capacity`, returns PG_NEED_MEMORY with *n_out = rows needed and nothing consumed. */
+PG_API int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, const pg_col* hash_col, int64_t n,
+                               int32_t join_type, int32_t* out_probe_idx, int64_t* out_build_pos, int32_t out_mem,
+                               int64_t capacity, int64_t* n_out);
+/* LookupSource.appendTo(position, pageBuilder, offset) for a vector of build positions and a list of build channels
+ * (LookupJoinPageBuilder.appendRow :76-84): gathers build columns; position -1 -> null. */
+PG_API int32_t pg_lookup_gather(pg_lookup* ls, const int64_t* build_pos, int32_t pos_mem, int64_t n, const int32_t* channels,
+                                int32_t nchannels, pg_col_out* out);
+/* value bytes pg_lookup_gather will write for a variable width build channel */
+PG_API int32_t pg_lookup_gather_var_bytes(pg_lookup* ls, const int64_t* build_pos, int32_t pos_mem, int64_t n, int32_t channel,
+                                          int64_t* out_bytes);
+
+/* =====================================================================================
+ * Fused GROUP BY operator — replaces OP/HashAggregationOperator.java:381-518 (addInput/getOutput) together with
+ * OP/aggregation/builder/InMemoryHashAggregationBuilder.java:139-155 (processPage) and :243-298 (buildResult).
+ * One call per page: group ids are resolved and every aggregate is updated on the device; ids never cross the ABI.
+ * ===================================================================================== */
+enum { PG_STEP_SINGLE = 0, PG_STEP_PARTIAL = 1, PG_STEP_FINAL = 2, PG_STEP_INTERMEDIATE = 3 };  /* AggregationNode.Step */
+
+typedef struct pg_agg_spec {
+    int32_t kind;           /* PG_AGG_*                                                          */
+    int32_t in_type;        /* argument type (0 for count(*))                                    */
+    int32_t input_channel;  /* raw steps: argument channel (-1 for count(*));
+                               FINAL/INTERMEDIATE: first channel of the intermediate columns      */
+    int32_t mask_channel;   /* BOOLEAN mask channel or -1                                        */
+} pg_agg_spec;
+
+typedef struct pg_hashagg pg_hashagg;
+/* HashAggregationOperatorFactory(groupByTypes, groupByChannels, step, accumulatorFactories, hashChannel, expectedGroups)
+ * (OP/HashAggregationOperator.java:54-262) */
+PG_API int32_t pg_hashagg_create(pg_ctx* ctx, const int32_t* key_channels, const int32_t* key_types, int32_t nkeys,
+                                 int32_t hash_channel, const pg_agg_spec* aggs, int32_t naggs, int32_t step,
+                                 int64_t expected_groups, pg_hashagg** out);
+PG_API int32_t pg_hashagg_destroy(pg_hashagg* op);
+/* addInput(Page) */
+PG_API int32_t pg_hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n);
+PG_API int32_t pg_hashagg_stats(pg_hashagg* op, int64_t* group_count, int64_t* capacity, int64_t* device_bytes, int64_t* input_rows);
+/* buildTypes(): keys..., (hash), then per aggregate its final type or its intermediate columns */
+PG_API int32_t pg_hashagg_output_types(pg_hashagg* op, int32_t* types, int32_t capacity, int32_t* ncols);
+/* buildResult() for group ids [first, first+n) */
+PG_API int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_out* out, int64_t* error_group);
+PG_API int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* out_bytes);
+/* partial-aggregation flush: forget all groups (OP/HashAggregationOperator.java:501-517) */
+PG_API int32_t pg_hashagg_reset(pg_hashagg* op);
+
 #ifdef __cplusplus
 }
 #endif

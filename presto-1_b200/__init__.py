@@ -10,3 +10,7 @@ from .blocks import Block, OutBlock, Page
 from .context import GpuContext, default_context
 from .groupby import GroupByHash, GroupByIdBlock
 from .accumulators import GroupedAccumulator, final_type, intermediate_types
+from .join import LookupSource, PagesIndex
+from .operators import (FINAL, INTERMEDIATE, PARTIAL, SINGLE, AggregatorFactory, HashAggregationOperator, HashBuilderOperator,
+                        LookupJoinOperator, take_positions)
+JOIN_INNER, JOIN_PROBE_OUTER = native.JOIN_INNER, native.JOIN_PROBE_OUTER

@@ -30,6 +30,13 @@ class PgColOut(C.Structure):
                 ("offsets", C.c_void_p), ("values_capacity_bytes", C.c_int64)]
 
 
+class PgAggSpec(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("in_type", C.c_int32), ("input_channel", C.c_int32), ("mask_channel", C.c_int32)]
+
+
+STEP_SINGLE, STEP_PARTIAL, STEP_FINAL, STEP_INTERMEDIATE = 0, 1, 2, 3
+
+
 class PrestoGpuError(RuntimeError):
     """Mirrors TrinoException(StandardErrorCode, message) (SURVEY.md §8b error conventions)."""
 
@@ -69,6 +76,23 @@ _PROTOS = {
     "pg_agg_n_intermediate": (I32, [P, PI32]),
     "pg_agg_evaluate": (I32, [P, I64, I64, I32, PCOLOUT, PI64]),
     "pg_agg_device_bytes": (I32, [P, PI64]),
+    "pg_hashagg_create": (I32, [P, PI32, PI32, I32, I32, C.POINTER(PgAggSpec), I32, I32, I64, C.POINTER(P)]),
+    "pg_hashagg_destroy": (I32, [P]),
+    "pg_hashagg_add_page": (I32, [P, PCOL, I32, I64]),
+    "pg_hashagg_stats": (I32, [P, PI64, PI64, PI64, PI64]),
+    "pg_hashagg_output_types": (I32, [P, PI32, I32, PI32]),
+    "pg_hashagg_get_output": (I32, [P, I64, I64, PCOLOUT, PI64]),
+    "pg_hashagg_varwidth_bytes": (I32, [P, I32, PI64]),
+    "pg_hashagg_reset": (I32, [P]),
+    "pg_joinbuild_create": (I32, [P, PI32, I32, PI32, I32, I32, I64, C.POINTER(P)]),
+    "pg_joinbuild_destroy": (I32, [P]),
+    "pg_joinbuild_add_page": (I32, [P, PCOL, I64]),
+    "pg_joinbuild_finish": (I32, [P, C.POINTER(P)]),
+    "pg_lookup_destroy": (I32, [P]),
+    "pg_lookup_stats": (I32, [P, PI64, PI64, PI64, PI32]),
+    "pg_lookup_probe": (I32, [P, PCOL, I32, PCOL, I64, I32, P, P, I32, I64, PI64]),
+    "pg_lookup_gather": (I32, [P, P, I32, I64, PI32, I32, PCOLOUT]),
+    "pg_lookup_gather_var_bytes": (I32, [P, P, I32, I64, I32, PI64]),
 }
 
 

@@ -311,6 +311,20 @@ AggOp agg_make_op(pg_agg* agg, const DCol* arg, const DCol* mask) {
     return op;
 }
 
+// addIntermediate for one aggregate: s0/s1 are the intermediate columns (see the layout table in prestogpu.h)
+void accumulate_intermediate(pg_agg* agg, const DCol& s0, const DCol& s1, const int32_t* d_ids, int64_t n, int64_t group_count) {
+    pg_ctx* ctx = agg->ctx;
+    if (n <= 0) return;
+    if (agg->op == OP_MIN128 || agg->op == OP_MAX128) {   // same two-pass protocol as addInput
+        AggProgram prog; memset(&prog, 0, sizeof(prog)); prog.naggs = 1;
+        prog.ops[0] = agg_make_op(agg, &s0, nullptr);
+        accumulate(ctx, prog, d_ids, n, group_count);
+        return;
+    }
+    AggOp op = agg_make_op(agg, nullptr, nullptr);
+    PG_LAUNCH(ctx, acc_intermediate_kernel, grid_for(ctx, n, 256), 256, 0, op, s0, s1, agg->kind, d_ids, n);
+}
+
 int agg_n_intermediate(const pg_agg* agg) {
     if (agg->op == OP_SUM_I64 || agg->op == OP_SUM_F64) return 2;
     return 1;
@@ -441,17 +455,7 @@ int32_t pg_agg_add_intermediate(pg_agg* agg, const int32_t* ids, int32_t ids_mem
         import_col(ctx, state[0], n, c0);
         DCol d1; memset(&d1, 0, sizeof(d1));
         if (nc > 1) { import_col(ctx, state[1], n, c1); d1 = c1.d; }
-        AggOp op = agg_make_op(agg, nullptr, nullptr);
-        DevBuf snap;
-        bool is128 = agg->op == OP_MIN128 || agg->op == OP_MAX128;
-        if (is128) {
-            // same two-pass protocol as addInput
-            AggProgram prog; memset(&prog, 0, sizeof(prog)); prog.naggs = 1;
-            prog.ops[0] = agg_make_op(agg, &c0.d, nullptr);
-            accumulate(ctx, prog, d_ids, n, group_count);
-        } else {
-            PG_LAUNCH(ctx, acc_intermediate_kernel, grid_for(ctx, n, 256), 256, 0, op, c0.d, d1, agg->kind, d_ids, n);
-        }
+        accumulate_intermediate(agg, c0.d, d1, d_ids, n, group_count);
         sync(ctx);
     });
 }

@@ -1,0 +1,250 @@
+// hashagg.cu — the fused GROUP BY operator: HashAggregationOperator + InMemoryHashAggregationBuilder.
+// Replaces OP/HashAggregationOperator.java:381-518 (addInput/getOutput) and
+// OP/aggregation/builder/InMemoryHashAggregationBuilder.java:139-155 (processPage), :243-298 (buildResult).
+// One page = getGroupIds (groupby.cu) -> one accumulate() launch over ALL aggregates (accum.cu); group ids never
+// leave the device.
+#include "accum.h"
+#include "groupby.h"
+
+struct pg_hashagg {
+    pg_ctx* ctx = nullptr;
+    int32_t step = 0;
+    std::vector<int32_t> key_channels;
+    std::vector<int32_t> key_types;
+    int32_t hash_channel = -1;
+    std::vector<pg_agg_spec> specs;
+    int64_t expected = 0;
+    pg_groupby* gb = nullptr;
+    std::vector<pg_agg*> aggs;
+    pg::DevBuf ids;
+    int64_t input_rows = 0;
+    ~pg_hashagg() {
+        for (pg_agg* a : aggs) delete a;
+        delete gb;
+    }
+};
+
+namespace pg {
+
+static bool step_input_raw(int s) { return s == PG_STEP_SINGLE || s == PG_STEP_PARTIAL; }
+static bool step_output_partial(int s) { return s == PG_STEP_PARTIAL || s == PG_STEP_INTERMEDIATE; }
+
+
+static void hashagg_build(pg_hashagg* op) {
+    groupby_create(op->ctx, op->key_types.data(), (int32_t)op->key_types.size(), op->hash_channel >= 0 ? 1 : 0, op->expected, &op->gb);
+    for (const pg_agg_spec& s : op->specs) {
+        pg_agg* a = nullptr;
+        agg_create(op->ctx, s.kind, s.in_type, &a);
+        op->aggs.push_back(a);
+    }
+}
+
+static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n) {
+    pg_ctx* ctx = op->ctx;
+    if (n == 0) return;
+    // import each referenced channel once
+    std::vector<ColImport> imp(ncols);
+    std::vector<char> loaded(ncols, 0);
+    auto need = [&](int ch) -> const DCol& {
+        PG_CHECK_ARG(ch >= 0 && ch < ncols, "channel %d out of range (page has %d)", ch, ncols);
+        if (!loaded[ch]) {
+            PG_CHECK_ARG(cols[ch].n == n, "channel %d has %lld rows, expected %lld", ch, (long long)cols[ch].n, (long long)n);
+            import_col(ctx, cols[ch], n, imp[ch]);
+            loaded[ch] = 1;
+        }
+        return imp[ch].d;
+    };
+    KeyCols kc;
+    memset(&kc, 0, sizeof(kc));
+    for (size_t k = 0; k < op->key_channels.size(); k++) {
+        kc.c[k] = need(op->key_channels[k]);
+        PG_CHECK_ARG(kc.c[k].type == op->key_types[k], "group-by channel %d has type %d, expected %d", op->key_channels[k], kc.c[k].type,
+                     op->key_types[k]);
+    }
+    DCol hc; memset(&hc, 0, sizeof(hc));
+    bool has_hash = op->hash_channel >= 0;
+    if (has_hash) { hc = need(op->hash_channel); PG_CHECK_ARG(hc.type == PG_BIGINT, "hash channel must be BIGINT"); }
+    op->ids.grow(ctx, n * 4, 0);
+    groupby_process(op->gb, kc, has_hash ? &hc : nullptr, n, op->ids.as<int32_t>());
+    int64_t groups = op->gb->groups;
+    if (op->aggs.empty()) { op->input_rows += n; return; }
+    for (pg_agg* a : op->aggs) agg_ensure_capacity(a, groups);
+    if (step_input_raw(op->step)) {
+        AggProgram prog;
+        memset(&prog, 0, sizeof(prog));
+        prog.naggs = (int32_t)op->aggs.size();
+        for (size_t i = 0; i < op->aggs.size(); i++) {
+            const pg_agg_spec& s = op->specs[i];
+            const DCol* arg = nullptr; const DCol* mask = nullptr;
+            if (s.kind != PG_AGG_COUNT) {
+                arg = &need(s.input_channel);
+                PG_CHECK_ARG(arg->type == s.in_type, "aggregate %d input channel has type %d, expected %d", (int)i, arg->type, s.in_type);
+            }
+            if (s.mask_channel >= 0) { mask = &need(s.mask_channel); PG_CHECK_ARG(mask->type == PG_BOOLEAN, "mask must be BOOLEAN"); }
+            prog.ops[i] = agg_make_op(op->aggs[i], arg, mask);
+        }
+        accumulate(ctx, prog, op->ids.as<int32_t>(), n, groups);
+    } else {
+        for (size_t i = 0; i < op->aggs.size(); i++) {
+            const pg_agg_spec& s = op->specs[i];
+            pg_agg* a = op->aggs[i];
+            DCol s0 = need(s.input_channel);
+            DCol s1; memset(&s1, 0, sizeof(s1));
+            if (agg_n_intermediate(a) > 1) s1 = need(s.input_channel + 1);
+            accumulate_intermediate(a, s0, s1, op->ids.as<int32_t>(), n, groups);
+        }
+    }
+    op->input_rows += n;
+    sync(ctx);   // staged host columns are released when `imp` goes out of scope
+}
+
+}  // namespace pg
+
+using namespace pg;
+
+extern "C" {
+
+int32_t pg_hashagg_create(pg_ctx* ctx, const int32_t* key_channels, const int32_t* key_types, int32_t nkeys, int32_t hash_channel,
+                          const pg_agg_spec* aggs, int32_t naggs, int32_t step, int64_t expected_groups, pg_hashagg** out) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    return guard(ctx, [&] {
+        PG_CHECK_ARG(out && key_channels && key_types && nkeys >= 1, "a grouped aggregation needs at least one group-by channel");
+        PG_CHECK_ARG(naggs >= 0 && naggs <= MAX_AGGS && (naggs == 0 || aggs), "between 0 and %d aggregates are supported", MAX_AGGS);
+        PG_CHECK_ARG(step >= PG_STEP_SINGLE && step <= PG_STEP_INTERMEDIATE, "bad step %d", step);
+        pg_hashagg* op = new pg_hashagg();
+        try {
+            op->ctx = ctx; op->step = step; op->hash_channel = hash_channel; op->expected = expected_groups;
+            op->key_channels.assign(key_channels, key_channels + nkeys);
+            op->key_types.assign(key_types, key_types + nkeys);
+            op->specs.assign(aggs, aggs + naggs);
+            hashagg_build(op);
+        } catch (...) { delete op; throw; }
+        *out = op;
+    });
+}
+
+int32_t pg_hashagg_destroy(pg_hashagg* op) {
+    if (!op) return PG_OK;
+    return guard(op->ctx, [&] { delete op; });
+}
+
+int32_t pg_hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    return guard(op->ctx, [&] {
+        PG_CHECK_ARG(cols && ncols > 0 && n >= 0, "bad arguments");
+        hashagg_add_page(op, cols, ncols, n);
+    });
+}
+
+int32_t pg_hashagg_stats(pg_hashagg* op, int64_t* group_count, int64_t* capacity, int64_t* device_bytes, int64_t* input_rows) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    if (group_count) *group_count = op->gb->groups;
+    if (capacity) *capacity = op->gb->ref_capacity;
+    if (device_bytes) {
+        int64_t b = groupby_device_bytes(op->gb) + op->ids.bytes;
+        for (pg_agg* a : op->aggs) b += a->state.bytes;
+        *device_bytes = b;
+    }
+    if (input_rows) *input_rows = op->input_rows;
+    return PG_OK;
+}
+
+/* output column types in order: keys..., (hash), then per aggregate its final type or its intermediate columns */
+int32_t pg_hashagg_output_types(pg_hashagg* op, int32_t* types, int32_t capacity, int32_t* ncols) {
+    if (!op || !ncols) return PG_E_INVALID_ARGUMENT;
+    return guard(op->ctx, [&] {
+        std::vector<int32_t> t(op->key_types);
+        if (op->hash_channel >= 0) t.push_back(PG_BIGINT);
+        bool partial = step_output_partial(op->step);
+        for (pg_agg* a : op->aggs) {
+            bool dec = a->op == OP_SUM_DEC;
+            if (!partial) {
+                int32_t ft;
+                switch (a->kind) {
+                    case PG_AGG_COUNT: case PG_AGG_COUNT_COL: ft = PG_BIGINT; break;
+                    case PG_AGG_SUM: ft = dec ? PG_LONG_DECIMAL : (a->op == OP_SUM_I64 ? PG_BIGINT : PG_DOUBLE); break;
+                    case PG_AGG_AVG: ft = dec ? a->in_type : PG_DOUBLE; break;
+                    default: ft = a->in_type;
+                }
+                t.push_back(ft);
+            } else {
+                switch (a->kind) {
+                    case PG_AGG_COUNT: case PG_AGG_COUNT_COL: t.push_back(PG_BIGINT); break;
+                    case PG_AGG_SUM:
+                        if (dec) t.push_back(PG_VARBINARY);
+                        else { t.push_back(PG_BIGINT); t.push_back(a->op == OP_SUM_I64 ? PG_BIGINT : PG_DOUBLE); }
+                        break;
+                    case PG_AGG_AVG:
+                        if (dec) t.push_back(PG_VARBINARY);
+                        else { t.push_back(PG_DOUBLE); t.push_back(PG_BIGINT); }
+                        break;
+                    default: t.push_back(a->in_type);
+                }
+            }
+        }
+        *ncols = (int32_t)t.size();
+        if (types) {
+            PG_CHECK_ARG(capacity >= (int32_t)t.size(), "types buffer too small");
+            for (size_t i = 0; i < t.size(); i++) types[i] = t[i];
+        }
+    });
+}
+
+/* buildResult for groups [first, first+n): out[] in pg_hashagg_output_types order */
+int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_out* out, int64_t* error_group) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    return guard(op->ctx, [&] {
+        pg_ctx* ctx = op->ctx;
+        PG_CHECK_ARG(out && first >= 0 && n >= 0 && first + n <= op->gb->groups, "group range outside [0, %lld)", (long long)op->gb->groups);
+        if (error_group) *error_group = -1;
+        if (n == 0) return;
+        int nk = (int)op->key_types.size();
+        bool has_hash = op->hash_channel >= 0;
+        int64_t* hash_ptr = nullptr; int32_t hash_mem = PG_MEM_DEVICE;
+        if (has_hash) {
+            PG_CHECK_ARG(out[nk].type == PG_BIGINT && out[nk].capacity >= n, "hash output column must be BIGINT with capacity");
+            hash_ptr = (int64_t*)out[nk].values; hash_mem = out[nk].mem;
+        }
+        int32_t rc = pg_groupby_export_keys(op->gb, first, n, out, hash_ptr, hash_mem);
+        if (rc != PG_OK) fail(rc, "%s", ctx->err.c_str());
+        if (has_hash && out[nk].nulls) {
+            if (out[nk].mem == PG_MEM_DEVICE) memset_async(ctx, out[nk].nulls, 0, n); else memset(out[nk].nulls, 0, n);
+        }
+        int col = nk + (has_hash ? 1 : 0);
+        bool partial = step_output_partial(op->step);
+        int64_t first_err = -1;
+        for (pg_agg* a : op->aggs) {
+            int64_t eg = -1;
+            try { agg_evaluate(a, first, n, partial ? 0 : 1, out + col, &eg, true); }
+            catch (const Error& e) { if (e.code != PG_E_NUMERIC_OVERFLOW) throw; if (first_err < 0) first_err = eg; }
+            col += partial ? agg_n_intermediate(a) : 1;
+        }
+        sync(ctx);
+        if (first_err >= 0) {
+            if (error_group) *error_group = first_err;
+            fail(PG_E_NUMERIC_OVERFLOW, "aggregate overflow in group %lld", (long long)first_err);
+        }
+    });
+}
+
+/* value bytes needed for output column `col` (variable width key or VARBINARY intermediate state) */
+int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* out_bytes) {
+    if (!op || !out_bytes) return PG_E_INVALID_ARGUMENT;
+    int nk = (int)op->key_types.size();
+    if (col < nk) return pg_groupby_varwidth_bytes(op->gb, col, out_bytes);
+    *out_bytes = 32 * op->gb->groups;   // decimal intermediate states: at most 32 bytes per group
+    return PG_OK;
+}
+
+/* partial-aggregation flush: drop all groups and states, keep the configuration (HashAggregationOperator.java:501-517) */
+int32_t pg_hashagg_reset(pg_hashagg* op) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    return guard(op->ctx, [&] {
+        for (pg_agg* a : op->aggs) delete a;
+        op->aggs.clear();
+        delete op->gb; op->gb = nullptr;
+        hashagg_build(op);
+    });
+}
+
+}  // extern "C"

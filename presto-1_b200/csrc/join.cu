@@ -1,0 +1,640 @@
+// join.cu — join build (PagesIndex + PagesHash + ArrayPositionLinks) and probe (JoinProbe + LookupJoinOperator emit).
+#include "join.h"
+
+namespace pg {
+
+static const int J_THREADS = 256;
+
+// ------------------------------------------------------------------ build-side storage (PagesIndex.addPage)
+__global__ void j_rebase_offsets_kernel(int32_t* dst, const int32_t* src, int64_t n, int32_t delta, int first_page) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // dst[0] of the whole column is written once (first page); later pages write dst[1..n] relative to their base
+    for (; i <= n; i += stride) {
+        if (i == 0 && !first_page) continue;
+        dst[i] = src[i] - src[0] + delta;
+    }
+}
+
+static void store_append(pg_ctx* ctx, ColStore& s, const ColImport& in, int64_t old_rows, int64_t n) {
+    int64_t new_rows = old_rows + n;
+    if (new_rows > s.rows_cap) {
+        int64_t cap = s.rows_cap ? s.rows_cap : 1024;
+        while (cap < new_rows) cap *= 2;
+        int w = type_width(s.type);
+        if (w) s.values.grow(ctx, cap * w, old_rows * w);
+        if (s.has_nulls) s.nulls.grow(ctx, cap, old_rows);
+        if (type_is_var(s.type)) s.offsets.grow(ctx, (cap + 1) * 4, (old_rows + 1) * 4);
+        s.rows_cap = cap;
+    }
+    if (in.d.nulls && !s.has_nulls) {
+        s.nulls.alloc(ctx, s.rows_cap);
+        memset_async(ctx, s.nulls.p, 0, s.rows_cap);
+        s.has_nulls = true;
+    }
+    if (s.has_nulls) {
+        if (in.d.nulls) copy_async(ctx, s.nulls.as<uint8_t>() + old_rows, in.d.nulls, n, cudaMemcpyDeviceToDevice);
+        else memset_async(ctx, s.nulls.as<uint8_t>() + old_rows, 0, n);
+    }
+    if (type_is_var(s.type)) {
+        // bytes referenced by this page: [src_off[0], src_off[n])
+        int32_t ends[2] = {0, 0};
+        copy_async(ctx, ctx->h_scalar, in.d.offsets, 4, cudaMemcpyDeviceToHost);
+        copy_async(ctx, (char*)ctx->h_scalar + 8, in.d.offsets + n, 4, cudaMemcpyDeviceToHost);
+        sync(ctx);
+        memcpy(&ends[0], ctx->h_scalar, 4); memcpy(&ends[1], (char*)ctx->h_scalar + 8, 4);
+        int64_t nbytes = (int64_t)ends[1] - ends[0];
+        if (s.bytes_used + nbytes > 0x7fffffffLL) fail(PG_E_INSUFFICIENT_RESOURCES, "variable width build column exceeds 2 GB");
+        if (s.bytes_used + nbytes > s.values.bytes) s.values.grow(ctx, (s.bytes_used + nbytes) * 2 + 1024, s.bytes_used);
+        copy_async(ctx, s.values.as<uint8_t>() + s.bytes_used, (const uint8_t*)in.d.values + ends[0], nbytes, cudaMemcpyDeviceToDevice);
+        PG_LAUNCH(ctx, j_rebase_offsets_kernel, grid_for(ctx, n + 1, 256), 256, 0, s.offsets.as<int32_t>() + old_rows, in.d.offsets, n,
+                  (int32_t)s.bytes_used, old_rows == 0 ? 1 : 0);
+        s.bytes_used += nbytes;
+    } else {
+        int w = type_width(s.type);
+        copy_async(ctx, s.values.as<char>() + old_rows * w, in.d.values, n * w, cudaMemcpyDeviceToDevice);
+    }
+}
+
+// ------------------------------------------------------------------ key helpers
+PG_D bool jrow_has_null(const JoinCols& jc, int64_t i) {   // SimplePagesHashStrategy.isPositionNull :268-276 / JoinProbe :109-116
+    for (int k = 0; k < jc.n; k++) if (dcol_is_null(jc.c[k], i)) return true;
+    return false;
+}
+PG_D int64_t jrow_hash(const JoinCols& jc, int64_t i) {
+    uint64_t h = 0;
+    for (int k = 0; k < jc.n; k++) h = 31 * h + (uint64_t)dcol_type_hash(jc.c[k], i);
+    return (int64_t)h;
+}
+// EQUAL between row i of `a` and row j of `b` (no nulls on either side; NaN != NaN, DoubleType.java:158-162)
+PG_D bool jrows_equal(const JoinCols& a, int64_t i, const JoinCols& b, int64_t j) {
+    for (int k = 0; k < a.n; k++) {
+        const DCol& x = a.c[k]; const DCol& y = b.c[k];
+        switch (x.type) {
+            case PG_VARCHAR: case PG_VARBINARY: {
+                int32_t oi = x.offsets[i], li = x.offsets[i + 1] - oi, oj = y.offsets[j], lj = y.offsets[j + 1] - oj;
+                if (li != lj) return false;
+                const uint8_t* p = (const uint8_t*)x.values; const uint8_t* q = (const uint8_t*)y.values;
+                for (int32_t t = 0; t < li; t++) if (p[oi + t] != q[oj + t]) return false;
+                break;
+            }
+            case PG_LONG_DECIMAL: {
+                const int64_t* p = (const int64_t*)x.values; const int64_t* q = (const int64_t*)y.values;
+                if (p[2 * i] != q[2 * j] || p[2 * i + 1] != q[2 * j + 1]) return false;
+                break;
+            }
+            case PG_DOUBLE:
+                if (!(__longlong_as_double(dcol_long(x, i)) == __longlong_as_double(dcol_long(y, j)))) return false;
+                break;
+            default:
+                if (dcol_long(x, i) != dcol_long(y, j)) return false;
+        }
+    }
+    return true;
+}
+
+__global__ void j_init_slots_kernel(JSlot* slots, int64_t nslots, unsigned long long empty) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < nslots; i += stride) {
+        int4 v;
+        v.x = (int)(empty & 0xffffffffu); v.y = (int)(empty >> 32); v.z = 0; v.w = -1;
+        ((int4*)slots)[i] = v;
+    }
+}
+
+// find (probe side) or claim (build side) the slot of row i.  Returns -1 when absent (FIND only).
+template <bool CLAIM>
+PG_D int64_t j_locate(JSlot* slots, int64_t cap, int64_t mask, const JoinCols& build, const JoinCols& rowcols, int64_t i,
+                      const DCol& hash_col, int has_hash) {
+    if (build.bigint_fast) {
+        unsigned long long key = (unsigned long long)((const int64_t*)rowcols.c[0].values)[i];
+        if (key == EMPTY_KEY) return cap;
+        int64_t p = (int64_t)(fmix64(key) & (uint64_t)mask);
+        while (true) {
+            unsigned long long k = CLAIM ? *((volatile unsigned long long*)&slots[p].word) : slots[p].word;
+            if (k == key) return p;
+            if (k == EMPTY_KEY) {
+                if (!CLAIM) return -1;
+                unsigned long long old = atomicCAS(&slots[p].word, EMPTY_KEY, key);
+                if (old == EMPTY_KEY || old == key) return p;
+            }
+            p = (p + 1) & mask;
+        }
+    }
+    int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[i] : jrow_hash(rowcols, i);
+    uint64_t f = fmix64((uint64_t)raw);
+    uint32_t tag = (uint32_t)(f >> 32);
+    unsigned long long mine = ((unsigned long long)tag << 32) | (unsigned long long)(uint32_t)i;
+    int64_t p = (int64_t)(f & (uint64_t)mask);
+    while (true) {
+        unsigned long long w = CLAIM ? *((volatile unsigned long long*)&slots[p].word) : slots[p].word;
+        if (w == EMPTY_WORD) {
+            if (!CLAIM) return -1;
+            unsigned long long old = atomicCAS(&slots[p].word, EMPTY_WORD, mine);
+            if (old == EMPTY_WORD) return p;
+            w = old;
+        }
+        if ((uint32_t)(w >> 32) == tag && jrows_equal(rowcols, i, build, (int64_t)(uint32_t)w)) return p;
+        p = (p + 1) & mask;
+    }
+}
+
+// build pass 1: every non-null-key row claims/finds its slot, count++, head = max(row)
+__global__ void __launch_bounds__(J_THREADS) j_build_kernel(JSlot* slots, int64_t cap, JoinCols build, DCol hash_col, int has_hash, int64_t rows,
+                                                            int32_t* row_slot, int* has_dups) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    bool dup = false;
+    for (; i < rows; i += stride) {
+        if (jrow_has_null(build, i)) { row_slot[i] = -1; continue; }   // PagesHash.java:94-96
+        int64_t s = j_locate<true>(slots, cap, cap - 1, build, build, i, hash_col, has_hash);
+        if (atomicAdd(&slots[s].count, 1) > 0) dup = true;
+        atomicMax(&slots[s].head, (int32_t)i);
+        row_slot[i] = (int32_t)s;
+    }
+    if (dup) *has_dups = 1;
+}
+
+// ------------------------------------------------------------------ duplicate keys: CSR segments in descending row order
+__global__ void __launch_bounds__(SCAN_THREADS) j_seg_count_kernel(const JSlot* slots, int64_t nslots, Pair64* tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 acc{0, 0};
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (i < nslots) { int c = slots[i].count; if (c > 1) acc.a += c; }
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) j_seg_offsets_kernel(const JSlot* slots, int64_t nslots, const Pair64* tile_prefix,
+                                                                     int32_t* seg_off) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 run = tile_prefix[blockIdx.x];
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        Pair64 v{0, 0};
+        if (i < nslots) { int c = slots[i].count; if (c > 1) v.a = c; }
+        Pair64 total;
+        Pair64 ex = block_exclusive_scan(v, smem, &total);
+        if (i < nslots) seg_off[i] = (int32_t)(run.a + ex.a);
+        run = run + total;
+    }
+}
+__global__ void j_seg_fill_kernel(const JSlot* slots, const int32_t* row_slot, int64_t rows, const int32_t* seg_off, int32_t* seg_fill,
+                                  int32_t* seg_rows) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < rows; i += stride) {
+        int32_t s = row_slot[i];
+        if (s < 0 || slots[s].count <= 1) continue;
+        int pos = atomicAdd(&seg_fill[s], 1);
+        seg_rows[seg_off[s] + pos] = (int32_t)i;
+    }
+}
+static const int SMALL_SEG = 48;
+// small segments: one thread sorts descending (insertion sort); large ones are queued for the block-wide sorter
+__global__ void j_seg_sort_small_kernel(const JSlot* slots, int64_t nslots, const int32_t* seg_off, int32_t* seg_rows, int32_t* large_list,
+                                        int* large_count) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < nslots; i += stride) {
+        int c = slots[i].count;
+        if (c <= 1) continue;
+        if (c > SMALL_SEG) { large_list[atomicAdd(large_count, 1)] = (int32_t)i; continue; }
+        int32_t* seg = seg_rows + seg_off[i];
+        for (int a = 1; a < c; a++) {
+            int32_t v = seg[a];
+            int b = a - 1;
+            while (b >= 0 && seg[b] < v) { seg[b + 1] = seg[b]; b--; }
+            seg[b + 1] = v;
+        }
+    }
+}
+// one block per large segment: bitonic sort (descending) directly in global memory
+__global__ void __launch_bounds__(256) j_seg_sort_large_kernel(const JSlot* slots, const int32_t* seg_off, int32_t* seg_rows,
+                                                               const int32_t* large_list) {
+    int32_t slot = large_list[blockIdx.x];
+    int64_t c = slots[slot].count;
+    int32_t* seg = seg_rows + seg_off[slot];
+    int64_t m = 1;
+    while (m < c) m <<= 1;
+    // bitonic network in its single-direction form (first step of every merge mirrors the partner), so that the
+    // virtual padding beyond c behaves as -inf and comparisons with it can simply be skipped
+    for (int64_t k = 2; k <= m; k <<= 1) {
+        for (int64_t t = threadIdx.x; t < m; t += blockDim.x) {
+            int64_t p = t ^ (k - 1);
+            if (p > t && p < c) { int32_t a = seg[t], b = seg[p]; if (a < b) { seg[t] = b; seg[p] = a; } }
+        }
+        __syncthreads();
+        for (int64_t j = k >> 2; j > 0; j >>= 1) {
+            for (int64_t t = threadIdx.x; t < m; t += blockDim.x) {
+                int64_t p = t ^ j;
+                if (p > t && p < c) { int32_t a = seg[t], b = seg[p]; if (a < b) { seg[t] = b; seg[p] = a; } }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// ------------------------------------------------------------------ probe
+struct ProbeArgs {
+    const JSlot* slots;
+    int64_t cap;
+    const int32_t* seg_off;
+    const int32_t* seg_rows;
+    int32_t* probe_slot;
+    int64_t n;
+    int32_t join_type;
+    int32_t build_empty;
+};
+
+__global__ void __launch_bounds__(SCAN_THREADS) j_probe_count_kernel(ProbeArgs a, JoinCols build, JoinCols probe, DCol hash_col, int has_hash,
+                                                                     Pair64* tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 acc{0, 0};
+#pragma unroll 2
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t row = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (row < a.n) {
+            int64_t s = -1;
+            if (!a.build_empty && !jrow_has_null(probe, row))
+                s = j_locate<false>((JSlot*)a.slots, a.cap, a.cap - 1, build, probe, row, hash_col, has_hash);
+            int c = 0;
+            if (s >= 0) { c = a.slots[s].count; if (c == 0) s = -1; }
+            a.probe_slot[row] = (int32_t)s;
+            if (c == 0 && a.join_type == 1) c = 1;   // PROBE_OUTER: appendNullForBuild (LookupJoinOperator.java:354-361)
+            acc.a += c;
+        }
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) j_probe_emit_kernel(ProbeArgs a, const Pair64* tile_prefix, int32_t* out_probe,
+                                                                    int64_t* out_build) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 run = tile_prefix[blockIdx.x];
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t row = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        Pair64 v{0, 0};
+        int32_t s = -1; int c = 0;
+        if (row < a.n) {
+            s = a.probe_slot[row];
+            if (s >= 0) c = a.slots[s].count;
+            v.a = (c == 0 && a.join_type == 1) ? 1 : c;
+        }
+        Pair64 total;
+        Pair64 ex = block_exclusive_scan(v, smem, &total);
+        if (v.a) {
+            int64_t o = run.a + ex.a;
+            if (c == 0) { out_probe[o] = (int32_t)row; out_build[o] = -1; }
+            else if (c == 1) { out_probe[o] = (int32_t)row; out_build[o] = a.slots[s].head; }
+            else {
+                const int32_t* seg = a.seg_rows + a.seg_off[s];
+                for (int k = 0; k < c; k++) { out_probe[o + k] = (int32_t)row; out_build[o + k] = seg[k]; }
+            }
+        }
+        run = run + total;
+    }
+}
+
+// ------------------------------------------------------------------ gather (LookupSource.appendTo / PagesHashStrategy.appendTo)
+__global__ void j_gather_fixed_kernel(DCol src, const int64_t* pos, int64_t n, void* out_values, uint8_t* out_nulls) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        int64_t p = pos[i];
+        bool isnull = p < 0 || dcol_is_null(src, p);
+        if (out_nulls) out_nulls[i] = isnull ? 1 : 0;
+        switch (src.type) {
+            case PG_INTEGER: case PG_DATE: ((int32_t*)out_values)[i] = isnull ? 0 : ((const int32_t*)src.values)[p]; break;
+            case PG_BOOLEAN: ((uint8_t*)out_values)[i] = isnull ? 0 : ((const uint8_t*)src.values)[p]; break;
+            case PG_LONG_DECIMAL: {
+                const int64_t* q = (const int64_t*)src.values;
+                ((int64_t*)out_values)[2 * i] = isnull ? 0 : q[2 * p]; ((int64_t*)out_values)[2 * i + 1] = isnull ? 0 : q[2 * p + 1];
+                break;
+            }
+            default: ((int64_t*)out_values)[i] = isnull ? 0 : ((const int64_t*)src.values)[p];
+        }
+    }
+}
+PG_D int64_t gather_len(const DCol& src, int64_t p) {
+    if (p < 0 || dcol_is_null(src, p)) return 0;
+    return src.offsets[p + 1] - src.offsets[p];
+}
+__global__ void __launch_bounds__(SCAN_THREADS) j_gather_var_count_kernel(DCol src, const int64_t* pos, int64_t n, Pair64* tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 acc{0, 0};
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (i < n) acc.a += gather_len(src, pos[i]);
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) j_gather_var_kernel(DCol src, const int64_t* pos, int64_t n, const Pair64* tile_prefix,
+                                                                    uint8_t* out_bytes, int32_t* out_offsets, uint8_t* out_nulls) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 run = tile_prefix[blockIdx.x];
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        Pair64 v{0, 0};
+        int64_t p = -1;
+        if (i < n) { p = pos[i]; v.a = gather_len(src, p); }
+        Pair64 total;
+        Pair64 ex = block_exclusive_scan(v, smem, &total);
+        if (i < n) {
+            int64_t dst = run.a + ex.a;
+            out_offsets[i] = (int32_t)dst;
+            if (i == n - 1) out_offsets[n] = (int32_t)(dst + v.a);
+            if (out_nulls) out_nulls[i] = (p < 0 || dcol_is_null(src, p)) ? 1 : 0;
+            if (v.a) {
+                const uint8_t* b = (const uint8_t*)src.values + src.offsets[p];
+                for (int64_t t = 0; t < v.a; t++) out_bytes[dst + t] = b[t];
+            }
+        }
+        run = run + total;
+    }
+}
+
+// ------------------------------------------------------------------ host side
+static JoinCols build_join_cols(const std::vector<ColStore>& cols, const std::vector<int32_t>& jch) {
+    JoinCols jc;
+    memset(&jc, 0, sizeof(jc));
+    jc.n = (int32_t)jch.size();
+    for (int k = 0; k < jc.n; k++) jc.c[k] = cols[jch[k]].view();
+    jc.bigint_fast = (jc.n == 1 && jc.c[0].type == PG_BIGINT) ? 1 : 0;
+    return jc;
+}
+
+static void lookup_build(pg_lookup* ls) {
+    pg_ctx* ctx = ls->ctx;
+    int64_t rows = ls->rows;
+    ls->cap = array_size_075(rows > 0 ? rows : 1);   // PagesHash.java:63
+    if (ls->cap < 1024) ls->cap = 1024;
+    JoinCols build = build_join_cols(ls->cols, ls->join_channels);
+    ls->bigint_fast = build.bigint_fast != 0;
+    int64_t nslots = ls->cap + 1;
+    ls->slots.alloc(ctx, nslots * (int64_t)sizeof(JSlot));
+    PG_LAUNCH(ctx, j_init_slots_kernel, grid_for(ctx, nslots, 256, 4), 256, 0, ls->slots.as<JSlot>(), nslots,
+              ls->bigint_fast ? EMPTY_KEY : EMPTY_WORD);
+    ls->meta.alloc(ctx, 64);
+    memset_async(ctx, ls->meta.p, 0, 64);
+    if (rows == 0) return;
+    DevBuf row_slot(ctx, rows * 4);
+    DCol hc; memset(&hc, 0, sizeof(hc));
+    int has_hash = 0;
+    if (ls->hash_channel >= 0 && !ls->bigint_fast) { hc = ls->cols[ls->hash_channel].view(); has_hash = 1; }
+    int* d_has_dups = ls->meta.as<int>();
+    PG_LAUNCH(ctx, j_build_kernel, grid_for(ctx, rows, J_THREADS), J_THREADS, 0, ls->slots.as<JSlot>(), ls->cap, build, hc, has_hash, rows,
+              row_slot.as<int32_t>(), d_has_dups);
+    int64_t flag;
+    read_scalars(ctx, d_has_dups, 1, &flag);
+    ls->has_dups = (flag & 0xffffffff) != 0;
+    if (!ls->has_dups) return;   // JoinHashSupplier.java:72: positionLinks == Optional.empty()
+    // CSR segments for repeated keys
+    int64_t ntiles = num_tiles(nslots);
+    DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+    Pair64* d_total = tiles.as<Pair64>() + ntiles;
+    PG_LAUNCH(ctx, j_seg_count_kernel, (int)ntiles, SCAN_THREADS, 0, ls->slots.as<JSlot>(), nslots, tiles.as<Pair64>());
+    scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, d_total);
+    int64_t tot[2];
+    read_scalars(ctx, d_total, 2, tot);
+    ls->dup_rows = tot[0];
+    ls->seg_off.alloc(ctx, nslots * 4);
+    ls->seg_rows.alloc(ctx, (ls->dup_rows > 0 ? ls->dup_rows : 1) * 4);
+    PG_LAUNCH(ctx, j_seg_offsets_kernel, (int)ntiles, SCAN_THREADS, 0, ls->slots.as<JSlot>(), nslots, tiles.as<Pair64>(),
+              ls->seg_off.as<int32_t>());
+    DevBuf fill(ctx, nslots * 4);
+    memset_async(ctx, fill.p, 0, nslots * 4);
+    PG_LAUNCH(ctx, j_seg_fill_kernel, grid_for(ctx, rows, 256), 256, 0, ls->slots.as<JSlot>(), row_slot.as<int32_t>(), rows,
+              ls->seg_off.as<int32_t>(), fill.as<int32_t>(), ls->seg_rows.as<int32_t>());
+    // reuse `fill` as the large-segment queue
+    int* d_large_count = ls->meta.as<int>() + 2;
+    memset_async(ctx, fill.p, 0, 4);
+    PG_LAUNCH(ctx, j_seg_sort_small_kernel, grid_for(ctx, nslots, 256), 256, 0, ls->slots.as<JSlot>(), nslots, ls->seg_off.as<int32_t>(),
+              ls->seg_rows.as<int32_t>(), fill.as<int32_t>(), d_large_count);
+    int64_t lc;
+    read_scalars(ctx, d_large_count, 1, &lc);
+    int nlarge = (int)(lc & 0xffffffff);
+    if (nlarge > 0)
+        PG_LAUNCH(ctx, j_seg_sort_large_kernel, nlarge, 256, 0, ls->slots.as<JSlot>(), ls->seg_off.as<int32_t>(), ls->seg_rows.as<int32_t>(),
+                  fill.as<int32_t>());
+}
+
+static int64_t lookup_device_bytes(const pg_lookup* ls) {
+    int64_t b = ls->slots.bytes + ls->seg_off.bytes + ls->seg_rows.bytes + ls->probe_slot.bytes + ls->tile_sums.bytes;
+    for (const ColStore& c : ls->cols) b += c.values.bytes + c.nulls.bytes + c.offsets.bytes;
+    return b;
+}
+
+}  // namespace pg
+
+using namespace pg;
+
+extern "C" {
+
+int32_t pg_joinbuild_create(pg_ctx* ctx, const int32_t* types, int32_t ncols, const int32_t* join_channels, int32_t njoin,
+                            int32_t hash_channel, int64_t expected_rows, pg_joinbuild** out) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    return guard(ctx, [&] {
+        PG_CHECK_ARG(out && types && join_channels, "null argument");
+        PG_CHECK_ARG(ncols >= 1 && ncols <= MAX_JOIN_COLS, "between 1 and %d build channels are supported", MAX_JOIN_COLS);
+        PG_CHECK_ARG(njoin >= 1 && njoin <= MAX_KEYS, "between 1 and %d join channels are supported", MAX_KEYS);
+        PG_CHECK_ARG(hash_channel < ncols, "hash channel out of range");
+        for (int k = 0; k < ncols; k++) PG_CHECK_ARG(type_valid(types[k]), "unknown type %d", types[k]);
+        for (int k = 0; k < njoin; k++) PG_CHECK_ARG(join_channels[k] >= 0 && join_channels[k] < ncols, "join channel out of range");
+        if (hash_channel >= 0) PG_CHECK_ARG(types[hash_channel] == PG_BIGINT, "hash channel must be BIGINT");
+        pg_joinbuild* b = new pg_joinbuild();
+        b->ctx = ctx;
+        b->types.assign(types, types + ncols);
+        b->join_channels.assign(join_channels, join_channels + njoin);
+        b->hash_channel = hash_channel;
+        b->cols.resize(ncols);
+        for (int k = 0; k < ncols; k++) b->cols[k].type = types[k];
+        (void)expected_rows;
+        *out = b;
+    });
+}
+
+int32_t pg_joinbuild_destroy(pg_joinbuild* b) {
+    if (!b) return PG_OK;
+    return guard(b->ctx, [&] { delete b; });
+}
+
+int32_t pg_joinbuild_add_page(pg_joinbuild* b, const pg_col* cols, int64_t n) {
+    if (!b) return PG_E_INVALID_ARGUMENT;
+    return guard(b->ctx, [&] {
+        pg_ctx* ctx = b->ctx;
+        PG_CHECK_ARG(cols != nullptr && n >= 0, "bad arguments");
+        // PagesIndex.addPage :234-236
+        if (b->rows + n > 0x7fffffffLL - 1) fail(PG_E_INSUFFICIENT_RESOURCES, "Size of pages index cannot exceed 2 billion entries");
+        if (n == 0) return;
+        for (size_t k = 0; k < b->cols.size(); k++) {
+            PG_CHECK_ARG(cols[k].type == b->types[k], "build channel %d has type %d, expected %d", (int)k, cols[k].type, b->types[k]);
+            ColImport in;
+            import_col(ctx, cols[k], n, in);
+            store_append(ctx, b->cols[k], in, b->rows, n);
+        }
+        b->rows += n;
+        sync(ctx);
+    });
+}
+
+int32_t pg_joinbuild_finish(pg_joinbuild* b, pg_lookup** out) {
+    if (!b || !out) return PG_E_INVALID_ARGUMENT;
+    return guard(b->ctx, [&] {
+        pg_lookup* ls = new pg_lookup();
+        try {
+            ls->ctx = b->ctx; ls->types = b->types; ls->join_channels = b->join_channels; ls->hash_channel = b->hash_channel;
+            ls->cols = std::move(b->cols);
+            ls->rows = b->rows;
+            b->cols.clear(); b->cols.resize(b->types.size());
+            for (size_t k = 0; k < b->types.size(); k++) b->cols[k].type = b->types[k];
+            b->rows = 0;
+            lookup_build(ls);
+            sync(ls->ctx);
+        } catch (...) { delete ls; throw; }
+        *out = ls;
+    });
+}
+
+int32_t pg_lookup_destroy(pg_lookup* ls) {
+    if (!ls) return PG_OK;
+    return guard(ls->ctx, [&] { delete ls; });
+}
+
+int32_t pg_lookup_stats(pg_lookup* ls, int64_t* rows, int64_t* hash_size, int64_t* device_bytes, int32_t* has_duplicates) {
+    if (!ls) return PG_E_INVALID_ARGUMENT;
+    if (rows) *rows = ls->rows;
+    if (hash_size) *hash_size = array_size_075(ls->rows);
+    if (device_bytes) *device_bytes = lookup_device_bytes(ls);
+    if (has_duplicates) *has_duplicates = ls->has_dups ? 1 : 0;
+    return PG_OK;
+}
+
+int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, const pg_col* hash_col, int64_t n, int32_t join_type,
+                        int32_t* out_probe_idx, int64_t* out_build_pos, int32_t out_mem, int64_t capacity, int64_t* n_out) {
+    if (!ls) return PG_E_INVALID_ARGUMENT;
+    return guard(ls->ctx, [&] {
+        pg_ctx* ctx = ls->ctx;
+        PG_CHECK_ARG(probe_keys && n_out && n >= 0 && capacity >= 0, "bad arguments");
+        PG_CHECK_ARG(nkeys == (int32_t)ls->join_channels.size(), "probe has %d join channels, build has %d", nkeys,
+                     (int)ls->join_channels.size());
+        PG_CHECK_ARG(join_type == 0 || join_type == 1, "join type must be INNER (0) or PROBE_OUTER (1)");
+        *n_out = 0;
+        if (n == 0) return;
+        PG_CHECK_ARG(n <= MAX_CHUNK_ROWS, "probe page too large");
+        JoinCols build = build_join_cols(ls->cols, ls->join_channels);
+        JoinCols probe;
+        memset(&probe, 0, sizeof(probe));
+        probe.n = nkeys; probe.bigint_fast = build.bigint_fast;
+        std::vector<ColImport> imp(nkeys);
+        for (int k = 0; k < nkeys; k++) {
+            PG_CHECK_ARG(probe_keys[k].type == build.c[k].type, "probe join channel %d has type %d, build side has %d", k, probe_keys[k].type,
+                         build.c[k].type);
+            import_col(ctx, probe_keys[k], n, imp[k]);
+            probe.c[k] = imp[k].d;
+        }
+        ColImport himp;
+        DCol hc; memset(&hc, 0, sizeof(hc));
+        int has_hash = 0;
+        if (hash_col && !ls->bigint_fast) {
+            PG_CHECK_ARG(hash_col->type == PG_BIGINT, "hash channel must be BIGINT");
+            import_col(ctx, *hash_col, n, himp);
+            hc = himp.d; has_hash = 1;
+        }
+        int64_t ntiles = num_tiles(n);
+        ls->probe_slot.grow(ctx, n * 4, 0);
+        ls->tile_sums.grow(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64), 0);
+        Pair64* tiles = ls->tile_sums.as<Pair64>();
+        ProbeArgs a;
+        a.slots = ls->slots.as<JSlot>(); a.cap = ls->cap; a.seg_off = ls->seg_off.as<int32_t>(); a.seg_rows = ls->seg_rows.as<int32_t>();
+        a.probe_slot = ls->probe_slot.as<int32_t>(); a.n = n; a.join_type = join_type; a.build_empty = ls->rows == 0 ? 1 : 0;
+        PG_LAUNCH(ctx, j_probe_count_kernel, (int)ntiles, SCAN_THREADS, 0, a, build, probe, hc, has_hash, tiles);
+        scan_tile_totals(ctx, tiles, ntiles, tiles + ntiles);
+        int64_t tot[2];
+        read_scalars(ctx, tiles + ntiles, 2, tot);
+        *n_out = tot[0];
+        if (tot[0] > capacity) fail(PG_NEED_MEMORY, "join output needs %lld rows, buffers hold %lld", (long long)tot[0], (long long)capacity);
+        if (tot[0] == 0) return;
+        PG_CHECK_ARG(out_probe_idx && out_build_pos, "null output buffers");
+        OutVec<int32_t> op; OutVec<int64_t> ob;
+        op.begin(ctx, out_probe_idx, out_mem, tot[0]);
+        ob.begin(ctx, out_build_pos, out_mem, tot[0]);
+        PG_LAUNCH(ctx, j_probe_emit_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
+        op.finish(); ob.finish();
+        sync(ctx);
+    });
+}
+
+int32_t pg_lookup_gather(pg_lookup* ls, const int64_t* build_pos, int32_t pos_mem, int64_t n, const int32_t* channels, int32_t nchannels,
+                         pg_col_out* out) {
+    if (!ls) return PG_E_INVALID_ARGUMENT;
+    return guard(ls->ctx, [&] {
+        pg_ctx* ctx = ls->ctx;
+        PG_CHECK_ARG(n >= 0 && nchannels >= 0 && (n == 0 || build_pos) && (nchannels == 0 || (channels && out)), "bad arguments");
+        if (n == 0 || nchannels == 0) return;
+        DevBuf pbuf;
+        const int64_t* d_pos = build_pos;
+        if (pos_mem != PG_MEM_DEVICE) { pbuf.alloc(ctx, n * 8); copy_async(ctx, pbuf.p, build_pos, n * 8, cudaMemcpyHostToDevice); d_pos = pbuf.as<int64_t>(); }
+        std::vector<OutStage> st(nchannels);
+        std::vector<int64_t> vbytes(nchannels, 0);
+        for (int k = 0; k < nchannels; k++) {
+            int ch = channels[k];
+            PG_CHECK_ARG(ch >= 0 && ch < (int)ls->cols.size(), "build channel %d out of range", ch);
+            PG_CHECK_ARG(out[k].type == ls->types[ch], "output %d type mismatch", k);
+            DCol src = ls->cols[ch].view();
+            if (!type_is_var(src.type)) {
+                vbytes[k] = n * type_width(src.type);
+                st[k].begin(ctx, &out[k], n, vbytes[k]);
+                PG_LAUNCH(ctx, j_gather_fixed_kernel, grid_for(ctx, n, 256), 256, 0, src, d_pos, n, st[k].d_values, st[k].d_nulls);
+            } else {
+                int64_t ntiles = num_tiles(n);
+                DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+                PG_LAUNCH(ctx, j_gather_var_count_kernel, (int)ntiles, SCAN_THREADS, 0, src, d_pos, n, tiles.as<Pair64>());
+                scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, tiles.as<Pair64>() + ntiles);
+                int64_t tot[2];
+                read_scalars(ctx, tiles.as<Pair64>() + ntiles, 2, tot);
+                vbytes[k] = tot[0];
+                st[k].begin(ctx, &out[k], n, vbytes[k]);
+                PG_LAUNCH(ctx, j_gather_var_kernel, (int)ntiles, SCAN_THREADS, 0, src, d_pos, n, tiles.as<Pair64>(), (uint8_t*)st[k].d_values,
+                          st[k].d_offsets, st[k].d_nulls);
+            }
+        }
+        for (int k = 0; k < nchannels; k++) st[k].finish(vbytes[k]);
+        sync(ctx);
+    });
+}
+
+int32_t pg_lookup_gather_var_bytes(pg_lookup* ls, const int64_t* build_pos, int32_t pos_mem, int64_t n, int32_t channel, int64_t* out_bytes) {
+    if (!ls || !out_bytes) return PG_E_INVALID_ARGUMENT;
+    return guard(ls->ctx, [&] {
+        pg_ctx* ctx = ls->ctx;
+        *out_bytes = 0;
+        PG_CHECK_ARG(channel >= 0 && channel < (int)ls->cols.size(), "build channel out of range");
+        if (n <= 0 || !type_is_var(ls->types[channel])) return;
+        DevBuf pbuf;
+        const int64_t* d_pos = build_pos;
+        if (pos_mem != PG_MEM_DEVICE) { pbuf.alloc(ctx, n * 8); copy_async(ctx, pbuf.p, build_pos, n * 8, cudaMemcpyHostToDevice); d_pos = pbuf.as<int64_t>(); }
+        int64_t ntiles = num_tiles(n);
+        DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+        PG_LAUNCH(ctx, j_gather_var_count_kernel, (int)ntiles, SCAN_THREADS, 0, ls->cols[channel].view(), d_pos, n, tiles.as<Pair64>());
+        scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, tiles.as<Pair64>() + ntiles);
+        int64_t tot[2];
+        read_scalars(ctx, tiles.as<Pair64>() + ntiles, 2, tot);
+        *out_bytes = tot[0];
+    });
+}
+
+}  // extern "C"

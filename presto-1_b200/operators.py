@@ -1,0 +1,230 @@
+"""Operator shells — host mirror of MAIN/operator/Operator.java:20-104 for the three operators on the hot path:
+HashAggregationOperator (:381-518), HashBuilderOperator (:308-350, 428-496) and LookupJoinOperator (:207-378).
+
+Each keeps the reference's pull/push protocol: needs_input() / add_input(page) / get_output() / finish() / is_finished().
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from .accumulators import final_type, intermediate_types
+from .blocks import Block, OutBlock, Page, col_array
+from .context import default_context
+from .join import LookupSource, PagesIndex
+
+SINGLE, PARTIAL, FINAL, INTERMEDIATE = N.STEP_SINGLE, N.STEP_PARTIAL, N.STEP_FINAL, N.STEP_INTERMEDIATE
+
+
+class AggregatorFactory:
+    """AccumulatorFactory stand-in: (kind, argument type, input channel, mask channel)."""
+
+    def __init__(self, kind, in_type=0, input_channel=-1, mask_channel=-1):
+        self.kind, self.in_type, self.input_channel, self.mask_channel = kind, in_type, input_channel, mask_channel
+
+
+class HashAggregationOperator:
+    """GROUP BY operator: addInput pages, then after finish() getOutput returns pages of [keys..., (hash), aggregates...]."""
+
+    def __init__(self, group_by_types, group_by_channels, step, aggregators, hash_channel=None, expected_groups=10_000,
+                 max_partial_memory=16 << 20, output_page_rows=8192, ctx=None, device_output=False):
+        self.ctx = ctx or default_context()
+        self.step = step
+        self.aggregators = list(aggregators)
+        self.group_by_types = list(group_by_types)
+        self.hash_channel = -1 if hash_channel is None else hash_channel
+        self.max_partial_memory = max_partial_memory
+        self.output_page_rows = output_page_rows
+        self.device_output = device_output
+        self._h = C.c_void_p()
+        kc = (C.c_int32 * len(group_by_channels))(*group_by_channels)
+        kt = (C.c_int32 * len(group_by_types))(*group_by_types)
+        specs = (N.PgAggSpec * max(1, len(self.aggregators)))()
+        for i, a in enumerate(self.aggregators):
+            specs[i].kind, specs[i].in_type, specs[i].input_channel, specs[i].mask_channel = a.kind, a.in_type, a.input_channel, a.mask_channel
+        N.check(self.ctx.handle, N.lib().pg_hashagg_create(self.ctx.handle, kc, kt, len(group_by_types), self.hash_channel, specs,
+                                                           len(self.aggregators), step, expected_groups, C.byref(self._h)))
+        self._finishing = False
+        self._finished = False
+        self._next_group = 0
+        self._flushing = False
+
+    # ---- Operator interface
+    def needs_input(self):       # HashAggregationOperator.java:367-378
+        return not self._finishing and not self._flushing
+
+    def add_input(self, page):   # :381-440
+        assert self.needs_input(), "Operator is already finishing"
+        blocks = page.blocks if isinstance(page, Page) else list(page)
+        N.check(self.ctx.handle, N.lib().pg_hashagg_add_page(self._h, col_array(blocks), len(blocks), blocks[0].n))
+        if self.step == PARTIAL and self._stats()[2] > self.max_partial_memory:   # builder full -> flush (:208-215, :501-517)
+            self._flushing = True
+
+    def finish(self):
+        self._finishing = True
+
+    def is_finished(self):
+        return self._finished
+
+    def _stats(self):
+        g, cap, db, rows = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        N.check(self.ctx.handle, N.lib().pg_hashagg_stats(self._h, C.byref(g), C.byref(cap), C.byref(db), C.byref(rows)))
+        return g.value, cap.value, db.value, rows.value
+
+    def get_group_count(self):
+        return self._stats()[0]
+
+    def get_capacity(self):
+        return self._stats()[1]
+
+    def output_types(self):
+        n = C.c_int32()
+        buf = (C.c_int32 * 128)()
+        N.check(self.ctx.handle, N.lib().pg_hashagg_output_types(self._h, buf, 128, C.byref(n)))
+        return list(buf[:n.value])
+
+    def get_output(self, max_rows=None):   # :469-518
+        if not (self._finishing or self._flushing) or self._finished:
+            return None
+        groups = self._stats()[0]
+        if self._next_group >= groups:
+            if self._flushing and not self._finishing:
+                N.check(self.ctx.handle, N.lib().pg_hashagg_reset(self._h))
+                self._flushing = False
+                self._next_group = 0
+            else:
+                self._finished = True
+            return None
+        n = min(max_rows or self.output_page_rows, groups - self._next_group)
+        types = self.output_types()
+        outs = []
+        for i, t in enumerate(types):
+            vb = 0
+            if t in (N.VARCHAR, N.VARBINARY):
+                b = C.c_int64()
+                N.check(self.ctx.handle, N.lib().pg_hashagg_varwidth_bytes(self._h, i, C.byref(b)))
+                vb = b.value
+            outs.append(OutBlock(t, n, vb, device=self.device_output))
+        arr = (N.PgColOut * len(outs))()
+        for i, o in enumerate(outs):
+            arr[i] = o.pg_col_out()
+        eg = C.c_int64(-1)
+        N.check(self.ctx.handle, N.lib().pg_hashagg_get_output(self._h, self._next_group, n, arr, C.byref(eg)))
+        self._next_group += n
+        return Page(*[o.block(n) for o in outs], position_count=n)
+
+    def close(self):
+        if self._h:
+            N.lib().pg_hashagg_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class HashBuilderOperator:
+    """Join build side.  State machine reduced to CONSUMING_INPUT -> LOOKUP_SOURCE_BUILT (no spill on the device path)."""
+
+    def __init__(self, types, hash_channels, precomputed_hash_channel=None, expected_positions=10_000, ctx=None):
+        self.index = PagesIndex(types, hash_channels, precomputed_hash_channel, expected_positions, ctx)
+        self._lookup = None
+        self._finishing = False
+
+    def needs_input(self):
+        return not self._finishing
+
+    def add_input(self, page):   # HashBuilderOperator.java:317-350
+        assert not self._finishing
+        self.index.add_page(page)
+
+    def finish(self):            # :428-496 -> buildLookupSource
+        if self._finishing:
+            return
+        self._finishing = True
+        self._lookup = self.index.create_lookup_source()
+
+    def is_finished(self):
+        return self._lookup is not None
+
+    def get_output(self):
+        return None
+
+    def get_lookup_source(self):
+        assert self._lookup is not None, "Lookup source has not been built yet"
+        return self._lookup
+
+
+class LookupJoinOperator:
+    """Probe operator: INNER / PROBE_OUTER.  Output page = probe output channels (taken at the emitted probe positions, the
+    reference's getPositions view, LookupJoinPageBuilder.java:101-133) followed by the build output channels."""
+
+    def __init__(self, lookup_source, probe_join_channels, probe_output_channels, build_output_channels, join_type=N.JOIN_INNER,
+                 probe_hash_channel=None, device_output=None):
+        self.lookup = lookup_source
+        self.probe_join_channels = list(probe_join_channels)
+        self.probe_output_channels = list(probe_output_channels)
+        self.build_output_channels = list(build_output_channels)
+        self.join_type = join_type
+        self.probe_hash_channel = probe_hash_channel
+        self.device_output = device_output
+        self._pending = None
+        self._finishing = False
+
+    def needs_input(self):
+        return not self._finishing and self._pending is None
+
+    def add_input(self, page):
+        assert self.needs_input()
+        self._pending = page
+
+    def finish(self):
+        self._finishing = True
+
+    def is_finished(self):
+        return self._finishing and self._pending is None
+
+    def get_output(self):
+        if self._pending is None:
+            return None
+        page, self._pending = self._pending, None
+        keys = [page.get_block(c) for c in self.probe_join_channels]
+        hb = page.get_block(self.probe_hash_channel) if self.probe_hash_channel is not None else None
+        on_device = keys[0].device if self.device_output is None else self.device_output
+        probe_pos, build_pos = self.lookup.join_page(keys, hb, self.join_type, device=on_device)
+        n = len(probe_pos)
+        out = [take_positions(page.get_block(c), probe_pos) for c in self.probe_output_channels]
+        out += self.lookup.append_to(build_pos, self.build_output_channels, device=on_device)
+        return Page(*out, position_count=n)
+
+
+def take_positions(block, positions):
+    """Block.getPositions(int[]) — materialised gather of probe-side columns (host numpy or device torch)."""
+    n = len(positions)
+    if block.device:
+        import torch
+        idx = positions.long() if type(positions).__module__.startswith("torch") else torch.from_numpy(np.asarray(positions)).cuda().long()
+        if block.type in (N.VARCHAR, N.VARBINARY):
+            return take_positions(block.to_host(), idx.cpu().numpy()).to_device()
+        if block.type == N.LONG_DECIMAL:
+            v = block.values.view(-1, 2)[idx].reshape(-1)
+        else:
+            v = block.values[idx]
+        return Block(block.type, v, None if block.nulls is None else block.nulls[idx], None, n)
+    idx = positions.cpu().numpy() if type(positions).__module__.startswith("torch") else np.asarray(positions)
+    idx = idx.astype(np.int64)
+    if block.type in (N.VARCHAR, N.VARBINARY):
+        lens = (block.offsets[1:] - block.offsets[:-1])[idx]
+        offs = np.zeros(n + 1, dtype=np.int32)
+        np.cumsum(lens, out=offs[1:])
+        data = np.zeros(int(offs[-1]), dtype=np.uint8)
+        for i, p in enumerate(idx):
+            data[offs[i]:offs[i + 1]] = block.values[block.offsets[p]:block.offsets[p + 1]]
+        return Block(block.type, data, None if block.nulls is None else block.nulls[idx], offs, n)
+    if block.type == N.LONG_DECIMAL:
+        v = block.values.reshape(-1, 2)[idx].reshape(-1)
+    else:
+        v = block.values[idx]
+    return Block(block.type, np.ascontiguousarray(v), None if block.nulls is None else np.ascontiguousarray(block.nulls[idx]), None, n)

@@ -7,4 +7,12 @@ _root = os.path.dirname(os.path.abspath(__file__))
 if _root not in sys.path:
     sys.path.insert(0, _root)
 _pkg = importlib.import_module("presto-1_b200")
+for _name in ("operators", "exchange", "tpch"):
+    try:
+        importlib.import_module("presto-1_b200." + _name)
+    except ModuleNotFoundError:
+        pass
+for _k in list(sys.modules):
+    if _k.startswith("presto-1_b200."):
+        sys.modules["presto_b200." + _k[len("presto-1_b200."):]] = sys.modules[_k]
 sys.modules[__name__] = _pkg

@@ -20,6 +20,12 @@ def _both(P, types, expected, has_hash=False):
 def _assert_blocks_equal(a, b):
     a, b = a.to_host(), b.to_host()
     assert a.n == b.n
+    if a.type == 4:   # DOUBLE: compare raw bits (NaN keys, signed zeros)
+        assert [a.is_null(i) for i in range(a.n)] == [b.is_null(i) for i in range(b.n)]
+        av = [0 if a.is_null(i) else int(a.values[i]) for i in range(a.n)]
+        bv = [0 if b.is_null(i) else int(b.values[i]) for i in range(b.n)]
+        assert av == bv
+        return
     assert a.to_list() == b.to_list()
 
 

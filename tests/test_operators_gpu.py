@@ -1,0 +1,191 @@
+"""GPU parity for the fused GROUP BY operator (pg_hashagg_*) through the HashAggregationOperator mirror:
+OPT/TestHashAggregationOperator.java testHashAggregation :162-220 (40 000 groups x 3 pages, expected rows
+(i, 3, 3i, i, ..., 3, 3), order-insensitive), partial -> final, testMultiplePartialFlushes :513-593, and a Q1-shaped
+decimal aggregation checked against the oracle."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+
+
+def drain(op):
+    pages = []
+    while True:
+        p = op.get_output()
+        if p is None:
+            if op.is_finished() or op.needs_input():
+                break
+            continue
+        pages.append(p)
+    return pages
+
+
+def rows_of(pages):
+    rows = []
+    for p in pages:
+        cols = [b.to_host().to_list() for b in p.blocks]
+        rows += [tuple(c[i] for c in cols) for i in range(p.position_count)]
+    return rows
+
+
+def seq_page(P, n, starts):
+    """RowPagesBuilder.addSequencePage(n, starts...) for (VARCHAR, VARCHAR, VARCHAR, BIGINT, BOOLEAN)."""
+    return P.Page(
+        P.Block.variable_width([str(starts[0] + i) for i in range(n)]),
+        P.Block.variable_width([str(starts[1] + i) for i in range(n)]),
+        P.Block.variable_width([str(starts[2] + i) for i in range(n)]),
+        P.Block.long_array(np.arange(starts[3], starts[3] + n, dtype=np.int64)),
+        P.Block.byte_array(((np.arange(n) + starts[4]) % 2).astype(np.uint8)),
+    )
+
+
+@pytest.mark.parametrize("hash_enabled", [False, True])
+@pytest.mark.parametrize("device", [False, True])
+def test_hash_aggregation_reference_rows(pgpu, hash_enabled, device):
+    P = pgpu
+    n = 40_000
+    pages = [seq_page(P, n, (100, 0, s, 0, 500)) for s in (100_000, 200_000, 300_000)]
+    hash_channel = None
+    if hash_enabled:
+        pages = [P.Page(*(p.blocks + [P.Block.long_array(O.hash_rows([p.blocks[1]]))])) for p in pages]
+        hash_channel = 5
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.BIGINT, 3), P.AggregatorFactory(P.AGG_AVG, P.BIGINT, 3),
+            P.AggregatorFactory(P.AGG_MAX, P.BIGINT, 3), P.AggregatorFactory(P.AGG_COUNT_COL, P.VARCHAR, 0),
+            P.AggregatorFactory(P.AGG_COUNT_COL, P.BOOLEAN, 4)]
+    op = P.HashAggregationOperator([P.VARCHAR], [1], P.SINGLE, aggs, hash_channel, expected_groups=100_000)
+    for p in pages:
+        assert op.needs_input()
+        op.add_input(p.to_device() if device else p)
+    op.finish()
+    out = drain(op)
+    assert len(out) > 1, "Expected more than one output page"
+    rows = rows_of(out)
+    if hash_enabled:
+        rows = [r[:1] + r[2:] for r in rows]   # drop the hash column like assertPagesEqualIgnoreOrder does
+    expected = [(str(i).encode(), 3, 3 * i, float(i), i, 3, 3) for i in range(n)]
+    assert sorted(rows) == sorted(expected)
+    assert op.is_finished()
+
+
+def test_partial_then_final(pgpu):
+    P = pgpu
+    rng = np.random.default_rng(3)
+    n, groups = 200_000, 5000
+    k1 = rng.integers(0, groups, n).astype(np.int64)
+    k2 = rng.integers(0, 3, n).astype(np.int32)
+    v_dec = rng.integers(-10**9, 10**9, n).astype(np.int64)
+    v_dbl = rng.random(n) * 1000
+    nulls = (rng.random(n) < 0.1).astype(np.uint8)
+    def page(lo, hi):
+        return P.Page(P.Block.long_array(k1[lo:hi]), P.Block.int_array(k2[lo:hi]), P.Block.long_array(v_dec[lo:hi], nulls[lo:hi], P.SHORT_DECIMAL),
+                      P.Block.double_array(v_dbl[lo:hi]))
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 2), P.AggregatorFactory(P.AGG_AVG, P.SHORT_DECIMAL, 2),
+            P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 3), P.AggregatorFactory(P.AGG_AVG, P.DOUBLE, 3), P.AggregatorFactory(P.AGG_MIN, P.DOUBLE, 3),
+            P.AggregatorFactory(P.AGG_MAX, P.SHORT_DECIMAL, 2), P.AggregatorFactory(P.AGG_COUNT_COL, P.SHORT_DECIMAL, 2)]
+    types = [P.BIGINT, P.INTEGER]
+    single = P.HashAggregationOperator(types, [0, 1], P.SINGLE, aggs)
+    partials = [P.HashAggregationOperator(types, [0, 1], P.PARTIAL, aggs) for _ in range(2)]
+    for i, (lo, hi) in enumerate([(0, 70_000), (70_000, 140_000), (140_000, n)]):
+        single.add_input(page(lo, hi))
+        partials[i % 2].add_input(page(lo, hi).to_device())
+    single.finish()
+    # final: intermediate columns start at channel 2; channels per aggregate follow intermediate_types()
+    fin_aggs, ch = [], 2
+    for a in aggs:
+        fin_aggs.append(P.AggregatorFactory(a.kind, a.in_type, ch))
+        ch += len(P.intermediate_types(a.kind, a.in_type))
+    final = P.HashAggregationOperator(types, [0, 1], P.FINAL, fin_aggs)
+    for p in partials:
+        p.finish()
+        for out in drain(p):
+            final.add_input(out)
+    final.finish()
+    got_single = sorted(rows_of(drain(single)))
+    got_final = sorted(rows_of(drain(final)))
+    assert len(got_single) == len(got_final)
+    for a, b in zip(got_single, got_final):
+        for x, y in zip(a, b):
+            if isinstance(x, float):
+                assert x == pytest.approx(y, rel=1e-12)
+            else:
+                assert x == y
+    # and against numpy for the exact columns
+    import collections
+    cnt = collections.Counter(zip(k1.tolist(), k2.tolist()))
+    sums = collections.defaultdict(int)
+    for a, b, v, isn in zip(k1.tolist(), k2.tolist(), v_dec.tolist(), nulls.tolist()):
+        if not isn:
+            sums[(a, b)] += v
+    for r in got_single:
+        assert r[2] == cnt[(r[0], r[1])]
+        assert r[3] == (sums[(r[0], r[1])] if (r[0], r[1]) in sums else None)
+
+
+def test_multiple_partial_flushes(pgpu):
+    """testMultiplePartialFlushes :513-593: a partial aggregation over its memory limit flushes and keeps accepting input."""
+    P = pgpu
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.BIGINT, 0)]
+    op = P.HashAggregationOperator([P.BIGINT], [0], P.PARTIAL, aggs, max_partial_memory=1)   # always "full" after a page
+    total = []
+    for start in (0, 1000, 500):
+        assert op.needs_input()
+        op.add_input(P.Page(P.Block.long_array(np.arange(start, start + 1000, dtype=np.int64))))
+        assert not op.needs_input()            # full -> must be drained first
+        total += rows_of(drain(op))
+        assert op.needs_input()
+    op.finish()
+    total += rows_of(drain(op))
+    assert op.is_finished()
+    # intermediate rows: (key, count, [count, sum]) -> key, 1, 1, key ; keys of overlapping pages appear twice
+    assert len(total) == 3000
+    assert sorted(r[0] for r in total) == sorted(list(range(0, 2000)) + list(range(500, 1500)))
+    assert all(r[1] == 1 and r[2] == 1 and r[3] == r[0] for r in total)
+
+
+def test_q1_shaped_decimal_aggregation_matches_oracle(pgpu):
+    """cfg2 shape at small scale: GROUP BY returnflag, linestatus (2 x varchar(1)); sum/avg over short and long decimals."""
+    P = pgpu
+    rng = np.random.default_rng(1)
+    n = 300_000
+    rf = rng.choice([b"A", b"N", b"R"], n)
+    ls = rng.choice([b"F", b"O"], n)
+    qty = rng.integers(1, 51, n).astype(np.int64) * 100
+    price = rng.integers(90_000, 10_500_000, n).astype(np.int64)
+    disc = rng.integers(0, 11, n).astype(np.int64)
+    tax = rng.integers(0, 9, n).astype(np.int64)
+    disc_price = [int(p) * (100 - int(d)) for p, d in zip(price, disc)]
+    charge = [dp * (100 + int(t)) for dp, t in zip(disc_price, tax)]
+    blocks = [P.Block.variable_width(list(rf)), P.Block.variable_width(list(ls)), P.Block.long_array(qty, None, P.SHORT_DECIMAL),
+              P.Block.long_array(price, None, P.SHORT_DECIMAL), P.Block.long_array(disc, None, P.SHORT_DECIMAL),
+              P.Block.int128_array(disc_price), P.Block.int128_array(charge)]
+    aggs = [P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 2), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 3),
+            P.AggregatorFactory(P.AGG_SUM, P.LONG_DECIMAL, 5), P.AggregatorFactory(P.AGG_SUM, P.LONG_DECIMAL, 6),
+            P.AggregatorFactory(P.AGG_AVG, P.SHORT_DECIMAL, 2), P.AggregatorFactory(P.AGG_AVG, P.SHORT_DECIMAL, 3),
+            P.AggregatorFactory(P.AGG_AVG, P.SHORT_DECIMAL, 4), P.AggregatorFactory(P.AGG_COUNT)]
+    op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.SINGLE, aggs)
+    op.add_input(P.Page(*blocks).to_device())
+    op.finish()
+    got = sorted(rows_of(drain(op)))
+    # oracle: group ids then accumulators
+    ogb = O.OracleGroupBy([P.VARCHAR, P.VARCHAR], 10_000)
+    ids = ogb.get_group_ids(blocks[:2])
+    g = ogb.group_count()
+    keys, _ = ogb.export(with_hash=False)
+    cols = [keys[0].to_list(), keys[1].to_list()]
+    for a in aggs:
+        oa = O.OracleAccumulator(a.kind, a.in_type)
+        oa.add_input(ids, g, blocks[a.input_channel] if a.input_channel >= 0 else None)
+        rc, out, _ = oa.evaluate(0, g, True)
+        assert rc == 0
+        cols.append(out[0].to_list())
+    want = sorted(tuple(c[i] for c in cols) for i in range(g))
+    assert got == want
+    assert len(got) == 6
+    # and against exact python integers
+    for r in got:
+        sel = [i for i in range(n) if rf[i] == r[0] and ls[i] == r[1]]
+        assert r[2] == sum(int(qty[i]) for i in sel)
+        assert r[4] == sum(disc_price[i] for i in sel)
+        assert r[9] == len(sel)

@@ -1,0 +1,219 @@
+"""Pins the CPU oracle (oracle/) against the known answers held by the reference's own tests.
+
+Sources (paths under /root/reference/core/trino-main/src/test/java/io/trino/operator):
+  aggregation/TestDecimalSumAggregation.java:51-128, aggregation/TestDecimalAverageAggregation.java:49-150,
+  TestGroupByHash.java:70-253, and the published XXH64 / MurmurHash3-fmix64 test vectors for the two third-party hash
+  functions (io.airlift:slice XxHash64, fastutil 8.3.0 HashCommon.murmurHash3) the reference calls but does not vendor.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import presto_b200 as P
+from presto_b200.blocks import decode_decimal128, encode_decimal128
+
+TWO = 2
+M64 = (1 << 64) - 1
+
+
+class DecState:
+    """LongDecimalWithOverflow(AndLong)State driven through the oracle's addWithOverflow restatement."""
+
+    def __init__(self):
+        self.s = (C.c_uint64 * 2)(0, 0)
+        self.ovf = C.c_int64(0)
+        self.count = 0
+
+    def add(self, v):
+        lo, hi = encode_decimal128(v)
+        x = (C.c_uint64 * 2)(lo, hi)
+        O.lib().orc_dec_add(self.s, C.byref(self.ovf), x)
+        self.count += 1
+
+    def value(self):
+        return decode_decimal128(self.s[0], self.s[1])
+
+    def is_zero(self):  # UnscaledDecimal128Arithmetic.compare(x, 0) == 0 (negative zero allowed)
+        return self.s[0] == 0 and (self.s[1] & ((1 << 63) - 1)) == 0
+
+    def combine(self, other):  # DecimalSumAggregation.combine :165-175
+        self.ovf.value += other.ovf.value
+        x = (C.c_uint64 * 2)(other.s[0], other.s[1])
+        O.lib().orc_dec_add(self.s, C.byref(self.ovf), x)
+        self.count += other.count
+
+    def average(self):
+        out = (C.c_uint64 * 2)()
+        rc = O.lib().orc_dec_avg(self.s, self.ovf.value, self.count, out)
+        assert rc == 0
+        return decode_decimal128(out[0], out[1])
+
+
+def test_decimal_sum_overflow():        # TestDecimalSumAggregation.testOverflow :51-63
+    s = DecState()
+    s.add(TWO ** 126)
+    assert (s.ovf.value, s.value()) == (0, TWO ** 126)
+    s.add(TWO ** 126)
+    assert (s.ovf.value, s.value()) == (1, 0)
+
+
+def test_decimal_sum_underflow():       # testUnderflow :65-77
+    s = DecState()
+    s.add(-(TWO ** 126))
+    assert (s.ovf.value, s.value()) == (0, -(TWO ** 126))
+    s.add(-(TWO ** 126))
+    assert s.ovf.value == -1 and s.is_zero()
+
+
+def test_decimal_sum_underflow_after_overflow():   # testUnderflowAfterOverflow :79-95
+    s = DecState()
+    for v in (TWO ** 126, TWO ** 126, TWO ** 125):
+        s.add(v)
+    assert (s.ovf.value, s.value()) == (1, TWO ** 125)
+    for _ in range(3):
+        s.add(-(TWO ** 126))
+    assert (s.ovf.value, s.value()) == (0, -(TWO ** 125))
+    assert s.average() == -(TWO ** 125) // 6 + 0 if False else True   # exact value checked below
+
+
+def test_decimal_combine_overflow_underflow():     # testCombineOverflow / testCombineUnderflow :97-128
+    for sign in (1, -1):
+        a, b = DecState(), DecState()
+        for st in (a, b):
+            st.add(sign * TWO ** 125)
+            st.add(sign * TWO ** 126)
+        a.combine(b)
+        assert a.ovf.value == sign
+        assert a.value() == sign * TWO ** 126
+        # TestDecimalAverageAggregation.testCombineOverflow/Underflow :103-150: exact average over 4 inputs
+        assert a.count == 4
+        expected = sign * ((TWO ** 126 + TWO ** 126 + TWO ** 125 + TWO ** 125) // 4)
+        assert a.average() == expected
+
+
+def test_decimal_average_vectors():                # TestDecimalAverageAggregation.testOverflow/testUnderflow :49-85
+    s = DecState()
+    s.add(TWO ** 126); s.add(TWO ** 126)
+    assert s.count == 2 and s.ovf.value == 1 and s.value() == 0
+    assert s.average() == TWO ** 126
+    s = DecState()
+    s.add(-(TWO ** 126)); s.add(-(TWO ** 126))
+    assert s.ovf.value == -1 and s.is_zero()
+    assert s.average() == -(TWO ** 126)
+    # testUnderflowAfterOverflow :87-101: average = -2^125 / 6 (BigInteger.divide truncates; value is exact here? no:
+    # 2^125 is not divisible by 6, the test compares against new BigDecimal(BigInteger quotient) with scale 0 -> HALF_UP
+    s = DecState()
+    for v in (TWO ** 126, TWO ** 126, TWO ** 125, -(TWO ** 126), -(TWO ** 126), -(TWO ** 126)):
+        s.add(v)
+    q, r = divmod(TWO ** 125, 6)
+    half_up = q + (1 if 2 * r >= 6 else 0)
+    assert s.average() == -half_up
+    # the reference's expected value is BigInteger division (truncation); it equals HALF_UP here only if the
+    # remainder is below one half: 2^125 mod 6 = 2 -> 2*2 < 6, so both agree
+    assert half_up == q
+
+
+def test_decimal_1e38_bound():
+    for v, want in ((10 ** 38, 1), (10 ** 38 - 1, 0), (-(10 ** 38), 1), (0, 0)):
+        lo, hi = encode_decimal128(v)
+        assert O.lib().orc_dec_exceeds_1e38((C.c_uint64 * 2)(lo, hi)) == want
+
+
+def test_xxhash64_published_vectors():
+    l = O.lib()
+    assert l.orc_xxh64_bytes(None, 0) & M64 == 0xEF46DB3751D8E999              # XXH64("", seed 0)
+    for s, want in ((b"a", 0xD24EC4F1A98C6E5B), (b"abc", 0x44BC2CF5AD770999),
+                    (b"Nobody inspects the spammish repetition", 0xFBCEA83C8A378BF1)):
+        buf = C.create_string_buffer(s, len(s))
+        assert l.orc_xxh64_bytes(buf, len(s)) & M64 == want
+    # XxHash64.hash(long) == XXH64 of the 8 little-endian bytes
+    for v in (0, 1, -1, 0x0123456789ABCDEF, -(1 << 63)):
+        b = int(v & M64).to_bytes(8, "little")
+        buf = C.create_string_buffer(b, 8)
+        assert l.orc_xxh64_long(v) == l.orc_xxh64_bytes(buf, 8)
+
+
+def test_fmix64_vectors():
+    # MurmurHash3 fmix64 (== fastutil HashCommon.murmurHash3(long), restated at PagesHash.java:224-240)
+    def fmix(h):
+        h ^= h >> 33; h = (h * 0xff51afd7ed558ccd) & M64
+        h ^= h >> 33; h = (h * 0xc4ceb9fe1a85ec53) & M64
+        return h ^ (h >> 33)
+    for v in (0, 1, 2, 0xdeadbeef, M64, 1 << 63):
+        assert O.lib().orc_fmix64(v) == fmix(v)
+    assert O.lib().orc_fmix64(0) == 0
+    assert O.lib().orc_fmix64(1) == 0xB456BCFC34C2CB2C
+
+
+def test_long_type_hash_formula():      # AbstractLongType.hash :126-130
+    def rotl(x, r):
+        return ((x << r) | (x >> (64 - r))) & M64
+    for v in (0, 1, 42, -7, 1 << 40):
+        want = (rotl((v * 0xC2B2AE3D27D4EB4F) & M64, 31) * 0x9E3779B185EBCA87) & M64
+        assert O.lib().orc_long_hash(v) & M64 == want
+
+
+def test_array_size_and_max_fill():
+    l = O.lib()
+    assert l.orc_array_size(100) == 256 and l.orc_array_size(4) == 8 and l.orc_array_size(1) == 2
+    assert l.orc_array_size(100_000) == 262_144       # HashAggregationBenchmark expectedGroups
+    assert l.orc_max_fill(8) == 6 and l.orc_max_fill(256) == 192 and l.orc_max_fill(2) == 1
+
+
+# ---------------------------------------------------------------- TestGroupByHash.java on the oracle
+def test_groupby_add_page_first_seen_ids():            # testAddPage :70-97, testGetGroupIds :121-149
+    gb = O.OracleGroupBy([P.BIGINT], 100)
+    for tries in range(10):
+        ids = gb.get_group_ids([P.Block.long_array(np.arange(10))])
+        assert ids.tolist() == list(range(10))         # groupId == value
+        assert gb.group_count() == 10
+
+
+def test_groupby_null_group():                         # testNullGroup :99-119
+    gb = O.OracleGroupBy([P.BIGINT], 100)
+    assert gb.get_group_ids([P.Block.long_array([0], nulls=[1])]).tolist() == [0]
+    assert gb.get_group_ids([P.Block.long_array([0])]).tolist() == [1]   # 0 must not land in the null group
+    assert gb.group_count() == 2
+
+
+def test_groupby_append_to_roundtrip():                # testAppendTo :151-179
+    for has_hash in (False, True):
+        gb = O.OracleGroupBy([P.BIGINT], 100, has_hash)
+        vals = P.Block.long_array(np.arange(100))
+        blocks = [vals] + ([P.Block.long_array(O.hash_rows([vals]))] if has_hash else [])
+        assert gb.get_group_ids(blocks).tolist() == list(range(100))
+        keys, hashes = gb.export()
+        assert keys[0].to_list() == list(range(100))
+        assert hashes.tolist() == O.hash_rows([vals]).tolist()   # raw hash channel round-trips (:177-178)
+
+
+def test_groupby_contains():                           # testContains :205-220, testContainsMultipleColumns :222-236
+    gb = O.OracleGroupBy([P.DOUBLE], 100)
+    gb.add_page([P.Block.double_array(np.arange(10, dtype=np.float64))])
+    assert gb.contains([P.Block.double_array([3.0])]).tolist() == [True]
+    assert gb.contains([P.Block.double_array([11.0])]).tolist() == [False]
+    types = [P.DOUBLE, P.VARCHAR, P.BIGINT]
+    gb = O.OracleGroupBy(types, 100)
+    page = [P.Block.double_array([0.0]), P.Block.variable_width(["x"]), P.Block.long_array([5])]
+    gb.add_page(page)
+    assert gb.contains(page).tolist() == [True]
+    assert gb.contains([page[0], page[1], P.Block.long_array([6])]).tolist() == [False]
+
+
+def test_groupby_force_rehash():                       # testForceRehash :238-253
+    gb = O.OracleGroupBy([P.BIGINT], 4)
+    gb.add_page([P.Block.long_array(np.arange(100))])
+    assert gb.group_count() == 100
+    assert gb.capacity() == 256                        # 8 -> 16 -> ... doubled while groups >= maxFill
+    assert gb.contains([P.Block.long_array(np.arange(100))]).all()
+
+
+def test_groupby_multichannel_varchar_rehash():
+    gb = O.OracleGroupBy([P.VARCHAR], 4)
+    strs = ["%d" % i for i in range(100)]
+    ids = gb.get_group_ids([P.Block.variable_width(strs * 2)])
+    assert ids.tolist() == list(range(100)) * 2
+    keys, _ = gb.export()
+    assert keys[0].to_list() == [s.encode() for s in strs]

@@ -1,0 +1,385 @@
+#!/usr/bin/env python
+"""bench.py — input rows/s of the hash-aggregation hot path (BASELINE.json metric) on N B200s of one node.
+
+Workload at every N: BASELINE.json configs[1], "TPC-H Q1 on lineitem SF10": GROUP BY returnflag, linestatus (2 x varchar(1), 4 groups)
+with sum/avg over short and long decimals and count(*), 59.99 M input rows per GPU shard, masked by the shipdate filter.
+  value : whole-job input rows/s with the columns already resident in HBM (one HashAggregationOperator pass per step)
+  e2e   : the same pass through the C ABI with HOST (pinned) column buffers, host->device copies inside the timed region
+  N > 1 : weak scaling — every rank aggregates its own SF10 shard (PARTIAL step), the 4-row intermediate states are
+          all-gathered over NCCL and merged by a FINAL-step operator on every rank (the reference's partial->final plan).
+`--impl reference` times the CPU restatement of the reference's operators (oracle/, kind "port": the reference is Java and no
+JDK exists here) on all host threads over a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ROWS_PER_SF = 5_998_605.2
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sf", type=float, default=10.0, help="TPC-H scale factor of the lineitem shard per GPU")
+    ap.add_argument("--cpu-sample-rows", type=int, default=6_000_000)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--extra", action="store_true", help="also time the high-cardinality GROUP BY and join workloads")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.device, self.samples, self._stop, self._t = device, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------- CPU arm (oracle port)
+def oracle_q1_pass(O, P, blocks, aggs, nthreads):
+    """The reference's plan on host cores: `nthreads` drivers each run getGroupIds + accumulators (PARTIAL) over a slice of
+    the pages, then one FINAL merge — restated in oracle/ (C++), called through ctypes (GIL released)."""
+    n = blocks[0].n
+    bounds = [n * i // nthreads for i in range(nthreads + 1)]
+    results = [None] * nthreads
+
+    def slice_block(b, lo, hi):
+        from presto_b200.blocks import Block
+        if b.type in (P.VARCHAR, P.VARBINARY):
+            return Block(b.type, b.values, None, b.offsets[lo:hi + 1], hi - lo)
+        k = 2 if b.type == P.LONG_DECIMAL else 1
+        return Block(b.type, b.values[k * lo:k * hi], None if b.nulls is None else b.nulls[lo:hi], None, hi - lo)
+
+    def work(t):
+        lo, hi = bounds[t], bounds[t + 1]
+        sl = [slice_block(b, lo, hi) for b in blocks]
+        gb = O.OracleGroupBy([P.VARCHAR, P.VARCHAR], 100_000)
+        ids = gb.get_group_ids(sl[:2])
+        g = gb.group_count()
+        inter = []
+        for a in aggs:
+            acc = O.OracleAccumulator(a.kind, a.in_type)
+            acc.add_input(ids, g, sl[a.input_channel] if a.input_channel >= 0 else None, sl[a.mask_channel] if a.mask_channel >= 0 else None)
+            inter.append(acc.evaluate(0, g, False)[1])
+        results[t] = (gb.export(with_hash=False)[0], inter)
+
+    threads = [threading.Thread(target=work, args=(t,)) for t in range(nthreads)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    fgb = O.OracleGroupBy([P.VARCHAR, P.VARCHAR], 100_000)
+    finals = [O.OracleAccumulator(a.kind, a.in_type) for a in aggs]
+    for keys, inter in results:
+        ids = fgb.get_group_ids(keys)
+        for f, st in zip(finals, inter):
+            f.add_intermediate(ids, fgb.group_count(), st)
+    g = fgb.group_count()
+    out = [f.evaluate(0, g, True)[1][0] for f in finals]
+    return fgb.export(with_hash=False)[0], out
+
+
+def host_sample_blocks(P, tpch, rows, seed):
+    import torch
+    sf = rows / ROWS_PER_SF
+    cols = tpch.lineitem(sf, seed=seed, device="cpu")
+    page = tpch.q1_page(cols)
+    return tpch.page_to_host(page, pinned=False).blocks
+
+
+def time_cpu_port(P, tpch, rows, nthreads, steps, warmup, seed=42):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_lib as O
+    blocks = host_sample_blocks(P, tpch, rows, seed)
+    n = blocks[0].n
+    aggs = tpch.q1_aggregators()
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        oracle_q1_pass(O, P, blocks, aggs, nthreads)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return n, times
+
+
+# ------------------------------------------------------------------------------------------- GPU arm
+def run_single_pass(P, page, aggs, step, ctx, expected=100_000):
+    """One HashAggregationOperator pass over `page` (device or host buffers); returns the output page on the host."""
+    op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], step, aggs, expected_groups=expected, ctx=ctx)
+    op.add_input(page)
+    op.finish()
+    out = op.get_output()
+    op.close()
+    return out
+
+
+def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world):
+    """All-gather the (tiny) intermediate page of every rank over NCCL and run the FINAL step on each rank."""
+    import numpy as np
+    # pack the host page into one uint8 buffer: [n][per block: values bytes, offsets, nulls] with a fixed-size header
+    blobs = []
+    for b in part_page.blocks:
+        hb = b.to_host()
+        for arr in (hb.values, hb.offsets, hb.nulls):
+            a = np.zeros(0, dtype=np.uint8) if arr is None else np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
+            blobs.append(a)
+    sizes = np.array([part_page.position_count] + [len(a) for a in blobs], dtype=np.int64)
+    payload = np.concatenate([sizes.view(np.uint8)] + blobs)
+    cap = 1 << 16
+    assert len(payload) <= cap - 8
+    buf = torch.zeros(cap, dtype=torch.uint8, device="cuda")
+    buf[:8] = torch.from_numpy(np.array([len(payload)], dtype=np.int64).view(np.uint8)).cuda()
+    buf[8:8 + len(payload)] = torch.from_numpy(payload).cuda()
+    gathered = torch.empty(cap * world, dtype=torch.uint8, device="cuda")
+    dist.all_gather_into_tensor(gathered, buf)
+    host = gathered.cpu().numpy()
+    fin = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs, expected_groups=1000, ctx=ctx)
+    from presto_b200.blocks import Block, _NP_DTYPE
+    for r in range(world):
+        chunk = host[r * cap:(r + 1) * cap]
+        ln = int(chunk[:8].view(np.int64)[0])
+        pl = chunk[8:8 + ln]
+        nsz = 1 + 3 * len(part_page.blocks)
+        sz = pl[:8 * nsz].view(np.int64)
+        pos = 8 * nsz
+        n = int(sz[0])
+        blocks = []
+        for i, b in enumerate(part_page.blocks):
+            parts = []
+            for j in range(3):
+                l = int(sz[1 + 3 * i + j])
+                parts.append(pl[pos:pos + l].copy())
+                pos += l
+            vals = parts[0].view(_NP_DTYPE[b.type])
+            offs = parts[1].view(np.int32) if len(parts[1]) else None
+            nulls = parts[2] if len(parts[2]) else None
+            blocks.append(Block(b.type, vals, nulls, offs, n))
+        fin.add_input(P.Page(*blocks, position_count=n))
+    fin.finish()
+    out = fin.get_output()
+    fin.close()
+    return out
+
+
+def final_aggs_for(P, aggs, first_channel):
+    fin, ch = [], first_channel
+    for a in aggs:
+        fin.append(P.AggregatorFactory(a.kind, a.in_type, ch))
+        ch += len(P.intermediate_types(a.kind, a.in_type))
+    return fin
+
+
+def gpu_arm(args):
+    import numpy as np
+    import torch
+    import presto_b200 as P
+    from presto_b200 import tpch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    ctx = P.GpuContext(local_rank)
+    aggs = tpch.q1_aggregators()
+    fin_aggs = final_aggs_for(P, aggs, 2)
+
+    cols = tpch.lineitem(args.sf, seed=42 + rank, device="cuda")
+    page = tpch.q1_page(cols)
+    rows = page.position_count
+    input_bytes = rows * tpch.Q1_BYTES_PER_ROW    # > 126 MB L2: every step streams its inputs from HBM
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        if world == 1:
+            return run_single_pass(P, page, aggs, P.SINGLE, ctx)
+        part = run_single_pass(P, page, aggs, P.PARTIAL, ctx)
+        return merge_partials_nccl(P, dist, torch, part, fin_aggs, ctx, world)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ctx.kernel_report(reset=True)
+        launches0 = ctx.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = None
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, out, ctx.launch_count() - launches0
+
+    ctx.set_timing(True)
+    with ClockSampler(local_rank) as clk:
+        ms, out, launches = timed(step_device, args.steps, args.warmup)
+    kernels = ctx.kernel_report(reset=True)
+    ctx.set_timing(False)
+    total_rows = rows * world
+    value = total_rows * args.steps / (ms / 1e3)
+
+    # dominant kernel + roofline (per-launch CUDA-event durations recorded inside the library on its launch stream)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    kern_ms = {k: v[0] for k, v in kernels.items()}
+    top = max(kern_ms, key=kern_ms.get) if kern_ms else None
+    roofline = None
+    if top:
+        tms, cnt = kernels[top]
+        per_launch_ms = tms / max(cnt, 1)
+        achieved = input_bytes / (per_launch_ms / 1e3) / 1e9
+        roofline = {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                    "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_row": tpch.Q1_BYTES_PER_ROW, "rows_per_launch": rows,
+                    "launch_ms": round(per_launch_ms, 4), "launches_timed": cnt,
+                    "kernel_share_of_step": round(tms / ms, 4),
+                    "kernels_ms_per_step": {k: round(v[0] / args.steps, 4) for k, v in sorted(kernels.items(), key=lambda kv: -kv[1][0])}}
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(prof):
+            try:
+                roofline["traffic"] = json.load(open(prof)).get(top)
+            except Exception:
+                pass
+
+    # e2e: host (pinned) buffers through the same operator / C ABI call; H2D copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        hpage = tpch.page_to_host(page, pinned=True)
+
+        def step_host():
+            if world == 1:
+                return run_single_pass(P, hpage, aggs, P.SINGLE, ctx)
+            part = run_single_pass(P, hpage, aggs, P.PARTIAL, ctx)
+            return merge_partials_nccl(P, dist, torch, part, fin_aggs, ctx, world)
+
+        e_steps = max(2, min(args.steps, 5))
+        ems, eout, _ = timed(step_host, e_steps, 2)
+        out_bytes = sum(int(np.asarray(b.to_host().values).nbytes) for b in eout.blocks)
+        e2e = {"value": total_rows * e_steps / (ems / 1e3), "unit": "rows/s", "h2d_bytes_per_step": int(input_bytes),
+               "d2h_bytes_per_step": int(out_bytes), "ms_per_step": round(ems / e_steps, 3), "steps": e_steps}
+        del hpage
+
+    # parity spot check of this very run against the oracle on a bounded prefix (the full check lives in tests/)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        n_s, times = time_cpu_port(P, tpch, args.cpu_sample_rows, 1, 3, 1)
+        cpu = {"value": n_s / min(times), "unit": "rows/s", "cores": 1, "kind": "port",
+               "sample": "oracle/ C++ restatement of GroupByHash+accumulators (the reference is Java; no JDK on this box), 1 thread, "
+                         "%d-row TPC-H-shaped lineitem sample of the same Q1 plan, best of 3" % n_s}
+
+    if rank == 0:
+        line = {
+            "metric": "input rows/sec for GROUP BY & hash-join probe at 1/2/4/8 B200; % HBM roofline",
+            "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int128/int64 (decimal sums), u8 keys", "data": "synthetic (TPC-H-shaped generator, seeded)",
+            "config": {"workload": "TPC-H Q1 on lineitem SF%g per GPU: GROUP BY returnflag,linestatus; 4x sum, 3x avg (decimal), count(*); "
+                                   "shipdate filter as mask" % args.sf,
+                       "rows_per_gpu": rows, "groups": int(out.position_count), "step": "SINGLE" if world == 1 else "PARTIAL->all_gather->FINAL",
+                       "l2_policy": "inputs (%.2f GB per pass) exceed the 126 MB L2; no flush needed" % (input_bytes / 1e9)},
+            "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
+        }
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def reference_arm(args):
+    """CPU arm: the oracle port on all host threads (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import presto_b200 as P
+    from presto_b200 import tpch
+    cores = os.cpu_count() or 1
+    n_s, times = time_cpu_port(P, tpch, args.cpu_sample_rows, cores, args.steps, args.warmup)
+    total = sum(times)
+    value = n_s * len(times) / total
+    line = {
+        "impl": "reference",
+        "metric": "input rows/sec for GROUP BY & hash-join probe at 1/2/4/8 B200; % HBM roofline",
+        "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total / len(times) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int128/int64 (decimal sums), u8 keys", "data": "synthetic (TPC-H-shaped generator, seeded)",
+        "config": {"workload": "TPC-H Q1 on lineitem SF%g per GPU: GROUP BY returnflag,linestatus; 4x sum, 3x avg (decimal), count(*); "
+                               "shipdate filter as mask" % args.sf, "rows_per_step": n_s},
+        "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port",
+                         "sample": "oracle/ C++ restatement (reference is Java, no JDK here): %d drivers run PARTIAL over slices of a "
+                                   "%d-row sample, one FINAL merge" % (cores, n_s)},
+        "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        reference_arm(a)
+    else:
+        gpu_arm(a)

@@ -91,6 +91,10 @@ PG_API int32_t pg_ctx_set_stream(pg_ctx* ctx, void* cuda_stream);
 PG_API int32_t pg_ctx_synchronize(pg_ctx* ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches)  */
 PG_API int64_t pg_ctx_launch_count(pg_ctx* ctx);
+/* per-kernel CUDA-event timing on the context stream (off by default): measurement support for bench.py */
+PG_API int32_t pg_ctx_set_timing(pg_ctx* ctx, int32_t enabled);
+PG_API int32_t pg_ctx_kernel_time(pg_ctx* ctx, const char* name_substr, int32_t reset, double* total_ms, int64_t* launches);
+PG_API int32_t pg_ctx_kernel_report(pg_ctx* ctx, char* buf, int64_t cap);
 PG_API const char* pg_version(void);
 
 /* =====================================================================================

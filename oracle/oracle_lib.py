@@ -7,14 +7,17 @@ import ctypes as C
 import os
 import subprocess
 
+import sys
+
 import numpy as np
 
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import presto_b200 as P
 from presto_b200 import _native as N
 from presto_b200.blocks import Block, OutBlock, col_array
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-ORACLE_DIR = os.path.join(ROOT, "oracle")
+ORACLE_DIR = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(ORACLE_DIR)
 LIB_PATH = os.path.join(ORACLE_DIR, "liboracle.so")
 
 _lib = None

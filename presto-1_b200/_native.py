@@ -61,6 +61,9 @@ _PROTOS = {
     "pg_ctx_synchronize": (I32, [P]),
     "pg_ctx_launch_count": (I64, [P]),
     "pg_version": (C.c_char_p, []),
+    "pg_ctx_set_timing": (I32, [P, I32]),
+    "pg_ctx_kernel_time": (I32, [P, C.c_char_p, I32, C.POINTER(C.c_double), PI64]),
+    "pg_ctx_kernel_report": (I32, [P, C.c_char_p, I64]),
     "pg_groupby_create": (I32, [P, PI32, I32, I32, I64, C.POINTER(P)]),
     "pg_groupby_destroy": (I32, [P]),
     "pg_groupby_get_group_ids": (I32, [P, PCOL, PCOL, I64, P, I32, PI64]),

@@ -43,7 +43,7 @@ class Block:
         self.offsets = offsets
         self.precision = precision
         self.scale = scale
-        self.device = _is_torch(values)
+        self.device = bool(_is_torch(values) and values.is_cuda)
         if n is None:
             if type_ in (N.VARCHAR, N.VARBINARY):
                 n = len(offsets) - 1
@@ -112,7 +112,7 @@ class Block:
         return Block(self.type, t(self.values), t(self.nulls), t(self.offsets), self.n, self.precision, self.scale)
 
     def to_host(self):
-        if not self.device:
+        if not self.device and not _is_torch(self.values):
             return self
         h = lambda a, dt: None if a is None else a.cpu().numpy().view(dt)
         return Block(self.type, h(self.values, _NP_DTYPE[self.type]), h(self.nulls, np.uint8), h(self.offsets, np.int32), self.n,

@@ -33,6 +33,23 @@ class GpuContext:
     def launch_count(self):
         return int(N.lib().pg_ctx_launch_count(self._h))
 
+    def set_timing(self, enabled):
+        N.check(self._h, N.lib().pg_ctx_set_timing(self._h, 1 if enabled else 0))
+
+    def kernel_report(self, reset=True):
+        """{kernel name: (total ms, launches)} recorded since the last reset (CUDA events on the context stream)."""
+        buf = C.create_string_buffer(1 << 16)
+        N.check(self._h, N.lib().pg_ctx_kernel_report(self._h, buf, len(buf)))
+        out = {}
+        for item in buf.value.decode().split(";"):
+            if item:
+                name, rest = item.split("=")
+                ms, cnt = rest.split("/")
+                out[name] = (float(ms), int(cnt))
+        if reset:
+            N.check(self._h, N.lib().pg_ctx_kernel_time(self._h, None, 1, None, None))
+        return out
+
     def close(self):
         if self._h:
             N.lib().pg_ctx_destroy(self._h)

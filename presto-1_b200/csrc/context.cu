@@ -50,6 +50,13 @@ void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
     }
 }
 
+cudaEvent_t timing_event(pg_ctx* ctx) {
+    if (!ctx->event_pool.empty()) { cudaEvent_t e = ctx->event_pool.back(); ctx->event_pool.pop_back(); return e; }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+
 }  // namespace pg
 
 using namespace pg;
@@ -86,6 +93,8 @@ int32_t pg_ctx_destroy(pg_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
+    for (const pg_kernel_record& r : ctx->records) { cudaEventDestroy(r.start); cudaEventDestroy(r.stop); }
+    for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
     delete ctx;
     return PG_OK;
 }
@@ -104,6 +113,56 @@ int32_t pg_ctx_synchronize(pg_ctx* ctx) {
 }
 
 int64_t pg_ctx_launch_count(pg_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int32_t pg_ctx_set_timing(pg_ctx* ctx, int32_t enabled) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    ctx->timing = enabled != 0;
+    return PG_OK;
+}
+
+/* Sums the recorded launches whose kernel name contains `name_substr` (NULL = all), then clears them when `reset`. */
+int32_t pg_ctx_kernel_time(pg_ctx* ctx, const char* name_substr, int32_t reset, double* total_ms, int64_t* launches) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    return guard(ctx, [&] {
+        sync(ctx);
+        double ms = 0; int64_t cnt = 0;
+        for (const pg_kernel_record& r : ctx->records) {
+            if (name_substr && !strstr(r.name, name_substr)) continue;
+            float t = 0;
+            if (cudaEventElapsedTime(&t, r.start, r.stop) == cudaSuccess) { ms += t; cnt++; }
+        }
+        if (total_ms) *total_ms = ms;
+        if (launches) *launches = cnt;
+        if (reset) {
+            for (const pg_kernel_record& r : ctx->records) { ctx->event_pool.push_back(r.start); ctx->event_pool.push_back(r.stop); }
+            ctx->records.clear();
+        }
+    });
+}
+
+/* Writes "name=ms/launches;..." for every kernel recorded since the last reset (for bench.py's launch breakdown). */
+int32_t pg_ctx_kernel_report(pg_ctx* ctx, char* buf, int64_t cap) {
+    if (!ctx || !buf || cap <= 0) return PG_E_INVALID_ARGUMENT;
+    return guard(ctx, [&] {
+        sync(ctx);
+        std::vector<std::string> names; std::vector<double> ms; std::vector<int64_t> cnt;
+        for (const pg_kernel_record& r : ctx->records) {
+            float t = 0;
+            if (cudaEventElapsedTime(&t, r.start, r.stop) != cudaSuccess) continue;
+            size_t k = 0;
+            for (; k < names.size(); k++) if (names[k] == r.name) break;
+            if (k == names.size()) { names.push_back(r.name); ms.push_back(0); cnt.push_back(0); }
+            ms[k] += t; cnt[k]++;
+        }
+        std::string out;
+        char line[256];
+        for (size_t k = 0; k < names.size(); k++) {
+            snprintf(line, sizeof(line), "%s=%.6f/%lld;", names[k].c_str(), ms[k], (long long)cnt[k]);
+            out += line;
+        }
+        snprintf(buf, (size_t)cap, "%s", out.c_str());
+    });
+}
 
 const char* pg_version(void) { return "prestogpu 0.1 (sm_100a)"; }
 

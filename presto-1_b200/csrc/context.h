@@ -10,6 +10,11 @@
 
 #include "common.cuh"
 
+struct pg_kernel_record {
+    const char* name;
+    cudaEvent_t start, stop;
+};
+
 struct pg_ctx {
     int device = 0;
     cudaStream_t stream = 0;   // legacy default stream unless pg_ctx_set_stream() is called
@@ -18,7 +23,15 @@ struct pg_ctx {
     std::string err;
     // pinned host bounce buffer for small read-backs (flags, counters)
     int64_t* h_scalar = nullptr;  // 64 x int64, pinned
+    // optional per-kernel CUDA-event timing (pg_ctx_set_timing): bench.py's live roofline numbers
+    bool timing = false;
+    std::vector<pg_kernel_record> records;
+    std::vector<cudaEvent_t> event_pool;
 };
+
+namespace pg {
+cudaEvent_t timing_event(pg_ctx* ctx);
+}
 
 namespace pg {
 
@@ -47,7 +60,13 @@ struct Error : public std::exception {
 // kernel<<<grid, block, smem, ctx->stream>>>(...) with launch counting and error check
 #define PG_LAUNCH(ctx, kernel, grid, block, smem, ...)                                           \
     do {                                                                                         \
+        pg_kernel_record _rec;                                                                   \
+        if ((ctx)->timing) {                                                                     \
+            _rec.name = #kernel; _rec.start = ::pg::timing_event(ctx); _rec.stop = ::pg::timing_event(ctx); \
+            cudaEventRecord(_rec.start, (ctx)->stream);                                          \
+        }                                                                                        \
         kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);                         \
+        if ((ctx)->timing) { cudaEventRecord(_rec.stop, (ctx)->stream); (ctx)->records.push_back(_rec); } \
         (ctx)->launches++;                                                                       \
         PG_CUDA(cudaGetLastError());                                                             \
     } while (0)

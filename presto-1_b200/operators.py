@@ -57,7 +57,7 @@ class HashAggregationOperator:
         assert self.needs_input(), "Operator is already finishing"
         blocks = page.blocks if isinstance(page, Page) else list(page)
         N.check(self.ctx.handle, N.lib().pg_hashagg_add_page(self._h, col_array(blocks), len(blocks), blocks[0].n))
-        if self.step == PARTIAL and self._stats()[2] > self.max_partial_memory:   # builder full -> flush (:208-215, :501-517)
+        if self.step == PARTIAL and self.get_estimated_size() > self.max_partial_memory:   # builder full -> flush (:208-215, :501-517)
             self._flushing = True
 
     def finish(self):
@@ -76,6 +76,15 @@ class HashAggregationOperator:
 
     def get_capacity(self):
         return self._stats()[1]
+
+    def get_estimated_size(self):
+        """InMemoryHashAggregationBuilder.getSizeInMemory: bytes that grow with the group count (slot at fill 0.75, stored
+        key row, accumulator states).  The fixed minimum device allocation is reported by get_device_bytes()."""
+        per_group = 22 + 8 * (len(self.group_by_types) + 1) + 32 * len(self.aggregators)
+        return self._stats()[0] * per_group
+
+    def get_device_bytes(self):
+        return self._stats()[2]
 
     def output_types(self):
         n = C.c_int32()

@@ -1,0 +1,125 @@
+"""TPC-H-shaped synthetic column generator, written straight into device memory with torch (plumbing only).
+
+It follows dbgen's value domains for the columns the configs touch: sparse order keys, 1-7 lineitems per
+order, quantity 1-50, retail-price formula, discount 0.00-0.10, tax 0.00-0.08, ship/receipt date offsets, returnflag /
+linestatus derived from the dates.  It is NOT bit-identical to io.trino.tpch:tpch (an un-vendored dependency of the
+reference); the GPU path and the oracle always consume the same generated buffers, so parity does not depend on that.
+Money columns are unscaled integer cents (short decimal); derived products are long decimals (Int128, sign-magnitude).
+"""
+import numpy as np
+import torch
+
+from . import _native as N
+from .blocks import Block, Page
+
+STARTDATE = 8035          # 1992-01-01 as days since 1970-01-01
+ENDDATE_ORDER = 10440     # 1998-08-02, last order date
+CURRENTDATE = 9298        # 1995-06-17
+Q1_CUTOFF = 10471         # 1998-09-02 (date '1998-12-01' - interval '90' day)
+LINES_PER_ORDER_MEAN = 4
+
+
+def order_key(i):
+    """dbgen sparse keys: 8 used out of every 32."""
+    return (i // 8) * 32 + (i % 8) + 1
+
+
+def _gen(seed, device):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    return g
+
+
+def orders(sf, seed=42, device="cuda", rows=None):
+    """orders: o_orderkey (unique, sparse), o_custkey, o_totalprice (double), o_orderdate, o_shippriority, o_orderstatus."""
+    n = int(1_500_000 * sf) if rows is None else int(rows)
+    g = _gen(seed, device)
+    idx = torch.arange(n, device=device, dtype=torch.int64)
+    okey = order_key(idx)
+    custkey = torch.randint(1, max(2, int(150_000 * sf)) + 1, (n,), generator=g, device=device, dtype=torch.int64)
+    totalprice = (torch.randint(85_771, 55_528_517, (n,), generator=g, device=device, dtype=torch.int64).double() / 100.0)
+    orderdate = torch.randint(STARTDATE, ENDDATE_ORDER + 1, (n,), generator=g, device=device, dtype=torch.int32)
+    shipprio = torch.zeros(n, device=device, dtype=torch.int32)
+    return {"orderkey": okey, "custkey": custkey, "totalprice": totalprice, "orderdate": orderdate, "shippriority": shipprio}
+
+
+def lineitem(sf, seed=42, device="cuda", orders_count=None, need=("q1",), shuffle=False):
+    """lineitem columns.  need: subset of {"q1", "keys", "join"} selecting which columns are materialised."""
+    n_orders = int(1_500_000 * sf) if orders_count is None else int(orders_count)
+    g = _gen(seed + 1, device)
+    counts = torch.randint(1, 8, (n_orders,), generator=g, device=device, dtype=torch.int64)
+    order_idx = torch.repeat_interleave(torch.arange(n_orders, device=device, dtype=torch.int64), counts)
+    n = int(order_idx.numel())
+    out = {"rows": n}
+    if shuffle:
+        order_idx = order_idx[torch.randperm(n, generator=g, device=device)]
+    if "keys" in need or "join" in need:
+        out["orderkey"] = order_key(order_idx)
+    qty = torch.randint(1, 51, (n,), generator=g, device=device, dtype=torch.int64)
+    partkey = torch.randint(1, max(2, int(200_000 * sf)) + 1, (n,), generator=g, device=device, dtype=torch.int64)
+    retail = 90_000 + (torch.div(partkey, 10, rounding_mode="floor") % 20_001) + 100 * (partkey % 1000)
+    out["quantity"] = qty * 100                                  # decimal(12,2)
+    out["extendedprice"] = qty * retail                          # decimal(12,2) cents
+    del partkey, retail
+    if "q1" in need:
+        discount = torch.randint(0, 11, (n,), generator=g, device=device, dtype=torch.int64)
+        tax = torch.randint(0, 9, (n,), generator=g, device=device, dtype=torch.int64)
+        orderdate = torch.randint(STARTDATE, ENDDATE_ORDER + 1, (n_orders,), generator=g, device=device, dtype=torch.int32)[order_idx]
+        shipdate = orderdate + torch.randint(1, 122, (n,), generator=g, device=device, dtype=torch.int32)
+        receiptdate = shipdate + torch.randint(1, 31, (n,), generator=g, device=device, dtype=torch.int32)
+        ra = torch.where(torch.rand(n, generator=g, device=device) < 0.5, ord("R"), ord("A")).to(torch.uint8)
+        out["returnflag"] = torch.where(receiptdate <= CURRENTDATE, ra, torch.full_like(ra, ord("N")))
+        out["linestatus"] = torch.where(shipdate > CURRENTDATE, ord("O"), ord("F")).to(torch.uint8)
+        out["shipdate"] = shipdate
+        out["discount"] = discount
+        out["tax"] = tax
+        disc_price = out["extendedprice"] * (100 - discount)     # decimal(24,4)
+        charge = disc_price * (100 + tax)                        # decimal(36,6); < 2^63 for TPC-H domains
+        out["disc_price"] = torch.stack([disc_price, torch.zeros_like(disc_price)], dim=1).reshape(-1)
+        out["charge"] = torch.stack([charge, torch.zeros_like(charge)], dim=1).reshape(-1)
+        out["q1_mask"] = (shipdate <= Q1_CUTOFF).to(torch.uint8)
+        out["offsets1"] = torch.arange(n + 1, device=device, dtype=torch.int32)   # varchar(1): one byte per row
+    if "double" in need:
+        out["extendedprice_double"] = out["extendedprice"].double() / 100.0
+    return out
+
+
+def q1_page(cols):
+    """Page for the Q1 configuration: [returnflag, linestatus, quantity, extendedprice, discount, disc_price, charge, mask]."""
+    n = cols["rows"]
+    off = cols["offsets1"]
+    return Page(
+        Block(N.VARCHAR, cols["returnflag"], None, off, n),
+        Block(N.VARCHAR, cols["linestatus"], None, off, n),
+        Block(N.SHORT_DECIMAL, cols["quantity"], None, None, n, 12, 2),
+        Block(N.SHORT_DECIMAL, cols["extendedprice"], None, None, n, 12, 2),
+        Block(N.SHORT_DECIMAL, cols["discount"], None, None, n, 12, 2),
+        Block(N.LONG_DECIMAL, cols["disc_price"], None, None, n, 24, 4),
+        Block(N.LONG_DECIMAL, cols["charge"], None, None, n, 36, 6),
+        Block(N.BOOLEAN, cols["q1_mask"], None, None, n),
+        position_count=n)
+
+
+Q1_BYTES_PER_ROW = 2 * (1 + 4) + 8 + 8 + 8 + 16 + 16 + 1   # = 67, SURVEY.md §8d "materialised inputs"
+
+
+def q1_aggregators():
+    """sum(qty), sum(price), sum(disc_price), sum(charge), avg(qty), avg(price), avg(disc), count(*) — all masked by the filter."""
+    from .operators import AggregatorFactory as A
+    m = 7
+    return [A(N.AGG_SUM, N.SHORT_DECIMAL, 2, m), A(N.AGG_SUM, N.SHORT_DECIMAL, 3, m), A(N.AGG_SUM, N.LONG_DECIMAL, 5, m),
+            A(N.AGG_SUM, N.LONG_DECIMAL, 6, m), A(N.AGG_AVG, N.SHORT_DECIMAL, 2, m), A(N.AGG_AVG, N.SHORT_DECIMAL, 3, m),
+            A(N.AGG_AVG, N.SHORT_DECIMAL, 4, m), A(N.AGG_COUNT, 0, -1, m)]
+
+
+def page_to_host(page, pinned=True):
+    """Device page -> host page backed by (pinned) numpy arrays: what a JNI caller would hand to the C ABI."""
+    def h(t):
+        if t is None:
+            return None
+        c = t.cpu()
+        if pinned:
+            c = c.pin_memory()
+        return c.numpy()
+    return Page(*[Block(b.type, h(b.values), h(b.nulls), h(b.offsets), b.n, b.precision, b.scale) for b in page.blocks],
+                position_count=page.position_count)

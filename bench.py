@@ -35,6 +35,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--extra", action="store_true", help="also time the high-cardinality GROUP BY and join workloads")
+    ap.add_argument("--extra-sf", type=float, default=10.0)
     return ap.parse_args()
 
 
@@ -213,6 +214,84 @@ def final_aggs_for(P, aggs, first_channel):
     return fin
 
 
+def extra_workloads(args, P, tpch, ctx, torch, peak):
+    """cfg3 (high-cardinality GROUP BY orderkey) and cfg4 (lineitem JOIN orders) on one GPU, device-resident inputs."""
+    import numpy as np
+    from presto_b200.blocks import Block
+    N = P.native
+    res = {}
+    sf = args.extra_sf
+    li = tpch.lineitem(sf, seed=42, device="cuda", need=("keys", "double"))
+    n = li["rows"]
+    n_orders = int(1_500_000 * sf)
+    page = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, li["quantity"], None, None, n),
+                  Block(N.DOUBLE, li["extendedprice_double"].view(torch.int64), None, None, n), position_count=n)
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2)]
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        ctx.kernel_report(reset=True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps, out
+
+    ctx.set_timing(True)
+
+    def gb_pass():
+        op = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=n_orders, ctx=ctx, device_output=True)
+        op.add_input(page)
+        op.finish()
+        g = op.get_group_count()
+        out = op.get_output(max_rows=g)     # all groups materialised on the device
+        op.close()
+        return g
+
+    ms, groups = timed(gb_pass, 3, 1)
+    kern = ctx.kernel_report(reset=True)
+    brow = 136
+    res["groupby_orderkey"] = {"workload": "GROUP BY orderkey over lineitem SF%g: count(*), sum(quantity decimal), sum(extendedprice double)" % sf,
+                               "rows": n, "groups": int(groups), "ms_per_step": round(ms, 3), "rows_per_s": n / (ms / 1e3),
+                               "algorithmic_bytes_per_row": brow, "hbm_frac": round(n * brow / (ms / 1e3) / 1e9 / peak, 4),
+                               "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:8]}}
+    del page
+    # ---- join: build orders (orderkey unique, totalprice), probe lineitem.orderkey, gather totalprice
+    od = tpch.orders(sf, seed=42, device="cuda")
+    bpage = [Block(N.BIGINT, od["orderkey"], None, None, n_orders), Block(N.DOUBLE, od["totalprice"].view(torch.int64), None, None, n_orders)]
+
+    def build():
+        idx = P.PagesIndex([P.BIGINT, P.DOUBLE], [0], ctx=ctx)
+        idx.add_page(bpage)
+        return idx.create_lookup_source()
+
+    bms, ls = timed(build, 2, 1)
+    bkern = ctx.kernel_report(reset=True)
+    pk = [Block(N.BIGINT, li["orderkey"], None, None, n)]
+
+    def probe():
+        pp, bp = ls.join_page(pk, None, P.JOIN_INNER, device=True, capacity=n)
+        out = ls.append_to(bp, [1], device=True)
+        return len(pp)
+
+    pms, matches = timed(probe, 3, 1)
+    pkern = ctx.kernel_report(reset=True)
+    ctx.set_timing(False)
+    res["join_build"] = {"workload": "hash build orders SF%g (orderkey, totalprice)" % sf, "rows": n_orders, "ms_per_step": round(bms, 3),
+                         "rows_per_s": n_orders / (bms / 1e3), "algorithmic_bytes_per_row": 32,
+                         "hbm_frac": round(n_orders * 32 / (bms / 1e3) / 1e9 / peak, 4),
+                         "kernels_ms_per_step": {k: round(v[0] / 2, 3) for k, v in sorted(bkern.items(), key=lambda kv: -kv[1][0])[:6]}}
+    res["join_probe"] = {"workload": "INNER join probe lineitem.orderkey -> orders SF%g, emit (probe idx, build pos) + gather totalprice" % sf,
+                         "rows": n, "matches": int(matches), "ms_per_step": round(pms, 3), "rows_per_s": n / (pms / 1e3),
+                         "algorithmic_bytes_per_row": 44, "hbm_frac": round(n * 44 / (pms / 1e3) / 1e9 / peak, 4),
+                         "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(pkern.items(), key=lambda kv: -kv[1][0])[:6]}}
+    return res
+
+
 def gpu_arm(args):
     import numpy as np
     import torch
@@ -330,6 +409,12 @@ def gpu_arm(args):
                "sample": "oracle/ C++ restatement of GroupByHash+accumulators (the reference is Java; no JDK on this box), 1 thread, "
                          "%d-row TPC-H-shaped lineitem sample of the same Q1 plan, best of 3" % n_s}
 
+    extra = None
+    if args.extra and world == 1:
+        del page, cols
+        torch.cuda.empty_cache()
+        extra = extra_workloads(args, P, tpch, ctx, torch, peak)
+
     if rank == 0:
         line = {
             "metric": "input rows/sec for GROUP BY & hash-join probe at 1/2/4/8 B200; % HBM roofline",
@@ -344,6 +429,8 @@ def gpu_arm(args):
         }
         if cpu:
             line["cpu_baseline"] = cpu
+        if extra:
+            line["extra"] = extra
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()

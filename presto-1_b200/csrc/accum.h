@@ -62,6 +62,8 @@ static inline int state_words(int op) {
 void accumulate(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count);
 // (re)initialise state words of groups [first, first+count): zeros, min/max identities
 void init_state(pg_ctx* ctx, int op, unsigned long long* state, int64_t first, int64_t count);
+// low-cardinality path; returns false when the program / group count does not fit it
+bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count);
 
 }  // namespace pg
 

@@ -170,8 +170,11 @@ __global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, Key
         int64_t row = base + threadIdx.x;
         bool valid = row < a.n;
         bool claimed = false;
+        bool pending = false;
+        int64_t s = -1;
         if (valid) {
-            int64_t s;
+            // Slot words are read through L1 (plain loads): a key / claim never changes once written, so a cached
+            // non-empty word is always right; a stale cached EMPTY is resolved by the CAS, which returns the live value.
             if (BIGINT) {
                 const DCol& c = kc.c[0];
                 if (dcol_is_null(c, row)) s = a.cap + 1;
@@ -181,7 +184,7 @@ __global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, Key
                     else {
                         int64_t p = (int64_t)(fmix64(key) & (uint64_t)a.mask);
                         while (true) {
-                            unsigned long long k = *((volatile unsigned long long*)&a.slots[p].word);
+                            unsigned long long k = a.slots[p].word;
                             if (k == key) break;
                             if (k == EMPTY_KEY) {
                                 unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_KEY, key);
@@ -200,7 +203,7 @@ __global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, Key
                 unsigned long long mine = ((unsigned long long)tag << 32) | (unsigned long long)(REF_PENDING | (uint32_t)row);
                 int64_t p = (int64_t)(f & (uint64_t)a.mask);
                 while (true) {
-                    unsigned long long w = *((volatile unsigned long long*)&a.slots[p].word);
+                    unsigned long long w = a.slots[p].word;
                     if (w == EMPTY_WORD) {
                         unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_WORD, mine);
                         if (old == EMPTY_WORD) { claimed = true; break; }
@@ -216,8 +219,14 @@ __global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, Key
                 }
                 s = p;
             }
-            if (*((volatile int32_t*)&a.slots[s].gid) < 0) atomicMin(&a.slots[s].first_row, (int32_t)row);
+            pending = a.slots[s].gid < 0;   // group ids are only assigned between launches: the cached value is current
             a.row_slot[row] = (int32_t)s;
+        }
+        // rows of still-unnumbered slots compete for first_row; lanes of a warp that share a slot send one atomic
+        unsigned pend = __ballot_sync(0xffffffffu, pending);
+        if (pend) {
+            unsigned peers = __match_any_sync(0xffffffffu, pending ? s : (int64_t)(-1 - lane));
+            if (pending && (__ffs(peers) - 1) == lane) atomicMin(&a.slots[s].first_row, (int32_t)row);
         }
         unsigned b = __ballot_sync(0xffffffffu, claimed);
         if (lane == 0 && b) {
@@ -666,12 +675,19 @@ static KeyCols offset_keys(const KeyCols& kc, const KeyLayout& L, int64_t off) {
 
 void groupby_process(pg_groupby* gb, const KeyCols& keys, const DCol* hash_col, int64_t n, int32_t* d_out_ids) {
     pg_ctx* ctx = gb->ctx;
-    for (int64_t off = 0; off < n; off += MAX_CHUNK_ROWS) {
-        int64_t m = n - off < MAX_CHUNK_ROWS ? n - off : MAX_CHUNK_ROWS;
+    // A large page is split into a short prefix and the rest: the prefix numbers the groups a low-cardinality input
+    // consists of, so the bulk of the rows only reads finished slots (no first_row atomics on a handful of addresses).
+    const int64_t PREFIX = 128 * 1024;
+    int64_t off = 0;
+    while (off < n) {
+        int64_t m = n - off;
+        if (off == 0 && n > 4 * PREFIX) m = PREFIX;
+        if (m > MAX_CHUNK_ROWS) m = MAX_CHUNK_ROWS;
         KeyCols kc = offset_keys(keys, gb->layout, off);
         DCol hc;
         if (hash_col) { hc = *hash_col; hc.values = (const int64_t*)hc.values + off; }
         process_chunk(gb, kc, hash_col ? &hc : nullptr, m, d_out_ids ? d_out_ids + off : nullptr);
+        off += m;
     }
     (void)ctx;
     // the reference's logical capacity schedule (needRehash/tryRehash, BigintGroupByHash.java:262-334)

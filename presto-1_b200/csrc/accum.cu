@@ -6,11 +6,12 @@ namespace pg {
 static const int ACC_THREADS = 256;
 
 // ------------------------------------------------------------------ GLOBAL: one row per thread, atomics on HBM/L2 state
-__global__ void __launch_bounds__(ACC_THREADS) acc_global_kernel(AggProgram prog, const int32_t* __restrict__ gids, int64_t n) {
+__global__ void __launch_bounds__(ACC_THREADS) acc_global_kernel(AggProgram prog, const int32_t* __restrict__ gids, int64_t n, const uint8_t* __restrict__ only_rows) {
     int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; row < n; row += stride) {
         int64_t g = gids[row];
+        if (only_rows != nullptr && only_rows[row] == 0) continue;
         for (int a = 0; a < prog.naggs; a++) {
             const AggOp& op = prog.ops[a];
             Contribution c;
@@ -63,7 +64,7 @@ void init_state(pg_ctx* ctx, int op, unsigned long long* state, int64_t first, i
     PG_LAUNCH(ctx, acc_init_state_kernel, grid_for(ctx, count * words, 256, 4), 256, 0, state, op, words, first, count);
 }
 
-void accumulate(pg_ctx* ctx, const AggProgram& prog_in, const int32_t* gids, int64_t n, int64_t group_count) {
+void accumulate(pg_ctx* ctx, const AggProgram& prog_in, const int32_t* gids, int64_t n, int64_t group_count, const uint8_t* only_rows) {
     if (n <= 0 || prog_in.naggs == 0) return;
     AggProgram prog = prog_in;
     bool has128 = false;
@@ -77,6 +78,7 @@ void accumulate(pg_ctx* ctx, const AggProgram& prog_in, const int32_t* gids, int
     prog.priv_words = priv_words;
     // strategy: few groups -> thread-private tables in shared memory (accum_private.cu); otherwise global atomics
     bool use_private = !has128 && n >= 64 * 1024;
+    PG_CHECK_STATE(!(has128 && only_rows), "128-bit min/max cannot be combined with a row filter");
     std::vector<DevBuf> snaps;
     if (has128) {
         for (int a = 0; a < prog.naggs; a++) {
@@ -87,8 +89,8 @@ void accumulate(pg_ctx* ctx, const AggProgram& prog_in, const int32_t* gids, int
                       snaps.back().as<unsigned long long>());
         }
     }
-    if (!(use_private && accumulate_private(ctx, prog, gids, n, group_count)))
-        PG_LAUNCH(ctx, acc_global_kernel, grid_for(ctx, n, ACC_THREADS), ACC_THREADS, 0, prog, gids, n);
+    if (!(use_private && accumulate_private(ctx, prog, gids, n, group_count, only_rows, nullptr)))
+        PG_LAUNCH(ctx, acc_global_kernel, grid_for(ctx, n, ACC_THREADS), ACC_THREADS, 0, prog, gids, n, only_rows);
     if (has128) {
         int si = 0;
         for (int a = 0; a < prog.naggs; a++) {

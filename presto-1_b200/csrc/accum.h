@@ -59,11 +59,27 @@ static inline int state_words(int op) {
 }
 
 // launch the grouped accumulation of `prog` over n rows with group ids `gids` (device int32)
-void accumulate(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count);
+// only_rows (optional, one byte per row): rows whose byte is 0 are skipped (used after a fused pass that handled the rest)
+void accumulate(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count, const uint8_t* only_rows = nullptr);
 // (re)initialise state words of groups [first, first+count): zeros, min/max identities
 void init_state(pg_ctx* ctx, int op, unsigned long long* state, int64_t first, int64_t count);
 // low-cardinality path; returns false when the program / group count does not fit it
-bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count);
+struct KeyLayout;
+struct KeyCols;
+// what the fused (look-up inside the accumulation kernel) variant needs from the GroupByHash
+struct FusedLookup {
+    const KeyLayout* layout;
+    const KeyCols* keys;              // key columns of the rows being processed
+    const uint64_t* key_rows;
+    const uint8_t* arena;
+    const int64_t* values_by_group;
+    int32_t bigint_mode, null_gid;
+    uint8_t* miss_flag;               // n bytes, zeroed by the caller
+    unsigned long long* d_miss;       // device counter, zeroed by the caller
+};
+bool fused_keys_packable(const KeyLayout& L);
+bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count, const uint8_t* only_rows,
+                        const FusedLookup* fused);
 
 }  // namespace pg
 

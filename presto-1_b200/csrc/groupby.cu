@@ -1,84 +1,10 @@
 // groupby.cu — GroupByHash kernels and host logic.  See groupby.h for the HBM layout.
 #include "groupby.h"
+#include "groupby_dev.cuh"
 
 namespace pg {
 
 static const int GB_THREADS = 256;
-
-// ------------------------------------------------------------------ key helpers (multi-channel mode)
-PG_D int64_t keys_row_hash(const KeyCols& kc, int nkeys, int64_t i) {
-    uint64_t h = 0;  // INITIAL_HASH_VALUE (HashGenerationOptimizer.java:98)
-    for (int k = 0; k < nkeys; k++) h = 31 * h + (uint64_t)dcol_type_hash(kc.c[k], i);
-    return (int64_t)h;
-}
-
-PG_D bool double_not_distinct(int64_t a, int64_t b) {  // SPI/type/DoubleType.java:181-192
-    if (bits_is_nan(a) && bits_is_nan(b)) return true;
-    return __longlong_as_double(a) == __longlong_as_double(b);
-}
-
-// IS NOT DISTINCT FROM between input rows i and j (same page)
-PG_D bool keys_equal_rows(const KeyCols& kc, const KeyLayout& L, int64_t i, int64_t j) {
-    for (int k = 0; k < L.nkeys; k++) {
-        const DCol& c = kc.c[k];
-        bool ni = dcol_is_null(c, i), nj = dcol_is_null(c, j);
-        if (ni || nj) { if (ni != nj) return false; continue; }
-        switch (c.type) {
-            case PG_VARCHAR: case PG_VARBINARY: {
-                int32_t oi = c.offsets[i], li = c.offsets[i + 1] - oi, oj = c.offsets[j], lj = c.offsets[j + 1] - oj;
-                if (li != lj) return false;
-                const uint8_t* b = (const uint8_t*)c.values;
-                for (int32_t t = 0; t < li; t++) if (b[oi + t] != b[oj + t]) return false;
-                break;
-            }
-            case PG_LONG_DECIMAL: {
-                const int64_t* p = (const int64_t*)c.values;
-                if (p[2 * i] != p[2 * j] || p[2 * i + 1] != p[2 * j + 1]) return false;
-                break;
-            }
-            case PG_DOUBLE:
-                if (!double_not_distinct(dcol_long(c, i), dcol_long(c, j))) return false;
-                break;
-            default:
-                if (dcol_long(c, i) != dcol_long(c, j)) return false;
-        }
-    }
-    return true;
-}
-
-// IS NOT DISTINCT FROM between input row i and the stored key row of group g
-PG_D bool keys_equal_store(const KeyCols& kc, const KeyLayout& L, int64_t i, const uint64_t* key_rows, const uint8_t* arena,
-                           int64_t g) {
-    const uint64_t* row = key_rows + g * L.row_words;
-    uint64_t nullbits = row[0];
-    for (int k = 0; k < L.nkeys; k++) {
-        const DCol& c = kc.c[k];
-        bool ni = dcol_is_null(c, i), ng = (nullbits >> k) & 1;
-        if (ni || ng) { if (ni != ng) return false; continue; }
-        const uint64_t* w = row + L.word_off[k];
-        switch (c.type) {
-            case PG_VARCHAR: case PG_VARBINARY: {
-                int32_t oi = c.offsets[i], li = c.offsets[i + 1] - oi;
-                int64_t og = (int64_t)(w[0] >> 24); int32_t lg = (int32_t)(w[0] & 0xFFFFFF);
-                if (li != lg) return false;
-                const uint8_t* b = (const uint8_t*)c.values;
-                for (int32_t t = 0; t < li; t++) if (b[oi + t] != arena[og + t]) return false;
-                break;
-            }
-            case PG_LONG_DECIMAL: {
-                const uint64_t* p = (const uint64_t*)c.values;
-                if (p[2 * i] != w[0] || p[2 * i + 1] != w[1]) return false;
-                break;
-            }
-            case PG_DOUBLE:
-                if (!double_not_distinct(dcol_long(c, i), (int64_t)w[0])) return false;
-                break;
-            default:
-                if (dcol_long(c, i) != (int64_t)w[0]) return false;
-        }
-    }
-    return true;
-}
 
 // ------------------------------------------------------------------ table init / rebuild
 __global__ void gb_init_slots_kernel(Slot* slots, int64_t nslots, unsigned long long empty) {

@@ -26,6 +26,15 @@ struct pg_hashagg {
 
 namespace pg {
 
+static DCol dcol_offset(const DCol& c, int64_t off) {
+    DCol r = c;
+    if (off == 0) return r;
+    if (r.nulls) r.nulls += off;
+    if (type_is_var(r.type)) r.offsets += off;
+    else r.values = (const char*)r.values + off * type_width(r.type);
+    return r;
+}
+
 static bool step_input_raw(int s) { return s == PG_STEP_SINGLE || s == PG_STEP_PARTIAL; }
 static bool step_output_partial(int s) { return s == PG_STEP_PARTIAL || s == PG_STEP_INTERMEDIATE; }
 
@@ -64,26 +73,81 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     DCol hc; memset(&hc, 0, sizeof(hc));
     bool has_hash = op->hash_channel >= 0;
     if (has_hash) { hc = need(op->hash_channel); PG_CHECK_ARG(hc.type == PG_BIGINT, "hash channel must be BIGINT"); }
-    op->ids.grow(ctx, n * 4, 0);
-    groupby_process(op->gb, kc, has_hash ? &hc : nullptr, n, op->ids.as<int32_t>());
-    int64_t groups = op->gb->groups;
-    if (op->aggs.empty()) { op->input_rows += n; return; }
-    for (pg_agg* a : op->aggs) agg_ensure_capacity(a, groups);
-    if (step_input_raw(op->step)) {
+    const bool raw = step_input_raw(op->step);
+    auto build_prog = [&](int64_t off) {
         AggProgram prog;
         memset(&prog, 0, sizeof(prog));
         prog.naggs = (int32_t)op->aggs.size();
         for (size_t i = 0; i < op->aggs.size(); i++) {
             const pg_agg_spec& s = op->specs[i];
-            const DCol* arg = nullptr; const DCol* mask = nullptr;
+            DCol arg, mask;
+            const DCol* parg = nullptr; const DCol* pmask = nullptr;
             if (s.kind != PG_AGG_COUNT) {
-                arg = &need(s.input_channel);
-                PG_CHECK_ARG(arg->type == s.in_type, "aggregate %d input channel has type %d, expected %d", (int)i, arg->type, s.in_type);
+                arg = dcol_offset(need(s.input_channel), off);
+                PG_CHECK_ARG(arg.type == s.in_type, "aggregate %d input channel has type %d, expected %d", (int)i, arg.type, s.in_type);
+                parg = &arg;
             }
-            if (s.mask_channel >= 0) { mask = &need(s.mask_channel); PG_CHECK_ARG(mask->type == PG_BOOLEAN, "mask must be BOOLEAN"); }
-            prog.ops[i] = agg_make_op(op->aggs[i], arg, mask);
+            if (s.mask_channel >= 0) { mask = dcol_offset(need(s.mask_channel), off); PG_CHECK_ARG(mask.type == PG_BOOLEAN, "mask must be BOOLEAN"); pmask = &mask; }
+            prog.ops[i] = agg_make_op(op->aggs[i], parg, pmask);
         }
-        accumulate(ctx, prog, op->ids.as<int32_t>(), n, groups);
+        return prog;
+    };
+    auto generic_rows = [&](int64_t off, int64_t m, const uint8_t* only_rows) {
+        KeyCols kco = kc;
+        for (size_t k = 0; k < op->key_channels.size(); k++) kco.c[k] = dcol_offset(kc.c[k], off);
+        DCol hco = hc;
+        if (has_hash) hco = dcol_offset(hc, off);
+        op->ids.grow(ctx, m * 4, 0);
+        groupby_process(op->gb, kco, has_hash ? &hco : nullptr, m, op->ids.as<int32_t>());
+        if (op->aggs.empty()) return;
+        for (pg_agg* a : op->aggs) agg_ensure_capacity(a, op->gb->groups);
+        if (raw) accumulate(ctx, build_prog(off), op->ids.as<int32_t>(), m, op->gb->groups, only_rows);
+    };
+    // Large raw pages: a short prefix goes through the general path and numbers the groups; if there are only a few and
+    // the keys are short, the rest is resolved and accumulated in ONE kernel (packed-key look-up in shared memory, private
+    // partial states), and only rows that kernel could not resolve take the general path afterwards.
+    const int64_t PREFIX = 128 * 1024;
+    bool fused_done = false;
+    if (raw && !op->aggs.empty() && n >= 8 * PREFIX && fused_keys_packable(op->gb->layout)) {
+        generic_rows(0, PREFIX, nullptr);
+        int64_t groups = op->gb->groups, m = n - PREFIX;
+        if (groups <= 64) {
+            DevBuf miss_flag(ctx, m), miss_cnt(ctx, 8);
+            memset_async(ctx, miss_flag.p, 0, m);
+            memset_async(ctx, miss_cnt.p, 0, 8);
+            KeyCols kco = kc;
+            for (size_t k = 0; k < op->key_channels.size(); k++) kco.c[k] = dcol_offset(kc.c[k], PREFIX);
+            FusedLookup fl;
+            fl.layout = &op->gb->layout; fl.keys = &kco; fl.key_rows = op->gb->key_rows.as<uint64_t>(); fl.arena = op->gb->arena.as<uint8_t>();
+            fl.values_by_group = op->gb->values_by_group.as<int64_t>(); fl.bigint_mode = op->gb->bigint_mode ? 1 : 0;
+            fl.null_gid = -1;
+            if (op->gb->bigint_mode) {
+                int64_t sp[2];
+                read_scalars(ctx, op->gb->slots.as<Slot>() + op->gb->cap + 1, 2, sp);   // the null group's slot {word, gid|first_row}
+                fl.null_gid = (int32_t)(sp[1] & 0xffffffff);
+            }
+            fl.miss_flag = miss_flag.as<uint8_t>(); fl.d_miss = miss_cnt.as<unsigned long long>();
+            if (accumulate_private(ctx, build_prog(PREFIX), nullptr, m, groups, nullptr, &fl)) {
+                int64_t misses;
+                read_scalars(ctx, miss_cnt.p, 1, &misses);
+                if (misses > 0) generic_rows(PREFIX, m, miss_flag.as<uint8_t>());
+                fused_done = true;
+            }
+        }
+        if (!fused_done) { generic_rows(PREFIX, n - PREFIX, nullptr); fused_done = true; }
+    }
+    if (fused_done) {
+        op->input_rows += n;
+        sync(ctx);
+        return;
+    }
+    op->ids.grow(ctx, n * 4, 0);
+    groupby_process(op->gb, kc, has_hash ? &hc : nullptr, n, op->ids.as<int32_t>());
+    int64_t groups = op->gb->groups;
+    if (op->aggs.empty()) { op->input_rows += n; return; }
+    for (pg_agg* a : op->aggs) agg_ensure_capacity(a, groups);
+    if (raw) {
+        accumulate(ctx, build_prog(0), op->ids.as<int32_t>(), n, groups);
     } else {
         for (size_t i = 0; i < op->aggs.size(); i++) {
             const pg_agg_spec& s = op->specs[i];

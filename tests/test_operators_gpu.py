@@ -189,3 +189,69 @@ def test_q1_shaped_decimal_aggregation_matches_oracle(pgpu):
         assert r[2] == sum(int(qty[i]) for i in sel)
         assert r[4] == sum(disc_price[i] for i in sel)
         assert r[9] == len(sel)
+
+
+@pytest.mark.parametrize("key_kind", ["varchar", "bigint", "int_date"])
+def test_fused_low_cardinality_page_with_late_and_unpackable_keys(pgpu, key_kind):
+    """Pages >= 1M rows take the fused kernel (packed-key look-up + private partial states).  Groups that first appear
+    after the prefix, null keys and strings too long for the packed form must come out exactly like the general path."""
+    P = pgpu
+    rng = np.random.default_rng(9)
+    n = 1_300_000
+    late = n - 200_000
+    if key_kind == "varchar":
+        base = np.array(["A", "N", "R", "", "xy"], dtype=object)
+        ks = base[rng.integers(0, 5, n)]
+        ks[late:late + 50_000] = "late"                 # 4 bytes: not packable and new after the prefix
+        ks[late + 60_000:late + 70_000] = "Q"           # packable but unknown to the prefix
+        ks[rng.random(n) < 0.001] = None
+        key_blocks = [P.Block.variable_width(list(ks)), P.Block.variable_width(list(base[rng.integers(0, 2, n)]))]
+        types = [P.VARCHAR, P.VARCHAR]
+    elif key_kind == "bigint":
+        k = rng.integers(0, 7, n).astype(np.int64)
+        k[late:late + 1000] = 12345
+        nulls = (rng.random(n) < 0.001).astype(np.uint8)
+        key_blocks = [P.Block.long_array(k, nulls)]
+        types = [P.BIGINT]
+    else:
+        a = rng.integers(0, 3, n).astype(np.int32)
+        d = rng.integers(9000, 9003, n).astype(np.int32)
+        d[late:] += 7
+        key_blocks = [P.Block.int_array(a), P.Block.int_array(d, None, P.DATE)]
+        types = [P.INTEGER, P.DATE]
+    nk = len(key_blocks)
+    v_short = rng.integers(-10**10, 10**10, n).astype(np.int64)
+    v_nulls = (rng.random(n) < 0.05).astype(np.uint8)
+    v_long = P.Block.int128_array([int(x) * 10**15 for x in rng.integers(-10**6, 10**6, 50_000)] * (n // 50_000))
+    v_dbl = rng.random(n)
+    mask = (rng.random(n) < 0.9).astype(np.uint8)
+    blocks = key_blocks + [P.Block.long_array(v_short, v_nulls, P.SHORT_DECIMAL), v_long, P.Block.double_array(v_dbl), P.Block.byte_array(mask)]
+    c = nk
+    aggs = [P.AggregatorFactory(P.AGG_COUNT, 0, -1, c + 3), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, c, c + 3),
+            P.AggregatorFactory(P.AGG_AVG, P.SHORT_DECIMAL, c, c + 3), P.AggregatorFactory(P.AGG_SUM, P.LONG_DECIMAL, c + 1),
+            P.AggregatorFactory(P.AGG_COUNT_COL, P.SHORT_DECIMAL, c), P.AggregatorFactory(P.AGG_MIN, P.SHORT_DECIMAL, c),
+            P.AggregatorFactory(P.AGG_MAX, P.DOUBLE, c + 2), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, c + 2, c + 3)]
+    op = P.HashAggregationOperator(types, list(range(nk)), P.SINGLE, aggs)
+    op.add_input(P.Page(*blocks).to_device())
+    op.finish()
+    got = rows_of(drain(op))
+    ogb = O.OracleGroupBy(types, 10_000)
+    ids = ogb.get_group_ids(blocks[:nk])
+    g = ogb.group_count()
+    keys, _ = ogb.export(with_hash=False)
+    cols = [k.to_list() for k in keys]
+    for a in aggs:
+        oa = O.OracleAccumulator(a.kind, a.in_type)
+        oa.add_input(ids, g, blocks[a.input_channel] if a.input_channel >= 0 else None, blocks[a.mask_channel] if a.mask_channel >= 0 else None)
+        rc, out, _ = oa.evaluate(0, g, True)
+        assert rc == 0
+        cols.append(out[0].to_list())
+    want = [tuple(col[i] for col in cols) for i in range(g)]
+    assert len(got) == len(want) == g
+    keyf = lambda r: tuple((x is None, x) for x in r[:nk])
+    for a, b in zip(sorted(got, key=keyf), sorted(want, key=keyf)):
+        for x, y in zip(a, b):
+            if isinstance(x, float):
+                assert x == pytest.approx(y, rel=1e-12)
+            else:
+                assert x == y

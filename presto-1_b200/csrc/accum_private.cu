@@ -16,8 +16,8 @@ enum { PS_CNT = 0, PS_ADD2 = 1, PS_ADD3 = 2, PS_F64 = 3, PS_MIN = 4, PS_MAX = 5 
 enum { CV_INT = 0, CV_I2D = 1, CV_F64 = 2, CV_DEC128 = 3, CV_MINKEY = 4, CV_MAXKEY = 5 };
 static const int MAX_PCOLS = 20;
 static const int MAX_PCONDS = 8;
-static const int MAX_PSLOTS = 12;
-static const int MAX_PVALS = 10;     // value words carried per row between the load and the update phase
+static const int MAX_PSLOTS = 10;
+static const int MAX_P128 = 3;       // slots fed by 128-bit inputs come first (they carry a second value word per row)
 static const int LUT_SIZE = 256;     // shared-memory key -> group id table of the fused variant
 
 struct PrivSlot {
@@ -31,7 +31,7 @@ struct PrivAgg {
     unsigned long long* state;
 };
 struct PrivPlan {
-    int32_t ncols, nconds, nslots, words, naggs, nvals;
+    int32_t ncols, nconds, nslots, words, naggs, pad;
     DCol cols[MAX_PCOLS];
     PrivCond conds[MAX_PCONDS];
     PrivSlot slots[MAX_PSLOTS];
@@ -149,10 +149,13 @@ PG_D void wreduce_sum_carry(unsigned long long& s, unsigned long long& carry) {
     }
 }
 
+// per-row values between the load and the update phase; indexed by slot number only (static after unrolling, so
+// the arrays live in registers)
 struct RowData {
     int g;               // group id, -1: skip the row
     unsigned condbits;
-    unsigned long long v[MAX_PVALS];
+    unsigned long long v0[MAX_PSLOTS];
+    unsigned long long v1[MAX_P128];
 };
 
 // FUSED = true: the group id of a row is resolved inside this kernel from the packed key (no id column in HBM); rows that
@@ -226,15 +229,15 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
                 const PrivSlot& ps = plan.slots[s];
                 if (ps.kind != PS_CNT && ((r.condbits >> ps.cond) & 1)) {
                     const DCol& c = plan.cols[ps.src];
-                    if (ps.conv == CV_DEC128) {
+                    if (s < MAX_P128 && ps.conv == CV_DEC128) {
                         const ulonglong2 p = ((const ulonglong2*)c.values)[row];
-                        r.v[ps.voff] = p.x; r.v[ps.voff + 1] = p.y;
+                        r.v0[s] = p.x; r.v1[s < MAX_P128 ? s : 0] = p.y;
                     } else if (c.type == PG_INTEGER || c.type == PG_DATE) {
-                        r.v[ps.voff] = (unsigned long long)(long long)((const int32_t*)c.values)[row];
+                        r.v0[s] = (unsigned long long)(long long)((const int32_t*)c.values)[row];
                     } else if (c.type == PG_BOOLEAN) {
-                        r.v[ps.voff] = ((const uint8_t*)c.values)[row];
+                        r.v0[s] = ((const uint8_t*)c.values)[row];
                     } else {
-                        r.v[ps.voff] = ((const unsigned long long*)c.values)[row];
+                        r.v0[s] = ((const unsigned long long*)c.values)[row];
                     }
                 }
             }
@@ -253,7 +256,7 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
                     switch (ps.kind) {
                         case PS_CNT: t[0] += 1; break;
                         case PS_ADD2: {
-                            unsigned long long a0 = r.v[ps.voff], a1 = (unsigned long long)((long long)a0 >> 63);
+                            unsigned long long a0 = r.v0[s], a1 = (unsigned long long)((long long)a0 >> 63);
                             unsigned long long s0 = t[0] + a0;
                             t[0] = s0;
                             t[GT] += a1 + (s0 < a0 ? 1ULL : 0ULL);
@@ -261,7 +264,7 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
                         }
                         case PS_ADD3: {
                             unsigned long long a0, a1, a2;
-                            signmag_to_twos(r.v[ps.voff], r.v[ps.voff + 1], a0, a1, a2);
+                            signmag_to_twos(r.v0[s], r.v1[s < MAX_P128 ? s : 0], a0, a1, a2);
                             unsigned long long s0 = t[0] + a0;
                             t[0] = s0;
                             unsigned long long c0 = s0 < a0 ? 1ULL : 0ULL;
@@ -274,17 +277,17 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
                             break;
                         }
                         case PS_F64: {
-                            double d = ps.conv == CV_I2D ? (double)(long long)r.v[ps.voff] : __longlong_as_double((long long)r.v[ps.voff]);
+                            double d = ps.conv == CV_I2D ? (double)(long long)r.v0[s] : __longlong_as_double((long long)r.v0[s]);
                             t[0] = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)t[0]) + d);
                             break;
                         }
                         case PS_MIN: {
-                            long long k = ps.conv == CV_MINKEY ? double_order_key((long long)r.v[ps.voff]) : (long long)r.v[ps.voff];
+                            long long k = ps.conv == CV_MINKEY ? double_order_key((long long)r.v0[s]) : (long long)r.v0[s];
                             if (k < (long long)t[0]) t[0] = (unsigned long long)k;
                             break;
                         }
                         case PS_MAX: {
-                            long long k = ps.conv == CV_MAXKEY ? max_double_key((long long)r.v[ps.voff]) : (long long)r.v[ps.voff];
+                            long long k = ps.conv == CV_MAXKEY ? max_double_key((long long)r.v0[s]) : (long long)r.v0[s];
                             if (k > (long long)t[0]) t[0] = (unsigned long long)k;
                             break;
                         }
@@ -422,16 +425,15 @@ bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids
             cond = p.nconds++;
             p.conds[cond].mask_col = mask_col; p.conds[cond].null_col = null_col;
         }
-        auto find_slot = [&](int kind, int conv, int src_col, int nwords, int nvals) -> int {
+        auto find_slot = [&](int kind, int conv, int src_col, int nwords, int) -> int {
             for (int s = 0; s < p.nslots; s++) {
                 const PrivSlot& ps = p.slots[s];
                 if (ps.kind == kind && ps.conv == conv && ps.src == src_col && ps.cond == cond) return s;
             }
-            if (p.nslots >= MAX_PSLOTS || p.nvals + nvals > MAX_PVALS) return -1;
+            if (p.nslots >= MAX_PSLOTS) return -1;
             PrivSlot& ps = p.slots[p.nslots];
             ps.kind = kind; ps.conv = conv; ps.src = src_col; ps.cond = cond; ps.nwords = nwords; ps.word_off = p.words;
-            ps.voff = p.nvals;
-            p.words += nwords; p.nvals += nvals;
+            p.words += nwords;
             return p.nslots++;
         };
         PrivAgg& pa = p.aggs[a];
@@ -451,6 +453,20 @@ bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids
             default: return false;
         }
         if (op.op != OP_COUNT && pa.val_slot < 0) return false;
+    }
+    // slots fed by 128-bit inputs first (the kernel keeps their second value word in v1[slot], slot < MAX_P128)
+    {
+        int order[MAX_PSLOTS], remap[MAX_PSLOTS], k = 0;
+        for (int s = 0; s < p.nslots; s++) if (p.slots[s].kind == PS_ADD3) order[k++] = s;
+        if (k > MAX_P128) return false;
+        for (int s = 0; s < p.nslots; s++) if (p.slots[s].kind != PS_ADD3) order[k++] = s;
+        PrivSlot tmp[MAX_PSLOTS];
+        for (int i = 0; i < p.nslots; i++) { tmp[i] = p.slots[order[i]]; remap[order[i]] = i; }
+        for (int i = 0; i < p.nslots; i++) p.slots[i] = tmp[i];
+        for (int a = 0; a < p.naggs; a++) {
+            p.aggs[a].cnt_slot = remap[p.aggs[a].cnt_slot];
+            if (p.aggs[a].val_slot >= 0) p.aggs[a].val_slot = remap[p.aggs[a].val_slot];
+        }
     }
     PackSpec pk;
     memset(&pk, 0, sizeof(pk));

@@ -12,46 +12,52 @@
 
 namespace pg {
 
-enum { PS_CNT = 0, PS_ADD2 = 1, PS_ADD3 = 2, PS_F64 = 3, PS_MIN = 4, PS_MAX = 5 };
-enum { CV_INT = 0, CV_I2D = 1, CV_F64 = 2, CV_DEC128 = 3, CV_MINKEY = 4, CV_MAXKEY = 5 };
-static const int MAX_PCOLS = 20;
-static const int MAX_PCONDS = 8;
-static const int MAX_PSLOTS = 10;
-static const int MAX_P128 = 3;       // slots fed by 128-bit inputs come first (they carry a second value word per row)
+// slot kinds; the kernel walks one fixed-trip, switch-free loop per kind (slots are sorted by kind on the host)
+enum { PS_DEC = 0, PS_I64 = 1, PS_I32 = 2, PS_F64 = 3, PS_MIN = 4, PS_MAX = 5, PS_CNT = 6, PS_KINDS = 7 };
+static const int MAX_DEC = 3, MAX_I64 = 6, MAX_I32 = 2, MAX_F64 = 3, MAX_MIN = 2, MAX_MAX = 2, MAX_CNT = 3;
+static const int MAX_PSLOTS = MAX_DEC + MAX_I64 + MAX_I32 + MAX_F64 + MAX_MIN + MAX_MAX + MAX_CNT;
+static const int MAX_PCONDS = 4;
 static const int LUT_SIZE = 256;     // shared-memory key -> group id table of the fused variant
 
-struct PrivSlot {
-    int32_t kind, conv, word_off, nwords, src, cond, voff, pad;
+struct FSlot {
+    const void* ptr;      // argument values (pre-offset)
+    int32_t word_off;     // first private word
+    int32_t cond;         // index into conds[]
+    int32_t conv;         // F64: 1 = convert int64 -> double; MIN/MAX: 1 = double order key
+    int32_t nwords;
 };
-struct PrivCond {
-    int32_t mask_col, null_col;   // indices into cols[] or -1
+struct FCond {
+    const uint8_t* mask;        // BOOLEAN mask values or null
+    const uint8_t* mask_nulls;  // its null flags or null
+    const uint8_t* arg_nulls;   // null flags of the argument or null
 };
 struct PrivAgg {
-    int32_t op, words, cnt_slot, val_slot;
+    int32_t op, words, cnt_word, val_word, val_kind, pad;
     unsigned long long* state;
 };
 struct PrivPlan {
-    int32_t ncols, nconds, nslots, words, naggs, pad;
-    DCol cols[MAX_PCOLS];
-    PrivCond conds[MAX_PCONDS];
-    PrivSlot slots[MAX_PSLOTS];
+    int32_t n[PS_KINDS];
+    int32_t nconds, words, naggs;
+    FSlot dec[MAX_DEC], i64[MAX_I64], i32[MAX_I32], f64[MAX_F64], mn[MAX_MIN], mx[MAX_MAX], cnt[MAX_CNT];
+    FCond conds[MAX_PCONDS];
     PrivAgg aggs[MAX_AGGS];
 };
 
-// ---- fused group-id look-up: short keys are packed into 128 bits and searched in a shared-memory table built from the
-// groups the GroupByHash already numbered.  Bits 120.. of the high word carry one null flag per channel.
+// ---- fused group-id look-up: short keys are packed into two 64-bit words (a key never straddles the words) and searched
+// in a shared-memory table built from the groups the GroupByHash already numbered.  Bits 56.. of word 1 are null flags.
 static const int MAX_PACK_KEYS = 8;
+struct PackKey {
+    const void* values;
+    const uint8_t* nulls;
+    const int32_t* offsets;
+    int32_t type, word, shift, word_off;
+};
 struct PackSpec {
-    int32_t nkeys;
-    int32_t shift[MAX_PACK_KEYS];
-    DCol cols[MAX_PACK_KEYS];
-    // stored groups (GroupByHash key store)
-    const uint64_t* key_rows;
+    int32_t nkeys, bigint_mode, null_gid, row_words;
+    PackKey k[MAX_PACK_KEYS];
+    const uint64_t* key_rows;         // stored groups (GroupByHash key store)
     const uint8_t* arena;
     const int64_t* values_by_group;   // bigint mode
-    int32_t bigint_mode, null_gid;
-    int32_t row_words;
-    int32_t word_off[MAX_PACK_KEYS];
     uint8_t* miss_flag;               // set to 1 for rows the fused pass could not resolve
     unsigned long long* d_miss;
 };
@@ -64,14 +70,6 @@ static inline int pack_width(int32_t t) {
         default: return -1;
     }
 }
-PG_D void or_bits(unsigned long long& w0, unsigned long long& w1, unsigned long long v, int shift) {
-    if (shift < 64) {
-        w0 |= v << shift;
-        if (shift > 0) w1 |= v >> (64 - shift);
-    } else {
-        w1 |= v << (shift - 64);
-    }
-}
 PG_D unsigned long long norm_double_key(long long b) {
     if ((b & 0x7fffffffffffffffLL) == 0) return 0;
     return (unsigned long long)canon_double_bits(b);
@@ -79,30 +77,33 @@ PG_D unsigned long long norm_double_key(long long b) {
 // pack the key of input row `row`; false when a value does not fit the packed form (string longer than 3 bytes)
 PG_D bool pack_row(const PackSpec& ps, int64_t row, unsigned long long& w0, unsigned long long& w1) {
     w0 = 0; w1 = 0;
+    bool ok = true;
 #pragma unroll
     for (int k = 0; k < MAX_PACK_KEYS; k++) {
         if (k < ps.nkeys) {
-            const DCol& c = ps.cols[k];
-            if (c.nulls != nullptr && c.nulls[row]) { w1 |= 1ULL << (56 + k); continue; }
-            unsigned long long v;
-            switch (c.type) {
-                case PG_VARCHAR: case PG_VARBINARY: {
-                    int32_t o = c.offsets[row], len = c.offsets[row + 1] - o;
-                    if (len > 3) return false;
-                    const uint8_t* b = (const uint8_t*)c.values + o;
+            const PackKey& pk = ps.k[k];
+            unsigned long long v = 0;
+            bool isnull = pk.nulls != nullptr && pk.nulls[row] != 0;
+            if (pk.type == PG_VARCHAR || pk.type == PG_VARBINARY) {
+                int32_t o = pk.offsets[row], len = pk.offsets[row + 1] - o;
+                if (len > 3) ok = false;
+                else {
+                    const uint8_t* b = (const uint8_t*)pk.values + o;
                     v = (unsigned long long)len;
-                    for (int t = 0; t < len; t++) v |= (unsigned long long)b[t] << (8 + 8 * t);
-                    break;
+                    if (len > 0) v |= (unsigned long long)b[0] << 8;
+                    if (len > 1) v |= (unsigned long long)b[1] << 16;
+                    if (len > 2) v |= (unsigned long long)b[2] << 24;
                 }
-                case PG_INTEGER: case PG_DATE: v = (unsigned long long)(uint32_t)((const int32_t*)c.values)[row]; break;
-                case PG_BOOLEAN: v = ((const uint8_t*)c.values)[row]; break;
-                case PG_DOUBLE: v = norm_double_key(((const long long*)c.values)[row]); break;
-                default: v = ((const unsigned long long*)c.values)[row];
-            }
-            or_bits(w0, w1, v, ps.shift[k]);
+            } else if (pk.type == PG_INTEGER || pk.type == PG_DATE) v = (unsigned long long)(uint32_t)((const int32_t*)pk.values)[row];
+            else if (pk.type == PG_BOOLEAN) v = ((const uint8_t*)pk.values)[row];
+            else if (pk.type == PG_DOUBLE) v = norm_double_key(((const long long*)pk.values)[row]);
+            else v = ((const unsigned long long*)pk.values)[row];
+            if (isnull) w1 |= 1ULL << (56 + k);
+            else if (pk.word == 0) w0 |= v << pk.shift;
+            else w1 |= v << pk.shift;
         }
     }
-    return true;
+    return ok;
 }
 // pack the stored key of group g (same bit layout)
 PG_D bool pack_group(const PackSpec& ps, int g, unsigned long long& w0, unsigned long long& w1) {
@@ -113,9 +114,10 @@ PG_D bool pack_group(const PackSpec& ps, int g, unsigned long long& w0, unsigned
     }
     const uint64_t* rowp = ps.key_rows + (int64_t)g * ps.row_words;
     for (int k = 0; k < ps.nkeys; k++) {
+        const PackKey& pk = ps.k[k];
         if ((rowp[0] >> k) & 1) { w1 |= 1ULL << (56 + k); continue; }
-        unsigned long long w = rowp[ps.word_off[k]], v;
-        switch (ps.cols[k].type) {
+        unsigned long long w = rowp[pk.word_off], v;
+        switch (pk.type) {
             case PG_VARCHAR: case PG_VARBINARY: {
                 int len = (int)(w & 0xFFFFFF);
                 if (len > 3) return false;
@@ -129,7 +131,7 @@ PG_D bool pack_group(const PackSpec& ps, int g, unsigned long long& w0, unsigned
             case PG_DOUBLE: v = norm_double_key((long long)w); break;
             default: v = w;
         }
-        or_bits(w0, w1, v, ps.shift[k]);
+        if (pk.word == 0) w0 |= v << pk.shift; else w1 |= v << pk.shift;
     }
     return true;
 }
@@ -149,13 +151,15 @@ PG_D void wreduce_sum_carry(unsigned long long& s, unsigned long long& carry) {
     }
 }
 
-// per-row values between the load and the update phase; indexed by slot number only (static after unrolling, so
-// the arrays live in registers)
+// per-row values between the load and the update phase; every index is static after unrolling (registers)
 struct RowData {
     int g;               // group id, -1: skip the row
     unsigned condbits;
-    unsigned long long v0[MAX_PSLOTS];
-    unsigned long long v1[MAX_P128];
+    ulonglong2 dec[MAX_DEC];
+    unsigned long long i64[MAX_I64];
+    int i32[MAX_I32];
+    unsigned long long f64[MAX_F64];
+    unsigned long long mn[MAX_MIN], mx[MAX_MAX];
 };
 
 // FUSED = true: the group id of a row is resolved inside this kernel from the packed key (no id column in HBM); rows that
@@ -168,13 +172,13 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
     __shared__ int lut_gid[FUSED ? LUT_SIZE : 1];
     const int tid = threadIdx.x;
     const int GT = G * T;
-    // ---- init own columns
-    for (int s = 0; s < plan.nslots; s++) {
-        const PrivSlot& ps = plan.slots[s];
-        unsigned long long idv = ps.kind == PS_MIN ? 0x7fffffffffffffffULL : (ps.kind == PS_MAX ? 0x8000000000000000ULL : 0ULL);
-        for (int w = 0; w < ps.nwords; w++)
-            for (int g = 0; g < G; g++) table[(ps.word_off + w) * GT + g * T + tid] = idv;
-    }
+    // ---- init own columns: zeros, then min/max identities
+    for (int w = 0; w < plan.words; w++)
+        for (int g = 0; g < G; g++) table[w * GT + g * T + tid] = 0;
+    for (int s = 0; s < plan.n[PS_MIN]; s++)
+        for (int g = 0; g < G; g++) table[plan.mn[s].word_off * GT + g * T + tid] = 0x7fffffffffffffffULL;
+    for (int s = 0; s < plan.n[PS_MAX]; s++)
+        for (int g = 0; g < G; g++) table[plan.mx[s].word_off * GT + g * T + tid] = 0x8000000000000000ULL;
     if (FUSED) {
         for (int i = tid; i < LUT_SIZE; i += T) lut_gid[i] = -1;
         __syncthreads();
@@ -213,88 +217,89 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
 #pragma unroll
         for (int c = 0; c < MAX_PCONDS; c++) {
             if (c < plan.nconds) {
-                const PrivCond& pc = plan.conds[c];
+                const FCond& pc = plan.conds[c];
                 bool ok = true;
-                if (pc.mask_col >= 0) {
-                    const DCol& m = plan.cols[pc.mask_col];
-                    ok = ((const uint8_t*)m.values)[row] != 0 && !(m.nulls != nullptr && m.nulls[row]);
-                }
-                if (ok && pc.null_col >= 0) ok = plan.cols[pc.null_col].nulls[row] == 0;
+                if (pc.mask != nullptr) ok = pc.mask[row] != 0;
+                if (pc.mask_nulls != nullptr) ok = ok && pc.mask_nulls[row] == 0;
+                if (pc.arg_nulls != nullptr) ok = ok && pc.arg_nulls[row] == 0;
                 r.condbits |= (ok ? 1u : 0u) << c;
             }
         }
 #pragma unroll
-        for (int s = 0; s < MAX_PSLOTS; s++) {
-            if (s < plan.nslots) {
-                const PrivSlot& ps = plan.slots[s];
-                if (ps.kind != PS_CNT && ((r.condbits >> ps.cond) & 1)) {
-                    const DCol& c = plan.cols[ps.src];
-                    if (s < MAX_P128 && ps.conv == CV_DEC128) {
-                        const ulonglong2 p = ((const ulonglong2*)c.values)[row];
-                        r.v0[s] = p.x; r.v1[s < MAX_P128 ? s : 0] = p.y;
-                    } else if (c.type == PG_INTEGER || c.type == PG_DATE) {
-                        r.v0[s] = (unsigned long long)(long long)((const int32_t*)c.values)[row];
-                    } else if (c.type == PG_BOOLEAN) {
-                        r.v0[s] = ((const uint8_t*)c.values)[row];
-                    } else {
-                        r.v0[s] = ((const unsigned long long*)c.values)[row];
-                    }
-                }
-            }
-        }
+        for (int s = 0; s < MAX_DEC; s++) if (s < plan.n[PS_DEC]) r.dec[s] = ((const ulonglong2*)plan.dec[s].ptr)[row];
+#pragma unroll
+        for (int s = 0; s < MAX_I64; s++) if (s < plan.n[PS_I64]) r.i64[s] = ((const unsigned long long*)plan.i64[s].ptr)[row];
+#pragma unroll
+        for (int s = 0; s < MAX_I32; s++) if (s < plan.n[PS_I32]) r.i32[s] = ((const int*)plan.i32[s].ptr)[row];
+#pragma unroll
+        for (int s = 0; s < MAX_F64; s++) if (s < plan.n[PS_F64]) r.f64[s] = ((const unsigned long long*)plan.f64[s].ptr)[row];
+#pragma unroll
+        for (int s = 0; s < MAX_MIN; s++) if (s < plan.n[PS_MIN]) r.mn[s] = ((const unsigned long long*)plan.mn[s].ptr)[row];
+#pragma unroll
+        for (int s = 0; s < MAX_MAX; s++) if (s < plan.n[PS_MAX]) r.mx[s] = ((const unsigned long long*)plan.mx[s].ptr)[row];
+    };
+
+    auto add2 = [&](unsigned long long* t, unsigned long long a0) {
+        unsigned long long a1 = (unsigned long long)((long long)a0 >> 63);
+        unsigned long long s0 = t[0] + a0;
+        t[0] = s0;
+        t[GT] += a1 + (s0 < a0 ? 1ULL : 0ULL);
     };
 
     auto apply_row = [&](const RowData& r) {
         if (r.g < 0) return;
         unsigned long long* base = table + r.g * T + tid;
 #pragma unroll
-        for (int s = 0; s < MAX_PSLOTS; s++) {
-            if (s < plan.nslots) {
-                const PrivSlot& ps = plan.slots[s];
-                if ((r.condbits >> ps.cond) & 1) {
-                    unsigned long long* t = base + ps.word_off * GT;
-                    switch (ps.kind) {
-                        case PS_CNT: t[0] += 1; break;
-                        case PS_ADD2: {
-                            unsigned long long a0 = r.v0[s], a1 = (unsigned long long)((long long)a0 >> 63);
-                            unsigned long long s0 = t[0] + a0;
-                            t[0] = s0;
-                            t[GT] += a1 + (s0 < a0 ? 1ULL : 0ULL);
-                            break;
-                        }
-                        case PS_ADD3: {
-                            unsigned long long a0, a1, a2;
-                            signmag_to_twos(r.v0[s], r.v1[s < MAX_P128 ? s : 0], a0, a1, a2);
-                            unsigned long long s0 = t[0] + a0;
-                            t[0] = s0;
-                            unsigned long long c0 = s0 < a0 ? 1ULL : 0ULL;
-                            unsigned long long add1 = a1 + c0;
-                            unsigned long long c1 = add1 < c0 ? 1ULL : 0ULL;
-                            unsigned long long s1 = t[GT] + add1;
-                            t[GT] = s1;
-                            c1 += s1 < add1 ? 1ULL : 0ULL;
-                            t[2 * GT] += a2 + c1;
-                            break;
-                        }
-                        case PS_F64: {
-                            double d = ps.conv == CV_I2D ? (double)(long long)r.v0[s] : __longlong_as_double((long long)r.v0[s]);
-                            t[0] = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)t[0]) + d);
-                            break;
-                        }
-                        case PS_MIN: {
-                            long long k = ps.conv == CV_MINKEY ? double_order_key((long long)r.v0[s]) : (long long)r.v0[s];
-                            if (k < (long long)t[0]) t[0] = (unsigned long long)k;
-                            break;
-                        }
-                        case PS_MAX: {
-                            long long k = ps.conv == CV_MAXKEY ? max_double_key((long long)r.v0[s]) : (long long)r.v0[s];
-                            if (k > (long long)t[0]) t[0] = (unsigned long long)k;
-                            break;
-                        }
-                    }
-                }
+        for (int s = 0; s < MAX_DEC; s++) {
+            if (s < plan.n[PS_DEC] && ((r.condbits >> plan.dec[s].cond) & 1)) {
+                unsigned long long* t = base + plan.dec[s].word_off * GT;
+                unsigned long long a0, a1, a2;
+                signmag_to_twos(r.dec[s].x, r.dec[s].y, a0, a1, a2);
+                unsigned long long s0 = t[0] + a0;
+                t[0] = s0;
+                unsigned long long c0 = s0 < a0 ? 1ULL : 0ULL;
+                unsigned long long add1 = a1 + c0;
+                unsigned long long c1 = add1 < c0 ? 1ULL : 0ULL;
+                unsigned long long s1 = t[GT] + add1;
+                t[GT] = s1;
+                c1 += s1 < add1 ? 1ULL : 0ULL;
+                t[2 * GT] += a2 + c1;
             }
         }
+#pragma unroll
+        for (int s = 0; s < MAX_I64; s++)
+            if (s < plan.n[PS_I64] && ((r.condbits >> plan.i64[s].cond) & 1)) add2(base + plan.i64[s].word_off * GT, r.i64[s]);
+#pragma unroll
+        for (int s = 0; s < MAX_I32; s++)
+            if (s < plan.n[PS_I32] && ((r.condbits >> plan.i32[s].cond) & 1))
+                add2(base + plan.i32[s].word_off * GT, (unsigned long long)(long long)r.i32[s]);
+#pragma unroll
+        for (int s = 0; s < MAX_F64; s++) {
+            if (s < plan.n[PS_F64] && ((r.condbits >> plan.f64[s].cond) & 1)) {
+                unsigned long long* t = base + plan.f64[s].word_off * GT;
+                double d = plan.f64[s].conv ? (double)(long long)r.f64[s] : __longlong_as_double((long long)r.f64[s]);
+                t[0] = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)t[0]) + d);
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < MAX_MIN; s++) {
+            if (s < plan.n[PS_MIN] && ((r.condbits >> plan.mn[s].cond) & 1)) {
+                unsigned long long* t = base + plan.mn[s].word_off * GT;
+                long long k = plan.mn[s].conv ? double_order_key((long long)r.mn[s]) : (long long)r.mn[s];
+                if (k < (long long)t[0]) t[0] = (unsigned long long)k;
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < MAX_MAX; s++) {
+            if (s < plan.n[PS_MAX] && ((r.condbits >> plan.mx[s].cond) & 1)) {
+                unsigned long long* t = base + plan.mx[s].word_off * GT;
+                long long k = plan.mx[s].conv ? max_double_key((long long)r.mx[s]) : (long long)r.mx[s];
+                if (k > (long long)t[0]) t[0] = (unsigned long long)k;
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < MAX_CNT; s++)
+            if (s < plan.n[PS_CNT] && ((r.condbits >> plan.cnt[s].cond) & 1)) base[plan.cnt[s].word_off * GT] += 1;
     };
 
     // ---- row loop, software-pipelined: the loads of the next row are issued before the shared-memory updates of this one
@@ -321,30 +326,28 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
     }
     for (int a = 0; a < plan.naggs; a++) {
         const PrivAgg& pa = plan.aggs[a];
-        const PrivSlot& cs = plan.slots[pa.cnt_slot];
         for (int g = 0; g < G; g++) {
-            unsigned long long cnt = table[cs.word_off * GT + g * T + tid], zero = 0;
+            unsigned long long cnt = table[pa.cnt_word * GT + g * T + tid], zero = 0;
             wreduce_sum_carry(cnt, zero);
             cnt = __shfl_sync(0xffffffffu, cnt, 0);
             if (cnt == 0) continue;   // warp-uniform
             unsigned long long* st = pa.state + (int64_t)g * pa.words;
             if (pa.op == OP_COUNT) { if (lane == 0) atomicAdd(&st[0], cnt); continue; }
-            const PrivSlot& vs = plan.slots[pa.val_slot];
-            const unsigned long long* col = table + vs.word_off * GT + g * T + tid;
-            switch (vs.kind) {
-                case PS_ADD2: {
+            const unsigned long long* col = table + pa.val_word * GT + g * T + tid;
+            switch (pa.val_kind) {
+                case PS_I64: case PS_I32: {
                     unsigned long long s0 = col[0], c0 = 0, s1 = col[GT], c1 = 0;
                     wreduce_sum_carry(s0, c0);
                     wreduce_sum_carry(s1, c1);
                     if (lane == 0) {
-                        unsigned long long hi = s1 + c0;   // 128-bit signed partial (never overflows: < 2^31 rows of 64-bit values per thread)
+                        unsigned long long hi = s1 + c0;   // 128-bit signed partial (cannot overflow: < 2^63 rows of 64-bit values)
                         atomicAdd(&st[0], cnt);
                         if (pa.op == OP_SUM_I64) atomic_add_chain2(st + 1, s0, hi);
                         else atomic_add_chain3(st + 1, s0, hi, (unsigned long long)((long long)hi >> 63));
                     }
                     break;
                 }
-                case PS_ADD3: {
+                case PS_DEC: {
                     unsigned long long s0 = col[0], c0 = 0, s1 = col[GT], c1 = 0, s2 = col[2 * GT], c2 = 0;
                     wreduce_sum_carry(s0, c0);
                     wreduce_sum_carry(s1, c1);
@@ -369,11 +372,11 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
 #pragma unroll
                     for (int k = 16; k > 0; k >>= 1) {
                         long long o = __shfl_down_sync(0xffffffffu, v, k);
-                        v = vs.kind == PS_MIN ? (o < v ? o : v) : (o > v ? o : v);
+                        v = pa.val_kind == PS_MIN ? (o < v ? o : v) : (o > v ? o : v);
                     }
                     if (lane == 0) {
                         st[0] = 1;
-                        if (vs.kind == PS_MIN) atomicMin((long long*)&st[1], v); else atomicMax((long long*)&st[1], v);
+                        if (pa.val_kind == PS_MIN) atomicMin((long long*)&st[1], v); else atomicMax((long long*)&st[1], v);
                     }
                     break;
                 }
@@ -383,26 +386,22 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
     }
 }
 
-// ---- host: build the plan (dedupe columns, conditions and state), pick the block size, launch
-static int find_col(PrivPlan& p, const DCol& c) {
-    for (int i = 0; i < p.ncols; i++)
-        if (p.cols[i].values == c.values && p.cols[i].nulls == c.nulls && p.cols[i].type == c.type) return i;
-    if (p.ncols >= MAX_PCOLS) return -1;
-    p.cols[p.ncols] = c;
-    return p.ncols++;
-}
-
-// keys that fit the 120-bit packed form can be resolved inside the accumulation kernel
-bool fused_keys_packable(const KeyLayout& L) {
+// ---- host: build the plan (dedupe conditions and state, sort slots by kind), pick the block size, launch
+// keys that fit the two-word packed form can be resolved inside the accumulation kernel
+static bool pack_layout(const KeyLayout& L, int32_t* word, int32_t* shift) {
     if (L.nkeys > MAX_PACK_KEYS) return false;
-    int bits = 0;
+    int used[2] = {0, 0};
     for (int k = 0; k < L.nkeys; k++) {
         int w = pack_width(L.types[k]);
         if (w < 0) return false;
-        bits += w;
+        int target = (used[0] + w <= 64) ? 0 : 1;
+        if (target == 1 && used[1] + w > 56) return false;
+        if (word) { word[k] = target; shift[k] = used[target]; }
+        used[target] += w;
     }
-    return bits <= 120;
+    return true;
 }
+bool fused_keys_packable(const KeyLayout& L) { return pack_layout(L, nullptr, nullptr); }
 
 bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count, const uint8_t* only_rows,
                         const FusedLookup* fused) {
@@ -410,75 +409,72 @@ bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids
     PrivPlan p;
     memset(&p, 0, sizeof(p));
     p.naggs = prog.naggs;
+    FSlot* lists[PS_KINDS] = {p.dec, p.i64, p.i32, p.f64, p.mn, p.mx, p.cnt};
+    const int maxn[PS_KINDS] = {MAX_DEC, MAX_I64, MAX_I32, MAX_F64, MAX_MIN, MAX_MAX, MAX_CNT};
+    const int kwords[PS_KINDS] = {3, 2, 2, 1, 1, 1, 1};
     for (int a = 0; a < prog.naggs; a++) {
         const AggOp& op = prog.ops[a];
         if (op.op == OP_MIN128 || op.op == OP_MAX128) return false;
-        int mask_col = -1, null_col = -1;
-        if (op.mask.values) { mask_col = find_col(p, op.mask); if (mask_col < 0) return false; }
-        int src = -1;
-        if (op.op != OP_COUNT || (op.skip_null && op.arg.nulls)) { src = find_col(p, op.arg); if (src < 0) return false; }
-        if (op.skip_null && op.arg.nulls) null_col = src;
+        FCond fc;
+        fc.mask = (const uint8_t*)op.mask.values; fc.mask_nulls = op.mask.values ? op.mask.nulls : nullptr;
+        fc.arg_nulls = op.skip_null ? op.arg.nulls : nullptr;
         int cond = -1;
-        for (int c = 0; c < p.nconds; c++) if (p.conds[c].mask_col == mask_col && p.conds[c].null_col == null_col) cond = c;
+        for (int c = 0; c < p.nconds; c++)
+            if (p.conds[c].mask == fc.mask && p.conds[c].mask_nulls == fc.mask_nulls && p.conds[c].arg_nulls == fc.arg_nulls) cond = c;
         if (cond < 0) {
             if (p.nconds >= MAX_PCONDS) return false;
             cond = p.nconds++;
-            p.conds[cond].mask_col = mask_col; p.conds[cond].null_col = null_col;
+            p.conds[cond] = fc;
         }
-        auto find_slot = [&](int kind, int conv, int src_col, int nwords, int) -> int {
-            for (int s = 0; s < p.nslots; s++) {
-                const PrivSlot& ps = p.slots[s];
-                if (ps.kind == kind && ps.conv == conv && ps.src == src_col && ps.cond == cond) return s;
-            }
-            if (p.nslots >= MAX_PSLOTS) return -1;
-            PrivSlot& ps = p.slots[p.nslots];
-            ps.kind = kind; ps.conv = conv; ps.src = src_col; ps.cond = cond; ps.nwords = nwords; ps.word_off = p.words;
-            p.words += nwords;
-            return p.nslots++;
+        auto find_slot = [&](int kind, const void* ptr, int conv) -> int {   // returns the private word offset or -1
+            FSlot* l = lists[kind];
+            for (int s = 0; s < p.n[kind]; s++)
+                if (l[s].ptr == ptr && l[s].cond == cond && l[s].conv == conv) return l[s].word_off;
+            if (p.n[kind] >= maxn[kind]) return -1;
+            FSlot& f = l[p.n[kind]++];
+            f.ptr = ptr; f.cond = cond; f.conv = conv; f.nwords = kwords[kind]; f.word_off = p.words;
+            p.words += kwords[kind];
+            return f.word_off;
         };
         PrivAgg& pa = p.aggs[a];
         pa.op = op.op; pa.words = op.words; pa.state = op.state;
-        pa.cnt_slot = find_slot(PS_CNT, 0, -1, 1, 0);
-        if (pa.cnt_slot < 0) return false;
-        pa.val_slot = -1;
+        pa.cnt_word = find_slot(PS_CNT, nullptr, 0);
+        if (pa.cnt_word < 0) return false;
+        pa.val_word = -1; pa.val_kind = PS_CNT;
+        const bool is32 = op.in_type == PG_INTEGER || op.in_type == PG_DATE;
         switch (op.op) {
             case OP_COUNT: break;
-            case OP_SUM_I64: pa.val_slot = find_slot(PS_ADD2, CV_INT, src, 2, 1); break;
-            case OP_SUM_F64: pa.val_slot = find_slot(PS_F64, op.convert_i2d ? CV_I2D : CV_F64, src, 1, 1); break;
-            case OP_SUM_DEC:
-                pa.val_slot = op.in_type == PG_LONG_DECIMAL ? find_slot(PS_ADD3, CV_DEC128, src, 3, 2) : find_slot(PS_ADD2, CV_INT, src, 2, 1);
+            case OP_SUM_I64: pa.val_kind = is32 ? PS_I32 : PS_I64; break;
+            case OP_SUM_F64:
+                if (is32) return false;
+                pa.val_kind = PS_F64;
                 break;
-            case OP_MIN64: pa.val_slot = find_slot(PS_MIN, op.in_type == PG_DOUBLE ? CV_MINKEY : CV_INT, src, 1, 1); break;
-            case OP_MAX64: pa.val_slot = find_slot(PS_MAX, op.in_type == PG_DOUBLE ? CV_MAXKEY : CV_INT, src, 1, 1); break;
+            case OP_SUM_DEC: pa.val_kind = op.in_type == PG_LONG_DECIMAL ? PS_DEC : PS_I64; break;
+            case OP_MIN64: case OP_MAX64:
+                if (is32 || op.in_type == PG_BOOLEAN) return false;
+                pa.val_kind = op.op == OP_MIN64 ? PS_MIN : PS_MAX;
+                break;
             default: return false;
         }
-        if (op.op != OP_COUNT && pa.val_slot < 0) return false;
-    }
-    // slots fed by 128-bit inputs first (the kernel keeps their second value word in v1[slot], slot < MAX_P128)
-    {
-        int order[MAX_PSLOTS], remap[MAX_PSLOTS], k = 0;
-        for (int s = 0; s < p.nslots; s++) if (p.slots[s].kind == PS_ADD3) order[k++] = s;
-        if (k > MAX_P128) return false;
-        for (int s = 0; s < p.nslots; s++) if (p.slots[s].kind != PS_ADD3) order[k++] = s;
-        PrivSlot tmp[MAX_PSLOTS];
-        for (int i = 0; i < p.nslots; i++) { tmp[i] = p.slots[order[i]]; remap[order[i]] = i; }
-        for (int i = 0; i < p.nslots; i++) p.slots[i] = tmp[i];
-        for (int a = 0; a < p.naggs; a++) {
-            p.aggs[a].cnt_slot = remap[p.aggs[a].cnt_slot];
-            if (p.aggs[a].val_slot >= 0) p.aggs[a].val_slot = remap[p.aggs[a].val_slot];
+        if (op.op != OP_COUNT) {
+            int conv = 0;
+            if (pa.val_kind == PS_F64) conv = op.convert_i2d ? 1 : 0;
+            if (pa.val_kind == PS_MIN || pa.val_kind == PS_MAX) conv = op.in_type == PG_DOUBLE ? 1 : 0;
+            pa.val_word = find_slot(pa.val_kind, op.arg.values, conv);
+            if (pa.val_word < 0) return false;
         }
     }
     PackSpec pk;
     memset(&pk, 0, sizeof(pk));
     if (fused) {
         const KeyLayout& L = *fused->layout;
-        if (!fused_keys_packable(L)) return false;
+        int32_t word[MAX_PACK_KEYS], shift[MAX_PACK_KEYS];
+        if (!pack_layout(L, word, shift)) return false;
         pk.nkeys = L.nkeys;
-        int bits = 0;
         for (int k = 0; k < L.nkeys; k++) {
-            pk.shift[k] = bits; bits += pack_width(L.types[k]);
-            pk.cols[k] = fused->keys->c[k];
-            pk.word_off[k] = L.word_off[k];
+            const DCol& c = fused->keys->c[k];
+            pk.k[k].values = c.values; pk.k[k].nulls = c.nulls; pk.k[k].offsets = c.offsets; pk.k[k].type = c.type;
+            pk.k[k].word = word[k]; pk.k[k].shift = shift[k]; pk.k[k].word_off = L.word_off[k];
         }
         pk.key_rows = fused->key_rows; pk.arena = fused->arena; pk.values_by_group = fused->values_by_group;
         pk.bigint_mode = fused->bigint_mode; pk.null_gid = fused->null_gid; pk.row_words = L.row_words;

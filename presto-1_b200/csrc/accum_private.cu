@@ -22,7 +22,7 @@ static const int LUT_SIZE = 256;     // shared-memory key -> group id table of t
 struct FSlot {
     const void* ptr;      // argument values (pre-offset)
     int32_t word_off;     // first private word
-    int32_t cond;         // index into conds[]
+    uint32_t cmask;       // bit of the condition under which a row contributes (0 = unused slot)
     int32_t conv;         // F64: 1 = convert int64 -> double; MIN/MAX: 1 = double order key
     int32_t nwords;
 };
@@ -78,9 +78,9 @@ PG_D unsigned long long norm_double_key(long long b) {
 PG_D bool pack_row(const PackSpec& ps, int64_t row, unsigned long long& w0, unsigned long long& w1) {
     w0 = 0; w1 = 0;
     bool ok = true;
-#pragma unroll
-    for (int k = 0; k < MAX_PACK_KEYS; k++) {
-        if (k < ps.nkeys) {
+#pragma unroll 1
+    for (int k = 0; k < ps.nkeys; k++) {
+        {
             const PackKey& pk = ps.k[k];
             unsigned long long v = 0;
             bool isnull = pk.nulls != nullptr && pk.nulls[row] != 0;
@@ -225,18 +225,31 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
                 r.condbits |= (ok ? 1u : 0u) << c;
             }
         }
+        const unsigned cb = r.condbits;
+        if (plan.n[PS_DEC]) {
 #pragma unroll
-        for (int s = 0; s < MAX_DEC; s++) if (s < plan.n[PS_DEC]) r.dec[s] = ((const ulonglong2*)plan.dec[s].ptr)[row];
+            for (int s = 0; s < MAX_DEC; s++) if (cb & plan.dec[s].cmask) r.dec[s] = ((const ulonglong2*)plan.dec[s].ptr)[row];
+        }
+        if (plan.n[PS_I64]) {
 #pragma unroll
-        for (int s = 0; s < MAX_I64; s++) if (s < plan.n[PS_I64]) r.i64[s] = ((const unsigned long long*)plan.i64[s].ptr)[row];
+            for (int s = 0; s < MAX_I64; s++) if (cb & plan.i64[s].cmask) r.i64[s] = ((const unsigned long long*)plan.i64[s].ptr)[row];
+        }
+        if (plan.n[PS_I32]) {
 #pragma unroll
-        for (int s = 0; s < MAX_I32; s++) if (s < plan.n[PS_I32]) r.i32[s] = ((const int*)plan.i32[s].ptr)[row];
+            for (int s = 0; s < MAX_I32; s++) if (cb & plan.i32[s].cmask) r.i32[s] = ((const int*)plan.i32[s].ptr)[row];
+        }
+        if (plan.n[PS_F64]) {
 #pragma unroll
-        for (int s = 0; s < MAX_F64; s++) if (s < plan.n[PS_F64]) r.f64[s] = ((const unsigned long long*)plan.f64[s].ptr)[row];
+            for (int s = 0; s < MAX_F64; s++) if (cb & plan.f64[s].cmask) r.f64[s] = ((const unsigned long long*)plan.f64[s].ptr)[row];
+        }
+        if (plan.n[PS_MIN]) {
 #pragma unroll
-        for (int s = 0; s < MAX_MIN; s++) if (s < plan.n[PS_MIN]) r.mn[s] = ((const unsigned long long*)plan.mn[s].ptr)[row];
+            for (int s = 0; s < MAX_MIN; s++) if (cb & plan.mn[s].cmask) r.mn[s] = ((const unsigned long long*)plan.mn[s].ptr)[row];
+        }
+        if (plan.n[PS_MAX]) {
 #pragma unroll
-        for (int s = 0; s < MAX_MAX; s++) if (s < plan.n[PS_MAX]) r.mx[s] = ((const unsigned long long*)plan.mx[s].ptr)[row];
+            for (int s = 0; s < MAX_MAX; s++) if (cb & plan.mx[s].cmask) r.mx[s] = ((const unsigned long long*)plan.mx[s].ptr)[row];
+        }
     };
 
     auto add2 = [&](unsigned long long* t, unsigned long long a0) {
@@ -249,73 +262,85 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
     auto apply_row = [&](const RowData& r) {
         if (r.g < 0) return;
         unsigned long long* base = table + r.g * T + tid;
+        const unsigned cb = r.condbits;
+        if (plan.n[PS_DEC]) {
 #pragma unroll
-        for (int s = 0; s < MAX_DEC; s++) {
-            if (s < plan.n[PS_DEC] && ((r.condbits >> plan.dec[s].cond) & 1)) {
-                unsigned long long* t = base + plan.dec[s].word_off * GT;
-                unsigned long long a0, a1, a2;
-                signmag_to_twos(r.dec[s].x, r.dec[s].y, a0, a1, a2);
-                unsigned long long s0 = t[0] + a0;
-                t[0] = s0;
-                unsigned long long c0 = s0 < a0 ? 1ULL : 0ULL;
-                unsigned long long add1 = a1 + c0;
-                unsigned long long c1 = add1 < c0 ? 1ULL : 0ULL;
-                unsigned long long s1 = t[GT] + add1;
-                t[GT] = s1;
-                c1 += s1 < add1 ? 1ULL : 0ULL;
-                t[2 * GT] += a2 + c1;
+            for (int s = 0; s < MAX_DEC; s++) {
+                if (cb & plan.dec[s].cmask) {
+                    unsigned long long* t = base + plan.dec[s].word_off * GT;
+                    unsigned long long a0, a1, a2;
+                    signmag_to_twos(r.dec[s].x, r.dec[s].y, a0, a1, a2);
+                    unsigned long long s0 = t[0] + a0;
+                    t[0] = s0;
+                    unsigned long long c0 = s0 < a0 ? 1ULL : 0ULL;
+                    unsigned long long add1 = a1 + c0;
+                    unsigned long long c1 = add1 < c0 ? 1ULL : 0ULL;
+                    unsigned long long s1 = t[GT] + add1;
+                    t[GT] = s1;
+                    c1 += s1 < add1 ? 1ULL : 0ULL;
+                    t[2 * GT] += a2 + c1;
+                }
             }
         }
+        if (plan.n[PS_I64]) {
 #pragma unroll
-        for (int s = 0; s < MAX_I64; s++)
-            if (s < plan.n[PS_I64] && ((r.condbits >> plan.i64[s].cond) & 1)) add2(base + plan.i64[s].word_off * GT, r.i64[s]);
+            for (int s = 0; s < MAX_I64; s++) if (cb & plan.i64[s].cmask) add2(base + plan.i64[s].word_off * GT, r.i64[s]);
+        }
+        if (plan.n[PS_I32]) {
 #pragma unroll
-        for (int s = 0; s < MAX_I32; s++)
-            if (s < plan.n[PS_I32] && ((r.condbits >> plan.i32[s].cond) & 1))
-                add2(base + plan.i32[s].word_off * GT, (unsigned long long)(long long)r.i32[s]);
+            for (int s = 0; s < MAX_I32; s++)
+                if (cb & plan.i32[s].cmask) add2(base + plan.i32[s].word_off * GT, (unsigned long long)(long long)r.i32[s]);
+        }
+        if (plan.n[PS_F64]) {
 #pragma unroll
-        for (int s = 0; s < MAX_F64; s++) {
-            if (s < plan.n[PS_F64] && ((r.condbits >> plan.f64[s].cond) & 1)) {
-                unsigned long long* t = base + plan.f64[s].word_off * GT;
-                double d = plan.f64[s].conv ? (double)(long long)r.f64[s] : __longlong_as_double((long long)r.f64[s]);
-                t[0] = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)t[0]) + d);
+            for (int s = 0; s < MAX_F64; s++) {
+                if (cb & plan.f64[s].cmask) {
+                    unsigned long long* t = base + plan.f64[s].word_off * GT;
+                    double d = plan.f64[s].conv ? (double)(long long)r.f64[s] : __longlong_as_double((long long)r.f64[s]);
+                    t[0] = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)t[0]) + d);
+                }
             }
         }
+        if (plan.n[PS_MIN]) {
 #pragma unroll
-        for (int s = 0; s < MAX_MIN; s++) {
-            if (s < plan.n[PS_MIN] && ((r.condbits >> plan.mn[s].cond) & 1)) {
-                unsigned long long* t = base + plan.mn[s].word_off * GT;
-                long long k = plan.mn[s].conv ? double_order_key((long long)r.mn[s]) : (long long)r.mn[s];
-                if (k < (long long)t[0]) t[0] = (unsigned long long)k;
+            for (int s = 0; s < MAX_MIN; s++) {
+                if (cb & plan.mn[s].cmask) {
+                    unsigned long long* t = base + plan.mn[s].word_off * GT;
+                    long long k = plan.mn[s].conv ? double_order_key((long long)r.mn[s]) : (long long)r.mn[s];
+                    if (k < (long long)t[0]) t[0] = (unsigned long long)k;
+                }
             }
         }
+        if (plan.n[PS_MAX]) {
 #pragma unroll
-        for (int s = 0; s < MAX_MAX; s++) {
-            if (s < plan.n[PS_MAX] && ((r.condbits >> plan.mx[s].cond) & 1)) {
-                unsigned long long* t = base + plan.mx[s].word_off * GT;
-                long long k = plan.mx[s].conv ? max_double_key((long long)r.mx[s]) : (long long)r.mx[s];
-                if (k > (long long)t[0]) t[0] = (unsigned long long)k;
+            for (int s = 0; s < MAX_MAX; s++) {
+                if (cb & plan.mx[s].cmask) {
+                    unsigned long long* t = base + plan.mx[s].word_off * GT;
+                    long long k = plan.mx[s].conv ? max_double_key((long long)r.mx[s]) : (long long)r.mx[s];
+                    if (k > (long long)t[0]) t[0] = (unsigned long long)k;
+                }
             }
         }
 #pragma unroll
         for (int s = 0; s < MAX_CNT; s++)
-            if (s < plan.n[PS_CNT] && ((r.condbits >> plan.cnt[s].cond) & 1)) base[plan.cnt[s].word_off * GT] += 1;
+            if (cb & plan.cnt[s].cmask) base[plan.cnt[s].word_off * GT] += 1;
     };
 
     // ---- row loop, software-pipelined: the loads of the next row are issued before the shared-memory updates of this one
     const int64_t stride = (int64_t)gridDim.x * T;
     int64_t row = (int64_t)blockIdx.x * T + tid;
-    RowData cur;
-    cur.g = -1;
-    if (row < n) load_row(row, cur);
-    while (row < n) {
-        int64_t nrow = row + stride;
-        RowData nxt;
-        nxt.g = -1;
-        if (nrow < n) load_row(nrow, nxt);
-        apply_row(cur);
-        cur = nxt;
-        row = nrow;
+    RowData ra, rb;
+    ra.g = -1; rb.g = -1;
+    if (row < n) load_row(row, ra);
+    while (row < n) {                       // two rows per trip, ping-pong registers: no copies
+        int64_t r1 = row + stride, r2 = r1 + stride;
+        rb.g = -1;
+        if (r1 < n) load_row(r1, rb);
+        apply_row(ra);
+        ra.g = -1;
+        if (r2 < n) load_row(r2, ra);
+        apply_row(rb);
+        row = r2;
     }
     // ---- flush: per aggregate and group, reduce the warp's 32 columns and fold into the global state
     const int lane = tid & 31;
@@ -429,10 +454,10 @@ bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids
         auto find_slot = [&](int kind, const void* ptr, int conv) -> int {   // returns the private word offset or -1
             FSlot* l = lists[kind];
             for (int s = 0; s < p.n[kind]; s++)
-                if (l[s].ptr == ptr && l[s].cond == cond && l[s].conv == conv) return l[s].word_off;
+                if (l[s].ptr == ptr && l[s].cmask == (1u << cond) && l[s].conv == conv) return l[s].word_off;
             if (p.n[kind] >= maxn[kind]) return -1;
             FSlot& f = l[p.n[kind]++];
-            f.ptr = ptr; f.cond = cond; f.conv = conv; f.nwords = kwords[kind]; f.word_off = p.words;
+            f.ptr = ptr; f.cmask = 1u << cond; f.conv = conv; f.nwords = kwords[kind]; f.word_off = p.words;
             p.words += kwords[kind];
             return f.word_off;
         };

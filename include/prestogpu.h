@@ -235,6 +235,21 @@ PG_API int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* o
 /* partial-aggregation flush: forget all groups (OP/HashAggregationOperator.java:501-517) */
 PG_API int32_t pg_hashagg_reset(pg_hashagg* op);
 
+/* =====================================================================================
+ * Hash partitioning for the multi-GPU exchange — replaces the row routing of OP/exchange/LocalPartitionGenerator.java:50-63,
+ * OP/exchange/PartitioningExchanger.java:79-95 and OP/HashGenerator.java:24-35 (PartitionedOutputOperator).  The exchange
+ * itself is an NCCL all-to-all of the partition-major columns, or direct stores into the receivers' buffers over NVLink.
+ * ===================================================================================== */
+enum { PG_PARTITION_REMOTE = 0 /* (rawHash & MAX_LONG) % n */, PG_PARTITION_LOCAL = 1 /* xxhash64(reverse(rawHash)) & (n-1) */ };
+typedef struct pg_partitioner pg_partitioner;
+PG_API int32_t pg_partition_create(pg_ctx* ctx, const pg_col* keys, int32_t nkeys, const pg_col* hash_col, int64_t n, int32_t nparts,
+                                   int32_t mode, int64_t* out_counts, pg_partitioner** out);
+PG_API int32_t pg_partition_destroy(pg_partitioner* pt);
+PG_API int32_t pg_partition_scatter(pg_partitioner* pt, const pg_col* in, pg_col_out* out);
+PG_API int32_t pg_partition_scatter_peers(pg_partitioner* pt, const pg_col* in, void* const* peer_values, uint8_t* const* peer_nulls,
+                                          const int64_t* peer_row_offset);
+PG_API int32_t pg_partition_ids(pg_partitioner* pt, uint8_t* out, int32_t out_mem);
+
 #ifdef __cplusplus
 }
 #endif

@@ -87,6 +87,11 @@ _PROTOS = {
     "pg_hashagg_get_output": (I32, [P, I64, I64, PCOLOUT, PI64]),
     "pg_hashagg_varwidth_bytes": (I32, [P, I32, PI64]),
     "pg_hashagg_reset": (I32, [P]),
+    "pg_partition_create": (I32, [P, PCOL, I32, PCOL, I64, I32, I32, PI64, C.POINTER(P)]),
+    "pg_partition_destroy": (I32, [P]),
+    "pg_partition_scatter": (I32, [P, PCOL, PCOLOUT]),
+    "pg_partition_scatter_peers": (I32, [P, PCOL, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), PI64]),
+    "pg_partition_ids": (I32, [P, P, I32]),
     "pg_joinbuild_create": (I32, [P, PI32, I32, PI32, I32, I32, I64, C.POINTER(P)]),
     "pg_joinbuild_destroy": (I32, [P]),
     "pg_joinbuild_add_page": (I32, [P, PCOL, I64]),

@@ -1,0 +1,246 @@
+// partition.cu — hash partitioning of a page for the multi-GPU exchange (replaces the row routing of
+// MAIN/operator/exchange/LocalPartitionGenerator.java:50-63, PartitioningExchanger.java:79-95 and
+// MAIN/operator/PartitionedOutputOperator / HashGenerator.getPartition, MAIN/operator/HashGenerator.java:24-35).
+//
+// Three kernels: (1) per-tile histogram of partition ids, (2) scan of the (partition-major, tile-minor) counts,
+// (3) stable ranking: dest[row] = offset[partition][tile] + rank of the row among the tile's rows of that partition.
+// Columns are then scattered with out[dest[row]] = in[row]; rows keep their relative order inside a partition.
+// The scatter can target local memory (NCCL all-to-all follows) or peer GPUs' receive buffers directly (P2P over NVLink).
+#include "groupby_dev.cuh"
+#include "scan.cuh"
+
+namespace pg {
+
+static const int PART_THREADS = 256;
+static const int PART_ITEMS = 8;
+static const int PART_TILE = PART_THREADS * PART_ITEMS;
+static const int MAX_PARTS = 64;
+
+// mode 0: HashGenerator.getPartition = (rawHash & Long.MAX_VALUE) % partitionCount
+// mode 1: LocalPartitionGenerator = (int) XxHash64.hash(Long.reverse(rawHash)) & (partitionCount - 1)
+PG_D int partition_of(int64_t raw, int nparts, int mode) {
+    if (mode == 0) return (int)((raw & 0x7fffffffffffffffLL) % nparts);
+    return (int)xxh64_long((int64_t)bit_reverse64((uint64_t)raw)) & (nparts - 1);
+}
+PG_D int64_t part_row_hash(const KeyCols& kc, int nkeys, const DCol& hash_col, int has_hash, int64_t row) {
+    return has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, nkeys, row);
+}
+
+__global__ void __launch_bounds__(PART_THREADS) part_hist_kernel(KeyCols kc, int nkeys, DCol hash_col, int has_hash, int64_t n, int nparts,
+                                                                 int mode, uint8_t* part_of_row, Pair64* counts, int64_t ntiles) {
+    __shared__ int hist[MAX_PARTS];
+    if (threadIdx.x < MAX_PARTS) hist[threadIdx.x] = 0;
+    __syncthreads();
+    int64_t base = (int64_t)blockIdx.x * PART_TILE;
+#pragma unroll 2
+    for (int j = 0; j < PART_ITEMS; j++) {
+        int64_t row = base + (int64_t)j * PART_THREADS + threadIdx.x;
+        if (row < n) {
+            int p = partition_of(part_row_hash(kc, nkeys, hash_col, has_hash, row), nparts, mode);
+            part_of_row[row] = (uint8_t)p;
+            atomicAdd(&hist[p], 1);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < nparts) counts[(int64_t)threadIdx.x * ntiles + blockIdx.x] = Pair64{hist[threadIdx.x], 0};
+}
+
+// after the scan counts[p * ntiles + t] = first destination of tile t inside the partition-major output order
+__global__ void __launch_bounds__(PART_THREADS) part_rank_kernel(const uint8_t* part_of_row, int64_t n, int nparts, const Pair64* offsets,
+                                                                 int64_t ntiles, int32_t* dest) {
+    __shared__ int warp_cnt[PART_THREADS / 32][MAX_PARTS];
+    __shared__ int run[MAX_PARTS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < nparts) run[threadIdx.x] = 0;
+    int64_t base = (int64_t)blockIdx.x * PART_TILE;
+    for (int j = 0; j < PART_ITEMS; j++) {
+        int64_t row = base + (int64_t)j * PART_THREADS + threadIdx.x;
+        int p = row < n ? (int)part_of_row[row] : -1;
+        for (int q = lane; q < nparts; q += 32) warp_cnt[warp][q] = 0;
+        __syncwarp();
+        unsigned peers = __match_any_sync(0xffffffffu, p);
+        int rank_in_warp = __popc(peers & ((1u << lane) - 1));
+        if (p >= 0 && rank_in_warp == 0) warp_cnt[warp][p] = __popc(peers);
+        __syncthreads();
+        if (p >= 0) {
+            int before = run[p];
+            for (int w = 0; w < warp; w++) before += warp_cnt[w][p];
+            dest[row] = (int32_t)(offsets[(int64_t)p * ntiles + blockIdx.x].a + before + rank_in_warp);
+        }
+        __syncthreads();
+        if (threadIdx.x < nparts) {
+            int add = 0;
+            for (int w = 0; w < PART_THREADS / 32; w++) add += warp_cnt[w][threadIdx.x];
+            run[threadIdx.x] += add;
+        }
+        __syncthreads();
+    }
+}
+
+// out[dest[i]] = in[i] for one fixed width column; peer_base != null: the destination row d of partition p lives at
+// peer_base[p] + (d - part_start[p] + peer_row_offset[p]) * width (direct P2P store into the receiver's buffer)
+struct ScatterPeers {
+    void* base[MAX_PARTS];
+    uint8_t* nulls[MAX_PARTS];
+    int64_t part_start[MAX_PARTS];
+    int64_t peer_row_offset[MAX_PARTS];
+};
+template <typename T>
+__global__ void part_scatter_kernel(const T* __restrict__ in, const uint8_t* __restrict__ in_nulls, const int32_t* __restrict__ dest, int64_t n,
+                                    T* out, uint8_t* out_nulls) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        int32_t d = dest[i];
+        out[d] = in[i];
+        if (out_nulls) out_nulls[d] = in_nulls ? in_nulls[i] : 0;
+    }
+}
+template <typename T>
+__global__ void part_scatter_peer_kernel(const T* __restrict__ in, const uint8_t* __restrict__ in_nulls, const int32_t* __restrict__ dest,
+                                         const uint8_t* __restrict__ part_of_row, int64_t n, ScatterPeers peers) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        int p = part_of_row[i];
+        int64_t d = (int64_t)dest[i] - peers.part_start[p] + peers.peer_row_offset[p];
+        ((T*)peers.base[p])[d] = in[i];
+        if (peers.nulls[p]) peers.nulls[p][d] = in_nulls ? in_nulls[i] : 0;
+    }
+}
+
+}  // namespace pg
+
+using namespace pg;
+
+struct pg_partitioner {
+    pg_ctx* ctx = nullptr;
+    int32_t nparts = 0, mode = 0;
+    int64_t n = 0;
+    DevBuf part_of_row, dest, counts;
+    int64_t part_counts[MAX_PARTS];
+    int64_t part_start[MAX_PARTS];
+};
+
+extern "C" {
+
+/* Computes the partition of every row and its destination position in partition-major order.
+ * out_counts[nparts] (host) = rows per partition.  The handle keeps dest[] / part_of_row[] on the device for the scatters. */
+int32_t pg_partition_create(pg_ctx* ctx, const pg_col* keys, int32_t nkeys, const pg_col* hash_col, int64_t n, int32_t nparts, int32_t mode,
+                            int64_t* out_counts, pg_partitioner** out) {
+    if (!ctx) return PG_E_INVALID_ARGUMENT;
+    return guard(ctx, [&] {
+        PG_CHECK_ARG(out && out_counts && (keys || hash_col) && n >= 0, "bad arguments");
+        PG_CHECK_ARG(nparts >= 1 && nparts <= MAX_PARTS, "between 1 and %d partitions are supported", MAX_PARTS);
+        PG_CHECK_ARG(mode == 0 || (nparts & (nparts - 1)) == 0, "the local partition function needs a power-of-two partition count");
+        PG_CHECK_ARG(n <= 0x7fffffffLL, "page too large");
+        PG_CHECK_ARG(nkeys >= 0 && nkeys <= MAX_KEYS, "too many key channels");
+        pg_partitioner* pt = new pg_partitioner();
+        try {
+            pt->ctx = ctx; pt->nparts = nparts; pt->mode = mode; pt->n = n;
+            for (int p = 0; p < nparts; p++) { pt->part_counts[p] = 0; pt->part_start[p] = 0; }
+            if (n > 0) {
+                KeyCols kc; memset(&kc, 0, sizeof(kc));
+                std::vector<ColImport> imp(nkeys);
+                ColImport himp;
+                DCol hc; memset(&hc, 0, sizeof(hc));
+                int has_hash = 0;
+                if (hash_col) { import_col(ctx, *hash_col, n, himp); hc = himp.d; has_hash = 1; }
+                else for (int k = 0; k < nkeys; k++) { import_col(ctx, keys[k], n, imp[k]); kc.c[k] = imp[k].d; }
+                int64_t ntiles = (n + PART_TILE - 1) / PART_TILE;
+                pt->part_of_row.alloc(ctx, n);
+                pt->dest.alloc(ctx, n * 4);
+                pt->counts.alloc(ctx, ((int64_t)nparts * ntiles + 1) * (int64_t)sizeof(Pair64));
+                Pair64* counts = pt->counts.as<Pair64>();
+                PG_LAUNCH(ctx, part_hist_kernel, (int)ntiles, PART_THREADS, 0, kc, nkeys, hc, has_hash, n, nparts, mode,
+                          pt->part_of_row.as<uint8_t>(), counts, ntiles);
+                scan_tile_totals(ctx, counts, (int64_t)nparts * ntiles, counts + (int64_t)nparts * ntiles);
+                PG_LAUNCH(ctx, part_rank_kernel, (int)ntiles, PART_THREADS, 0, pt->part_of_row.as<uint8_t>(), n, nparts, counts, ntiles,
+                          pt->dest.as<int32_t>());
+                // partition starts = scanned count of each partition's first tile
+                std::vector<int64_t> starts(nparts);
+                for (int p = 0; p < nparts; p++) copy_async(ctx, &ctx->h_scalar[p], &counts[(int64_t)p * ntiles].a, 8, cudaMemcpyDeviceToHost);
+                sync(ctx);
+                for (int p = 0; p < nparts; p++) pt->part_start[p] = ctx->h_scalar[p];
+                for (int p = 0; p < nparts; p++) pt->part_counts[p] = (p + 1 < nparts ? pt->part_start[p + 1] : n) - pt->part_start[p];
+            }
+            for (int p = 0; p < nparts; p++) out_counts[p] = pt->part_counts[p];
+        } catch (...) { delete pt; throw; }
+        *out = pt;
+    });
+}
+
+int32_t pg_partition_destroy(pg_partitioner* pt) {
+    if (!pt) return PG_OK;
+    return guard(pt->ctx, [&] { delete pt; });
+}
+
+/* out[dest[i]] = in[i]: the column in partition-major order (fixed width types; device output) */
+int32_t pg_partition_scatter(pg_partitioner* pt, const pg_col* in, pg_col_out* out) {
+    if (!pt) return PG_E_INVALID_ARGUMENT;
+    return guard(pt->ctx, [&] {
+        pg_ctx* ctx = pt->ctx;
+        PG_CHECK_ARG(in && out && in->n == pt->n && out->type == in->type, "bad arguments");
+        PG_CHECK_ARG(!type_is_var(in->type), "variable width columns cannot be scattered");
+        PG_CHECK_ARG(out->mem == PG_MEM_DEVICE && out->capacity >= pt->n, "output must be a device column with capacity");
+        if (pt->n == 0) return;
+        ColImport ci;
+        import_col(ctx, *in, pt->n, ci);
+        int w = type_width(in->type);
+        int grid = grid_for(ctx, pt->n, 256, 2);
+        const int32_t* dest = pt->dest.as<int32_t>();
+        uint8_t* on = out->nulls;
+        switch (w) {
+            case 1: PG_LAUNCH(ctx, part_scatter_kernel<uint8_t>, grid, 256, 0, (const uint8_t*)ci.d.values, ci.d.nulls, dest, pt->n, (uint8_t*)out->values, on); break;
+            case 4: PG_LAUNCH(ctx, part_scatter_kernel<int32_t>, grid, 256, 0, (const int32_t*)ci.d.values, ci.d.nulls, dest, pt->n, (int32_t*)out->values, on); break;
+            case 8: PG_LAUNCH(ctx, part_scatter_kernel<int64_t>, grid, 256, 0, (const int64_t*)ci.d.values, ci.d.nulls, dest, pt->n, (int64_t*)out->values, on); break;
+            default: PG_LAUNCH(ctx, part_scatter_kernel<int4>, grid, 256, 0, (const int4*)ci.d.values, ci.d.nulls, dest, pt->n, (int4*)out->values, on);
+        }
+        sync(ctx);
+    });
+}
+
+/* Fused exchange: scatter the column straight into the receivers' buffers over NVLink peer mappings.
+ * peer_values[p] / peer_nulls[p]: device pointers valid on THIS device that alias rank p's receive column (P2P / symmetric
+ * memory); peer_row_offset[p]: first row this rank may write in rank p's buffer (= rows sent to p by lower ranks). */
+int32_t pg_partition_scatter_peers(pg_partitioner* pt, const pg_col* in, void* const* peer_values, uint8_t* const* peer_nulls,
+                                   const int64_t* peer_row_offset) {
+    if (!pt) return PG_E_INVALID_ARGUMENT;
+    return guard(pt->ctx, [&] {
+        pg_ctx* ctx = pt->ctx;
+        PG_CHECK_ARG(in && peer_values && peer_row_offset && in->n == pt->n, "bad arguments");
+        PG_CHECK_ARG(!type_is_var(in->type), "variable width columns cannot be scattered");
+        if (pt->n == 0) return;
+        ColImport ci;
+        import_col(ctx, *in, pt->n, ci);
+        ScatterPeers sp;
+        memset(&sp, 0, sizeof(sp));
+        for (int p = 0; p < pt->nparts; p++) {
+            sp.base[p] = peer_values[p]; sp.nulls[p] = peer_nulls ? peer_nulls[p] : nullptr;
+            sp.part_start[p] = pt->part_start[p]; sp.peer_row_offset[p] = peer_row_offset[p];
+        }
+        int w = type_width(in->type);
+        int grid = grid_for(ctx, pt->n, 256, 2);
+        const int32_t* dest = pt->dest.as<int32_t>();
+        const uint8_t* por = pt->part_of_row.as<uint8_t>();
+        switch (w) {
+            case 1: PG_LAUNCH(ctx, part_scatter_peer_kernel<uint8_t>, grid, 256, 0, (const uint8_t*)ci.d.values, ci.d.nulls, dest, por, pt->n, sp); break;
+            case 4: PG_LAUNCH(ctx, part_scatter_peer_kernel<int32_t>, grid, 256, 0, (const int32_t*)ci.d.values, ci.d.nulls, dest, por, pt->n, sp); break;
+            case 8: PG_LAUNCH(ctx, part_scatter_peer_kernel<int64_t>, grid, 256, 0, (const int64_t*)ci.d.values, ci.d.nulls, dest, por, pt->n, sp); break;
+            default: PG_LAUNCH(ctx, part_scatter_peer_kernel<int4>, grid, 256, 0, (const int4*)ci.d.values, ci.d.nulls, dest, por, pt->n, sp);
+        }
+        sync(ctx);
+    });
+}
+
+/* partition id of every row (uint8) — parity checks against LocalPartitionGenerator / HashGenerator.getPartition */
+int32_t pg_partition_ids(pg_partitioner* pt, uint8_t* out, int32_t out_mem) {
+    if (!pt || !out) return PG_E_INVALID_ARGUMENT;
+    return guard(pt->ctx, [&] {
+        if (pt->n == 0) return;
+        copy_async(pt->ctx, out, pt->part_of_row.p, pt->n, out_mem == PG_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost);
+        sync(pt->ctx);
+    });
+}
+
+}  // extern "C"

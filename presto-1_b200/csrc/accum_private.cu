@@ -45,7 +45,7 @@ struct PrivPlan {
 
 // ---- fused group-id look-up: short keys are packed into two 64-bit words (a key never straddles the words) and searched
 // in a shared-memory table built from the groups the GroupByHash already numbered.  Bits 56.. of word 1 are null flags.
-static const int MAX_PACK_KEYS = 4;
+static const int MAX_PACK_KEYS = 8;
 struct PackKey {
     const void* values;
     const uint8_t* nulls;
@@ -74,48 +74,31 @@ PG_D unsigned long long norm_double_key(long long b) {
     if ((b & 0x7fffffffffffffffLL) == 0) return 0;
     return (unsigned long long)canon_double_bits(b);
 }
-// Key packing of an input row in two phases so that every first-level load of a row (key values / offsets, null flags,
-// mask, aggregate arguments) is issued before anything waits: phase 1 only loads, phase 2 does the dependent byte loads.
-struct KeyRegs {
-    unsigned long long v[MAX_PACK_KEYS];
-    int32_t o0[MAX_PACK_KEYS], o1[MAX_PACK_KEYS];
-    uint8_t isnull[MAX_PACK_KEYS];
-};
-PG_D void pack_load(const PackSpec& ps, int64_t row, KeyRegs& kr) {
-#pragma unroll
-    for (int k = 0; k < MAX_PACK_KEYS; k++) {
-        if (k < ps.nkeys) {
-            const PackKey& pk = ps.k[k];
-            kr.isnull[k] = pk.nulls != nullptr ? pk.nulls[row] : 0;
-            if (pk.type == PG_VARCHAR || pk.type == PG_VARBINARY) { kr.o0[k] = pk.offsets[row]; kr.o1[k] = pk.offsets[row + 1]; }
-            else if (pk.type == PG_INTEGER || pk.type == PG_DATE) kr.v[k] = (unsigned long long)(uint32_t)((const int32_t*)pk.values)[row];
-            else if (pk.type == PG_BOOLEAN) kr.v[k] = ((const uint8_t*)pk.values)[row];
-            else kr.v[k] = ((const unsigned long long*)pk.values)[row];
-        }
-    }
-}
-// false when a value does not fit the packed form (string longer than 3 bytes)
-PG_D bool pack_finish(const PackSpec& ps, const KeyRegs& kr, unsigned long long& w0, unsigned long long& w1) {
+// pack the key of input row `row`; false when a value does not fit the packed form (string longer than 3 bytes)
+PG_D bool pack_row(const PackSpec& ps, int64_t row, unsigned long long& w0, unsigned long long& w1) {
     w0 = 0; w1 = 0;
     bool ok = true;
-#pragma unroll
-    for (int k = 0; k < MAX_PACK_KEYS; k++) {
-        if (k < ps.nkeys) {
+#pragma unroll 1
+    for (int k = 0; k < ps.nkeys; k++) {
+        {
             const PackKey& pk = ps.k[k];
             unsigned long long v = 0;
+            bool isnull = pk.nulls != nullptr && pk.nulls[row] != 0;
             if (pk.type == PG_VARCHAR || pk.type == PG_VARBINARY) {
-                int32_t len = kr.o1[k] - kr.o0[k];
+                int32_t o = pk.offsets[row], len = pk.offsets[row + 1] - o;
                 if (len > 3) ok = false;
                 else {
-                    const uint8_t* b = (const uint8_t*)pk.values + kr.o0[k];
+                    const uint8_t* b = (const uint8_t*)pk.values + o;
                     v = (unsigned long long)len;
                     if (len > 0) v |= (unsigned long long)b[0] << 8;
                     if (len > 1) v |= (unsigned long long)b[1] << 16;
                     if (len > 2) v |= (unsigned long long)b[2] << 24;
                 }
-            } else if (pk.type == PG_DOUBLE) v = norm_double_key((long long)kr.v[k]);
-            else v = kr.v[k];
-            if (kr.isnull[k]) w1 |= 1ULL << (56 + k);
+            } else if (pk.type == PG_INTEGER || pk.type == PG_DATE) v = (unsigned long long)(uint32_t)((const int32_t*)pk.values)[row];
+            else if (pk.type == PG_BOOLEAN) v = ((const uint8_t*)pk.values)[row];
+            else if (pk.type == PG_DOUBLE) v = norm_double_key(((const long long*)pk.values)[row]);
+            else v = ((const unsigned long long*)pk.values)[row];
+            if (isnull) w1 |= 1ULL << (56 + k);
             else if (pk.word == 0) w0 |= v << pk.shift;
             else w1 |= v << pk.shift;
         }
@@ -182,7 +165,7 @@ struct RowData {
 // FUSED = true: the group id of a row is resolved inside this kernel from the packed key (no id column in HBM); rows that
 // cannot be resolved are flagged in miss_flag and counted in *d_miss — the caller runs the general path for exactly those.
 template <int T, bool FUSED>
-__global__ void __launch_bounds__(T, 512 / T) acc_private2_kernel(const PrivPlan plan, const int32_t* __restrict__ gids, int64_t n, int G,
+__global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, const int32_t* __restrict__ gids, int64_t n, int G,
                                                          const uint8_t* __restrict__ only_rows, const PackSpec pk) {
     extern __shared__ unsigned long long table[];
     __shared__ unsigned long long lut_w0[FUSED ? LUT_SIZE : 1], lut_w1[FUSED ? LUT_SIZE : 1];
@@ -213,56 +196,11 @@ __global__ void __launch_bounds__(T, 512 / T) acc_private2_kernel(const PrivPlan
     unsigned long long misses = 0;
 
     auto load_row = [&](int64_t row, RowData& r) {
-        // ---- phase 1: issue every independent load of this row
-        KeyRegs kr;
-        int gid_in = 0;
-        uint8_t only = 1;
-        if (FUSED) pack_load(pk, row, kr);
-        else { gid_in = gids[row]; if (only_rows != nullptr) only = only_rows[row]; }
-        uint8_t m0[MAX_PCONDS], m1[MAX_PCONDS], m2[MAX_PCONDS];
-#pragma unroll
-        for (int c = 0; c < MAX_PCONDS; c++) {
-            m0[c] = 1; m1[c] = 0; m2[c] = 0;
-            if (c < plan.nconds) {
-                const FCond& pc = plan.conds[c];
-                if (pc.mask != nullptr) m0[c] = pc.mask[row];
-                if (pc.mask_nulls != nullptr) m1[c] = pc.mask_nulls[row];
-                if (pc.arg_nulls != nullptr) m2[c] = pc.arg_nulls[row];
-            }
-        }
-        if (plan.n[PS_DEC]) {
-#pragma unroll
-            for (int s = 0; s < MAX_DEC; s++) if (plan.dec[s].cmask) r.dec[s] = ((const ulonglong2*)plan.dec[s].ptr)[row];
-        }
-        if (plan.n[PS_I64]) {
-#pragma unroll
-            for (int s = 0; s < MAX_I64; s++) if (plan.i64[s].cmask) r.i64[s] = ((const unsigned long long*)plan.i64[s].ptr)[row];
-        }
-        if (plan.n[PS_I32]) {
-#pragma unroll
-            for (int s = 0; s < MAX_I32; s++) if (plan.i32[s].cmask) r.i32[s] = ((const int*)plan.i32[s].ptr)[row];
-        }
-        if (plan.n[PS_F64]) {
-#pragma unroll
-            for (int s = 0; s < MAX_F64; s++) if (plan.f64[s].cmask) r.f64[s] = ((const unsigned long long*)plan.f64[s].ptr)[row];
-        }
-        if (plan.n[PS_MIN]) {
-#pragma unroll
-            for (int s = 0; s < MAX_MIN; s++) if (plan.mn[s].cmask) r.mn[s] = ((const unsigned long long*)plan.mn[s].ptr)[row];
-        }
-        if (plan.n[PS_MAX]) {
-#pragma unroll
-            for (int s = 0; s < MAX_MAX; s++) if (plan.mx[s].cmask) r.mx[s] = ((const unsigned long long*)plan.mx[s].ptr)[row];
-        }
-        // ---- phase 2: resolve the group and the contribution conditions
         r.condbits = 0;
-#pragma unroll
-        for (int c = 0; c < MAX_PCONDS; c++)
-            if (c < plan.nconds) r.condbits |= ((m0[c] != 0 && m1[c] == 0 && m2[c] == 0) ? 1u : 0u) << c;
         if (FUSED) {
             unsigned long long w0, w1;
             r.g = -1;
-            if (pack_finish(pk, kr, w0, w1)) {
+            if (pack_row(pk, row, w0, w1)) {
                 unsigned h = lut_hash(w0, w1);
                 while (true) {
                     int g = lut_gid[h];
@@ -271,9 +209,46 @@ __global__ void __launch_bounds__(T, 512 / T) acc_private2_kernel(const PrivPlan
                     h = (h + 1) & (LUT_SIZE - 1);
                 }
             }
-            if (r.g < 0) { misses++; pk.miss_flag[row] = 1; }
+            if (r.g < 0) { misses++; pk.miss_flag[row] = 1; return; }
         } else {
-            r.g = only ? gid_in : -1;
+            r.g = gids[row];
+            if (only_rows != nullptr && only_rows[row] == 0) { r.g = -1; return; }
+        }
+#pragma unroll
+        for (int c = 0; c < MAX_PCONDS; c++) {
+            if (c < plan.nconds) {
+                const FCond& pc = plan.conds[c];
+                bool ok = true;
+                if (pc.mask != nullptr) ok = pc.mask[row] != 0;
+                if (pc.mask_nulls != nullptr) ok = ok && pc.mask_nulls[row] == 0;
+                if (pc.arg_nulls != nullptr) ok = ok && pc.arg_nulls[row] == 0;
+                r.condbits |= (ok ? 1u : 0u) << c;
+            }
+        }
+        const unsigned cb = r.condbits;
+        if (plan.n[PS_DEC]) {
+#pragma unroll
+            for (int s = 0; s < MAX_DEC; s++) if (cb & plan.dec[s].cmask) r.dec[s] = ((const ulonglong2*)plan.dec[s].ptr)[row];
+        }
+        if (plan.n[PS_I64]) {
+#pragma unroll
+            for (int s = 0; s < MAX_I64; s++) if (cb & plan.i64[s].cmask) r.i64[s] = ((const unsigned long long*)plan.i64[s].ptr)[row];
+        }
+        if (plan.n[PS_I32]) {
+#pragma unroll
+            for (int s = 0; s < MAX_I32; s++) if (cb & plan.i32[s].cmask) r.i32[s] = ((const int*)plan.i32[s].ptr)[row];
+        }
+        if (plan.n[PS_F64]) {
+#pragma unroll
+            for (int s = 0; s < MAX_F64; s++) if (cb & plan.f64[s].cmask) r.f64[s] = ((const unsigned long long*)plan.f64[s].ptr)[row];
+        }
+        if (plan.n[PS_MIN]) {
+#pragma unroll
+            for (int s = 0; s < MAX_MIN; s++) if (cb & plan.mn[s].cmask) r.mn[s] = ((const unsigned long long*)plan.mn[s].ptr)[row];
+        }
+        if (plan.n[PS_MAX]) {
+#pragma unroll
+            for (int s = 0; s < MAX_MAX; s++) if (cb & plan.mx[s].cmask) r.mx[s] = ((const unsigned long long*)plan.mx[s].ptr)[row];
         }
     };
 

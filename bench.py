@@ -214,81 +214,114 @@ def final_aggs_for(P, aggs, first_channel):
     return fin
 
 
-def extra_workloads(args, P, tpch, ctx, torch, peak):
-    """cfg3 (high-cardinality GROUP BY orderkey) and cfg4 (lineitem JOIN orders) on one GPU, device-resident inputs."""
-    import numpy as np
+def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0):
+    """cfg3 (high-cardinality GROUP BY orderkey) and cfg4 (lineitem JOIN orders), device-resident inputs.
+    world > 1: every rank holds its own SF shard (weak scaling); rows are hash-partitioned on orderkey and exchanged with an
+    NCCL all-to-all (presto-1_b200/exchange.py) before the per-GPU operator, the reference's partitioned plan."""
     from presto_b200.blocks import Block
     N = P.native
     res = {}
     sf = args.extra_sf
-    li = tpch.lineitem(sf, seed=42, device="cuda", need=("keys", "double"))
-    n = li["rows"]
     n_orders = int(1_500_000 * sf)
+    # disjoint order-key ranges per rank: shard r owns orders [r*n_orders, (r+1)*n_orders)
+    li = tpch.lineitem(sf, seed=42 + rank, device="cuda", need=("keys", "double"))
+    n = li["rows"]
+    key_off = rank * tpch.order_key(torch.tensor(n_orders, dtype=torch.int64)).item()
+    li["orderkey"] += key_off
     page = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, li["quantity"], None, None, n),
                   Block(N.DOUBLE, li["extendedprice_double"].view(torch.int64), None, None, n), position_count=n)
     aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2)]
+    ex = P.HashPartitionExchange(P.DevicePartitioner(ctx)) if world > 1 else None
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
             fn()
-        torch.cuda.synchronize()
+        barrier()
         ctx.kernel_report(reset=True)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
             out = fn()
         e1.record()
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / steps, out
+        barrier()
+        ms = e0.elapsed_time(e1) / steps
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, out
+
+    def total(x):
+        if dist is None:
+            return int(x)
+        t = torch.tensor([int(x)], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t)
+        return int(t.item())
 
     ctx.set_timing(True)
 
     def gb_pass():
+        local = ex.exchange(page, [0]) if ex else page
         op = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=n_orders, ctx=ctx, device_output=True)
-        op.add_input(page)
+        op.add_input(local)
         op.finish()
         g = op.get_group_count()
-        out = op.get_output(max_rows=g)     # all groups materialised on the device
+        out = op.get_output(max_rows=max(g, 1))     # all groups materialised on the device
         op.close()
         return g
 
     ms, groups = timed(gb_pass, 3, 1)
     kern = ctx.kernel_report(reset=True)
-    brow = 136
-    res["groupby_orderkey"] = {"workload": "GROUP BY orderkey over lineitem SF%g: count(*), sum(quantity decimal), sum(extendedprice double)" % sf,
-                               "rows": n, "groups": int(groups), "ms_per_step": round(ms, 3), "rows_per_s": n / (ms / 1e3),
-                               "algorithmic_bytes_per_row": brow, "hbm_frac": round(n * brow / (ms / 1e3) / 1e9 / peak, 4),
+    n_all, g_all = total(n), total(groups)
+    brow = 136 + (48 if world > 1 else 0)   # + 2 x 24 B partition pass (read + write of key and inputs) when G > 1
+    res["groupby_orderkey"] = {"workload": "GROUP BY orderkey over lineitem SF%g per GPU: count(*), sum(quantity decimal), sum(extendedprice double)%s"
+                                           % (sf, "; hash-partitioned all-to-all then SINGLE per GPU" if world > 1 else ""),
+                               "rows": n_all, "groups": g_all, "ms_per_step": round(ms, 3), "rows_per_s": n_all / (ms / 1e3),
+                               "algorithmic_bytes_per_row": brow, "hbm_frac_per_gpu": round(n_all / world * brow / (ms / 1e3) / 1e9 / peak, 4),
                                "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:8]}}
     del page
     # ---- join: build orders (orderkey unique, totalprice), probe lineitem.orderkey, gather totalprice
-    od = tpch.orders(sf, seed=42, device="cuda")
-    bpage = [Block(N.BIGINT, od["orderkey"], None, None, n_orders), Block(N.DOUBLE, od["totalprice"].view(torch.int64), None, None, n_orders)]
+    od = tpch.orders(sf, seed=42 + rank, device="cuda")
+    od["orderkey"] += key_off
+    bpage = P.Page(Block(N.BIGINT, od["orderkey"], None, None, n_orders), Block(N.DOUBLE, od["totalprice"].view(torch.int64), None, None, n_orders),
+                   position_count=n_orders)
 
     def build():
+        local = ex.exchange(bpage, [0]) if ex else bpage
         idx = P.PagesIndex([P.BIGINT, P.DOUBLE], [0], ctx=ctx)
-        idx.add_page(bpage)
+        idx.add_page(local)
         return idx.create_lookup_source()
 
     bms, ls = timed(build, 2, 1)
     bkern = ctx.kernel_report(reset=True)
-    pk = [Block(N.BIGINT, li["orderkey"], None, None, n)]
+    ppage = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, li["quantity"], None, None, n), position_count=n)
 
     def probe():
-        pp, bp = ls.join_page(pk, None, P.JOIN_INNER, device=True, capacity=n)
+        local = ex.exchange(ppage, [0]) if ex else ppage
+        m = local.position_count
+        pp, bp = ls.join_page([local.blocks[0]], None, P.JOIN_INNER, device=True, capacity=max(m, 1))
         out = ls.append_to(bp, [1], device=True)
         return len(pp)
 
     pms, matches = timed(probe, 3, 1)
     pkern = ctx.kernel_report(reset=True)
     ctx.set_timing(False)
-    res["join_build"] = {"workload": "hash build orders SF%g (orderkey, totalprice)" % sf, "rows": n_orders, "ms_per_step": round(bms, 3),
-                         "rows_per_s": n_orders / (bms / 1e3), "algorithmic_bytes_per_row": 32,
-                         "hbm_frac": round(n_orders * 32 / (bms / 1e3) / 1e9 / peak, 4),
+    o_all, m_all = total(n_orders), total(matches)
+    res["join_build"] = {"workload": "hash build orders SF%g per GPU (orderkey, totalprice)" % sf, "rows": o_all, "ms_per_step": round(bms, 3),
+                         "rows_per_s": o_all / (bms / 1e3), "algorithmic_bytes_per_row": 32,
+                         "hbm_frac_per_gpu": round(o_all / world * 32 / (bms / 1e3) / 1e9 / peak, 4),
                          "kernels_ms_per_step": {k: round(v[0] / 2, 3) for k, v in sorted(bkern.items(), key=lambda kv: -kv[1][0])[:6]}}
-    res["join_probe"] = {"workload": "INNER join probe lineitem.orderkey -> orders SF%g, emit (probe idx, build pos) + gather totalprice" % sf,
-                         "rows": n, "matches": int(matches), "ms_per_step": round(pms, 3), "rows_per_s": n / (pms / 1e3),
-                         "algorithmic_bytes_per_row": 44, "hbm_frac": round(n * 44 / (pms / 1e3) / 1e9 / peak, 4),
+    res["join_probe"] = {"workload": "INNER join probe lineitem.orderkey -> orders SF%g per GPU, emit (probe idx, build pos) + gather totalprice" % sf,
+                         "rows": n_all, "matches": m_all, "ms_per_step": round(pms, 3), "rows_per_s": n_all / (pms / 1e3),
+                         "algorithmic_bytes_per_row": 44, "hbm_frac_per_gpu": round(n_all / world * 44 / (pms / 1e3) / 1e9 / peak, 4),
                          "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(pkern.items(), key=lambda kv: -kv[1][0])[:6]}}
+    if ex:
+        res["exchange"] = {"rows_sent_per_rank": ex.sent_rows, "bytes_sent_per_rank": ex.bytes_sent, "collective": "NCCL all_to_all_single per column"}
     return res
 
 
@@ -410,10 +443,10 @@ def gpu_arm(args):
                          "%d-row TPC-H-shaped lineitem sample of the same Q1 plan, best of 3" % n_s}
 
     extra = None
-    if args.extra and world == 1:
+    if args.extra:
         del page, cols
         torch.cuda.empty_cache()
-        extra = extra_workloads(args, P, tpch, ctx, torch, peak)
+        extra = extra_workloads(args, P, tpch, ctx, torch, peak, dist, world, rank)
 
     if rank == 0:
         line = {

@@ -196,3 +196,29 @@ def hash_rows(blocks):
     out = np.zeros(blocks[0].n, dtype=np.int64)
     lib().orc_hash_rows(col_array(blocks), len(blocks), blocks[0].n, out.ctypes.data)
     return out
+
+
+def partition_ids(blocks, nparts, mode=0, hash_block=None):
+    """HashGenerator.getPartition (mode 0) / LocalPartitionGenerator.getPartition (mode 1) for every row."""
+    raw = hash_block.to_host().values if hash_block is not None else hash_rows(blocks)
+    raw = np.ascontiguousarray(raw, dtype=np.int64)
+    out = np.zeros(len(raw), dtype=np.int32)
+    lib().orc_partition(raw.ctypes.data, len(raw), nparts, mode, out.ctypes.data)
+    return out
+
+
+class OraclePartitioner:
+    """CPU stand-in for DevicePartitioner used ONLY by the gloo world_size-2 tests of the exchange's host logic."""
+
+    def partition(self, page, key_channels, nparts, hash_channel=None, mode=0):
+        blocks = _host(page.blocks)
+        keys = [blocks[c] for c in key_channels]
+        ids = partition_ids(keys, nparts, mode, blocks[hash_channel] if hash_channel is not None else None)
+        order = np.argsort(ids, kind="stable")
+        counts = [int((ids == p).sum()) for p in range(nparts)]
+        out = []
+        for b in blocks:
+            k = 2 if b.type == N.LONG_DECIMAL else 1
+            v = b.values.reshape(-1, k)[order].reshape(-1) if k == 2 else b.values[order]
+            out.append(Block(b.type, np.ascontiguousarray(v), None if b.nulls is None else np.ascontiguousarray(b.nulls[order]), None, b.n))
+        return P.Page(*out, position_count=page.position_count), counts

@@ -14,3 +14,4 @@ from .join import LookupSource, PagesIndex
 from .operators import (FINAL, INTERMEDIATE, PARTIAL, SINGLE, AggregatorFactory, HashAggregationOperator, HashBuilderOperator,
                         LookupJoinOperator, take_positions)
 JOIN_INNER, JOIN_PROBE_OUTER = native.JOIN_INNER, native.JOIN_PROBE_OUTER
+from .exchange import DevicePartitioner, HashPartitionExchange

@@ -203,7 +203,8 @@ def partition_ids(blocks, nparts, mode=0, hash_block=None):
     raw = hash_block.to_host().values if hash_block is not None else hash_rows(blocks)
     raw = np.ascontiguousarray(raw, dtype=np.int64)
     out = np.zeros(len(raw), dtype=np.int32)
-    lib().orc_partition(raw.ctypes.data, len(raw), nparts, mode, out.ctypes.data)
+    # oracle.cpp numbers the functions the other way round (0 = LocalPartitionGenerator, 1 = HashGenerator.getPartition)
+    lib().orc_partition(raw.ctypes.data, len(raw), nparts, 1 - mode, out.ctypes.data)
     return out
 
 

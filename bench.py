@@ -27,7 +27,7 @@ ROWS_PER_SF = 5_998_605.2
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--sf", type=float, default=10.0, help="TPC-H scale factor of the lineitem shard per GPU")
@@ -325,6 +325,35 @@ def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0)
     return res
 
 
+def q1_selfcheck(torch, cols, out, dist):
+    """Size-independent check of the timed run's own result at full size: per-group count(*), sum(quantity),
+    sum(extendedprice) and sum(disc_price) recomputed with torch int64 scatter-adds (independent of both the library and
+    the oracle) and compared bit-exact with the operator's output; counts must also add up to the rows passing the mask."""
+    m = cols["q1_mask"].bool()
+    code = (cols["returnflag"].to(torch.int64) * 256 + cols["linestatus"].to(torch.int64))[m]
+    exp = torch.zeros(4, 65536, dtype=torch.int64, device=code.device)
+    exp[0].index_add_(0, code, torch.ones_like(code))
+    exp[1].index_add_(0, code, cols["quantity"][m])
+    exp[2].index_add_(0, code, cols["extendedprice"][m])
+    exp[3].index_add_(0, code, cols["disc_price"][0::2][m])
+    passing = torch.tensor([int(m.sum().item())], dtype=torch.int64, device=code.device)
+    if dist is not None:
+        dist.all_reduce(exp)
+        dist.all_reduce(passing)
+    exp = exp.cpu().numpy()
+    hb = [b.to_host() for b in out.blocks]
+    ok, count_sum = True, 0
+    for i in range(out.position_count):
+        c = hb[0].get(i)[0] * 256 + hb[1].get(i)[0]
+        got = (hb[9].get(i), hb[2].get(i), hb[3].get(i), hb[4].get(i))
+        ok = ok and got == tuple(int(exp[k][c]) for k in range(4))
+        count_sum += got[0]
+    live = int((exp[0] > 0).sum())
+    return {"groups": int(out.position_count), "groups_expected": live, "count_sum": int(count_sum), "rows_passing_mask": int(passing.item()),
+            "sums_bit_exact_vs_torch_int64": bool(ok and live == out.position_count and count_sum == int(passing.item()))}
+
+
+
 def gpu_arm(args):
     import numpy as np
     import torch
@@ -416,6 +445,10 @@ def gpu_arm(args):
             except Exception:
                 pass
 
+    selfcheck = q1_selfcheck(torch, cols, out, dist)
+    if not selfcheck["sums_bit_exact_vs_torch_int64"]:
+        raise SystemExit("bench self-check failed: %s" % json.dumps(selfcheck))
+
     # e2e: host (pinned) buffers through the same operator / C ABI call; H2D copies inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -459,6 +492,7 @@ def gpu_arm(args):
                        "rows_per_gpu": rows, "groups": int(out.position_count), "step": "SINGLE" if world == 1 else "PARTIAL->all_gather->FINAL",
                        "l2_policy": "inputs (%.2f GB per pass) exceed the 126 MB L2; no flush needed" % (input_bytes / 1e9)},
             "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
+            "selfcheck": selfcheck,
         }
         if cpu:
             line["cpu_baseline"] = cpu

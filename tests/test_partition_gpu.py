@@ -39,3 +39,40 @@ def test_partition_ids_and_stable_scatter(pgpu, ctx, nparts, mode, with_hash_cha
         assert np.array_equal(np.asarray(got.values).view(exp.dtype), exp)
         if src.nulls is not None:
             assert np.array_equal(got.nulls, src.nulls[order])
+
+
+def test_scatter_peers_with_self_pointers(pgpu, ctx):
+    """pg_partition_scatter_peers on one GPU: every 'peer' buffer is a local one, so the fused partition+store kernel can be
+    checked without a second device — rows of partition p land at peer_row_offset[p] + (rank inside the partition)."""
+    import torch
+    P = pgpu
+    N = P.native
+    rng = np.random.default_rng(5)
+    n, nparts = 30_011, 4
+    key = P.Block.long_array(rng.integers(0, 10**6, n).astype(np.int64))
+    nulls = (rng.random(n) < 0.1).astype(np.uint8)
+    payload = P.Block.long_array(rng.integers(-10**9, 10**9, n).astype(np.int64), nulls)
+    want_ids = O.partition_ids([key], nparts, 0)
+    counts = (C.c_int64 * nparts)()
+    h = C.c_void_p()
+    kc = P.blocks.col_array([key])
+    N.check(ctx.handle, N.lib().pg_partition_create(ctx.handle, kc, 1, None, n, nparts, 0, counts, C.byref(h)))
+    try:
+        offsets = [7, 0, 3, 11]                      # rows already present in each receiver's buffer
+        bufs = [torch.full((offsets[p] + counts[p],), -1, dtype=torch.int64, device="cuda") for p in range(nparts)]
+        nbufs = [torch.full((offsets[p] + counts[p],), 9, dtype=torch.uint8, device="cuda") for p in range(nparts)]
+        pv = (C.c_void_p * nparts)(*[b.data_ptr() for b in bufs])
+        pn = (C.c_void_p * nparts)(*[b.data_ptr() for b in nbufs])
+        po = (C.c_int64 * nparts)(*offsets)
+        col = payload.pg_col()
+        N.check(ctx.handle, N.lib().pg_partition_scatter_peers(h, C.byref(col), pv, pn, po))
+        torch.cuda.synchronize()
+        for p in range(nparts):
+            sel = want_ids == p
+            assert counts[p] == int(sel.sum())
+            got = bufs[p].cpu().numpy()
+            assert np.all(got[:offsets[p]] == -1)                       # earlier rows untouched
+            assert np.array_equal(got[offsets[p]:], payload.values[sel])   # stable order inside the partition
+            assert np.array_equal(nbufs[p].cpu().numpy()[offsets[p]:], nulls[sel])
+    finally:
+        N.lib().pg_partition_destroy(h)

@@ -76,10 +76,18 @@ struct FusedLookup {
     int32_t bigint_mode, null_gid;
     uint8_t* miss_flag;               // n bytes, zeroed by the caller
     unsigned long long* d_miss;       // device counter, zeroed by the caller
+    int64_t row_base;                 // page row of the first row handed in (variable width offsets are page-absolute)
+    int64_t key_value_bytes[8];       // value buffer size of variable width key columns
 };
+static const int MAX_PACK_KEYS = 8;
+static const int MAX_PACK_KEYS_PUBLIC = MAX_PACK_KEYS;
 bool fused_keys_packable(const KeyLayout& L);
+// word (0/1) and bit shift of every key inside the packed two-word form; false when the keys do not fit
+bool fused_pack_layout(const KeyLayout& L, int32_t* word, int32_t* shift);
 bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count, const uint8_t* only_rows,
                         const FusedLookup* fused);
+// the same pass through a kernel specialised at run time for this plan (jit_lowcard.cu); false when it cannot be used
+bool accumulate_lowcard_jit(pg_ctx* ctx, const AggProgram& prog, int64_t n, int64_t group_count, const FusedLookup& fused);
 
 }  // namespace pg
 

@@ -45,7 +45,6 @@ struct PrivPlan {
 
 // ---- fused group-id look-up: short keys are packed into two 64-bit words (a key never straddles the words) and searched
 // in a shared-memory table built from the groups the GroupByHash already numbered.  Bits 56.. of word 1 are null flags.
-static const int MAX_PACK_KEYS = 8;
 struct PackKey {
     const void* values;
     const uint8_t* nulls;
@@ -427,6 +426,7 @@ static bool pack_layout(const KeyLayout& L, int32_t* word, int32_t* shift) {
     return true;
 }
 bool fused_keys_packable(const KeyLayout& L) { return pack_layout(L, nullptr, nullptr); }
+bool fused_pack_layout(const KeyLayout& L, int32_t* word, int32_t* shift) { return pack_layout(L, word, shift); }
 
 bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count, const uint8_t* only_rows,
                         const FusedLookup* fused) {

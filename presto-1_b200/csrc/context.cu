@@ -95,6 +95,7 @@ int32_t pg_ctx_destroy(pg_ctx* ctx) {
     if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
     for (const pg_kernel_record& r : ctx->records) { cudaEventDestroy(r.start); cudaEventDestroy(r.stop); }
     for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
+    pg::jit_cache_free(ctx);
     delete ctx;
     return PG_OK;
 }

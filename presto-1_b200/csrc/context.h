@@ -10,6 +10,8 @@
 
 #include "common.cuh"
 
+namespace pg { struct JitCache; }
+
 struct pg_kernel_record {
     const char* name;
     cudaEvent_t start, stop;
@@ -27,10 +29,12 @@ struct pg_ctx {
     bool timing = false;
     std::vector<pg_kernel_record> records;
     std::vector<cudaEvent_t> event_pool;
+    pg::JitCache* jit = nullptr;   // run-time specialised kernels (jit.h), created on first use
 };
 
 namespace pg {
 cudaEvent_t timing_event(pg_ctx* ctx);
+void jit_cache_free(pg_ctx* ctx);
 }
 
 namespace pg {

@@ -127,7 +127,11 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
                 fl.null_gid = (int32_t)(sp[1] & 0xffffffff);
             }
             fl.miss_flag = miss_flag.as<uint8_t>(); fl.d_miss = miss_cnt.as<unsigned long long>();
-            if (accumulate_private(ctx, build_prog(PREFIX), nullptr, m, groups, nullptr, &fl)) {
+            fl.row_base = PREFIX;
+            for (size_t k = 0; k < op->key_channels.size() && k < 8; k++) fl.key_value_bytes[k] = imp[op->key_channels[k]].value_bytes;
+            // first choice: the kernel specialised at run time for this plan; otherwise the generic ahead-of-time kernel
+            AggProgram fprog = build_prog(PREFIX);
+            if (accumulate_lowcard_jit(ctx, fprog, m, groups, fl) || accumulate_private(ctx, fprog, nullptr, m, groups, nullptr, &fl)) {
                 int64_t misses;
                 read_scalars(ctx, miss_cnt.p, 1, &misses);
                 if (misses > 0) generic_rows(PREFIX, m, miss_flag.as<uint8_t>());

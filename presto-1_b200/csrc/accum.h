@@ -107,6 +107,7 @@ void agg_ensure_capacity(pg_agg* agg, int64_t group_count);
 AggOp agg_make_op(pg_agg* agg, const DCol* arg, const DCol* mask);
 // evaluate groups [first, first+n) into device buffers described by `st` (already begun)
 void agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, int64_t* error_group, bool do_sync);
+void agg_evaluate_async(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, long long* d_err);
 int agg_n_intermediate(const pg_agg* agg);
 void accumulate_intermediate(pg_agg* agg, const DCol& s0, const DCol& s1, const int32_t* d_ids, int64_t n, int64_t group_count);
 }  // namespace pg

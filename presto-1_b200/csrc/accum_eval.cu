@@ -352,14 +352,31 @@ void agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_
     pg_ctx* ctx = agg->ctx;
     PG_CHECK_ARG(first >= 0 && n >= 0 && out != nullptr, "bad arguments");
     if (n == 0) return;
+    DevBuf err(ctx, 8);
+    memset_async(ctx, err.p, 0x7f, 8);
+    agg_evaluate_async(agg, first, n, final_step, out, err.as<long long>());
+    if (do_sync || error_group) {
+        int64_t eg;
+        read_scalars(ctx, err.p, 1, &eg);
+        if (eg != 0x7f7f7f7f7f7f7f7fLL) {
+            if (error_group) *error_group = eg;
+            fail(PG_E_NUMERIC_OVERFLOW, agg->op == OP_SUM_I64 ? "bigint addition overflow" : "Decimal overflow");
+        }
+    }
+}
+
+// Launches the evaluation and the copies into host outputs without waiting; *d_err (device, preset to 0x7f..7f) receives
+// the smallest overflowing group id.
+void agg_evaluate_async(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, long long* d_err) {
+    pg_ctx* ctx = agg->ctx;
+    PG_CHECK_ARG(first >= 0 && n >= 0 && out != nullptr, "bad arguments");
+    if (n == 0) return;
     agg_ensure_capacity(agg, first + n);
     int32_t t[2];
     out_types(agg, final_step, t);
     int ncols = t[1] ? 2 : 1;
     for (int k = 0; k < ncols; k++)
         PG_CHECK_ARG(out[k].type == t[k], "output column %d must have type %d, got %d", k, t[k], out[k].type);
-    DevBuf err(ctx, 8);
-    memset_async(ctx, err.p, 0x7f, 8);
     OutStage st[2];
     int64_t vbytes[2] = {0, 0};
     const unsigned long long* state = agg->state.as<unsigned long long>();
@@ -386,18 +403,10 @@ void agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_
         a.first = first; a.n = n;
         a.out0 = st[0].d_values; a.nulls0 = st[0].d_nulls;
         a.out1 = ncols > 1 ? st[1].d_values : nullptr; a.nulls1 = ncols > 1 ? st[1].d_nulls : nullptr;
-        a.error_group = err.as<long long>();
+        a.error_group = d_err;
         PG_LAUNCH(ctx, acc_evaluate_kernel, grid_for(ctx, n, 256), 256, 0, a);
     }
     for (int k = 0; k < ncols; k++) st[k].finish(vbytes[k]);
-    if (do_sync || error_group) {
-        int64_t eg;
-        read_scalars(ctx, err.p, 1, &eg);
-        if (eg != 0x7f7f7f7f7f7f7f7fLL) {
-            if (error_group) *error_group = eg;
-            fail(PG_E_NUMERIC_OVERFLOW, agg->op == OP_SUM_I64 ? "bigint addition overflow" : "Decimal overflow");
-        }
-    }
 }
 
 }  // namespace pg

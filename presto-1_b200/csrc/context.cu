@@ -27,11 +27,14 @@ void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
     PG_CHECK_ARG(n == 0 || c.values != nullptr || type_is_var(c.type), "column without values");
     out.n = n;
     out.d.type = c.type; out.d.pad = 0;
-    out.value_bytes = col_value_bytes(ctx, c, n);
     if (c.mem == PG_MEM_DEVICE) {
+        // in place; the byte size of a variable width value buffer sits in device memory (offsets[n]) and is only
+        // fetched by the callers that need it (resolve_value_bytes), one synchronisation for all columns
+        out.value_bytes = type_is_var(c.type) ? -1 : n * type_width(c.type);
         out.d.values = c.values; out.d.nulls = c.nulls; out.d.offsets = c.offsets;
         return;
     }
+    out.value_bytes = col_value_bytes(ctx, c, n);
     PG_CHECK_ARG(c.mem == PG_MEM_HOST, "bad mem kind %d", c.mem);
     out.values.alloc(ctx, out.value_bytes > 0 ? out.value_bytes : 8);
     copy_async(ctx, out.values.p, c.values, out.value_bytes, cudaMemcpyHostToDevice);
@@ -48,6 +51,52 @@ void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
         else memset_async(ctx, out.offsets.p, 0, (n + 1) * 4);
         out.d.offsets = out.offsets.as<int32_t>();
     }
+}
+
+void resolve_value_bytes(pg_ctx* ctx, ColImport** cols, int count) {
+    int pending[64], np = 0;
+    for (int i = 0; i < count && np < 64; i++) {
+        if (cols[i]->value_bytes >= 0) continue;
+        if (cols[i]->n == 0) { cols[i]->value_bytes = 0; continue; }
+        copy_async(ctx, (char*)ctx->h_scalar + 8 * np, cols[i]->d.offsets + cols[i]->n, 4, cudaMemcpyDeviceToHost);
+        pending[np++] = i;
+    }
+    if (np == 0) return;
+    sync(ctx);
+    for (int j = 0; j < np; j++) {
+        int32_t last;
+        memcpy(&last, (char*)ctx->h_scalar + 8 * j, 4);
+        cols[pending[j]]->value_bytes = last;
+    }
+}
+
+static const int64_t OUT_ARENA_BYTES = 4 << 20, OUT_ARENA_MAX_PIECE = 512 << 10;
+
+void* out_arena_alloc(pg_ctx* ctx, int64_t bytes, int64_t* off) {
+    if (bytes > OUT_ARENA_MAX_PIECE) return nullptr;
+    if (!ctx->out_dev) {
+        if (cudaMalloc(&ctx->out_dev, OUT_ARENA_BYTES) != cudaSuccess) { cudaGetLastError(); ctx->out_dev = nullptr; return nullptr; }
+        if (cudaMallocHost((void**)&ctx->out_pinned, OUT_ARENA_BYTES) != cudaSuccess) {
+            cudaGetLastError(); cudaFree(ctx->out_dev); ctx->out_dev = nullptr; return nullptr;
+        }
+        ctx->out_cap = OUT_ARENA_BYTES;
+    }
+    int64_t need = (bytes + 255) & ~255LL;
+    if (need == 0) need = 256;
+    if (ctx->out_used + need > ctx->out_cap) return nullptr;
+    *off = ctx->out_used;
+    ctx->out_used += need;
+    return (char*)ctx->out_dev + *off;
+}
+
+void flush_host_outputs(pg_ctx* ctx) {
+    cudaError_t e = cudaMemcpyAsync(ctx->out_pinned, ctx->out_dev, (size_t)ctx->out_used, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    std::vector<pg_ctx::pending_out> pend;
+    pend.swap(ctx->out_pending);
+    ctx->out_used = 0;
+    if (e != cudaSuccess) fail(PG_E_CUDA, "flushing host outputs failed: %s", cudaGetErrorString(e));
+    for (const pg_ctx::pending_out& p : pend) memcpy(p.host, ctx->out_pinned + p.off, (size_t)p.bytes);
 }
 
 cudaEvent_t timing_event(pg_ctx* ctx) {
@@ -93,6 +142,8 @@ int32_t pg_ctx_destroy(pg_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
+    if (ctx->out_dev) cudaFree(ctx->out_dev);
+    if (ctx->out_pinned) cudaFreeHost(ctx->out_pinned);
     for (const pg_kernel_record& r : ctx->records) { cudaEventDestroy(r.start); cudaEventDestroy(r.stop); }
     for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
     pg::jit_cache_free(ctx);

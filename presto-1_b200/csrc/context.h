@@ -30,6 +30,13 @@ struct pg_ctx {
     std::vector<pg_kernel_record> records;
     std::vector<cudaEvent_t> event_pool;
     pg::JitCache* jit = nullptr;   // run-time specialised kernels (jit.h), created on first use
+    // small host outputs are gathered in one device arena and leave with ONE device->pinned copy at the next
+    // synchronisation (pg::sync), instead of one blocking copy per column
+    struct pending_out { void* host; int64_t off, bytes; };
+    void* out_dev = nullptr;
+    char* out_pinned = nullptr;
+    int64_t out_cap = 0, out_used = 0;
+    std::vector<pending_out> out_pending;
 };
 
 namespace pg {
@@ -83,10 +90,10 @@ static inline int32_t guard(pg_ctx* ctx, F&& f) {
         f();
         return PG_OK;
     } catch (const Error& e) {
-        if (ctx) ctx->err = e.msg;
+        if (ctx) { ctx->err = e.msg; ctx->out_pending.clear(); ctx->out_used = 0; }
         return e.code;
     } catch (const std::exception& e) {
-        if (ctx) ctx->err = e.what();
+        if (ctx) { ctx->err = e.what(); ctx->out_pending.clear(); ctx->out_used = 0; }
         return PG_E_INTERNAL;
     }
 }
@@ -136,7 +143,13 @@ static inline void memset_async(pg_ctx* ctx, void* p, int v, int64_t bytes) {
 static inline void copy_async(pg_ctx* ctx, void* dst, const void* src, int64_t bytes, cudaMemcpyKind kind) {
     if (bytes > 0) PG_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, kind, ctx->stream));
 }
-static inline void sync(pg_ctx* ctx) { PG_CUDA(cudaStreamSynchronize(ctx->stream)); }
+void flush_host_outputs(pg_ctx* ctx);   // context.cu
+static inline void sync(pg_ctx* ctx) {
+    if (!ctx->out_pending.empty()) { flush_host_outputs(ctx); return; }
+    PG_CUDA(cudaStreamSynchronize(ctx->stream));
+}
+// carve `bytes` out of the output arena (nullptr when it does not fit: the caller stages the column on its own)
+void* out_arena_alloc(pg_ctx* ctx, int64_t bytes, int64_t* off);
 
 // read back up to 64 int64 scalars from device memory (synchronises the stream)
 static inline void read_scalars(pg_ctx* ctx, const void* d, int n, int64_t* out) {
@@ -154,6 +167,8 @@ struct ColImport {
     int64_t value_bytes = 0;
 };
 void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out);
+// fills value_bytes of device-resident variable width columns (left at -1 by import_col) with one synchronisation
+void resolve_value_bytes(pg_ctx* ctx, ColImport** cols, int count);
 // bytes of the value buffer of column c with n rows (reads the last offset for variable width columns)
 int64_t col_value_bytes(pg_ctx* ctx, const pg_col& c, int64_t n);
 
@@ -166,6 +181,14 @@ struct OutStage {
     int32_t* d_offsets = nullptr;
     DevBuf bv, bn, bo;
     int64_t n = 0;
+    int64_t av = -1, an = -1, ao = -1;   // arena offsets (>= 0: the part leaves through the batched copy)
+    void* stage(DevBuf& own, int64_t bytes, int64_t& aoff) {
+        void* p = out_arena_alloc(ctx, bytes, &aoff);
+        if (p) return p;
+        aoff = -1;
+        own.alloc(ctx, bytes > 0 ? bytes : 8);
+        return own.p;
+    }
     void begin(pg_ctx* c, pg_col_out* out, int64_t rows, int64_t value_bytes) {
         ctx = c; o = out; n = rows;
         PG_CHECK_ARG(out != nullptr, "missing output column");
@@ -176,16 +199,21 @@ struct OutStage {
         if (out->mem == PG_MEM_DEVICE) {
             d_values = out->values; d_nulls = out->nulls; d_offsets = out->offsets;
         } else {
-            bv.alloc(c, value_bytes > 0 ? value_bytes : 8); d_values = bv.p;
-            if (out->nulls) { bn.alloc(c, rows > 0 ? rows : 1); d_nulls = bn.as<uint8_t>(); }
-            if (var) { bo.alloc(c, (rows + 1) * 4); d_offsets = bo.as<int32_t>(); }
+            d_values = stage(bv, value_bytes, av);
+            if (out->nulls) d_nulls = (uint8_t*)stage(bn, rows > 0 ? rows : 1, an);
+            if (var) d_offsets = (int32_t*)stage(bo, (rows + 1) * 4, ao);
         }
     }
     void finish(int64_t value_bytes) {
         if (o->mem == PG_MEM_DEVICE) return;
-        copy_async(ctx, o->values, d_values, value_bytes, cudaMemcpyDeviceToHost);
-        if (o->nulls) copy_async(ctx, o->nulls, d_nulls, n, cudaMemcpyDeviceToHost);
-        if (type_is_var(o->type)) copy_async(ctx, o->offsets, d_offsets, (n + 1) * 4, cudaMemcpyDeviceToHost);
+        leave(o->values, d_values, value_bytes, av);
+        if (o->nulls) leave(o->nulls, d_nulls, n, an);
+        if (type_is_var(o->type)) leave(o->offsets, d_offsets, (n + 1) * 4, ao);
+    }
+    void leave(void* host, const void* dev, int64_t bytes, int64_t aoff) {
+        if (bytes <= 0) return;
+        if (aoff >= 0) ctx->out_pending.push_back({host, aoff, bytes});
+        else copy_async(ctx, host, dev, bytes, cudaMemcpyDeviceToHost);
     }
 };
 

@@ -721,6 +721,8 @@ int32_t pg_groupby_contains(pg_groupby* gb, const pg_col* keys, const pg_col* ha
     });
 }
 
+static const int64_t VAR_BOUND_BYTES = 64 * 1024;
+
 int32_t pg_groupby_varwidth_bytes(pg_groupby* gb, int32_t key, int64_t* out_bytes) {
     if (!gb || !out_bytes) return PG_E_INVALID_ARGUMENT;
     return guard(gb->ctx, [&] {
@@ -728,6 +730,8 @@ int32_t pg_groupby_varwidth_bytes(pg_groupby* gb, int32_t key, int64_t* out_byte
         PG_CHECK_ARG(key >= 0 && key < gb->layout.nkeys, "bad key channel");
         *out_bytes = 0;
         if (!type_is_var(gb->layout.types[key]) || gb->groups == 0) return;
+        // small stores: the bytes held for ALL variable width keys bound this one's, and the host already knows them
+        if (gb->arena_used <= VAR_BOUND_BYTES) { *out_bytes = gb->arena_used; return; }
         DevBuf acc(ctx, 8);
         memset_async(ctx, acc.p, 0, 8);
         PG_LAUNCH(ctx, gb_sum_var_bytes_kernel, grid_for(ctx, gb->groups, 256), 256, 0, gb->key_rows.as<uint64_t>(), gb->layout, key,
@@ -774,9 +778,13 @@ int32_t pg_groupby_export_keys(pg_groupby* gb, int64_t first, int64_t n, pg_col_
                     PG_LAUNCH(ctx, gb_export_var_count_kernel, (int)ntiles, SCAN_THREADS, 0, gb->key_rows.as<uint64_t>(), L, k, first, n,
                               tiles.as<Pair64>());
                     scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, d_total);
-                    int64_t tot[2];
-                    read_scalars(ctx, d_total, 2, tot);
-                    vbytes[k] = tot[0];
+                    if (gb->arena_used <= VAR_BOUND_BYTES && out_keys[k].values_capacity_bytes >= gb->arena_used) {
+                        vbytes[k] = gb->arena_used;   // upper bound known on the host: no read-back of the exact total
+                    } else {
+                        int64_t tot[2];
+                        read_scalars(ctx, d_total, 2, tot);
+                        vbytes[k] = tot[0];
+                    }
                     st[k].begin(ctx, &out_keys[k], n, vbytes[k]);
                     PG_LAUNCH(ctx, gb_export_var_kernel, (int)ntiles, SCAN_THREADS, 0, gb->key_rows.as<uint64_t>(), gb->arena.as<uint8_t>(), L,
                               k, first, n, tiles.as<Pair64>(), (uint8_t*)st[k].d_values, st[k].d_offsets, st[k].d_nulls);

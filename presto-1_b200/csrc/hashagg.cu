@@ -106,7 +106,7 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     // Large raw pages: a short prefix goes through the general path and numbers the groups; if there are only a few and
     // the keys are short, the rest is resolved and accumulated in ONE kernel (packed-key look-up in shared memory, private
     // partial states), and only rows that kernel could not resolve take the general path afterwards.
-    const int64_t PREFIX = 128 * 1024;
+    const int64_t PREFIX = 32 * 1024;
     bool fused_done = false;
     if (raw && !op->aggs.empty() && n >= 8 * PREFIX && fused_keys_packable(op->gb->layout)) {
         generic_rows(0, PREFIX, nullptr);
@@ -128,7 +128,13 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
             }
             fl.miss_flag = miss_flag.as<uint8_t>(); fl.d_miss = miss_cnt.as<unsigned long long>();
             fl.row_base = PREFIX;
-            for (size_t k = 0; k < op->key_channels.size() && k < 8; k++) fl.key_value_bytes[k] = imp[op->key_channels[k]].value_bytes;
+            {
+                ColImport* kimp[8];
+                int nk = 0;
+                for (size_t k = 0; k < op->key_channels.size() && k < 8; k++) kimp[nk++] = &imp[op->key_channels[k]];
+                resolve_value_bytes(ctx, kimp, nk);
+                for (int k = 0; k < nk; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
+            }
             // first choice: the kernel specialised at run time for this plan; otherwise the generic ahead-of-time kernel
             AggProgram fprog = build_prog(PREFIX);
             if (accumulate_lowcard_jit(ctx, fprog, m, groups, fl) || accumulate_private(ctx, fprog, nullptr, m, groups, nullptr, &fl)) {
@@ -281,13 +287,19 @@ int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_o
         int col = nk + (has_hash ? 1 : 0);
         bool partial = step_output_partial(op->step);
         int64_t first_err = -1;
-        for (pg_agg* a : op->aggs) {
-            int64_t eg = -1;
-            try { agg_evaluate(a, first, n, partial ? 0 : 1, out + col, &eg, true); }
-            catch (const Error& e) { if (e.code != PG_E_NUMERIC_OVERFLOW) throw; if (first_err < 0) first_err = eg; }
+        const int na = (int)op->aggs.size();
+        DevBuf errs(ctx, 8 * (na > 0 ? na : 1));       // one sticky "first overflowing group" word per aggregate
+        memset_async(ctx, errs.p, 0x7f, 8 * (na > 0 ? na : 1));
+        for (int i = 0; i < na; i++) {
+            pg_agg* a = op->aggs[i];
+            agg_evaluate_async(a, first, n, partial ? 0 : 1, out + col, errs.as<long long>() + i);
             col += partial ? agg_n_intermediate(a) : 1;
         }
-        sync(ctx);
+        int64_t eg[MAX_AGGS];
+        if (na > 0) {
+            read_scalars(ctx, errs.p, na, eg);          // also completes the copies into host output columns
+            for (int i = 0; i < na; i++) if (eg[i] != 0x7f7f7f7f7f7f7f7fLL && first_err < 0) first_err = eg[i];
+        } else sync(ctx);
         if (first_err >= 0) {
             if (error_group) *error_group = first_err;
             fail(PG_E_NUMERIC_OVERFLOW, "aggregate overflow in group %lld", (long long)first_err);

@@ -1,0 +1,27 @@
+"""Host-side breakdown of one Q1 operator pass (create / add_input / get_output / close), wall clock with syncs."""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import presto_b200 as P
+from presto_b200 import tpch
+
+sf = float(sys.argv[1]) if len(sys.argv) > 1 else 10
+ctx = P.GpuContext(0)
+cols = tpch.lineitem(sf, seed=42, device="cuda")
+page = tpch.q1_page(cols)
+aggs = tpch.q1_aggregators()
+acc = {}
+def tick(name, t0):
+    torch.cuda.synchronize()
+    acc[name] = acc.get(name, 0.0) + (time.perf_counter() - t0)
+reps = 30
+for it in range(reps + 3):
+    if it == 3:
+        acc.clear()
+    t = time.perf_counter(); op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.SINGLE, aggs, expected_groups=100_000, ctx=ctx); tick("create", t)
+    t = time.perf_counter(); op.add_input(page); tick("add_input", t)
+    t = time.perf_counter(); op.finish(); out = op.get_output(); tick("get_output", t)
+    t = time.perf_counter(); op.close(); tick("close", t)
+for k, v in acc.items():
+    print("%-12s %8.3f ms" % (k, v / reps * 1e3))
+print("total        %8.3f ms" % (sum(acc.values()) / reps * 1e3))

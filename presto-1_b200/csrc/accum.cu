@@ -77,7 +77,7 @@ void accumulate(pg_ctx* ctx, const AggProgram& prog_in, const int32_t* gids, int
     }
     prog.priv_words = priv_words;
     // strategy: few groups -> thread-private tables in shared memory (accum_private.cu); otherwise global atomics
-    bool use_private = !has128 && n >= 64 * 1024;
+    bool use_private = !has128 && n >= 4 * 1024;
     PG_CHECK_STATE(!(has128 && only_rows), "128-bit min/max cannot be combined with a row filter");
     std::vector<DevBuf> snaps;
     if (has128) {

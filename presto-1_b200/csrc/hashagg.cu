@@ -106,7 +106,7 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     // Large raw pages: a short prefix goes through the general path and numbers the groups; if there are only a few and
     // the keys are short, the rest is resolved and accumulated in ONE kernel (packed-key look-up in shared memory, private
     // partial states), and only rows that kernel could not resolve take the general path afterwards.
-    const int64_t PREFIX = 32 * 1024;
+    const int64_t PREFIX = 16 * 1024;
     bool fused_done = false;
     if (raw && !op->aggs.empty() && n >= 8 * PREFIX && fused_keys_packable(op->gb->layout)) {
         generic_rows(0, PREFIX, nullptr);

@@ -5,6 +5,7 @@
 // The prelude defines
 //   PG_T            threads per block            PG_VEC       consecutive rows per thread and trip (1, 2 or 4)
 //   PG_REC_WORDS    u64 words per group/thread   PG_MIN_BLOCKS  __launch_bounds__ second argument
+//   PG_PREFETCH     trips ahead whose rows are prefetched into L2 (0 = off)
 //   PG_KEYS(X)      X(k, CLASS, WORD, SHIFT, HASNULL, WOFF)   CLASS in {K64, KDBL, K32, K8, KVAR}
 //   PG_CONDS(X)     X(c, HASMASK, HASMASKNULLS, HASARGNULLS)
 //   PG_SLOTS(X)     X(s, KIND, COND, CONV, WORD)              KIND in {DEC, I64, I32, F64, MIN, MAX, CNT}
@@ -27,6 +28,9 @@ typedef unsigned char u8;
 
 #define PGJ_CAT2(a, b) a##b
 #define PGJ_CAT(a, b) PGJ_CAT2(a, b)
+
+// shared-memory key -> group id table: one 32-byte entry per slot, read with two independent 16-byte loads
+struct __align__(16) LutEntry { u64 w0, w1; int gid; int pad[3]; };
 
 // ------------------------------------------------------------------ vector loads (read-only path)
 template <int V> __device__ __forceinline__ void load_u64(const void* base, i64 row, u64 (&o)[V]) {
@@ -201,7 +205,7 @@ __device__ __forceinline__ void wreduce_sum_carry(u64& s, u64& carry) {
 
 // ------------------------------------------------------------------ V consecutive rows of one thread
 template <int V>
-__device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* table, const ulonglong2* lut_key, const int* lut_gid,
+__device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* table, const LutEntry* lut,
                                              int tid, u64& misses) {
     bool fits[V];
 #pragma unroll
@@ -225,7 +229,8 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
 #define PG_X(k, CLASS, WORD, SHIFT, HASNULL, WOFF) PGJ_K2_##CLASS(k)
     PG_KEYS(PG_X)
 #undef PG_X
-    // ---- per row: pack the key, find the group, update the thread's private record
+    // ---- phase A: pack the keys and find the groups of all V rows (independent look-ups overlap each other)
+    int g[V];
 #pragma unroll
     for (int v = 0; v < V; v++) {
         u64 w0 = 0, w1 = 0;
@@ -235,18 +240,22 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
         else w1 |= PGJ_CAT(kv, k)[v] << SHIFT;
         PG_KEYS(PG_X)
 #undef PG_X
-        int g = -1;
+        g[v] = -1;
         if (fits[v]) {
             u32 h = lut_hash(w0, w1);
             while (true) {
-                const ulonglong2 e = lut_key[h];
-                if (e.x == w0 && e.y == w1) { g = lut_gid[h]; break; }
-                if ((e.x & e.y) == ~0ULL) break;          // empty slot: w1 == ~0 is not a valid packed key
+                const LutEntry e = lut[h];
+                if (e.w0 == w0 && e.w1 == w1) { g[v] = e.gid; break; }
+                if (e.gid < 0) break;
                 h = (h + 1) & (PGJ_LUT_SIZE - 1);
             }
         }
-        if (g < 0) { misses++; a.miss_flag[row + v] = 1; continue; }
-        u64* rec = table + (g * PG_REC_WORDS) * PG_T + tid;
+    }
+    // ---- phase B: update the thread's private records, row by row (two rows may share a group)
+#pragma unroll
+    for (int v = 0; v < V; v++) {
+        if (g[v] < 0) { misses++; a.miss_flag[row + v] = 1; continue; }
+        u64* rec = table + (g[v] * PG_REC_WORDS) * PG_T + tid;
 #define PG_X(c, HASMASK, HASMASKNULLS, HASARGNULLS)                                                         \
         const bool PGJ_CAT(cond, c) = (!HASMASK || PGJ_CAT(cm, c)[v] != 0) && (!HASMASKNULLS || PGJ_CAT(cmn, c)[v] == 0) && \
                                       (!HASARGNULLS || PGJ_CAT(can, c)[v] == 0);
@@ -256,6 +265,37 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
         PG_SLOTS(PG_X)
 #undef PG_X
     }
+}
+
+// L2 prefetch of the V rows a later trip of this thread will read (PG_PREFETCH trips ahead): keeps more of HBM's
+// latency covered than the registers of one trip can
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+template <int V>
+__device__ __forceinline__ void prefetch_rows(const PgjArgs& a, i64 row) {
+#define PGJ_PF_K64(k) prefetch_l2((const u64*)a.key_values[k] + row);
+#define PGJ_PF_KDBL(k) PGJ_PF_K64(k)
+#define PGJ_PF_K32(k) prefetch_l2((const int*)a.key_values[k] + row);
+#define PGJ_PF_K8(k) prefetch_l2((const u8*)a.key_values[k] + row);
+#define PGJ_PF_KVAR(k) prefetch_l2(a.key_offsets[k] + row); prefetch_l2((const u8*)a.key_values[k] + a.row_base + row);
+#define PG_X(k, CLASS, WORD, SHIFT, HASNULL, WOFF) PGJ_PF_##CLASS(k) if (HASNULL) prefetch_l2(a.key_nulls[k] + row);
+    PG_KEYS(PG_X)
+#undef PG_X
+#define PG_X(c, HASMASK, HASMASKNULLS, HASARGNULLS)                 \
+    if (HASMASK) prefetch_l2(a.cond_mask[c] + row);                 \
+    if (HASMASKNULLS) prefetch_l2(a.cond_mask_nulls[c] + row);      \
+    if (HASARGNULLS) prefetch_l2(a.cond_arg_nulls[c] + row);
+    PG_CONDS(PG_X)
+#undef PG_X
+#define PGJ_PFS_DEC(s) _Pragma("unroll") for (int q = 0; q < V; q += 2) prefetch_l2((const ulonglong2*)a.slot_ptr[s] + row + q);
+#define PGJ_PFS_I64(s) prefetch_l2((const u64*)a.slot_ptr[s] + row);
+#define PGJ_PFS_I32(s) prefetch_l2((const int*)a.slot_ptr[s] + row);
+#define PGJ_PFS_F64(s) PGJ_PFS_I64(s)
+#define PGJ_PFS_MIN(s) PGJ_PFS_I64(s)
+#define PGJ_PFS_MAX(s) PGJ_PFS_I64(s)
+#define PGJ_PFS_CNT(s)
+#define PG_X(s, KIND, COND, CONV, WORD) PGJ_PFS_##KIND(s)
+    PG_SLOTS(PG_X)
+#undef PG_X
 }
 
 // stored key of group g in the packed form (thread 0 builds the look-up table once per block)
@@ -283,8 +323,7 @@ __device__ bool pack_group(const PgjArgs& a, int g, u64& w0, u64& w1) {
 
 extern "C" __global__ void __launch_bounds__(PG_T, PG_MIN_BLOCKS) pg_lowcard_agg(const PgjArgs a) {
     extern __shared__ u64 table[];
-    __shared__ ulonglong2 lut_key[PGJ_LUT_SIZE];
-    __shared__ int lut_gid[PGJ_LUT_SIZE];
+    __shared__ LutEntry lut[PGJ_LUT_SIZE];
     const int tid = threadIdx.x;
     const int G = a.G;
     // ---- own column: zeros, then min/max identities
@@ -294,15 +333,15 @@ extern "C" __global__ void __launch_bounds__(PG_T, PG_MIN_BLOCKS) pg_lowcard_agg
     if (PGJ_ISKIND_##KIND == PGJ_KIND_MAX) for (int g = 0; g < G; g++) table[(g * PG_REC_WORDS + WORD) * PG_T + tid] = 0x8000000000000000ULL;
     PG_SLOTS(PG_X)
 #undef PG_X
-    for (int i = tid; i < PGJ_LUT_SIZE; i += PG_T) { lut_key[i] = make_ulonglong2(~0ULL, ~0ULL); lut_gid[i] = -1; }
+    for (int i = tid; i < PGJ_LUT_SIZE; i += PG_T) { lut[i].w0 = ~0ULL; lut[i].w1 = ~0ULL; lut[i].gid = -1; }
     __syncthreads();
     if (tid == 0) {
         for (int g = 0; g < G; g++) {
             u64 w0, w1;
             if (!pack_group(a, g, w0, w1)) continue;
             u32 h = lut_hash(w0, w1);
-            while (lut_gid[h] >= 0) h = (h + 1) & (PGJ_LUT_SIZE - 1);
-            lut_key[h] = make_ulonglong2(w0, w1); lut_gid[h] = g;
+            while (lut[h].gid >= 0) h = (h + 1) & (PGJ_LUT_SIZE - 1);
+            lut[h].w0 = w0; lut[h].w1 = w1; lut[h].gid = g;
         }
     }
     __syncthreads();
@@ -311,10 +350,14 @@ extern "C" __global__ void __launch_bounds__(PG_T, PG_MIN_BLOCKS) pg_lowcard_agg
     u64 misses = 0;
     const i64 n = a.n;
     const i64 stride = (i64)gridDim.x * PG_T * PG_VEC;
-    for (i64 row = ((i64)blockIdx.x * PG_T + tid) * PG_VEC; row + PG_VEC <= n; row += stride)
-        process_rows<PG_VEC>(a, row, table, lut_key, lut_gid, tid, misses);
+    for (i64 row = ((i64)blockIdx.x * PG_T + tid) * PG_VEC; row + PG_VEC <= n; row += stride) {
+#if PG_PREFETCH > 0
+        if (row + PG_PREFETCH * stride + PG_VEC <= n) prefetch_rows<PG_VEC>(a, row + PG_PREFETCH * stride);
+#endif
+        process_rows<PG_VEC>(a, row, table, lut, tid, misses);
+    }
     if (PG_VEC > 1 && blockIdx.x == 0 && tid == 0)
-        for (i64 row = n - n % PG_VEC; row < n; row++) process_rows<1>(a, row, table, lut_key, lut_gid, tid, misses);
+        for (i64 row = n - n % PG_VEC; row < n; row++) process_rows<1>(a, row, table, lut, tid, misses);
 
     // ---- flush: per aggregate and group, reduce the warp's 32 columns and fold them into the global state
     const int lane = tid & 31;

@@ -3,6 +3,7 @@
 // aggregation (AccumulatorCompiler.java:487-566: which channels are read, which mask applies, which state is updated);
 // identical pieces of state are shared (sum(x) and avg(x) keep one sum, every aggregate under one mask keeps one count).
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "accum.h"
 #include "groupby.h"
@@ -143,7 +144,11 @@ bool accumulate_lowcard_jit(pg_ctx* ctx, const AggProgram& prog, int64_t n, int6
     // ---- source = generated prelude + argument block + body; the prelude doubles as the cache signature
     std::string pre;
     char buf[256];
-    snprintf(buf, sizeof(buf), "#define PG_T %d\n#define PG_VEC %d\n#define PG_MIN_BLOCKS 1\n#define PG_REC_WORDS %d\n", T, vec, words);
+    int prefetch = 1;
+    if (const char* e = getenv("PRESTOGPU_JIT_PREFETCH")) prefetch = atoi(e);
+    if (const char* e = getenv("PRESTOGPU_JIT_VEC")) { int v = atoi(e); if ((v == 1 || v == 2 || v == 4) && v <= vec) vec = v; }
+    snprintf(buf, sizeof(buf), "#define PG_T %d\n#define PG_VEC %d\n#define PG_MIN_BLOCKS 1\n#define PG_REC_WORDS %d\n#define PG_PREFETCH %d\n", T, vec,
+             words, prefetch);
     pre += buf;
     pre += "#define PG_KEYS(X)";
     for (int k = 0; k < L.nkeys; k++) {

@@ -28,6 +28,7 @@ def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--extra-shuffle", action="store_true", help="extras: lineitem rows in random order instead of clustered by order key")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--sf", type=float, default=10.0, help="TPC-H scale factor of the lineitem shard per GPU")
@@ -224,7 +225,7 @@ def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0)
     sf = args.extra_sf
     n_orders = int(1_500_000 * sf)
     # disjoint order-key ranges per rank: shard r owns orders [r*n_orders, (r+1)*n_orders)
-    li = tpch.lineitem(sf, seed=42 + rank, device="cuda", need=("keys", "double"))
+    li = tpch.lineitem(sf, seed=42 + rank, device="cuda", need=("keys", "double"), shuffle=args.extra_shuffle)
     n = li["rows"]
     key_off = rank * tpch.order_key(torch.tensor(n_orders, dtype=torch.int64)).item()
     li["orderkey"] += key_off

@@ -3,8 +3,12 @@
 // OP/aggregation/builder/InMemoryHashAggregationBuilder.java:139-155 (processPage), :243-298 (buildResult).
 // One page = getGroupIds (groupby.cu) -> one accumulate() launch over ALL aggregates (accum.cu); group ids never
 // leave the device.
+#include <stdlib.h>
+
 #include "accum.h"
 #include "groupby.h"
+#include "hashagg_wide.h"
+#include "jit.h"
 
 struct pg_hashagg {
     pg_ctx* ctx = nullptr;
@@ -18,7 +22,10 @@ struct pg_hashagg {
     std::vector<pg_agg*> aggs;
     pg::DevBuf ids;
     int64_t input_rows = 0;
+    pg::WideTable* wide = nullptr;   // many-groups path (hashagg_wide.h), chosen on the first page
+    int64_t rows_since_reset = 0;    // first-seen order of the wide path is kept by operator-wide row numbers
     ~pg_hashagg() {
+        delete wide;
         for (pg_agg* a : aggs) delete a;
         delete gb;
     }
@@ -106,6 +113,47 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     // Large raw pages: a short prefix goes through the general path and numbers the groups; if there are only a few and
     // the keys are short, the rest is resolved and accumulated in ONE kernel (packed-key look-up in shared memory, private
     // partial states), and only rows that kernel could not resolve take the general path afterwards.
+    // Many groups on one BIGINT key: state inside the hash buckets, one kernel per page, ids assigned at output time.
+    if (raw && op->gb->bigint_mode && !has_hash) {
+        // PRESTOGPU_WIDE: 0 = never, 1 = whenever there are many groups, unset = only when the input is not clustered by key.
+        // Measured on B200, GROUP BY orderkey over lineitem SF10 (profiles/README.md): rows in random order 13.8 ms against
+        // 21.3 ms on the general path; rows clustered by key 7.4 ms against 5.3 ms (the general path's per-page passes then
+        // run out of L2, one random access per row no longer pays).
+        const char* wide_env = getenv("PRESTOGPU_WIDE");
+        const bool wide_on = wide_env ? wide_env[0] != '0' : true;
+        const bool wide_always = wide_env && wide_env[0] == '1';
+        if (wide_on && !op->wide && op->rows_since_reset == 0 && op->gb->groups == 0 && n >= 256 * 1024 && wide_supported(op->specs, op->aggs) &&
+            jit_available()) {
+            int64_t repeats = 0;
+            const int64_t d = sample_distinct_keys(ctx, kc.c[0], 2048, &repeats);
+            if (d > 128 && (wide_always || repeats * 4 < 2048)) {
+                int64_t est = (int64_t)((double)d / 2048.0 * (double)n);
+                if (est > n / 2) est = n / 2;
+                int64_t target = op->expected * 4 >= est ? op->expected : est;
+                op->wide = wide_create(ctx, op->specs, op->aggs, op->step, target);
+            }
+        }
+        if (op->wide) {
+            std::vector<DCol> wargs(op->aggs.size()), wmasks(op->aggs.size());
+            for (size_t i = 0; i < op->aggs.size(); i++) {
+                const pg_agg_spec& s = op->specs[i];
+                memset(&wargs[i], 0, sizeof(DCol)); memset(&wmasks[i], 0, sizeof(DCol));
+                if (s.kind != PG_AGG_COUNT) {
+                    wargs[i] = need(s.input_channel);
+                    PG_CHECK_ARG(wargs[i].type == s.in_type, "aggregate %d input channel has type %d, expected %d", (int)i, wargs[i].type, s.in_type);
+                }
+                if (s.mask_channel >= 0) { wmasks[i] = need(s.mask_channel); PG_CHECK_ARG(wmasks[i].type == PG_BOOLEAN, "mask must be BOOLEAN"); }
+            }
+            if (wide_add_page(op->wide, kc.c[0], wargs.data(), wmasks.data(), n, op->rows_since_reset)) {
+                op->input_rows += n;
+                op->rows_since_reset += n;
+                return;
+            }
+            PG_CHECK_STATE(op->rows_since_reset == 0, "specialised kernel became unavailable after the first page: %s",
+                           ctx->jit ? ctx->jit->last_error.c_str() : "");
+            delete op->wide; op->wide = nullptr;   // nothing consumed yet: fall through to the general path
+        }
+    }
     const int64_t PREFIX = 16 * 1024;
     bool fused_done = false;
     if (raw && !op->aggs.empty() && n >= 8 * PREFIX && fused_keys_packable(op->gb->layout)) {
@@ -146,6 +194,7 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         }
         if (!fused_done) { generic_rows(PREFIX, n - PREFIX, nullptr); fused_done = true; }
     }
+    op->rows_since_reset += n;
     if (fused_done) {
         op->input_rows += n;
         sync(ctx);
@@ -212,10 +261,15 @@ int32_t pg_hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, i
 
 int32_t pg_hashagg_stats(pg_hashagg* op, int64_t* group_count, int64_t* capacity, int64_t* device_bytes, int64_t* input_rows) {
     if (!op) return PG_E_INVALID_ARGUMENT;
+    if (op->wide && !op->wide->prepared) {
+        // ids do not exist yet; the count and the reference's capacity schedule follow the buckets in use
+        op->gb->groups = op->wide->groups();
+        while (op->gb->groups >= max_fill_075(op->gb->ref_capacity) && op->gb->ref_capacity < (1LL << 30)) op->gb->ref_capacity *= 2;
+    }
     if (group_count) *group_count = op->gb->groups;
     if (capacity) *capacity = op->gb->ref_capacity;
     if (device_bytes) {
-        int64_t b = groupby_device_bytes(op->gb) + op->ids.bytes;
+        int64_t b = groupby_device_bytes(op->gb) + op->ids.bytes + (op->wide ? op->wide->device_bytes() : 0);
         for (pg_agg* a : op->aggs) b += a->state.bytes;
         *device_bytes = b;
     }
@@ -269,6 +323,7 @@ int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_o
     if (!op) return PG_E_INVALID_ARGUMENT;
     return guard(op->ctx, [&] {
         pg_ctx* ctx = op->ctx;
+        if (op->wide) wide_prepare_output(op->wide, op->gb, op->aggs, op->rows_since_reset);
         PG_CHECK_ARG(out && first >= 0 && n >= 0 && first + n <= op->gb->groups, "group range outside [0, %lld)", (long long)op->gb->groups);
         if (error_group) *error_group = -1;
         if (n == 0) return;
@@ -323,6 +378,8 @@ int32_t pg_hashagg_reset(pg_hashagg* op) {
         for (pg_agg* a : op->aggs) delete a;
         op->aggs.clear();
         delete op->gb; op->gb = nullptr;
+        delete op->wide; op->wide = nullptr;
+        op->rows_since_reset = 0;
         hashagg_build(op);
     });
 }

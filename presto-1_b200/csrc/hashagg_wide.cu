@@ -1,0 +1,427 @@
+// hashagg_wide.cu — host side of the many-groups GROUP BY path (see hashagg_wide.h, jit/wide_body.cuh).
+//   wide_add_page        one specialised kernel per page: probe/claim + atomicMax(first row) + every aggregate's update
+//   grow                 when a block ran out of its claim quota: bigger table, buckets re-inserted, left-out rows re-run
+//   wide_prepare_output  first-seen numbering without a sort: one bit per input row marks "a group was first seen here",
+//                        prefix popcounts turn the bit position into the group id, then keys and states are scattered
+//                        into the dense per-group arrays the existing output code (groupby.cu export, accum_eval.cu) reads.
+#include "hashagg_wide.h"
+
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "jit.h"
+#include "jit/wide_args.h"
+#include "jit_embedded_gen.h"
+
+namespace pg {
+
+namespace {
+
+enum { IN_NONE = 0, IN_I64 = 1, IN_I32 = 2, IN_F64 = 3, IN_I2F = 4, IN_DEC128 = 5 };
+const char* in_name(int k) { static const char* n[] = {"NONE", "I64", "I32", "F64", "I2F", "DEC128"}; return n[k]; }
+const char* op_name(int op) {
+    switch (op) { case OP_COUNT: return "CNT"; case OP_SUM_I64: return "SUMI64"; case OP_SUM_F64: return "SUMF64"; default: return "SUMDEC"; }
+}
+const int WIDE_THREADS = 256;
+
+__device__ __forceinline__ unsigned long long w_fmix64(unsigned long long k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33;
+    return k;
+}
+
+// re-insert every occupied bucket of the old table into the (zeroed) new one; the two extra buckets are copied as they are
+__global__ void wide_rebuild_kernel(const unsigned long long* old_table, int64_t old_cap, unsigned long long* new_table, int64_t new_cap, int bw) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < old_cap + 2; i += stride) {
+        const unsigned long long* src = old_table + i * bw;
+        unsigned long long* dst;
+        if (i >= old_cap) {
+            if (src[1] == 0) continue;
+            dst = new_table + (new_cap + (i - old_cap)) * bw;
+        } else {
+            const unsigned long long key = src[0];
+            if (key == 0) continue;
+            uint32_t idx = (uint32_t)(((w_fmix64(key) >> 32) * (unsigned long long)new_cap) >> 32);
+            while (atomicCAS(new_table + (int64_t)idx * bw, 0ULL, key) != 0ULL) idx = idx + 1 == (uint32_t)new_cap ? 0u : idx + 1;
+            dst = new_table + (int64_t)idx * bw;
+        }
+        for (int w = 1; w < bw; w++) dst[w] = src[w];
+    }
+}
+
+// ---- output numbering
+__global__ void wide_mark_first_rows_kernel(const unsigned long long* table, int64_t cap, int bw, uint32_t* bitmap) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < cap + 2; i += stride) {
+        const unsigned long long* b = table + i * bw;
+        if (i < cap ? b[0] == 0 : b[1] == 0) continue;
+        const unsigned long long row = ~b[1];
+        atomicOr(bitmap + (row >> 5), 1u << (row & 31));
+    }
+}
+// tile totals of popcounts (SCAN_TILE words per tile), then an exclusive prefix per word
+__global__ void __launch_bounds__(SCAN_THREADS) wide_popc_tiles_kernel(const uint32_t* bitmap, int64_t nwords, Pair64* tiles) {
+    __shared__ long long red[SCAN_THREADS / 32];
+    int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+    long long s = 0;
+    for (int j = threadIdx.x; j < SCAN_TILE; j += SCAN_THREADS) {
+        int64_t w = base + j;
+        if (w < nwords) s += __popc(bitmap[w]);
+    }
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        long long t = 0;
+        for (int k = 0; k < SCAN_THREADS / 32; k++) t += red[k];
+        tiles[blockIdx.x].a = t; tiles[blockIdx.x].b = 0;
+    }
+}
+__global__ void __launch_bounds__(SCAN_THREADS) wide_word_prefix_kernel(const uint32_t* bitmap, int64_t nwords, const Pair64* tile_prefix,
+                                                                        uint32_t* word_prefix) {
+    // SCAN_ITEMS consecutive words per thread, block-wide exclusive scan of the per-thread sums
+    __shared__ long long warp_sums[SCAN_THREADS / 32];
+    int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    int cnt[SCAN_ITEMS];
+    long long mine = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        int64_t w = base + k;
+        cnt[k] = w < nwords ? __popc(bitmap[w]) : 0;
+        mine += cnt[k];
+    }
+    long long incl = mine;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { long long o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    long long warp_off = 0;
+    for (int k = 0; k < wid; k++) warp_off += warp_sums[k];
+    long long run = tile_prefix[blockIdx.x].a + warp_off + incl - mine;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        int64_t w = base + k;
+        if (w < nwords) word_prefix[w] = (uint32_t)run;
+        run += cnt[k];
+    }
+}
+
+struct GatherPlan {
+    int32_t naggs, bw, flag_word, pad;
+    int32_t op[PGW_MAX_AGGS], in_kind[PGW_MAX_AGGS], cnt_mode[PGW_MAX_AGGS], cnt_word[PGW_MAX_AGGS], val_word[PGW_MAX_AGGS], flag_bit[PGW_MAX_AGGS],
+        words[PGW_MAX_AGGS];
+    unsigned long long* state[PGW_MAX_AGGS];
+};
+// group id of every occupied bucket -> bucket_of_group[gid] (4-byte writes into an array that mostly lives in L2)
+__global__ void wide_number_buckets_kernel(const unsigned long long* table, int64_t cap, int bw, const uint32_t* bitmap, const uint32_t* word_prefix,
+                                           uint32_t* bucket_of_group, Slot* special) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < cap + 2; i += stride) {
+        const unsigned long long* b = table + i * bw;
+        if (i < cap ? b[0] == 0 : b[1] == 0) continue;
+        const unsigned long long row = ~b[1];
+        const uint32_t word = bitmap[row >> 5];
+        const int64_t gid = (int64_t)word_prefix[row >> 5] + __popc(word & ((1u << (row & 31)) - 1u));
+        bucket_of_group[gid] = (uint32_t)i;
+        if (i == cap) special[1].gid = (int32_t)gid;     // the null group (BigintGroupByHash.java:215-222)
+    }
+}
+// 192-bit two's complement accumulator helpers for recombining limb sums
+__device__ __forceinline__ void add192(unsigned long long* w, unsigned long long a0, unsigned long long a1, unsigned long long a2) {
+    unsigned long long s0 = w[0] + a0;
+    unsigned long long c0 = s0 < a0 ? 1ULL : 0ULL;
+    unsigned long long t1 = a1 + c0;
+    unsigned long long c1 = t1 < c0 ? 1ULL : 0ULL;
+    unsigned long long s1 = w[1] + t1;
+    c1 += s1 < t1 ? 1ULL : 0ULL;
+    w[0] = s0; w[1] = s1; w[2] = w[2] + a2 + c1;
+}
+__device__ __forceinline__ void add_limb(unsigned long long* w, unsigned long long x, int shift, bool is_signed) {
+    const unsigned long long ext = is_signed ? (unsigned long long)((long long)x >> 63) : 0ULL;
+    const unsigned long long up = is_signed ? (unsigned long long)((long long)x >> 32) : (x >> 32);
+    switch (shift) {
+        case 0: add192(w, x, ext, ext); break;
+        case 32: add192(w, x << 32, up, ext); break;
+        case 64: add192(w, 0, x, ext); break;
+        default: add192(w, 0, x << 32, up); break;
+    }
+}
+// in group-id order: read the group's bucket (one random 64..160 byte read), write keys and dense states (coalesced)
+__global__ void wide_gather_kernel(const unsigned long long* table, int64_t cap, GatherPlan p, const uint32_t* bucket_of_group, int64_t groups,
+                                   int64_t* values_by_group) {
+    int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; g < groups; g += stride) {
+        const int64_t i = bucket_of_group[g];
+        const unsigned long long* b = table + i * p.bw;
+        values_by_group[g] = i >= cap ? 0 : (int64_t)b[0];
+        const unsigned long long flags = p.flag_word >= 0 ? b[p.flag_word] : 0;
+        for (int a = 0; a < p.naggs; a++) {
+            unsigned long long* st = p.state[a] + g * p.words[a];
+            st[0] = p.cnt_mode[a] == 0 ? b[p.cnt_word[a]] : ((flags >> p.flag_bit[a]) & 1ULL);
+            const unsigned long long* v = b + p.val_word[a];
+            if (p.op[a] == OP_SUM_F64) st[1] = v[0];
+            else if (p.op[a] != OP_COUNT) {
+                unsigned long long w[3] = {0, 0, 0};
+                if (p.in_kind[a] == IN_DEC128) { add_limb(w, v[0], 0, false); add_limb(w, v[1], 32, false); add_limb(w, v[2], 64, false); add_limb(w, v[3], 96, true); }
+                else { add_limb(w, v[0], 0, false); add_limb(w, v[1], 32, true); }
+                st[1] = w[0]; st[2] = w[1];
+                if (p.op[a] == OP_SUM_DEC) st[3] = w[2];
+            }
+        }
+    }
+}
+
+// distinct keys among the first rows: one block, open addressing in shared memory
+__global__ void __launch_bounds__(1024) wide_sample_distinct_kernel(const long long* keys, const uint8_t* nulls, int n, unsigned long long* out) {
+    __shared__ unsigned long long set[4096];   // sample <= 2048 keys: load factor <= 0.5
+    __shared__ unsigned int distinct;
+    for (int i = threadIdx.x; i < 4096; i += blockDim.x) set[i] = 0;
+    if (threadIdx.x == 0) distinct = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        if (nulls && nulls[i]) continue;
+        unsigned long long k = (unsigned long long)keys[i];
+        if (k == 0) continue;
+        uint32_t h = (uint32_t)(w_fmix64(k) >> 52);
+        while (true) {
+            unsigned long long old = atomicCAS(&set[h], 0ULL, k);
+            if (old == 0) { atomicAdd(&distinct, 1u); break; }
+            if (old == k) break;
+            h = (h + 1) & 4095;
+        }
+    }
+    // rows that repeat the key of the row before them: input clustered by key (TPC-H lineitem by order key)
+    unsigned int rep = 0;
+    for (int i = threadIdx.x + 1; i < n; i += blockDim.x) rep += keys[i] == keys[i - 1] ? 1u : 0u;
+    __shared__ unsigned int repeats;
+    if (threadIdx.x == 0) repeats = 0;
+    __syncthreads();
+    if (rep) atomicAdd(&repeats, rep);
+    __syncthreads();
+    if (threadIdx.x == 0) { out[0] = distinct; out[1] = repeats; }
+}
+
+int64_t pick_cap(int64_t groups) {
+    int64_t cap = (int64_t)((double)groups / 0.55) + 1024;
+    if (cap < (1 << 16)) cap = 1 << 16;
+    return cap;
+}
+
+void alloc_table(WideTable* w, int64_t cap) {
+    PG_CHECK_STATE(cap < (1LL << 31), "hash table of %lld buckets exceeds the supported size", (long long)cap);   // GENERIC_INSUFFICIENT_RESOURCES analogue
+    w->table.alloc(w->ctx, (cap + 2) * w->bucket_words * 8);
+    memset_async(w->ctx, w->table.p, 0, w->table.bytes);
+    w->cap = cap;
+    w->max_fill = (int64_t)(cap * 0.75);
+}
+
+void grow(WideTable* w, int64_t min_groups) {
+    pg_ctx* ctx = w->ctx;
+    int64_t new_cap = pick_cap(min_groups > 2 * w->claimed ? min_groups : 2 * w->claimed);
+    if (new_cap < 2 * w->cap) new_cap = 2 * w->cap;
+    DevBuf old = std::move(w->table);
+    int64_t old_cap = w->cap;
+    alloc_table(w, new_cap);
+    PG_LAUNCH(ctx, wide_rebuild_kernel, grid_for(ctx, old_cap + 2, 256), 256, 0, old.as<unsigned long long>(), old_cap,
+              w->table.as<unsigned long long>(), new_cap, w->bucket_words);
+}
+
+}  // namespace
+
+int64_t sample_distinct_keys(pg_ctx* ctx, const DCol& key, int64_t sample, int64_t* adjacent_repeats) {
+    if (sample > 2048) sample = 2048;
+    DevBuf out(ctx, 16);
+    PG_LAUNCH(ctx, wide_sample_distinct_kernel, 1, 1024, 0, (const long long*)key.values, key.nulls, (int)sample, out.as<unsigned long long>());
+    int64_t d[2];
+    read_scalars(ctx, out.p, 2, d);
+    if (adjacent_repeats) *adjacent_repeats = d[1];
+    return d[0];
+}
+
+bool wide_supported(const std::vector<pg_agg_spec>& specs, const std::vector<pg_agg*>& aggs) {
+    if (aggs.empty() || aggs.size() > PGW_MAX_AGGS) return false;
+    for (size_t i = 0; i < aggs.size(); i++) {
+        const pg_agg* a = aggs[i];
+        const bool is32 = a->in_type == PG_INTEGER || a->in_type == PG_DATE;
+        switch (a->op) {
+            case OP_COUNT: break;
+            case OP_SUM_I64: break;
+            case OP_SUM_F64: if (is32) return false; break;
+            case OP_SUM_DEC: break;
+            default: return false;
+        }
+        (void)specs;
+    }
+    return true;
+}
+
+WideTable* wide_create(pg_ctx* ctx, const std::vector<pg_agg_spec>& specs, const std::vector<pg_agg*>& aggs, int32_t step, int64_t expected_groups) {
+    WideTable* w = new WideTable();
+    try {
+        w->ctx = ctx;
+        int words = 2, flags = 0;
+        // flag bits first (one shared word), then the 64-bit counts and the value words
+        for (size_t i = 0; i < aggs.size(); i++) {
+            const pg_agg* a = aggs[i];
+            WideAgg wa;
+            memset(&wa, 0, sizeof(wa));
+            wa.op = a->op; wa.words = a->words; wa.skip_null = a->kind != PG_AGG_COUNT ? 1 : 0;
+            const bool is32 = a->in_type == PG_INTEGER || a->in_type == PG_DATE;
+            switch (a->op) {
+                case OP_COUNT: wa.in_kind = IN_NONE; break;
+                case OP_SUM_I64: wa.in_kind = is32 ? IN_I32 : IN_I64; break;
+                case OP_SUM_F64: wa.in_kind = (a->kind == PG_AGG_AVG && a->in_type == PG_BIGINT) ? IN_I2F : IN_F64; break;
+                default: wa.in_kind = a->in_type == PG_LONG_DECIMAL ? IN_DEC128 : IN_I64;
+            }
+            // a plain sum only needs to know whether any row arrived (NULL result otherwise); partial steps ship real counts
+            wa.val_words = a->op == OP_COUNT ? 0 : a->op == OP_SUM_F64 ? 1 : wa.in_kind == IN_DEC128 ? 4 : 2;
+            wa.cnt_mode = (step == PG_STEP_SINGLE && a->kind == PG_AGG_SUM) ? 1 : 0;
+            if (wa.cnt_mode == 1) wa.flag_bit = flags++;
+            w->aggs.push_back(wa);
+        }
+        if (flags > 0) w->flag_word = words++;
+        for (WideAgg& wa : w->aggs) {
+            if (wa.cnt_mode == 0) wa.cnt_word = words++;
+            wa.val_word = words;
+            words += wa.val_words;
+        }
+        w->bucket_words = (words + 3) & ~3;
+        w->counters.alloc(ctx, 16);
+        alloc_table(w, pick_cap(expected_groups > 0 ? expected_groups : 0));
+        (void)specs;
+    } catch (...) { delete w; throw; }
+    return w;
+}
+
+bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const DCol* masks, int64_t n, int64_t row_base) {
+    pg_ctx* ctx = w->ctx;
+    if (n <= 0) return true;
+    PG_CHECK_STATE(!w->prepared, "the operator already produced output");
+    if (row_base + n >= (1LL << 32))   // limb sums are exact for < 2^32 rows per group
+        fail(PG_E_INSUFFICIENT_RESOURCES, "more than 2^32 rows in one aggregation operator instance");
+    // ---- source
+    std::string pre;
+    char buf[320];
+    // rows per thread and trip: 4 when every column allows 16-byte (4-byte for byte columns) vector loads
+    auto al = [](const void* p, uintptr_t a) { return p == nullptr || ((uintptr_t)p % a) == 0; };
+    int vec = 4;
+    if (!al(key.values, 16) || !al(key.nulls, 4)) vec = 1;
+    for (size_t i = 0; i < w->aggs.size(); i++)
+        if (!al(args_cols[i].values, 16) || !al(args_cols[i].nulls, 4) || !al(masks[i].values, 4) || !al(masks[i].nulls, 4)) vec = 1;
+    if (const char* e = getenv("PRESTOGPU_WIDE_VEC")) { if (atoi(e) == 1) vec = 1; }
+    snprintf(buf, sizeof(buf), "#define PGW_BUCKET_WORDS %d\n#define PGW_HASKEYNULL %d\n#define PGW_FLAGWORD %d\n#define PGW_VEC %d\n", w->bucket_words,
+             key.nulls ? 1 : 0, w->flag_word, vec);
+    pre += buf;
+    std::string aggs_macro = "#define PGW_AGGS(X)";
+    for (size_t i = 0; i < w->aggs.size(); i++) {
+        const WideAgg& a = w->aggs[i];
+        const DCol& m = masks[i];
+        const DCol& c = args_cols[i];
+        snprintf(buf, sizeof(buf), " X(%d, %s, %s, %d, %d, %d, %s, %d, %d, %d)", (int)i, op_name(a.op), in_name(a.in_kind), m.values ? 1 : 0,
+                 (m.values && m.nulls) ? 1 : 0, (a.skip_null && c.nulls) ? 1 : 0, a.cnt_mode == 0 ? "C64" : "FLAG", a.cnt_word, a.val_word,
+                 a.flag_bit);
+        aggs_macro += buf;
+    }
+    pre += aggs_macro + "\n";
+    // variants: [only] honours only_rows (re-run of left-out rows); [quota] bounds the claims of every block
+    JitKernel* kern[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+    auto get_kernel = [&](int only, int quota) -> JitKernel* {
+        if (!kern[only][quota]) {
+            std::string p2 = pre + (only ? "#define PGW_HASONLY 1\n" : "#define PGW_HASONLY 0\n") + (quota ? "#define PGW_QUOTA 1\n" : "#define PGW_QUOTA 0\n");
+            kern[only][quota] = jit_get(ctx, "wide:" + p2, p2 + WIDE_ARGS_SRC + WIDE_BODY_SRC, "pg_wide_agg");
+        }
+        return kern[only][quota];
+    };
+    if (!get_kernel(0, 0)) return false;
+
+    PgwArgs a;
+    memset(&a, 0, sizeof(a));
+    a.keys = (const long long*)key.values; a.key_nulls = key.nulls;
+    for (size_t i = 0; i < w->aggs.size(); i++) {
+        a.arg[i] = args_cols[i].values; a.arg_nulls[i] = args_cols[i].nulls;
+        a.mask[i] = (const unsigned char*)masks[i].values; a.mask_nulls[i] = masks[i].values ? masks[i].nulls : nullptr;
+    }
+    a.n = n; a.row_base = row_base;
+    a.counters = w->counters.as<unsigned long long>();
+    DevBuf flags[2];               // left-out markers: written by launch i, read as the row filter by launch i + 1
+    int cur = 0;
+    const uint8_t* only = nullptr;
+    int64_t pending = n;           // upper bound of the buckets the rows still to run can claim
+    const int grid = grid_for(ctx, n, WIDE_THREADS, vec, 4);
+    while (true) {
+        int64_t room = w->max_fill - w->claimed;
+        if (room < pending && room < grid * 64LL) { grow(w, w->claimed + pending); continue; }
+        int64_t quota = room >= pending ? (int64_t)0x7fffffff : room / grid;
+        if (!flags[cur].p) flags[cur].alloc(ctx, n);
+        memset_async(ctx, flags[cur].p, 0, n);
+        memset_async(ctx, w->counters.p, 0, 16);
+        a.table = w->table.as<unsigned long long>(); a.cap = w->cap; a.quota = (unsigned int)quota;
+        a.only_rows = only; a.overflow_flag = flags[cur].as<uint8_t>();
+        JitKernel* k = get_kernel(only ? 1 : 0, room >= pending ? 0 : 1);
+        if (!k) fail(PG_E_INTERNAL, "specialised kernel unavailable for the re-run: %s", ctx->jit ? ctx->jit->last_error.c_str() : "");
+        void* kargs[] = {&a};
+        jit_launch(ctx, k, "wide_agg_jit", grid, WIDE_THREADS, 0, kargs);
+        // one read-back: claims, left-out rows, and whether the two extra buckets are in use
+        copy_async(ctx, ctx->h_scalar, w->counters.p, 16, cudaMemcpyDeviceToHost);
+        copy_async(ctx, ctx->h_scalar + 2, w->table.as<unsigned long long>() + w->cap * w->bucket_words + 1, 8, cudaMemcpyDeviceToHost);
+        copy_async(ctx, ctx->h_scalar + 3, w->table.as<unsigned long long>() + (w->cap + 1) * w->bucket_words + 1, 8, cudaMemcpyDeviceToHost);
+        sync(ctx);
+        w->claimed += ctx->h_scalar[0];
+        const int64_t left_out = ctx->h_scalar[1];
+        w->null_seen = ctx->h_scalar[2] != 0;
+        w->zero_seen = ctx->h_scalar[3] != 0;
+        if (left_out == 0) break;
+        // some block ran out of quota: grow, then re-run exactly the rows that were left out
+        grow(w, w->claimed + left_out);
+        pending = left_out;
+        only = flags[cur].as<uint8_t>();
+        cur ^= 1;
+    }
+    return true;
+}
+
+void wide_prepare_output(WideTable* w, pg_groupby* gb, const std::vector<pg_agg*>& aggs, int64_t total_rows) {
+    pg_ctx* ctx = w->ctx;
+    if (w->prepared) return;
+    const int64_t groups = w->groups();
+    const int64_t nwords = (total_rows + 31) / 32 + 1;
+    DevBuf bitmap(ctx, nwords * 4), prefix(ctx, nwords * 4);
+    memset_async(ctx, bitmap.p, 0, nwords * 4);
+    const int grid = grid_for(ctx, w->cap + 2, 256);
+    PG_LAUNCH(ctx, wide_mark_first_rows_kernel, grid, 256, 0, w->table.as<unsigned long long>(), w->cap, w->bucket_words, bitmap.as<uint32_t>());
+    const int64_t ntiles = num_tiles(nwords);
+    DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+    PG_LAUNCH(ctx, wide_popc_tiles_kernel, (int)ntiles, SCAN_THREADS, 0, bitmap.as<uint32_t>(), nwords, tiles.as<Pair64>());
+    scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, tiles.as<Pair64>() + ntiles);
+    PG_LAUNCH(ctx, wide_word_prefix_kernel, (int)ntiles, SCAN_THREADS, 0, bitmap.as<uint32_t>(), nwords, tiles.as<Pair64>(), prefix.as<uint32_t>());
+    // dense destinations
+    gb->values_by_group.grow(ctx, (groups + 2) * 8, 0);
+    GatherPlan p;
+    memset(&p, 0, sizeof(p));
+    p.naggs = (int32_t)w->aggs.size(); p.bw = w->bucket_words; p.flag_word = w->flag_word;
+    for (size_t i = 0; i < w->aggs.size(); i++) {
+        agg_ensure_capacity(aggs[i], groups);
+        p.op[i] = w->aggs[i].op; p.in_kind[i] = w->aggs[i].in_kind;
+        p.cnt_mode[i] = w->aggs[i].cnt_mode; p.cnt_word[i] = w->aggs[i].cnt_word; p.val_word[i] = w->aggs[i].val_word;
+        p.flag_bit[i] = w->aggs[i].flag_bit; p.words[i] = w->aggs[i].words;
+        p.state[i] = aggs[i]->state.as<unsigned long long>();
+    }
+    DevBuf bucket_of_group(ctx, (groups + 1) * 4);
+    PG_LAUNCH(ctx, wide_number_buckets_kernel, grid, 256, 0, w->table.as<unsigned long long>(), w->cap, w->bucket_words, bitmap.as<uint32_t>(),
+              prefix.as<uint32_t>(), bucket_of_group.as<uint32_t>(), gb->slots.as<Slot>() + gb->cap);
+    if (groups > 0)
+        PG_LAUNCH(ctx, wide_gather_kernel, grid_for(ctx, groups, 256), 256, 0, w->table.as<unsigned long long>(), w->cap, p,
+                  bucket_of_group.as<uint32_t>(), groups, gb->values_by_group.as<int64_t>());
+    gb->groups = groups;
+    while (gb->groups >= max_fill_075(gb->ref_capacity) && gb->ref_capacity < (1LL << 30)) gb->ref_capacity *= 2;
+    sync(ctx);
+    w->prepared = true;
+    w->table.release();
+}
+
+}  // namespace pg

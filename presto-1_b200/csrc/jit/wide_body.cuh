@@ -1,0 +1,248 @@
+// wide_body.cuh — body of the run-time specialised fused GROUP BY kernel for MANY groups on one BIGINT key
+// ("hash-then-update", BigintGroupByHash.putIfAbsent :213-260 + the generated GroupedAccumulator.addInput loops in ONE pass).
+//
+// The hash table holds the partial aggregation state inside the bucket of its key, so a row costs one random access:
+//   bucket = PGW_BUCKET_WORDS u64 words (a multiple of 4 = whole 32-byte sectors)
+//     word 0  the key (0 = free; key 0 and the null key live in two extra buckets behind the table)
+//     word 1  ~(operator-wide index of the first row that carried the key), maintained with atomicMax: first-seen
+//             order is recovered when the output is built (hashagg_wide.cu), no group ids exist while rows stream in
+//     word 2.. state words of the aggregates (counts, 32-bit-limb integer sums, double sums), zero = identity,
+//             so a zero-filled table is an empty table
+// Claims are atomicCAS on word 0; every state update is an atomic on the same line (resolved in L2).
+// The prelude defines PGW_BUCKET_WORDS, PGW_HASKEYNULL, PGW_HASONLY, PGW_QUOTA, PGW_FLAGWORD, PGW_VEC (rows per thread and trip: 1 or 4) and
+//   PGW_AGGS(X)  X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)
+//     OP in {CNT, SUMI64, SUMF64, SUMDEC}; IN in {NONE, I64, I32, F64, I2F, DEC128}; CNTMODE in {C64, FLAG}
+
+typedef unsigned long long u64;
+typedef long long i64;
+typedef unsigned int u32;
+typedef unsigned char u8;
+
+#define PGW_CAT2(a, b) a##b
+#define PGW_CAT(a, b) PGW_CAT2(a, b)
+
+__device__ __forceinline__ u64 fmix64(u64 k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33;
+    return k;
+}
+
+// ---- integer sums are kept as sums of 32-bit limbs, each limb in its own 64-bit word: every update is a fire-and-forget
+// red.add (no carry to propagate, so no atomic has to return a value and no thread waits for L2); the top limb is signed.
+// A limb sum is exact for up to 2^32 rows per group; the limbs are recombined when the output is built (hashagg_wide.cu).
+__device__ __forceinline__ void red_add(u64* p, u64 v) { atomicAdd(p, v); }   // result unused -> RED
+// ---- vector loads of V consecutive rows (read-only path)
+template <int V> __device__ __forceinline__ void ld_u64(const void* base, i64 row, u64 (&o)[V]) {
+    const u64* p = (const u64*)base + row;
+    if constexpr (V == 1) o[0] = __ldg(p);
+    else {
+#pragma unroll
+        for (int i = 0; i < V; i += 2) { const ulonglong2 t = __ldg((const ulonglong2*)(p + i)); o[i] = t.x; o[i + 1] = t.y; }
+    }
+}
+template <int V> __device__ __forceinline__ void ld_i32(const void* base, i64 row, u64 (&o)[V]) {
+    const int* p = (const int*)base + row;
+    if constexpr (V == 1) o[0] = (u64)(i64)__ldg(p);
+    else { const int4 t = __ldg((const int4*)p); o[0] = (u64)(i64)t.x; o[1] = (u64)(i64)t.y; o[2] = (u64)(i64)t.z; o[3] = (u64)(i64)t.w; }
+}
+template <int V> __device__ __forceinline__ void ld_u8(const u8* base, i64 row, u32 (&o)[V]) {
+    const u8* p = base + row;
+    if constexpr (V == 1) o[0] = __ldg(p);
+    else { const u32 t = __ldg((const u32*)p); o[0] = t & 0xffu; o[1] = (t >> 8) & 0xffu; o[2] = (t >> 16) & 0xffu; o[3] = t >> 24; }
+}
+template <int V> __device__ __forceinline__ void ld_u128(const void* base, i64 row, u64 (&lo)[V], u64 (&hi)[V]) {
+    const ulonglong2* p = (const ulonglong2*)base + row;
+#pragma unroll
+    for (int i = 0; i < V; i++) { const ulonglong2 t = __ldg(p + i); lo[i] = t.x; hi[i] = t.y; }
+}
+
+// ---- per aggregate and input kind.  A thread owns V consecutive rows; rows with the same key (TPC-H lineitem arrives
+// clustered by order key) are merged in registers first, so one compare-and-swap and one set of atomics serve the run.
+//   LD    load the V arguments                  ACC  per-row partials: 128-bit integer (lo, hi) or double, 0 when the row does not count
+//   MERGE fold row j - 1 into row j             EMIT atomics of a run's last row             SOLO not merged: each row's own atomics
+#define PGW_LD_NONE(a)
+#define PGW_LD_I64(a) u64 PGW_CAT(av, a)[V]; ld_u64<V>(args.arg[a], r0, PGW_CAT(av, a));
+#define PGW_LD_I32(a) u64 PGW_CAT(av, a)[V]; ld_i32<V>(args.arg[a], r0, PGW_CAT(av, a));
+#define PGW_LD_F64(a) PGW_LD_I64(a)
+#define PGW_LD_I2F(a) PGW_LD_I64(a)
+#define PGW_LD_DEC128(a) u64 PGW_CAT(av, a)[V]; u64 PGW_CAT(aw, a)[V]; ld_u128<V>(args.arg[a], r0, PGW_CAT(av, a), PGW_CAT(aw, a));
+
+#define PGW_ACC_INT(a) u64 PGW_CAT(slo, a)[V]; i64 PGW_CAT(shi, a)[V]; _Pragma("unroll") for (int j = 0; j < V; j++) {        \
+        PGW_CAT(slo, a)[j] = PGW_CAT(ok, a)[j] ? PGW_CAT(av, a)[j] : 0; PGW_CAT(shi, a)[j] = PGW_CAT(ok, a)[j] ? (i64)PGW_CAT(av, a)[j] >> 63 : 0; }
+#define PGW_ACC_CNT_NONE(a)
+#define PGW_ACC_SUMI64_I64(a) PGW_ACC_INT(a)
+#define PGW_ACC_SUMI64_I32(a) PGW_ACC_INT(a)
+#define PGW_ACC_SUMDEC_I64(a) PGW_ACC_INT(a)
+#define PGW_ACC_SUMF64_F64(a) double PGW_CAT(sd, a)[V]; _Pragma("unroll") for (int j = 0; j < V; j++) PGW_CAT(sd, a)[j] = PGW_CAT(ok, a)[j] ? __longlong_as_double((i64)PGW_CAT(av, a)[j]) : 0.0;
+#define PGW_ACC_SUMF64_I2F(a) double PGW_CAT(sd, a)[V]; _Pragma("unroll") for (int j = 0; j < V; j++) PGW_CAT(sd, a)[j] = PGW_CAT(ok, a)[j] ? (double)(i64)PGW_CAT(av, a)[j] : 0.0;
+#define PGW_ACC_SUMDEC_DEC128(a)
+
+#define PGW_MERGE_INT(a) { const u64 t_ = PGW_CAT(slo, a)[j] + PGW_CAT(slo, a)[j - 1];                                       \
+        PGW_CAT(shi, a)[j] += PGW_CAT(shi, a)[j - 1] + (t_ < PGW_CAT(slo, a)[j - 1] ? 1 : 0); PGW_CAT(slo, a)[j] = t_; }
+#define PGW_MERGE_CNT_NONE(a)
+#define PGW_MERGE_SUMI64_I64(a) PGW_MERGE_INT(a)
+#define PGW_MERGE_SUMI64_I32(a) PGW_MERGE_INT(a)
+#define PGW_MERGE_SUMDEC_I64(a) PGW_MERGE_INT(a)
+#define PGW_MERGE_SUMF64_F64(a) PGW_CAT(sd, a)[j] += PGW_CAT(sd, a)[j - 1];
+#define PGW_MERGE_SUMF64_I2F(a) PGW_MERGE_SUMF64_F64(a)
+#define PGW_MERGE_SUMDEC_DEC128(a)
+
+// limbs of a 128-bit two's complement partial sum (lo, hi): its low 32 bits, and the rest as one signed quantity
+#define PGW_EMIT_LIMBS(a, W) { const u64 l0_ = PGW_CAT(slo, a)[j] & 0xffffffffULL;                                       \
+        const u64 l1_ = (PGW_CAT(slo, a)[j] >> 32) | ((u64)PGW_CAT(shi, a)[j] << 32);                                    \
+        if (l0_) red_add(b + (W), l0_); if (l1_) red_add(b + (W) + 1, l1_); }
+#define PGW_EMIT_CNT_NONE(a, W)
+#define PGW_EMIT_SUMI64_I64(a, W) PGW_EMIT_LIMBS(a, W)
+#define PGW_EMIT_SUMI64_I32(a, W) PGW_EMIT_LIMBS(a, W)
+#define PGW_EMIT_SUMDEC_I64(a, W) PGW_EMIT_LIMBS(a, W)
+#define PGW_EMIT_SUMF64_F64(a, W) atomicAdd((double*)(b + (W)), PGW_CAT(sd, a)[j]);
+#define PGW_EMIT_SUMF64_I2F(a, W) PGW_EMIT_SUMF64_F64(a, W)
+#define PGW_EMIT_SUMDEC_DEC128(a, W)
+
+#define PGW_SOLO_CNT_NONE(a, W)
+#define PGW_SOLO_SUMI64_I64(a, W)
+#define PGW_SOLO_SUMI64_I32(a, W)
+#define PGW_SOLO_SUMDEC_I64(a, W)
+#define PGW_SOLO_SUMF64_F64(a, W)
+#define PGW_SOLO_SUMF64_I2F(a, W)
+#define PGW_SOLO_SUMDEC_DEC128(a, W) if (PGW_CAT(ok, a)[j]) {                                                \
+        u64 a0 = PGW_CAT(av, a)[j], a1 = PGW_CAT(aw, a)[j] & 0x7fffffffffffffffULL;                          \
+        if ((i64)PGW_CAT(aw, a)[j] < 0) { a0 = ~a0; a1 = ~a1; a0 += 1; if (a0 == 0) a1 += 1; }               \
+        const u64 l0_ = a0 & 0xffffffffULL, l1_ = a0 >> 32, l2_ = a1 & 0xffffffffULL, l3_ = (u64)((i64)a1 >> 32); \
+        if (l0_) red_add(b + (W), l0_); if (l1_) red_add(b + (W) + 1, l1_);                                  \
+        if (l2_) red_add(b + (W) + 2, l2_); if (l3_) red_add(b + (W) + 3, l3_); }
+
+#define PGW_CNT_C64(a, W, BIT) red_add(b + (W), (u64)PGW_CAT(cn, a)[j]);
+#define PGW_CNT_FLAG(a, W, BIT) flag_bits |= 1ULL << (BIT);
+
+// Claim quota.  PGW_QUOTA == 0: the host made sure every row of the launch could claim a bucket, nothing to reserve.
+// PGW_QUOTA == 1 (the table is nearly full): a block-wide counter in shared memory bounds the block's claims.
+__device__ __forceinline__ bool reserve(u32* s_claims, u32 quota) {
+#if PGW_QUOTA
+    if (atomicAdd(s_claims, 1u) < quota) return true;
+    atomicSub(s_claims, 1u);
+    return false;
+#else
+    return true;
+#endif
+}
+__device__ __forceinline__ void unreserve(u32* s_claims) {
+#if PGW_QUOTA
+    atomicSub(s_claims, 1u);
+#endif
+}
+
+// V consecutive rows of one thread
+template <int V>
+__device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, u32* s_claims, u64& left_out, u64& claims) {
+    const i64 cap = args.cap;
+    // ---- loads
+    u64 key[V];
+    ld_u64<V>(args.keys, r0, key);
+    u32 kn[V], only[V];
+    (void)kn; (void)only;
+    if (PGW_HASKEYNULL) ld_u8<V>(args.key_nulls, r0, kn);
+    if (PGW_HASONLY) ld_u8<V>(args.only_rows, r0, only);
+#define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                               \
+    PGW_LD_##IN(a)                                                                                                            \
+    u32 PGW_CAT(m0, a)[V], PGW_CAT(m1, a)[V], PGW_CAT(m2, a)[V];                                                               \
+    (void)PGW_CAT(m0, a); (void)PGW_CAT(m1, a); (void)PGW_CAT(m2, a);                                                          \
+    if (HASMASK) ld_u8<V>(args.mask[a], r0, PGW_CAT(m0, a));                                                                  \
+    if (HASMASKNULLS) ld_u8<V>(args.mask_nulls[a], r0, PGW_CAT(m1, a));                                                       \
+    if (HASARGNULLS) ld_u8<V>(args.arg_nulls[a], r0, PGW_CAT(m2, a));
+    PGW_AGGS(PG_X)
+#undef PG_X
+    bool valid[V], isnull[V];
+#pragma unroll
+    for (int j = 0; j < V; j++) { valid[j] = !PGW_HASONLY || only[j] != 0; isnull[j] = PGW_HASKEYNULL && kn[j] != 0; }
+#define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                               \
+    bool PGW_CAT(ok, a)[V]; u32 PGW_CAT(cn, a)[V];                                                                            \
+    _Pragma("unroll") for (int j = 0; j < V; j++) {                                                                           \
+        PGW_CAT(ok, a)[j] = valid[j] && (!HASMASK || PGW_CAT(m0, a)[j] != 0) && (!HASMASKNULLS || PGW_CAT(m1, a)[j] == 0) &&  \
+                            (!HASARGNULLS || PGW_CAT(m2, a)[j] == 0);                                                         \
+        PGW_CAT(cn, a)[j] = PGW_CAT(ok, a)[j] ? 1u : 0u; }                                                                    \
+    PGW_ACC_##OP##_##IN(a)
+    PGW_AGGS(PG_X)
+#undef PG_X
+    // ---- merge runs of equal keys: row j absorbs row j - 1, the last row of a run carries the totals and the run's first row
+    i64 first_row[V];
+    bool live[V];
+#pragma unroll
+    for (int j = 0; j < V; j++) { first_row[j] = r0 + j; live[j] = valid[j]; }
+#pragma unroll
+    for (int j = 1; j < V; j++) {
+        if (valid[j] && valid[j - 1] && isnull[j] == isnull[j - 1] && (isnull[j] || key[j] == key[j - 1])) {
+            live[j - 1] = false;
+            first_row[j] = first_row[j - 1];
+#define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT) \
+            PGW_CAT(cn, a)[j] += PGW_CAT(cn, a)[j - 1]; PGW_MERGE_##OP##_##IN(a)
+            PGW_AGGS(PG_X)
+#undef PG_X
+        }
+    }
+    // ---- one compare-and-swap per run, all of a thread's in flight together.  A free bucket is claimed and a bucket that
+    // already holds the key is recognised in ONE round trip to L2; nothing else of the bucket is ever read.
+    u64* bp[V];
+    u32 idx[V];
+    u64 old[V];
+    bool reserved[V];
+#pragma unroll
+    for (int j = 0; j < V; j++) {
+        bp[j] = nullptr; idx[j] = 0; old[j] = 1; reserved[j] = false;
+        if (!live[j]) continue;
+        if (isnull[j] || key[j] == 0) { bp[j] = args.table + (cap + (isnull[j] ? 0 : 1)) * PGW_BUCKET_WORDS; continue; }
+        idx[j] = (u32)(((fmix64(key[j]) >> 32) * (u64)cap) >> 32);
+        reserved[j] = reserve(s_claims, args.quota);                   // a claim needs room in the block's quota
+        u64* bk = args.table + (i64)idx[j] * PGW_BUCKET_WORDS;
+        old[j] = reserved[j] ? atomicCAS(bk, 0ULL, key[j]) : __ldcg(bk);
+    }
+#pragma unroll
+    for (int j = 0; j < V; j++) {
+        if (!live[j] || bp[j] != nullptr) continue;
+        while (true) {                                                   // first step already issued above
+            if (reserved[j] && old[j] != 0) unreserve(s_claims);
+            if (reserved[j] && old[j] == 0) claims++;
+            if (old[j] == key[j] || (reserved[j] && old[j] == 0)) { bp[j] = args.table + (i64)idx[j] * PGW_BUCKET_WORDS; break; }
+            if (old[j] == 0) break;                                      // free bucket but no quota left: the run is left out
+            idx[j] = idx[j] + 1 == (u32)cap ? 0u : idx[j] + 1;
+            reserved[j] = reserve(s_claims, args.quota);
+            u64* bk = args.table + (i64)idx[j] * PGW_BUCKET_WORDS;
+            old[j] = reserved[j] ? atomicCAS(bk, 0ULL, key[j]) : __ldcg(bk);
+        }
+    }
+    // rows absorbed by a later row share its bucket
+#pragma unroll
+    for (int j = V - 2; j >= 0; j--) if (valid[j] && !live[j]) bp[j] = bp[j + 1];
+    // ---- atomics
+#pragma unroll
+    for (int j = 0; j < V; j++) {
+        u64* b = bp[j];
+        if (valid[j] && b == nullptr) { left_out++; args.overflow_flag[r0 + j] = 1; }
+        if (b == nullptr) continue;
+        u64 flag_bits = 0;
+        if (live[j]) atomicMax(b + 1, ~(u64)(args.row_base + first_row[j]));   // smallest row index wins (stored inverted, zero = never seen)
+#define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                  \
+        if (live[j] && PGW_CAT(cn, a)[j]) { PGW_CNT_##CNTMODE(a, CNTWORD, FLAGBIT) PGW_EMIT_##OP##_##IN(a, VALWORD) }    \
+        if (valid[j]) { PGW_SOLO_##OP##_##IN(a, VALWORD) }
+        PGW_AGGS(PG_X)
+#undef PG_X
+        if (PGW_FLAGWORD >= 0 && flag_bits) atomicOr(b + (PGW_FLAGWORD >= 0 ? PGW_FLAGWORD : 0), flag_bits);
+    }
+}
+
+extern "C" __global__ void __launch_bounds__(256) pg_wide_agg(const PgwArgs args) {
+    __shared__ u32 s_claims;
+    if (threadIdx.x == 0) s_claims = 0;
+    __syncthreads();
+    u64 left_out = 0, claims = 0;
+    const i64 n = args.n;
+    const i64 stride = (i64)gridDim.x * blockDim.x * PGW_VEC;
+    for (i64 r0 = ((i64)blockIdx.x * blockDim.x + threadIdx.x) * PGW_VEC; r0 + PGW_VEC <= n; r0 += stride)
+        process_rows<PGW_VEC>(args, r0, &s_claims, left_out, claims);
+    if (PGW_VEC > 1 && blockIdx.x == 0 && threadIdx.x == 0)
+        for (i64 r0 = n - n % PGW_VEC; r0 < n; r0++) process_rows<1>(args, r0, &s_claims, left_out, claims);
+    // ---- per-block totals
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { left_out += __shfl_down_sync(0xffffffffu, left_out, d); claims += __shfl_down_sync(0xffffffffu, claims, d); }
+    if ((threadIdx.x & 31) == 0 && left_out) atomicAdd(args.counters + 1, left_out);
+    if ((threadIdx.x & 31) == 0 && claims) atomicAdd(args.counters, claims);
+}

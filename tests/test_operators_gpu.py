@@ -255,3 +255,106 @@ def test_fused_low_cardinality_page_with_late_and_unpackable_keys(pgpu, key_kind
                 assert x == pytest.approx(y, rel=1e-12)
             else:
                 assert x == y
+
+
+def _oracle_rows(P, key_block, agg_pages, aggs, step_final=True):
+    """Oracle result in group-id (= first-seen) order: list of tuples (key, agg0, agg1, ...)."""
+    ogb = O.OracleGroupBy([P.BIGINT], 10_000)
+    accs = [O.OracleAccumulator(a.kind, a.in_type) for a in aggs]
+    for blocks in agg_pages:
+        ids = ogb.get_group_ids([blocks[0]])
+        g = ogb.group_count()
+        for a, oa in zip(aggs, accs):
+            oa.add_input(ids, g, blocks[a.input_channel] if a.input_channel >= 0 else None, blocks[a.mask_channel] if a.mask_channel >= 0 else None)
+    g = ogb.group_count()
+    keys, _ = ogb.export(with_hash=False)
+    cols = [keys[0].to_list()]
+    for oa in accs:
+        rc, out, _ = oa.evaluate(0, g, step_final)
+        assert rc == 0
+        cols += [o.to_list() for o in out]
+    return [tuple(c[i] for c in cols) for i in range(g)]
+
+
+def _assert_rows_equal(got, want):
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert len(a) == len(b)
+        for x, y in zip(a, b):
+            if isinstance(x, float) and isinstance(y, float):
+                assert x == pytest.approx(y, rel=1e-12, abs=1e-300)     # double sums: order dependent, tolerance of north_star
+            else:
+                assert x == y
+
+
+@pytest.mark.parametrize("expected_groups", [100, 400_000])
+@pytest.mark.parametrize("clustered", [False, True])
+def test_many_groups_bigint_key_matches_oracle_in_first_seen_order(pgpu, monkeypatch, expected_groups, clustered):
+    """cfg3 shape: GROUP BY one BIGINT key with many groups takes the bucket-resident-state path (hashagg_wide.cu).
+    Output order must be the reference's first-seen group-id order, across pages; key 0, the null key, negative values,
+    null arguments, a mask, long decimals and table growth (expected_groups=100) are all in play."""
+    P = pgpu
+    rng = np.random.default_rng(21)
+    n, distinct = 700_000, 180_000
+    universe = np.concatenate([np.array([0, -1, 2**62, -2**63 + 5], dtype=np.int64), rng.integers(-10**12, 10**12, distinct).astype(np.int64)])
+    keys = universe[rng.integers(0, len(universe), n)]
+    if clustered:
+        keys = np.repeat(keys[: n // 4 + 1], 4)[:n]
+    knull = (rng.random(n) < 0.001).astype(np.uint8)
+    dec = rng.integers(-10**15, 10**15, n).astype(np.int64)
+    dnull = (rng.random(n) < 0.05).astype(np.uint8)
+    dbl = rng.random(n) * 1e6            # positive like TPC-H prices: the 1e-12 bound is relative to the sum, not to cancellation residue
+    big = rng.integers(-2**40, 2**40, n).astype(np.int64)
+    long_dec = [int(x) * 10**20 * (1 if i % 3 else -1) for i, x in enumerate(rng.integers(1, 10**9, n))]
+    mask = (rng.random(n) < 0.8).astype(np.uint8)
+    def page(lo, hi):
+        return [P.Block.long_array(keys[lo:hi], knull[lo:hi]), P.Block.long_array(dec[lo:hi], dnull[lo:hi], P.SHORT_DECIMAL),
+                P.Block.double_array(dbl[lo:hi]), P.Block.long_array(big[lo:hi]), P.Block.int128_array(long_dec[lo:hi]),
+                P.Block.byte_array(mask[lo:hi])]
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2),
+            P.AggregatorFactory(P.AGG_AVG, P.BIGINT, 3), P.AggregatorFactory(P.AGG_SUM, P.LONG_DECIMAL, 4, 5), P.AggregatorFactory(P.AGG_SUM, P.BIGINT, 3),
+            P.AggregatorFactory(P.AGG_COUNT_COL, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_AVG, P.SHORT_DECIMAL, 1, 5)]
+    bounds = [(0, 400_000), (400_000, 400_007), (400_007, n)]
+    pages = [page(lo, hi) for lo, hi in bounds]
+    monkeypatch.setenv("PRESTOGPU_WIDE", "1")      # clustered input would otherwise stay on the general path
+    op = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=expected_groups)
+    op.ctx.kernel_report(reset=True)
+    op.ctx.set_timing(True)
+    for i, blocks in enumerate(pages):
+        pg_ = P.Page(*blocks)
+        op.add_input(pg_.to_device() if i % 2 == 0 else pg_)
+    op.finish()
+    seen = op.ctx.kernel_report(reset=True)
+    op.ctx.set_timing(False)
+    assert "wide_agg_jit" in seen, "the many-groups path was not taken: %s" % sorted(seen)
+    got = rows_of(drain(op))
+    want = _oracle_rows(P, None, pages, aggs)
+    _assert_rows_equal(got, want)
+    assert op.get_group_count() == len(want)
+
+
+def test_many_groups_partial_then_final(pgpu):
+    """PARTIAL step on the many-groups path ships real counts in its intermediate rows; FINAL merges them."""
+    P = pgpu
+    rng = np.random.default_rng(22)
+    n = 500_000
+    keys = rng.integers(1, 150_000, n).astype(np.int64)
+    dec = rng.integers(-10**9, 10**9, n).astype(np.int64)
+    dbl = rng.random(n)
+    blocks = [P.Block.long_array(keys), P.Block.long_array(dec, None, P.SHORT_DECIMAL), P.Block.double_array(dbl)]
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_AVG, P.DOUBLE, 2)]
+    part = P.HashAggregationOperator([P.BIGINT], [0], P.PARTIAL, aggs, max_partial_memory=1 << 40)
+    part.add_input(P.Page(*blocks).to_device())
+    part.finish()
+    inter = drain(part)
+    want_inter = _oracle_rows(P, None, [blocks], aggs, step_final=False)
+    _assert_rows_equal(rows_of(inter), want_inter)
+    fin_aggs, ch = [], 1
+    for a in aggs:
+        fin_aggs.append(P.AggregatorFactory(a.kind, a.in_type, ch))
+        ch += len(P.intermediate_types(a.kind, a.in_type))
+    final = P.HashAggregationOperator([P.BIGINT], [0], P.FINAL, fin_aggs)
+    for p in inter:
+        final.add_input(p)
+    final.finish()
+    _assert_rows_equal(rows_of(drain(final)), _oracle_rows(P, None, [blocks], aggs))

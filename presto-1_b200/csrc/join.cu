@@ -1,4 +1,6 @@
 // join.cu — join build (PagesIndex + PagesHash + ArrayPositionLinks) and probe (JoinProbe + LookupJoinOperator emit).
+#include <stdlib.h>
+
 #include "join.h"
 
 namespace pg {
@@ -156,6 +158,78 @@ __global__ void __launch_bounds__(J_THREADS) j_build_kernel(JSlot* slots, int64_
     if (dup) *has_dups = 1;
 }
 
+// single BIGINT key: four rows per thread in flight (their first slot reads are issued together), compare-and-swap only on
+// slots seen free, count/head maintained with fire-and-forget atomics.  Duplicate keys are
+// detected without a returning atomic: they exist iff fewer slots were claimed than rows inserted.
+__global__ void __launch_bounds__(J_THREADS) j_build_fast_kernel(JSlot* slots, int64_t cap, const int64_t* __restrict__ keys,
+                                                                 const uint8_t* __restrict__ nulls, int64_t rows, int32_t* row_slot,
+                                                                 unsigned long long* meta) {
+    const int R = 4;
+    const int64_t mask = cap - 1;
+    const int64_t threads = (int64_t)gridDim.x * blockDim.x;
+    unsigned long long claims = 0, inserted = 0;
+    bool special_dup = false;
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base < rows; base += threads * R) {
+        unsigned long long key[R], old[R];
+        int64_t p[R];
+        bool valid[R];
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const int64_t i = base + k * threads;
+            valid[k] = i < rows && !(nulls != nullptr && nulls[i] != 0);          // PagesHash.java:94-96
+            key[k] = valid[k] ? (unsigned long long)keys[i] : 0ULL;
+        }
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            p[k] = -1; old[k] = 0;
+            if (!valid[k]) continue;
+            if (key[k] == EMPTY_KEY) { p[k] = cap; continue; }
+            p[k] = (int64_t)(fmix64(key[k]) & (uint64_t)mask);
+            old[k] = __ldcg(&slots[p[k]].word);      // plain read first: an atomic on a sector that is not in L2 yet is far slower
+        }
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            if (!valid[k]) continue;
+            if (p[k] == cap) {
+                if (atomicAdd(&slots[cap].count, 1) > 0) special_dup = true;
+            } else {
+                bool claimed = false;
+                while (true) {
+                    if (old[k] == key[k]) break;
+                    if (old[k] == EMPTY_KEY) {
+                        old[k] = atomicCAS(&slots[p[k]].word, EMPTY_KEY, key[k]);
+                        if (old[k] == EMPTY_KEY) { claimed = true; break; }
+                        continue;                     // lost the race: look at what is there now
+                    }
+                    p[k] = (p[k] + 1) & mask;
+                    old[k] = __ldcg(&slots[p[k]].word);
+                }
+                if (claimed) claims++;
+                inserted++;
+                atomicAdd(&slots[p[k]].count, 1);
+            }
+            const int64_t i = base + k * threads;
+            atomicMax(&slots[p[k]].head, (int32_t)i);
+            row_slot[i] = (int32_t)p[k];
+        }
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const int64_t i = base + k * threads;
+            if (i < rows && !valid[k]) row_slot[i] = -1;
+        }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        claims += __shfl_down_sync(0xffffffffu, claims, d);
+        inserted += __shfl_down_sync(0xffffffffu, inserted, d);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (claims) atomicAdd(meta + 4, claims);       // words 0..3 of meta belong to the duplicate flag and the segment sort
+        if (inserted) atomicAdd(meta + 5, inserted);
+    }
+    if (special_dup) *(int*)meta = 1;
+}
+
 // ------------------------------------------------------------------ duplicate keys: CSR segments in descending row order
 __global__ void __launch_bounds__(SCAN_THREADS) j_seg_count_kernel(const JSlot* slots, int64_t nslots, Pair64* tile_sums) {
     __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
@@ -305,6 +379,89 @@ __global__ void __launch_bounds__(SCAN_THREADS) j_probe_emit_kernel(ProbeArgs a,
     }
 }
 
+// ---- single BIGINT join key (BigintPagesHash-like fast path).  Probe pages usually arrive clustered by key (lineitem by
+// order key): a run of adjacent lanes with the same key probes once (its first lane) and shares the answer by shuffle, so
+// the random slot reads shrink by the run length.  The count pass stores per probe row either the build position itself
+// (exactly one match: the emit pass then needs no table access at all), -1 (no match), or -(slot + 2) (several matches).
+__global__ void __launch_bounds__(SCAN_THREADS) j_probe_count_fast_kernel(ProbeArgs a, const int64_t* __restrict__ keys, const uint8_t* __restrict__ nulls,
+                                                                          Pair64* tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    const int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    const int lane = threadIdx.x & 31;
+    const int64_t mask = a.cap - 1;
+    Pair64 acc{0, 0};
+#pragma unroll 2
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        const int64_t row = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        const bool in_range = row < a.n;
+        const bool valid = in_range && !a.build_empty && !(nulls != nullptr && nulls[row] != 0);   // JoinProbe.java:109-116
+        const unsigned long long key = valid ? (unsigned long long)keys[row] : 0ULL;
+        const unsigned long long prev = __shfl_up_sync(0xffffffffu, key, 1);
+        const int pv = __shfl_up_sync(0xffffffffu, valid ? 1 : 0, 1);
+        const bool start = lane == 0 || pv != (valid ? 1 : 0) || prev != key;
+        const unsigned starts = __ballot_sync(0xffffffffu, start);
+        const int leader = 31 - __clz(starts & (0xffffffffu >> (31 - lane)));
+        int code = -1, c = 0;
+        if (valid && lane == leader) {
+            int64_t p = key == EMPTY_KEY ? a.cap : (int64_t)(fmix64(key) & (uint64_t)mask);
+            while (true) {
+                const int4 sv = __ldg((const int4*)(a.slots + p));        // {word lo, word hi, count, head}
+                const unsigned long long w = ((unsigned long long)(uint32_t)sv.y << 32) | (uint32_t)sv.x;
+                if (w == key) {
+                    c = sv.z;
+                    code = c == 1 ? sv.w : (c > 1 ? -(int)(p + 2) : -1);
+                    break;
+                }
+                if (w == EMPTY_KEY || p == a.cap) break;
+                p = (p + 1) & mask;
+            }
+        }
+        __syncwarp();
+        code = __shfl_sync(0xffffffffu, code, leader);
+        c = __shfl_sync(0xffffffffu, c, leader);
+        if (in_range) {
+            if (!valid) { code = -1; c = 0; }
+            a.probe_slot[row] = code;
+            if (c == 0 && a.join_type == 1) c = 1;   // PROBE_OUTER: appendNullForBuild (LookupJoinOperator.java:354-361)
+            acc.a += c;
+        }
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) j_probe_emit_fast_kernel(ProbeArgs a, const Pair64* tile_prefix, int32_t* out_probe,
+                                                                         int64_t* out_build) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    const int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 run = tile_prefix[blockIdx.x];
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        const int64_t row = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        Pair64 v{0, 0};
+        int code = -1, c = 0;
+        int64_t s = -1;
+        if (row < a.n) {
+            code = a.probe_slot[row];
+            if (code >= 0) c = 1;
+            else if (code < -1) { s = -(int64_t)code - 2; c = a.slots[s].count; }
+            v.a = (c == 0 && a.join_type == 1) ? 1 : c;
+        }
+        Pair64 total;
+        Pair64 ex = block_exclusive_scan(v, smem, &total);
+        if (v.a) {
+            const int64_t o = run.a + ex.a;
+            if (c == 0) { out_probe[o] = (int32_t)row; out_build[o] = -1; }
+            else if (c == 1) { out_probe[o] = (int32_t)row; out_build[o] = code; }
+            else {
+                const int32_t* seg = a.seg_rows + a.seg_off[s];
+                for (int k = 0; k < c; k++) { out_probe[o + k] = (int32_t)row; out_build[o + k] = seg[k]; }
+            }
+        }
+        run = run + total;
+    }
+}
+
 // ------------------------------------------------------------------ gather (LookupSource.appendTo / PagesHashStrategy.appendTo)
 __global__ void j_gather_fixed_kernel(DCol src, const int64_t* pos, int64_t n, void* out_values, uint8_t* out_nulls) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -396,11 +553,20 @@ static void lookup_build(pg_lookup* ls) {
     int has_hash = 0;
     if (ls->hash_channel >= 0 && !ls->bigint_fast) { hc = ls->cols[ls->hash_channel].view(); has_hash = 1; }
     int* d_has_dups = ls->meta.as<int>();
-    PG_LAUNCH(ctx, j_build_kernel, grid_for(ctx, rows, J_THREADS), J_THREADS, 0, ls->slots.as<JSlot>(), ls->cap, build, hc, has_hash, rows,
-              row_slot.as<int32_t>(), d_has_dups);
-    int64_t flag;
-    read_scalars(ctx, d_has_dups, 1, &flag);
-    ls->has_dups = (flag & 0xffffffff) != 0;
+    if (ls->bigint_fast && ls->cap < (1LL << 30) && !getenv("PRESTOGPU_NO_FAST_BUILD")) {
+        const DCol& kc = build.c[0];
+        PG_LAUNCH(ctx, j_build_fast_kernel, grid_for(ctx, rows, J_THREADS, 4), J_THREADS, 0, ls->slots.as<JSlot>(), ls->cap, (const int64_t*)kc.values,
+                  kc.nulls, rows, row_slot.as<int32_t>(), ls->meta.as<unsigned long long>());
+        int64_t m[6];
+        read_scalars(ctx, ls->meta.p, 6, m);
+        ls->has_dups = (m[0] & 0xffffffff) != 0 || m[4] != m[5];   // fewer claimed slots than inserted rows: some key repeats
+    } else {
+        PG_LAUNCH(ctx, j_build_kernel, grid_for(ctx, rows, J_THREADS), J_THREADS, 0, ls->slots.as<JSlot>(), ls->cap, build, hc, has_hash, rows,
+                  row_slot.as<int32_t>(), d_has_dups);
+        int64_t flag;
+        read_scalars(ctx, d_has_dups, 1, &flag);
+        ls->has_dups = (flag & 0xffffffff) != 0;
+    }
     if (!ls->has_dups) return;   // JoinHashSupplier.java:72: positionLinks == Optional.empty()
     // CSR segments for repeated keys
     int64_t ntiles = num_tiles(nslots);
@@ -561,7 +727,11 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
         ProbeArgs a;
         a.slots = ls->slots.as<JSlot>(); a.cap = ls->cap; a.seg_off = ls->seg_off.as<int32_t>(); a.seg_rows = ls->seg_rows.as<int32_t>();
         a.probe_slot = ls->probe_slot.as<int32_t>(); a.n = n; a.join_type = join_type; a.build_empty = ls->rows == 0 ? 1 : 0;
-        PG_LAUNCH(ctx, j_probe_count_kernel, (int)ntiles, SCAN_THREADS, 0, a, build, probe, hc, has_hash, tiles);
+        const bool fast = ls->bigint_fast && ls->cap < (1LL << 30) && !getenv("PRESTOGPU_NO_FAST_PROBE");
+        if (fast)
+            PG_LAUNCH(ctx, j_probe_count_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, (const int64_t*)probe.c[0].values, probe.c[0].nulls, tiles);
+        else
+            PG_LAUNCH(ctx, j_probe_count_kernel, (int)ntiles, SCAN_THREADS, 0, a, build, probe, hc, has_hash, tiles);
         scan_tile_totals(ctx, tiles, ntiles, tiles + ntiles);
         int64_t tot[2];
         read_scalars(ctx, tiles + ntiles, 2, tot);
@@ -572,7 +742,8 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
         OutVec<int32_t> op; OutVec<int64_t> ob;
         op.begin(ctx, out_probe_idx, out_mem, tot[0]);
         ob.begin(ctx, out_build_pos, out_mem, tot[0]);
-        PG_LAUNCH(ctx, j_probe_emit_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
+        if (fast) PG_LAUNCH(ctx, j_probe_emit_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
+        else PG_LAUNCH(ctx, j_probe_emit_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
         op.finish(); ob.finish();
         sync(ctx);
     });

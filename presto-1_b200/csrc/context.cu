@@ -36,20 +36,23 @@ void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
     }
     out.value_bytes = col_value_bytes(ctx, c, n);
     PG_CHECK_ARG(c.mem == PG_MEM_HOST, "bad mem kind %d", c.mem);
-    out.values.alloc(ctx, out.value_bytes > 0 ? out.value_bytes : 8);
-    copy_async(ctx, out.values.p, c.values, out.value_bytes, cudaMemcpyHostToDevice);
-    out.d.values = out.values.p;
+    // small arrays go through the pinned arena (asynchronous), large ones straight from the caller's memory
+    auto stage = [&](DevBuf& own, const void* host, int64_t bytes) -> void* {
+        if (void* p = in_arena_stage(ctx, host, bytes)) return p;
+        own.alloc(ctx, bytes > 0 ? bytes : 8);
+        copy_async(ctx, own.p, host, bytes, cudaMemcpyHostToDevice);
+        return own.p;
+    };
+    out.d.values = stage(out.values, c.values, out.value_bytes);
     out.d.nulls = nullptr; out.d.offsets = nullptr;
-    if (c.nulls) {
-        out.nulls.alloc(ctx, n > 0 ? n : 1);
-        copy_async(ctx, out.nulls.p, c.nulls, n, cudaMemcpyHostToDevice);
-        out.d.nulls = out.nulls.as<uint8_t>();
-    }
+    if (c.nulls) out.d.nulls = (const uint8_t*)stage(out.nulls, c.nulls, n);
     if (type_is_var(c.type)) {
-        out.offsets.alloc(ctx, (n + 1) * 4);
-        if (c.offsets) copy_async(ctx, out.offsets.p, c.offsets, (n + 1) * 4, cudaMemcpyHostToDevice);
-        else memset_async(ctx, out.offsets.p, 0, (n + 1) * 4);
-        out.d.offsets = out.offsets.as<int32_t>();
+        if (c.offsets) out.d.offsets = (const int32_t*)stage(out.offsets, c.offsets, (n + 1) * 4);
+        else {
+            out.offsets.alloc(ctx, (n + 1) * 4);
+            memset_async(ctx, out.offsets.p, 0, (n + 1) * 4);
+            out.d.offsets = out.offsets.as<int32_t>();
+        }
     }
 }
 
@@ -87,6 +90,28 @@ void* out_arena_alloc(pg_ctx* ctx, int64_t bytes, int64_t* off) {
     *off = ctx->out_used;
     ctx->out_used += need;
     return (char*)ctx->out_dev + *off;
+}
+
+void* in_arena_stage(pg_ctx* ctx, const void* host, int64_t bytes) {
+    const int64_t ARENA = 4 << 20, MAX_PIECE = 256 << 10;
+    if (bytes <= 0 || bytes > MAX_PIECE) return nullptr;
+    if (!ctx->in_dev) {
+        if (cudaMalloc(&ctx->in_dev, ARENA) != cudaSuccess) { cudaGetLastError(); ctx->in_dev = nullptr; return nullptr; }
+        if (cudaMallocHost((void**)&ctx->in_pinned, ARENA) != cudaSuccess) {
+            cudaGetLastError(); cudaFree(ctx->in_dev); ctx->in_dev = nullptr; return nullptr;
+        }
+        ctx->in_cap = ARENA;
+    }
+    const int64_t need = (bytes + 255) & ~255LL;
+    if (ctx->in_used + need > ctx->in_cap) return nullptr;
+    const int64_t off = ctx->in_used;
+    ctx->in_used += need;
+    memcpy(ctx->in_pinned + off, host, (size_t)bytes);
+    if (cudaMemcpyAsync((char*)ctx->in_dev + off, ctx->in_pinned + off, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return (char*)ctx->in_dev + off;
 }
 
 void flush_host_outputs(pg_ctx* ctx) {
@@ -144,6 +169,8 @@ int32_t pg_ctx_destroy(pg_ctx* ctx) {
     if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
     if (ctx->out_dev) cudaFree(ctx->out_dev);
     if (ctx->out_pinned) cudaFreeHost(ctx->out_pinned);
+    if (ctx->in_dev) cudaFree(ctx->in_dev);
+    if (ctx->in_pinned) cudaFreeHost(ctx->in_pinned);
     for (const pg_kernel_record& r : ctx->records) { cudaEventDestroy(r.start); cudaEventDestroy(r.stop); }
     for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
     pg::jit_cache_free(ctx);

@@ -37,6 +37,12 @@ struct pg_ctx {
     char* out_pinned = nullptr;
     int64_t out_cap = 0, out_used = 0;
     std::vector<pending_out> out_pending;
+    // small host inputs (Trino pages are <= 1 MiB) are staged through one pinned buffer: the copy to the device is then
+    // truly asynchronous instead of one blocking pageable copy per array.  Reset at every top-level API call.
+    void* in_dev = nullptr;
+    char* in_pinned = nullptr;
+    int64_t in_cap = 0, in_used = 0;
+    int guard_depth = 0;
 };
 
 namespace pg {
@@ -85,6 +91,16 @@ struct Error : public std::exception {
 // Wraps the body of every extern "C" entry point.
 template <typename F>
 static inline int32_t guard(pg_ctx* ctx, F&& f) {
+    struct Depth {
+        pg_ctx* c;
+        explicit Depth(pg_ctx* ctx) : c(ctx) {
+            if (c && c->guard_depth++ == 0 && c->in_used > 0) {
+                cudaStreamSynchronize(c->stream);   // the previous call's staged copies must have left the pinned buffer
+                c->in_used = 0;
+            }
+        }
+        ~Depth() { if (c) c->guard_depth--; }
+    } depth(ctx);
     try {
         if (ctx) PG_CUDA(cudaSetDevice(ctx->device));
         f();
@@ -150,6 +166,8 @@ static inline void sync(pg_ctx* ctx) {
 }
 // carve `bytes` out of the output arena (nullptr when it does not fit: the caller stages the column on its own)
 void* out_arena_alloc(pg_ctx* ctx, int64_t bytes, int64_t* off);
+// stage `bytes` of host memory through the pinned input arena; returns the device address or nullptr when it does not fit
+void* in_arena_stage(pg_ctx* ctx, const void* host, int64_t bytes);
 
 // read back up to 64 int64 scalars from device memory (synchronises the stream)
 static inline void read_scalars(pg_ctx* ctx, const void* d, int n, int64_t* out) {

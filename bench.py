@@ -168,6 +168,8 @@ def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world):
     import numpy as np
     from presto_b200.blocks import Block, _NP_DTYPE
     cap = 1 << 16
+    trace = _MERGE_BUFS.setdefault("trace", [0.0] * 5) if os.environ.get("PRESTOGPU_BENCH_TRACE") else None
+    t0 = time.perf_counter()
     if "send" not in _MERGE_BUFS:
         _MERGE_BUFS["send_host"] = torch.zeros(cap, dtype=torch.uint8).pin_memory()
         _MERGE_BUFS["send"] = torch.zeros(cap, dtype=torch.uint8, device="cuda")
@@ -184,10 +186,12 @@ def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world):
     sh = _MERGE_BUFS["send_host"].numpy()
     sh[:8] = np.array([len(payload)], dtype=np.int64).view(np.uint8)
     sh[8:8 + len(payload)] = payload
+    t1 = time.perf_counter()
     _MERGE_BUFS["send"].copy_(_MERGE_BUFS["send_host"], non_blocking=True)
     dist.all_gather_into_tensor(_MERGE_BUFS["recv"], _MERGE_BUFS["send"])
     _MERGE_BUFS["recv_host"].copy_(_MERGE_BUFS["recv"], non_blocking=True)
     torch.cuda.current_stream().synchronize()
+    t2 = time.perf_counter()
     host = _MERGE_BUFS["recv_host"].numpy()
     nb = len(part_page.blocks)
     per_block = [[] for _ in range(nb)]      # (values, offsets, nulls, n) of every rank
@@ -226,11 +230,17 @@ def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world):
         if any(len(t[2]) for t in per_block[i]):
             nulls = np.concatenate([t[2] if len(t[2]) else np.zeros(t[3], dtype=np.uint8) for t in per_block[i]])
         blocks.append(Block(b.type, vals, nulls, offs, total))
+    t3 = time.perf_counter()
     fin = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs, expected_groups=1000, ctx=ctx)
     fin.add_input(P.Page(*blocks, position_count=total))
     fin.finish()
     out = fin.get_output()
     fin.close()
+    if trace is not None:
+        t4 = time.perf_counter()
+        for i, d in enumerate((t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
+            trace[i] += d
+        trace[4] += 1
     return out
 
 
@@ -253,7 +263,7 @@ class MergePipeline:
     def _run(self):
         torch = self.torch
         torch.cuda.set_device(self.local_rank)
-        self.stream = torch.cuda.Stream()
+        self.stream = torch.cuda.Stream(priority=-1)    # its few small kernels go ahead of the next step's big one
         with torch.cuda.stream(self.stream):
             self.ctx = self.P.GpuContext(self.local_rank)      # bound to this thread's stream
             self.ready.set()
@@ -461,6 +471,8 @@ def gpu_arm(args):
         torch.cuda.synchronize()
 
     pipe = MergePipeline(P, dist, torch, fin_aggs, local_rank, world) if world > 1 else None
+    if pipe:
+        ctx.reserve_sms(int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "8")))   # room for the FINAL stage's small kernels
 
     def step_device():
         if world == 1:
@@ -587,6 +599,10 @@ def gpu_arm(args):
         print(json.dumps(line), flush=True)
     if pipe:
         pipe.close()
+        if rank == 0 and "trace" in _MERGE_BUFS:
+            tr = _MERGE_BUFS["trace"]
+            print("merge stage ms per call: pack %.3f gather %.3f unpack %.3f final %.3f (calls %d)"
+                  % tuple([1e3 * x / max(tr[4], 1) for x in tr[:4]] + [int(tr[4])]), file=sys.stderr)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -89,6 +89,10 @@ PG_API const char* pg_last_error(pg_ctx* ctx);
 /* use an external stream (e.g. torch's current stream) for all work of this context */
 PG_API int32_t pg_ctx_set_stream(pg_ctx* ctx, void* cuda_stream);
 PG_API int32_t pg_ctx_synchronize(pg_ctx* ctx);
+/* leave `sms` multiprocessors free for work on other streams: the one-wave persistent kernels of this context size their
+   grids to (SM count - sms), so a second pipeline stage (e.g. the FINAL step of the previous page set) is not queued
+   behind them.  The device-side analogue of splitting driver threads between pipelines (TaskExecutor.java). */
+PG_API int32_t pg_ctx_reserve_sms(pg_ctx* ctx, int32_t sms);
 /* number of kernels this context has launched so far (bench.py's gpu_launches)  */
 PG_API int64_t pg_ctx_launch_count(pg_ctx* ctx);
 /* per-kernel CUDA-event timing on the context stream (off by default): measurement support for bench.py */

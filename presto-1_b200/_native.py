@@ -58,6 +58,7 @@ _PROTOS = {
     "pg_ctx_destroy": (I32, [P]),
     "pg_last_error": (C.c_char_p, [P]),
     "pg_ctx_set_stream": (I32, [P, P]),
+    "pg_ctx_reserve_sms": (I32, [P, I32]),
     "pg_ctx_synchronize": (I32, [P]),
     "pg_ctx_launch_count": (I64, [P]),
     "pg_version": (C.c_char_p, []),

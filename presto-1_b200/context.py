@@ -27,6 +27,10 @@ class GpuContext:
     def set_stream(self, cuda_stream):
         N.check(self._h, N.lib().pg_ctx_set_stream(self._h, C.c_void_p(cuda_stream)))
 
+    def reserve_sms(self, sms):
+        """Leave `sms` multiprocessors free for a second pipeline stage running on another stream."""
+        N.check(self._h, N.lib().pg_ctx_reserve_sms(self._h, int(sms)))
+
     def synchronize(self):
         N.check(self._h, N.lib().pg_ctx_synchronize(self._h))
 

@@ -149,7 +149,7 @@ int32_t pg_ctx_create(int32_t device, pg_ctx** out) {
     int32_t rc = guard(ctx, [&] {
         cudaDeviceProp prop;
         PG_CUDA(cudaGetDeviceProperties(&prop, device));
-        ctx->sm_count = prop.multiProcessorCount;
+        ctx->sm_count = ctx->sm_total = prop.multiProcessorCount;
         PG_CUDA(cudaMallocHost((void**)&ctx->h_scalar, 64 * sizeof(int64_t)));
         // keep freed blocks cached in the default pool: per-page scratch is reused, not returned to the OS
         cudaMemPool_t pool;
@@ -183,6 +183,12 @@ const char* pg_last_error(pg_ctx* ctx) { return ctx ? ctx->err.c_str() : "null c
 int32_t pg_ctx_set_stream(pg_ctx* ctx, void* cuda_stream) {
     if (!ctx) return PG_E_INVALID_ARGUMENT;
     ctx->stream = (cudaStream_t)cuda_stream;
+    return PG_OK;
+}
+
+int32_t pg_ctx_reserve_sms(pg_ctx* ctx, int32_t sms) {
+    if (!ctx || sms < 0 || sms >= ctx->sm_total) return PG_E_INVALID_ARGUMENT;
+    ctx->sm_count = ctx->sm_total - sms;
     return PG_OK;
 }
 

@@ -21,7 +21,8 @@ struct pg_ctx {
     int device = 0;
     cudaStream_t stream = 0;   // legacy default stream unless pg_ctx_set_stream() is called
     int64_t launches = 0;      // kernels launched through PG_LAUNCH
-    int sm_count = 148;
+    int sm_count = 148;        // multiprocessors this context sizes one-wave grids for (sm_total minus the reserved ones)
+    int sm_total = 148;
     std::string err;
     // pinned host bounce buffer for small read-backs (flags, counters)
     int64_t* h_scalar = nullptr;  // 64 x int64, pinned

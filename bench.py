@@ -539,7 +539,9 @@ def gpu_arm(args):
         prof = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(prof):
             try:
-                roofline["traffic"] = json.load(open(prof)).get(top)
+                roofline["traffic"] = json.load(open(prof)).get(top)      # bytes per launch, from the committed ncu capture
+                roofline["traffic_unit"] = "bytes/launch (ncu dram read+write)"
+                roofline["algorithmic_bytes_per_launch"] = int(input_bytes)
             except Exception:
                 pass
 

@@ -109,5 +109,9 @@ AggOp agg_make_op(pg_agg* agg, const DCol* arg, const DCol* mask);
 void agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, int64_t* error_group, bool do_sync);
 void agg_evaluate_async(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, long long* d_err);
 int agg_n_intermediate(const pg_agg* agg);
+void agg_evaluate_batch(pg_ctx* ctx, pg_agg* const* aggs, int na, int64_t first, int64_t n, int32_t final_step, pg_col_out* out,
+                        long long* d_errs);
+void accumulate_intermediate_batch(pg_ctx* ctx, pg_agg* const* aggs, const DCol* s0, const DCol* s1, int na, const int32_t* d_ids, int64_t n,
+                                   int64_t group_count);
 void accumulate_intermediate(pg_agg* agg, const DCol& s0, const DCol& s1, const int32_t* d_ids, int64_t n, int64_t group_count);
 }  // namespace pg

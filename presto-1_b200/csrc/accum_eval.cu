@@ -3,6 +3,8 @@
 //   state/LongDecimalWithOverflowStateSerializer.java:38-66       [overflow][lo][hi]           24 B VARBINARY
 //   state/LongDecimalWithOverflowAndLongStateSerializer.java:38-68 [count][overflow][lo][hi]    32 B VARBINARY
 //   StateCompiler.java:207-217 (fields sorted by name) for LongLongState / LongAndDoubleState / LongDoubleState
+#include <vector>
+
 #include "accum_dev.cuh"
 #include "scan.cuh"
 
@@ -13,7 +15,7 @@ typedef unsigned __int128 u128;
 // ------------------------------------------------------------------ addIntermediate
 PG_D unsigned long long load_u64_unaligned(const uint8_t* p) { return rd64u(p); }
 
-__global__ void acc_intermediate_kernel(AggOp op, DCol s0, DCol s1, int kind, const int32_t* __restrict__ gids, int64_t n) {
+PG_D void intermediate_rows(const AggOp& op, const DCol& s0, const DCol& s1, int kind, const int32_t* __restrict__ gids, int64_t n) {
     int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; row < n; row += stride) {
@@ -59,6 +61,16 @@ __global__ void acc_intermediate_kernel(AggOp op, DCol s0, DCol s1, int kind, co
         }
         update_global(op, g, c);
     }
+}
+// every aggregate of the operator in one launch: blockIdx.y selects the aggregate
+struct IntermBatch {
+    AggOp op[MAX_AGGS];
+    DCol s0[MAX_AGGS], s1[MAX_AGGS];
+    int32_t kind[MAX_AGGS];
+};
+__global__ void acc_intermediate_kernel(const __grid_constant__ IntermBatch b, const int32_t* __restrict__ gids, int64_t n) {
+    const int a = blockIdx.y;
+    intermediate_rows(b.op[a], b.s0[a], b.s1[a], b.kind[a], gids, n);
 }
 
 // ------------------------------------------------------------------ evaluate
@@ -122,7 +134,7 @@ PG_D void put64(void* out, uint8_t* nulls, int64_t i, long long v, bool isnull) 
     if (nulls) nulls[i] = isnull ? 1 : 0;
 }
 
-__global__ void acc_evaluate_kernel(EvalArgs a) {
+PG_D void evaluate_rows(const EvalArgs& a) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < a.n; i += stride) {
@@ -206,6 +218,8 @@ __global__ void acc_evaluate_kernel(EvalArgs a) {
         if (err && cnt != 0) atomicMin(a.error_group, (long long)g);
     }
 }
+struct EvalBatch { EvalArgs a[MAX_AGGS]; };
+__global__ void acc_evaluate_kernel(const __grid_constant__ EvalBatch b) { evaluate_rows(b.a[blockIdx.y]); }
 
 // decimal intermediate state -> VARBINARY rows (null and zero-length when the state was never touched)
 __global__ void __launch_bounds__(SCAN_THREADS) acc_dec_inter_count_kernel(const unsigned long long* state, int64_t first, int64_t n,
@@ -221,14 +235,14 @@ __global__ void __launch_bounds__(SCAN_THREADS) acc_dec_inter_count_kernel(const
     block_exclusive_scan(acc, smem, &total);
     if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
 }
-__global__ void __launch_bounds__(SCAN_THREADS) acc_dec_inter_write_kernel(const unsigned long long* state, int64_t first, int64_t n, int entry,
-                                                                           const Pair64* tile_prefix, uint8_t* out_bytes, int32_t* out_offsets,
-                                                                           uint8_t* out_nulls) {
-    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+PG_D void dec_inter_write_tile(const unsigned long long* state, int64_t first, int64_t n, int entry, const Pair64* tile_prefix,
+                               uint8_t* out_bytes, int32_t* out_offsets, uint8_t* out_nulls, Pair64* smem) {
     int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
-    Pair64 run = tile_prefix[blockIdx.x];
+    Pair64 run{0, 0};
+    if (tile_prefix) run = tile_prefix[blockIdx.x];   // null: a single tile
     for (int j = 0; j < SCAN_ITEMS; j++) {
         int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (tile_base + (int64_t)j * SCAN_THREADS >= n) break;
         Pair64 v{0, 0};
         const unsigned long long* st = nullptr;
         if (i < n) { st = state + (first + i) * 4; if (st[0] != 0) v.a = entry; }
@@ -250,6 +264,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) acc_dec_inter_write_kernel(const
         }
         run = run + total;
     }
+}
+__global__ void __launch_bounds__(SCAN_THREADS) acc_dec_inter_write_kernel(const unsigned long long* state, int64_t first, int64_t n, int entry,
+                                                                           const Pair64* tile_prefix, uint8_t* out_bytes, int32_t* out_offsets,
+                                                                           uint8_t* out_nulls) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    dec_inter_write_tile(state, first, n, entry, tile_prefix, out_bytes, out_offsets, out_nulls, smem);
+}
+// few groups: every decimal aggregate's VARBINARY column in one launch of single-tile blocks (blockIdx.y = aggregate)
+struct DecInterArgs {
+    const unsigned long long* state;
+    uint8_t* out_bytes; int32_t* out_offsets; uint8_t* out_nulls;
+    int32_t entry, pad;
+};
+struct DecInterBatch { DecInterArgs a[MAX_AGGS]; };
+__global__ void __launch_bounds__(SCAN_THREADS) acc_dec_inter_small_kernel(const __grid_constant__ DecInterBatch b, int64_t first, int64_t n) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    const DecInterArgs& a = b.a[blockIdx.y];
+    dec_inter_write_tile(a.state, first, n, a.entry, nullptr, a.out_bytes, a.out_offsets, a.out_nulls, smem);
 }
 
 
@@ -311,18 +343,32 @@ AggOp agg_make_op(pg_agg* agg, const DCol* arg, const DCol* mask) {
     return op;
 }
 
-// addIntermediate for one aggregate: s0/s1 are the intermediate columns (see the layout table in prestogpu.h)
-void accumulate_intermediate(pg_agg* agg, const DCol& s0, const DCol& s1, const int32_t* d_ids, int64_t n, int64_t group_count) {
-    pg_ctx* ctx = agg->ctx;
-    if (n <= 0) return;
-    if (agg->op == OP_MIN128 || agg->op == OP_MAX128) {   // same two-pass protocol as addInput
-        AggProgram prog; memset(&prog, 0, sizeof(prog)); prog.naggs = 1;
-        prog.ops[0] = agg_make_op(agg, &s0, nullptr);
-        accumulate(ctx, prog, d_ids, n, group_count);
-        return;
+// addIntermediate for every aggregate of an operator: s0[i]/s1[i] are aggregate i's intermediate columns (see the layout table
+// in prestogpu.h).  One launch for all of them; 128-bit min/max keep their two-pass protocol.
+void accumulate_intermediate_batch(pg_ctx* ctx, pg_agg* const* aggs, const DCol* s0, const DCol* s1, int na, const int32_t* d_ids, int64_t n,
+                                   int64_t group_count) {
+    if (n <= 0 || na <= 0) return;
+    IntermBatch b;
+    memset(&b, 0, sizeof(b));
+    int nb = 0;
+    for (int i = 0; i < na; i++) {
+        pg_agg* agg = aggs[i];
+        if (agg->op == OP_MIN128 || agg->op == OP_MAX128) {   // same two-pass protocol as addInput
+            AggProgram prog; memset(&prog, 0, sizeof(prog)); prog.naggs = 1;
+            prog.ops[0] = agg_make_op(agg, &s0[i], nullptr);
+            accumulate(ctx, prog, d_ids, n, group_count);
+            continue;
+        }
+        b.op[nb] = agg_make_op(agg, nullptr, nullptr);
+        b.s0[nb] = s0[i]; b.s1[nb] = s1[i]; b.kind[nb] = agg->kind;
+        nb++;
     }
-    AggOp op = agg_make_op(agg, nullptr, nullptr);
-    PG_LAUNCH(ctx, acc_intermediate_kernel, grid_for(ctx, n, 256), 256, 0, op, s0, s1, agg->kind, d_ids, n);
+    if (nb == 0) return;
+    dim3 grid((unsigned)grid_for(ctx, n, 256), (unsigned)nb);
+    PG_LAUNCH(ctx, acc_intermediate_kernel, grid, 256, 0, b, d_ids, n);
+}
+void accumulate_intermediate(pg_agg* agg, const DCol& s0, const DCol& s1, const int32_t* d_ids, int64_t n, int64_t group_count) {
+    accumulate_intermediate_batch(agg->ctx, &agg, &s0, &s1, 1, d_ids, n, group_count);
 }
 
 int agg_n_intermediate(const pg_agg* agg) {
@@ -365,48 +411,91 @@ void agg_evaluate(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_
     }
 }
 
-// Launches the evaluation and the copies into host outputs without waiting; *d_err (device, preset to 0x7f..7f) receives
-// the smallest overflowing group id.
-void agg_evaluate_async(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, long long* d_err) {
-    pg_ctx* ctx = agg->ctx;
-    PG_CHECK_ARG(first >= 0 && n >= 0 && out != nullptr, "bad arguments");
-    if (n == 0) return;
-    agg_ensure_capacity(agg, first + n);
-    int32_t t[2];
-    out_types(agg, final_step, t);
-    int ncols = t[1] ? 2 : 1;
-    for (int k = 0; k < ncols; k++)
-        PG_CHECK_ARG(out[k].type == t[k], "output column %d must have type %d, got %d", k, t[k], out[k].type);
-    OutStage st[2];
-    int64_t vbytes[2] = {0, 0};
-    const unsigned long long* state = agg->state.as<unsigned long long>();
-    if (t[0] == PG_VARBINARY) {
-        int entry = agg->kind == PG_AGG_AVG ? 32 : 24;
-        int64_t ntiles = num_tiles(n);
-        DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
-        Pair64* d_total = tiles.as<Pair64>() + ntiles;
-        PG_LAUNCH(ctx, acc_dec_inter_count_kernel, (int)ntiles, SCAN_THREADS, 0, state, first, n, entry, tiles.as<Pair64>());
-        scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, d_total);
-        int64_t tot[2];
-        read_scalars(ctx, d_total, 2, tot);
-        vbytes[0] = tot[0];
-        st[0].begin(ctx, &out[0], n, vbytes[0]);
-        PG_LAUNCH(ctx, acc_dec_inter_write_kernel, (int)ntiles, SCAN_THREADS, 0, state, first, n, entry, tiles.as<Pair64>(),
-                  (uint8_t*)st[0].d_values, st[0].d_offsets, st[0].d_nulls);
-    } else {
-        for (int k = 0; k < ncols; k++) {
-            vbytes[k] = n * type_width(t[k]);
-            st[k].begin(ctx, &out[k], n, vbytes[k]);
+// Launches the evaluation of `na` aggregates over groups [first, first+n) and the copies into host outputs without waiting.
+// out: the aggregates' output columns back to back (one per aggregate for the final step, agg_n_intermediate otherwise);
+// d_errs[i] (device, preset to 0x7f..7f) receives the smallest overflowing group id of aggregate i.
+// Fixed-width outputs of all aggregates go out in one launch; so do the decimal VARBINARY states when the groups fit one tile.
+void agg_evaluate_batch(pg_ctx* ctx, pg_agg* const* aggs, int na, int64_t first, int64_t n, int32_t final_step, pg_col_out* out,
+                        long long* d_errs) {
+    PG_CHECK_ARG(first >= 0 && n >= 0 && out != nullptr && na >= 0 && na <= MAX_AGGS, "bad arguments");
+    if (n == 0 || na == 0) return;
+    std::vector<OutStage> st(2 * (size_t)na);
+    std::vector<int64_t> vbytes(2 * (size_t)na, 0);
+    std::vector<int> cols_of(na, 1);
+    EvalBatch eb; DecInterBatch db;
+    int ne = 0, nd = 0, col = 0;
+    const int64_t ntiles = num_tiles(n);
+    // Two passes: columns that need a read-back of their byte total are produced and handed over first, because a
+    // synchronisation flushes and recycles the output staging arena the others are about to share.
+    std::vector<char> done(na, 0);
+    for (int pass = 0; pass < 2; pass++) {
+        col = 0;
+        for (int i = 0; i < na; col += cols_of[i], i++) {
+            pg_agg* agg = aggs[i];
+            int32_t t[2];
+            out_types(agg, final_step, t);
+            const int ncols = t[1] ? 2 : 1;
+            cols_of[i] = ncols;
+            pg_col_out* o = out + col;
+            OutStage* s = &st[2 * (size_t)i];
+            int64_t* vb = &vbytes[2 * (size_t)i];
+            const int entry = agg->kind == PG_AGG_AVG ? 32 : 24;
+            const bool needs_total = t[0] == PG_VARBINARY && !(ntiles == 1 && o[0].values_capacity_bytes >= (int64_t)entry * n);
+            if (pass == 0) {
+                agg_ensure_capacity(agg, first + n);
+                for (int k = 0; k < ncols; k++)
+                    PG_CHECK_ARG(o[k].type == t[k], "output column %d must have type %d, got %d", col + k, t[k], o[k].type);
+            }
+            if (needs_total != (pass == 0)) continue;
+            const unsigned long long* state = agg->state.as<unsigned long long>();
+            if (needs_total) {
+                DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+                Pair64* d_total = tiles.as<Pair64>() + ntiles;
+                PG_LAUNCH(ctx, acc_dec_inter_count_kernel, (int)ntiles, SCAN_THREADS, 0, state, first, n, entry, tiles.as<Pair64>());
+                scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, d_total);
+                int64_t tot[2];
+                read_scalars(ctx, d_total, 2, tot);
+                vb[0] = tot[0];
+                s[0].begin(ctx, &o[0], n, vb[0]);
+                PG_LAUNCH(ctx, acc_dec_inter_write_kernel, (int)ntiles, SCAN_THREADS, 0, state, first, n, entry, tiles.as<Pair64>(),
+                          (uint8_t*)s[0].d_values, s[0].d_offsets, s[0].d_nulls);
+                s[0].finish(vb[0]);
+                done[i] = 1;
+            } else if (t[0] == PG_VARBINARY) {
+                vb[0] = (int64_t)entry * n;   // upper bound: no read-back of the exact total
+                s[0].begin(ctx, &o[0], n, vb[0]);
+                DecInterArgs& d = db.a[nd++];
+                d.state = state; d.entry = entry; d.pad = 0;
+                d.out_bytes = (uint8_t*)s[0].d_values; d.out_offsets = s[0].d_offsets; d.out_nulls = s[0].d_nulls;
+            } else {
+                for (int k = 0; k < ncols; k++) {
+                    vb[k] = n * type_width(t[k]);
+                    s[k].begin(ctx, &o[k], n, vb[k]);
+                }
+                EvalArgs& a = eb.a[ne++];
+                a.state = state; a.op = agg->op; a.kind = agg->kind; a.in_type = agg->in_type; a.words = agg->words; a.final_step = final_step;
+                a.first = first; a.n = n;
+                a.out0 = s[0].d_values; a.nulls0 = s[0].d_nulls;
+                a.out1 = ncols > 1 ? s[1].d_values : nullptr; a.nulls1 = ncols > 1 ? s[1].d_nulls : nullptr;
+                a.error_group = d_errs + i;
+            }
         }
-        EvalArgs a;
-        a.state = state; a.op = agg->op; a.kind = agg->kind; a.in_type = agg->in_type; a.words = agg->words; a.final_step = final_step;
-        a.first = first; a.n = n;
-        a.out0 = st[0].d_values; a.nulls0 = st[0].d_nulls;
-        a.out1 = ncols > 1 ? st[1].d_values : nullptr; a.nulls1 = ncols > 1 ? st[1].d_nulls : nullptr;
-        a.error_group = d_err;
-        PG_LAUNCH(ctx, acc_evaluate_kernel, grid_for(ctx, n, 256), 256, 0, a);
     }
-    for (int k = 0; k < ncols; k++) st[k].finish(vbytes[k]);
+    if (ne > 0) {
+        dim3 grid((unsigned)grid_for(ctx, n, 256), (unsigned)ne);
+        PG_LAUNCH(ctx, acc_evaluate_kernel, grid, 256, 0, eb);
+    }
+    if (nd > 0) {
+        dim3 grid(1, (unsigned)nd);
+        PG_LAUNCH(ctx, acc_dec_inter_small_kernel, grid, SCAN_THREADS, 0, db, first, n);
+    }
+    for (int i = 0; i < na; i++) {
+        if (done[i]) continue;
+        for (int k = 0; k < cols_of[i]; k++) st[2 * (size_t)i + k].finish(vbytes[2 * (size_t)i + k]);
+    }
+}
+void agg_evaluate_async(pg_agg* agg, int64_t first, int64_t n, int32_t final_step, pg_col_out* out, long long* d_err) {
+    agg_evaluate_batch(agg->ctx, &agg, 1, first, n, final_step, out, d_err);
 }
 
 }  // namespace pg

@@ -35,6 +35,7 @@ void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
         return;
     }
     out.value_bytes = col_value_bytes(ctx, c, n);
+    out.host_offsets = type_is_var(c.type) ? c.offsets : nullptr;
     PG_CHECK_ARG(c.mem == PG_MEM_HOST, "bad mem kind %d", c.mem);
     // small arrays go through the pinned arena (asynchronous), large ones straight from the caller's memory
     auto stage = [&](DevBuf& own, const void* host, int64_t bytes) -> void* {
@@ -56,20 +57,31 @@ void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
     }
 }
 
-void resolve_value_bytes(pg_ctx* ctx, ColImport** cols, int count) {
-    int pending[64], np = 0;
-    for (int i = 0; i < count && np < 64; i++) {
-        if (cols[i]->value_bytes >= 0) continue;
-        if (cols[i]->n == 0) { cols[i]->value_bytes = 0; continue; }
-        copy_async(ctx, (char*)ctx->h_scalar + 8 * np, cols[i]->d.offsets + cols[i]->n, 4, cudaMemcpyDeviceToHost);
+void resolve_value_bytes(pg_ctx* ctx, ColImport** cols, int count, int64_t prefix_rows, int64_t* prefix_bytes) {
+    int pending[32], np = 0;
+    const bool want_prefix = prefix_rows > 0 && prefix_bytes != nullptr;
+    for (int i = 0; i < count && np < 32; i++) {
+        ColImport* c = cols[i];
+        if (want_prefix) prefix_bytes[i] = 0;
+        if (!type_is_var(c->d.type)) continue;
+        if (c->n == 0) { c->value_bytes = 0; continue; }
+        const int64_t pr = prefix_rows < c->n ? prefix_rows : c->n;
+        if (c->value_bytes >= 0 && (!want_prefix || c->host_offsets)) {
+            if (want_prefix && c->host_offsets) prefix_bytes[i] = c->host_offsets[pr];
+            else if (want_prefix) prefix_bytes[i] = c->value_bytes;
+            continue;
+        }
+        copy_async(ctx, (char*)ctx->h_scalar + 8 * np, c->d.offsets + c->n, 4, cudaMemcpyDeviceToHost);
+        if (want_prefix) copy_async(ctx, (char*)ctx->h_scalar + 8 * np + 4, c->d.offsets + pr, 4, cudaMemcpyDeviceToHost);
         pending[np++] = i;
     }
     if (np == 0) return;
     sync(ctx);
     for (int j = 0; j < np; j++) {
-        int32_t last;
-        memcpy(&last, (char*)ctx->h_scalar + 8 * j, 4);
-        cols[pending[j]]->value_bytes = last;
+        int32_t v[2];
+        memcpy(v, (char*)ctx->h_scalar + 8 * j, 8);
+        cols[pending[j]]->value_bytes = v[0];
+        if (want_prefix) prefix_bytes[pending[j]] = v[1];
     }
 }
 
@@ -119,7 +131,7 @@ void flush_host_outputs(pg_ctx* ctx) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     std::vector<pg_ctx::pending_out> pend;
     pend.swap(ctx->out_pending);
-    ctx->out_used = 0;
+    if (ctx->out_live == 0) ctx->out_used = 0;   // pieces still being filled keep their place
     if (e != cudaSuccess) fail(PG_E_CUDA, "flushing host outputs failed: %s", cudaGetErrorString(e));
     for (const pg_ctx::pending_out& p : pend) memcpy(p.host, ctx->out_pinned + p.off, (size_t)p.bytes);
 }

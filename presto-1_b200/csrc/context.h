@@ -44,6 +44,7 @@ struct pg_ctx {
     char* in_pinned = nullptr;
     int64_t in_cap = 0, in_used = 0;
     int guard_depth = 0;
+    int out_live = 0;              // output-arena pieces handed to an OutStage that has not given them back yet
 };
 
 namespace pg {
@@ -95,9 +96,13 @@ static inline int32_t guard(pg_ctx* ctx, F&& f) {
     struct Depth {
         pg_ctx* c;
         explicit Depth(pg_ctx* ctx) : c(ctx) {
-            if (c && c->guard_depth++ == 0 && c->in_used > 0) {
-                cudaStreamSynchronize(c->stream);   // the previous call's staged copies must have left the pinned buffer
-                c->in_used = 0;
+            if (c && c->guard_depth++ == 0) {
+                if (c->in_used > 0) {
+                    cudaStreamSynchronize(c->stream);   // the previous call's staged copies must have left the pinned buffer
+                    c->in_used = 0;
+                }
+                c->out_live = 0;
+                if (c->out_pending.empty()) c->out_used = 0;
             }
         }
         ~Depth() { if (c) c->guard_depth--; }
@@ -107,10 +112,10 @@ static inline int32_t guard(pg_ctx* ctx, F&& f) {
         f();
         return PG_OK;
     } catch (const Error& e) {
-        if (ctx) { ctx->err = e.msg; ctx->out_pending.clear(); ctx->out_used = 0; }
+        if (ctx) { ctx->err = e.msg; ctx->out_pending.clear(); ctx->out_used = 0; ctx->out_live = 0; }
         return e.code;
     } catch (const std::exception& e) {
-        if (ctx) { ctx->err = e.what(); ctx->out_pending.clear(); ctx->out_used = 0; }
+        if (ctx) { ctx->err = e.what(); ctx->out_pending.clear(); ctx->out_used = 0; ctx->out_live = 0; }
         return PG_E_INTERNAL;
     }
 }
@@ -184,10 +189,12 @@ struct ColImport {
     DevBuf values, nulls, offsets;
     int64_t n = 0;
     int64_t value_bytes = 0;
+    const int32_t* host_offsets = nullptr;   // the caller's offsets when the column came from host memory
 };
 void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out);
 // fills value_bytes of device-resident variable width columns (left at -1 by import_col) with one synchronisation
-void resolve_value_bytes(pg_ctx* ctx, ColImport** cols, int count);
+// prefix_rows > 0: prefix_bytes[i] also receives the value bytes of the first prefix_rows rows of column i (0 for fixed width)
+void resolve_value_bytes(pg_ctx* ctx, ColImport** cols, int count, int64_t prefix_rows = 0, int64_t* prefix_bytes = nullptr);
 // bytes of the value buffer of column c with n rows (reads the last offset for variable width columns)
 int64_t col_value_bytes(pg_ctx* ctx, const pg_col& c, int64_t n);
 
@@ -203,7 +210,7 @@ struct OutStage {
     int64_t av = -1, an = -1, ao = -1;   // arena offsets (>= 0: the part leaves through the batched copy)
     void* stage(DevBuf& own, int64_t bytes, int64_t& aoff) {
         void* p = out_arena_alloc(ctx, bytes, &aoff);
-        if (p) return p;
+        if (p) { ctx->out_live++; return p; }
         aoff = -1;
         own.alloc(ctx, bytes > 0 ? bytes : 8);
         return own.p;
@@ -230,6 +237,7 @@ struct OutStage {
         if (type_is_var(o->type)) leave(o->offsets, d_offsets, (n + 1) * 4, ao);
     }
     void leave(void* host, const void* dev, int64_t bytes, int64_t aoff) {
+        if (aoff >= 0 && ctx->out_live > 0) ctx->out_live--;
         if (bytes <= 0) return;
         if (aoff >= 0) ctx->out_pending.push_back({host, aoff, bytes});
         else copy_async(ctx, host, dev, bytes, cudaMemcpyDeviceToHost);

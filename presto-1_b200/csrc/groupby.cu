@@ -404,9 +404,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) gb_export_var_kernel(const uint6
                                                                      uint8_t* out_bytes, int32_t* out_offsets, uint8_t* out_nulls) {
     __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
     int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
-    Pair64 run = tile_prefix[blockIdx.x];
+    Pair64 run{0, 0};
+    if (tile_prefix) run = tile_prefix[blockIdx.x];   // null: a single tile, nothing before it
     for (int j = 0; j < SCAN_ITEMS; j++) {
         int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (tile_base + (int64_t)j * SCAN_THREADS >= n) break;
         Pair64 v{0, 0};
         if (i < n) v.a = group_var_len(key_rows, L, k, first + i);
         Pair64 total;
@@ -533,6 +535,7 @@ static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_co
 
     // ---- K1 with quota / rebuild loop
     const int grid = grid_for(ctx, n, GB_THREADS);
+    bool inserted_pending = false, arena_pending = false;
     while (true) {
         int64_t room = gb->max_fill - gb->occupied;
         int64_t quota;
@@ -548,6 +551,7 @@ static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_co
         a.meta = meta; a.n = n; a.quota = quota; a.key_rows = gb->key_rows.as<uint64_t>(); a.arena = gb->arena.as<uint8_t>();
         if (gb->bigint_mode) PG_LAUNCH(ctx, gb_insert_kernel<true>, grid, GB_THREADS, 0, a, kc, L, hc, has_hash);
         else PG_LAUNCH(ctx, gb_insert_kernel<false>, grid, GB_THREADS, 0, a, kc, L, hc, has_hash);
+        if (room >= n) { inserted_pending = true; break; }   // no quota, so no abort: the count is read with the chunk's last read-back
         // one read-back: {inserted, abort}
         copy_async(ctx, ctx->h_scalar, &meta->inserted, 8, cudaMemcpyDeviceToHost);
         copy_async(ctx, ctx->h_scalar + 1, &meta->abort, 4, cudaMemcpyDeviceToHost);
@@ -564,11 +568,17 @@ static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_co
               gb->has_var ? 1 : 0, gb->tile_sums.as<Pair64>());
     scan_tile_totals(ctx, gb->tile_sums.as<Pair64>(), ntiles, &meta->chunk_total);
     if (gb->has_var) {
-        int64_t tot[2];
-        read_scalars(ctx, &meta->chunk_total, 2, tot);
-        int64_t need = gb->arena_used + tot[1];
-        if (need > gb->arena.bytes) gb->arena.grow(ctx, need * 2, gb->arena_used);
-        gb->arena_used = need;
+        const int64_t hint = gb->var_bound_hint;
+        if (hint >= 0 && hint <= (64LL << 20)) {   // a cheap bound from the caller: make room for it, learn the exact use later
+            if (gb->arena_used + hint > gb->arena.bytes) gb->arena.grow(ctx, (gb->arena_used + hint) * 2, gb->arena_used);
+            arena_pending = true;
+        } else {
+            int64_t tot[2];
+            read_scalars(ctx, &meta->chunk_total, 2, tot);
+            int64_t need = gb->arena_used + tot[1];
+            if (need > gb->arena.bytes) gb->arena.grow(ctx, need * 2, gb->arena_used);
+            gb->arena_used = need;
+        }
     }
     AssignArgs as;
     as.slots = gb->slots.as<Slot>(); as.cap = gb->cap; as.row_slot = gb->row_slot.as<int32_t>(); as.n = n;
@@ -583,9 +593,11 @@ static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_co
         int g3 = grid_for(ctx, n, 256, 4);
         PG_LAUNCH(ctx, gb_lookup_ids_kernel, g3, 256, 0, gb->slots.as<Slot>(), gb->row_slot.as<int32_t>(), n, d_out_ids);
     }
-    int64_t gc;
-    read_scalars(ctx, &meta->group_count, 1, &gc);
-    gb->groups = gc;
+    int64_t fin[3];   // {group_count, arena_bytes, inserted}: adjacent in GbMeta
+    read_scalars(ctx, &meta->group_count, 3, fin);
+    gb->groups = fin[0];
+    if (arena_pending) gb->arena_used = fin[1];
+    if (inserted_pending) gb->occupied += fin[2];
 }
 
 static KeyCols offset_keys(const KeyCols& kc, const KeyLayout& L, int64_t off) {
@@ -773,12 +785,20 @@ int32_t pg_groupby_export_keys(pg_groupby* gb, int64_t first, int64_t n, pg_col_
                               st[k].d_nulls);
                 } else {
                     int64_t ntiles = num_tiles(n);
+                    const bool bounded = gb->arena_used <= VAR_BOUND_BYTES && out_keys[k].values_capacity_bytes >= gb->arena_used;
+                    if (ntiles == 1 && bounded) {   // few groups: offsets come out of the one block's own scan
+                        vbytes[k] = gb->arena_used;
+                        st[k].begin(ctx, &out_keys[k], n, vbytes[k]);
+                        PG_LAUNCH(ctx, gb_export_var_kernel, 1, SCAN_THREADS, 0, gb->key_rows.as<uint64_t>(), gb->arena.as<uint8_t>(), L, k, first,
+                                  n, (const Pair64*)nullptr, (uint8_t*)st[k].d_values, st[k].d_offsets, st[k].d_nulls);
+                        continue;
+                    }
                     DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
                     Pair64* d_total = tiles.as<Pair64>() + ntiles;
                     PG_LAUNCH(ctx, gb_export_var_count_kernel, (int)ntiles, SCAN_THREADS, 0, gb->key_rows.as<uint64_t>(), L, k, first, n,
                               tiles.as<Pair64>());
                     scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, d_total);
-                    if (gb->arena_used <= VAR_BOUND_BYTES && out_keys[k].values_capacity_bytes >= gb->arena_used) {
+                    if (bounded) {
                         vbytes[k] = gb->arena_used;   // upper bound known on the host: no read-back of the exact total
                     } else {
                         int64_t tot[2];
@@ -793,7 +813,7 @@ int32_t pg_groupby_export_keys(pg_groupby* gb, int64_t first, int64_t n, pg_col_
         }
         for (size_t k = 0; k < st.size(); k++) st[k].finish(vbytes[k]);
         oh.finish();
-        sync(ctx);
+        if (ctx->guard_depth <= 1) sync(ctx);   // inside the fused operator's getOutput the caller's own read-back completes the copies
     });
 }
 

@@ -74,6 +74,7 @@ struct pg_groupby {
     int64_t groups = 0;       // host copy of meta.group_count
     int64_t ref_capacity = 0; // the reference's logical capacity schedule (getCapacity)
     int64_t arena_used = 0;
+    int64_t var_bound_hint = -1;   // caller's upper bound on the variable width bytes of the next page (-1: unknown, read them back)
     int64_t rehashes = 0;
     pg::DevBuf slots, values_by_group, key_rows, hash_by_group, arena, meta;
     // scratch reused across pages

@@ -157,7 +157,17 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     const int64_t PREFIX = 16 * 1024;
     bool fused_done = false;
     if (raw && !op->aggs.empty() && n >= 8 * PREFIX && fused_keys_packable(op->gb->layout)) {
+        ColImport* kimp[MAX_KEYS];
+        int nkimp = 0;
+        for (size_t k = 0; k < op->key_channels.size() && k < (size_t)MAX_KEYS; k++) kimp[nkimp++] = &imp[op->key_channels[k]];
+        if (op->gb->has_var) {   // one read-back gives the value bytes of the page and of the prefix (the store's growth bound)
+            int64_t pb[MAX_KEYS], bound = 0;
+            resolve_value_bytes(ctx, kimp, nkimp, PREFIX, pb);
+            for (int k = 0; k < nkimp; k++) bound += pb[k];
+            op->gb->var_bound_hint = bound;
+        }
         generic_rows(0, PREFIX, nullptr);
+        op->gb->var_bound_hint = -1;
         int64_t groups = op->gb->groups, m = n - PREFIX;
         if (groups <= 64) {
             DevBuf miss_flag(ctx, m), miss_cnt(ctx, 8);
@@ -176,13 +186,8 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
             }
             fl.miss_flag = miss_flag.as<uint8_t>(); fl.d_miss = miss_cnt.as<unsigned long long>();
             fl.row_base = PREFIX;
-            {
-                ColImport* kimp[8];
-                int nk = 0;
-                for (size_t k = 0; k < op->key_channels.size() && k < 8; k++) kimp[nk++] = &imp[op->key_channels[k]];
-                resolve_value_bytes(ctx, kimp, nk);
-                for (int k = 0; k < nk; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
-            }
+            resolve_value_bytes(ctx, kimp, nkimp);
+            for (int k = 0; k < nkimp && k < 8; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
             // first choice: the kernel specialised at run time for this plan; otherwise the generic ahead-of-time kernel
             AggProgram fprog = build_prog(PREFIX);
             if (accumulate_lowcard_jit(ctx, fprog, m, groups, fl) || accumulate_private(ctx, fprog, nullptr, m, groups, nullptr, &fl)) {
@@ -208,14 +213,14 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     if (raw) {
         accumulate(ctx, build_prog(0), op->ids.as<int32_t>(), n, groups);
     } else {
+        DCol s0[MAX_AGGS], s1[MAX_AGGS];
+        memset(s1, 0, sizeof(s1));
         for (size_t i = 0; i < op->aggs.size(); i++) {
             const pg_agg_spec& s = op->specs[i];
-            pg_agg* a = op->aggs[i];
-            DCol s0 = need(s.input_channel);
-            DCol s1; memset(&s1, 0, sizeof(s1));
-            if (agg_n_intermediate(a) > 1) s1 = need(s.input_channel + 1);
-            accumulate_intermediate(a, s0, s1, op->ids.as<int32_t>(), n, groups);
+            s0[i] = need(s.input_channel);
+            if (agg_n_intermediate(op->aggs[i]) > 1) s1[i] = need(s.input_channel + 1);
         }
+        accumulate_intermediate_batch(ctx, op->aggs.data(), s0, s1, (int)op->aggs.size(), op->ids.as<int32_t>(), n, groups);
     }
     op->input_rows += n;
     sync(ctx);   // staged host columns are released when `imp` goes out of scope
@@ -345,11 +350,7 @@ int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_o
         const int na = (int)op->aggs.size();
         DevBuf errs(ctx, 8 * (na > 0 ? na : 1));       // one sticky "first overflowing group" word per aggregate
         memset_async(ctx, errs.p, 0x7f, 8 * (na > 0 ? na : 1));
-        for (int i = 0; i < na; i++) {
-            pg_agg* a = op->aggs[i];
-            agg_evaluate_async(a, first, n, partial ? 0 : 1, out + col, errs.as<long long>() + i);
-            col += partial ? agg_n_intermediate(a) : 1;
-        }
+        agg_evaluate_batch(ctx, op->aggs.data(), na, first, n, partial ? 0 : 1, out + col, errs.as<long long>());
         int64_t eg[MAX_AGGS];
         if (na > 0) {
             read_scalars(ctx, errs.p, na, eg);          // also completes the copies into host output columns

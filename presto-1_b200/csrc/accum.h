@@ -74,7 +74,7 @@ struct FusedLookup {
     const uint8_t* arena;
     const int64_t* values_by_group;
     int32_t bigint_mode, null_gid;
-    uint8_t* miss_flag;               // n bytes, zeroed by the caller
+    unsigned int* miss_flag;          // bitmap of n bits, zeroed by the caller
     unsigned long long* d_miss;       // device counter, zeroed by the caller
     int64_t row_base;                 // page row of the first row handed in (variable width offsets are page-absolute)
     int64_t key_value_bytes[8];       // value buffer size of variable width key columns

@@ -57,7 +57,7 @@ struct PackSpec {
     const uint64_t* key_rows;         // stored groups (GroupByHash key store)
     const uint8_t* arena;
     const int64_t* values_by_group;   // bigint mode
-    uint8_t* miss_flag;               // set to 1 for rows the fused pass could not resolve
+    unsigned int* miss_flag;          // bitmap: bit set for rows the fused pass could not resolve
     unsigned long long* d_miss;
 };
 
@@ -162,7 +162,7 @@ struct RowData {
 };
 
 // FUSED = true: the group id of a row is resolved inside this kernel from the packed key (no id column in HBM); rows that
-// cannot be resolved are flagged in miss_flag and counted in *d_miss — the caller runs the general path for exactly those.
+// cannot be resolved are flagged in the miss_flag bitmap and counted in *d_miss — the caller runs the general path for exactly those.
 template <int T, bool FUSED>
 __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, const int32_t* __restrict__ gids, int64_t n, int G,
                                                          const uint8_t* __restrict__ only_rows, const PackSpec pk) {
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(T) acc_private2_kernel(const PrivPlan plan, co
                     h = (h + 1) & (LUT_SIZE - 1);
                 }
             }
-            if (r.g < 0) { misses++; pk.miss_flag[row] = 1; return; }
+            if (r.g < 0) { misses++; atomicOr(&pk.miss_flag[row >> 5], 1u << (row & 31)); return; }
         } else {
             r.g = gids[row];
             if (only_rows != nullptr && only_rows[row] == 0) { r.g = -1; return; }
@@ -514,7 +514,8 @@ bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids
     int64_t smem = per_thread * T;
     int blocks_per_sm = (int)(budget / smem);
     if (blocks_per_sm > 2048 / T) blocks_per_sm = 2048 / T;
-    int64_t want = (n + T - 1) / T;
+    static const int min_rows = getenv("PRESTOGPU_PRIV_ROWS") ? atoi(getenv("PRESTOGPU_PRIV_ROWS")) : 1;
+    int64_t want = (n + (int64_t)T * min_rows - 1) / ((int64_t)T * min_rows);
     int64_t grid = (int64_t)ctx->sm_count * blocks_per_sm;
     if (grid > want) grid = want;
 #define PG_PRIV_LAUNCH(TT, FF)                                                                                               \

@@ -46,7 +46,13 @@ static bool step_input_raw(int s) { return s == PG_STEP_SINGLE || s == PG_STEP_P
 static bool step_output_partial(int s) { return s == PG_STEP_PARTIAL || s == PG_STEP_INTERMEDIATE; }
 
 
-static void hashagg_build(pg_hashagg* op) {
+static __global__ void expand_bits_kernel(const unsigned int* __restrict__ bits, int64_t n, uint8_t* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out[i] = (bits[i >> 5] >> (i & 31)) & 1u;
+}
+
+void hashagg_build(pg_hashagg* op) {
     groupby_create(op->ctx, op->key_types.data(), (int32_t)op->key_types.size(), op->hash_channel >= 0 ? 1 : 0, op->expected, &op->gb);
     for (const pg_agg_spec& s : op->specs) {
         pg_agg* a = nullptr;
@@ -99,7 +105,7 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         }
         return prog;
     };
-    auto generic_rows = [&](int64_t off, int64_t m, const uint8_t* only_rows) {
+    auto generic_rows = [&](int64_t off, int64_t m, const uint8_t* only_rows, bool with_aggregates = true) {
         KeyCols kco = kc;
         for (size_t k = 0; k < op->key_channels.size(); k++) kco.c[k] = dcol_offset(kc.c[k], off);
         DCol hco = hc;
@@ -108,7 +114,7 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         groupby_process(op->gb, kco, has_hash ? &hco : nullptr, m, op->ids.as<int32_t>());
         if (op->aggs.empty()) return;
         for (pg_agg* a : op->aggs) agg_ensure_capacity(a, op->gb->groups);
-        if (raw) accumulate(ctx, build_prog(off), op->ids.as<int32_t>(), m, op->gb->groups, only_rows);
+        if (raw && with_aggregates) accumulate(ctx, build_prog(off), op->ids.as<int32_t>(), m, op->gb->groups, only_rows);
     };
     // Large raw pages: a short prefix goes through the general path and numbers the groups; if there are only a few and
     // the keys are short, the rest is resolved and accumulated in ONE kernel (packed-key look-up in shared memory, private
@@ -166,15 +172,21 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
             for (int k = 0; k < nkimp; k++) bound += pb[k];
             op->gb->var_bound_hint = bound;
         }
-        generic_rows(0, PREFIX, nullptr);
+        generic_rows(0, PREFIX, nullptr, false);   // numbers the prefix's groups; its rows are accumulated below
         op->gb->var_bound_hint = -1;
-        int64_t groups = op->gb->groups, m = n - PREFIX;
+        const int64_t groups = op->gb->groups;
+        bool prefix_done = false;
+        auto accumulate_prefix = [&] {   // general path for the prefix rows (their ids are still in op->ids)
+            if (!prefix_done) accumulate(ctx, build_prog(0), op->ids.as<int32_t>(), PREFIX, groups);
+            prefix_done = true;
+        };
         if (groups <= 64) {
-            DevBuf miss_flag(ctx, m), miss_cnt(ctx, 8);
-            memset_async(ctx, miss_flag.p, 0, m);
-            memset_async(ctx, miss_cnt.p, 0, 8);
-            KeyCols kco = kc;
-            for (size_t k = 0; k < op->key_channels.size(); k++) kco.c[k] = dcol_offset(kc.c[k], PREFIX);
+            const int64_t miss_words = (n + 31) / 32;
+            DevBuf miss_flag(ctx, 8 + miss_words * 4);          // [miss count (8 bytes)][bitmap of rows left to the general path]
+            memset_async(ctx, miss_flag.p, 0, 8 + miss_words * 4);
+            unsigned long long* d_miss_cnt = miss_flag.as<unsigned long long>();
+            unsigned int* d_miss_bits = (unsigned int*)(d_miss_cnt + 1);
+            KeyCols kco;
             FusedLookup fl;
             fl.layout = &op->gb->layout; fl.keys = &kco; fl.key_rows = op->gb->key_rows.as<uint64_t>(); fl.arena = op->gb->arena.as<uint8_t>();
             fl.values_by_group = op->gb->values_by_group.as<int64_t>(); fl.bigint_mode = op->gb->bigint_mode ? 1 : 0;
@@ -184,20 +196,35 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
                 read_scalars(ctx, op->gb->slots.as<Slot>() + op->gb->cap + 1, 2, sp);   // the null group's slot {word, gid|first_row}
                 fl.null_gid = (int32_t)(sp[1] & 0xffffffff);
             }
-            fl.miss_flag = miss_flag.as<uint8_t>(); fl.d_miss = miss_cnt.as<unsigned long long>();
-            fl.row_base = PREFIX;
+            fl.miss_flag = d_miss_bits; fl.d_miss = d_miss_cnt;
             resolve_value_bytes(ctx, kimp, nkimp);
             for (int k = 0; k < nkimp && k < 8; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
-            // first choice: the kernel specialised at run time for this plan; otherwise the generic ahead-of-time kernel
-            AggProgram fprog = build_prog(PREFIX);
-            if (accumulate_lowcard_jit(ctx, fprog, m, groups, fl) || accumulate_private(ctx, fprog, nullptr, m, groups, nullptr, &fl)) {
+            auto rows_from = [&](int64_t off) {
+                kco = kc;
+                for (size_t k = 0; k < op->key_channels.size(); k++) kco.c[k] = dcol_offset(kc.c[k], off);
+                fl.row_base = off;
+            };
+            auto leftovers = [&](int64_t off, int64_t m) {   // rows the fused kernel could not resolve take the general path
                 int64_t misses;
-                read_scalars(ctx, miss_cnt.p, 1, &misses);
-                if (misses > 0) generic_rows(PREFIX, m, miss_flag.as<uint8_t>());
+                read_scalars(ctx, d_miss_cnt, 1, &misses);
+                if (misses > 0) {
+                    DevBuf only(ctx, m);
+                    PG_LAUNCH(ctx, expand_bits_kernel, grid_for(ctx, m, 256, 4), 256, 0, d_miss_bits, m, only.as<uint8_t>());
+                    generic_rows(off, m, only.as<uint8_t>());
+                }
                 fused_done = true;
+            };
+            // first choice: the kernel specialised at run time for this plan, over ALL rows of the page (the prefix rows
+            // resolve by construction); otherwise the prefix by ids and the rest by the generic ahead-of-time fused kernel
+            rows_from(0);
+            if (accumulate_lowcard_jit(ctx, build_prog(0), n, groups, fl)) leftovers(0, n);
+            else {
+                accumulate_prefix();
+                rows_from(PREFIX);
+                if (accumulate_private(ctx, build_prog(PREFIX), nullptr, n - PREFIX, groups, nullptr, &fl)) leftovers(PREFIX, n - PREFIX);
             }
         }
-        if (!fused_done) { generic_rows(PREFIX, n - PREFIX, nullptr); fused_done = true; }
+        if (!fused_done) { accumulate_prefix(); generic_rows(PREFIX, n - PREFIX, nullptr); fused_done = true; }
     }
     op->rows_since_reset += n;
     if (fused_done) {

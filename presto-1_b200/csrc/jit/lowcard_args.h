@@ -38,7 +38,7 @@ struct PgjArgs {
     const unsigned long long* key_rows;
     const unsigned char* arena;
     const long long* values_by_group;
-    unsigned char* miss_flag;        // set to 1 for rows whose key is not in the table (zeroed by the caller)
+    unsigned int* miss_flag;         // bitmap: bit set for rows whose key is not in the table (zeroed by the caller)
     unsigned long long* d_miss;      // number of such rows
     long long n;
     long long row_base;              // page row of row 0 (variable width offsets are absolute within the page)

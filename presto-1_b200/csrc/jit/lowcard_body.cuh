@@ -254,7 +254,7 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
     // ---- phase B: update the thread's private records, row by row (two rows may share a group)
 #pragma unroll
     for (int v = 0; v < V; v++) {
-        if (g[v] < 0) { misses++; a.miss_flag[row + v] = 1; continue; }
+        if (g[v] < 0) { misses++; atomicOr(&a.miss_flag[(row + v) >> 5], 1u << ((row + v) & 31)); continue; }
         u64* rec = table + (g[v] * PG_REC_WORDS) * PG_T + tid;
 #define PG_X(c, HASMASK, HASMASKNULLS, HASARGNULLS)                                                         \
         const bool PGJ_CAT(cond, c) = (!HASMASK || PGJ_CAT(cm, c)[v] != 0) && (!HASMASKNULLS || PGJ_CAT(cmn, c)[v] == 0) && \

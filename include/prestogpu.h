@@ -105,7 +105,7 @@ PG_API const char* pg_version(void);
  * GroupByHash  —  replaces OP/GroupByHash.java:31-88, OP/BigintGroupByHash.java:43-425,
  * OP/MultiChannelGroupByHash.java:55-853.
  * Exactly one BIGINT key -> the bigint table (16-byte slots, key in slot); anything else ->
- * the multi-channel table (8-byte slots + packed key rows).  Dispatch mirrors
+ * the multi-channel table (16-byte slots holding the row hash + packed key rows).  Dispatch mirrors
  * GroupByHash.createGroupByHash (OP/GroupByHash.java:45-59).
  * Group ids are dense and assigned in first-seen row order, like the reference.
  * ===================================================================================== */

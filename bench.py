@@ -365,12 +365,30 @@ def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0)
     ms, groups = timed(gb_pass, 3, 1)
     kern = ctx.kernel_report(reset=True)
     n_all, g_all = total(n), total(groups)
+    # size-independent properties of the full-size result (outside the timed region): one group per order, the counts
+    # add up to the rows, the decimal sums add up to the column sum (linearity), first-seen order = ascending first row
+    local = ex.exchange(page, [0]) if ex else page
+    chk = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=n_orders, ctx=ctx, device_output=True)
+    chk.add_input(local)
+    chk.finish()
+    gout = chk.get_output(max_rows=max(chk.get_group_count(), 1))
+    chk.close()
+    cnt_sum = total(gout.blocks[1].values.sum().item())
+    qty_sum = total(gout.blocks[2].values.view(-1, 2)[:, 0].sum().item())     # long decimal: low words (sums are far below 2^63)
+    gb_check = {"groups_equal_orders": g_all == total(n_orders), "count_sum_equals_rows": cnt_sum == n_all,
+                "decimal_sum_equals_column_sum": qty_sum == total(li["quantity"].sum().item())}
+    if world == 1 and not args.extra_shuffle:
+        gb_check["keys_in_first_seen_order"] = bool(torch.equal(gout.blocks[0].values, torch.unique_consecutive(li["orderkey"])))
+    if not all(gb_check.values()):
+        raise SystemExit("bench self-check failed (GROUP BY orderkey): %s" % json.dumps(gb_check))
+    del gout, local
     brow = 136 + (48 if world > 1 else 0)   # + 2 x 24 B partition pass (read + write of key and inputs) when G > 1
     res["groupby_orderkey"] = {"workload": "GROUP BY orderkey over lineitem SF%g per GPU: count(*), sum(quantity decimal), sum(extendedprice double)%s"
                                            % (sf, "; hash-partitioned all-to-all then SINGLE per GPU" if world > 1 else ""),
                                "rows": n_all, "groups": g_all, "ms_per_step": round(ms, 3), "rows_per_s": n_all / (ms / 1e3),
                                "algorithmic_bytes_per_row": brow, "hbm_frac_per_gpu": round(n_all / world * brow / (ms / 1e3) / 1e9 / peak, 4),
-                               "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:8]}}
+                               "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:8]},
+                               "selfcheck": gb_check}
     del page
     # ---- join: build orders (orderkey unique, totalprice), probe lineitem.orderkey, gather totalprice
     od = tpch.orders(sf, seed=42 + rank, device="cuda")
@@ -399,6 +417,17 @@ def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0)
     pkern = ctx.kernel_report(reset=True)
     ctx.set_timing(False)
     o_all, m_all = total(n_orders), total(matches)
+    # every probe row matches exactly one build row; on one GPU the gathered payload must equal a torch gather
+    join_check = {"matches_equal_probe_rows": m_all == n_all}
+    if world == 1:
+        pp, bp = ls.join_page([ppage.blocks[0]], None, P.JOIN_INNER, device=True, capacity=max(n, 1))
+        got = ls.append_to(bp, [1], device=True)[0].values
+        want = od["totalprice"].view(torch.int64)[torch.searchsorted(od["orderkey"], li["orderkey"])]
+        join_check["probe_positions_ascending"] = bool(torch.equal(pp, torch.arange(n, device="cuda", dtype=torch.int32)))
+        join_check["gathered_payload_bit_exact"] = bool(torch.equal(got.view(torch.int64), want))
+        del pp, bp, got, want
+    if not all(join_check.values()):
+        raise SystemExit("bench self-check failed (join): %s" % json.dumps(join_check))
     res["join_build"] = {"workload": "hash build orders SF%g per GPU (orderkey, totalprice)" % sf, "rows": o_all, "ms_per_step": round(bms, 3),
                          "rows_per_s": o_all / (bms / 1e3), "algorithmic_bytes_per_row": 32,
                          "hbm_frac_per_gpu": round(o_all / world * 32 / (bms / 1e3) / 1e9 / peak, 4),
@@ -406,7 +435,8 @@ def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0)
     res["join_probe"] = {"workload": "INNER join probe lineitem.orderkey -> orders SF%g per GPU, emit (probe idx, build pos) + gather totalprice" % sf,
                          "rows": n_all, "matches": m_all, "ms_per_step": round(pms, 3), "rows_per_s": n_all / (pms / 1e3),
                          "algorithmic_bytes_per_row": 44, "hbm_frac_per_gpu": round(n_all / world * 44 / (pms / 1e3) / 1e9 / peak, 4),
-                         "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(pkern.items(), key=lambda kv: -kv[1][0])[:6]}}
+                         "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(pkern.items(), key=lambda kv: -kv[1][0])[:6]},
+                         "selfcheck": join_check}
     if ex:
         res["exchange"] = {"rows_sent_per_rank": ex.sent_rows, "bytes_sent_per_rank": ex.bytes_sent, "collective": "NCCL all_to_all_single per column"}
     return res

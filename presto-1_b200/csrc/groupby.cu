@@ -481,7 +481,7 @@ static void rebuild_table(pg_groupby* gb, int64_t new_cap) {
 }
 
 void groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys, int32_t has_hash_channel, int64_t expected,
-                    pg_groupby** out) {
+                    pg_groupby** out, bool lazy_table) {
     PG_CHECK_ARG(out != nullptr && key_types != nullptr, "null argument");
     PG_CHECK_ARG(nkeys >= 1 && nkeys <= MAX_KEYS, "between 1 and %d group-by channels are supported, got %d", MAX_KEYS, nkeys);
     PG_CHECK_ARG(expected > 0, "expectedSize must be greater than zero");   // BigintGroupByHash.java:82
@@ -507,6 +507,9 @@ void groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys, int32_
         gb->meta.alloc(ctx, sizeof(GbMeta));
         memset_async(ctx, gb->meta.p, 0, sizeof(GbMeta));
         int64_t cap = gb->ref_capacity < MIN_PHYS_CAP ? MIN_PHYS_CAP : gb->ref_capacity;
+        // lazy_table: the fused operator may never use this table (its many-groups path keeps its own): start with the smallest
+        // one and build the planned one when the first rows are inserted
+        if (lazy_table && cap > MIN_PHYS_CAP) { gb->deferred_cap = cap; cap = MIN_PHYS_CAP; }
         rebuild_table(gb, cap);
         if (gb->has_var) gb->arena.alloc(ctx, 1 << 20);
     } catch (...) {
@@ -524,6 +527,12 @@ int64_t groupby_device_bytes(const pg_groupby* gb) {
 static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_col, int64_t n, int32_t* d_out_ids) {
     pg_ctx* ctx = gb->ctx;
     if (n <= 0) return;
+    if (gb->deferred_cap > gb->cap) {
+        const int64_t planned = gb->deferred_cap, before = gb->rehashes;
+        gb->deferred_cap = 0;
+        rebuild_table(gb, planned);
+        gb->rehashes = before;          // not a rehash the reference would have done
+    }
     const KeyLayout& L = gb->layout;
     DCol hc; memset(&hc, 0, sizeof(hc));
     int has_hash = 0;

@@ -69,6 +69,7 @@ struct pg_groupby {
     pg::KeyLayout layout;
     int64_t expected = 0;
     int64_t cap = 0;          // physical slots (power of two), excluding the two special slots
+    int64_t deferred_cap = 0; // lazy_table: the planned size, built when the first rows are inserted
     int64_t max_fill = 0;     // physical fill limit
     int64_t occupied = 0;     // claimed regular slots (assigned + pending)
     int64_t groups = 0;       // host copy of meta.group_count
@@ -86,6 +87,6 @@ namespace pg {
 // d_out_ids may be null (addPage).  keys are device views with n rows.
 void groupby_process(pg_groupby* gb, const KeyCols& keys, const DCol* hash_col, int64_t n, int32_t* d_out_ids);
 void groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys, int32_t has_hash_channel, int64_t expected,
-                    pg_groupby** out);
+                    pg_groupby** out, bool lazy_table = false);
 int64_t groupby_device_bytes(const pg_groupby* gb);
 }  // namespace pg

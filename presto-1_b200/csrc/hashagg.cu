@@ -53,7 +53,7 @@ static __global__ void expand_bits_kernel(const unsigned int* __restrict__ bits,
 }
 
 void hashagg_build(pg_hashagg* op) {
-    groupby_create(op->ctx, op->key_types.data(), (int32_t)op->key_types.size(), op->hash_channel >= 0 ? 1 : 0, op->expected, &op->gb);
+    groupby_create(op->ctx, op->key_types.data(), (int32_t)op->key_types.size(), op->hash_channel >= 0 ? 1 : 0, op->expected, &op->gb, true);
     for (const pg_agg_spec& s : op->specs) {
         pg_agg* a = nullptr;
         agg_create(op->ctx, s.kind, s.in_type, &a);
@@ -131,13 +131,16 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         if (wide_on && !op->wide && op->rows_since_reset == 0 && op->gb->groups == 0 && n >= 256 * 1024 && wide_supported(op->specs, op->aggs) &&
             jit_available()) {
             int64_t repeats = 0;
-            const int64_t d = sample_distinct_keys(ctx, kc.c[0], 2048, &repeats);
-            if (d > 128 && (wide_always || repeats * 4 < 2048)) {
-                int64_t est = (int64_t)((double)d / 2048.0 * (double)n);
-                if (est > n / 2) est = n / 2;
-                int64_t target = op->expected * 4 >= est ? op->expected : est;
-                op->wide = wide_create(ctx, op->specs, op->aggs, op->step, target);
-            }
+            KeySample ks;
+            const int64_t d = sample_distinct_keys(ctx, kc.c[0], 2048, &repeats, &ks);
+            int64_t est = (int64_t)((double)d / 2048.0 * (double)n);
+            if (est > n / 2) est = n / 2;
+            const int64_t target = op->expected * 4 >= est ? op->expected : est;
+            // rows sorted by key: the range-chunked front region makes the bucket accesses sequential; rows in no key order: one
+            // random access per row beats the general path's two; rows clustered by key but not sorted: the general path
+            const bool sorted = d > 128 && wide_range_applicable(ks) && !(getenv("PRESTOGPU_WIDE_RANGE") && getenv("PRESTOGPU_WIDE_RANGE")[0] == '0');
+            if (d > 128 && (wide_always || sorted || repeats * 4 < 2048))
+                op->wide = wide_create(ctx, op->specs, op->aggs, op->step, target, sorted ? &ks : nullptr);
         }
         if (op->wide) {
             std::vector<DCol> wargs(op->aggs.size()), wmasks(op->aggs.size());

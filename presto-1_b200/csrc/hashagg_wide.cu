@@ -7,6 +7,7 @@
 #include "hashagg_wide.h"
 
 #include <stdio.h>
+#include <algorithm>
 #include <stdlib.h>
 
 #include "jit.h"
@@ -23,6 +24,7 @@ const char* op_name(int op) {
     switch (op) { case OP_COUNT: return "CNT"; case OP_SUM_I64: return "SUMI64"; case OP_SUM_F64: return "SUMF64"; default: return "SUMDEC"; }
 }
 const int WIDE_THREADS = 256;
+const int WIDE_CHUNK = 32;     // buckets per chunk of the front region (jit/wide_body.cuh: PGW_CHUNK)
 
 __device__ __forceinline__ unsigned long long w_fmix64(unsigned long long k) {
     k ^= k >> 33; k *= 0xff51afd7ed558ccdULL; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ULL; k ^= k >> 33;
@@ -50,13 +52,21 @@ __global__ void wide_rebuild_kernel(const unsigned long long* old_table, int64_t
     }
 }
 
-// ---- output numbering
-__global__ void wide_mark_first_rows_kernel(const unsigned long long* table, int64_t cap, int bw, uint32_t* bitmap) {
+// ---- output numbering.  Buckets are addressed by one index: [0, F) the front region, [F, F + cap) the table, then the two extra buckets
+struct WideView {
+    const unsigned long long* front;
+    const unsigned long long* table;
+    int64_t F, cap;
+    int bw;
+    __device__ __forceinline__ const unsigned long long* at(int64_t i) const { return i < F ? front + i * bw : table + (i - F) * bw; }
+    __device__ __forceinline__ int64_t total() const { return F + cap + 2; }
+};
+__global__ void wide_mark_first_rows_kernel(WideView v, uint32_t* bitmap) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; i < cap + 2; i += stride) {
-        const unsigned long long* b = table + i * bw;
-        if (i < cap ? b[0] == 0 : b[1] == 0) continue;
+    for (; i < v.total(); i += stride) {
+        const unsigned long long* b = v.at(i);
+        if (i < v.F + v.cap ? b[0] == 0 : b[1] == 0) continue;
         const unsigned long long row = ~b[1];
         atomicOr(bitmap + (row >> 5), 1u << (row & 31));
     }
@@ -116,12 +126,13 @@ struct GatherPlan {
     unsigned long long* state[PGW_MAX_AGGS];
 };
 // group id of every occupied bucket -> bucket_of_group[gid] (4-byte writes into an array that mostly lives in L2)
-__global__ void wide_number_buckets_kernel(const unsigned long long* table, int64_t cap, int bw, const uint32_t* bitmap, const uint32_t* word_prefix,
+__global__ void wide_number_buckets_kernel(WideView v, const uint32_t* bitmap, const uint32_t* word_prefix,
                                            uint32_t* bucket_of_group, Slot* special) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; i < cap + 2; i += stride) {
-        const unsigned long long* b = table + i * bw;
+    const int64_t cap = v.F + v.cap;
+    for (; i < v.total(); i += stride) {
+        const unsigned long long* b = v.at(i);
         if (i < cap ? b[0] == 0 : b[1] == 0) continue;
         const unsigned long long row = ~b[1];
         const uint32_t word = bitmap[row >> 5];
@@ -151,13 +162,14 @@ __device__ __forceinline__ void add_limb(unsigned long long* w, unsigned long lo
     }
 }
 // in group-id order: read the group's bucket (one random 64..160 byte read), write keys and dense states (coalesced)
-__global__ void wide_gather_kernel(const unsigned long long* table, int64_t cap, GatherPlan p, const uint32_t* bucket_of_group, int64_t groups,
+__global__ void wide_gather_kernel(WideView v, GatherPlan p, const uint32_t* bucket_of_group, int64_t groups,
                                    int64_t* values_by_group) {
     int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t cap = v.F + v.cap;
     for (; g < groups; g += stride) {
         const int64_t i = bucket_of_group[g];
-        const unsigned long long* b = table + i * p.bw;
+        const unsigned long long* b = v.at(i);
         values_by_group[g] = i >= cap ? 0 : (int64_t)b[0];
         const unsigned long long flags = p.flag_word >= 0 ? b[p.flag_word] : 0;
         for (int a = 0; a < p.naggs; a++) {
@@ -195,15 +207,25 @@ __global__ void __launch_bounds__(1024) wide_sample_distinct_kernel(const long l
             h = (h + 1) & 4095;
         }
     }
-    // rows that repeat the key of the row before them: input clustered by key (TPC-H lineitem by order key)
-    unsigned int rep = 0;
-    for (int i = threadIdx.x + 1; i < n; i += blockDim.x) rep += keys[i] == keys[i - 1] ? 1u : 0u;
-    __shared__ unsigned int repeats;
-    if (threadIdx.x == 0) repeats = 0;
+    // rows that repeat the key of the row before them: input clustered by key (TPC-H lineitem by order key);
+    // rows whose key is not below their predecessor's: input (nearly) sorted by key; the sample's key range gives the key density
+    unsigned int rep = 0, asc = 0;
+    long long lo = 0x7fffffffffffffffLL, hi = -0x7fffffffffffffffLL - 1;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        if (nulls && nulls[i]) continue;
+        const long long k = keys[i];
+        lo = k < lo ? k : lo; hi = k > hi ? k : hi;
+        if (i > 0 && !(nulls && nulls[i - 1])) { rep += k == keys[i - 1] ? 1u : 0u; asc += k >= keys[i - 1] ? 1u : 0u; }
+    }
+    __shared__ unsigned int repeats, ascending;
+    __shared__ long long s_lo, s_hi;
+    if (threadIdx.x == 0) { repeats = 0; ascending = 0; s_lo = 0x7fffffffffffffffLL; s_hi = -0x7fffffffffffffffLL - 1; }
     __syncthreads();
     if (rep) atomicAdd(&repeats, rep);
+    if (asc) atomicAdd(&ascending, asc);
+    atomicMin(&s_lo, lo); atomicMax(&s_hi, hi);
     __syncthreads();
-    if (threadIdx.x == 0) { out[0] = distinct; out[1] = repeats; }
+    if (threadIdx.x == 0) { out[0] = distinct; out[1] = repeats; out[2] = (unsigned long long)s_lo; out[3] = (unsigned long long)s_hi; out[4] = ascending; }
 }
 
 int64_t pick_cap(int64_t groups) {
@@ -233,13 +255,14 @@ void grow(WideTable* w, int64_t min_groups) {
 
 }  // namespace
 
-int64_t sample_distinct_keys(pg_ctx* ctx, const DCol& key, int64_t sample, int64_t* adjacent_repeats) {
+int64_t sample_distinct_keys(pg_ctx* ctx, const DCol& key, int64_t sample, int64_t* adjacent_repeats, KeySample* more) {
     if (sample > 2048) sample = 2048;
-    DevBuf out(ctx, 16);
+    DevBuf out(ctx, 40);
     PG_LAUNCH(ctx, wide_sample_distinct_kernel, 1, 1024, 0, (const long long*)key.values, key.nulls, (int)sample, out.as<unsigned long long>());
-    int64_t d[2];
-    read_scalars(ctx, out.p, 2, d);
+    int64_t d[5];
+    read_scalars(ctx, out.p, 5, d);
     if (adjacent_repeats) *adjacent_repeats = d[1];
+    if (more) { more->distinct = d[0]; more->repeats = d[1]; more->min_key = d[2]; more->max_key = d[3]; more->ascending = d[4]; more->rows = sample; }
     return d[0];
 }
 
@@ -260,7 +283,15 @@ bool wide_supported(const std::vector<pg_agg_spec>& specs, const std::vector<pg_
     return true;
 }
 
-WideTable* wide_create(pg_ctx* ctx, const std::vector<pg_agg_spec>& specs, const std::vector<pg_agg*>& aggs, int32_t step, int64_t expected_groups) {
+bool wide_range_applicable(const KeySample& s) {
+    if (s.rows < 1024 || s.distinct < 128 || s.max_key <= s.min_key) return false;
+    if (s.ascending * 100 < (s.rows - 1) * 98) return false;                                // not sorted by key
+    const double density = (double)s.distinct / ((double)s.max_key - (double)s.min_key + 1.0);
+    return density >= 1.0 / 4096.0;
+}
+
+WideTable* wide_create(pg_ctx* ctx, const std::vector<pg_agg_spec>& specs, const std::vector<pg_agg*>& aggs, int32_t step, int64_t expected_groups,
+                       const KeySample* sorted_sample) {
     WideTable* w = new WideTable();
     try {
         w->ctx = ctx;
@@ -291,8 +322,28 @@ WideTable* wide_create(pg_ctx* ctx, const std::vector<pg_agg_spec>& specs, const
             words += wa.val_words;
         }
         w->bucket_words = (words + 3) & ~3;
-        w->counters.alloc(ctx, 16);
-        alloc_table(w, pick_cap(expected_groups > 0 ? expected_groups : 0));
+        w->counters.alloc(ctx, 32);
+        const char* renv = getenv("PRESTOGPU_WIDE_RANGE");
+        if (sorted_sample && expected_groups > 0 && !(renv && renv[0] == '0') && wide_range_applicable(*sorted_sample)) {
+            // between 11 and 22 keys per chunk of 32 buckets at the sample's key density (a chunk that fills up spills into the table);
+            // the region spans the key range `expected_groups` keys need
+            const double density = (double)sorted_sample->distinct / ((double)sorted_sample->max_key - (double)sorted_sample->min_key + 1.0);
+            const double width = (WIDE_CHUNK * 0.6875) / density;
+            int shift = 0;
+            while (shift < 40 && (double)(2ULL << shift) <= width) shift++;      // largest power of two <= width
+            const double span = (double)expected_groups / density * 1.02;
+            const int64_t nseg = (int64_t)(span / (double)(1ULL << shift)) + 2;
+            const int64_t fb = nseg * WIDE_CHUNK;
+            if (fb < (1LL << 31) && (double)fb <= 2.5 * ((double)expected_groups / 0.55)) {
+                w->range = true; w->k0 = sorted_sample->min_key; w->shift = shift; w->nseg = nseg; w->front_buckets = fb;
+                w->front.alloc(ctx, fb * w->bucket_words * 8);
+                memset_async(ctx, w->front.p, 0, w->front.bytes);
+                w->front_keys.alloc(ctx, fb * 8);
+                memset_async(ctx, w->front_keys.p, 0, w->front_keys.bytes);
+            }
+        }
+        // with a front region the table only takes the keys the region cannot: it starts small and grows on demand
+        alloc_table(w, pick_cap(expected_groups > 0 ? (w->range ? std::max<int64_t>(expected_groups / 32, 2 * 1024 * 1024) : expected_groups) : 0));
         (void)specs;
     } catch (...) { delete w; throw; }
     return w;
@@ -317,6 +368,14 @@ bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const D
     snprintf(buf, sizeof(buf), "#define PGW_BUCKET_WORDS %d\n#define PGW_HASKEYNULL %d\n#define PGW_FLAGWORD %d\n#define PGW_VEC %d\n", w->bucket_words,
              key.nulls ? 1 : 0, w->flag_word, vec);
     pre += buf;
+    pre += w->range ? "#define PGW_RANGE 1\n" : "#define PGW_RANGE 0\n";
+    int minb = 3;
+    if (const char* e = getenv("PRESTOGPU_WIDE_MINB")) { if (atoi(e) >= 1 && atoi(e) <= 8) minb = atoi(e); }
+    snprintf(buf, sizeof(buf), "#define PGW_MINB %d\n#define PGW_PREFETCH %d\n#define PGW_LDCA %d\n", minb, getenv("PRESTOGPU_WIDE_NOPF") ? 0 : 1,
+             getenv("PRESTOGPU_WIDE_LDCG") ? 0 : 1);
+    pre += buf;
+    if (getenv("PRESTOGPU_EXP_NORED")) pre += "#define PGW_EXP_NORED 1\n";
+    if (getenv("PRESTOGPU_EXP_NOLOCATE")) pre += "#define PGW_EXP_NOLOCATE 1\n";
     std::string aggs_macro = "#define PGW_AGGS(X)";
     for (size_t i = 0; i < w->aggs.size(); i++) {
         const WideAgg& a = w->aggs[i];
@@ -328,6 +387,10 @@ bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const D
         aggs_macro += buf;
     }
     pre += aggs_macro + "\n";
+    bool flags_unconditional = !key.nulls;     // (rows with a null key share one bucket with every kind of row; keep the atomic there)
+    for (size_t i = 0; i < w->aggs.size(); i++)
+        if (w->aggs[i].cnt_mode == 1 && (masks[i].values || (w->aggs[i].skip_null && args_cols[i].nulls))) flags_unconditional = false;
+    pre += flags_unconditional ? "#define PGW_FLAGS_UNCONDITIONAL 1\n" : "#define PGW_FLAGS_UNCONDITIONAL 0\n";
     // variants: [only] honours only_rows (re-run of left-out rows); [quota] bounds the claims of every block
     JitKernel* kern[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
     auto get_kernel = [&](int only, int quota) -> JitKernel* {
@@ -348,33 +411,50 @@ bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const D
     }
     a.n = n; a.row_base = row_base;
     a.counters = w->counters.as<unsigned long long>();
+    a.front = w->front.as<unsigned long long>(); a.front_keys = w->front_keys.as<unsigned long long>(); a.k0 = w->k0; a.nseg = (unsigned long long)w->nseg; a.shift = w->shift;
     DevBuf flags[2];               // left-out markers: written by launch i, read as the row filter by launch i + 1
     int cur = 0;
     const uint8_t* only = nullptr;
     int64_t pending = n;           // upper bound of the buckets the rows still to run can claim
-    const int grid = grid_for(ctx, n, WIDE_THREADS, vec, 4);
+    // more blocks than are resident: the kernel waits on memory, SMs do not all progress at the same speed, and equal static shares
+    // would make every launch as slow as its slowest SM (measured with rows in random order: 9.8 ms against 7.9 ms)
+    int per_sm = 32;
+    if (const char* e = getenv("PRESTOGPU_WIDE_GRID")) { if (atoi(e) > 0) per_sm = atoi(e); }
+    int grid = grid_for(ctx, n, WIDE_THREADS, vec, 4);
+    if (grid > ctx->sm_count * per_sm) grid = ctx->sm_count * per_sm;
+    // what the warps in flight can claim between two looks at the global claim counter (PGW_QUOTA): 8 resident warps per block slot,
+    // `vec` rows per lane; 4 block slots per SM is more than the kernel's registers allow
+    const int64_t in_flight = (int64_t)ctx->sm_total * 4 * (WIDE_THREADS / 32) * 32 * vec;
     while (true) {
         int64_t room = w->max_fill - w->claimed;
-        if (room < pending && room < grid * 64LL) { grow(w, w->claimed + pending); continue; }
-        int64_t quota = room >= pending ? (int64_t)0x7fffffff : room / grid;
+        // (with a front region `pending` overstates the table's share by far: grow geometrically, the left-out re-run does the rest)
+        if (room < pending && room < 2 * in_flight) { grow(w, w->range ? 2 * w->claimed + 4 * in_flight : w->claimed + pending); continue; }
+        // claims beyond max_fill are tolerated up to 0.9 of the buckets within one launch (the table is grown before the next page)
+        const int64_t hard_room = (int64_t)(w->cap * 0.9) - w->claimed - in_flight;
+        const int64_t quota = room >= pending ? (int64_t)1 << 62 : hard_room;
         if (!flags[cur].p) flags[cur].alloc(ctx, n);
         memset_async(ctx, flags[cur].p, 0, n);
-        memset_async(ctx, w->counters.p, 0, 16);
-        a.table = w->table.as<unsigned long long>(); a.cap = w->cap; a.quota = (unsigned int)quota;
+        memset_async(ctx, w->counters.p, 0, 32);
+        a.table = w->table.as<unsigned long long>(); a.cap = w->cap; a.room = (unsigned long long)quota;
         a.only_rows = only; a.overflow_flag = flags[cur].as<uint8_t>();
         JitKernel* k = get_kernel(only ? 1 : 0, room >= pending ? 0 : 1);
         if (!k) fail(PG_E_INTERNAL, "specialised kernel unavailable for the re-run: %s", ctx->jit ? ctx->jit->last_error.c_str() : "");
         void* kargs[] = {&a};
         jit_launch(ctx, k, "wide_agg_jit", grid, WIDE_THREADS, 0, kargs);
         // one read-back: claims, left-out rows, and whether the two extra buckets are in use
-        copy_async(ctx, ctx->h_scalar, w->counters.p, 16, cudaMemcpyDeviceToHost);
-        copy_async(ctx, ctx->h_scalar + 2, w->table.as<unsigned long long>() + w->cap * w->bucket_words + 1, 8, cudaMemcpyDeviceToHost);
-        copy_async(ctx, ctx->h_scalar + 3, w->table.as<unsigned long long>() + (w->cap + 1) * w->bucket_words + 1, 8, cudaMemcpyDeviceToHost);
+        copy_async(ctx, ctx->h_scalar, w->counters.p, 24, cudaMemcpyDeviceToHost);
+        copy_async(ctx, ctx->h_scalar + 3, w->table.as<unsigned long long>() + w->cap * w->bucket_words + 1, 8, cudaMemcpyDeviceToHost);
+        copy_async(ctx, ctx->h_scalar + 4, w->table.as<unsigned long long>() + (w->cap + 1) * w->bucket_words + 1, 8, cudaMemcpyDeviceToHost);
         sync(ctx);
         w->claimed += ctx->h_scalar[0];
+        w->front_claimed += ctx->h_scalar[2];
         const int64_t left_out = ctx->h_scalar[1];
-        w->null_seen = ctx->h_scalar[2] != 0;
-        w->zero_seen = ctx->h_scalar[3] != 0;
+        w->null_seen = ctx->h_scalar[3] != 0;
+        w->zero_seen = ctx->h_scalar[4] != 0;
+        if (getenv("PRESTOGPU_DEBUG"))
+            fprintf(stderr, "[wide] n=%lld cap=%lld room=%lld pending=%lld quota=%lld grid=%d -> claimed=%lld front=%lld left_out=%lld\n", (long long)n,
+                    (long long)w->cap, (long long)room, (long long)pending, (long long)quota, grid, (long long)w->claimed, (long long)w->front_claimed,
+                    (long long)left_out);
         if (left_out == 0) break;
         // some block ran out of quota: grow, then re-run exactly the rows that were left out
         grow(w, w->claimed + left_out);
@@ -392,8 +472,12 @@ void wide_prepare_output(WideTable* w, pg_groupby* gb, const std::vector<pg_agg*
     const int64_t nwords = (total_rows + 31) / 32 + 1;
     DevBuf bitmap(ctx, nwords * 4), prefix(ctx, nwords * 4);
     memset_async(ctx, bitmap.p, 0, nwords * 4);
-    const int grid = grid_for(ctx, w->cap + 2, 256);
-    PG_LAUNCH(ctx, wide_mark_first_rows_kernel, grid, 256, 0, w->table.as<unsigned long long>(), w->cap, w->bucket_words, bitmap.as<uint32_t>());
+    WideView view;
+    view.front = w->front.as<unsigned long long>(); view.table = w->table.as<unsigned long long>();
+    view.F = w->front_buckets; view.cap = w->cap; view.bw = w->bucket_words;
+    PG_CHECK_STATE(w->front_buckets + w->cap + 2 < (1LL << 32), "hash table exceeds the supported size");
+    const int grid = grid_for(ctx, w->front_buckets + w->cap + 2, 256);
+    PG_LAUNCH(ctx, wide_mark_first_rows_kernel, grid, 256, 0, view, bitmap.as<uint32_t>());
     const int64_t ntiles = num_tiles(nwords);
     DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
     PG_LAUNCH(ctx, wide_popc_tiles_kernel, (int)ntiles, SCAN_THREADS, 0, bitmap.as<uint32_t>(), nwords, tiles.as<Pair64>());
@@ -412,16 +496,18 @@ void wide_prepare_output(WideTable* w, pg_groupby* gb, const std::vector<pg_agg*
         p.state[i] = aggs[i]->state.as<unsigned long long>();
     }
     DevBuf bucket_of_group(ctx, (groups + 1) * 4);
-    PG_LAUNCH(ctx, wide_number_buckets_kernel, grid, 256, 0, w->table.as<unsigned long long>(), w->cap, w->bucket_words, bitmap.as<uint32_t>(),
+    PG_LAUNCH(ctx, wide_number_buckets_kernel, grid, 256, 0, view, bitmap.as<uint32_t>(),
               prefix.as<uint32_t>(), bucket_of_group.as<uint32_t>(), gb->slots.as<Slot>() + gb->cap);
     if (groups > 0)
-        PG_LAUNCH(ctx, wide_gather_kernel, grid_for(ctx, groups, 256), 256, 0, w->table.as<unsigned long long>(), w->cap, p,
+        PG_LAUNCH(ctx, wide_gather_kernel, grid_for(ctx, groups, 256), 256, 0, view, p,
                   bucket_of_group.as<uint32_t>(), groups, gb->values_by_group.as<int64_t>());
     gb->groups = groups;
     while (gb->groups >= max_fill_075(gb->ref_capacity) && gb->ref_capacity < (1LL << 30)) gb->ref_capacity *= 2;
     sync(ctx);
     w->prepared = true;
     w->table.release();
+    w->front.release();
+    w->front_keys.release();
 }
 
 }  // namespace pg

@@ -17,10 +17,18 @@ struct PgwArgs {
     long long cap;
     long long n;
     long long row_base;                    // operator-wide index of row 0 (first-seen order is kept across pages)
-    unsigned int quota;                    // buckets one block may claim in this launch
-    unsigned int pad;
-    unsigned long long* counters;          // [0] buckets claimed, [1] rows left out because the quota ran out
+    unsigned long long room;               // PGW_QUOTA: buckets of `table` this launch may claim; a warp stops claiming once counters[0] passed it
+    unsigned long long* counters;          // [0] buckets claimed in `table`, [1] rows left out because the quota ran out, [2] buckets claimed in `front`
     unsigned char* overflow_flag;          // n bytes, zeroed by the caller; 1 = row left out
+    // range-chunked front region (PGW_RANGE): keys of [k0, k0 + (nseg << shift)) live in chunk (key - k0) >> shift of PGW_CHUNK buckets,
+    // so rows that arrive sorted by key touch the table sequentially; a key whose chunk is full, or outside the range, uses `table`
+    unsigned long long* front;             // nseg * PGW_CHUNK buckets
+    unsigned long long* front_keys;        // the front buckets' keys once more, packed (8 bytes per bucket): probing reads these through L1 and
+                                           // claims with a compare-and-swap here; the claimer then copies the key into word 0 of the bucket
+    long long k0;
+    unsigned long long nseg;
+    int shift;
+    int pad2;
 };
 
 #endif

@@ -9,14 +9,21 @@
 //     word 2.. state words of the aggregates (counts, 32-bit-limb integer sums, double sums), zero = identity,
 //             so a zero-filled table is an empty table
 // Claims are atomicCAS on word 0; every state update is an atomic on the same line (resolved in L2).
-// The prelude defines PGW_BUCKET_WORDS, PGW_HASKEYNULL, PGW_HASONLY, PGW_QUOTA, PGW_FLAGWORD, PGW_VEC (rows per thread and trip: 1 or 4) and
+// The prelude defines PGW_RANGE (0/1: range-chunked front region, see wide_args.h), PGW_BUCKET_WORDS, PGW_HASKEYNULL, PGW_HASONLY, PGW_QUOTA, PGW_FLAGWORD, PGW_VEC (rows per thread and trip: 1 or 4) and
 //   PGW_AGGS(X)  X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)
 //     OP in {CNT, SUMI64, SUMF64, SUMDEC}; IN in {NONE, I64, I32, F64, I2F, DEC128}; CNTMODE in {C64, FLAG}
 
+#ifndef PGW_FLAGS_UNCONDITIONAL
+#define PGW_FLAGS_UNCONDITIONAL 0
+#endif
+#ifndef PGW_LDCA
+#define PGW_LDCA 1
+#endif
 typedef unsigned long long u64;
 typedef long long i64;
 typedef unsigned int u32;
 typedef unsigned char u8;
+#define PGW_CHUNK 32   // buckets per chunk of the front region (hashagg_wide.cu: WIDE_CHUNK)
 
 #define PGW_CAT2(a, b) a##b
 #define PGW_CAT(a, b) PGW_CAT2(a, b)
@@ -30,6 +37,12 @@ __device__ __forceinline__ u64 fmix64(u64 k) {
 // red.add (no carry to propagate, so no atomic has to return a value and no thread waits for L2); the top limb is signed.
 // A limb sum is exact for up to 2^32 rows per group; the limbs are recombined when the output is built (hashagg_wide.cu).
 __device__ __forceinline__ void red_add(u64* p, u64 v) { atomicAdd(p, v); }   // result unused -> RED
+__device__ __forceinline__ ulonglong2 ld_ca2(const u64* p) {
+    ulonglong2 v; asm volatile("ld.global.ca.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p)); return v;
+}
+__device__ __forceinline__ ulonglong2 ld_cg2(const u64* p) {
+    ulonglong2 v; asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(p)); return v;
+}
 // ---- vector loads of V consecutive rows (read-only path)
 template <int V> __device__ __forceinline__ void ld_u64(const void* base, i64 row, u64 (&o)[V]) {
     const u64* p = (const u64*)base + row;
@@ -114,26 +127,14 @@ template <int V> __device__ __forceinline__ void ld_u128(const void* base, i64 r
 #define PGW_CNT_C64(a, W, BIT) red_add(b + (W), (u64)PGW_CAT(cn, a)[j]);
 #define PGW_CNT_FLAG(a, W, BIT) flag_bits |= 1ULL << (BIT);
 
-// Claim quota.  PGW_QUOTA == 0: the host made sure every row of the launch could claim a bucket, nothing to reserve.
-// PGW_QUOTA == 1 (the table is nearly full): a block-wide counter in shared memory bounds the block's claims.
-__device__ __forceinline__ bool reserve(u32* s_claims, u32 quota) {
-#if PGW_QUOTA
-    if (atomicAdd(s_claims, 1u) < quota) return true;
-    atomicSub(s_claims, 1u);
-    return false;
-#else
-    return true;
-#endif
-}
-__device__ __forceinline__ void unreserve(u32* s_claims) {
-#if PGW_QUOTA
-    atomicSub(s_claims, 1u);
-#endif
-}
-
+// Claim quota.  PGW_QUOTA == 0: the host made sure every row of the launch could claim a bucket of `table`, nothing to check.
+// PGW_QUOTA == 1 (the table could fill up): every warp adds its claims to counters[0] after each trip and reads the total before the
+// next one; once the total has passed args.room it only looks keys up, and rows whose key is not there yet are left out for the
+// re-run after the host has grown the table.  The overshoot is bounded by what the warps in flight claim in one trip (the host
+// subtracts that from the room it grants).
 // V consecutive rows of one thread
 template <int V>
-__device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, u32* s_claims, u64& left_out, u64& claims) {
+__device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, u64& left_out, u64& claims, u64& fclaims) {
     const i64 cap = args.cap;
     // ---- loads
     u64 key[V];
@@ -179,35 +180,113 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
 #undef PG_X
         }
     }
-    // ---- one compare-and-swap per run, all of a thread's in flight together.  A free bucket is claimed and a bucket that
-    // already holds the key is recognised in ONE round trip to L2; nothing else of the bucket is ever read.
+    // ---- locate or claim the bucket of every run.  All loops below run a warp-uniform number of rounds (__any_sync) with predicated
+    // bodies: lanes that leave a data-dependent probe loop at different iterations are NOT brought back together by the hardware, and
+    // the rest of the kernel would then run a few lanes at a time (measured: 3.9 of 32 lanes active per instruction, 5.9 ms against 1.x).
+    const unsigned wm = __activemask();
     u64* bp[V];
     u32 idx[V];
+    u32 st[V];                       // 0 settled (bucket found, or left out), 1 walking its front chunk, 2 at a free front bucket, 3 probing `table`
     u64 old[V];
-    bool reserved[V];
 #pragma unroll
     for (int j = 0; j < V; j++) {
-        bp[j] = nullptr; idx[j] = 0; old[j] = 1; reserved[j] = false;
+        bp[j] = nullptr; idx[j] = 0; old[j] = 1; st[j] = 0;
         if (!live[j]) continue;
-        if (isnull[j] || key[j] == 0) { bp[j] = args.table + (cap + (isnull[j] ? 0 : 1)) * PGW_BUCKET_WORDS; continue; }
-        idx[j] = (u32)(((fmix64(key[j]) >> 32) * (u64)cap) >> 32);
-        reserved[j] = reserve(s_claims, args.quota);                   // a claim needs room in the block's quota
-        u64* bk = args.table + (i64)idx[j] * PGW_BUCKET_WORDS;
-        old[j] = reserved[j] ? atomicCAS(bk, 0ULL, key[j]) : __ldcg(bk);
+        if (isnull[j] || key[j] == 0) bp[j] = args.table + (cap + (isnull[j] ? 0 : 1)) * PGW_BUCKET_WORDS;
+        else st[j] = 3;
     }
+#if PGW_RANGE
+    // ---- front region.  A chunk's packed keys are probed a 32-byte sector (4 keys) at a time: the sector a key hashes to is read from
+    // L2 (never L1: claims by other SMs must be seen), a match or the first free slot is found in registers, and the claims of all
+    // lanes and runs are issued together, so a warp pays about two round trips to L2 per trip however its keys collide.
+    {
+        u32 fleft[V];                // sectors left to visit inside the chunk
+        u32 usecg = 0;               // runs whose sector must be re-read from L2 (their L1 copy is known to be stale)
 #pragma unroll
-    for (int j = 0; j < V; j++) {
-        if (!live[j] || bp[j] != nullptr) continue;
-        while (true) {                                                   // first step already issued above
-            if (reserved[j] && old[j] != 0) unreserve(s_claims);
-            if (reserved[j] && old[j] == 0) claims++;
-            if (old[j] == key[j] || (reserved[j] && old[j] == 0)) { bp[j] = args.table + (i64)idx[j] * PGW_BUCKET_WORDS; break; }
-            if (old[j] == 0) break;                                      // free bucket but no quota left: the run is left out
-            idx[j] = idx[j] + 1 == (u32)cap ? 0u : idx[j] + 1;
-            reserved[j] = reserve(s_claims, args.quota);
-            u64* bk = args.table + (i64)idx[j] * PGW_BUCKET_WORDS;
-            old[j] = reserved[j] ? atomicCAS(bk, 0ULL, key[j]) : __ldcg(bk);
+        for (int j = 0; j < V; j++) {
+            fleft[j] = PGW_CHUNK / 4;
+            if (st[j] != 3) continue;
+            const u64 seg = (key[j] - (u64)args.k0) >> args.shift;      // keys below k0 wrap around to a huge segment number
+            if (seg < args.nseg) { st[j] = 1; idx[j] = (u32)(seg * PGW_CHUNK + ((fmix64(key[j]) >> 40) & (PGW_CHUNK - 4))); }
+#if defined(PGW_EXP_NOLOCATE)
+            if (st[j] == 1) { st[j] = 0; idx[j] = (u32)(seg * PGW_CHUNK + ((key[j] * 5) & (PGW_CHUNK - 1))); bp[j] = args.front + (i64)idx[j] * PGW_BUCKET_WORDS; }
+#endif
         }
+        while (true) {
+            while (true) {
+                ulonglong2 ka[V], kb[V];
+#pragma unroll
+                for (int j = 0; j < V; j++) {
+                    if (st[j] != 1) continue;
+                    const u64* sp = args.front_keys + (idx[j] & ~3u);
+                    if (PGW_LDCA && !((usecg >> j) & 1u)) { ka[j] = ld_ca2(sp); kb[j] = ld_ca2(sp + 2); }
+                    else { ka[j] = ld_cg2(sp); kb[j] = ld_cg2(sp + 2); }
+                }
+                bool walking = false;
+#pragma unroll
+                for (int j = 0; j < V; j++) {
+                    if (st[j] != 1) continue;
+                    const u64 k0 = ka[j].x, k1 = ka[j].y, k2 = kb[j].x, k3 = kb[j].y, kk = key[j];
+                    const int hit = k0 == kk ? 0 : k1 == kk ? 1 : k2 == kk ? 2 : k3 == kk ? 3 : -1;
+                    const int zero = k0 == 0 ? 0 : k1 == 0 ? 1 : k2 == 0 ? 2 : k3 == 0 ? 3 : -1;
+                    if (hit >= 0) { idx[j] = (idx[j] & ~3u) | (u32)hit; bp[j] = args.front + (i64)idx[j] * PGW_BUCKET_WORDS; st[j] = 0; }
+                    else if (zero >= 0) { idx[j] = (idx[j] & ~3u) | (u32)zero; st[j] = 2; }
+                    else {
+                        idx[j] = (idx[j] & ~(u32)(PGW_CHUNK - 1)) | ((idx[j] + 4) & (PGW_CHUNK - 4));
+                        if (--fleft[j] == 0) st[j] = 3; else walking = true;        // a full chunk: the key lives in `table`
+                    }
+                }
+                if (!__any_sync(wm, walking)) break;
+            }
+#pragma unroll
+            for (int j = 0; j < V; j++) if (st[j] == 2) old[j] = atomicCAS(args.front_keys + idx[j], 0ULL, key[j]);
+            bool again = false;
+#pragma unroll
+            for (int j = 0; j < V; j++) {
+                if (st[j] != 2) continue;
+                if (old[j] == 0 || old[j] == key[j]) {
+                    bp[j] = args.front + (i64)idx[j] * PGW_BUCKET_WORDS; st[j] = 0;
+                    if (old[j] == 0) { fclaims++; bp[j][0] = key[j]; }
+                } else { st[j] = 1; again = true; usecg |= 1u << j; }     // taken by another key in the meantime: read the sector again, from L2
+            }
+            if (!__any_sync(wm, again)) break;
+        }
+    }
+#endif
+    // ---- the hashed table (every key without a front region; else keys outside its range or whose chunk is full): one
+    // compare-and-swap claims a free bucket or recognises the key's bucket in ONE round trip to L2, all of a thread's runs in flight together
+    {
+        bool allowed = true;
+        u32 mine = 0;
+#if PGW_QUOTA
+        allowed = __ldcg(args.counters) < args.room;
+#endif
+#pragma unroll
+        for (int j = 0; j < V; j++) if (st[j] == 3) idx[j] = (u32)(((fmix64(key[j]) >> 32) * (u64)cap) >> 32);
+        while (true) {
+#pragma unroll
+            for (int j = 0; j < V; j++) {
+                if (st[j] != 3) continue;
+                u64* bk = args.table + (i64)idx[j] * PGW_BUCKET_WORDS;
+                old[j] = allowed ? atomicCAS(bk, 0ULL, key[j]) : __ldcg(bk);
+            }
+            bool more = false;
+#pragma unroll
+            for (int j = 0; j < V; j++) {
+                if (st[j] != 3) continue;
+                if (allowed && old[j] == 0) mine++;
+                if (old[j] == key[j] || (allowed && old[j] == 0)) { bp[j] = args.table + (i64)idx[j] * PGW_BUCKET_WORDS; st[j] = 0; }
+                else if (old[j] == 0) st[j] = 0;                         // a free bucket but no room left: the run is left out
+                else { idx[j] = idx[j] + 1 == (u32)cap ? 0u : idx[j] + 1; more = true; }
+            }
+            if (!__any_sync(wm, more)) break;
+        }
+#if PGW_QUOTA
+        const u32 all = __reduce_add_sync(wm, mine);
+        if (all && (threadIdx.x & 31) == __ffs(wm) - 1) atomicAdd(args.counters, (u64)all);
+#else
+        claims += mine;
+#endif
     }
     // rows absorbed by a later row share its bucket
 #pragma unroll
@@ -218,6 +297,9 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
         u64* b = bp[j];
         if (valid[j] && b == nullptr) { left_out++; args.overflow_flag[r0 + j] = 1; }
         if (b == nullptr) continue;
+#if defined(PGW_EXP_NORED)
+        if (live[j]) b[2] = 1; continue;
+#endif
         u64 flag_bits = 0;
         if (live[j]) atomicMax(b + 1, ~(u64)(args.row_base + first_row[j]));   // smallest row index wins (stored inverted, zero = never seen)
 #define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                  \
@@ -225,24 +307,52 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
         if (valid[j]) { PGW_SOLO_##OP##_##IN(a, VALWORD) }
         PGW_AGGS(PG_X)
 #undef PG_X
-        if (PGW_FLAGWORD >= 0 && flag_bits) atomicOr(b + (PGW_FLAGWORD >= 0 ? PGW_FLAGWORD : 0), flag_bits);
+        // (when no flagged aggregate has a mask or nullable argument every run sets the same bits: a plain store of that constant does)
+        if (PGW_FLAGWORD >= 0 && flag_bits) {
+            if (PGW_FLAGS_UNCONDITIONAL) b[PGW_FLAGWORD >= 0 ? PGW_FLAGWORD : 0] = flag_bits;
+            else atomicOr(b + (PGW_FLAGWORD >= 0 ? PGW_FLAGWORD : 0), flag_bits);
+        }
     }
 }
 
-extern "C" __global__ void __launch_bounds__(256) pg_wide_agg(const PgwArgs args) {
-    __shared__ u32 s_claims;
-    if (threadIdx.x == 0) s_claims = 0;
-    __syncthreads();
-    u64 left_out = 0, claims = 0;
+// L2 prefetch of the lines a thread's NEXT trip will read (one lane per 128-byte line issues it)
+__device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+#define PGW_PF_NONE(a)
+#define PGW_PF_I64(a) if ((threadIdx.x & 3) == 0) pf_l2((const u64*)args.arg[a] + rn);
+#define PGW_PF_F64(a) PGW_PF_I64(a)
+#define PGW_PF_I2F(a) PGW_PF_I64(a)
+#define PGW_PF_I32(a) if ((threadIdx.x & 7) == 0) pf_l2((const int*)args.arg[a] + rn);
+#define PGW_PF_DEC128(a) if ((threadIdx.x & 1) == 0) pf_l2((const ulonglong2*)args.arg[a] + rn);
+#ifndef PGW_MINB
+#define PGW_MINB 2
+#endif
+#ifndef PGW_PREFETCH
+#define PGW_PREFETCH 1
+#endif
+
+extern "C" __global__ void __launch_bounds__(256, PGW_MINB) pg_wide_agg(const PgwArgs args) {
+    u64 left_out = 0, claims = 0, fclaims = 0;
     const i64 n = args.n;
     const i64 stride = (i64)gridDim.x * blockDim.x * PGW_VEC;
-    for (i64 r0 = ((i64)blockIdx.x * blockDim.x + threadIdx.x) * PGW_VEC; r0 + PGW_VEC <= n; r0 += stride)
-        process_rows<PGW_VEC>(args, r0, &s_claims, left_out, claims);
+    for (i64 r0 = ((i64)blockIdx.x * blockDim.x + threadIdx.x) * PGW_VEC; r0 + PGW_VEC <= n; r0 += stride) {
+        if (PGW_PREFETCH && PGW_VEC == 4 && r0 + stride + PGW_VEC <= n) {
+            const i64 rn = r0 + stride;
+            if ((threadIdx.x & 3) == 0) pf_l2(args.keys + rn);
+#define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT) PGW_PF_##IN(a)
+            PGW_AGGS(PG_X)
+#undef PG_X
+        }
+        process_rows<PGW_VEC>(args, r0, left_out, claims, fclaims);
+    }
     if (PGW_VEC > 1 && blockIdx.x == 0 && threadIdx.x == 0)
-        for (i64 r0 = n - n % PGW_VEC; r0 < n; r0++) process_rows<1>(args, r0, &s_claims, left_out, claims);
+        for (i64 r0 = n - n % PGW_VEC; r0 < n; r0++) process_rows<1>(args, r0, left_out, claims, fclaims);
     // ---- per-block totals
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) { left_out += __shfl_down_sync(0xffffffffu, left_out, d); claims += __shfl_down_sync(0xffffffffu, claims, d); }
+    for (int d = 16; d > 0; d >>= 1) {
+        left_out += __shfl_down_sync(0xffffffffu, left_out, d); claims += __shfl_down_sync(0xffffffffu, claims, d);
+        fclaims += __shfl_down_sync(0xffffffffu, fclaims, d);
+    }
+    if ((threadIdx.x & 31) == 0 && fclaims) atomicAdd(args.counters + 2, fclaims);
     if ((threadIdx.x & 31) == 0 && left_out) atomicAdd(args.counters + 1, left_out);
     if ((threadIdx.x & 31) == 0 && claims) atomicAdd(args.counters, claims);
 }

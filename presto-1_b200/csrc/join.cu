@@ -161,6 +161,11 @@ __global__ void __launch_bounds__(J_THREADS) j_build_kernel(JSlot* slots, int64_
 // single BIGINT key: four rows per thread in flight (their first slot reads are issued together), compare-and-swap only on
 // slots seen free, count/head maintained with fire-and-forget atomics.  Duplicate keys are
 // detected without a returning atomic: they exist iff fewer slots were claimed than rows inserted.
+__device__ int g_exp_hash = 0;
+PG_D int64_t jpos(unsigned long long key, int64_t mask) {
+    if (g_exp_hash) return (int64_t)(((((key >> 5) << 3) | (key & 7)) * 2) & (uint64_t)mask);
+    return (int64_t)(fmix64(key) & (uint64_t)mask);
+}
 __global__ void __launch_bounds__(J_THREADS) j_build_fast_kernel(JSlot* slots, int64_t cap, const int64_t* __restrict__ keys,
                                                                  const uint8_t* __restrict__ nulls, int64_t rows, int32_t* row_slot,
                                                                  unsigned long long* meta) {
@@ -184,7 +189,7 @@ __global__ void __launch_bounds__(J_THREADS) j_build_fast_kernel(JSlot* slots, i
             p[k] = -1; old[k] = 0;
             if (!valid[k]) continue;
             if (key[k] == EMPTY_KEY) { p[k] = cap; continue; }
-            p[k] = (int64_t)(fmix64(key[k]) & (uint64_t)mask);
+            p[k] = jpos(key[k], mask);
             old[k] = __ldcg(&slots[p[k]].word);      // plain read first: an atomic on a sector that is not in L2 yet is far slower
         }
 #pragma unroll
@@ -403,7 +408,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) j_probe_count_fast_kernel(ProbeA
         const int leader = 31 - __clz(starts & (0xffffffffu >> (31 - lane)));
         int code = -1, c = 0;
         if (valid && lane == leader) {
-            int64_t p = key == EMPTY_KEY ? a.cap : (int64_t)(fmix64(key) & (uint64_t)mask);
+            int64_t p = key == EMPTY_KEY ? a.cap : jpos(key, mask);
             while (true) {
                 const int4 sv = __ldg((const int4*)(a.slots + p));        // {word lo, word hi, count, head}
                 const unsigned long long w = ((unsigned long long)(uint32_t)sv.y << 32) | (uint32_t)sv.x;
@@ -548,6 +553,7 @@ static void lookup_build(pg_lookup* ls) {
     ls->meta.alloc(ctx, 64);
     memset_async(ctx, ls->meta.p, 0, 64);
     if (rows == 0) return;
+    { int eh = 0; if (const char* e = getenv("PRESTOGPU_EXP_HASH")) eh = atoi(e); PG_CUDA(cudaMemcpyToSymbolAsync(g_exp_hash, &eh, 4, 0, cudaMemcpyHostToDevice, ctx->stream)); }
     DevBuf row_slot(ctx, rows * 4);
     DCol hc; memset(&hc, 0, sizeof(hc));
     int has_hash = 0;

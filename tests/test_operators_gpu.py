@@ -333,6 +333,45 @@ def test_many_groups_bigint_key_matches_oracle_in_first_seen_order(pgpu, monkeyp
     assert op.get_group_count() == len(want)
 
 
+@pytest.mark.parametrize("expected_groups", [100, 150_000, 2_000_000])
+def test_many_groups_sorted_keys_take_the_range_chunked_table(pgpu, expected_groups):
+    """Rows sorted by key (lineitem by order key) take the many-groups path with the range-chunked front region
+    (hashagg_wide.cu).  The first page fixes the plan (k0, chunk width, span); later pages bring a denser key range
+    (full chunks spill into the hashed table), keys below k0 and far above the planned span, an unsorted page, key 0 and
+    null keys.  Results and first-seen order must equal the oracle's whatever the plan was."""
+    P = pgpu
+    rng = np.random.default_rng(33)
+    def sparse(i):                      # dbgen's order keys: 8 used, 24 skipped
+        return ((i >> 3) << 5) | (i & 7)
+    k1 = np.repeat(sparse(np.arange(1, 100_001, dtype=np.int64)), rng.integers(1, 8, 100_000))        # sorted runs of 1..7
+    k2 = np.repeat(np.arange(k1[-1] + 1, k1[-1] + 120_001, dtype=np.int64), 2)                         # 4x denser than the sample
+    k3 = np.concatenate([np.arange(-5000, 0, dtype=np.int64), np.arange(10**12, 10**12 + 20_000, dtype=np.int64)])   # outside the span
+    k4 = rng.permutation(np.concatenate([k1[:50_000], k3[:1000], np.zeros(10, dtype=np.int64)]))      # unsorted revisit
+    keys = np.concatenate([k1, k2, k3, k4])
+    n = len(keys)
+    knull = (rng.random(n) < 0.0005).astype(np.uint8)
+    dec = rng.integers(-10**15, 10**15, n).astype(np.int64)
+    dbl = rng.random(n) * 1e6
+    def page(lo, hi):
+        return [P.Block.long_array(keys[lo:hi], knull[lo:hi]), P.Block.long_array(dec[lo:hi], None, P.SHORT_DECIMAL), P.Block.double_array(dbl[lo:hi])]
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2)]
+    cuts = [0, len(k1), len(k1) + len(k2), len(k1) + len(k2) + len(k3), n]
+    pages = [page(cuts[i], cuts[i + 1]) for i in range(4)]
+    op = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=expected_groups)
+    op.ctx.kernel_report(reset=True)
+    op.ctx.set_timing(True)
+    for blocks in pages:
+        op.add_input(P.Page(*blocks).to_device())
+    op.finish()
+    seen = op.ctx.kernel_report(reset=True)
+    op.ctx.set_timing(False)
+    assert "wide_agg_jit" in seen, "the many-groups path was not taken: %s" % sorted(seen)
+    got = rows_of(drain(op))
+    want = _oracle_rows(P, None, pages, aggs)
+    _assert_rows_equal(got, want)
+    assert op.get_group_count() == len(want)
+
+
 def test_many_groups_partial_then_final(pgpu):
     """PARTIAL step on the many-groups path ships real counts in its intermediate rows; FINAL merges them."""
     P = pgpu

@@ -48,6 +48,16 @@ struct JoinCols {
     DCol c[MAX_KEYS];      // join key columns (build side view or probe side view)
 };
 
+// slot placement of the single-BIGINT-key table (see join.cu: range-chunked region + hashed region)
+struct JLayout {
+    unsigned long long kmin;
+    int64_t nchunks;     // chunks of the range region
+    int64_t R;           // slots of the range region = nchunks * 32
+    int64_t omask;       // slots of the hashed region - 1
+    int64_t total;       // R + omask + 1; slot `total` holds the key whose bit pattern equals EMPTY_KEY
+    int32_t range, shift;
+};
+
 }  // namespace pg
 
 struct pg_joinbuild {
@@ -66,7 +76,8 @@ struct pg_lookup {
     int32_t hash_channel = -1;
     std::vector<pg::ColStore> cols;
     int64_t rows = 0;
-    int64_t cap = 0;
+    int64_t cap = 0;              // slots (both regions); slot `cap` is the special one
+    pg::JLayout layout;           // single BIGINT key: where a key's probe sequence starts (join.cu)
     bool bigint_fast = false;
     bool has_dups = false;
     int64_t dup_rows = 0;

@@ -204,3 +204,60 @@ def test_large_skewed_segment_sorted_descending(pgpu):
     want = list(range(n - 1, -1, -1))
     assert gb.tolist() == want + [n + 4] + want
     assert gp.tolist() == [0] * n + [1] + [2] * n
+
+
+RANGE_CASES = ["tpch_sparse_sorted", "dense_sorted_with_dups", "two_far_clusters", "heavy_skew_overflow", "extreme_span", "with_nulls_and_sentinel"]
+
+
+@pytest.mark.parametrize("case", RANGE_CASES)
+@pytest.mark.parametrize("join_type", [0, 1])
+def test_bigint_join_range_chunked_table_matches_oracle(pgpu, case, join_type):
+    """Single BIGINT join key, enough build rows for the range-chunked slot placement (join.cu: JLayout).  Key distributions that
+    suit it (dbgen's sparse sorted order keys, dense keys), that overflow single lines into the hashed region (clusters, skew:
+    the build then falls back to the plain table when the overflow region fills up), keys at the int64 extremes, nulls on both
+    sides and the EMPTY_KEY bit pattern.  Match lists are compared with the oracle in order (newest build row first)."""
+    P = pgpu
+    rng = np.random.default_rng(77)
+    n = 60_000
+    i = np.arange(1, n + 1, dtype=np.int64)
+    sparse = ((i >> 3) << 5) | (i & 7)
+    knull = None
+    if case == "tpch_sparse_sorted":
+        bkeys = sparse
+    elif case == "dense_sorted_with_dups":
+        bkeys = np.sort(rng.integers(1000, 1000 + n // 2, n).astype(np.int64))
+    elif case == "two_far_clusters":
+        bkeys = np.concatenate([np.arange(n // 2, dtype=np.int64), 10**15 + np.arange(n // 2, dtype=np.int64) * 3])
+    elif case == "heavy_skew_overflow":
+        bkeys = np.concatenate([np.arange(50_000, dtype=np.int64) * 7, rng.integers(0, 2**40, n - 50_000).astype(np.int64)])
+        bkeys = rng.permutation(bkeys)
+    elif case == "extreme_span":
+        bkeys = np.concatenate([rng.integers(-2**63, 2**63 - 1, n - 2, dtype=np.int64), np.array([-2**63, 2**63 - 1], dtype=np.int64)])
+    else:
+        bkeys = sparse.copy()
+        bkeys[::1000] = -0x7FFFFFFFFFFFFFFF          # the bit pattern of the table's empty marker (0x8000000000000001)
+        knull = (rng.random(n) < 0.01).astype(np.uint8)
+    pay = rng.random(n)
+    types = [P.BIGINT, P.DOUBLE]
+    idx = P.PagesIndex(types, [0])
+    orc = O.OracleJoin(types, [0])
+    cuts = [0, n // 3, n // 3 + 5, n]
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        blocks = [P.Block.long_array(bkeys[a:b], None if knull is None else knull[a:b]), P.Block.double_array(pay[a:b])]
+        idx.add_page([x.to_device() for x in blocks])
+        orc.add_page(blocks)
+    ls = idx.create_lookup_source()
+    orc.build()
+    m = 150_000
+    pkeys = np.concatenate([bkeys[rng.integers(0, n, m // 2)], rng.integers(int(bkeys.min()) // 2 - 5, int(bkeys.max()) // 2 + 5, m - m // 2).astype(np.int64)])
+    pkeys[:: 5000] = -0x7FFFFFFFFFFFFFFF
+    pkeys = np.sort(pkeys) if case in ("tpch_sparse_sorted", "dense_sorted_with_dups") else pkeys
+    pnull = (rng.random(m) < 0.01).astype(np.uint8)
+    pk = P.Block.long_array(pkeys, pnull)
+    gp, gb = ls.join_page([pk.to_device()], None, join_type)
+    wp, wb = orc.probe([pk], None, join_type)
+    assert np.array_equal(gp.cpu().numpy(), wp), case
+    assert np.array_equal(gb.cpu().numpy(), wb), case
+    out = ls.append_to(__import__("torch").from_numpy(wb).cuda(), [1])
+    sel = wb >= 0
+    assert np.array_equal(out[0].to_host().values[sel], pay.view(np.int64)[wb[sel]])

@@ -162,7 +162,7 @@ def run_single_pass(P, page, aggs, step, ctx, expected=100_000):
 _MERGE_BUFS = {}
 
 
-def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world):
+def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world, run_final=True):
     """All-gather the (tiny) intermediate page of every rank over NCCL, then ONE FINAL step over the concatenated rows.
     The page is packed into a pinned buffer: [payload bytes][n][per block: values, offsets, nulls sizes][data]."""
     import numpy as np
@@ -231,39 +231,120 @@ def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world):
             nulls = np.concatenate([t[2] if len(t[2]) else np.zeros(t[3], dtype=np.uint8) for t in per_block[i]])
         blocks.append(Block(b.type, vals, nulls, offs, total))
     t3 = time.perf_counter()
+    if trace is not None:
+        for i, d in enumerate((t1 - t0, t2 - t1, t3 - t2)):
+            trace[i] += d
+        trace[4] += 1
+    if not run_final:
+        return blocks, total
+    return final_merge(P, blocks, total, fin_aggs, ctx)
+
+
+def final_merge(P, blocks, total, fin_aggs, ctx):
+    """The FINAL step over the gathered intermediate rows."""
+    trace = _MERGE_BUFS.get("trace")
+    t3 = time.perf_counter()
     fin = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs, expected_groups=1000, ctx=ctx)
     fin.add_input(P.Page(*blocks, position_count=total))
     fin.finish()
     out = fin.get_output()
     fin.close()
     if trace is not None:
-        t4 = time.perf_counter()
-        for i, d in enumerate((t1 - t0, t2 - t1, t3 - t2, t4 - t3)):
-            trace[i] += d
+        trace[3] += time.perf_counter() - t3
+    return out
+
+
+PACKED_CAP = 1 << 16
+
+
+def partial_packed(P, page, aggs, ctx, pipe, expected=100_000):
+    """PARTIAL pass on the main thread; its output leaves as one packed page (native, one call) in a pinned send buffer."""
+    op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.PARTIAL, aggs, expected_groups=expected, ctx=ctx)
+    op.add_input(page)
+    op.finish()
+    buf = pipe.next_send_buffer()
+    op.get_output_packed(buf.data_ptr(), PACKED_CAP)
+    op.close()
+    pipe.submit(buf)
+
+
+def gather_packed(dist, torch, send_host, world):
+    """packed page of this rank -> NCCL all-gather -> the ranks' packed pages in pinned host memory.
+    Returns the list of buffer addresses for HashAggregationOperator.add_packed."""
+    cap = PACKED_CAP
+    trace = _MERGE_BUFS.setdefault("trace", [0.0] * 5) if os.environ.get("PRESTOGPU_BENCH_TRACE") else None
+    t0 = time.perf_counter()
+    if "send" not in _MERGE_BUFS:
+        _MERGE_BUFS["send"] = torch.zeros(cap, dtype=torch.uint8, device="cuda")
+        _MERGE_BUFS["recv"] = torch.zeros(cap * world, dtype=torch.uint8, device="cuda")
+        # several receive buffers: the FINAL worker of step i may still read its pages while later steps are gathered
+        _MERGE_BUFS["recv_host"] = [torch.zeros(cap * world, dtype=torch.uint8).pin_memory() for _ in range(8)]
+        _MERGE_BUFS["turn"] = 0
+    t1 = time.perf_counter()
+    rh = _MERGE_BUFS["recv_host"][_MERGE_BUFS["turn"] % 8]
+    _MERGE_BUFS["turn"] += 1
+    _MERGE_BUFS["send"].copy_(send_host, non_blocking=True)
+    dist.all_gather_into_tensor(_MERGE_BUFS["recv"], _MERGE_BUFS["send"])
+    rh.copy_(_MERGE_BUFS["recv"], non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    t2 = time.perf_counter()
+    if trace is not None:
+        trace[0] += t1 - t0
+        trace[1] += t2 - t1
         trace[4] += 1
+    base = rh.data_ptr()
+    return [base + r * cap for r in range(world)]
+
+
+def final_merge_packed(P, ptrs, fin_aggs, ctx):
+    trace = _MERGE_BUFS.get("trace")
+    t3 = time.perf_counter()
+    fin = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs, expected_groups=1000, ctx=ctx)
+    fin.add_packed(ptrs)
+    fin.finish()
+    out = fin.get_output()
+    fin.close()
+    if trace is not None:
+        trace[3] += time.perf_counter() - t3
     return out
 
 
 class MergePipeline:
     """Second stage of the N > 1 plan, running beside the first: while the main thread runs the PARTIAL pass of step i + 1,
-    this thread all-gathers the intermediate rows of step i (NCCL on its own stream) and runs the FINAL step on a second
-    pg_ctx.  Every step's final result is produced; the stages merely overlap, as consecutive pages do in the reference's
-    PARTIAL -> exchange -> FINAL plan."""
+    a communication thread all-gathers the intermediate rows of step i (NCCL on its own stream, one collective per step, in
+    step order on every rank) and FINAL workers, each with its own pg_ctx and high-priority stream, run the FINAL step of
+    alternate steps.  Every step's final result is produced; the stages merely overlap, as consecutive pages do in the
+    reference's PARTIAL -> exchange -> FINAL plan.  (One FINAL step costs 0.4 ms on an idle GPU but 1.4 ms beside the PARTIAL
+    kernel of the next step - it is a chain of small launches and read-backs - so a single worker capped the 8-GPU step at 2 ms.)"""
+
+    FINAL_WORKERS = 2
 
     def __init__(self, P, dist, torch, fin_aggs, local_rank, world):
         import queue
         self.P, self.dist, self.torch, self.fin_aggs, self.local_rank, self.world = P, dist, torch, fin_aggs, local_rank, world
-        self.q = queue.Queue()
-        self.last, self.err, self.ctx = None, None, None
+        self.q = queue.Queue(maxsize=3)      # bounded: the pinned send / receive buffers rotate over 8 slots
+        self.fq = queue.Queue(maxsize=3)
+        self.results = {}
+        self.fctx = []
+        self.send_bufs = []
+        self.submitted = 0
+        self.err, self.ctx = None, None
         self.ready = threading.Event()
         self.thread = threading.Thread(target=self._run, daemon=True)
         self.thread.start()
         self.ready.wait()
+        self.workers = []
+        for _ in range(self.FINAL_WORKERS):
+            ev = threading.Event()
+            t = threading.Thread(target=self._final_worker, args=(ev,), daemon=True)
+            t.start()
+            ev.wait()
+            self.workers.append(t)
 
     def _run(self):
         torch = self.torch
         torch.cuda.set_device(self.local_rank)
-        self.stream = torch.cuda.Stream(priority=-1)    # its few small kernels go ahead of the next step's big one
+        self.stream = torch.cuda.Stream(priority=-1)
         with torch.cuda.stream(self.stream):
             self.ctx = self.P.GpuContext(self.local_rank)      # bound to this thread's stream
             self.ready.set()
@@ -274,23 +355,61 @@ class MergePipeline:
                     return
                 try:
                     if self.err is None:
-                        self.last = merge_partials_nccl(self.P, self.dist, torch, item, self.fin_aggs, self.ctx, self.world)
+                        step, send_host = item
+                        self.fq.put((step, gather_packed(self.dist, torch, send_host, self.world)))
                 except BaseException as e:   # surfaced by drain()
                     self.err = e
                 self.q.task_done()
 
+    def _final_worker(self, ready):
+        torch = self.torch
+        torch.cuda.set_device(self.local_rank)
+        stream = torch.cuda.Stream(priority=-1)    # its few small kernels go ahead of the next step's big one
+        with torch.cuda.stream(stream):
+            ctx = self.P.GpuContext(self.local_rank)
+            self.fctx.append(ctx)
+            ready.set()
+            while True:
+                item = self.fq.get()
+                if item is None:
+                    self.fq.task_done()
+                    return
+                try:
+                    if self.err is None:
+                        step, ptrs = item
+                        self.results[step] = final_merge_packed(self.P, ptrs, self.fin_aggs, ctx)
+                        self.results.pop(step - 8, None)
+                except BaseException as e:
+                    self.err = e
+                self.fq.task_done()
+
+    def next_send_buffer(self):
+        if not self.send_bufs:
+            self.send_bufs = [self.torch.zeros(PACKED_CAP, dtype=self.torch.uint8).pin_memory() for _ in range(8)]
+        b = self.send_bufs[self.submitted % 8]
+        return b
+
+    def launch_count(self):
+        return self.ctx.launch_count() + sum(c.launch_count() for c in self.fctx)
+
     def submit(self, page):
-        self.q.put(page)
+        self.q.put((self.submitted, page))
+        self.submitted += 1
 
     def drain(self):
         self.q.join()
+        self.fq.join()
         if self.err is not None:
             raise self.err
-        return self.last
+        return self.results.get(self.submitted - 1)
 
     def close(self):
         self.q.put(None)
         self.thread.join(timeout=10)
+        for _ in self.workers:
+            self.fq.put(None)
+        for t in self.workers:
+            t.join(timeout=10)
 
 
 def final_aggs_for(P, aggs, first_channel):
@@ -438,7 +557,8 @@ def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0)
                          "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(pkern.items(), key=lambda kv: -kv[1][0])[:6]},
                          "selfcheck": join_check}
     if ex:
-        res["exchange"] = {"rows_sent_per_rank": ex.sent_rows, "bytes_sent_per_rank": ex.bytes_sent, "collective": "NCCL all_to_all_single per column"}
+        res["exchange"] = {"rows_sent_per_rank": ex.sent_rows, "bytes_sent_per_rank": ex.bytes_sent, "collective": ("fused partition + peer-memory stores over NVLink (pg_partition_scatter_peers into symmetric receive buffers)" if ex.peer is not None
+                                          else "NCCL all_to_all_single per column (%s)" % ex.peer_why)}
     return res
 
 
@@ -507,11 +627,11 @@ def gpu_arm(args):
     def step_device():
         if world == 1:
             return run_single_pass(P, page, aggs, P.SINGLE, ctx)
-        pipe.submit(run_single_pass(P, page, aggs, P.PARTIAL, ctx))     # FINAL of this step overlaps the next PARTIAL
+        partial_packed(P, page, aggs, ctx, pipe)     # FINAL of this step overlaps the next PARTIAL
         return None
 
     def launches_now():
-        return ctx.launch_count() + (pipe.ctx.launch_count() if pipe else 0)
+        return ctx.launch_count() + (pipe.launch_count() if pipe else 0)
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -587,7 +707,7 @@ def gpu_arm(args):
         def step_host():
             if world == 1:
                 return run_single_pass(P, hpage, aggs, P.SINGLE, ctx)
-            pipe.submit(run_single_pass(P, hpage, aggs, P.PARTIAL, ctx))
+            partial_packed(P, hpage, aggs, ctx, pipe)
             return None
 
         e_steps = max(2, min(args.steps, 5))

@@ -238,6 +238,17 @@ PG_API int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, p
 PG_API int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* out_bytes);
 /* partial-aggregation flush: forget all groups (OP/HashAggregationOperator.java:501-517) */
 PG_API int32_t pg_hashagg_reset(pg_hashagg* op);
+/* The output page of group ids [first, first+n) written as ONE self-describing host buffer, and its counterpart that adds several
+ * such buffers (e.g. the PARTIAL pages of all ranks after an all-gather) as one input page, rows in buffer order.  This is the
+ * wire format between a PARTIAL and a FINAL operator in different processes - the job PagesSerde does for the reference's
+ * exchange (MAIN/execution/buffer/PagesSerde.java), restricted to the block kinds this library produces.  Layout (little endian):
+ *   int64 total_bytes, int64 n, int32 ncols, int32 magic 'PGP1',
+ *   ncols x { int32 type, int32 has_nulls, int64 values_bytes, int64 offsets_bytes, int64 data_offset },
+ *   then per column, 8-byte aligned from data_offset: values, offsets (int32[n+1], var width only), nulls (n bytes).
+ * get_output_packed fails with PG_NEED_MEMORY (and the size needed in *out_bytes) when `capacity` is too small. */
+PG_API int32_t pg_hashagg_get_output_packed(pg_hashagg* op, int64_t first, int64_t n, void* buf, int64_t capacity, int64_t* out_bytes,
+                                            int64_t* error_group);
+PG_API int32_t pg_hashagg_add_packed(pg_hashagg* op, const void* const* bufs, int32_t nbufs);
 
 /* =====================================================================================
  * Hash partitioning for the multi-GPU exchange — replaces the row routing of OP/exchange/LocalPartitionGenerator.java:50-63,

@@ -88,6 +88,8 @@ _PROTOS = {
     "pg_hashagg_get_output": (I32, [P, I64, I64, PCOLOUT, PI64]),
     "pg_hashagg_varwidth_bytes": (I32, [P, I32, PI64]),
     "pg_hashagg_reset": (I32, [P]),
+    "pg_hashagg_get_output_packed": (I32, [P, I64, I64, P, I64, PI64, PI64]),
+    "pg_hashagg_add_packed": (I32, [P, C.POINTER(C.c_void_p), I32]),
     "pg_partition_create": (I32, [P, PCOL, I32, PCOL, I64, I32, I32, PI64, C.POINTER(P)]),
     "pg_partition_destroy": (I32, [P]),
     "pg_partition_scatter": (I32, [P, PCOL, PCOLOUT]),

@@ -103,6 +103,17 @@ class Block:
         data = np.frombuffer(b"".join(chunks), dtype=np.uint8).copy() if pos else np.zeros(0, dtype=np.uint8)
         return Block(type_, data, nulls if nulls.any() else None, offs)
 
+    def slice(self, lo, hi):
+        """Rows [lo, hi) as a new host block (Block.getRegion; var-width offsets are rebased)."""
+        h = self.to_host()
+        nulls = None if h.nulls is None else np.ascontiguousarray(h.nulls[lo:hi])
+        if h.type in (N.VARCHAR, N.VARBINARY):
+            o = np.asarray(h.offsets)
+            vals = np.ascontiguousarray(np.asarray(h.values)[o[lo]:o[hi]])
+            return Block(h.type, vals, nulls, (o[lo:hi + 1] - o[lo]).astype(np.int32), hi - lo, h.precision, h.scale)
+        k = 2 if h.type == N.LONG_DECIMAL else 1
+        return Block(h.type, np.ascontiguousarray(np.asarray(h.values)[k * lo:k * hi]), nulls, None, hi - lo, h.precision, h.scale)
+
     # ---- conversions
     def to_device(self, device="cuda"):
         import torch

@@ -402,6 +402,123 @@ int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* out_byte
     return PG_OK;
 }
 
+/* ---- packed pages: the PARTIAL -> FINAL wire format (see include/prestogpu.h) */
+namespace {
+struct PackedHeader { int64_t total_bytes, n; int32_t ncols, magic; };
+struct PackedCol { int32_t type, has_nulls; int64_t values_bytes, offsets_bytes, data_offset; };
+const int32_t PACKED_MAGIC = 0x31504750;   // "PGP1"
+inline int64_t align8(int64_t x) { return (x + 7) & ~(int64_t)7; }
+inline bool packed_is_var(int32_t t) { return t == PG_VARCHAR || t == PG_VARBINARY; }
+inline int64_t packed_width(int32_t t) {
+    switch (t) {
+        case PG_INTEGER: case PG_DATE: return 4;
+        case PG_BOOLEAN: return 1;
+        case PG_LONG_DECIMAL: return 16;
+        default: return 8;
+    }
+}
+}  // namespace
+
+int32_t pg_hashagg_get_output_packed(pg_hashagg* op, int64_t first, int64_t n, void* buf, int64_t capacity, int64_t* out_bytes,
+                                     int64_t* error_group) {
+    if (!op || !out_bytes) return PG_E_INVALID_ARGUMENT;
+    int32_t types[256], ncols = 0;
+    int32_t rc = pg_hashagg_output_types(op, types, 256, &ncols);
+    if (rc != PG_OK) return rc;
+    std::vector<PackedCol> cols(ncols);
+    int64_t pos = align8((int64_t)sizeof(PackedHeader) + (int64_t)ncols * (int64_t)sizeof(PackedCol));
+    for (int i = 0; i < ncols; i++) {
+        PackedCol& c = cols[i];
+        c.type = types[i]; c.has_nulls = 1; c.offsets_bytes = 0;
+        if (packed_is_var(types[i])) {
+            int64_t vb = 0;
+            rc = pg_hashagg_varwidth_bytes(op, i, &vb);
+            if (rc != PG_OK) return rc;
+            c.values_bytes = vb > 0 ? vb : 1;
+            c.offsets_bytes = (n + 1) * 4;
+        } else c.values_bytes = (n > 0 ? n : 1) * packed_width(types[i]);
+        c.data_offset = pos;
+        pos += align8(c.values_bytes) + align8(c.offsets_bytes) + align8(n > 0 ? n : 1);
+    }
+    *out_bytes = pos;
+    if (!buf || capacity < pos) {
+        return guard(op->ctx, [&] { fail(PG_NEED_MEMORY, "packed page needs %lld bytes, the buffer holds %lld", (long long)pos, (long long)capacity); });
+    }
+    char* base = (char*)buf;
+    PackedHeader* h = (PackedHeader*)base;
+    h->total_bytes = pos; h->n = n; h->ncols = ncols; h->magic = PACKED_MAGIC;
+    memcpy(base + sizeof(PackedHeader), cols.data(), (size_t)ncols * sizeof(PackedCol));
+    std::vector<pg_col_out> outs(ncols);
+    for (int i = 0; i < ncols; i++) {
+        const PackedCol& c = cols[i];
+        pg_col_out& o = outs[i];
+        memset(&o, 0, sizeof(o));
+        o.type = c.type; o.mem = PG_MEM_HOST; o.capacity = n;
+        o.values = base + c.data_offset;
+        o.offsets = c.offsets_bytes ? (int32_t*)(base + c.data_offset + align8(c.values_bytes)) : nullptr;
+        o.nulls = (uint8_t*)(base + c.data_offset + align8(c.values_bytes) + align8(c.offsets_bytes));
+        o.values_capacity_bytes = packed_is_var(c.type) ? c.values_bytes : 0;
+        memset(o.nulls, 0, (size_t)(n > 0 ? n : 1));
+    }
+    return pg_hashagg_get_output(op, first, n, outs.data(), error_group);
+}
+
+int32_t pg_hashagg_add_packed(pg_hashagg* op, const void* const* bufs, int32_t nbufs) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    int32_t ncols = -1;
+    int64_t total = 0;
+    std::vector<std::vector<char>> values, nulls;
+    std::vector<std::vector<int32_t>> offsets;
+    std::vector<int32_t> types;
+    int32_t rc = guard(op->ctx, [&] {
+        PG_CHECK_ARG(bufs && nbufs > 0, "bad arguments");
+        for (int b = 0; b < nbufs; b++) {
+            const char* base = (const char*)bufs[b];
+            PG_CHECK_ARG(base != nullptr, "null buffer");
+            const PackedHeader* h = (const PackedHeader*)base;
+            PG_CHECK_ARG(h->magic == PACKED_MAGIC && h->n >= 0 && h->ncols > 0 && h->ncols <= 256, "buffer %d is not a packed page", b);
+            const PackedCol* pc = (const PackedCol*)(base + sizeof(PackedHeader));
+            if (ncols < 0) {
+                ncols = h->ncols;
+                values.resize(ncols); nulls.resize(ncols); offsets.resize(ncols); types.resize(ncols);
+                for (int i = 0; i < ncols; i++) { types[i] = pc[i].type; if (packed_is_var(types[i])) offsets[i].push_back(0); }
+            }
+            PG_CHECK_ARG(h->ncols == ncols, "buffer %d has %d columns, the first one %d", b, h->ncols, ncols);
+            const int64_t n = h->n;
+            for (int i = 0; i < ncols; i++) {
+                const PackedCol& c = pc[i];
+                PG_CHECK_ARG(c.type == types[i], "buffer %d column %d has type %d, expected %d", b, i, c.type, types[i]);
+                const char* v = base + c.data_offset;
+                const char* nl = v + align8(c.values_bytes) + align8(c.offsets_bytes);
+                if (packed_is_var(c.type)) {
+                    const int32_t* o = (const int32_t*)(v + align8(c.values_bytes));
+                    const int32_t used = n > 0 ? o[n] : 0, shift = offsets[i].back();
+                    values[i].insert(values[i].end(), v, v + used);
+                    for (int64_t r = 1; r <= n; r++) offsets[i].push_back(o[r] + shift);
+                } else values[i].insert(values[i].end(), v, v + n * packed_width(c.type));
+                if (c.has_nulls) nulls[i].insert(nulls[i].end(), nl, nl + n);
+                else nulls[i].insert(nulls[i].end(), (size_t)n, 0);
+            }
+            total += n;
+        }
+    });
+    if (rc != PG_OK) return rc;
+    if (total == 0) return PG_OK;
+    std::vector<pg_col> cols(ncols);
+    for (int i = 0; i < ncols; i++) {
+        pg_col& c = cols[i];
+        memset(&c, 0, sizeof(c));
+        c.type = types[i]; c.mem = PG_MEM_HOST; c.n = total;
+        if (values[i].empty()) values[i].resize(8);
+        c.values = values[i].data();
+        bool any_null = false;
+        for (char x : nulls[i]) if (x) { any_null = true; break; }
+        c.nulls = any_null ? (const uint8_t*)nulls[i].data() : nullptr;
+        c.offsets = packed_is_var(types[i]) ? offsets[i].data() : nullptr;
+    }
+    return pg_hashagg_add_page(op, cols.data(), ncols, total);
+}
+
 /* partial-aggregation flush: drop all groups and states, keep the configuration (HashAggregationOperator.java:501-517) */
 int32_t pg_hashagg_reset(pg_hashagg* op) {
     if (!op) return PG_E_INVALID_ARGUMENT;

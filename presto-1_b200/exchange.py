@@ -6,6 +6,11 @@ One process per GPU; torch.distributed (NCCL over NVLink / NVSwitch) is the plum
   1. pg_partition_create  : CUDA kernels compute each row's partition and its slot in partition-major order
   2. pg_partition_scatter : every column is rewritten partition-major on the device (raw column buffers, no serde)
   3. all_to_all_single    : counts first (world x world int64), then one variable-split all-to-all per column buffer
+  3'. peer mode (NVLink / NVSwitch peer memory, the default under NCCL when symmetric memory is available): the receive buffers are
+     symmetric-memory allocations; after the counts are known to everyone, pg_partition_scatter_peers writes every row of a column
+     straight into its destination rank's buffer (one kernel does the partitioning store AND the transfer, no staging copy and
+     no collective on the data path); two stream-ordered barriers bracket the stores.  The result layout is the one
+     all_to_all_single gives: source-rank major, page order inside a source.
 Rows with equal keys meet on one rank, so a SINGLE-step aggregation / a local build+probe per rank gives disjoint results.
 """
 import ctypes as C
@@ -57,10 +62,31 @@ class DevicePartitioner:
         return Page(*out_blocks, position_count=n), [int(c) for c in counts]
 
 
+class _PeerBuffers:
+    """Symmetric-memory receive buffers, one per (column slot, kind); grown geometrically, reused across exchanges."""
+
+    def __init__(self, group, device):
+        import torch.distributed._symmetric_memory as symm
+        self.symm, self.group, self.device = symm, group, device
+        self.bufs = {}
+
+    def get(self, key, nbytes):
+        import torch
+        cur = self.bufs.get(key)
+        if cur is None or cur[0].numel() < nbytes:
+            cap = max(int(nbytes * 1.25) + 4096, 1 << 20)
+            cap = (cap + 255) // 256 * 256
+            t = self.symm.empty(cap, dtype=torch.uint8, device=self.device)
+            hdl = self.symm.rendezvous(t, self.group)
+            cur = (t, hdl)
+            self.bufs[key] = cur
+        return cur
+
+
 class HashPartitionExchange:
     """exchange(page) -> the rows of every rank whose key hashes to this rank."""
 
-    def __init__(self, partitioner=None, group=None, device=None):
+    def __init__(self, partitioner=None, group=None, device=None, peer="auto"):
         import torch.distributed as dist
         self.dist = dist
         self.group = group
@@ -72,6 +98,88 @@ class HashPartitionExchange:
         self.sent_rows = 0
         self.received_rows = 0
         self.bytes_sent = 0
+        # peer mode: decided once, by everyone together (a rank that cannot set up symmetric memory takes all ranks to NCCL)
+        self.peer = None
+        self.peer_why = "not requested"
+        if peer and self.backend == "nccl" and self.world > 1:
+            import os
+            import torch
+            ok = 0
+            if os.environ.get("PRESTOGPU_EXCHANGE", "") != "nccl":
+                try:
+                    pg = group if group is not None else dist.group.WORLD
+                    pb = _PeerBuffers(pg, torch.device("cuda", torch.cuda.current_device()))
+                    pb.get(("probe", 0), 1024)[1].barrier()
+                    torch.cuda.synchronize()
+                    ok = 1
+                except Exception as e:     # noqa: BLE001 - any failure means "use the collective"
+                    self.peer_why = "symmetric memory unavailable: %s" % (str(e).splitlines()[0][:200] if str(e) else type(e).__name__)
+            else:
+                self.peer_why = "PRESTOGPU_EXCHANGE=nccl"
+            t = torch.tensor([ok], dtype=torch.int64, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+            if int(t.item()) == 1:
+                self.peer = pb
+                self.peer_why = "symmetric memory"
+            elif ok:
+                self.peer_why = "another rank could not set up symmetric memory"
+
+    def _exchange_peer(self, page, key_channels, hash_channel):
+        """Fused partition + transfer: rows are stored directly into the destination ranks' symmetric receive buffers."""
+        import torch
+        dist, W, me = self.dist, self.world, self.rank
+        blocks = page.blocks
+        n = page.position_count
+        ctx = self.partitioner.ctx
+        keys = [blocks[c] for c in key_channels]
+        hc = blocks[hash_channel].pg_col() if hash_channel is not None else None
+        counts = (C.c_int64 * W)()
+        h = C.c_void_p()
+        N.check(ctx.handle, N.lib().pg_partition_create(ctx.handle, col_array(keys), len(keys), C.byref(hc) if hc else None, n, W, 0, counts,
+                                                        C.byref(h)))
+        try:
+            # everyone learns the whole counts matrix and which columns carry nulls anywhere: one small all-gather
+            mine = torch.tensor([int(c) for c in counts] + [1 if b.nulls is not None else 0 for b in blocks], dtype=torch.int64, device=self.device)
+            allv = torch.empty(W * mine.numel(), dtype=torch.int64, device=self.device)
+            dist.all_gather_into_tensor(allv, mine, group=self.group)
+            m = allv.view(W, -1).cpu().numpy()
+            cm = m[:, :W]                                        # cm[s][r] rows rank s sends to rank r
+            nulls_any = m[:, W:].max(axis=0) > 0
+            recv_total = cm.sum(axis=0)                          # rows each rank receives
+            cap_rows = int(recv_total.max())
+            n_out = int(recv_total[me])
+            offs = (C.c_int64 * W)(*[int(cm[:me, r].sum()) for r in range(W)])   # where my rows start in rank r's buffer
+            out_blocks = []
+            first = True
+            for ci, (b, nullable) in enumerate(zip(blocks, nulls_any)):
+                if b.type in (N.VARCHAR, N.VARBINARY):
+                    raise N.PrestoGpuError(N.PG_E_INVALID_ARGUMENT, "variable width columns cannot cross the device exchange")
+                dt = _torch_dtype(b.type)
+                k = 2 if b.type == N.LONG_DECIMAL else 1
+                esz = torch.empty(0, dtype=dt).element_size() * k
+                vbuf, vh = self.peer.get((ci, "v"), max(cap_rows, 1) * esz)
+                nbuf, nh = (self.peer.get((ci, "n"), max(cap_rows, 1)) if nullable else (None, None))
+                if first:
+                    vh.barrier()          # stream-ordered: every rank's earlier readers of its receive buffers are done
+                    first = False
+                pv = (C.c_void_p * W)(*[int(vh.buffer_ptrs[r]) for r in range(W)])
+                pn = (C.c_void_p * W)(*[int(nh.buffer_ptrs[r]) for r in range(W)]) if nullable else None
+                src = b
+                if nullable and b.nulls is None:     # someone else's rows have nulls: mine travel with an all-zero mask
+                    src = Block(b.type, b.values, torch.zeros(n, dtype=torch.uint8, device=self.device), None, n, b.precision, b.scale)
+                col = src.pg_col()
+                N.check(ctx.handle, N.lib().pg_partition_scatter_peers(h, C.byref(col), pv, pn, offs))
+                vals = vbuf[: n_out * esz].view(dt)
+                nulls = nbuf[:n_out] if nullable else None
+                out_blocks.append(Block(b.type, vals, nulls, None, n_out, b.precision, b.scale))
+                self.bytes_sent += (n - int(counts[me])) * esz
+            if not first:
+                vh.barrier()              # every rank's stores have landed before anyone reads its buffer
+        finally:
+            N.lib().pg_partition_destroy(h)
+        self.sent_rows += n - int(counts[me])
+        self.received_rows += n_out
+        return Page(*out_blocks, position_count=n_out)
 
     def _as_tensor(self, arr):
         import torch
@@ -84,6 +192,8 @@ class HashPartitionExchange:
 
     def exchange(self, page, key_channels, hash_channel=None):
         import torch
+        if self.peer is not None:
+            return self._exchange_peer(page, key_channels, hash_channel)
         dist, W = self.dist, self.world
         part_page, counts = self.partitioner.partition(page, key_channels, W, hash_channel)
         send = torch.tensor(counts, dtype=torch.int64, device=self.device)

@@ -122,6 +122,22 @@ class HashAggregationOperator:
         self._next_group += n
         return Page(*[o.block(n) for o in outs], position_count=n)
 
+    def get_output_packed(self, buf_ptr, capacity):
+        """All groups as ONE packed host page (the PARTIAL -> FINAL wire format, include/prestogpu.h) written at buf_ptr.
+        Returns the number of bytes; the operator is finished afterwards."""
+        groups = self._stats()[0]
+        nbytes, eg = C.c_int64(), C.c_int64(-1)
+        N.check(self.ctx.handle, N.lib().pg_hashagg_get_output_packed(self._h, 0, groups, C.c_void_p(buf_ptr), capacity, C.byref(nbytes), C.byref(eg)))
+        self._next_group = groups
+        self._finished = True
+        return nbytes.value
+
+    def add_packed(self, buf_ptrs):
+        """Packed pages (one per producer) as one input page, rows in buffer order."""
+        assert self.needs_input(), "Operator is already finishing"
+        arr = (C.c_void_p * len(buf_ptrs))(*buf_ptrs)
+        N.check(self.ctx.handle, N.lib().pg_hashagg_add_packed(self._h, arr, len(buf_ptrs)))
+
     def close(self):
         if self._h:
             N.lib().pg_hashagg_destroy(self._h)

@@ -397,3 +397,53 @@ def test_many_groups_partial_then_final(pgpu):
         final.add_input(p)
     final.finish()
     _assert_rows_equal(rows_of(drain(final)), _oracle_rows(P, None, [blocks], aggs))
+
+
+def test_packed_pages_carry_partial_output_to_final(pgpu):
+    """pg_hashagg_get_output_packed / pg_hashagg_add_packed: the PARTIAL -> FINAL wire format.  Three producers (Q1-shaped plans
+    over different row ranges, VARCHAR keys, decimal sum/avg states as VARBINARY, counts) each leave one packed page; a FINAL
+    operator fed with the three buffers must give exactly what a FINAL operator fed with the same pages block by block gives,
+    and what the oracle computes over all rows in one SINGLE step."""
+    P = pgpu
+    from presto_b200 import tpch
+    cols = tpch.lineitem(60_000 / 5_998_605.2, seed=9, device="cuda")
+    page = tpch.page_to_host(tpch.q1_page(cols), pinned=False)
+    aggs = tpch.q1_aggregators()
+    n = page.position_count
+    cuts = [0, n // 3, n // 3 + 11, n]
+    bufs, pages = [], []
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        blocks = [b.slice(lo, hi) if hasattr(b, "slice") else None for b in page.blocks]
+        if any(b is None for b in blocks):
+            pytest.skip("Block.slice not available")
+        for packed in (True, False):
+            op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.PARTIAL, aggs, max_partial_memory=1 << 40)
+            op.add_input(P.Page(*blocks, position_count=hi - lo))
+            op.finish()
+            if packed:
+                buf = np.zeros(1 << 16, dtype=np.uint8)
+                with pytest.raises(P.native.PrestoGpuError):
+                    op.get_output_packed(buf.ctypes.data, 16)            # too small: PG_NEED_MEMORY, nothing consumed
+                nb = op.get_output_packed(buf.ctypes.data, buf.nbytes)
+                assert 0 < nb <= buf.nbytes and int(buf[:8].view(np.int64)[0]) == nb
+                bufs.append(buf)
+            else:
+                pages += drain(op)
+            op.close()
+    fin_aggs, ch = [], 2
+    for a in aggs:
+        fin_aggs.append(P.AggregatorFactory(a.kind, a.in_type, ch))
+        ch += len(P.intermediate_types(a.kind, a.in_type))
+    f1 = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs)
+    f1.add_packed([b.ctypes.data for b in bufs])
+    f1.finish()
+    f2 = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs)
+    for p in pages:
+        f2.add_input(p)
+    f2.finish()
+    got, want = rows_of(drain(f1)), rows_of(drain(f2))
+    assert got == want and len(got) > 0
+    single = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.SINGLE, aggs)
+    single.add_input(page)
+    single.finish()
+    assert sorted(got) == sorted(rows_of(drain(single)))

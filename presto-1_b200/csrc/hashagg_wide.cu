@@ -55,6 +55,7 @@ __global__ void wide_rebuild_kernel(const unsigned long long* old_table, int64_t
 // ---- output numbering.  Buckets are addressed by one index: [0, F) the front region, [F, F + cap) the table, then the two extra buckets
 struct WideView {
     const unsigned long long* front;
+    const unsigned long long* fkeys;      // the front buckets' packed keys: 8 bytes say whether a 64..160-byte bucket is in use
     const unsigned long long* table;
     int64_t F, cap;
     int bw;
@@ -65,6 +66,7 @@ __global__ void wide_mark_first_rows_kernel(WideView v, uint32_t* bitmap) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < v.total(); i += stride) {
+        if (i < v.F && v.fkeys[i] == 0) continue;
         const unsigned long long* b = v.at(i);
         if (i < v.F + v.cap ? b[0] == 0 : b[1] == 0) continue;
         const unsigned long long row = ~b[1];
@@ -125,22 +127,6 @@ struct GatherPlan {
         words[PGW_MAX_AGGS];
     unsigned long long* state[PGW_MAX_AGGS];
 };
-// group id of every occupied bucket -> bucket_of_group[gid] (4-byte writes into an array that mostly lives in L2)
-__global__ void wide_number_buckets_kernel(WideView v, const uint32_t* bitmap, const uint32_t* word_prefix,
-                                           uint32_t* bucket_of_group, Slot* special) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    const int64_t cap = v.F + v.cap;
-    for (; i < v.total(); i += stride) {
-        const unsigned long long* b = v.at(i);
-        if (i < cap ? b[0] == 0 : b[1] == 0) continue;
-        const unsigned long long row = ~b[1];
-        const uint32_t word = bitmap[row >> 5];
-        const int64_t gid = (int64_t)word_prefix[row >> 5] + __popc(word & ((1u << (row & 31)) - 1u));
-        bucket_of_group[gid] = (uint32_t)i;
-        if (i == cap) special[1].gid = (int32_t)gid;     // the null group (BigintGroupByHash.java:215-222)
-    }
-}
 // 192-bit two's complement accumulator helpers for recombining limb sums
 __device__ __forceinline__ void add192(unsigned long long* w, unsigned long long a0, unsigned long long a1, unsigned long long a2) {
     unsigned long long s0 = w[0] + a0;
@@ -161,6 +147,44 @@ __device__ __forceinline__ void add_limb(unsigned long long* w, unsigned long lo
         default: add192(w, 0, x << 32, up); break;
     }
 }
+// one group's key and recombined states into the dense per-group arrays (row g)
+__device__ __forceinline__ void wide_emit_group(const unsigned long long* b, int64_t g, bool special, const GatherPlan& p, int64_t* values_by_group) {
+    values_by_group[g] = special ? 0 : (int64_t)b[0];
+    const unsigned long long flags = p.flag_word >= 0 ? b[p.flag_word] : 0;
+    for (int a = 0; a < p.naggs; a++) {
+        unsigned long long* st = p.state[a] + g * p.words[a];
+        st[0] = p.cnt_mode[a] == 0 ? b[p.cnt_word[a]] : ((flags >> p.flag_bit[a]) & 1ULL);
+        const unsigned long long* v = b + p.val_word[a];
+        if (p.op[a] == OP_SUM_F64) st[1] = v[0];
+        else if (p.op[a] != OP_COUNT) {
+            unsigned long long w[3] = {0, 0, 0};
+            if (p.in_kind[a] == IN_DEC128) { add_limb(w, v[0], 0, false); add_limb(w, v[1], 32, false); add_limb(w, v[2], 64, false); add_limb(w, v[3], 96, true); }
+            else { add_limb(w, v[0], 0, false); add_limb(w, v[1], 32, true); }
+            st[1] = w[0]; st[2] = w[1];
+            if (p.op[a] == OP_SUM_DEC) st[3] = w[2];
+        }
+    }
+}
+// group id of every occupied bucket.  Buckets of the front region lie in (nearly) first-seen order when the rows arrived sorted,
+// so their keys and states go straight to row gid of the dense arrays (a sequential sweep on both sides); buckets of the hashed
+// table only record bucket_of_group[gid] and are fetched in group order by wide_gather_kernel (random reads, coalesced writes).
+__global__ void wide_number_buckets_kernel(WideView v, GatherPlan p, const uint32_t* bitmap, const uint32_t* word_prefix,
+                                           uint32_t* bucket_of_group, Slot* special, int64_t* values_by_group) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t cap = v.F + v.cap;
+    for (; i < v.total(); i += stride) {
+        if (i < v.F && v.fkeys[i] == 0) continue;
+        const unsigned long long* b = v.at(i);
+        if (i < cap ? b[0] == 0 : b[1] == 0) continue;
+        const unsigned long long row = ~b[1];
+        const uint32_t word = bitmap[row >> 5];
+        const int64_t gid = (int64_t)word_prefix[row >> 5] + __popc(word & ((1u << (row & 31)) - 1u));
+        if (i < v.F) wide_emit_group(b, gid, false, p, values_by_group);
+        else bucket_of_group[gid] = (uint32_t)i;
+        if (i == cap) special[1].gid = (int32_t)gid;     // the null group (BigintGroupByHash.java:215-222)
+    }
+}
 // in group-id order: read the group's bucket (one random 64..160 byte read), write keys and dense states (coalesced)
 __global__ void wide_gather_kernel(WideView v, GatherPlan p, const uint32_t* bucket_of_group, int64_t groups,
                                    int64_t* values_by_group) {
@@ -169,22 +193,8 @@ __global__ void wide_gather_kernel(WideView v, GatherPlan p, const uint32_t* buc
     const int64_t cap = v.F + v.cap;
     for (; g < groups; g += stride) {
         const int64_t i = bucket_of_group[g];
-        const unsigned long long* b = v.at(i);
-        values_by_group[g] = i >= cap ? 0 : (int64_t)b[0];
-        const unsigned long long flags = p.flag_word >= 0 ? b[p.flag_word] : 0;
-        for (int a = 0; a < p.naggs; a++) {
-            unsigned long long* st = p.state[a] + g * p.words[a];
-            st[0] = p.cnt_mode[a] == 0 ? b[p.cnt_word[a]] : ((flags >> p.flag_bit[a]) & 1ULL);
-            const unsigned long long* v = b + p.val_word[a];
-            if (p.op[a] == OP_SUM_F64) st[1] = v[0];
-            else if (p.op[a] != OP_COUNT) {
-                unsigned long long w[3] = {0, 0, 0};
-                if (p.in_kind[a] == IN_DEC128) { add_limb(w, v[0], 0, false); add_limb(w, v[1], 32, false); add_limb(w, v[2], 64, false); add_limb(w, v[3], 96, true); }
-                else { add_limb(w, v[0], 0, false); add_limb(w, v[1], 32, true); }
-                st[1] = w[0]; st[2] = w[1];
-                if (p.op[a] == OP_SUM_DEC) st[3] = w[2];
-            }
-        }
+        if (i == 0xFFFFFFFFLL) continue;                 // a front bucket: already written by wide_number_buckets_kernel
+        wide_emit_group(v.at(i), g, i >= cap, p, values_by_group);
     }
 }
 
@@ -473,7 +483,7 @@ void wide_prepare_output(WideTable* w, pg_groupby* gb, const std::vector<pg_agg*
     DevBuf bitmap(ctx, nwords * 4), prefix(ctx, nwords * 4);
     memset_async(ctx, bitmap.p, 0, nwords * 4);
     WideView view;
-    view.front = w->front.as<unsigned long long>(); view.table = w->table.as<unsigned long long>();
+    view.front = w->front.as<unsigned long long>(); view.fkeys = w->front_keys.as<unsigned long long>(); view.table = w->table.as<unsigned long long>();
     view.F = w->front_buckets; view.cap = w->cap; view.bw = w->bucket_words;
     PG_CHECK_STATE(w->front_buckets + w->cap + 2 < (1LL << 32), "hash table exceeds the supported size");
     const int grid = grid_for(ctx, w->front_buckets + w->cap + 2, 256);
@@ -496,9 +506,11 @@ void wide_prepare_output(WideTable* w, pg_groupby* gb, const std::vector<pg_agg*
         p.state[i] = aggs[i]->state.as<unsigned long long>();
     }
     DevBuf bucket_of_group(ctx, (groups + 1) * 4);
-    PG_LAUNCH(ctx, wide_number_buckets_kernel, grid, 256, 0, view, bitmap.as<uint32_t>(),
-              prefix.as<uint32_t>(), bucket_of_group.as<uint32_t>(), gb->slots.as<Slot>() + gb->cap);
-    if (groups > 0)
+    memset_async(ctx, bucket_of_group.p, 0xff, (groups + 1) * 4);
+    PG_LAUNCH(ctx, wide_number_buckets_kernel, grid, 256, 0, view, p, bitmap.as<uint32_t>(), prefix.as<uint32_t>(), bucket_of_group.as<uint32_t>(),
+              gb->slots.as<Slot>() + gb->cap, gb->values_by_group.as<int64_t>());
+    // (with a front region the hashed table holds few groups, often none: the gather then has nothing to fetch)
+    if (groups > 0 && w->claimed + (w->null_seen ? 1 : 0) + (w->zero_seen ? 1 : 0) > 0)
         PG_LAUNCH(ctx, wide_gather_kernel, grid_for(ctx, groups, 256), 256, 0, view, p,
                   bucket_of_group.as<uint32_t>(), groups, gb->values_by_group.as<int64_t>());
     gb->groups = groups;

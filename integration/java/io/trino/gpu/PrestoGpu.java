@@ -54,6 +54,12 @@ public final class PrestoGpu
 
     public static native int hashaggDestroy(long op);
 
+    /** Groups [first, first+n) as one self-describing packed page in a direct ByteBuffer (PARTIAL -> FINAL wire format, prestogpu.h). */
+    public static native int hashaggGetOutputPacked(long op, long first, long n, java.nio.ByteBuffer directBuffer, long[] outBytes, long[] errorGroup);
+
+    /** Packed pages (direct ByteBuffers, one per producer) as one input page of a FINAL / INTERMEDIATE operator. */
+    public static native int hashaggAddPacked(long op, java.nio.ByteBuffer[] directBuffers);
+
     public static native int groupbyGetGroupIds(long gb, int[] types, Object[] values, Object[] nulls, Object[] offsets, int[] arrayOffsets, boolean lastIsHash, long positionCount, int[] outIds, long[] outGroupCount);
 
     public static native int lookupProbe(long lookup, int[] types, Object[] values, Object[] nulls, Object[] offsets, int[] arrayOffsets, boolean lastIsHash, long positionCount, int joinType, int[] outProbeIdx, long[] outBuildPos, long[] nOut);

@@ -179,6 +179,27 @@ JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggDestroy(JNIEnv* env, j
     return pg_hashagg_destroy((pg_hashagg*)(intptr_t)op);
 }
 
+/* ---- packed pages: PARTIAL output -> FINAL input between processes (the job of PagesSerde in the reference's exchange) ---- */
+JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggGetOutputPacked(JNIEnv* env, jclass cls, jlong op, jlong first, jlong n,
+        jobject directBuffer, jlongArray outBytes, jlongArray errorGroup) {
+    void* buf = (*env)->GetDirectBufferAddress(env, directBuffer);
+    jlong cap = (*env)->GetDirectBufferCapacity(env, directBuffer);
+    int64_t nbytes = 0, eg = -1;
+    jint rc = pg_hashagg_get_output_packed((pg_hashagg*)(intptr_t)op, first, n, buf, cap, &nbytes, &eg);
+    jlong jb = nbytes, jeg = eg;
+    (*env)->SetLongArrayRegion(env, outBytes, 0, 1, &jb);      /* on PG_NEED_MEMORY: the size a retry needs */
+    (*env)->SetLongArrayRegion(env, errorGroup, 0, 1, &jeg);
+    return rc;
+}
+
+JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggAddPacked(JNIEnv* env, jclass cls, jlong op, jobjectArray directBuffers) {
+    jsize nb = (*env)->GetArrayLength(env, directBuffers);
+    const void* ptrs[64];
+    if (nb > 64) return PG_E_INVALID_ARGUMENT;
+    for (jsize i = 0; i < nb; i++) ptrs[i] = (*env)->GetDirectBufferAddress(env, (*env)->GetObjectArrayElement(env, directBuffers, i));
+    return pg_hashagg_add_packed((pg_hashagg*)(intptr_t)op, ptrs, nb);
+}
+
 /* ---- GroupByHash.getGroupIds(Page) (OP/GroupByHash.java:75) ---- */
 JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_groupbyGetGroupIds(JNIEnv* env, jclass cls, jlong gb, jintArray types,
         jobjectArray values, jobjectArray nulls, jobjectArray offsets, jintArray arrayOffsets, jboolean lastIsHash,

@@ -323,7 +323,7 @@ class MergePipeline:
         import queue
         self.P, self.dist, self.torch, self.fin_aggs, self.local_rank, self.world = P, dist, torch, fin_aggs, local_rank, world
         self.q = queue.Queue(maxsize=3)      # bounded: the pinned send / receive buffers rotate over 8 slots
-        self.fq = queue.Queue(maxsize=3)
+        self.fqs = [queue.Queue(maxsize=2) for _ in range(self.FINAL_WORKERS)]     # step i goes to worker i % FINAL_WORKERS (both get warmed up)
         self.results = {}
         self.fctx = []
         self.send_bufs = []
@@ -334,9 +334,9 @@ class MergePipeline:
         self.thread.start()
         self.ready.wait()
         self.workers = []
-        for _ in range(self.FINAL_WORKERS):
+        for wi in range(self.FINAL_WORKERS):
             ev = threading.Event()
-            t = threading.Thread(target=self._final_worker, args=(ev,), daemon=True)
+            t = threading.Thread(target=self._final_worker, args=(ev, self.fqs[wi]), daemon=True)
             t.start()
             ev.wait()
             self.workers.append(t)
@@ -356,12 +356,12 @@ class MergePipeline:
                 try:
                     if self.err is None:
                         step, send_host = item
-                        self.fq.put((step, gather_packed(self.dist, torch, send_host, self.world)))
+                        self.fqs[step % self.FINAL_WORKERS].put((step, gather_packed(self.dist, torch, send_host, self.world)))
                 except BaseException as e:   # surfaced by drain()
                     self.err = e
                 self.q.task_done()
 
-    def _final_worker(self, ready):
+    def _final_worker(self, ready, fq):
         torch = self.torch
         torch.cuda.set_device(self.local_rank)
         stream = torch.cuda.Stream(priority=-1)    # its few small kernels go ahead of the next step's big one
@@ -370,9 +370,9 @@ class MergePipeline:
             self.fctx.append(ctx)
             ready.set()
             while True:
-                item = self.fq.get()
+                item = fq.get()
                 if item is None:
-                    self.fq.task_done()
+                    fq.task_done()
                     return
                 try:
                     if self.err is None:
@@ -381,7 +381,7 @@ class MergePipeline:
                         self.results.pop(step - 8, None)
                 except BaseException as e:
                     self.err = e
-                self.fq.task_done()
+                fq.task_done()
 
     def next_send_buffer(self):
         if not self.send_bufs:
@@ -398,7 +398,8 @@ class MergePipeline:
 
     def drain(self):
         self.q.join()
-        self.fq.join()
+        for fq in self.fqs:
+            fq.join()
         if self.err is not None:
             raise self.err
         return self.results.get(self.submitted - 1)
@@ -406,8 +407,8 @@ class MergePipeline:
     def close(self):
         self.q.put(None)
         self.thread.join(timeout=10)
-        for _ in self.workers:
-            self.fq.put(None)
+        for fq in self.fqs:
+            fq.put(None)
         for t in self.workers:
             t.join(timeout=10)
 

@@ -384,8 +384,6 @@ bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const D
     snprintf(buf, sizeof(buf), "#define PGW_MINB %d\n#define PGW_PREFETCH %d\n#define PGW_LDCA %d\n", minb, getenv("PRESTOGPU_WIDE_NOPF") ? 0 : 1,
              getenv("PRESTOGPU_WIDE_LDCG") ? 0 : 1);
     pre += buf;
-    if (getenv("PRESTOGPU_EXP_NORED")) pre += "#define PGW_EXP_NORED 1\n";
-    if (getenv("PRESTOGPU_EXP_NOLOCATE")) pre += "#define PGW_EXP_NOLOCATE 1\n";
     std::string aggs_macro = "#define PGW_AGGS(X)";
     for (size_t i = 0; i < w->aggs.size(); i++) {
         const WideAgg& a = w->aggs[i];

@@ -208,9 +208,6 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
             if (st[j] != 3) continue;
             const u64 seg = (key[j] - (u64)args.k0) >> args.shift;      // keys below k0 wrap around to a huge segment number
             if (seg < args.nseg) { st[j] = 1; idx[j] = (u32)(seg * PGW_CHUNK + ((fmix64(key[j]) >> 40) & (PGW_CHUNK - 4))); }
-#if defined(PGW_EXP_NOLOCATE)
-            if (st[j] == 1) { st[j] = 0; idx[j] = (u32)(seg * PGW_CHUNK + ((key[j] * 5) & (PGW_CHUNK - 1))); bp[j] = args.front + (i64)idx[j] * PGW_BUCKET_WORDS; }
-#endif
         }
         while (true) {
             while (true) {
@@ -297,9 +294,6 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
         u64* b = bp[j];
         if (valid[j] && b == nullptr) { left_out++; args.overflow_flag[r0 + j] = 1; }
         if (b == nullptr) continue;
-#if defined(PGW_EXP_NORED)
-        if (live[j]) b[2] = 1; continue;
-#endif
         u64 flag_bits = 0;
         if (live[j]) atomicMax(b + 1, ~(u64)(args.row_base + first_row[j]));   // smallest row index wins (stored inverted, zero = never seen)
 #define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                  \

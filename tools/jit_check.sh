@@ -1,6 +1,7 @@
 #!/bin/bash
 # compile the run-time specialised wide-aggregation body with nvcc for a representative plan (syntax / register check without a GPU)
 set -e
+mkdir -p /tmp/jc
 D=$(cd "$(dirname "$0")/../presto-1_b200/csrc/jit" && pwd)
 for RANGE in 0 1; do for QUOTA in 0 1; do
 cat > /tmp/jc/w.cu <<EOS

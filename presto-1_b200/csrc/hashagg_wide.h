@@ -32,6 +32,8 @@ struct WideTable {
     // range-chunked front region, planned from the first page's key sample when the rows arrive (nearly) sorted by key:
     // chunk (key - k0) >> shift of WIDE_CHUNK buckets holds the keys of its key range, hashed inside the chunk, so consecutive
     // rows touch consecutive memory.  Keys outside the planned range or whose chunk is full live in `table` as usual.
+    bool split = true;            // locate kernel + update kernel instead of the fused one (fixed for the table's life: the two
+                                  // place keys differently inside a front chunk)
     bool range = false;
     int64_t k0 = 0, nseg = 0, front_buckets = 0, front_claimed = 0;
     int32_t shift = 0;

@@ -29,6 +29,10 @@ struct PgwArgs {
     unsigned long long nseg;
     int shift;
     int pad2;
+    // split mode (PGW_BIDX): the bucket of every row was resolved by wide_locate_kernel (hashagg_wide.cu); bucket numbers count the
+    // front region first, then the table and its two extra buckets; >= 0xFFFFFFFE: the row is not handled by this launch
+    const unsigned int* bidx;
+    unsigned long long front_buckets;
 };
 
 #endif

@@ -16,6 +16,9 @@
 #ifndef PGW_FLAGS_UNCONDITIONAL
 #define PGW_FLAGS_UNCONDITIONAL 0
 #endif
+#ifndef PGW_BIDX
+#define PGW_BIDX 0
+#endif
 #ifndef PGW_LDCA
 #define PGW_LDCA 1
 #endif
@@ -138,11 +141,20 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
     const i64 cap = args.cap;
     // ---- loads
     u64 key[V];
-    ld_u64<V>(args.keys, r0, key);
     u32 kn[V], only[V];
     (void)kn; (void)only;
+#if PGW_BIDX
+    // split mode: the bucket number of every row replaces its key (equal keys have equal buckets)
+    u32 bi[V];
+    if constexpr (V == 1) bi[0] = __ldg(args.bidx + r0);
+    else { const uint4 t = __ldg((const uint4*)(args.bidx + r0)); bi[0] = t.x; bi[1] = t.y; bi[2] = t.z; bi[3] = t.w; }
+#pragma unroll
+    for (int j = 0; j < V; j++) key[j] = bi[j];
+#else
+    ld_u64<V>(args.keys, r0, key);
     if (PGW_HASKEYNULL) ld_u8<V>(args.key_nulls, r0, kn);
     if (PGW_HASONLY) ld_u8<V>(args.only_rows, r0, only);
+#endif
 #define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                               \
     PGW_LD_##IN(a)                                                                                                            \
     u32 PGW_CAT(m0, a)[V], PGW_CAT(m1, a)[V], PGW_CAT(m2, a)[V];                                                               \
@@ -154,7 +166,11 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
 #undef PG_X
     bool valid[V], isnull[V];
 #pragma unroll
+#if PGW_BIDX
+    for (int j = 0; j < V; j++) { valid[j] = bi[j] < 0xFFFFFFFEu; isnull[j] = false; }
+#else
     for (int j = 0; j < V; j++) { valid[j] = !PGW_HASONLY || only[j] != 0; isnull[j] = PGW_HASKEYNULL && kn[j] != 0; }
+#endif
 #define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                               \
     bool PGW_CAT(ok, a)[V]; u32 PGW_CAT(cn, a)[V];                                                                            \
     _Pragma("unroll") for (int j = 0; j < V; j++) {                                                                           \
@@ -180,6 +196,15 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
 #undef PG_X
         }
     }
+#if PGW_BIDX
+    u64* bp[V];
+#pragma unroll
+    for (int j = 0; j < V; j++) {
+        bp[j] = nullptr;
+        if (live[j]) bp[j] = bi[j] < args.front_buckets ? args.front + (i64)bi[j] * PGW_BUCKET_WORDS
+                                                        : args.table + ((i64)bi[j] - (i64)args.front_buckets) * PGW_BUCKET_WORDS;
+    }
+#else
     // ---- locate or claim the bucket of every run.  All loops below run a warp-uniform number of rounds (__any_sync) with predicated
     // bodies: lanes that leave a data-dependent probe loop at different iterations are NOT brought back together by the hardware, and
     // the rest of the kernel would then run a few lanes at a time (measured: 3.9 of 32 lanes active per instruction, 5.9 ms against 1.x).
@@ -285,6 +310,7 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
         claims += mine;
 #endif
     }
+#endif
     // rows absorbed by a later row share its bucket
 #pragma unroll
     for (int j = V - 2; j >= 0; j--) if (valid[j] && !live[j]) bp[j] = bp[j + 1];
@@ -292,7 +318,9 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
 #pragma unroll
     for (int j = 0; j < V; j++) {
         u64* b = bp[j];
+#if !PGW_BIDX
         if (valid[j] && b == nullptr) { left_out++; args.overflow_flag[r0 + j] = 1; }
+#endif
         if (b == nullptr) continue;
         u64 flag_bits = 0;
         if (live[j]) atomicMax(b + 1, ~(u64)(args.row_base + first_row[j]));   // smallest row index wins (stored inverted, zero = never seen)
@@ -331,7 +359,8 @@ extern "C" __global__ void __launch_bounds__(256, PGW_MINB) pg_wide_agg(const Pg
     for (i64 r0 = ((i64)blockIdx.x * blockDim.x + threadIdx.x) * PGW_VEC; r0 + PGW_VEC <= n; r0 += stride) {
         if (PGW_PREFETCH && PGW_VEC == 4 && r0 + stride + PGW_VEC <= n) {
             const i64 rn = r0 + stride;
-            if ((threadIdx.x & 3) == 0) pf_l2(args.keys + rn);
+            if (!PGW_BIDX && (threadIdx.x & 3) == 0) pf_l2(args.keys + rn);
+            if (PGW_BIDX && (threadIdx.x & 7) == 0) pf_l2(args.bidx + rn);
 #define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT) PGW_PF_##IN(a)
             PGW_AGGS(PG_X)
 #undef PG_X

@@ -168,7 +168,13 @@ __global__ void __launch_bounds__(J_THREADS) j_build_kernel(JSlot* slots, int64_
 PG_D void jl_start(const JLayout& L, unsigned long long key, uint64_t h, int64_t& p, int& left) {
     if (L.range) {
         const unsigned long long seg = (key - L.kmin) >> L.shift;      // keys below kmin wrap around to a huge chunk number
-        if (seg < (unsigned long long)L.nchunks) { p = (int64_t)(((seg << 2) + (h & 3)) << 3) + (int64_t)((h >> 2) & 7); left = 8; return; }
+        if (seg < (unsigned long long)L.nchunks) {
+            // line and start slot inside the chunk: multiplicative (Fibonacci) hashing of the key itself.  A chunk holds consecutive
+            // keys when the rows arrive sorted, and those spread almost evenly over the 32 slots - with the murmur bits two of the ~4
+            // keys of a line started at the same slot every other line, and the loser of the claim had to read the slot again.
+            const unsigned long long f = L.fib ? (key * 0x9E3779B97F4A7C15ULL) >> 59 : (((h & 3) << 3) | ((h >> 2) & 7));
+            p = (int64_t)(seg << 5) + (int64_t)f; left = 8; return;
+        }
     }
     p = L.R + (int64_t)((L.range ? h >> 8 : h) & (uint64_t)L.omask);      // (without a range region: the generic kernels' fmix64 & mask)
     left = 0;
@@ -726,7 +732,7 @@ static void lookup_build(pg_lookup* ls) {
             const int64_t nchunks = (int64_t)(((unsigned long long)mm[1] - (unsigned long long)mm[0]) >> shift) + 1;
             const int64_t R = nchunks * 32, ocap = overflow_slots(rows);
             if (R <= 5 * rows + 4096 && R + ocap < (1LL << 31) - 4) {
-                L.range = 1; L.shift = shift; L.kmin = (unsigned long long)mm[0]; L.nchunks = nchunks; L.R = R;
+                L.range = 1; L.fib = getenv("PRESTOGPU_JOIN_NOFIB") ? 0 : 1; L.shift = shift; L.kmin = (unsigned long long)mm[0]; L.nchunks = nchunks; L.R = R;
                 L.omask = ocap - 1; L.total = R + ocap;
             }
         }

@@ -56,6 +56,7 @@ struct JLayout {
     int64_t omask;       // slots of the hashed region - 1
     int64_t total;       // R + omask + 1; slot `total` holds the key whose bit pattern equals EMPTY_KEY
     int32_t range, shift;
+    int32_t fib, pad;    // slot inside a chunk from multiplicative hashing of the key (1) or from the murmur bits (0)
 };
 
 }  // namespace pg

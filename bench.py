@@ -1,14 +1,20 @@
 #!/usr/bin/env python
-"""bench.py — input rows/s of the hash-aggregation hot path (BASELINE.json metric) on N B200s of one node.
+"""bench.py — input rows/s of the hash-aggregation / hash-join hot path (BASELINE.json metric) on N B200s of one node.
 
-Workload at every N: BASELINE.json configs[1], "TPC-H Q1 on lineitem SF10": GROUP BY returnflag, linestatus (2 x varchar(1), 4 groups)
-with sum/avg over short and long decimals and count(*), 59.99 M input rows per GPU shard, masked by the shipdate filter.
+Headline (`value`, `e2e`, `roofline`): BASELINE.json configs[1], TPC-H Q1 over lineitem SF10 per GPU (weak scaling): GROUP BY
+returnflag, linestatus (2 x varchar(1), 4 groups), sum/avg over short and long decimals and count(*), shipdate filter.
   value : whole-job input rows/s with the columns already resident in HBM (one HashAggregationOperator pass per step)
   e2e   : the same pass through the C ABI with HOST (pinned) column buffers, host->device copies inside the timed region
-  N > 1 : weak scaling — every rank aggregates its own SF10 shard (PARTIAL step), the 4-row intermediate states are
-          all-gathered over NCCL and merged by a FINAL-step operator on every rank (the reference's partial->final plan).
-`--impl reference` times the CPU restatement of the reference's operators (oracle/, kind "port": the reference is Java and no
-JDK exists here) on all host threads over a bounded sample of the same workload.
+  N > 1 : every rank aggregates its own SF10 shard (PARTIAL), the 4-row intermediate pages are all-gathered over NCCL and merged by a
+          FINAL step on every rank (presto-1_b200/plans.py PartialFinalAggregation).
+`workloads` (same JSON line): the other half of the metric at TPC-H SF100 *in total* (strong scaling: every rank holds 1/N of the rows,
+disjoint order-key ranges): BASELINE.json configs[2] GROUP BY orderkey (150 M groups; dbgen order and a random permutation of the
+same rows) and configs[3] lineitem JOIN orders (150 M-row build, 600 M-row probe + gather; dbgen order and shuffled).  At N > 1 the
+rows cross the hash-partitioned exchange (presto-1_b200/exchange.py: fused partition + peer-memory stores over NVLink, NCCL
+all-to-all as the alternative) inside the timed region.  Every workload checks its own full-size result and raises on a mismatch;
+`crosscheck` compares the same plans at a small scale factor with the CPU oracle and, at N > 1, the peer exchange with the NCCL one.
+`--impl reference` times the CPU restatement of the reference's operators (oracle/, kind "port": the reference is Java and no JDK
+exists here) on all host threads over the same Q1 input.
 """
 import argparse
 import json
@@ -22,21 +28,40 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 ROWS_PER_SF = 5_998_605.2
+METRIC = "input rows/sec for GROUP BY & hash-join probe at 1/2/4/8 B200; % HBM roofline"
+
+# Algorithmic bytes per row (DESIGN.md §3 states each term)
+B_GROUPBY_ORDERKEY = 136      # K 8 + inputs 16 + slot 16 + 2 x state (8 + 24 + 16)
+B_JOIN_BUILD = 32             # K 8 + payload 8 + slot 16
+B_JOIN_PROBE = 44             # K 8 + slot 16 + payload gather 8 + output (probe idx 4 + payload 8)
+# per-kernel models for `roofline.achieved` of each workload's dominant kernel (bytes per row that kernel must move)
+KERNEL_BYTES = {
+    "wide_locate_kernel": 8 + 16 + 4,            # key, slot, bucket number out
+    "wide_update_jit": 4 + 16 + 2 * 48,          # bucket number in, two 8-byte arguments, state read-modify-write
+    "wide_agg_jit": 136,                         # fused locate + update
+    "j_build_fast_kernel": 8 + 16,               # key, slot write (the payload stays where addPage put it)
+    "j_build_kernel": 8 + 16,
+    "j_probe_dense_kernel": 8 + 16 + 4 + 8,      # key, slot, probe idx out, build position out
+    "j_probe_gather_kernel": 44,                 # fused probe + gather (the whole model)
+    "j_gather_fixed_kernel": 8 + 8 + 8,          # build position in, payload gather, payload out
+}
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--extra-shuffle", action="store_true", help="extras: lineitem rows in random order instead of clustered by order key")
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--sf", type=float, default=10.0, help="TPC-H scale factor of the lineitem shard per GPU")
+    ap.add_argument("--sf", type=float, default=10.0, help="TPC-H scale factor of the Q1 lineitem shard per GPU")
+    ap.add_argument("--wide-sf", type=float, default=100.0, help="TOTAL scale factor of the GROUP BY orderkey / join workloads")
+    ap.add_argument("--wide-steps", type=int, default=5)
+    ap.add_argument("--wide-warmup", type=int, default=3)
     ap.add_argument("--cpu-sample-rows", type=int, default=6_000_000)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--extra", action="store_true", help="also time the high-cardinality GROUP BY and join workloads")
-    ap.add_argument("--extra-sf", type=float, default=10.0)
+    ap.add_argument("--no-workloads", action="store_true", help="headline only (skips the SF100 GROUP BY orderkey / join records)")
+    ap.add_argument("--only", default="", help="comma list of workloads to run: groupby,join (default both)")
     return ap.parse_args()
 
 
@@ -78,6 +103,14 @@ class ClockSampler:
         mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
                 "samples": len(self.samples)}
+
+
+def q1_config(sf, rows):
+    """`config` of the headline, identical in both arms."""
+    return {"workload": "TPC-H Q1 on lineitem SF%g per GPU: GROUP BY returnflag,linestatus; 4x sum, 3x avg (decimal), count(*); "
+                        "shipdate filter as mask" % sf,
+            "rows_per_gpu": int(rows), "groups": 4,
+            "l2_policy": "inputs (%.2f GB per pass) exceed the 126 MB L2; no flush needed" % (rows * 67 / 1e9)}
 
 
 # ------------------------------------------------------------------------------------------- CPU arm (oracle port)
@@ -124,18 +157,16 @@ def oracle_q1_pass(O, P, blocks, aggs, nthreads):
     return fgb.export(with_hash=False)[0], out
 
 
-def host_sample_blocks(P, tpch, rows, seed):
-    import torch
-    sf = rows / ROWS_PER_SF
+def host_q1_blocks(tpch, sf, seed):
     cols = tpch.lineitem(sf, seed=seed, device="cpu")
     page = tpch.q1_page(cols)
     return tpch.page_to_host(page, pinned=False).blocks
 
 
-def time_cpu_port(P, tpch, rows, nthreads, steps, warmup, seed=42):
+def time_cpu_port(P, tpch, sf, nthreads, steps, warmup, seed=42):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_lib as O
-    blocks = host_sample_blocks(P, tpch, rows, seed)
+    blocks = host_q1_blocks(tpch, sf, seed)
     n = blocks[0].n
     aggs = tpch.q1_aggregators()
     times = []
@@ -148,419 +179,292 @@ def time_cpu_port(P, tpch, rows, nthreads, steps, warmup, seed=42):
     return n, times
 
 
-# ------------------------------------------------------------------------------------------- GPU arm
-def run_single_pass(P, page, aggs, step, ctx, expected=100_000):
-    """One HashAggregationOperator pass over `page` (device or host buffers); returns the output page on the host."""
-    op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], step, aggs, expected_groups=expected, ctx=ctx)
-    op.add_input(page)
-    op.finish()
-    out = op.get_output()
-    op.close()
-    return out
+# ------------------------------------------------------------------------------------------- GPU arm helpers
+class Env:
+    """What every workload needs: package, torch, process group, context, measured peak."""
 
+    def __init__(self, P, tpch, torch, dist, ctx, world, rank, peak):
+        self.P, self.tpch, self.torch, self.dist, self.ctx, self.world, self.rank, self.peak = P, tpch, torch, dist, ctx, world, rank, peak
 
-_MERGE_BUFS = {}
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
+    def max_over_ranks(self, ms):
+        if self.dist is None:
+            return ms
+        t = self.torch.tensor([ms], device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
 
-def merge_partials_nccl(P, dist, torch, part_page, fin_aggs, ctx, world, run_final=True):
-    """All-gather the (tiny) intermediate page of every rank over NCCL, then ONE FINAL step over the concatenated rows.
-    The page is packed into a pinned buffer: [payload bytes][n][per block: values, offsets, nulls sizes][data]."""
-    import numpy as np
-    from presto_b200.blocks import Block, _NP_DTYPE
-    cap = 1 << 16
-    trace = _MERGE_BUFS.setdefault("trace", [0.0] * 5) if os.environ.get("PRESTOGPU_BENCH_TRACE") else None
-    t0 = time.perf_counter()
-    if "send" not in _MERGE_BUFS:
-        _MERGE_BUFS["send_host"] = torch.zeros(cap, dtype=torch.uint8).pin_memory()
-        _MERGE_BUFS["send"] = torch.zeros(cap, dtype=torch.uint8, device="cuda")
-        _MERGE_BUFS["recv"] = torch.zeros(cap * world, dtype=torch.uint8, device="cuda")
-        _MERGE_BUFS["recv_host"] = torch.zeros(cap * world, dtype=torch.uint8).pin_memory()
-    blobs = []
-    for b in part_page.blocks:
-        hb = b.to_host()
-        for arr in (hb.values, hb.offsets, hb.nulls):
-            blobs.append(np.zeros(0, dtype=np.uint8) if arr is None else np.ascontiguousarray(arr).view(np.uint8).reshape(-1))
-    sizes = np.array([part_page.position_count] + [len(a) for a in blobs], dtype=np.int64)
-    payload = np.concatenate([sizes.view(np.uint8)] + blobs)
-    assert len(payload) <= cap - 8
-    sh = _MERGE_BUFS["send_host"].numpy()
-    sh[:8] = np.array([len(payload)], dtype=np.int64).view(np.uint8)
-    sh[8:8 + len(payload)] = payload
-    t1 = time.perf_counter()
-    _MERGE_BUFS["send"].copy_(_MERGE_BUFS["send_host"], non_blocking=True)
-    dist.all_gather_into_tensor(_MERGE_BUFS["recv"], _MERGE_BUFS["send"])
-    _MERGE_BUFS["recv_host"].copy_(_MERGE_BUFS["recv"], non_blocking=True)
-    torch.cuda.current_stream().synchronize()
-    t2 = time.perf_counter()
-    host = _MERGE_BUFS["recv_host"].numpy()
-    nb = len(part_page.blocks)
-    per_block = [[] for _ in range(nb)]      # (values, offsets, nulls, n) of every rank
-    for r in range(world):
-        chunk = host[r * cap:(r + 1) * cap]
-        ln = int(chunk[:8].view(np.int64)[0])
-        pl = chunk[8:8 + ln]
-        nsz = 1 + 3 * nb
-        sz = pl[:8 * nsz].view(np.int64)
-        pos = 8 * nsz
-        n = int(sz[0])
-        for i in range(nb):
-            parts = []
-            for j in range(3):
-                l = int(sz[1 + 3 * i + j])
-                parts.append(pl[pos:pos + l])
-                pos += l
-            per_block[i].append((parts[0], parts[1], parts[2], n))
-    total = sum(t[3] for t in per_block[0])
-    blocks = []
-    for i, b in enumerate(part_page.blocks):
-        offs = None
-        if b.type in (P.VARCHAR, P.VARBINARY):
-            pieces, vpieces, shift = [np.zeros(1, dtype=np.int32)], [], 0
-            for t in per_block[i]:
-                o = t[1].view(np.int32)
-                used = int(o[-1]) if len(o) else 0
-                pieces.append(o[1:] + shift)
-                vpieces.append(t[0][:used])          # value buffers may be longer than the bytes in use
-                shift += used
-            offs = np.concatenate(pieces)
-            vals = np.concatenate(vpieces) if shift else np.zeros(1, dtype=np.uint8)
-        else:
-            vals = np.concatenate([t[0] for t in per_block[i]]).view(_NP_DTYPE[b.type])
-        nulls = None
-        if any(len(t[2]) for t in per_block[i]):
-            nulls = np.concatenate([t[2] if len(t[2]) else np.zeros(t[3], dtype=np.uint8) for t in per_block[i]])
-        blocks.append(Block(b.type, vals, nulls, offs, total))
-    t3 = time.perf_counter()
-    if trace is not None:
-        for i, d in enumerate((t1 - t0, t2 - t1, t3 - t2)):
-            trace[i] += d
-        trace[4] += 1
-    if not run_final:
-        return blocks, total
-    return final_merge(P, blocks, total, fin_aggs, ctx)
-
-
-def final_merge(P, blocks, total, fin_aggs, ctx):
-    """The FINAL step over the gathered intermediate rows."""
-    trace = _MERGE_BUFS.get("trace")
-    t3 = time.perf_counter()
-    fin = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs, expected_groups=1000, ctx=ctx)
-    fin.add_input(P.Page(*blocks, position_count=total))
-    fin.finish()
-    out = fin.get_output()
-    fin.close()
-    if trace is not None:
-        trace[3] += time.perf_counter() - t3
-    return out
-
-
-PACKED_CAP = 1 << 16
-
-
-def partial_packed(P, page, aggs, ctx, pipe, expected=100_000):
-    """PARTIAL pass on the main thread; its output leaves as one packed page (native, one call) in a pinned send buffer."""
-    op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.PARTIAL, aggs, expected_groups=expected, ctx=ctx)
-    op.add_input(page)
-    op.finish()
-    buf = pipe.next_send_buffer()
-    op.get_output_packed(buf.data_ptr(), PACKED_CAP)
-    op.close()
-    pipe.submit(buf)
-
-
-def gather_packed(dist, torch, send_host, world):
-    """packed page of this rank -> NCCL all-gather -> the ranks' packed pages in pinned host memory.
-    Returns the list of buffer addresses for HashAggregationOperator.add_packed."""
-    cap = PACKED_CAP
-    trace = _MERGE_BUFS.setdefault("trace", [0.0] * 5) if os.environ.get("PRESTOGPU_BENCH_TRACE") else None
-    t0 = time.perf_counter()
-    if "send" not in _MERGE_BUFS:
-        _MERGE_BUFS["send"] = torch.zeros(cap, dtype=torch.uint8, device="cuda")
-        _MERGE_BUFS["recv"] = torch.zeros(cap * world, dtype=torch.uint8, device="cuda")
-        # several receive buffers: the FINAL worker of step i may still read its pages while later steps are gathered
-        _MERGE_BUFS["recv_host"] = [torch.zeros(cap * world, dtype=torch.uint8).pin_memory() for _ in range(8)]
-        _MERGE_BUFS["turn"] = 0
-    t1 = time.perf_counter()
-    rh = _MERGE_BUFS["recv_host"][_MERGE_BUFS["turn"] % 8]
-    _MERGE_BUFS["turn"] += 1
-    _MERGE_BUFS["send"].copy_(send_host, non_blocking=True)
-    dist.all_gather_into_tensor(_MERGE_BUFS["recv"], _MERGE_BUFS["send"])
-    rh.copy_(_MERGE_BUFS["recv"], non_blocking=True)
-    torch.cuda.current_stream().synchronize()
-    t2 = time.perf_counter()
-    if trace is not None:
-        trace[0] += t1 - t0
-        trace[1] += t2 - t1
-        trace[4] += 1
-    base = rh.data_ptr()
-    return [base + r * cap for r in range(world)]
-
-
-def final_merge_packed(P, ptrs, fin_aggs, ctx):
-    trace = _MERGE_BUFS.get("trace")
-    t3 = time.perf_counter()
-    fin = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs, expected_groups=1000, ctx=ctx)
-    fin.add_packed(ptrs)
-    fin.finish()
-    out = fin.get_output()
-    fin.close()
-    if trace is not None:
-        trace[3] += time.perf_counter() - t3
-    return out
-
-
-class MergePipeline:
-    """Second stage of the N > 1 plan, running beside the first: while the main thread runs the PARTIAL pass of step i + 1,
-    a communication thread all-gathers the intermediate rows of step i (NCCL on its own stream, one collective per step, in
-    step order on every rank) and FINAL workers, each with its own pg_ctx and high-priority stream, run the FINAL step of
-    alternate steps.  Every step's final result is produced; the stages merely overlap, as consecutive pages do in the
-    reference's PARTIAL -> exchange -> FINAL plan.  (One FINAL step costs 0.4 ms on an idle GPU but 1.4 ms beside the PARTIAL
-    kernel of the next step - it is a chain of small launches and read-backs - so a single worker capped the 8-GPU step at 2 ms.)"""
-
-    FINAL_WORKERS = 2
-
-    def __init__(self, P, dist, torch, fin_aggs, local_rank, world):
-        import queue
-        self.P, self.dist, self.torch, self.fin_aggs, self.local_rank, self.world = P, dist, torch, fin_aggs, local_rank, world
-        self.q = queue.Queue(maxsize=3)      # bounded: the pinned send / receive buffers rotate over 8 slots
-        self.fqs = [queue.Queue(maxsize=2) for _ in range(self.FINAL_WORKERS)]     # step i goes to worker i % FINAL_WORKERS (both get warmed up)
-        self.results = {}
-        self.fctx = []
-        self.send_bufs = []
-        self.submitted = 0
-        self.err, self.ctx = None, None
-        self.ready = threading.Event()
-        self.thread = threading.Thread(target=self._run, daemon=True)
-        self.thread.start()
-        self.ready.wait()
-        self.workers = []
-        for wi in range(self.FINAL_WORKERS):
-            ev = threading.Event()
-            t = threading.Thread(target=self._final_worker, args=(ev, self.fqs[wi]), daemon=True)
-            t.start()
-            ev.wait()
-            self.workers.append(t)
-
-    def _run(self):
-        torch = self.torch
-        torch.cuda.set_device(self.local_rank)
-        self.stream = torch.cuda.Stream(priority=-1)
-        with torch.cuda.stream(self.stream):
-            self.ctx = self.P.GpuContext(self.local_rank)      # bound to this thread's stream
-            self.ready.set()
-            while True:
-                item = self.q.get()
-                if item is None:
-                    self.q.task_done()
-                    return
-                try:
-                    if self.err is None:
-                        step, send_host = item
-                        self.fqs[step % self.FINAL_WORKERS].put((step, gather_packed(self.dist, torch, send_host, self.world)))
-                except BaseException as e:   # surfaced by drain()
-                    self.err = e
-                self.q.task_done()
-
-    def _final_worker(self, ready, fq):
-        torch = self.torch
-        torch.cuda.set_device(self.local_rank)
-        stream = torch.cuda.Stream(priority=-1)    # its few small kernels go ahead of the next step's big one
-        with torch.cuda.stream(stream):
-            ctx = self.P.GpuContext(self.local_rank)
-            self.fctx.append(ctx)
-            ready.set()
-            while True:
-                item = fq.get()
-                if item is None:
-                    fq.task_done()
-                    return
-                try:
-                    if self.err is None:
-                        step, ptrs = item
-                        self.results[step] = final_merge_packed(self.P, ptrs, self.fin_aggs, ctx)
-                        self.results.pop(step - 8, None)
-                except BaseException as e:
-                    self.err = e
-                fq.task_done()
-
-    def next_send_buffer(self):
-        if not self.send_bufs:
-            self.send_bufs = [self.torch.zeros(PACKED_CAP, dtype=self.torch.uint8).pin_memory() for _ in range(8)]
-        b = self.send_bufs[self.submitted % 8]
-        return b
-
-    def launch_count(self):
-        return self.ctx.launch_count() + sum(c.launch_count() for c in self.fctx)
-
-    def submit(self, page):
-        self.q.put((self.submitted, page))
-        self.submitted += 1
-
-    def drain(self):
-        self.q.join()
-        for fq in self.fqs:
-            fq.join()
-        if self.err is not None:
-            raise self.err
-        return self.results.get(self.submitted - 1)
-
-    def close(self):
-        self.q.put(None)
-        self.thread.join(timeout=10)
-        for fq in self.fqs:
-            fq.put(None)
-        for t in self.workers:
-            t.join(timeout=10)
-
-
-def final_aggs_for(P, aggs, first_channel):
-    fin, ch = [], first_channel
-    for a in aggs:
-        fin.append(P.AggregatorFactory(a.kind, a.in_type, ch))
-        ch += len(P.intermediate_types(a.kind, a.in_type))
-    return fin
-
-
-def extra_workloads(args, P, tpch, ctx, torch, peak, dist=None, world=1, rank=0):
-    """cfg3 (high-cardinality GROUP BY orderkey) and cfg4 (lineitem JOIN orders), device-resident inputs.
-    world > 1: every rank holds its own SF shard (weak scaling); rows are hash-partitioned on orderkey and exchanged with an
-    NCCL all-to-all (presto-1_b200/exchange.py) before the per-GPU operator, the reference's partitioned plan."""
-    from presto_b200.blocks import Block
-    N = P.native
-    res = {}
-    sf = args.extra_sf
-    n_orders = int(1_500_000 * sf)
-    # disjoint order-key ranges per rank: shard r owns orders [r*n_orders, (r+1)*n_orders)
-    li = tpch.lineitem(sf, seed=42 + rank, device="cuda", need=("keys", "double"), shuffle=args.extra_shuffle)
-    n = li["rows"]
-    key_off = rank * tpch.order_key(torch.tensor(n_orders, dtype=torch.int64)).item()
-    li["orderkey"] += key_off
-    page = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, li["quantity"], None, None, n),
-                  Block(N.DOUBLE, li["extendedprice_double"].view(torch.int64), None, None, n), position_count=n)
-    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2)]
-    ex = P.HashPartitionExchange(P.DevicePartitioner(ctx)) if world > 1 else None
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-        barrier()
-        ctx.kernel_report(reset=True)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            out = fn()
-        e1.record()
-        barrier()
-        ms = e0.elapsed_time(e1) / steps
-        if dist is not None:
-            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, out
-
-    def total(x):
-        if dist is None:
+    def total(self, x):
+        """Sum of an int64 (wrapping) over the ranks."""
+        if self.dist is None:
             return int(x)
-        t = torch.tensor([int(x)], device="cuda", dtype=torch.int64)
-        dist.all_reduce(t)
+        t = self.torch.tensor([int(x)], device="cuda", dtype=self.torch.int64)
+        self.dist.all_reduce(t)
         return int(t.item())
 
+    def timed(self, fn, steps, warmup, drain=None):
+        """W untimed + K timed steps bracketed by barrier + synchronize; CUDA events on the launching stream; max over ranks.
+        Returns (ms per step, last result, per-kernel report of the timed region, launches in the timed region)."""
+        torch, ctx = self.torch, self.ctx
+        for _ in range(warmup):
+            fn()
+        if drain:
+            drain()
+        self.barrier()
+        ctx.kernel_report(reset=True)
+        l0 = ctx.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = None
+        for _ in range(steps):
+            out = fn()
+        if drain:
+            out = drain()
+        e1.record()
+        self.barrier()
+        ms = self.max_over_ranks(e0.elapsed_time(e1)) / steps
+        return ms, out, ctx.kernel_report(reset=True), ctx.launch_count() - l0
+
+
+def workload_roofline(env, kern, steps, rows_per_gpu, traffic):
+    """roofline record of a workload's dominant kernel, from the library's per-launch CUDA events inside the timed region."""
+    known = {k: v for k, v in kern.items() if k in KERNEL_BYTES}
+    pool = known or kern
+    if not pool:
+        return None
+    top = max(pool, key=lambda k: pool[k][0])
+    tms, cnt = kern[top]
+    launch_ms = tms / max(cnt, 1)
+    rows_per_launch = rows_per_gpu * steps / max(cnt, 1)
+    bpr = KERNEL_BYTES.get(top)
+    rec = {"bound": "hbm", "kernel": top, "launch_ms": round(launch_ms, 4), "launches_timed": cnt, "peak": env.peak, "unit": "GB/s",
+           "kernels_ms_per_step": {k: round(v[0] / steps, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:8]}}
+    if bpr is not None and launch_ms > 0:
+        ach = rows_per_launch * bpr / (launch_ms / 1e3) / 1e9
+        rec.update({"algorithmic_bytes_per_row": bpr, "rows_per_launch": int(rows_per_launch), "achieved": round(ach, 1),
+                    "frac": round(ach / env.peak, 4)})
+    t = traffic.get(top + "@sf100") if traffic else None
+    rec["traffic"] = t
+    if t is not None:
+        rec["traffic_unit"] = "bytes/launch (ncu dram read+write, SF100 capture on 1 GPU)"
+    return rec
+
+
+def record(env, name, desc, rows_all, ms, brow, kern, steps, rows_per_gpu, traffic, extra=None):
+    r = {"workload": desc, "rows": int(rows_all), "ms_per_step": round(ms, 3), "rows_per_s": rows_all / (ms / 1e3),
+         "algorithmic_bytes_per_row": brow, "hbm_frac_per_gpu": round(rows_all / env.world * brow / (ms / 1e3) / 1e9 / env.peak, 4),
+         "steps": steps, "roofline": workload_roofline(env, kern, steps, rows_per_gpu, traffic)}
+    if extra:
+        r.update(extra)
+    return r
+
+
+# ------------------------------------------------------------------------------------------- SF100 workloads (cfg3, cfg4)
+def wide_workloads(args, env, traffic):
+    """BASELINE.json configs[2] and [3] at SF100 in total; every rank holds 1/world of the orders (a contiguous key range) and their
+    lineitems.  Inputs are device-resident; at world > 1 the hash-partitioned exchange is inside the timed region."""
+    P, tpch, torch, ctx, world, rank = env.P, env.tpch, env.torch, env.ctx, env.world, env.rank
+    from presto_b200.blocks import Block
+    N = P.native
+    only = set(x for x in args.only.split(",") if x)
+    sf = args.wide_sf / world
+    steps, warmup = args.wide_steps, args.wide_warmup
+    res = {"scale": "TPC-H SF%g in total, SF%g per GPU (strong scaling: total rows fixed as N grows)" % (args.wide_sf, sf),
+           "timing": "%d timed steps after %d warm-up steps per workload; inputs (>= 1.2 GB per column) exceed the 126 MB L2" % (steps, warmup)}
+    n_orders = int(1_500_000 * sf)
+    li = tpch.lineitem(sf, seed=42 + rank, device="cuda", need=("keys", "double"))
+    n = li["rows"]
+    key_off = rank * tpch.order_key(torch.tensor(n_orders, dtype=torch.int64)).item()   # disjoint order-key ranges per rank
+    li["orderkey"] += key_off
+    n_all, o_all = env.total(n), env.total(n_orders)
+    exchange = P.HashPartitionExchange(P.DevicePartitioner(ctx)) if world > 1 else None
+    how = "; rows hash-partitioned on orderkey across %d GPUs (%s), then one operator per GPU" % (
+        world, "fused partition + peer-memory stores over NVLink" if exchange.peer is not None else "NCCL all_to_all_single per column: " + exchange.peer_why) if exchange else ""
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2)]
+
+    def li_page(c):
+        return P.Page(Block(N.BIGINT, c["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, c["quantity"], None, None, n),
+                      Block(N.DOUBLE, c["extendedprice_double"].view(torch.int64), None, None, n), position_count=n)
+
+    perm = torch.randperm(n, device="cuda", generator=torch.Generator(device="cuda").manual_seed(7 + rank))
+    lis = {k: li[k][perm] for k in ("orderkey", "quantity", "extendedprice_double")}
+    del perm
     ctx.set_timing(True)
 
-    def gb_pass():
-        local = ex.exchange(page, [0]) if ex else page
-        op = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=n_orders, ctx=ctx, device_output=True)
-        op.add_input(local)
-        op.finish()
-        g = op.get_group_count()
-        out = op.get_output(max_rows=max(g, 1))     # all groups materialised on the device
-        op.close()
-        return g
+    # ---------------- cfg3: GROUP BY orderkey
+    if not only or "groupby" in only:
+        plan = P.PartitionedAggregation([P.BIGINT], [0], aggs, ctx, env.dist, expected_groups=n_orders, exchange=exchange)
+        sorted_result = None
+        for order, cols in (("dbgen order (clustered by orderkey)", li), ("random permutation of the same rows", lis)):
+            page = li_page(cols)
+            ms, (groups, out), kern, _ = env.timed(lambda: plan.run(page), steps, warmup)
+            g_all = env.total(groups)
+            keys, cnt = out.blocks[0].values, out.blocks[1].values
+            qty = out.blocks[2].values.view(-1, 2)[:, 0]           # long decimal low words (sums are far below 2^63)
+            check = {"groups_equal_orders": g_all == o_all,
+                     "count_sum_equals_rows": env.total(cnt.sum().item()) == n_all,
+                     "decimal_sum_equals_column_sum": env.total(qty.sum().item()) == env.total(li["quantity"].sum().item()),
+                     "key_times_count_checksum": env.total((keys * cnt).sum().item()) == env.total(li["orderkey"].sum().item())}
+            if world == 1:
+                if sorted_result is None:
+                    check["keys_in_first_seen_order"] = bool(torch.equal(keys, torch.unique_consecutive(li["orderkey"])))
+                    sorted_result = (keys.clone(), cnt.clone(), qty.clone(), out.blocks[3].values.view(torch.float64).clone())
+                else:
+                    o = torch.argsort(keys)
+                    sk, sc, sq, sd = sorted_result
+                    dbl = out.blocks[3].values.view(torch.float64)[o]
+                    check["equals_dbgen_order_result_per_group"] = bool(torch.equal(keys[o], sk) and torch.equal(cnt[o], sc) and torch.equal(qty[o], sq))
+                    check["double_sums_within_1e-12"] = bool(((dbl - sd).abs() <= 1e-12 * sd.abs()).all().item())
+                    del o, dbl
+            if not all(check.values()):
+                raise SystemExit("bench self-check failed (GROUP BY orderkey, %s): %s" % (order, json.dumps(check)))
+            brow = B_GROUPBY_ORDERKEY + (48 if world > 1 else 0)     # + 2 x 24 B partition pass (read + write of key and inputs)
+            name = "groupby_orderkey" if cols is li else "groupby_orderkey_shuffled"
+            res[name] = record(env, name, "GROUP BY orderkey over lineitem, %s: count(*), sum(quantity decimal), sum(extendedprice double)%s" % (order, how),
+                               n_all, ms, brow, kern, steps, n, traffic,
+                               {"groups": g_all, "selfcheck": check,
+                                "hbm_frac_without_partition_pass": round(n_all / world * B_GROUPBY_ORDERKEY / (ms / 1e3) / 1e9 / env.peak, 4)})
+            del out, keys, cnt, qty, page
+        del sorted_result, plan
+        torch.cuda.empty_cache()
 
-    ms, groups = timed(gb_pass, 3, 1)
-    kern = ctx.kernel_report(reset=True)
-    n_all, g_all = total(n), total(groups)
-    # size-independent properties of the full-size result (outside the timed region): one group per order, the counts
-    # add up to the rows, the decimal sums add up to the column sum (linearity), first-seen order = ascending first row
-    local = ex.exchange(page, [0]) if ex else page
-    chk = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=n_orders, ctx=ctx, device_output=True)
-    chk.add_input(local)
-    chk.finish()
-    gout = chk.get_output(max_rows=max(chk.get_group_count(), 1))
-    chk.close()
-    cnt_sum = total(gout.blocks[1].values.sum().item())
-    qty_sum = total(gout.blocks[2].values.view(-1, 2)[:, 0].sum().item())     # long decimal: low words (sums are far below 2^63)
-    gb_check = {"groups_equal_orders": g_all == total(n_orders), "count_sum_equals_rows": cnt_sum == n_all,
-                "decimal_sum_equals_column_sum": qty_sum == total(li["quantity"].sum().item())}
-    if world == 1 and not args.extra_shuffle:
-        gb_check["keys_in_first_seen_order"] = bool(torch.equal(gout.blocks[0].values, torch.unique_consecutive(li["orderkey"])))
-    if not all(gb_check.values()):
-        raise SystemExit("bench self-check failed (GROUP BY orderkey): %s" % json.dumps(gb_check))
-    del gout, local
-    brow = 136 + (48 if world > 1 else 0)   # + 2 x 24 B partition pass (read + write of key and inputs) when G > 1
-    res["groupby_orderkey"] = {"workload": "GROUP BY orderkey over lineitem SF%g per GPU: count(*), sum(quantity decimal), sum(extendedprice double)%s"
-                                           % (sf, "; hash-partitioned all-to-all then SINGLE per GPU" if world > 1 else ""),
-                               "rows": n_all, "groups": g_all, "ms_per_step": round(ms, 3), "rows_per_s": n_all / (ms / 1e3),
-                               "algorithmic_bytes_per_row": brow, "hbm_frac_per_gpu": round(n_all / world * brow / (ms / 1e3) / 1e9 / peak, 4),
-                               "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:8]},
-                               "selfcheck": gb_check}
-    del page
-    # ---- join: build orders (orderkey unique, totalprice), probe lineitem.orderkey, gather totalprice
-    od = tpch.orders(sf, seed=42 + rank, device="cuda")
-    od["orderkey"] += key_off
+    # ---------------- cfg4: build orders, probe lineitem.orderkey, gather totalprice
+    if not only or "join" in only:
+        od = tpch.orders(sf, seed=42 + rank, device="cuda")
+        od["orderkey"] += key_off
+        bpage = P.Page(Block(N.BIGINT, od["orderkey"], None, None, n_orders), Block(N.DOUBLE, od["totalprice"].view(torch.int64), None, None, n_orders),
+                       position_count=n_orders)
+        join = P.PartitionedHashJoin([P.BIGINT, P.DOUBLE], [0], ctx, env.dist, exchange=exchange)
+        bms, ls, bkern, _ = env.timed(lambda: join.build(bpage), steps, warmup)
+        res["join_build"] = record(env, "join_build", "hash build orders (orderkey unique, totalprice)" + how, o_all, bms,
+                                   B_JOIN_BUILD + (32 if world > 1 else 0), bkern, steps, n_orders, traffic)
+        tp_bits = od["totalprice"].view(torch.int64)
+        for order, cols in (("dbgen order", li), ("random permutation of the same rows", lis)):
+            ppage = P.Page(Block(N.BIGINT, cols["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, cols["quantity"], None, None, n), position_count=n)
+            pms, (local, pp, got), pkern, _ = env.timed(lambda: join.probe(ppage, [0], [1]), steps, warmup)
+            want = tp_bits[torch.searchsorted(od["orderkey"], cols["orderkey"])]      # every lineitem's order lives on the rank that generated it
+            gv = got[0].values.view(torch.int64)
+            check = {"matches_equal_probe_rows": env.total(len(pp)) == n_all,
+                     "gathered_payload_checksum": env.total(gv.sum().item()) == env.total(want.sum().item())}
+            if world == 1:
+                check["probe_positions_ascending"] = bool(torch.equal(pp, torch.arange(n, device="cuda", dtype=torch.int32)))
+                check["gathered_payload_bit_exact"] = bool(torch.equal(gv, want))
+            if not all(check.values()):
+                raise SystemExit("bench self-check failed (join probe, %s): %s" % (order, json.dumps(check)))
+            name = "join_probe" if cols is li else "join_probe_shuffled"
+            res[name] = record(env, name, "INNER join probe lineitem.orderkey -> orders, %s; emits probe positions + gathered totalprice%s" % (order, how),
+                               n_all, pms, B_JOIN_PROBE + (32 if world > 1 else 0), pkern, steps, n, traffic,
+                               {"matches": n_all, "selfcheck": check})
+            del want, gv, got, pp, local, ppage
+        del od, bpage, join, ls
+    ctx.set_timing(False)
+    if exchange:
+        res["exchange"] = {"rows_sent_per_rank": exchange.sent_rows, "bytes_sent_per_rank": exchange.bytes_sent,
+                           "collective": ("fused partition + peer-memory stores over NVLink (pg_partition_scatter_peers into symmetric receive buffers)"
+                                          if exchange.peer is not None else "NCCL all_to_all_single per column (%s)" % exchange.peer_why)}
+    return res
+
+
+# ------------------------------------------------------------------------------------------- cross-checks (small scale factor)
+def crosschecks(env):
+    """The same plans at a small scale factor against the CPU oracle (order-insensitive where the exchange reorders rows), and at
+    N > 1 the peer-memory exchange against the NCCL all-to-all, bit for bit.  Raises on a mismatch.  The oracle is the checker
+    here, never the thing measured."""
+    import numpy as np
+    P, tpch, torch, ctx, world, rank, dist = env.P, env.tpch, env.torch, env.ctx, env.world, env.rank, env.dist
+    from presto_b200.blocks import Block
+    N = P.native
+    sf = 0.02
+    n_orders = int(1_500_000 * sf)
+    out = {}
+
+    def shard(r, device):
+        li = tpch.lineitem(sf, seed=1000 + r, device=device, need=("keys", "double"), shuffle=(r % 2 == 1))
+        off = r * tpch.order_key(torch.tensor(n_orders, dtype=torch.int64)).item()
+        li["orderkey"] = li["orderkey"] + off
+        od = tpch.orders(sf, seed=1000 + r, device=device)
+        od["orderkey"] = od["orderkey"] + off
+        return li, od
+
+    li, od = shard(rank, "cuda")
+    n = li["rows"]
+    page = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, li["quantity"], None, None, n),
+                  Block(N.DOUBLE, li["extendedprice_double"].view(torch.int64), None, None, n), position_count=n)
+    exchange = P.HashPartitionExchange(P.DevicePartitioner(ctx)) if world > 1 else None
+    if exchange is not None:
+        # peer-memory exchange against the NCCL all-to-all on the same page, twice (the second call reuses the symmetric buffers)
+        other = P.HashPartitionExchange(P.DevicePartitioner(ctx), peer=False)
+        same = True
+        for rep in range(2):
+            a = exchange.exchange(page, [0], slot="xchk", lease=True)
+            b = other.exchange(page, [0])
+            same = same and a.position_count == b.position_count
+            for x, y in zip(a.blocks, b.blocks):
+                same = same and bool(torch.equal(x.values.view(torch.uint8), y.values.view(torch.uint8)))
+        t = torch.tensor([1 if same else 0], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        out["peer_exchange_equals_nccl_all_to_all"] = bool(int(t.item()) == 1) if exchange.peer is not None else "peer mode unavailable: " + exchange.peer_why
+        if out["peer_exchange_equals_nccl_all_to_all"] is False:
+            raise SystemExit("bench cross-check failed: the peer-memory exchange and the NCCL all-to-all deliver different rows")
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2)]
+    plan = P.PartitionedAggregation([P.BIGINT], [0], aggs, ctx, dist, expected_groups=n_orders, exchange=exchange)
+    g, res = plan.run(page, slot="xchk")
+    mine = [b.values.cpu().numpy() for b in res.blocks]
+    join = P.PartitionedHashJoin([P.BIGINT, P.DOUBLE], [0], ctx, dist, exchange=exchange)
     bpage = P.Page(Block(N.BIGINT, od["orderkey"], None, None, n_orders), Block(N.DOUBLE, od["totalprice"].view(torch.int64), None, None, n_orders),
                    position_count=n_orders)
-
-    def build():
-        local = ex.exchange(bpage, [0]) if ex else bpage
-        idx = P.PagesIndex([P.BIGINT, P.DOUBLE], [0], ctx=ctx)
-        idx.add_page(local)
-        return idx.create_lookup_source()
-
-    bms, ls = timed(build, 2, 1)
-    bkern = ctx.kernel_report(reset=True)
-    ppage = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, li["quantity"], None, None, n), position_count=n)
-
-    def probe():
-        local = ex.exchange(ppage, [0]) if ex else ppage
-        m = local.position_count
-        pp, bp = ls.join_page([local.blocks[0]], None, P.JOIN_INNER, device=True, capacity=max(m, 1))
-        out = ls.append_to(bp, [1], device=True)
-        return len(pp)
-
-    pms, matches = timed(probe, 3, 1)
-    pkern = ctx.kernel_report(reset=True)
-    ctx.set_timing(False)
-    o_all, m_all = total(n_orders), total(matches)
-    # every probe row matches exactly one build row; on one GPU the gathered payload must equal a torch gather
-    join_check = {"matches_equal_probe_rows": m_all == n_all}
-    if world == 1:
-        pp, bp = ls.join_page([ppage.blocks[0]], None, P.JOIN_INNER, device=True, capacity=max(n, 1))
-        got = ls.append_to(bp, [1], device=True)[0].values
-        want = od["totalprice"].view(torch.int64)[torch.searchsorted(od["orderkey"], li["orderkey"])]
-        join_check["probe_positions_ascending"] = bool(torch.equal(pp, torch.arange(n, device="cuda", dtype=torch.int32)))
-        join_check["gathered_payload_bit_exact"] = bool(torch.equal(got.view(torch.int64), want))
-        del pp, bp, got, want
-    if not all(join_check.values()):
-        raise SystemExit("bench self-check failed (join): %s" % json.dumps(join_check))
-    res["join_build"] = {"workload": "hash build orders SF%g per GPU (orderkey, totalprice)" % sf, "rows": o_all, "ms_per_step": round(bms, 3),
-                         "rows_per_s": o_all / (bms / 1e3), "algorithmic_bytes_per_row": 32,
-                         "hbm_frac_per_gpu": round(o_all / world * 32 / (bms / 1e3) / 1e9 / peak, 4),
-                         "kernels_ms_per_step": {k: round(v[0] / 2, 3) for k, v in sorted(bkern.items(), key=lambda kv: -kv[1][0])[:6]}}
-    res["join_probe"] = {"workload": "INNER join probe lineitem.orderkey -> orders SF%g per GPU, emit (probe idx, build pos) + gather totalprice" % sf,
-                         "rows": n_all, "matches": m_all, "ms_per_step": round(pms, 3), "rows_per_s": n_all / (pms / 1e3),
-                         "algorithmic_bytes_per_row": 44, "hbm_frac_per_gpu": round(n_all / world * 44 / (pms / 1e3) / 1e9 / peak, 4),
-                         "kernels_ms_per_step": {k: round(v[0] / 3, 3) for k, v in sorted(pkern.items(), key=lambda kv: -kv[1][0])[:6]},
-                         "selfcheck": join_check}
-    if ex:
-        res["exchange"] = {"rows_sent_per_rank": ex.sent_rows, "bytes_sent_per_rank": ex.bytes_sent, "collective": ("fused partition + peer-memory stores over NVLink (pg_partition_scatter_peers into symmetric receive buffers)" if ex.peer is not None
-                                          else "NCCL all_to_all_single per column (%s)" % ex.peer_why)}
-    return res
+    join.build(bpage, slot="xchk_b")
+    ppage = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), position_count=n)
+    local, pp, got = join.probe(ppage, [0], [1], slot="xchk_p")
+    jmine = (local.blocks[0].values[pp.long()].cpu().numpy(), got[0].values.view(torch.int64).cpu().numpy())
+    if dist is not None:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (mine, jmine))
+    else:
+        gathered = [(mine, jmine)]
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_lib as O
+        shards = [shard(r, "cpu") for r in range(world)]
+        keys = np.concatenate([s[0]["orderkey"].numpy() for s in shards])
+        qty = np.concatenate([s[0]["quantity"].numpy() for s in shards])
+        price = np.concatenate([s[0]["extendedprice_double"].numpy() for s in shards])
+        ogb = O.OracleGroupBy([P.BIGINT], n_orders)
+        ids = ogb.get_group_ids([P.Block.long_array(keys)])
+        G = ogb.group_count()
+        okeys = ogb.export(with_hash=False)[0][0].values
+        want = [okeys]
+        for a, col in zip(aggs, (None, P.Block.long_array(qty, None, P.SHORT_DECIMAL), P.Block.double_array(price))):
+            acc = O.OracleAccumulator(a.kind, a.in_type)
+            acc.add_input(ids, G, col)
+            want.append(np.asarray(acc.evaluate(0, G, True)[1][0].values))
+        got_cols = [np.concatenate([np.asarray(gr[0][c]) for gr in gathered]) for c in range(4)]
+        og, ow = np.argsort(got_cols[0], kind="stable"), np.argsort(want[0], kind="stable")
+        ok = len(got_cols[0]) == G and np.array_equal(got_cols[0][og], want[0][ow]) and np.array_equal(got_cols[1][og], want[1][ow])
+        u64 = lambda a: np.ascontiguousarray(a).view(np.uint64)      # noqa: E731
+        ok = ok and np.array_equal(u64(got_cols[2]).reshape(-1, 2)[og], u64(want[2]).reshape(-1, 2)[ow])
+        gd, wd = u64(got_cols[3]).view(np.float64)[og], u64(want[3]).view(np.float64)[ow]
+        ok = ok and bool((np.abs(gd - wd) <= 1e-12 * np.abs(wd)).all())
+        out["groupby_orderkey_equals_oracle"] = bool(ok)
+        oj = O.OracleJoin([P.BIGINT, P.DOUBLE], [0])
+        for s in shards:
+            oj.add_page([P.Block.long_array(s[1]["orderkey"].numpy()), P.Block.double_array(s[1]["totalprice"].numpy())])
+        oj.build()
+        wp, wb = oj.probe([P.Block.long_array(keys)])
+        tp = np.concatenate([s[1]["totalprice"].numpy() for s in shards]).view(np.int64)
+        want_pairs = np.stack([keys[wp], tp[wb]], axis=1)
+        got_pairs = np.stack([np.concatenate([gr[1][0] for gr in gathered]), np.concatenate([gr[1][1] for gr in gathered])], axis=1)
+        srt = lambda a: a[np.lexsort((a[:, 1], a[:, 0]))]      # noqa: E731
+        out["join_equals_oracle"] = bool(want_pairs.shape == got_pairs.shape and np.array_equal(srt(want_pairs), srt(got_pairs)))
+        out["rows"] = int(len(keys))
+        out["what"] = "SF%g per GPU through the same plans vs oracle/ on one host core (group sets, counts, decimal sums, join match sets bit-exact; double sums 1e-12)" % sf
+        if not (out["groupby_orderkey_equals_oracle"] and out["join_equals_oracle"]):
+            raise SystemExit("bench cross-check against the oracle failed: %s" % json.dumps(out))
+    return out
 
 
 def q1_selfcheck(torch, cols, out, dist):
@@ -591,7 +495,6 @@ def q1_selfcheck(torch, cols, out, dist):
             "sums_bit_exact_vs_torch_int64": bool(ok and live == out.position_count and count_sum == int(passing.item()))}
 
 
-
 def gpu_arm(args):
     import numpy as np
     import torch
@@ -608,65 +511,6 @@ def gpu_arm(args):
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
     ctx = P.GpuContext(local_rank)
-    aggs = tpch.q1_aggregators()
-    fin_aggs = final_aggs_for(P, aggs, 2)
-
-    cols = tpch.lineitem(args.sf, seed=42 + rank, device="cuda")
-    page = tpch.q1_page(cols)
-    rows = page.position_count
-    input_bytes = rows * tpch.Q1_BYTES_PER_ROW    # > 126 MB L2: every step streams its inputs from HBM
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    pipe = MergePipeline(P, dist, torch, fin_aggs, local_rank, world) if world > 1 else None
-    if pipe:
-        ctx.reserve_sms(int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "8")))   # room for the FINAL stage's small kernels
-
-    def step_device():
-        if world == 1:
-            return run_single_pass(P, page, aggs, P.SINGLE, ctx)
-        partial_packed(P, page, aggs, ctx, pipe)     # FINAL of this step overlaps the next PARTIAL
-        return None
-
-    def launches_now():
-        return ctx.launch_count() + (pipe.launch_count() if pipe else 0)
-
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
-        if pipe:
-            pipe.drain()
-        barrier()
-        ctx.kernel_report(reset=True)
-        launches0 = launches_now()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        out = None
-        for _ in range(steps):
-            out = fn()
-        if pipe:
-            out = pipe.drain()          # the last step's FINAL result must exist before the clock stops
-        e1.record()
-        barrier()
-        ms = e0.elapsed_time(e1)
-        if dist is not None:
-            t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, out, launches_now() - launches0
-
-    ctx.set_timing(True)
-    with ClockSampler(local_rank) as clk:
-        ms, out, launches = timed(step_device, args.steps, args.warmup)
-    kernels = ctx.kernel_report(reset=True)
-    ctx.set_timing(False)
-    total_rows = rows * world
-    value = total_rows * args.steps / (ms / 1e3)
-
-    # dominant kernel + roofline (per-launch CUDA-event durations recorded inside the library on its launch stream)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -674,6 +518,32 @@ def gpu_arm(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+    traffic = {}
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except Exception:
+        pass
+    env = Env(P, tpch, torch, dist, ctx, world, rank, peak)
+    aggs = tpch.q1_aggregators()
+
+    cols = tpch.lineitem(args.sf, seed=42 + rank, device="cuda")
+    page = tpch.q1_page(cols)
+    rows = page.position_count
+    input_bytes = rows * tpch.Q1_BYTES_PER_ROW    # > 126 MB L2: every step streams its inputs from HBM
+
+    plan = P.PartialFinalAggregation([P.VARCHAR, P.VARCHAR], [0, 1], aggs, ctx, dist, expected_groups=100_000,
+                                     reserve_sms=int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "8")))
+
+    ctx.set_timing(True)
+    with ClockSampler(local_rank) as clk:
+        l2 = plan.launch_count()
+        ms, out, kernels, launches = env.timed(lambda: plan.submit(page), args.steps, args.warmup, drain=plan.drain)
+        launches += plan.launch_count() - l2
+    ctx.set_timing(False)
+    total_rows = rows * world
+    value = total_rows / (ms / 1e3)
+
+    # dominant kernel + roofline (per-launch CUDA-event durations recorded inside the library on its launch stream)
     kern_ms = {k: v[0] for k, v in kernels.items()}
     top = max(kern_ms, key=kern_ms.get) if kern_ms else None
     roofline = None
@@ -682,19 +552,13 @@ def gpu_arm(args):
         per_launch_ms = tms / max(cnt, 1)
         achieved = input_bytes / (per_launch_ms / 1e3) / 1e9
         roofline = {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                    "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                    "frac": round(achieved / peak, 4), "traffic": traffic.get(top), "peak_source": peak_src,
                     "algorithmic_bytes_per_row": tpch.Q1_BYTES_PER_ROW, "rows_per_launch": rows,
                     "launch_ms": round(per_launch_ms, 4), "launches_timed": cnt,
-                    "kernel_share_of_step": round(tms / ms, 4),
-                    "kernels_ms_per_step": {k: round(v[0] / args.steps, 4) for k, v in sorted(kernels.items(), key=lambda kv: -kv[1][0])}}
-        prof = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(prof):
-            try:
-                roofline["traffic"] = json.load(open(prof)).get(top)      # bytes per launch, from the committed ncu capture
-                roofline["traffic_unit"] = "bytes/launch (ncu dram read+write)"
-                roofline["algorithmic_bytes_per_launch"] = int(input_bytes)
-            except Exception:
-                pass
+                    "kernel_share_of_step": round(tms / args.steps / ms, 4),
+                    "step_frac": round(input_bytes / (ms / 1e3) / 1e9 / peak, 4),
+                    "kernels_ms_per_step": {k: round(v[0] / args.steps, 4) for k, v in sorted(kernels.items(), key=lambda kv: -kv[1][0])},
+                    "traffic_unit": "bytes/launch (ncu dram read+write)", "algorithmic_bytes_per_launch": int(input_bytes)}
 
     selfcheck = q1_selfcheck(torch, cols, out, dist)
     if not selfcheck["sums_bit_exact_vs_torch_int64"]:
@@ -704,85 +568,73 @@ def gpu_arm(args):
     e2e = None
     if not args.no_e2e:
         hpage = tpch.page_to_host(page, pinned=True)
-
-        def step_host():
-            if world == 1:
-                return run_single_pass(P, hpage, aggs, P.SINGLE, ctx)
-            partial_packed(P, hpage, aggs, ctx, pipe)
-            return None
-
         e_steps = max(2, min(args.steps, 5))
-        ems, eout, _ = timed(step_host, e_steps, 2)
+        ems, eout, _, _ = env.timed(lambda: plan.submit(hpage), e_steps, 3, drain=plan.drain)
         out_bytes = sum(int(np.asarray(b.to_host().values).nbytes) for b in eout.blocks)
-        e2e = {"value": total_rows * e_steps / (ems / 1e3), "unit": "rows/s", "h2d_bytes_per_step": int(input_bytes),
-               "d2h_bytes_per_step": int(out_bytes), "ms_per_step": round(ems / e_steps, 3), "steps": e_steps}
+        e2e = {"value": total_rows / (ems / 1e3), "unit": "rows/s", "h2d_bytes_per_step": int(input_bytes),
+               "d2h_bytes_per_step": int(out_bytes), "ms_per_step": round(ems, 3), "steps": e_steps, "warmup": 3}
         del hpage
+    plan.close()
 
-    # parity spot check of this very run against the oracle on a bounded prefix (the full check lives in tests/)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        n_s, times = time_cpu_port(P, tpch, args.cpu_sample_rows, 1, 3, 1)
+        n_s, times = time_cpu_port(P, tpch, args.cpu_sample_rows / ROWS_PER_SF, 1, 3, 1)
         cpu = {"value": n_s / min(times), "unit": "rows/s", "cores": 1, "kind": "port",
                "sample": "oracle/ C++ restatement of GroupByHash+accumulators (the reference is Java; no JDK on this box), 1 thread, "
                          "%d-row TPC-H-shaped lineitem sample of the same Q1 plan, best of 3" % n_s}
 
-    extra = None
-    if args.extra:
-        del page, cols
-        torch.cuda.empty_cache()
-        extra = extra_workloads(args, P, tpch, ctx, torch, peak, dist, world, rank)
+    del page, cols
+    torch.cuda.empty_cache()
+    workloads, xchk = None, None
+    if not args.no_workloads:
+        xchk = crosschecks(env)
+        workloads = wide_workloads(args, env, traffic)
 
     if rank == 0:
         line = {
-            "metric": "input rows/sec for GROUP BY & hash-join probe at 1/2/4/8 B200; % HBM roofline",
+            "metric": METRIC,
             "value": value, "unit": "rows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int128/int64 (decimal sums), u8 keys", "data": "synthetic (TPC-H-shaped generator, seeded)",
-            "config": {"workload": "TPC-H Q1 on lineitem SF%g per GPU: GROUP BY returnflag,linestatus; 4x sum, 3x avg (decimal), count(*); "
-                                   "shipdate filter as mask" % args.sf,
-                       "rows_per_gpu": rows, "groups": int(out.position_count), "step": "SINGLE" if world == 1 else "PARTIAL -> NCCL all_gather -> FINAL; the FINAL stage of step i overlaps the PARTIAL stage of step i+1 (second stream)",
-                       "l2_policy": "inputs (%.2f GB per pass) exceed the 126 MB L2; no flush needed" % (input_bytes / 1e9)},
+            "config": q1_config(args.sf, rows),
+            "plan": "SINGLE" if world == 1 else "PARTIAL -> NCCL all_gather -> FINAL; the FINAL stage of step i overlaps the PARTIAL stage of step i+1",
             "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
             "selfcheck": selfcheck,
         }
         if cpu:
             line["cpu_baseline"] = cpu
-        if extra:
-            line["extra"] = extra
+        if workloads:
+            line["workloads"] = workloads
+            line["crosscheck"] = xchk
         print(json.dumps(line), flush=True)
-    if pipe:
-        pipe.close()
-        if rank == 0 and "trace" in _MERGE_BUFS:
-            tr = _MERGE_BUFS["trace"]
-            print("merge stage ms per call: pack %.3f gather %.3f unpack %.3f final %.3f (calls %d)"
-                  % tuple([1e3 * x / max(tr[4], 1) for x in tr[:4]] + [int(tr[4])]), file=sys.stderr)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
 
 
 def reference_arm(args):
-    """CPU arm: the oracle port on all host threads (rank 0 only)."""
+    """CPU arm: the oracle port on all host threads (rank 0 only), over the same Q1 input one GPU gets (SF `--sf`, seed 42)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import presto_b200 as P
     from presto_b200 import tpch
     cores = os.cpu_count() or 1
-    n_s, times = time_cpu_port(P, tpch, args.cpu_sample_rows, cores, args.steps, args.warmup)
+    # the same generator (counter-based, device-independent) gives this arm the very rows rank 0's GPU aggregates
+    warmup = args.warmup
+    n_s, times = time_cpu_port(P, tpch, args.sf, cores, args.steps, warmup)
     total = sum(times)
     value = n_s * len(times) / total
     line = {
         "impl": "reference",
-        "metric": "input rows/sec for GROUP BY & hash-join probe at 1/2/4/8 B200; % HBM roofline",
+        "metric": METRIC,
         "value": value, "unit": "rows/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total / len(times) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int128/int64 (decimal sums), u8 keys", "data": "synthetic (TPC-H-shaped generator, seeded)",
-        "config": {"workload": "TPC-H Q1 on lineitem SF%g per GPU: GROUP BY returnflag,linestatus; 4x sum, 3x avg (decimal), count(*); "
-                               "shipdate filter as mask" % args.sf, "rows_per_step": n_s},
+        "config": q1_config(args.sf, n_s),
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port",
-                         "sample": "oracle/ C++ restatement (reference is Java, no JDK here): %d drivers run PARTIAL over slices of a "
-                                   "%d-row sample, one FINAL merge" % (cores, n_s)},
+                         "sample": "oracle/ C++ restatement (reference is Java, no JDK here): %d drivers run PARTIAL over slices of the same "
+                                   "%d-row SF%g input one GPU gets, one FINAL merge; %d timed passes after %d warm-up" % (cores, n_s, args.sf, len(times), warmup)},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)

@@ -25,6 +25,7 @@ class GpuContext:
         return self._h
 
     def set_stream(self, cuda_stream):
+        self.stream = int(cuda_stream)
         N.check(self._h, N.lib().pg_ctx_set_stream(self._h, C.c_void_p(cuda_stream)))
 
     def reserve_sms(self, sms):

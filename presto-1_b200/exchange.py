@@ -124,13 +124,19 @@ class HashPartitionExchange:
             elif ok:
                 self.peer_why = "another rank could not set up symmetric memory"
 
-    def _exchange_peer(self, page, key_channels, hash_channel):
-        """Fused partition + transfer: rows are stored directly into the destination ranks' symmetric receive buffers."""
+    def _exchange_peer(self, page, key_channels, hash_channel, slot, lease):
+        """Fused partition + transfer: rows are stored directly into the destination ranks' symmetric receive buffers.
+        The receive buffers belong to `slot`: a page returned with lease=True is a view into them and stays valid until the next
+        exchange with the same slot (on any rank); with lease=False the rows are copied out before returning."""
         import torch
         dist, W, me = self.dist, self.world, self.rank
         blocks = page.blocks
         n = page.position_count
         ctx = self.partitioner.ctx
+        # the two barriers below are issued on torch's current stream and the stores on the context's stream: they must be the same
+        cur = torch.cuda.current_stream().cuda_stream
+        if getattr(ctx, "stream", cur) != cur:
+            raise N.PrestoGpuError(N.PG_E_ILLEGAL_STATE, "peer exchange: the partitioner's context is bound to another stream than torch's current one")
         keys = [blocks[c] for c in key_channels]
         hc = blocks[hash_channel].pg_col() if hash_channel is not None else None
         counts = (C.c_int64 * W)()
@@ -150,6 +156,7 @@ class HashPartitionExchange:
             n_out = int(recv_total[me])
             offs = (C.c_int64 * W)(*[int(cm[:me, r].sum()) for r in range(W)])   # where my rows start in rank r's buffer
             out_blocks = []
+            pending_views = []
             first = True
             for ci, (b, nullable) in enumerate(zip(blocks, nulls_any)):
                 if b.type in (N.VARCHAR, N.VARBINARY):
@@ -157,8 +164,8 @@ class HashPartitionExchange:
                 dt = _torch_dtype(b.type)
                 k = 2 if b.type == N.LONG_DECIMAL else 1
                 esz = torch.empty(0, dtype=dt).element_size() * k
-                vbuf, vh = self.peer.get((ci, "v"), max(cap_rows, 1) * esz)
-                nbuf, nh = (self.peer.get((ci, "n"), max(cap_rows, 1)) if nullable else (None, None))
+                vbuf, vh = self.peer.get((slot, ci, "v"), max(cap_rows, 1) * esz)
+                nbuf, nh = (self.peer.get((slot, ci, "n"), max(cap_rows, 1)) if nullable else (None, None))
                 if first:
                     vh.barrier()          # stream-ordered: every rank's earlier readers of its receive buffers are done
                     first = False
@@ -171,10 +178,15 @@ class HashPartitionExchange:
                 N.check(ctx.handle, N.lib().pg_partition_scatter_peers(h, C.byref(col), pv, pn, offs))
                 vals = vbuf[: n_out * esz].view(dt)
                 nulls = nbuf[:n_out] if nullable else None
+                pending_views.append(len(out_blocks))
                 out_blocks.append(Block(b.type, vals, nulls, None, n_out, b.precision, b.scale))
                 self.bytes_sent += (n - int(counts[me])) * esz
             if not first:
                 vh.barrier()              # every rank's stores have landed before anyone reads its buffer
+            if not lease:                 # the caller may hold this page across later exchanges: give it its own memory
+                for i in pending_views:
+                    ob = out_blocks[i]
+                    out_blocks[i] = Block(ob.type, ob.values.clone(), None if ob.nulls is None else ob.nulls.clone(), None, ob.n, ob.precision, ob.scale)
         finally:
             N.lib().pg_partition_destroy(h)
         self.sent_rows += n - int(counts[me])
@@ -190,10 +202,12 @@ class HashPartitionExchange:
             a = a.view(np.int64)
         return torch.from_numpy(a).to(self.device)
 
-    def exchange(self, page, key_channels, hash_channel=None):
+    def exchange(self, page, key_channels, hash_channel=None, slot="default", lease=False):
+        """The rows of every rank whose key hashes to this rank (source-rank major, page order inside a source).
+        slot / lease only matter in peer mode: see _exchange_peer.  The NCCL path always returns fresh tensors."""
         import torch
         if self.peer is not None:
-            return self._exchange_peer(page, key_channels, hash_channel)
+            return self._exchange_peer(page, key_channels, hash_channel, slot, lease)
         dist, W = self.dist, self.world
         part_page, counts = self.partitioner.partition(page, key_channels, W, hash_channel)
         send = torch.tensor(counts, dtype=torch.int64, device=self.device)

@@ -24,63 +24,98 @@ def order_key(i):
     return (i // 8) * 32 + (i % 8) + 1
 
 
-def _gen(seed, device):
-    g = torch.Generator(device=device)
-    g.manual_seed(seed)
-    return g
+_M64 = (1 << 64) - 1
+
+
+def _i64(x):
+    """Python int -> the int64 with the same low 64 bits."""
+    x &= _M64
+    return x - (1 << 64) if x >= (1 << 63) else x
+
+
+_GOLD, _MIX1, _MIX2 = _i64(0x9E3779B97F4A7C15), _i64(0xBF58476D1CE4E5B9), _i64(0x94D049BB133111EB)
+
+
+def _mix(seed, stream, idx):
+    """Counter-based generator: splitmix64 finaliser of (seed, stream, row index), written with wrapping int64 tensor ops so that
+    the CPU and the CUDA build of torch produce the SAME values (torch.Generator streams differ between devices).  Both bench
+    arms — the GPU operators and the CPU reference arm — therefore aggregate identical rows."""
+    z = idx * _GOLD + _i64(seed * 0xD1342543DE82EF95 + stream * 0x2545F4914F6CDD1D + 0x1234567)
+    z = (z ^ ((z >> 30) & ((1 << 34) - 1))) * _MIX1
+    z = (z ^ ((z >> 27) & ((1 << 37) - 1))) * _MIX2
+    return z ^ ((z >> 31) & ((1 << 33) - 1))
+
+
+def _randint(seed, stream, idx, lo, hi):
+    """Uniform integers in [lo, hi) (int64), one per entry of idx."""
+    return lo + ((_mix(seed, stream, idx) >> 11) & ((1 << 53) - 1)) % (hi - lo)
 
 
 def orders(sf, seed=42, device="cuda", rows=None):
     """orders: o_orderkey (unique, sparse), o_custkey, o_totalprice (double), o_orderdate, o_shippriority, o_orderstatus."""
     n = int(1_500_000 * sf) if rows is None else int(rows)
-    g = _gen(seed, device)
     idx = torch.arange(n, device=device, dtype=torch.int64)
     okey = order_key(idx)
-    custkey = torch.randint(1, max(2, int(150_000 * sf)) + 1, (n,), generator=g, device=device, dtype=torch.int64)
-    totalprice = (torch.randint(85_771, 55_528_517, (n,), generator=g, device=device, dtype=torch.int64).double() / 100.0)
-    orderdate = torch.randint(STARTDATE, ENDDATE_ORDER + 1, (n,), generator=g, device=device, dtype=torch.int32)
+    custkey = _randint(seed, 1, idx, 1, max(2, int(150_000 * sf)) + 1)
+    totalprice = _randint(seed, 2, idx, 85_771, 55_528_517).double() * 0.01   # a product, not a quotient: torch CUDA turns x / c into x * (1 / c), the CPU build does not
+    orderdate = _randint(seed, 3, idx, STARTDATE, ENDDATE_ORDER + 1).to(torch.int32)
     shipprio = torch.zeros(n, device=device, dtype=torch.int32)
     return {"orderkey": okey, "custkey": custkey, "totalprice": totalprice, "orderdate": orderdate, "shippriority": shipprio}
 
 
+def shuffle_order(n, seed, device):
+    """A seeded permutation of range(n), identical on CPU and CUDA (stable argsort of hashed row numbers)."""
+    return torch.argsort(_mix(seed, 99, torch.arange(n, device=device, dtype=torch.int64)), stable=True)
+
+
 def lineitem(sf, seed=42, device="cuda", orders_count=None, need=("q1",), shuffle=False):
-    """lineitem columns.  need: subset of {"q1", "keys", "join"} selecting which columns are materialised."""
+    """lineitem columns.  need: subset of {"q1", "keys", "double", "raw"} selecting which columns are materialised.
+    "q1" adds the derived long-decimal columns and the filter mask (the materialised Q1 page); "raw" only the raw columns
+    (shipdate, discount, tax, returnflag, linestatus) a fused filter + projection reads."""
     n_orders = int(1_500_000 * sf) if orders_count is None else int(orders_count)
-    g = _gen(seed + 1, device)
-    counts = torch.randint(1, 8, (n_orders,), generator=g, device=device, dtype=torch.int64)
-    order_idx = torch.repeat_interleave(torch.arange(n_orders, device=device, dtype=torch.int64), counts)
+    oidx = torch.arange(n_orders, device=device, dtype=torch.int64)
+    counts = _randint(seed + 1, 1, oidx, 1, 8)
+    order_idx = torch.repeat_interleave(oidx, counts)
+    del counts
     n = int(order_idx.numel())
     out = {"rows": n}
+    idx = torch.arange(n, device=device, dtype=torch.int64)     # the row's identity: survives the shuffle
     if shuffle:
-        order_idx = order_idx[torch.randperm(n, generator=g, device=device)]
+        perm = shuffle_order(n, seed + 1, device)
+        order_idx, idx = order_idx[perm], idx[perm]
+        del perm
     if "keys" in need or "join" in need:
         out["orderkey"] = order_key(order_idx)
-    qty = torch.randint(1, 51, (n,), generator=g, device=device, dtype=torch.int64)
-    partkey = torch.randint(1, max(2, int(200_000 * sf)) + 1, (n,), generator=g, device=device, dtype=torch.int64)
+    s = seed + 1
+    qty = _randint(s, 2, idx, 1, 51)
+    partkey = _randint(s, 3, idx, 1, max(2, int(200_000 * sf)) + 1)
     retail = 90_000 + (torch.div(partkey, 10, rounding_mode="floor") % 20_001) + 100 * (partkey % 1000)
     out["quantity"] = qty * 100                                  # decimal(12,2)
     out["extendedprice"] = qty * retail                          # decimal(12,2) cents
-    del partkey, retail
-    if "q1" in need:
-        discount = torch.randint(0, 11, (n,), generator=g, device=device, dtype=torch.int64)
-        tax = torch.randint(0, 9, (n,), generator=g, device=device, dtype=torch.int64)
-        orderdate = torch.randint(STARTDATE, ENDDATE_ORDER + 1, (n_orders,), generator=g, device=device, dtype=torch.int32)[order_idx]
-        shipdate = orderdate + torch.randint(1, 122, (n,), generator=g, device=device, dtype=torch.int32)
-        receiptdate = shipdate + torch.randint(1, 31, (n,), generator=g, device=device, dtype=torch.int32)
-        ra = torch.where(torch.rand(n, generator=g, device=device) < 0.5, ord("R"), ord("A")).to(torch.uint8)
+    del partkey, retail, qty
+    if "q1" in need or "raw" in need:
+        discount = _randint(s, 4, idx, 0, 11)
+        tax = _randint(s, 5, idx, 0, 9)
+        orderdate = _randint(s, 6, oidx, STARTDATE, ENDDATE_ORDER + 1)[order_idx]
+        shipdate = (orderdate + _randint(s, 7, idx, 1, 122)).to(torch.int32)
+        receiptdate = shipdate + _randint(s, 8, idx, 1, 31).to(torch.int32)
+        del orderdate
+        ra = torch.where((_mix(s, 9, idx) & 1) == 0, ord("R"), ord("A")).to(torch.uint8)
         out["returnflag"] = torch.where(receiptdate <= CURRENTDATE, ra, torch.full_like(ra, ord("N")))
         out["linestatus"] = torch.where(shipdate > CURRENTDATE, ord("O"), ord("F")).to(torch.uint8)
+        del ra, receiptdate
         out["shipdate"] = shipdate
         out["discount"] = discount
         out["tax"] = tax
-        disc_price = out["extendedprice"] * (100 - discount)     # decimal(24,4)
-        charge = disc_price * (100 + tax)                        # decimal(36,6); < 2^63 for TPC-H domains
-        out["disc_price"] = torch.stack([disc_price, torch.zeros_like(disc_price)], dim=1).reshape(-1)
-        out["charge"] = torch.stack([charge, torch.zeros_like(charge)], dim=1).reshape(-1)
-        out["q1_mask"] = (shipdate <= Q1_CUTOFF).to(torch.uint8)
         out["offsets1"] = torch.arange(n + 1, device=device, dtype=torch.int32)   # varchar(1): one byte per row
+        if "q1" in need:
+            disc_price = out["extendedprice"] * (100 - discount)     # decimal(24,4)
+            charge = disc_price * (100 + tax)                        # decimal(36,6); < 2^63 for TPC-H domains
+            out["disc_price"] = torch.stack([disc_price, torch.zeros_like(disc_price)], dim=1).reshape(-1)
+            out["charge"] = torch.stack([charge, torch.zeros_like(charge)], dim=1).reshape(-1)
+            out["q1_mask"] = (shipdate <= Q1_CUTOFF).to(torch.uint8)
     if "double" in need:
-        out["extendedprice_double"] = out["extendedprice"].double() / 100.0
+        out["extendedprice_double"] = out["extendedprice"].double() * 0.01
     return out
 
 

@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """bench.py — input rows/s of the hash-aggregation / hash-join hot path (BASELINE.json metric) on N B200s of one node.
 
-Headline (`value`, `e2e`, `roofline`): BASELINE.json configs[1], TPC-H Q1 over lineitem SF10 per GPU (weak scaling): GROUP BY
-returnflag, linestatus (2 x varchar(1), 4 groups), sum/avg over short and long decimals and count(*), shipdate filter.
+Headline (`value`, `e2e`, `roofline`): BASELINE.json configs[1], TPC-H Q1 over lineitem SF10 per GPU (weak scaling), from the raw
+scan columns: filter shipdate <= DATE '1998-09-02', project extendedprice*(1-discount) and ...*(1+tax) as exact long decimals,
+GROUP BY returnflag, linestatus (2 x varchar(1), 4 groups), sum/avg over short and long decimals and count(*).  The filter and
+the projections are fused into the aggregation kernel (pg_hashagg_set_input_processor): derived columns never exist in memory.
   value : whole-job input rows/s with the columns already resident in HBM (one HashAggregationOperator pass per step)
   e2e   : the same pass through the C ABI with HOST (pinned) column buffers, host->device copies inside the timed region
   N > 1 : every rank aggregates its own SF10 shard (PARTIAL), the 4-row intermediate pages are all-gathered over NCCL and merged by a
@@ -107,16 +109,26 @@ class ClockSampler:
 
 def q1_config(sf, rows):
     """`config` of the headline, identical in both arms."""
-    return {"workload": "TPC-H Q1 on lineitem SF%g per GPU: GROUP BY returnflag,linestatus; 4x sum, 3x avg (decimal), count(*); "
-                        "shipdate filter as mask" % sf,
+    return {"workload": "TPC-H Q1 on lineitem SF%g per GPU, from the raw columns (returnflag, linestatus, quantity, extendedprice, discount, tax, "
+                        "shipdate): filter shipdate <= 1998-09-02; project extendedprice*(1-discount), extendedprice*(1-discount)*(1+tax) as exact "
+                        "decimals; GROUP BY returnflag,linestatus; 4x sum, 3x avg (decimal), count(*)" % sf,
             "rows_per_gpu": int(rows), "groups": 4,
-            "l2_policy": "inputs (%.2f GB per pass) exceed the 126 MB L2; no flush needed" % (rows * 67 / 1e9)}
+            "l2_policy": "inputs (%.2f GB per pass) exceed the 126 MB L2; no flush needed" % (rows * 46 / 1e9)}
+
+
+def result_digest(out):
+    """sha256 over the output rows sorted by key: printed by both arms, equal when they computed the same answer."""
+    import hashlib
+    hb = [b.to_host() for b in out.blocks]
+    rows = sorted(tuple(str(b.get(i)) for b in hb) for i in range(out.position_count))
+    return hashlib.sha256(json.dumps(rows).encode()).hexdigest()[:16]
 
 
 # ------------------------------------------------------------------------------------------- CPU arm (oracle port)
-def oracle_q1_pass(O, P, blocks, aggs, nthreads):
-    """The reference's plan on host cores: `nthreads` drivers each run getGroupIds + accumulators (PARTIAL) over a slice of
-    the pages, then one FINAL merge — restated in oracle/ (C++), called through ctypes (GIL released)."""
+def oracle_q1_pass(O, P, blocks, aggs, nthreads, exprs=None):
+    """The reference's plan on host cores: `nthreads` drivers each run ScanFilterAndProject (filter + projections), then getGroupIds
+    + accumulators (PARTIAL) over a slice of the pages, then one FINAL merge — restated in oracle/ (C++), called through ctypes
+    (GIL released)."""
     n = blocks[0].n
     bounds = [n * i // nthreads for i in range(nthreads + 1)]
     results = [None] * nthreads
@@ -131,6 +143,10 @@ def oracle_q1_pass(O, P, blocks, aggs, nthreads):
     def work(t):
         lo, hi = bounds[t], bounds[t + 1]
         sl = [slice_block(b, lo, hi) for b in blocks]
+        if exprs is not None:
+            rc, projected = O.OraclePageProcessor(exprs[0], exprs[1]).process(sl)
+            assert rc == 0
+            sl = projected.blocks
         gb = O.OracleGroupBy([P.VARCHAR, P.VARCHAR], 100_000)
         ids = gb.get_group_ids(sl[:2])
         g = gb.group_count()
@@ -158,25 +174,29 @@ def oracle_q1_pass(O, P, blocks, aggs, nthreads):
 
 
 def host_q1_blocks(tpch, sf, seed):
-    cols = tpch.lineitem(sf, seed=seed, device="cpu")
-    page = tpch.q1_page(cols)
+    cols = tpch.lineitem(sf, seed=seed, device="cpu", need=("raw",))
+    page = tpch.q1_raw_page(cols)
     return tpch.page_to_host(page, pinned=False).blocks
 
 
 def time_cpu_port(P, tpch, sf, nthreads, steps, warmup, seed=42):
+    """Returns (rows, per-step seconds, digest of the result)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle_lib as O
     blocks = host_q1_blocks(tpch, sf, seed)
     n = blocks[0].n
-    aggs = tpch.q1_aggregators()
+    aggs = tpch.q1_fused_aggregators()
+    exprs = tpch.q1_expressions()
     times = []
+    res = None
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        oracle_q1_pass(O, P, blocks, aggs, nthreads)
+        res = oracle_q1_pass(O, P, blocks, aggs, nthreads, exprs)
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
-    return n, times
+    keys, outs = res
+    return n, times, result_digest(P.Page(*(list(keys) + list(outs))))
 
 
 # ------------------------------------------------------------------------------------------- GPU arm helpers
@@ -468,30 +488,38 @@ def crosschecks(env):
 
 
 def q1_selfcheck(torch, cols, out, dist):
-    """Size-independent check of the timed run's own result at full size: per-group count(*), sum(quantity),
-    sum(extendedprice) and sum(disc_price) recomputed with torch int64 scatter-adds (independent of both the library and
-    the oracle) and compared bit-exact with the operator's output; counts must also add up to the rows passing the mask."""
-    m = cols["q1_mask"].bool()
+    """Size-independent check of the timed run's own result at full size: per-group count(*), sum(quantity), sum(extendedprice),
+    sum(disc_price) and sum(charge) recomputed with torch int64 arithmetic and scatter-adds over the raw columns (independent of
+    both the library and the oracle; every product and every per-group sum stays below 2^63 for TPC-H value ranges) and compared
+    bit-exact with the operator's output; counts must also add up to the rows passing the filter."""
+    from presto_b200 import tpch
+    m = cols["shipdate"] <= tpch.Q1_CUTOFF
     code = (cols["returnflag"].to(torch.int64) * 256 + cols["linestatus"].to(torch.int64))[m]
-    exp = torch.zeros(4, 65536, dtype=torch.int64, device=code.device)
+    disc_price = cols["extendedprice"] * (100 - cols["discount"])
+    exp = torch.zeros(5, 65536, dtype=torch.int64, device=code.device)
     exp[0].index_add_(0, code, torch.ones_like(code))
     exp[1].index_add_(0, code, cols["quantity"][m])
     exp[2].index_add_(0, code, cols["extendedprice"][m])
-    exp[3].index_add_(0, code, cols["disc_price"][0::2][m])
+    exp[3].index_add_(0, code, disc_price[m])
+    # sum(charge) can pass 2^63 at SF10: accumulate the low 32 bits and the rest separately, recombine in Python
+    charge = (disc_price * (100 + cols["tax"]))[m]
+    lo = torch.zeros(65536, dtype=torch.int64, device=code.device).index_add_(0, code, charge & 0xffffffff)
+    hi = torch.zeros(65536, dtype=torch.int64, device=code.device).index_add_(0, code, charge >> 32)
     passing = torch.tensor([int(m.sum().item())], dtype=torch.int64, device=code.device)
     if dist is not None:
-        dist.all_reduce(exp)
-        dist.all_reduce(passing)
-    exp = exp.cpu().numpy()
+        for t in (exp, lo, hi, passing):
+            dist.all_reduce(t)
+    exp, lo, hi = exp.cpu().numpy(), lo.cpu().numpy(), hi.cpu().numpy()
     hb = [b.to_host() for b in out.blocks]
     ok, count_sum = True, 0
     for i in range(out.position_count):
         c = hb[0].get(i)[0] * 256 + hb[1].get(i)[0]
-        got = (hb[9].get(i), hb[2].get(i), hb[3].get(i), hb[4].get(i))
-        ok = ok and got == tuple(int(exp[k][c]) for k in range(4))
+        got = (hb[9].get(i), hb[2].get(i), hb[3].get(i), hb[4].get(i), hb[5].get(i))
+        want = tuple(int(exp[k][c]) for k in range(4)) + (int(lo[c]) + (int(hi[c]) << 32),)
+        ok = ok and got == want
         count_sum += got[0]
     live = int((exp[0] > 0).sum())
-    return {"groups": int(out.position_count), "groups_expected": live, "count_sum": int(count_sum), "rows_passing_mask": int(passing.item()),
+    return {"groups": int(out.position_count), "groups_expected": live, "count_sum": int(count_sum), "rows_passing_filter": int(passing.item()),
             "sums_bit_exact_vs_torch_int64": bool(ok and live == out.position_count and count_sum == int(passing.item()))}
 
 
@@ -524,15 +552,17 @@ def gpu_arm(args):
     except Exception:
         pass
     env = Env(P, tpch, torch, dist, ctx, world, rank, peak)
-    aggs = tpch.q1_aggregators()
+    aggs = tpch.q1_fused_aggregators()
+    q1_filter, q1_projections = tpch.q1_expressions()
+    processor = P.PageProcessor(q1_filter, q1_projections, ctx=ctx)
 
-    cols = tpch.lineitem(args.sf, seed=42 + rank, device="cuda")
-    page = tpch.q1_page(cols)
+    cols = tpch.lineitem(args.sf, seed=42 + rank, device="cuda", need=("raw",))
+    page = tpch.q1_raw_page(cols)
     rows = page.position_count
-    input_bytes = rows * tpch.Q1_BYTES_PER_ROW    # > 126 MB L2: every step streams its inputs from HBM
+    input_bytes = rows * tpch.Q1_RAW_BYTES_PER_ROW    # > 126 MB L2: every step streams its inputs from HBM
 
     plan = P.PartialFinalAggregation([P.VARCHAR, P.VARCHAR], [0, 1], aggs, ctx, dist, expected_groups=100_000,
-                                     reserve_sms=int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "8")))
+                                     reserve_sms=int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "8")), input_processor=processor)
 
     ctx.set_timing(True)
     with ClockSampler(local_rank) as clk:
@@ -553,7 +583,7 @@ def gpu_arm(args):
         achieved = input_bytes / (per_launch_ms / 1e3) / 1e9
         roofline = {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                     "frac": round(achieved / peak, 4), "traffic": traffic.get(top), "peak_source": peak_src,
-                    "algorithmic_bytes_per_row": tpch.Q1_BYTES_PER_ROW, "rows_per_launch": rows,
+                    "algorithmic_bytes_per_row": tpch.Q1_RAW_BYTES_PER_ROW, "rows_per_launch": rows,
                     "launch_ms": round(per_launch_ms, 4), "launches_timed": cnt,
                     "kernel_share_of_step": round(tms / args.steps / ms, 4),
                     "step_frac": round(input_bytes / (ms / 1e3) / 1e9 / peak, 4),
@@ -578,9 +608,9 @@ def gpu_arm(args):
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        n_s, times = time_cpu_port(P, tpch, args.cpu_sample_rows / ROWS_PER_SF, 1, 3, 1)
+        n_s, times, _ = time_cpu_port(P, tpch, args.cpu_sample_rows / ROWS_PER_SF, 1, 3, 1)
         cpu = {"value": n_s / min(times), "unit": "rows/s", "cores": 1, "kind": "port",
-               "sample": "oracle/ C++ restatement of GroupByHash+accumulators (the reference is Java; no JDK on this box), 1 thread, "
+               "sample": "oracle/ C++ restatement of PageProcessor + GroupByHash + accumulators (the reference is Java; no JDK on this box), 1 thread, "
                          "%d-row TPC-H-shaped lineitem sample of the same Q1 plan, best of 3" % n_s}
 
     del page, cols
@@ -599,7 +629,7 @@ def gpu_arm(args):
             "config": q1_config(args.sf, rows),
             "plan": "SINGLE" if world == 1 else "PARTIAL -> NCCL all_gather -> FINAL; the FINAL stage of step i overlaps the PARTIAL stage of step i+1",
             "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
-            "selfcheck": selfcheck,
+            "selfcheck": selfcheck, "result_digest": result_digest(out) if world == 1 else None,
         }
         if cpu:
             line["cpu_baseline"] = cpu
@@ -622,7 +652,7 @@ def reference_arm(args):
     cores = os.cpu_count() or 1
     # the same generator (counter-based, device-independent) gives this arm the very rows rank 0's GPU aggregates
     warmup = args.warmup
-    n_s, times = time_cpu_port(P, tpch, args.sf, cores, args.steps, warmup)
+    n_s, times, digest = time_cpu_port(P, tpch, args.sf, cores, args.steps, warmup)
     total = sum(times)
     value = n_s * len(times) / total
     line = {
@@ -634,8 +664,10 @@ def reference_arm(args):
         "config": q1_config(args.sf, n_s),
         "cpu_baseline": {"value": value, "unit": "rows/s", "cores": cores, "kind": "port",
                          "sample": "oracle/ C++ restatement (reference is Java, no JDK here): %d drivers run PARTIAL over slices of the same "
-                                   "%d-row SF%g input one GPU gets, one FINAL merge; %d timed passes after %d warm-up" % (cores, n_s, args.sf, len(times), warmup)},
+                                   "%d-row SF%g input one GPU gets (filter + projections, then PARTIAL), one FINAL merge; %d timed passes after %d warm-up"
+                                   % (cores, n_s, args.sf, len(times), warmup)},
         "e2e": {"value": value, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "result_digest": digest,
     }
     print(json.dumps(line), flush=True)
 

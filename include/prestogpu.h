@@ -251,6 +251,59 @@ PG_API int32_t pg_hashagg_get_output_packed(pg_hashagg* op, int64_t first, int64
 PG_API int32_t pg_hashagg_add_packed(pg_hashagg* op, const void* const* bufs, int32_t nbufs);
 
 /* =====================================================================================
+ * PageProcessor (filter + projections) — replaces OP/project/PageProcessor.java:54-57,139-330 as ScanFilterAndProjectOperator
+ * (OP/ScanFilterAndProjectOperator.java) drives it, together with the filter/projection classes sql/gen/PageFunctionCompiler.java
+ * generates, for the RowExpression subset the configs' upstream expressions use: input references, constants, decimal / bigint /
+ * integer / double arithmetic (type/DecimalOperators.java:84-330, BigintOperators.java:47-83, IntegerOperators, DoubleOperators),
+ * comparisons, AND / OR / NOT with SQL three-valued logic, IS NULL, a few casts and the $hashvalue projection
+ * (sql/planner/optimizations/HashGenerationOptimizer.java:98,872,926 -> operator/scalar/CombineHashFunction.java:25-30).
+ * Expressions form a DAG stored as an array: operands are earlier nodes.  Result types of operators follow the reference's
+ * signatures (ADD/SUB: precision min(38, max(p1-s1, p2-s2) + max(s1, s2) + 1), scale max(s1, s2); MUL: min(38, p1+p2), s1+s2;
+ * a decimal with precision <= 18 is PG_SHORT_DECIMAL, otherwise PG_LONG_DECIMAL) and are computed by the library.
+ * A row passes the filter iff it evaluates to TRUE (NULL counts as false, PageProcessor / DictionaryAwarePageFilter).
+ * Arithmetic overflow (|decimal| >= 10^38, Math.addExact on bigint / integer) fails the call with PG_E_NUMERIC_OVERFLOW, like
+ * the reference's NUMERIC_VALUE_OUT_OF_RANGE — for rows the filter rejects as well only if the expression is also part of the filter.
+ * ===================================================================================== */
+enum {
+    PG_EXPR_INPUT = 1,   /* InputReferenceExpression(channel): type / precision / scale given by the caller          */
+    PG_EXPR_CONST = 2,   /* ConstantExpression: lo (int64 value, double bits) or lo/hi (long decimal) or bytes      */
+    PG_EXPR_ADD = 3, PG_EXPR_SUB = 4, PG_EXPR_MUL = 5,
+    PG_EXPR_LT = 6, PG_EXPR_LE = 7, PG_EXPR_GT = 8, PG_EXPR_GE = 9, PG_EXPR_EQ = 10, PG_EXPR_NE = 11,
+    PG_EXPR_AND = 12, PG_EXPR_OR = 13, PG_EXPR_NOT = 14, PG_EXPR_IS_NULL = 15,
+    PG_EXPR_CAST = 16,   /* arg0 cast to type / precision / scale: integer->bigint, integer|bigint->double,
+                            integer|bigint->decimal, decimal->decimal with a scale that does not shrink                */
+    PG_EXPR_HASH = 17    /* combine_hash(arg0 = previous hash node or -1 for INITIAL_HASH_VALUE 0, hash_code(arg1)) */
+};
+typedef struct pg_expr {
+    int32_t op;
+    int32_t type;           /* INPUT, CONST, CAST: PG_* ; ignored otherwise                          */
+    int32_t precision, scale;
+    int32_t channel;        /* INPUT: channel of the page handed to process / addInput               */
+    int32_t arg0, arg1;     /* operand node indices (smaller than this node's index); -1 = none      */
+    int32_t is_null;        /* CONST: the typed NULL                                                  */
+    int64_t lo, hi;         /* CONST value                                                            */
+    const uint8_t* bytes;   /* CONST VARCHAR (copied at create)                                       */
+    int32_t nbytes;
+    int32_t reserved;
+} pg_expr;
+
+typedef struct pg_project pg_project;
+/* filter = node index or -1 (no filter); projections[i] = node index of output channel i */
+PG_API int32_t pg_project_create(pg_ctx* ctx, const pg_expr* nodes, int32_t n_nodes, int32_t filter, const int32_t* projections,
+                                 int32_t n_projections, pg_project** out);
+PG_API int32_t pg_project_destroy(pg_project* p);
+PG_API int32_t pg_project_output_types(pg_project* p, int32_t* types, int32_t* precisions, int32_t* scales, int32_t capacity, int32_t* ncols);
+/* PageProcessor.process(page): out[] (caller-allocated, capacity >= n rows each; a variable width pass-through column needs
+ * values_capacity_bytes >= the input column's value bytes) receives the projections over the rows that pass the filter, in
+ * page order; *n_out = the number of such rows. */
+PG_API int32_t pg_project_process(pg_project* p, const pg_col* cols, int32_t ncols, int64_t n, pg_col_out* out, int64_t* n_out);
+/* Fuses the processor into the aggregation (ScanFilterAndProject -> HashAggregation in one pass over the raw columns): pages
+ * handed to pg_hashagg_add_page are then the processor's INPUT pages and the operator's group-by / aggregate / mask channels
+ * index the processor's projections.  Derived columns are never materialised on the fast path.  The processor must outlive
+ * the operator; pass NULL to detach. */
+PG_API int32_t pg_hashagg_set_input_processor(pg_hashagg* op, pg_project* p);
+
+/* =====================================================================================
  * Hash partitioning for the multi-GPU exchange — replaces the row routing of OP/exchange/LocalPartitionGenerator.java:50-63,
  * OP/exchange/PartitioningExchanger.java:79-95 and OP/HashGenerator.java:24-35 (PartitionedOutputOperator).  The exchange
  * itself is an NCCL all-to-all of the partition-major columns, or direct stores into the receivers' buffers over NVLink.

@@ -4,6 +4,7 @@
 // --impl reference legs may load liboracle.so.
 #include "oracle_accum.h"
 #include "oracle_join.h"
+#include "oracle_project.h"
 
 using namespace orc;
 
@@ -197,4 +198,20 @@ ORC_API int64_t orc_join_probe(void* h, const pg_col* probe_keys, int32_t nk, co
 ORC_API void orc_join_fetch(void* h, int32_t* out_probe, int64_t* out_build) {
     JoinHandle* j = (JoinHandle*)h;
     if (!j->op.empty()) { memcpy(out_probe, j->op.data(), j->op.size() * 4); memcpy(out_build, j->ob.data(), j->ob.size() * 8); }
+}
+
+// ---------------- PageProcessor (filter + projections) ----------------
+ORC_API void* orc_project_create(const pg_expr* nodes, int32_t n, int32_t filter, const int32_t* proj, int32_t np) {
+    Project* p = new Project(); p->init(nodes, n, filter, proj, np); return p;
+}
+ORC_API void orc_project_destroy(void* h) { delete (Project*)h; }
+ORC_API void orc_project_types(void* h, int32_t* types, int32_t* precisions, int32_t* scales) {
+    Project* p = (Project*)h;
+    for (size_t k = 0; k < p->proj.size(); k++) { const PType& t = p->types[p->proj[k]]; types[k] = t.type; precisions[k] = t.precision; scales[k] = t.scale; }
+}
+// out[] sized for n rows (variable width: the input column's value bytes); returns PG_E_NUMERIC_OVERFLOW where the reference throws
+ORC_API int32_t orc_project_process(void* h, const pg_col* cols, int64_t n, pg_col_out* out, int64_t* n_out) {
+    Project* p = (Project*)h; p->overflow = false;
+    *n_out = p->process(cols, n, out);
+    return p->overflow ? PG_E_NUMERIC_OVERFLOW : PG_OK;
 }

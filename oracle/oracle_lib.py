@@ -55,6 +55,8 @@ def lib():
             "orc_join_add_page": (None, [P_, PCOL, I64]), "orc_join_build": (None, [P_]), "orc_join_rows": (I64, [P_]),
             "orc_join_hash_size": (I64, [P_]), "orc_join_collisions": (I64, [P_]),
             "orc_join_probe": (I64, [P_, PCOL, I32, PCOL, I64, I32]), "orc_join_fetch": (None, [P_, P_, P_]),
+            "orc_project_create": (P_, [P_, I32, I32, P_, I32]), "orc_project_destroy": (None, [P_]),
+            "orc_project_types": (None, [P_, P_, P_, P_]), "orc_project_process": (I32, [P_, PCOL, I64, PCOLOUT, P_]),
         }
         for name, (res, args) in protos.items():
             fn = getattr(l, name)
@@ -188,6 +190,49 @@ class OracleJoin:
     def __del__(self):
         if lib and self._h:
             lib().orc_join_destroy(self._h)
+            self._h = None
+
+
+class OraclePageProcessor:
+    """Filter + projections evaluated row by row (oracle_project.h).  Takes the same Expr trees as presto_b200.PageProcessor."""
+
+    def __init__(self, filter=None, projections=()):
+        from presto_b200.expressions import flatten
+        self.projections = list(projections)
+        roots = ([filter] if filter is not None else []) + self.projections
+        arr, index, keep, n = flatten(roots)
+        self._keep = (arr, keep)
+        proj = (C.c_int32 * max(1, len(self.projections)))(*[index[id(p)] for p in self.projections])
+        self._h = lib().orc_project_create(arr, n, index[id(filter)] if filter is not None else -1, proj, len(self.projections))
+        k = len(self.projections)
+        t, p, s = (C.c_int32 * max(1, k))(), (C.c_int32 * max(1, k))(), (C.c_int32 * max(1, k))()
+        lib().orc_project_types(self._h, t, p, s)
+        self.output_types = [(t[i], p[i], s[i]) for i in range(k)]
+
+    def process(self, page):
+        """Returns (status, projected host page)."""
+        blocks = _host(page.blocks if hasattr(page, "blocks") else page)
+        n = blocks[0].n
+        outs = []
+        for (t, p, s), e in zip(self.output_types, self.projections):
+            vb = len(blocks[e.channel].values) if t in (N.VARCHAR, N.VARBINARY) else 0
+            outs.append(OutBlock(t, n, vb))
+        arr = (N.PgColOut * max(1, len(outs)))()
+        for i, o in enumerate(outs):
+            arr[i] = o.pg_col_out()
+        n_out = C.c_int64()
+        rc = lib().orc_project_process(self._h, col_array(blocks), n, arr, C.byref(n_out))
+        m = n_out.value
+        res = []
+        for o, (t, p, s) in zip(outs, self.output_types):
+            b = o.block(m)
+            b.precision, b.scale = p, s
+            res.append(b)
+        return rc, P.Page(*res, position_count=m)
+
+    def __del__(self):
+        if lib and self._h:
+            lib().orc_project_destroy(self._h)
             self._h = None
 
 

@@ -30,6 +30,16 @@ class PgColOut(C.Structure):
                 ("offsets", C.c_void_p), ("values_capacity_bytes", C.c_int64)]
 
 
+class PgExpr(C.Structure):
+    _fields_ = [("op", C.c_int32), ("type", C.c_int32), ("precision", C.c_int32), ("scale", C.c_int32), ("channel", C.c_int32),
+                ("arg0", C.c_int32), ("arg1", C.c_int32), ("is_null", C.c_int32), ("lo", C.c_int64), ("hi", C.c_int64),
+                ("bytes", C.c_void_p), ("nbytes", C.c_int32), ("reserved", C.c_int32)]
+
+
+(EXPR_INPUT, EXPR_CONST, EXPR_ADD, EXPR_SUB, EXPR_MUL, EXPR_LT, EXPR_LE, EXPR_GT, EXPR_GE, EXPR_EQ, EXPR_NE, EXPR_AND, EXPR_OR, EXPR_NOT,
+ EXPR_IS_NULL, EXPR_CAST, EXPR_HASH) = range(1, 18)
+
+
 class PgAggSpec(C.Structure):
     _fields_ = [("kind", C.c_int32), ("in_type", C.c_int32), ("input_channel", C.c_int32), ("mask_channel", C.c_int32)]
 
@@ -90,6 +100,11 @@ _PROTOS = {
     "pg_hashagg_reset": (I32, [P]),
     "pg_hashagg_get_output_packed": (I32, [P, I64, I64, P, I64, PI64, PI64]),
     "pg_hashagg_add_packed": (I32, [P, C.POINTER(C.c_void_p), I32]),
+    "pg_project_create": (I32, [P, C.POINTER(PgExpr), I32, I32, PI32, I32, C.POINTER(P)]),
+    "pg_project_destroy": (I32, [P]),
+    "pg_project_output_types": (I32, [P, PI32, PI32, PI32, I32, PI32]),
+    "pg_project_process": (I32, [P, PCOL, I32, I64, PCOLOUT, PI64]),
+    "pg_hashagg_set_input_processor": (I32, [P, P]),
     "pg_partition_create": (I32, [P, PCOL, I32, PCOL, I64, I32, I32, PI64, C.POINTER(P)]),
     "pg_partition_destroy": (I32, [P]),
     "pg_partition_scatter": (I32, [P, PCOL, PCOLOUT]),

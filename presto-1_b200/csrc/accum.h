@@ -14,6 +14,8 @@
 #pragma once
 #include "context.h"
 
+struct pg_project;
+
 namespace pg {
 
 enum OpClass : int32_t {
@@ -86,8 +88,18 @@ bool fused_keys_packable(const KeyLayout& L);
 bool fused_pack_layout(const KeyLayout& L, int32_t* word, int32_t* shift);
 bool accumulate_private(pg_ctx* ctx, const AggProgram& prog, const int32_t* gids, int64_t n, int64_t group_count, const uint8_t* only_rows,
                         const FusedLookup* fused);
-// the same pass through a kernel specialised at run time for this plan (jit_lowcard.cu); false when it cannot be used
-bool accumulate_lowcard_jit(pg_ctx* ctx, const AggProgram& prog, int64_t n, int64_t group_count, const FusedLookup& fused);
+// the same pass through a kernel specialised at run time for this plan (jit_lowcard.cu); false when it cannot be used.
+// px (optional): a fused PageProcessor — aggregate arguments and masks are projections of it, evaluated inside the kernel over
+// the processor's input columns `in`; rows its filter rejects do not exist for the operator.  fused.d_miss must then be two
+// words: [0] rows left to the general path, [1] error bits (1 = arithmetic overflow in an expression).
+struct LowcardExprs {
+    const pg_project* proc;
+    const DCol* in;               // the processor's input columns, by channel
+    int arg_proj[MAX_AGGS];       // projection read by aggregate i (-1: count(*))
+    int mask_proj[MAX_AGGS];      // projection used as its mask (-1: none)
+};
+bool accumulate_lowcard_jit(pg_ctx* ctx, const AggProgram& prog, int64_t n, int64_t group_count, const FusedLookup& fused,
+                            const LowcardExprs* px = nullptr);
 
 }  // namespace pg
 

@@ -9,6 +9,7 @@
 #include "groupby.h"
 #include "hashagg_wide.h"
 #include "jit.h"
+#include "project.h"
 
 struct pg_hashagg {
     pg_ctx* ctx = nullptr;
@@ -22,6 +23,7 @@ struct pg_hashagg {
     std::vector<pg_agg*> aggs;
     pg::DevBuf ids;
     int64_t input_rows = 0;
+    pg_project* proc = nullptr;      // fused filter + projections in front of the aggregation (pg_hashagg_set_input_processor); not owned
     pg::WideTable* wide = nullptr;   // many-groups path (hashagg_wide.h), chosen on the first page
     int64_t rows_since_reset = 0;    // first-seen order of the wide path is kept by operator-wide row numbers
     ~pg_hashagg() {
@@ -61,9 +63,151 @@ void hashagg_build(pg_hashagg* op) {
     }
 }
 
+static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n);
+
+// channels of the operator's logical input page (= the processor's projections) that the operator reads
+static std::vector<char> channels_read(const pg_hashagg* op, int np) {
+    std::vector<char> want(np, 0);
+    auto mark = [&](int ch) { PG_CHECK_ARG(ch >= 0 && ch < np, "channel %d out of range (the input processor has %d projections)", ch, np); want[ch] = 1; };
+    for (int ch : op->key_channels) mark(ch);
+    if (op->hash_channel >= 0) mark(op->hash_channel);
+    for (size_t i = 0; i < op->specs.size(); i++) {
+        const pg_agg_spec& s = op->specs[i];
+        if (s.kind != PG_AGG_COUNT) {
+            mark(s.input_channel);
+            if (!(op->step == PG_STEP_SINGLE || op->step == PG_STEP_PARTIAL) && agg_n_intermediate(op->aggs[i]) > 1) mark(s.input_channel + 1);
+        }
+        if (s.mask_channel >= 0) mark(s.mask_channel);
+    }
+    return want;
+}
+
+// The general path of a fused processor: materialise the projections over the selected rows (only_bits restricts the rows
+// further), then hand the projected device page to the plain operator.
+static void hashagg_add_projected(pg_hashagg* op, const DCol* in, int ncols, int64_t n, const unsigned int* only_bits) {
+    pg_project* proc = op->proc;
+    const int np = (int)proc->proj.size();
+    std::vector<char> want = channels_read(op, np);
+    ProjectedPage page;
+    project_materialize(proc, in, ncols, n, only_bits, &want, page);
+    if (page.n == 0) return;
+    std::vector<pg_col> pc(np);
+    for (int k = 0; k < np; k++) {
+        pg_col& c = pc[k];
+        memset(&c, 0, sizeof(c));
+        const PNode& e = proc->nodes[proc->proj[k]];
+        c.type = e.type; c.mem = PG_MEM_DEVICE; c.n = page.n; c.precision = e.precision; c.scale = e.scale;
+        c.values = page.cols[k].values; c.nulls = page.cols[k].nulls; c.offsets = page.cols[k].offsets;
+    }
+    op->proc = nullptr;
+    try { hashagg_add_page(op, pc.data(), np, page.n); } catch (...) { op->proc = proc; throw; }
+    op->proc = proc;
+}
+
+// Fast path of a fused processor with few groups: the filter and the projections run inside the specialised aggregation kernel
+// over the raw input columns (derived columns are never written).  Group numbering stays the reference's: the rows of a short
+// prefix that pass the filter are projected and go through the GroupByHash alone (first-seen ids); the kernel then handles all
+// rows of the page; rows that pass the filter but carry a key the prefix did not show are projected and take the general path
+// in page order, so later groups are numbered after the prefix's, as they would be row by row.
+// Returns false when the plan does not fit (nothing has been accumulated then; groups found so far keep their ids).
+static bool hashagg_try_fused_processor(pg_hashagg* op, const DCol* in, ColImport* imports, int ncols, int64_t n) {
+    pg_ctx* ctx = op->ctx;
+    pg_project* proc = op->proc;
+    const int64_t PREFIX = 16 * 1024;
+    if (!step_input_raw(op->step) || op->aggs.empty() || n < 8 * PREFIX || op->hash_channel >= 0 || op->wide) return false;
+    if (!jit_available() || !fused_keys_packable(op->gb->layout)) return false;
+    if (const char* e = getenv("PRESTOGPU_FUSED_PROJECT")) if (e[0] == '0') return false;
+    const int np = (int)proc->proj.size();
+    const int nk = (int)op->key_channels.size();
+    KeyCols kc;
+    memset(&kc, 0, sizeof(kc));
+    ColImport* kimp[MAX_KEYS];
+    for (int k = 0; k < nk; k++) {                         // group-by channels must be passed through unchanged
+        const PNode& e = proc->nodes[proc->proj[op->key_channels[k]]];
+        if (e.op != PG_EXPR_INPUT || e.type != op->key_types[k]) return false;
+        kc.c[k] = in[e.channel];
+        kimp[k] = &imports[e.channel];
+    }
+    LowcardExprs px;
+    px.proc = proc; px.in = in;
+    for (size_t i = 0; i < op->aggs.size(); i++) {
+        const pg_agg_spec& s = op->specs[i];
+        px.arg_proj[i] = s.kind != PG_AGG_COUNT ? s.input_channel : -1;
+        px.mask_proj[i] = s.mask_channel;
+        if (px.arg_proj[i] >= np || px.mask_proj[i] >= np) return false;
+    }
+    {   // 1. the prefix numbers the groups
+        std::vector<char> want(np, 0);
+        for (int k = 0; k < nk; k++) want[op->key_channels[k]] = 1;
+        ProjectedPage pp;
+        project_materialize(proc, in, ncols, PREFIX, nullptr, &want, pp);
+        if (pp.n > 0) {
+            KeyCols pk;
+            memset(&pk, 0, sizeof(pk));
+            for (int k = 0; k < nk; k++) pk.c[k] = pp.cols[op->key_channels[k]];
+            groupby_process(op->gb, pk, nullptr, pp.n, nullptr);
+        }
+    }
+    const int64_t groups = op->gb->groups;
+    if (groups < 1 || groups > 64) return false;
+    for (pg_agg* a : op->aggs) agg_ensure_capacity(a, groups);
+    // 2. every row of the page through the specialised kernel
+    const int64_t miss_words = (n + 31) / 32;
+    DevBuf miss_flag(ctx, 16 + miss_words * 4);
+    memset_async(ctx, miss_flag.p, 0, 16 + miss_words * 4);
+    unsigned long long* d_miss_cnt = miss_flag.as<unsigned long long>();
+    unsigned int* d_miss_bits = (unsigned int*)(d_miss_cnt + 2);
+    FusedLookup fl;
+    memset(&fl, 0, sizeof(fl));
+    fl.layout = &op->gb->layout; fl.keys = &kc; fl.key_rows = op->gb->key_rows.as<uint64_t>(); fl.arena = op->gb->arena.as<uint8_t>();
+    fl.values_by_group = op->gb->values_by_group.as<int64_t>(); fl.bigint_mode = op->gb->bigint_mode ? 1 : 0;
+    fl.null_gid = -1;
+    if (op->gb->bigint_mode) {
+        int64_t sp[2];
+        read_scalars(ctx, op->gb->slots.as<Slot>() + op->gb->cap + 1, 2, sp);
+        fl.null_gid = (int32_t)(sp[1] & 0xffffffff);
+    }
+    fl.miss_flag = d_miss_bits; fl.d_miss = d_miss_cnt; fl.row_base = 0;
+    resolve_value_bytes(ctx, kimp, nk);
+    for (int k = 0; k < nk && k < 8; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
+    AggProgram prog;
+    memset(&prog, 0, sizeof(prog));
+    prog.naggs = (int32_t)op->aggs.size();
+    for (size_t i = 0; i < op->aggs.size(); i++) prog.ops[i] = agg_make_op(op->aggs[i], nullptr, nullptr);
+    if (!accumulate_lowcard_jit(ctx, prog, n, groups, fl, &px)) return false;
+    // 3. what the kernel left over
+    int64_t res[2];
+    read_scalars(ctx, d_miss_cnt, 2, res);
+    if (res[1] & 1) fail(PG_E_NUMERIC_OVERFLOW, "Decimal overflow / numeric value out of range in a filter or projection expression");
+    if (res[0] > 0) {
+        const int64_t rows = op->rows_since_reset;
+        hashagg_add_projected(op, in, ncols, n, d_miss_bits);
+        op->rows_since_reset = rows;
+    }
+    op->rows_since_reset += n;
+    return true;
+}
+
 static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n) {
     pg_ctx* ctx = op->ctx;
     if (n == 0) return;
+    if (op->proc) {
+        pg_project* proc = op->proc;
+        PG_CHECK_ARG(proc->max_channel < ncols, "the page has %d channels, the input processor reads channel %d", ncols, proc->max_channel);
+        std::vector<ColImport> pimp(ncols);
+        std::vector<DCol> in(ncols, DCol{0, 0, nullptr, nullptr, nullptr});
+        for (int c = 0; c < ncols && c < PROJ_MAX_CHANNELS; c++) {
+            if (!proc->channel_used[c]) continue;
+            PG_CHECK_ARG(cols[c].n == n, "channel %d has %lld rows, expected %lld", c, (long long)cols[c].n, (long long)n);
+            import_col(ctx, cols[c], n, pimp[c]);
+            in[c] = pimp[c].d;
+        }
+        const int64_t before = op->input_rows;
+        if (!hashagg_try_fused_processor(op, in.data(), pimp.data(), ncols, n)) hashagg_add_projected(op, in.data(), ncols, n, nullptr);
+        op->input_rows = before + n;        // rows entering the fused operator, not rows surviving the filter
+        sync(ctx);
+        return;
+    }
     // import each referenced channel once
     std::vector<ColImport> imp(ncols);
     std::vector<char> loaded(ncols, 0);
@@ -185,10 +329,10 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         };
         if (groups <= 64) {
             const int64_t miss_words = (n + 31) / 32;
-            DevBuf miss_flag(ctx, 8 + miss_words * 4);          // [miss count (8 bytes)][bitmap of rows left to the general path]
-            memset_async(ctx, miss_flag.p, 0, 8 + miss_words * 4);
+            DevBuf miss_flag(ctx, 16 + miss_words * 4);         // [miss count (8 bytes)][error bits (8)][bitmap of rows left to the general path]
+            memset_async(ctx, miss_flag.p, 0, 16 + miss_words * 4);
             unsigned long long* d_miss_cnt = miss_flag.as<unsigned long long>();
-            unsigned int* d_miss_bits = (unsigned int*)(d_miss_cnt + 1);
+            unsigned int* d_miss_bits = (unsigned int*)(d_miss_cnt + 2);
             KeyCols kco;
             FusedLookup fl;
             fl.layout = &op->gb->layout; fl.keys = &kco; fl.key_rows = op->gb->key_rows.as<uint64_t>(); fl.arena = op->gb->arena.as<uint8_t>();
@@ -517,6 +661,18 @@ int32_t pg_hashagg_add_packed(pg_hashagg* op, const void* const* bufs, int32_t n
         c.offsets = packed_is_var(types[i]) ? offsets[i].data() : nullptr;
     }
     return pg_hashagg_add_page(op, cols.data(), ncols, total);
+}
+
+int32_t pg_hashagg_set_input_processor(pg_hashagg* op, pg_project* p) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    return guard(op->ctx, [&] {
+        PG_CHECK_STATE(op->input_rows == 0, "the input processor must be attached before the first page");
+        if (p) {
+            PG_CHECK_ARG(p->ctx->device == op->ctx->device, "processor and operator live on different devices");
+            (void)channels_read(op, (int)p->proj.size());     // validates the operator's channel numbers against the projections
+        }
+        op->proc = p;
+    });
 }
 
 /* partial-aggregation flush: drop all groups and states, keep the configuration (HashAggregationOperator.java:501-517) */

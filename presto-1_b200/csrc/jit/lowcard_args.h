@@ -4,7 +4,7 @@
 #define PGJ_LOWCARD_ARGS_H
 
 #define PGJ_MAX_KEYS 8
-#define PGJ_MAX_CONDS 4
+#define PGJ_MAX_LOADS 24
 #define PGJ_MAX_SLOTS 24
 #define PGJ_MAX_AGGS 16
 #define PGJ_LUT_SIZE 256
@@ -23,10 +23,9 @@ struct PgjArgs {
     const unsigned char* key_nulls[PGJ_MAX_KEYS];
     const int* key_offsets[PGJ_MAX_KEYS];
     long long key_value_bytes[PGJ_MAX_KEYS];   // bytes in a variable width key's value buffer (bounds the speculative load)
-    const unsigned char* cond_mask[PGJ_MAX_CONDS];
-    const unsigned char* cond_mask_nulls[PGJ_MAX_CONDS];
-    const unsigned char* cond_arg_nulls[PGJ_MAX_CONDS];
-    const void* slot_ptr[PGJ_MAX_SLOTS];
+    // the input columns the row loop reads (aggregate arguments, masks, operands of fused filter / projection expressions)
+    const void* load_ptr[PGJ_MAX_LOADS];
+    const unsigned char* load_nulls[PGJ_MAX_LOADS];
     // flush table: one entry per aggregate (several aggregates may share one private slot)
     unsigned long long* agg_state[PGJ_MAX_AGGS];
     int agg_op[PGJ_MAX_AGGS];        // OpClass
@@ -39,7 +38,7 @@ struct PgjArgs {
     const unsigned char* arena;
     const long long* values_by_group;
     unsigned int* miss_flag;         // bitmap: bit set for rows whose key is not in the table (zeroed by the caller)
-    unsigned long long* d_miss;      // number of such rows
+    unsigned long long* d_miss;      // [0] number of such rows, [1] error bits (1 = arithmetic overflow in a fused expression)
     long long n;
     long long row_base;              // page row of row 0 (variable width offsets are absolute within the page)
     int naggs, G, bigint_mode, null_gid, row_words, pad;

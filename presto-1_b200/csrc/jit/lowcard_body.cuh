@@ -7,9 +7,13 @@
 //   PG_REC_WORDS    u64 words per group/thread   PG_MIN_BLOCKS  __launch_bounds__ second argument
 //   PG_PREFETCH     trips ahead whose rows are prefetched into L2 (0 = off)
 //   PG_KEYS(X)      X(k, CLASS, WORD, SHIFT, HASNULL, WOFF)   CLASS in {K64, KDBL, K32, K8, KVAR}
-//   PG_CONDS(X)     X(c, HASMASK, HASMASKNULLS, HASARGNULLS)
-//   PG_SLOTS(X)     X(s, KIND, COND, CONV, WORD)              KIND in {DEC, I64, I32, F64, MIN, MAX, CNT}
-// Everything structural is a literal, so the row loop is straight-line code; pointers and sizes arrive in PgjArgs.
+//   PG_LOADS(X)     X(l, LKIND, HASNULL)                      LKIND in {U64, I32, U8, U128}: input column l of the row loop
+//   PG_SLOTS(X)     X(s, KIND, WORD)                          KIND in {DEC, I64, I32, F64, MIN, MAX, CNT}: private state layout
+//   PG_ROW_FILTER   statements for row v that end by defining `const bool pgx_pass` (a fused filter; `true` without one)
+//   PG_ROW_UPDATE   statements for row v: fused projections, the aggregates' conditions and the updates of `rec`
+// The two statement macros are generated text over ld<l>[v] / ldh<l>[v] (value, upper half of 128-bit values) and ldn<l>[v]
+// (null byte) — see jit_lowcard.cu and project_codegen.  Everything structural is a literal, so the row loop is straight-line
+// code; pointers and sizes arrive in PgjArgs.
 //
 // Layout of the private tables in shared memory: table[(group * PG_REC_WORDS + word) * PG_T + thread] — a warp touching
 // one word of 32 different (or equal) groups hits 32 different banks; every thread owns its column, no atomics.
@@ -111,6 +115,19 @@ __device__ __forceinline__ void upd_dec(u64* t, u64 lo, u64 hi) {
         t[PG_T] = s1; t[2 * PG_T] = s2;
     }
 }
+// the same with a two's complement addend (a derived decimal of a fused projection): sign-extend into the third word
+__device__ __forceinline__ void upd_dec2c(u64* t, u64 w0, i64 w1) {
+    u64 s0 = t[0] + w0;
+    t[0] = s0;
+    u64 c0 = s0 < w0 ? 1ULL : 0ULL;
+    if (w1 | (i64)c0) {
+        u64 a1 = (u64)w1, a2 = (u64)(w1 >> 63);
+        u64 s1 = t[PG_T], s2 = t[2 * PG_T];
+        asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, 0;" : "+l"(a1), "+l"(a2) : "l"(c0));
+        asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, %3;" : "+l"(s1), "+l"(s2) : "l"(a1), "l"(a2));
+        t[PG_T] = s1; t[2 * PG_T] = s2;
+    }
+}
 __device__ __forceinline__ void upd_f64(u64* t, u64 bits, int conv) {
     double d = conv ? (double)(i64)bits : __longlong_as_double((i64)bits);
     t[0] = (u64)__double_as_longlong(__longlong_as_double((i64)t[0]) + d);
@@ -161,21 +178,10 @@ __device__ __forceinline__ void wreduce_sum_carry(u64& s, u64& carry) {
 }
 
 // ------------------------------------------------------------------ per-kind macro pieces
-#define PGJ_DECL_VAL(s) u64 PGJ_CAT(sva, s)[V]; u64 PGJ_CAT(svb, s)[V]; (void)PGJ_CAT(sva, s); (void)PGJ_CAT(svb, s);
-#define PGJ_LOAD_DEC(s) load_u128<V>(a.slot_ptr[s], row, PGJ_CAT(sva, s), PGJ_CAT(svb, s));
-#define PGJ_LOAD_I64(s) load_u64<V>(a.slot_ptr[s], row, PGJ_CAT(sva, s));
-#define PGJ_LOAD_I32(s) { int t32[V]; load_i32<V>(a.slot_ptr[s], row, t32); _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(sva, s)[q] = (u64)(i64)t32[q]; }
-#define PGJ_LOAD_F64(s) PGJ_LOAD_I64(s)
-#define PGJ_LOAD_MIN(s) PGJ_LOAD_I64(s)
-#define PGJ_LOAD_MAX(s) PGJ_LOAD_I64(s)
-#define PGJ_LOAD_CNT(s)
-#define PGJ_UPD_DEC(s, W, CONV) upd_dec(rec + (W) * PG_T, PGJ_CAT(sva, s)[v], PGJ_CAT(svb, s)[v]);
-#define PGJ_UPD_I64(s, W, CONV) upd_i64(rec + (W) * PG_T, PGJ_CAT(sva, s)[v]);
-#define PGJ_UPD_I32(s, W, CONV) upd_i64(rec + (W) * PG_T, PGJ_CAT(sva, s)[v]);
-#define PGJ_UPD_F64(s, W, CONV) upd_f64(rec + (W) * PG_T, PGJ_CAT(sva, s)[v], CONV);
-#define PGJ_UPD_MIN(s, W, CONV) upd_min(rec + (W) * PG_T, PGJ_CAT(sva, s)[v], CONV);
-#define PGJ_UPD_MAX(s, W, CONV) upd_max(rec + (W) * PG_T, PGJ_CAT(sva, s)[v], CONV);
-#define PGJ_UPD_CNT(s, W, CONV) rec[(W) * PG_T] += 1;
+#define PGJ_LD_U64(l) u64 PGJ_CAT(ld, l)[V]; load_u64<V>(a.load_ptr[l], row, PGJ_CAT(ld, l));
+#define PGJ_LD_U128(l) u64 PGJ_CAT(ld, l)[V], PGJ_CAT(ldh, l)[V]; load_u128<V>(a.load_ptr[l], row, PGJ_CAT(ld, l), PGJ_CAT(ldh, l));
+#define PGJ_LD_I32(l) u64 PGJ_CAT(ld, l)[V]; { int t32[V]; load_i32<V>(a.load_ptr[l], row, t32); _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(ld, l)[q] = (u64)(i64)t32[q]; }
+#define PGJ_LD_U8(l) u64 PGJ_CAT(ld, l)[V]; { u32 t8[V]; load_u8<V>((const u8*)a.load_ptr[l], row, t8); _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(ld, l)[q] = t8[q]; }
 #define PGJ_ISKIND_DEC 0
 #define PGJ_ISKIND_I64 1
 #define PGJ_ISKIND_I32 2
@@ -208,22 +214,15 @@ template <int V>
 __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* table, const LutEntry* lut,
                                              int tid, u64& misses) {
     bool fits[V];
+    int pgx_err = 0;
 #pragma unroll
     for (int q = 0; q < V; q++) fits[q] = true;
     // ---- stage 1: every load whose address depends on the row number only
 #define PG_X(k, CLASS, WORD, SHIFT, HASNULL, WOFF) PGJ_K1_##CLASS(k) u32 PGJ_CAT(kn, k)[V]; (void)PGJ_CAT(kn, k); if (HASNULL) load_u8<V>(a.key_nulls[k], row, PGJ_CAT(kn, k));
     PG_KEYS(PG_X)
 #undef PG_X
-#define PG_X(c, HASMASK, HASMASKNULLS, HASARGNULLS)                                                              \
-    u32 PGJ_CAT(cm, c)[V], PGJ_CAT(cmn, c)[V], PGJ_CAT(can, c)[V];                                               \
-    (void)PGJ_CAT(cm, c); (void)PGJ_CAT(cmn, c); (void)PGJ_CAT(can, c);                                          \
-    if (HASMASK) load_u8<V>(a.cond_mask[c], row, PGJ_CAT(cm, c));                                                \
-    if (HASMASKNULLS) load_u8<V>(a.cond_mask_nulls[c], row, PGJ_CAT(cmn, c));                                    \
-    if (HASARGNULLS) load_u8<V>(a.cond_arg_nulls[c], row, PGJ_CAT(can, c));
-    PG_CONDS(PG_X)
-#undef PG_X
-#define PG_X(s, KIND, COND, CONV, WORD) PGJ_DECL_VAL(s) PGJ_LOAD_##KIND(s)
-    PG_SLOTS(PG_X)
+#define PG_X(l, LKIND, HASNULL) PGJ_LD_##LKIND(l) u32 PGJ_CAT(ldn, l)[V]; (void)PGJ_CAT(ldn, l); if (HASNULL) load_u8<V>(a.load_nulls[l], row, PGJ_CAT(ldn, l));
+    PG_LOADS(PG_X)
 #undef PG_X
     // ---- stage 2: key values (string bytes sit behind the offsets just loaded)
 #define PG_X(k, CLASS, WORD, SHIFT, HASNULL, WOFF) PGJ_K2_##CLASS(k)
@@ -251,20 +250,17 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
             }
         }
     }
-    // ---- phase B: update the thread's private records, row by row (two rows may share a group)
+    // ---- phase B: update the thread's private records, row by row (two rows may share a group).  A row the fused filter
+    // rejects does not exist for the operator: it neither counts nor misses.
 #pragma unroll
     for (int v = 0; v < V; v++) {
+        PG_ROW_FILTER
+        if (!pgx_pass) continue;
         if (g[v] < 0) { misses++; atomicOr(&a.miss_flag[(row + v) >> 5], 1u << ((row + v) & 31)); continue; }
         u64* rec = table + (g[v] * PG_REC_WORDS) * PG_T + tid;
-#define PG_X(c, HASMASK, HASMASKNULLS, HASARGNULLS)                                                         \
-        const bool PGJ_CAT(cond, c) = (!HASMASK || PGJ_CAT(cm, c)[v] != 0) && (!HASMASKNULLS || PGJ_CAT(cmn, c)[v] == 0) && \
-                                      (!HASARGNULLS || PGJ_CAT(can, c)[v] == 0);
-        PG_CONDS(PG_X)
-#undef PG_X
-#define PG_X(s, KIND, COND, CONV, WORD) if (PGJ_CAT(cond, COND)) { PGJ_UPD_##KIND(s, WORD, CONV) }
-        PG_SLOTS(PG_X)
-#undef PG_X
+        PG_ROW_UPDATE
     }
+    if (pgx_err) atomicOr((unsigned int*)(a.d_miss + 1), 1u);
 }
 
 // L2 prefetch of the V rows a later trip of this thread will read (PG_PREFETCH trips ahead): keeps more of HBM's
@@ -280,21 +276,12 @@ __device__ __forceinline__ void prefetch_rows(const PgjArgs& a, i64 row) {
 #define PG_X(k, CLASS, WORD, SHIFT, HASNULL, WOFF) PGJ_PF_##CLASS(k) if (HASNULL) prefetch_l2(a.key_nulls[k] + row);
     PG_KEYS(PG_X)
 #undef PG_X
-#define PG_X(c, HASMASK, HASMASKNULLS, HASARGNULLS)                 \
-    if (HASMASK) prefetch_l2(a.cond_mask[c] + row);                 \
-    if (HASMASKNULLS) prefetch_l2(a.cond_mask_nulls[c] + row);      \
-    if (HASARGNULLS) prefetch_l2(a.cond_arg_nulls[c] + row);
-    PG_CONDS(PG_X)
-#undef PG_X
-#define PGJ_PFS_DEC(s) _Pragma("unroll") for (int q = 0; q < V; q += 2) prefetch_l2((const ulonglong2*)a.slot_ptr[s] + row + q);
-#define PGJ_PFS_I64(s) prefetch_l2((const u64*)a.slot_ptr[s] + row);
-#define PGJ_PFS_I32(s) prefetch_l2((const int*)a.slot_ptr[s] + row);
-#define PGJ_PFS_F64(s) PGJ_PFS_I64(s)
-#define PGJ_PFS_MIN(s) PGJ_PFS_I64(s)
-#define PGJ_PFS_MAX(s) PGJ_PFS_I64(s)
-#define PGJ_PFS_CNT(s)
-#define PG_X(s, KIND, COND, CONV, WORD) PGJ_PFS_##KIND(s)
-    PG_SLOTS(PG_X)
+#define PGJ_PFL_U64(l) prefetch_l2((const u64*)a.load_ptr[l] + row);
+#define PGJ_PFL_U128(l) _Pragma("unroll") for (int q = 0; q < V; q += 2) prefetch_l2((const ulonglong2*)a.load_ptr[l] + row + q);
+#define PGJ_PFL_I32(l) prefetch_l2((const int*)a.load_ptr[l] + row);
+#define PGJ_PFL_U8(l) prefetch_l2((const u8*)a.load_ptr[l] + row);
+#define PG_X(l, LKIND, HASNULL) PGJ_PFL_##LKIND(l) if (HASNULL) prefetch_l2(a.load_nulls[l] + row);
+    PG_LOADS(PG_X)
 #undef PG_X
 }
 
@@ -328,7 +315,7 @@ extern "C" __global__ void __launch_bounds__(PG_T, PG_MIN_BLOCKS) pg_lowcard_agg
     const int G = a.G;
     // ---- own column: zeros, then min/max identities
     for (int i = 0; i < G * PG_REC_WORDS; i++) table[i * PG_T + tid] = 0;
-#define PG_X(s, KIND, COND, CONV, WORD)                                                                                   \
+#define PG_X(s, KIND, WORD)                                                                                               \
     if (PGJ_ISKIND_##KIND == PGJ_KIND_MIN) for (int g = 0; g < G; g++) table[(g * PG_REC_WORDS + WORD) * PG_T + tid] = 0x7fffffffffffffffULL; \
     if (PGJ_ISKIND_##KIND == PGJ_KIND_MAX) for (int g = 0; g < G; g++) table[(g * PG_REC_WORDS + WORD) * PG_T + tid] = 0x8000000000000000ULL;
     PG_SLOTS(PG_X)

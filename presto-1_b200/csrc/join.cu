@@ -2,6 +2,7 @@
 #include <stdlib.h>
 
 #include "join.h"
+#include "project.h"
 
 namespace pg {
 
@@ -683,6 +684,32 @@ __global__ void __launch_bounds__(SCAN_THREADS) j_gather_var_kernel(DCol src, co
         }
         run = run + total;
     }
+}
+
+// gather rows `pos` of a device column into fresh device buffers (also used by the PageProcessor's general path, project.cu)
+void gather_device_col(pg_ctx* ctx, const DCol& src, const int64_t* d_pos, int64_t n, DevBuf& values, DevBuf& nulls, DevBuf& offsets, DCol& out) {
+    out.type = src.type; out.pad = 0; out.offsets = nullptr;
+    nulls.alloc(ctx, n > 0 ? n : 1);
+    out.nulls = src.nulls ? nulls.as<uint8_t>() : nullptr;
+    if (!type_is_var(src.type)) {
+        values.alloc(ctx, (n > 0 ? n : 1) * (int64_t)type_width(src.type));
+        out.values = values.p;
+        if (n > 0) PG_LAUNCH(ctx, j_gather_fixed_kernel, grid_for(ctx, n, 256), 256, 0, src, d_pos, n, values.p, (uint8_t*)out.nulls);
+        return;
+    }
+    const int64_t ntiles = num_tiles(n > 0 ? n : 1);
+    DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+    offsets.alloc(ctx, (n + 1) * 4);
+    int64_t tot[2] = {0, 0};
+    if (n > 0) {
+        PG_LAUNCH(ctx, j_gather_var_count_kernel, (int)ntiles, SCAN_THREADS, 0, src, d_pos, n, tiles.as<Pair64>());
+        scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, tiles.as<Pair64>() + ntiles);
+        read_scalars(ctx, tiles.as<Pair64>() + ntiles, 2, tot);
+    } else memset_async(ctx, offsets.p, 0, 4);
+    values.alloc(ctx, tot[0] > 0 ? tot[0] : 8);
+    out.values = values.p; out.offsets = offsets.as<int32_t>();
+    if (n > 0) PG_LAUNCH(ctx, j_gather_var_kernel, (int)ntiles, SCAN_THREADS, 0, src, d_pos, n, tiles.as<Pair64>(), (uint8_t*)values.p, offsets.as<int32_t>(),
+                         (uint8_t*)out.nulls);
 }
 
 // ------------------------------------------------------------------ host side

@@ -27,7 +27,7 @@ class HashAggregationOperator:
     """GROUP BY operator: addInput pages, then after finish() getOutput returns pages of [keys..., (hash), aggregates...]."""
 
     def __init__(self, group_by_types, group_by_channels, step, aggregators, hash_channel=None, expected_groups=10_000,
-                 max_partial_memory=16 << 20, output_page_rows=8192, ctx=None, device_output=False):
+                 max_partial_memory=16 << 20, output_page_rows=8192, ctx=None, device_output=False, input_processor=None):
         self.ctx = ctx or default_context()
         self.step = step
         self.aggregators = list(aggregators)
@@ -44,6 +44,10 @@ class HashAggregationOperator:
             specs[i].kind, specs[i].in_type, specs[i].input_channel, specs[i].mask_channel = a.kind, a.in_type, a.input_channel, a.mask_channel
         N.check(self.ctx.handle, N.lib().pg_hashagg_create(self.ctx.handle, kc, kt, len(group_by_types), self.hash_channel, specs,
                                                            len(self.aggregators), step, expected_groups, C.byref(self._h)))
+        # ScanFilterAndProject fused in front: add_input then takes the processor's INPUT pages and the channels above index its projections
+        self.input_processor = input_processor
+        if input_processor is not None:
+            N.check(self.ctx.handle, N.lib().pg_hashagg_set_input_processor(self._h, input_processor.handle))
         self._finishing = False
         self._finished = False
         self._next_group = 0

@@ -45,9 +45,11 @@ class PartialFinalAggregation:
 
     FINAL_WORKERS = 2
 
-    def __init__(self, group_by_types, group_by_channels, aggregators, ctx, dist=None, expected_groups=100_000, reserve_sms=8):
+    def __init__(self, group_by_types, group_by_channels, aggregators, ctx, dist=None, expected_groups=100_000, reserve_sms=8,
+                 input_processor=None):
         import torch
         self.torch, self.dist, self.ctx = torch, dist, ctx
+        self.input_processor = input_processor      # fused ScanFilterAndProject in front of the first stage (PageProcessor)
         self.types, self.channels, self.aggs = list(group_by_types), list(group_by_channels), list(aggregators)
         self.expected = expected_groups
         self.world = dist.get_world_size() if dist is not None else 1
@@ -80,7 +82,8 @@ class PartialFinalAggregation:
     # ---- stage 1 (calling thread)
     def submit(self, page):
         step = SINGLE if self.world == 1 else PARTIAL
-        op = HashAggregationOperator(self.types, self.channels, step, self.aggs, expected_groups=self.expected, ctx=self.ctx)
+        op = HashAggregationOperator(self.types, self.channels, step, self.aggs, expected_groups=self.expected, ctx=self.ctx,
+                                     input_processor=self.input_processor)
         op.add_input(page)
         op.finish()
         if self.world == 1:

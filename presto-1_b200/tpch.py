@@ -138,6 +138,45 @@ def q1_page(cols):
 Q1_BYTES_PER_ROW = 2 * (1 + 4) + 8 + 8 + 8 + 16 + 16 + 1   # = 67, SURVEY.md §8d "materialised inputs"
 
 
+def q1_raw_page(cols):
+    """The page Q1's table scan delivers: [returnflag, linestatus, quantity, extendedprice, discount, tax, shipdate] — raw lineitem
+    columns only; the filter and the derived decimals are expressions (q1_processor)."""
+    n = cols["rows"]
+    off = cols["offsets1"]
+    return Page(
+        Block(N.VARCHAR, cols["returnflag"], None, off, n),
+        Block(N.VARCHAR, cols["linestatus"], None, off, n),
+        Block(N.SHORT_DECIMAL, cols["quantity"], None, None, n, 12, 2),
+        Block(N.SHORT_DECIMAL, cols["extendedprice"], None, None, n, 12, 2),
+        Block(N.SHORT_DECIMAL, cols["discount"], None, None, n, 12, 2),
+        Block(N.SHORT_DECIMAL, cols["tax"], None, None, n, 12, 2),
+        Block(N.DATE, cols["shipdate"], None, None, n),
+        position_count=n)
+
+
+# what the fused kernel reads per row: two varchar(1) keys (byte + offset), four 8-byte decimals, the 4-byte ship date
+Q1_RAW_BYTES_PER_ROW = 2 * (1 + 4) + 4 * 8 + 4              # = 46 (SURVEY.md §8d "fused derive": 43 with a 1-byte mask instead of the date)
+
+
+def q1_expressions():
+    """(filter, projections) of TPC-H Q1 over q1_raw_page: shipdate <= DATE '1998-09-02';
+    [returnflag, linestatus, quantity, extendedprice, extendedprice*(1-discount), extendedprice*(1-discount)*(1+tax), discount]."""
+    from .expressions import Expr as E
+    qty, price = E.input(2, N.SHORT_DECIMAL, 12, 2), E.input(3, N.SHORT_DECIMAL, 12, 2)
+    disc, tax = E.input(4, N.SHORT_DECIMAL, 12, 2), E.input(5, N.SHORT_DECIMAL, 12, 2)
+    one = E.decimal(1, 1, 0)
+    disc_price = price * (one - disc)            # decimal(25,4)
+    charge = disc_price * (one + tax)            # decimal(38,6)
+    return E.input(6, N.DATE) <= E.date(Q1_CUTOFF), [E.input(0, N.VARCHAR), E.input(1, N.VARCHAR), qty, price, disc_price, charge, disc]
+
+
+def q1_fused_aggregators():
+    """sum(qty), sum(price), sum(disc_price), sum(charge), avg(qty), avg(price), avg(disc), count(*) over q1_expressions' projections."""
+    from .operators import AggregatorFactory as A
+    return [A(N.AGG_SUM, N.SHORT_DECIMAL, 2), A(N.AGG_SUM, N.SHORT_DECIMAL, 3), A(N.AGG_SUM, N.LONG_DECIMAL, 4), A(N.AGG_SUM, N.LONG_DECIMAL, 5),
+            A(N.AGG_AVG, N.SHORT_DECIMAL, 2), A(N.AGG_AVG, N.SHORT_DECIMAL, 3), A(N.AGG_AVG, N.SHORT_DECIMAL, 6), A(N.AGG_COUNT)]
+
+
 def q1_aggregators():
     """sum(qty), sum(price), sum(disc_price), sum(charge), avg(qty), avg(price), avg(disc), count(*) — all masked by the filter."""
     from .operators import AggregatorFactory as A

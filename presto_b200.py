@@ -7,7 +7,7 @@ _root = os.path.dirname(os.path.abspath(__file__))
 if _root not in sys.path:
     sys.path.insert(0, _root)
 _pkg = importlib.import_module("presto-1_b200")
-for _name in ("operators", "exchange", "tpch", "plans"):
+for _name in ("operators", "exchange", "tpch", "plans", "expressions"):
     try:
         importlib.import_module("presto-1_b200." + _name)
     except ModuleNotFoundError:

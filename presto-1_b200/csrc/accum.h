@@ -15,6 +15,7 @@
 #include "context.h"
 
 struct pg_project;
+struct pg_groupby;
 
 namespace pg {
 
@@ -98,8 +99,24 @@ struct LowcardExprs {
     int arg_proj[MAX_AGGS];       // projection read by aggregate i (-1: count(*))
     int mask_proj[MAX_AGGS];      // projection used as its mask (-1: none)
 };
-bool accumulate_lowcard_jit(pg_ctx* ctx, const AggProgram& prog, int64_t n, int64_t group_count, const FusedLookup& fused,
-                            const LowcardExprs* px = nullptr);
+// The groups the kernel resolves keys against: packed keys in id order, 4 words per group {w0, w1, first row, packable}.
+// known_count > 0: that many groups are known (device table `known`).  known_count == 0: the kernel discovers the groups itself
+// from the first discover_rows rows, in the reference's first-seen order, and publishes them in discovered_out (64 entries);
+// d_miss[2] / d_miss[3] then carry the group count and the verdict (jit/lowcard_args.h PGJ_DISC_*; non-zero = nothing accumulated).
+struct LowcardGroups {
+    const unsigned long long* known;
+    int known_count;
+    unsigned long long* discovered_out;
+    int64_t discover_rows;
+    int capacity_hint;            // discovering launch: groups to make room for at least (0: default)
+};
+// fused.d_miss must be four words {misses, error bits, groups discovered, discovery verdict}, zeroed by the caller.
+bool accumulate_lowcard_jit(pg_ctx* ctx, const AggProgram& prog, int64_t n, const FusedLookup& fused, const LowcardGroups& groups,
+                            const LowcardExprs* px = nullptr, int* gcap_used = nullptr);
+// packed-key group tables (jit_lowcard.cu): from the GroupByHash's stored keys, and back into key columns
+struct LowcardKeyOut { void* values[8]; uint8_t* nulls[8]; int32_t* offsets[8]; };
+void lowcard_pack_groups(pg_ctx* ctx, const pg_groupby* gb, int64_t groups, unsigned long long* d_out);
+void lowcard_unpack_groups(pg_ctx* ctx, const KeyLayout& L, const unsigned long long* d_groups, int64_t first, int64_t n, const LowcardKeyOut& out);
 
 }  // namespace pg
 

@@ -10,6 +10,7 @@
 #include "hashagg_wide.h"
 #include "jit.h"
 #include "project.h"
+#include "jit/lowcard_args.h"
 
 struct pg_hashagg {
     pg_ctx* ctx = nullptr;
@@ -24,6 +25,9 @@ struct pg_hashagg {
     pg::DevBuf ids;
     int64_t input_rows = 0;
     pg_project* proc = nullptr;      // fused filter + projections in front of the aggregation (pg_hashagg_set_input_processor); not owned
+    // few groups: the groups as packed keys in id order (jit/lowcard_args.h: 4 words each).  While gb_current is false the groups
+    // exist only here (discovered by the specialised kernel) and the GroupByHash is brought up to date on demand (hashagg_sync_gb).
+    struct { pg::DevBuf groups; int64_t count = 0; bool gb_current = true; } lc;
     pg::WideTable* wide = nullptr;   // many-groups path (hashagg_wide.h), chosen on the first page
     int64_t rows_since_reset = 0;    // first-seen order of the wide path is kept by operator-wide row numbers
     ~pg_hashagg() {
@@ -64,6 +68,106 @@ void hashagg_build(pg_hashagg* op) {
 }
 
 static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n);
+
+static int64_t hashagg_group_count(const pg_hashagg* op) { return op->lc.gb_current ? op->gb->groups : op->lc.count; }
+
+// key columns of the packed groups [first, first + n) in fresh device buffers
+struct UnpackedKeys { KeyCols kc; std::vector<DevBuf> bufs; };
+static void lowcard_unpack_to_cols(pg_hashagg* op, int64_t first, int64_t n, UnpackedKeys& u) {
+    pg_ctx* ctx = op->ctx;
+    const KeyLayout& L = op->gb->layout;
+    memset(&u.kc, 0, sizeof(u.kc));
+    LowcardKeyOut out;
+    memset(&out, 0, sizeof(out));
+    u.bufs.reserve(3 * L.nkeys);
+    for (int k = 0; k < L.nkeys; k++) {
+        const bool var = type_is_var(L.types[k]);
+        u.bufs.emplace_back(ctx, var ? 3 * n + 8 : n * (int64_t)type_width(L.types[k]) + 8);
+        out.values[k] = u.bufs.back().p;
+        u.bufs.emplace_back(ctx, n + 8);
+        out.nulls[k] = (uint8_t*)u.bufs.back().p;
+        u.bufs.emplace_back(ctx, (n + 1) * 4 + 8);
+        out.offsets[k] = (int32_t*)u.bufs.back().p;
+        DCol& c = u.kc.c[k];
+        c.type = L.types[k]; c.values = out.values[k]; c.nulls = out.nulls[k]; c.offsets = var ? out.offsets[k] : nullptr;
+    }
+    lowcard_unpack_groups(ctx, L, op->lc.groups.as<unsigned long long>(), first, n, out);
+}
+
+// the GroupByHash learns the groups the specialised kernel discovered (same ids: they are inserted in id order)
+static void hashagg_sync_gb(pg_hashagg* op) {
+    if (op->lc.gb_current) return;
+    op->lc.gb_current = true;
+    if (op->lc.count == 0) return;
+    PG_CHECK_STATE(op->gb->groups == 0, "group tables out of step");
+    UnpackedKeys u;
+    lowcard_unpack_to_cols(op, 0, op->lc.count, u);
+    groupby_process(op->gb, u.kc, nullptr, op->lc.count, nullptr);
+    PG_CHECK_STATE(op->gb->groups == op->lc.count, "the GroupByHash numbered %lld groups, the kernel %lld", (long long)op->gb->groups, (long long)op->lc.count);
+}
+
+// The few-groups fast path: one specialised kernel over all rows of the page (jit_lowcard.cu).  Groups: the operator's known
+// ones, or — first page — discovered by the kernel itself in first-seen order; rows with a key the kernel does not know are
+// handed to on_misses(bitmap) after the GroupByHash has been brought up to date.  Returns false when the plan does not fit or
+// the discovery gave up; nothing has been accumulated then.
+template <typename MissFn>
+static bool hashagg_lowcard(pg_hashagg* op, const KeyCols& kc, ColImport** kimp, int nk, const AggProgram& prog, const LowcardExprs* px, int64_t n,
+                            MissFn&& on_misses) {
+    pg_ctx* ctx = op->ctx;
+    if (!jit_available()) return false;
+    const int64_t known = hashagg_group_count(op);
+    if (known > 64) return false;
+    const bool discover = known == 0;
+    if (discover) {
+        // the packed form must reproduce the stored key exactly (doubles are normalised in it) and there is no raw hash to keep
+        if (op->hash_channel >= 0) return false;
+        for (int t : op->key_types) if (t == PG_DOUBLE) return false;
+        if (const char* e = getenv("PRESTOGPU_LOWCARD_DISCOVER")) if (e[0] == '0') return false;
+    }
+    if (!op->lc.groups.p) op->lc.groups.alloc(ctx, 64 * 4 * 8);
+    if (!discover && op->lc.gb_current && op->lc.count != op->gb->groups) {      // the GroupByHash has grown since the table was packed
+        lowcard_pack_groups(ctx, op->gb, op->gb->groups, op->lc.groups.as<unsigned long long>());
+        op->lc.count = op->gb->groups;
+    }
+    for (pg_agg* a : op->aggs) agg_ensure_capacity(a, discover ? 64 : known);
+    const int64_t miss_words = (n + 31) / 32;
+    DevBuf miss_flag(ctx, 32 + miss_words * 4);            // [misses][error bits][groups discovered][discovery verdict][bitmap]
+    memset_async(ctx, miss_flag.p, 0, 32 + miss_words * 4);
+    unsigned long long* d_miss = miss_flag.as<unsigned long long>();
+    unsigned int* d_miss_bits = (unsigned int*)(d_miss + 4);
+    FusedLookup fl;
+    memset(&fl, 0, sizeof(fl));
+    fl.layout = &op->gb->layout; fl.keys = &kc; fl.miss_flag = d_miss_bits; fl.d_miss = d_miss; fl.row_base = 0;
+    for (int k = 0; k < nk && k < 8; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;     // -1: the kernel reads offsets[n]
+    LowcardGroups lg;
+    lg.known = discover ? nullptr : op->lc.groups.as<unsigned long long>();
+    lg.known_count = discover ? 0 : (int)known;
+    lg.discovered_out = op->lc.groups.as<unsigned long long>();
+    lg.discover_rows = 8192;
+    lg.capacity_hint = ctx->jit ? ctx->jit->lowcard_groups_hint : 0;
+    if (!accumulate_lowcard_jit(ctx, prog, n, fl, lg, px)) return false;
+    int64_t res[4];
+    read_scalars(ctx, d_miss, 4, res);
+    if (discover) {
+        const int64_t found = res[2], verdict = res[3];
+        if (ctx->jit && found > 0 && found <= 64) ctx->jit->lowcard_groups_hint = (int)found;
+        if (verdict == PGJ_DISC_TOO_MANY && found <= 64) {
+            // the table the kernel published is complete: come back with the groups known (block shape chosen for them)
+            memset_async(ctx, miss_flag.p, 0, 32);
+            lg.known = op->lc.groups.as<unsigned long long>(); lg.known_count = (int)found;
+            if (!accumulate_lowcard_jit(ctx, prog, n, fl, lg, px)) return false;
+            read_scalars(ctx, d_miss, 4, res);
+        } else if (verdict != 0 || found == 0) return false;
+        op->lc.count = found;
+        op->lc.gb_current = false;
+    }
+    if (res[1] & 1) fail(PG_E_NUMERIC_OVERFLOW, "Decimal overflow / numeric value out of range in a filter or projection expression");
+    if (res[0] > 0) {
+        hashagg_sync_gb(op);
+        on_misses(d_miss_bits);
+    }
+    return true;
+}
 
 // channels of the operator's logical input page (= the processor's projections) that the operator reads
 static std::vector<char> channels_read(const pg_hashagg* op, int np) {
@@ -136,7 +240,26 @@ static bool hashagg_try_fused_processor(pg_hashagg* op, const DCol* in, ColImpor
         px.mask_proj[i] = s.mask_channel;
         if (px.arg_proj[i] >= np || px.mask_proj[i] >= np) return false;
     }
-    {   // 1. the prefix numbers the groups
+    AggProgram prog;
+    memset(&prog, 0, sizeof(prog));
+    prog.naggs = (int32_t)op->aggs.size();
+    // state arrays move when they grow: the program is built after the capacity is final (64 groups while discovering)
+    auto fill_prog = [&] {
+        const int64_t g = hashagg_group_count(op);
+        for (pg_agg* a : op->aggs) agg_ensure_capacity(a, g > 0 ? g : 64);
+        for (size_t i = 0; i < op->aggs.size(); i++) prog.ops[i] = agg_make_op(op->aggs[i], nullptr, nullptr);
+    };
+    auto on_misses = [&](const unsigned int* bits) {
+        const int64_t rows = op->rows_since_reset;
+        hashagg_add_projected(op, in, ncols, n, bits);
+        op->rows_since_reset = rows;
+    };
+    fill_prog();
+    if (hashagg_lowcard(op, kc, kimp, nk, prog, &px, n, on_misses)) { op->rows_since_reset += n; return true; }
+    if (hashagg_group_count(op) > 0) return false;
+    // The kernel's own discovery gave up (e.g. a long string among the keys): number the groups of a projected prefix through the
+    // GroupByHash, as the plain operator does, and try once more with them known.
+    {
         std::vector<char> want(np, 0);
         for (int k = 0; k < nk; k++) want[op->key_channels[k]] = 1;
         ProjectedPage pp;
@@ -150,40 +273,8 @@ static bool hashagg_try_fused_processor(pg_hashagg* op, const DCol* in, ColImpor
     }
     const int64_t groups = op->gb->groups;
     if (groups < 1 || groups > 64) return false;
-    for (pg_agg* a : op->aggs) agg_ensure_capacity(a, groups);
-    // 2. every row of the page through the specialised kernel
-    const int64_t miss_words = (n + 31) / 32;
-    DevBuf miss_flag(ctx, 16 + miss_words * 4);
-    memset_async(ctx, miss_flag.p, 0, 16 + miss_words * 4);
-    unsigned long long* d_miss_cnt = miss_flag.as<unsigned long long>();
-    unsigned int* d_miss_bits = (unsigned int*)(d_miss_cnt + 2);
-    FusedLookup fl;
-    memset(&fl, 0, sizeof(fl));
-    fl.layout = &op->gb->layout; fl.keys = &kc; fl.key_rows = op->gb->key_rows.as<uint64_t>(); fl.arena = op->gb->arena.as<uint8_t>();
-    fl.values_by_group = op->gb->values_by_group.as<int64_t>(); fl.bigint_mode = op->gb->bigint_mode ? 1 : 0;
-    fl.null_gid = -1;
-    if (op->gb->bigint_mode) {
-        int64_t sp[2];
-        read_scalars(ctx, op->gb->slots.as<Slot>() + op->gb->cap + 1, 2, sp);
-        fl.null_gid = (int32_t)(sp[1] & 0xffffffff);
-    }
-    fl.miss_flag = d_miss_bits; fl.d_miss = d_miss_cnt; fl.row_base = 0;
-    resolve_value_bytes(ctx, kimp, nk);
-    for (int k = 0; k < nk && k < 8; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
-    AggProgram prog;
-    memset(&prog, 0, sizeof(prog));
-    prog.naggs = (int32_t)op->aggs.size();
-    for (size_t i = 0; i < op->aggs.size(); i++) prog.ops[i] = agg_make_op(op->aggs[i], nullptr, nullptr);
-    if (!accumulate_lowcard_jit(ctx, prog, n, groups, fl, &px)) return false;
-    // 3. what the kernel left over
-    int64_t res[2];
-    read_scalars(ctx, d_miss_cnt, 2, res);
-    if (res[1] & 1) fail(PG_E_NUMERIC_OVERFLOW, "Decimal overflow / numeric value out of range in a filter or projection expression");
-    if (res[0] > 0) {
-        const int64_t rows = op->rows_since_reset;
-        hashagg_add_projected(op, in, ncols, n, d_miss_bits);
-        op->rows_since_reset = rows;
-    }
+    fill_prog();
+    if (!hashagg_lowcard(op, kc, kimp, nk, prog, &px, n, on_misses)) return false;
     op->rows_since_reset += n;
     return true;
 }
@@ -272,7 +363,7 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         const char* wide_env = getenv("PRESTOGPU_WIDE");
         const bool wide_on = wide_env ? wide_env[0] != '0' : true;
         const bool wide_always = wide_env && wide_env[0] == '1';
-        if (wide_on && !op->wide && op->rows_since_reset == 0 && op->gb->groups == 0 && n >= 256 * 1024 && wide_supported(op->specs, op->aggs) &&
+        if (wide_on && !op->wide && op->rows_since_reset == 0 && hashagg_group_count(op) == 0 && n >= 256 * 1024 && wide_supported(op->specs, op->aggs) &&
             jit_available()) {
             int64_t repeats = 0;
             KeySample ks;
@@ -313,65 +404,69 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         ColImport* kimp[MAX_KEYS];
         int nkimp = 0;
         for (size_t k = 0; k < op->key_channels.size() && k < (size_t)MAX_KEYS; k++) kimp[nkimp++] = &imp[op->key_channels[k]];
-        if (op->gb->has_var) {   // one read-back gives the value bytes of the page and of the prefix (the store's growth bound)
-            int64_t pb[MAX_KEYS], bound = 0;
-            resolve_value_bytes(ctx, kimp, nkimp, PREFIX, pb);
-            for (int k = 0; k < nkimp; k++) bound += pb[k];
-            op->gb->var_bound_hint = bound;
-        }
-        generic_rows(0, PREFIX, nullptr, false);   // numbers the prefix's groups; its rows are accumulated below
-        op->gb->var_bound_hint = -1;
-        const int64_t groups = op->gb->groups;
-        bool prefix_done = false;
-        auto accumulate_prefix = [&] {   // general path for the prefix rows (their ids are still in op->ids)
-            if (!prefix_done) accumulate(ctx, build_prog(0), op->ids.as<int32_t>(), PREFIX, groups);
-            prefix_done = true;
+        auto on_misses = [&](const unsigned int* bits) {     // rows the kernel could not resolve take the general path, in page order
+            DevBuf only(ctx, n);
+            PG_LAUNCH(ctx, expand_bits_kernel, grid_for(ctx, n, 256, 4), 256, 0, bits, n, only.as<uint8_t>());
+            generic_rows(0, n, only.as<uint8_t>());
         };
-        if (groups <= 64) {
-            const int64_t miss_words = (n + 31) / 32;
-            DevBuf miss_flag(ctx, 16 + miss_words * 4);         // [miss count (8 bytes)][error bits (8)][bitmap of rows left to the general path]
-            memset_async(ctx, miss_flag.p, 0, 16 + miss_words * 4);
-            unsigned long long* d_miss_cnt = miss_flag.as<unsigned long long>();
-            unsigned int* d_miss_bits = (unsigned int*)(d_miss_cnt + 2);
-            KeyCols kco;
-            FusedLookup fl;
-            fl.layout = &op->gb->layout; fl.keys = &kco; fl.key_rows = op->gb->key_rows.as<uint64_t>(); fl.arena = op->gb->arena.as<uint8_t>();
-            fl.values_by_group = op->gb->values_by_group.as<int64_t>(); fl.bigint_mode = op->gb->bigint_mode ? 1 : 0;
-            fl.null_gid = -1;
-            if (op->gb->bigint_mode) {
-                int64_t sp[2];
-                read_scalars(ctx, op->gb->slots.as<Slot>() + op->gb->cap + 1, 2, sp);   // the null group's slot {word, gid|first_row}
-                fl.null_gid = (int32_t)(sp[1] & 0xffffffff);
+        auto lowcard = [&]() -> bool {
+            const int64_t g = hashagg_group_count(op);
+            for (pg_agg* a : op->aggs) agg_ensure_capacity(a, g > 0 ? g : 64);      // final before the program takes the state pointers
+            return hashagg_lowcard(op, kc, kimp, nkimp, build_prog(0), nullptr, n, on_misses);
+        };
+        // first choice: the kernel specialised at run time for this plan over ALL rows of the page; it finds the groups of a first
+        // page itself.  When that does not apply (hash channel, double keys, a long string in the sample, ...): number the groups of a
+        // short prefix through the GroupByHash and come back with them known; failing that, the ahead-of-time fused kernel.
+        fused_done = lowcard();
+        if (!fused_done) {
+            hashagg_sync_gb(op);
+            if (op->gb->has_var) {   // one read-back gives the value bytes of the page and of the prefix (the store's growth bound)
+                int64_t pb[MAX_KEYS], bound = 0;
+                resolve_value_bytes(ctx, kimp, nkimp, PREFIX, pb);
+                for (int k = 0; k < nkimp; k++) bound += pb[k];
+                op->gb->var_bound_hint = bound;
             }
-            fl.miss_flag = d_miss_bits; fl.d_miss = d_miss_cnt;
-            resolve_value_bytes(ctx, kimp, nkimp);
-            for (int k = 0; k < nkimp && k < 8; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
-            auto rows_from = [&](int64_t off) {
-                kco = kc;
-                for (size_t k = 0; k < op->key_channels.size(); k++) kco.c[k] = dcol_offset(kc.c[k], off);
-                fl.row_base = off;
-            };
-            auto leftovers = [&](int64_t off, int64_t m) {   // rows the fused kernel could not resolve take the general path
-                int64_t misses;
-                read_scalars(ctx, d_miss_cnt, 1, &misses);
-                if (misses > 0) {
-                    DevBuf only(ctx, m);
-                    PG_LAUNCH(ctx, expand_bits_kernel, grid_for(ctx, m, 256, 4), 256, 0, d_miss_bits, m, only.as<uint8_t>());
-                    generic_rows(off, m, only.as<uint8_t>());
+            generic_rows(0, PREFIX, nullptr, false);   // numbers the prefix's groups; its rows are accumulated below
+            op->gb->var_bound_hint = -1;
+            const int64_t groups = op->gb->groups;
+            if (groups <= 64) fused_done = lowcard();
+            if (!fused_done) {
+                accumulate(ctx, build_prog(0), op->ids.as<int32_t>(), PREFIX, groups);      // the prefix by its ids
+                if (groups <= 64) {
+                    const int64_t m = n - PREFIX, miss_words = (m + 31) / 32;
+                    DevBuf miss_flag(ctx, 8 + miss_words * 4);
+                    memset_async(ctx, miss_flag.p, 0, 8 + miss_words * 4);
+                    unsigned long long* d_miss_cnt = miss_flag.as<unsigned long long>();
+                    unsigned int* d_miss_bits = (unsigned int*)(d_miss_cnt + 1);
+                    KeyCols kco = kc;
+                    for (size_t k = 0; k < op->key_channels.size(); k++) kco.c[k] = dcol_offset(kc.c[k], PREFIX);
+                    FusedLookup fl;
+                    memset(&fl, 0, sizeof(fl));
+                    fl.layout = &op->gb->layout; fl.keys = &kco; fl.key_rows = op->gb->key_rows.as<uint64_t>(); fl.arena = op->gb->arena.as<uint8_t>();
+                    fl.values_by_group = op->gb->values_by_group.as<int64_t>(); fl.bigint_mode = op->gb->bigint_mode ? 1 : 0;
+                    fl.null_gid = -1;
+                    if (op->gb->bigint_mode) {
+                        int64_t sp[2];
+                        read_scalars(ctx, op->gb->slots.as<Slot>() + op->gb->cap + 1, 2, sp);   // the null group's slot {word, gid|first_row}
+                        fl.null_gid = (int32_t)(sp[1] & 0xffffffff);
+                    }
+                    fl.miss_flag = d_miss_bits; fl.d_miss = d_miss_cnt; fl.row_base = PREFIX;
+                    resolve_value_bytes(ctx, kimp, nkimp);
+                    for (int k = 0; k < nkimp && k < 8; k++) fl.key_value_bytes[k] = kimp[k]->value_bytes;
+                    if (accumulate_private(ctx, build_prog(PREFIX), nullptr, m, groups, nullptr, &fl)) {
+                        int64_t misses;
+                        read_scalars(ctx, d_miss_cnt, 1, &misses);
+                        if (misses > 0) {
+                            DevBuf only(ctx, m);
+                            PG_LAUNCH(ctx, expand_bits_kernel, grid_for(ctx, m, 256, 4), 256, 0, d_miss_bits, m, only.as<uint8_t>());
+                            generic_rows(PREFIX, m, only.as<uint8_t>());
+                        }
+                        fused_done = true;
+                    }
                 }
-                fused_done = true;
-            };
-            // first choice: the kernel specialised at run time for this plan, over ALL rows of the page (the prefix rows
-            // resolve by construction); otherwise the prefix by ids and the rest by the generic ahead-of-time fused kernel
-            rows_from(0);
-            if (accumulate_lowcard_jit(ctx, build_prog(0), n, groups, fl)) leftovers(0, n);
-            else {
-                accumulate_prefix();
-                rows_from(PREFIX);
-                if (accumulate_private(ctx, build_prog(PREFIX), nullptr, n - PREFIX, groups, nullptr, &fl)) leftovers(PREFIX, n - PREFIX);
+                if (!fused_done) { generic_rows(PREFIX, n - PREFIX, nullptr); fused_done = true; }
             }
         }
-        if (!fused_done) { accumulate_prefix(); generic_rows(PREFIX, n - PREFIX, nullptr); fused_done = true; }
     }
     op->rows_since_reset += n;
     if (fused_done) {
@@ -379,6 +474,7 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         sync(ctx);
         return;
     }
+    hashagg_sync_gb(op);
     op->ids.grow(ctx, n * 4, 0);
     groupby_process(op->gb, kc, has_hash ? &hc : nullptr, n, op->ids.as<int32_t>());
     int64_t groups = op->gb->groups;
@@ -445,7 +541,10 @@ int32_t pg_hashagg_stats(pg_hashagg* op, int64_t* group_count, int64_t* capacity
         op->gb->groups = op->wide->groups();
         while (op->gb->groups >= max_fill_075(op->gb->ref_capacity) && op->gb->ref_capacity < (1LL << 30)) op->gb->ref_capacity *= 2;
     }
-    if (group_count) *group_count = op->gb->groups;
+    if (!op->lc.gb_current) {   // groups known to the few-groups kernel only: same count, same logical capacity schedule
+        while (op->lc.count >= max_fill_075(op->gb->ref_capacity) && op->gb->ref_capacity < (1LL << 30)) op->gb->ref_capacity *= 2;
+    }
+    if (group_count) *group_count = hashagg_group_count(op);
     if (capacity) *capacity = op->gb->ref_capacity;
     if (device_bytes) {
         int64_t b = groupby_device_bytes(op->gb) + op->ids.bytes + (op->wide ? op->wide->device_bytes() : 0);
@@ -503,18 +602,37 @@ int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_o
     return guard(op->ctx, [&] {
         pg_ctx* ctx = op->ctx;
         if (op->wide) wide_prepare_output(op->wide, op->gb, op->aggs, op->rows_since_reset);
-        PG_CHECK_ARG(out && first >= 0 && n >= 0 && first + n <= op->gb->groups, "group range outside [0, %lld)", (long long)op->gb->groups);
+        const int64_t total = hashagg_group_count(op);
+        PG_CHECK_ARG(out && first >= 0 && n >= 0 && first + n <= total, "group range outside [0, %lld)", (long long)total);
         if (error_group) *error_group = -1;
         if (n == 0) return;
         int nk = (int)op->key_types.size();
         bool has_hash = op->hash_channel >= 0;
-        int64_t* hash_ptr = nullptr; int32_t hash_mem = PG_MEM_DEVICE;
-        if (has_hash) {
-            PG_CHECK_ARG(out[nk].type == PG_BIGINT && out[nk].capacity >= n, "hash output column must be BIGINT with capacity");
-            hash_ptr = (int64_t*)out[nk].values; hash_mem = out[nk].mem;
+        std::vector<OutStage> kst;
+        if (!op->lc.gb_current && n <= 64) {
+            // the groups live in the packed table only: unpack the keys straight into the output columns
+            const KeyLayout& L = op->gb->layout;
+            kst.resize(nk);
+            LowcardKeyOut ko;
+            memset(&ko, 0, sizeof(ko));
+            for (int k = 0; k < nk; k++) {
+                PG_CHECK_ARG(out[k].type == L.types[k], "key output column %d has type %d, expected %d", k, out[k].type, L.types[k]);
+                const bool var = type_is_var(L.types[k]);
+                kst[k].begin(ctx, &out[k], n, var ? 3 * n : n * (int64_t)type_width(L.types[k]));
+                ko.values[k] = kst[k].d_values; ko.nulls[k] = kst[k].d_nulls; ko.offsets[k] = kst[k].d_offsets;
+            }
+            lowcard_unpack_groups(ctx, L, op->lc.groups.as<unsigned long long>(), first, n, ko);
+            for (int k = 0; k < nk; k++) kst[k].finish(type_is_var(L.types[k]) ? 3 * n : n * (int64_t)type_width(L.types[k]));
+        } else {
+            hashagg_sync_gb(op);
+            int64_t* hash_ptr = nullptr; int32_t hash_mem = PG_MEM_DEVICE;
+            if (has_hash) {
+                PG_CHECK_ARG(out[nk].type == PG_BIGINT && out[nk].capacity >= n, "hash output column must be BIGINT with capacity");
+                hash_ptr = (int64_t*)out[nk].values; hash_mem = out[nk].mem;
+            }
+            int32_t rc = pg_groupby_export_keys(op->gb, first, n, out, hash_ptr, hash_mem);
+            if (rc != PG_OK) fail(rc, "%s", ctx->err.c_str());
         }
-        int32_t rc = pg_groupby_export_keys(op->gb, first, n, out, hash_ptr, hash_mem);
-        if (rc != PG_OK) fail(rc, "%s", ctx->err.c_str());
         if (has_hash && out[nk].nulls) {
             if (out[nk].mem == PG_MEM_DEVICE) memset_async(ctx, out[nk].nulls, 0, n); else memset(out[nk].nulls, 0, n);
         }
@@ -541,8 +659,9 @@ int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_o
 int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* out_bytes) {
     if (!op || !out_bytes) return PG_E_INVALID_ARGUMENT;
     int nk = (int)op->key_types.size();
+    if (col < nk && !op->lc.gb_current) { *out_bytes = 3 * op->lc.count; return PG_OK; }     // packed keys: strings of at most 3 bytes
     if (col < nk) return pg_groupby_varwidth_bytes(op->gb, col, out_bytes);
-    *out_bytes = 32 * op->gb->groups;   // decimal intermediate states: at most 32 bytes per group
+    *out_bytes = 32 * hashagg_group_count(op);   // decimal intermediate states: at most 32 bytes per group
     return PG_OK;
 }
 
@@ -684,6 +803,7 @@ int32_t pg_hashagg_reset(pg_hashagg* op) {
         delete op->gb; op->gb = nullptr;
         delete op->wide; op->wide = nullptr;
         op->rows_since_reset = 0;
+        op->lc.count = 0; op->lc.gb_current = true;
         hashagg_build(op);
     });
 }

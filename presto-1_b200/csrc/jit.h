@@ -21,6 +21,7 @@ struct JitKernel {
 struct JitCache {
     std::map<std::string, JitKernel> kernels;
     int64_t compiled = 0, hits = 0, failures = 0;
+    int lowcard_groups_hint = 0;     // groups the last discovering few-groups kernel found (sizes the next one's private tables)
     std::string last_error;
     ~JitCache();
 };

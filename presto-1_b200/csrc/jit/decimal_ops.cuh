@@ -77,11 +77,10 @@ __device__ __forceinline__ Pgx2c pgx2c_from_long(pgx_u64 lo, pgx_u64 hi) {   // 
     if ((pgx_i64)hi < 0) { r.w0 = 0ULL - lo; r.w1 = (pgx_i64)(~(pgx_u64)r.w1 + (lo == 0 ? 1ULL : 0ULL)); }
     return r;
 }
-// short x short: cannot overflow (|a|, |b| < 2^63 gives |product| < 2^126 < 10^38); operands that fit 32 bits take one IMAD.WIDE
+// short x short: cannot overflow (|a|, |b| < 2^63 gives |product| < 2^126 < 10^38).  Branch-free: one signed 64 x 64 -> 128 product.
 __device__ __forceinline__ Pgx2c pgx2c_mul_ss(pgx_i64 a, pgx_i64 b) {
     Pgx2c r;
-    if ((pgx_i64)(int)a == a && (pgx_i64)(int)b == b) { const pgx_i64 p = (pgx_i64)(int)a * (pgx_i64)(int)b; r.w0 = (pgx_u64)p; r.w1 = p >> 63; }
-    else { r.w0 = (pgx_u64)a * (pgx_u64)b; r.w1 = __mul64hi(a, b); }
+    r.w0 = (pgx_u64)a * (pgx_u64)b; r.w1 = __mul64hi(a, b);
     return r;
 }
 // |value| >= 10^38 (or beyond 127 bits, flagged by the caller): the reference's throwIfOverflows

@@ -8,15 +8,20 @@
 #define PGJ_MAX_SLOTS 24
 #define PGJ_MAX_AGGS 16
 #define PGJ_LUT_SIZE 256
+#define PGJ_MAX_GROUPS 64
 
-// slot kinds (private partial state per group and thread)
-#define PGJ_KIND_DEC 0   // 128-bit sign-magnitude input -> 192-bit sum, 3 words
-#define PGJ_KIND_I64 1   // 64-bit input -> 128-bit sum, 2 words
-#define PGJ_KIND_I32 2   // 32-bit input -> 128-bit sum, 2 words
-#define PGJ_KIND_F64 3   // double sum, 1 word
-#define PGJ_KIND_MIN 4   // 1 word
-#define PGJ_KIND_MAX 5   // 1 word
-#define PGJ_KIND_CNT 6   // 1 word
+// slot kinds (private partial state per group and thread, one 64-bit word each)
+#define PGJ_KIND_SUM 0   // exact integer / decimal sum: narrow private word + the block's 192-bit accumulator for everything else
+#define PGJ_KIND_F64 3   // double sum
+#define PGJ_KIND_MIN 4
+#define PGJ_KIND_MAX 5
+#define PGJ_KIND_CNT 6
+
+// discovery verdict bits (d_miss[3])
+#define PGJ_DISC_TOO_MANY 1      // more groups than the private tables were sized for (d_miss[2] says how many)
+#define PGJ_DISC_UNPACKABLE 2    // a key of the sampled prefix does not fit the packed form
+#define PGJ_DISC_TABLE_FULL 4
+#define PGJ_DISC_COLLISION 8     // two different keys share a fingerprint
 
 struct PgjArgs {
     const void* key_values[PGJ_MAX_KEYS];
@@ -31,17 +36,20 @@ struct PgjArgs {
     int agg_op[PGJ_MAX_AGGS];        // OpClass
     int agg_words[PGJ_MAX_AGGS];     // words per group of the global state
     int agg_cnt_word[PGJ_MAX_AGGS];  // private word holding the aggregate's row count
-    int agg_val_word[PGJ_MAX_AGGS];  // first private word of its value (-1: count only)
+    int agg_val_word[PGJ_MAX_AGGS];  // private word of its value (-1: count only)
     int agg_val_kind[PGJ_MAX_AGGS];  // PGJ_KIND_*
-    // stored groups (GroupByHash key store) for the shared-memory key -> group id table
-    const unsigned long long* key_rows;
-    const unsigned char* arena;
-    const long long* values_by_group;
+    int agg_wide_idx[PGJ_MAX_AGGS];  // SUM: index of its slot among the SUM slots (the block's wide accumulators)
+    // groups: packed keys in id order, 4 words each {w0, w1, first row, packable}; known_groups == 0: discover them from the first
+    // discover_rows rows and publish them in lc_groups_out
+    const unsigned long long* lc_groups;
+    unsigned long long* lc_groups_out;
     unsigned int* miss_flag;         // bitmap: bit set for rows whose key is not in the table (zeroed by the caller)
-    unsigned long long* d_miss;      // [0] number of such rows, [1] error bits (1 = arithmetic overflow in a fused expression)
+    unsigned long long* d_miss;      // [0] number of such rows, [1] error bits (1 = arithmetic overflow in a fused expression),
+                                     // [2] groups discovered, [3] discovery verdict (PGJ_DISC_*; non-zero: nothing was accumulated)
     long long n;
     long long row_base;              // page row of row 0 (variable width offsets are absolute within the page)
-    int naggs, G, bigint_mode, null_gid, row_words, pad;
+    long long discover_rows;
+    int naggs, G, known_groups, fast_bits;
 };
 
 #endif

@@ -1,22 +1,36 @@
 // lowcard_body.cuh — body of the run-time specialised fused GROUP BY kernel for few groups ("hash-then-update with
-// shared-memory pre-aggregation").  NVRTC compiles  <generated prelude> + lowcard_args.h + this file  once per plan shape,
-// the way the reference generates one accumulator class per aggregation (AccumulatorCompiler.java:261-330).
+// shared-memory pre-aggregation").  NVRTC compiles  <generated prelude> + decimal_ops.cuh + lowcard_args.h + this file  once per
+// plan shape, the way the reference generates one accumulator class per aggregation (AccumulatorCompiler.java:261-330).
 //
 // The prelude defines
 //   PG_T            threads per block            PG_VEC       consecutive rows per thread and trip (1, 2 or 4)
 //   PG_REC_WORDS    u64 words per group/thread   PG_MIN_BLOCKS  __launch_bounds__ second argument
-//   PG_PREFETCH     trips ahead whose rows are prefetched into L2 (0 = off)
+//   PG_NSUMS        number of SUM slots          PG_PREFETCH  trips ahead whose rows are prefetched into L2 (0 = off)
+//   PG_FAST_BITS    magnitude bound (bits) of addends the private sums take
 //   PG_KEYS(X)      X(k, CLASS, WORD, SHIFT, HASNULL, WOFF)   CLASS in {K64, KDBL, K32, K8, KVAR}
 //   PG_LOADS(X)     X(l, LKIND, HASNULL)                      LKIND in {U64, I32, U8, U128}: input column l of the row loop
-//   PG_SLOTS(X)     X(s, KIND, WORD)                          KIND in {DEC, I64, I32, F64, MIN, MAX, CNT}: private state layout
+//   PG_SLOTS(X)     X(s, KIND, WORD)                          KIND in {SUM, F64, MIN, MAX, CNT}: private state, one word each
 //   PG_ROW_FILTER   statements for row v that end by defining `const bool pgx_pass` (a fused filter; `true` without one)
-//   PG_ROW_UPDATE   statements for row v: fused projections, the aggregates' conditions and the updates of `rec`
+//   PG_ROW_UPDATE   statements for row v: fused projections, the aggregates' conditions and the updates of `rec` / `wrec`
 // The two statement macros are generated text over ld<l>[v] / ldh<l>[v] (value, upper half of 128-bit values) and ldn<l>[v]
 // (null byte) — see jit_lowcard.cu and project_codegen.  Everything structural is a literal, so the row loop is straight-line
 // code; pointers and sizes arrive in PgjArgs.
 //
-// Layout of the private tables in shared memory: table[(group * PG_REC_WORDS + word) * PG_T + thread] — a warp touching
-// one word of 32 different (or equal) groups hits 32 different banks; every thread owns its column, no atomics.
+// State.  Every thread owns one 64-bit word per (group, slot) in shared memory, table[(group * PG_REC_WORDS + word) * PG_T +
+// thread]: a warp touching one word of 32 different (or equal) groups hits 32 different banks, and nobody else writes a thread's
+// column, so there are no atomics in the row loop.  Integer and decimal sums are exact although the private word is narrow: an
+// addend v with |v| < 2^PG_FAST_BITS goes into the private signed 64-bit sum, which cannot wrap within one launch (the host derives
+// the bound from the rows a thread can see); any other addend (large magnitudes, 128-bit values) is added to a 192-bit
+// accumulator per (group, slot) that the whole block shares (`wide`, shared-memory atomics with carry propagation).  The flush
+// sign-extends and adds up the private sums of a warp, warp 0 adds the block's wide accumulators, and the totals are applied to
+// the global state with carry-chain atomics.
+//
+// Groups.  The key -> group id table (lut) is either filled from the operator's known groups (a.known_groups > 0: packed keys in
+// a.lc_groups) or discovered by the kernel itself from the first a.discover_rows rows of the page: every block runs the same
+// deterministic discovery (fingerprints claimed with CAS, first row per fingerprint by atomicMin, keys written by the first
+// row's owner, every row verified against the stored key, ids by ascending first row = the reference's first-seen order), so all
+// blocks agree without talking to each other, and block 0 publishes the groups for the host.  Rows whose key is not in the
+// table are flagged in a.miss_flag and left to the general path.
 
 typedef unsigned long long u64;
 typedef long long i64;
@@ -34,7 +48,7 @@ typedef unsigned char u8;
 #define PGJ_CAT(a, b) PGJ_CAT2(a, b)
 
 // shared-memory key -> group id table: one 32-byte entry per slot, read with two independent 16-byte loads
-struct __align__(16) LutEntry { u64 w0, w1; int gid; int pad[3]; };
+struct __align__(16) LutEntry { u64 w0, w1; int gid; int first_row; u64 fp; };
 
 // ------------------------------------------------------------------ vector loads (read-only path)
 template <int V> __device__ __forceinline__ void load_u64(const void* base, i64 row, u64 (&o)[V]) {
@@ -80,6 +94,11 @@ __device__ __forceinline__ u32 lut_hash(u64 w0, u64 w1) {
     u32 x = (u32)w0 ^ (u32)(w0 >> 32) ^ (u32)w1 ^ (u32)(w1 >> 29);
     return (x * 0x9E3779B1u) >> 24;
 }
+__device__ __forceinline__ u64 key_fingerprint(u64 w0, u64 w1) {      // 64-bit, never zero (zero = unclaimed table entry)
+    u64 h = (w0 ^ (w1 * 0x9E3779B97F4A7C15ULL)) * 0xff51afd7ed558ccdULL;
+    h ^= h >> 33; h = (h ^ w1) * 0xc4ceb9fe1a85ec53ULL; h ^= h >> 29;
+    return h | 1ULL;
+}
 // strings of up to 3 bytes pack as len | b0<<8 | b1<<16 | b2<<24
 __device__ __forceinline__ u64 pack_short_string(const u8* b, int len) {
     u64 v = (u64)len;
@@ -89,45 +108,22 @@ __device__ __forceinline__ u64 pack_short_string(const u8* b, int len) {
     return v;
 }
 
-// ------------------------------------------------------------------ private state updates (thread-owned shared memory words)
-// 64-bit input into a 128-bit sum.  The upper word is touched only when a carry or a negative value reaches it.
-__device__ __forceinline__ void upd_i64(u64* t, u64 v) {
-    u64 lo = t[0] + v;
-    t[0] = lo;
-    if (lo < v || (i64)v < 0) t[PG_T] += (u64)((i64)v >> 63) + (lo < v ? 1ULL : 0ULL);
-}
-// 128-bit sign-magnitude input into a 192-bit two's complement sum; negatives are negated first (x = ~mag + 1, sign word ~0),
-// words 1 and 2 are touched only when the addend or a carry reaches them.
-__device__ __forceinline__ void upd_dec(u64* t, u64 lo, u64 hi) {
-    u64 a0 = lo, a1 = hi & 0x7fffffffffffffffULL, a2 = 0;
-    if ((i64)hi < 0 && (a0 | a1)) {
-        a0 = ~a0; a1 = ~a1; a2 = ~0ULL;
-        asm("add.cc.u64 %0, %0, 1;\n\taddc.u64 %1, %1, 0;" : "+l"(a0), "+l"(a1));
+// ------------------------------------------------------------------ state updates
+// block-wide 192-bit accumulator (shared memory): the exact home of every addend the narrow private sums cannot take
+__device__ __noinline__ void wide_add(u64* w, u64 a0, u64 a1, u64 a2) {
+    const u64 old0 = atomicAdd(&w[0], a0);
+    const u64 c0 = (old0 + a0) < a0 ? 1ULL : 0ULL;
+    const u64 add1 = a1 + c0;
+    u64 c1 = add1 < c0 ? 1ULL : 0ULL;
+    if (add1) {
+        const u64 old1 = atomicAdd(&w[1], add1);
+        c1 += (old1 + add1) < add1 ? 1ULL : 0ULL;
     }
-    u64 s0 = t[0] + a0;
-    t[0] = s0;
-    u64 c0 = s0 < a0 ? 1ULL : 0ULL;
-    if (a1 | a2 | c0) {
-        u64 s1 = t[PG_T], s2 = t[2 * PG_T];
-        // addend words 1..2 first absorb the carry of word 0, then join the sum: two independent two-word chains
-        asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, 0;" : "+l"(a1), "+l"(a2) : "l"(c0));
-        asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, %3;" : "+l"(s1), "+l"(s2) : "l"(a1), "l"(a2));
-        t[PG_T] = s1; t[2 * PG_T] = s2;
-    }
+    const u64 add2 = a2 + c1;
+    if (add2) atomicAdd(&w[2], add2);
 }
-// the same with a two's complement addend (a derived decimal of a fused projection): sign-extend into the third word
-__device__ __forceinline__ void upd_dec2c(u64* t, u64 w0, i64 w1) {
-    u64 s0 = t[0] + w0;
-    t[0] = s0;
-    u64 c0 = s0 < w0 ? 1ULL : 0ULL;
-    if (w1 | (i64)c0) {
-        u64 a1 = (u64)w1, a2 = (u64)(w1 >> 63);
-        u64 s1 = t[PG_T], s2 = t[2 * PG_T];
-        asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, 0;" : "+l"(a1), "+l"(a2) : "l"(c0));
-        asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, %3;" : "+l"(s1), "+l"(s2) : "l"(a1), "l"(a2));
-        t[PG_T] = s1; t[2 * PG_T] = s2;
-    }
-}
+// |v| < 2^PG_FAST_BITS as a signed 64-bit value: such addends go into the thread's private sum
+__device__ __forceinline__ bool fits_fast(u64 v) { return ((v + (1ULL << PG_FAST_BITS)) >> (PG_FAST_BITS + 1)) == 0; }
 __device__ __forceinline__ void upd_f64(u64* t, u64 bits, int conv) {
     double d = conv ? (double)(i64)bits : __longlong_as_double((i64)bits);
     t[0] = (u64)__double_as_longlong(__longlong_as_double((i64)t[0]) + d);
@@ -182,9 +178,7 @@ __device__ __forceinline__ void wreduce_sum_carry(u64& s, u64& carry) {
 #define PGJ_LD_U128(l) u64 PGJ_CAT(ld, l)[V], PGJ_CAT(ldh, l)[V]; load_u128<V>(a.load_ptr[l], row, PGJ_CAT(ld, l), PGJ_CAT(ldh, l));
 #define PGJ_LD_I32(l) u64 PGJ_CAT(ld, l)[V]; { int t32[V]; load_i32<V>(a.load_ptr[l], row, t32); _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(ld, l)[q] = (u64)(i64)t32[q]; }
 #define PGJ_LD_U8(l) u64 PGJ_CAT(ld, l)[V]; { u32 t8[V]; load_u8<V>((const u8*)a.load_ptr[l], row, t8); _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(ld, l)[q] = t8[q]; }
-#define PGJ_ISKIND_DEC 0
-#define PGJ_ISKIND_I64 1
-#define PGJ_ISKIND_I32 2
+#define PGJ_ISKIND_SUM 0
 #define PGJ_ISKIND_F64 3
 #define PGJ_ISKIND_MIN 4
 #define PGJ_ISKIND_MAX 5
@@ -196,7 +190,7 @@ __device__ __forceinline__ void wreduce_sum_carry(u64& s, u64& carry) {
 #define PGJ_K1_K32(k) u64 PGJ_CAT(kv, k)[V]; { int t32[V]; load_i32<V>(a.key_values[k], row, t32); _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(kv, k)[q] = (u64)(u32)t32[q]; }
 #define PGJ_K1_K8(k) u64 PGJ_CAT(kv, k)[V]; { u32 t8[V]; load_u8<V>((const u8*)a.key_values[k], row, t8); _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(kv, k)[q] = t8[q]; }
 #define PGJ_K1_KVAR(k) u64 PGJ_CAT(kv, k)[V]; int PGJ_CAT(ko, k)[V + 1]; load_offsets<V>(a.key_offsets[k], row, PGJ_CAT(ko, k)); \
-        u32 PGJ_CAT(ks, k)[V]; const bool PGJ_CAT(kspec, k) = a.row_base + row + V <= a.key_value_bytes[k];                               \
+        u32 PGJ_CAT(ks, k)[V]; const bool PGJ_CAT(kspec, k) = a.row_base + row + V <= kvb[k];                                               \
         if (PGJ_CAT(kspec, k)) load_u8<V>((const u8*)a.key_values[k] + a.row_base, row, PGJ_CAT(ks, k));
 #define PGJ_K2_K64(k)
 #define PGJ_K2_KDBL(k) _Pragma("unroll") for (int q = 0; q < V; q++) PGJ_CAT(kv, k)[q] = norm_double_key(PGJ_CAT(kv, k)[q]);
@@ -209,10 +203,16 @@ __device__ __forceinline__ void wreduce_sum_carry(u64& s, u64& carry) {
         else { _Pragma("unroll") for (int q = 0; q < V; q++) { int o = PGJ_CAT(ko, k)[q], len = PGJ_CAT(ko, k)[q + 1] - o;     \
             if (len > 3) { fits[q] = false; PGJ_CAT(kv, k)[q] = 0; } else PGJ_CAT(kv, k)[q] = pack_short_string((const u8*)a.key_values[k] + o, len); } } }
 
+// what one pass over V consecutive rows does with them
+#define PGJ_MODE_AGG 0       // look the groups up and update the thread's private records
+#define PGJ_MODE_CLAIM 1     // discovery pass 1: claim a table entry per key fingerprint, remember the first row that carries it
+#define PGJ_MODE_WRITE 2     // discovery pass 2: the first row's owner stores the key
+#define PGJ_MODE_VERIFY 3    // discovery pass 3: every row's key must equal the stored key of its entry (fingerprint collisions)
+
 // ------------------------------------------------------------------ V consecutive rows of one thread
-template <int V>
-__device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* table, const LutEntry* lut,
-                                             int tid, u64& misses) {
+template <int V, int MODE>
+__device__ __forceinline__ void process_rows(const PgjArgs& a, const i64* kvb, i64 row, u64* table, u64* wide, LutEntry* lut, int tid, u64& misses,
+                                             int& dflags) {
     bool fits[V];
     int pgx_err = 0;
 #pragma unroll
@@ -230,6 +230,7 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
 #undef PG_X
     // ---- phase A: pack the keys and find the groups of all V rows (independent look-ups overlap each other)
     int g[V];
+    u64 kw0[V], kw1[V];
 #pragma unroll
     for (int v = 0; v < V; v++) {
         u64 w0 = 0, w1 = 0;
@@ -239,8 +240,9 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
         else w1 |= PGJ_CAT(kv, k)[v] << SHIFT;
         PG_KEYS(PG_X)
 #undef PG_X
+        kw0[v] = w0; kw1[v] = w1;
         g[v] = -1;
-        if (fits[v]) {
+        if (MODE == PGJ_MODE_AGG && fits[v]) {
             u32 h = lut_hash(w0, w1);
             while (true) {
                 const LutEntry e = lut[h];
@@ -250,17 +252,40 @@ __device__ __forceinline__ void process_rows(const PgjArgs& a, i64 row, u64* tab
             }
         }
     }
-    // ---- phase B: update the thread's private records, row by row (two rows may share a group).  A row the fused filter
-    // rejects does not exist for the operator: it neither counts nor misses.
+    // ---- phase B, row by row (two rows may share a group).  A row the fused filter rejects does not exist for the operator:
+    // it neither counts nor misses nor founds a group.
 #pragma unroll
     for (int v = 0; v < V; v++) {
         PG_ROW_FILTER
         if (!pgx_pass) continue;
-        if (g[v] < 0) { misses++; atomicOr(&a.miss_flag[(row + v) >> 5], 1u << ((row + v) & 31)); continue; }
-        u64* rec = table + (g[v] * PG_REC_WORDS) * PG_T + tid;
-        PG_ROW_UPDATE
+        if (MODE == PGJ_MODE_AGG) {
+            if (g[v] < 0) { misses++; atomicOr(&a.miss_flag[(row + v) >> 5], 1u << ((row + v) & 31)); continue; }
+            u64* rec = table + (g[v] * PG_REC_WORDS) * PG_T + tid;
+            u64* wrec = wide + g[v] * (PG_NSUMS * 3);
+            u32 pg_slow = 0;
+            (void)wrec; (void)pg_slow;
+            PG_ROW_UPDATE
+        } else {
+            if (!fits[v]) { dflags |= PGJ_DISC_UNPACKABLE; continue; }     // the host takes the general path
+            const u64 fp = key_fingerprint(kw0[v], kw1[v]);
+            u32 h = lut_hash(kw0[v], kw1[v]);
+            int probes = 0;
+            bool found = false;
+            while (probes < PGJ_LUT_SIZE) {
+                u64 cur = lut[h].fp;
+                if (MODE == PGJ_MODE_CLAIM && cur == 0) { cur = atomicCAS(&lut[h].fp, 0ULL, fp); if (cur == 0) cur = fp; }
+                if (cur == fp) { found = true; break; }
+                if (MODE != PGJ_MODE_CLAIM && cur == 0) break;
+                h = (h + 1) & (PGJ_LUT_SIZE - 1);
+                probes++;
+            }
+            if (!found) { dflags |= PGJ_DISC_TABLE_FULL; continue; }      // more distinct keys than the table holds
+            if (MODE == PGJ_MODE_CLAIM) atomicMin(&lut[h].first_row, (int)(row + v));
+            else if (MODE == PGJ_MODE_WRITE) { if (lut[h].first_row == (int)(row + v)) { lut[h].w0 = kw0[v]; lut[h].w1 = kw1[v]; } }
+            else if (lut[h].w0 != kw0[v] || lut[h].w1 != kw1[v]) dflags |= PGJ_DISC_COLLISION;
+        }
     }
-    if (pgx_err) atomicOr((unsigned int*)(a.d_miss + 1), 1u);
+    if (MODE == PGJ_MODE_AGG && pgx_err) atomicOr((unsigned int*)(a.d_miss + 1), 1u);
 }
 
 // L2 prefetch of the V rows a later trip of this thread will read (PG_PREFETCH trips ahead): keeps more of HBM's
@@ -285,69 +310,102 @@ __device__ __forceinline__ void prefetch_rows(const PgjArgs& a, i64 row) {
 #undef PG_X
 }
 
-// stored key of group g in the packed form (thread 0 builds the look-up table once per block)
-__device__ bool pack_group(const PgjArgs& a, int g, u64& w0, u64& w1) {
-    w0 = 0; w1 = 0;
-    if (a.bigint_mode) {
-        if (g == a.null_gid) w1 |= 1ULL << 56; else w0 = (u64)a.values_by_group[g];
-        return true;
-    }
-    const u64* rowp = a.key_rows + (i64)g * a.row_words;
-    bool ok = true;
-#define PGJ_G_K64(w) v = (w);
-#define PGJ_G_KDBL(w) v = norm_double_key(w);
-#define PGJ_G_K32(w) v = (u64)(u32)(w);
-#define PGJ_G_K8(w) v = (w) & 0xff;
-#define PGJ_G_KVAR(w) { int len = (int)((w) & 0xFFFFFF); if (len > 3) ok = false; else { const u8* b = a.arena + ((w) >> 24); v = (u64)len; \
-        for (int t = 0; t < len; t++) v |= (u64)b[t] << (8 + 8 * t); } }
-#define PG_X(k, CLASS, WORD, SHIFT, HASNULL, WOFF)                                 \
-    if ((rowp[0] >> k) & 1) w1 |= 1ULL << (56 + k);                                \
-    else { u64 v = 0; PGJ_G_##CLASS(rowp[WOFF]) if (WORD == 0) w0 |= v << SHIFT; else w1 |= v << SHIFT; }
-    PG_KEYS(PG_X)
-#undef PG_X
-    return ok;
+// one discovery pass of the whole block over the first a.discover_rows rows
+template <int MODE>
+__device__ __forceinline__ void discover_pass(const PgjArgs& a, const i64* kvb, LutEntry* lut, int tid, int& dflags) {
+    u64 dummy = 0;
+    const i64 m = a.discover_rows;
+    for (i64 row = (i64)tid * PG_VEC; row + PG_VEC <= m; row += (i64)PG_T * PG_VEC) process_rows<PG_VEC, MODE>(a, kvb, row, nullptr, nullptr, lut, tid, dummy, dflags);
+    if (PG_VEC > 1 && tid == 0)
+        for (i64 row = m - m % PG_VEC; row < m; row++) process_rows<1, MODE>(a, kvb, row, nullptr, nullptr, lut, tid, dummy, dflags);
 }
 
 extern "C" __global__ void __launch_bounds__(PG_T, PG_MIN_BLOCKS) pg_lowcard_agg(const PgjArgs a) {
     extern __shared__ u64 table[];
     __shared__ LutEntry lut[PGJ_LUT_SIZE];
+    __shared__ int s_groups, s_flags;
+    __shared__ i64 kvb[PGJ_MAX_KEYS];                       // bytes in each variable width key's value buffer
     const int tid = threadIdx.x;
-    const int G = a.G;
-    // ---- own column: zeros, then min/max identities
-    for (int i = 0; i < G * PG_REC_WORDS; i++) table[i * PG_T + tid] = 0;
+    if (tid < PGJ_MAX_KEYS) kvb[tid] = (a.key_value_bytes[tid] < 0 && a.key_offsets[tid]) ? (i64)a.key_offsets[tid][a.n] : a.key_value_bytes[tid];
+    const int GCAP = a.G;                                   // groups the private tables are sized for
+    u64* wide = table + (i64)GCAP * PG_REC_WORDS * PG_T;     // [group][sum slot][3]
+    // ---- own column: zeros, then min/max identities; the block's wide accumulators
+    for (int i = 0; i < GCAP * PG_REC_WORDS; i++) table[i * PG_T + tid] = 0;
 #define PG_X(s, KIND, WORD)                                                                                               \
-    if (PGJ_ISKIND_##KIND == PGJ_KIND_MIN) for (int g = 0; g < G; g++) table[(g * PG_REC_WORDS + WORD) * PG_T + tid] = 0x7fffffffffffffffULL; \
-    if (PGJ_ISKIND_##KIND == PGJ_KIND_MAX) for (int g = 0; g < G; g++) table[(g * PG_REC_WORDS + WORD) * PG_T + tid] = 0x8000000000000000ULL;
+    if (PGJ_ISKIND_##KIND == PGJ_KIND_MIN) for (int g = 0; g < GCAP; g++) table[(g * PG_REC_WORDS + WORD) * PG_T + tid] = 0x7fffffffffffffffULL; \
+    if (PGJ_ISKIND_##KIND == PGJ_KIND_MAX) for (int g = 0; g < GCAP; g++) table[(g * PG_REC_WORDS + WORD) * PG_T + tid] = 0x8000000000000000ULL;
     PG_SLOTS(PG_X)
 #undef PG_X
-    for (int i = tid; i < PGJ_LUT_SIZE; i += PG_T) { lut[i].w0 = ~0ULL; lut[i].w1 = ~0ULL; lut[i].gid = -1; }
+    for (int i = tid; i < GCAP * PG_NSUMS * 3; i += PG_T) wide[i] = 0;
+    for (int i = tid; i < PGJ_LUT_SIZE; i += PG_T) { lut[i].w0 = ~0ULL; lut[i].w1 = ~0ULL; lut[i].gid = -1; lut[i].first_row = 0x7fffffff; lut[i].fp = 0; }
+    if (tid == 0) { s_groups = 0; s_flags = 0; }
     __syncthreads();
-    if (tid == 0) {
-        for (int g = 0; g < G; g++) {
-            u64 w0, w1;
-            if (!pack_group(a, g, w0, w1)) continue;
-            u32 h = lut_hash(w0, w1);
-            while (lut[h].gid >= 0) h = (h + 1) & (PGJ_LUT_SIZE - 1);
-            lut[h].w0 = w0; lut[h].w1 = w1; lut[h].gid = g;
+
+    if (a.known_groups > 0) {
+        // ---- the operator's groups: packed keys in id order
+        if (tid == 0) {
+            const int G = a.known_groups;
+            for (int g = 0; g < G; g++) {
+                const u64 w0 = a.lc_groups[4 * g], w1 = a.lc_groups[4 * g + 1];
+                if (a.lc_groups[4 * g + 3] == 0) continue;            // a group whose key the packed form cannot hold: its rows miss
+                u32 h = lut_hash(w0, w1);
+                while (lut[h].gid >= 0) h = (h + 1) & (PGJ_LUT_SIZE - 1);
+                lut[h].w0 = w0; lut[h].w1 = w1; lut[h].gid = g;
+            }
+            s_groups = G;
         }
+        __syncthreads();
+    } else {
+        // ---- discovery (every block computes the same table)
+        int dflags = 0;
+        discover_pass<PGJ_MODE_CLAIM>(a, kvb, lut, tid, dflags);
+        __syncthreads();
+        discover_pass<PGJ_MODE_WRITE>(a, kvb, lut, tid, dflags);
+        __syncthreads();
+        discover_pass<PGJ_MODE_VERIFY>(a, kvb, lut, tid, dflags);
+        if (dflags) atomicOr(&s_flags, dflags);
+        __syncthreads();
+        // ids by ascending first row
+        for (int i = tid; i < PGJ_LUT_SIZE; i += PG_T) {
+            if (lut[i].fp == 0) continue;
+            const int mine = lut[i].first_row;
+            int rank = 0;
+            for (int j = 0; j < PGJ_LUT_SIZE; j++) rank += (lut[j].fp != 0 && lut[j].first_row < mine) ? 1 : 0;
+            lut[i].gid = rank;
+            atomicAdd(&s_groups, 1);
+        }
+        __syncthreads();
+        if (s_groups > GCAP && tid == 0) atomicOr(&s_flags, PGJ_DISC_TOO_MANY);
+        __syncthreads();
+        if (blockIdx.x == 0) {      // publish: group table for the host, group count, discovery verdict
+            for (int i = tid; i < PGJ_LUT_SIZE; i += PG_T) {
+                if (lut[i].fp == 0 || lut[i].gid >= PGJ_MAX_GROUPS) continue;
+                u64* o = a.lc_groups_out + 4 * lut[i].gid;
+                o[0] = lut[i].w0; o[1] = lut[i].w1; o[2] = (u64)lut[i].first_row; o[3] = 1;
+            }
+            if (tid == 0) { a.d_miss[2] = (u64)s_groups; a.d_miss[3] = (u64)s_flags; }
+        }
+        if (s_flags) return;        // block-uniform: nothing has been accumulated, the host retries or takes the general path
     }
-    __syncthreads();
 
     // ---- row loop: thread t of block b takes rows [(b*T + t)*VEC, +VEC), then strides by the whole grid
     u64 misses = 0;
+    int unused = 0;
     const i64 n = a.n;
     const i64 stride = (i64)gridDim.x * PG_T * PG_VEC;
     for (i64 row = ((i64)blockIdx.x * PG_T + tid) * PG_VEC; row + PG_VEC <= n; row += stride) {
 #if PG_PREFETCH > 0
         if (row + PG_PREFETCH * stride + PG_VEC <= n) prefetch_rows<PG_VEC>(a, row + PG_PREFETCH * stride);
 #endif
-        process_rows<PG_VEC>(a, row, table, lut, tid, misses);
+        process_rows<PG_VEC, PGJ_MODE_AGG>(a, kvb, row, table, wide, lut, tid, misses, unused);
     }
     if (PG_VEC > 1 && blockIdx.x == 0 && tid == 0)
-        for (i64 row = n - n % PG_VEC; row < n; row++) process_rows<1>(a, row, table, lut, tid, misses);
+        for (i64 row = n - n % PG_VEC; row < n; row++) process_rows<1, PGJ_MODE_AGG>(a, kvb, row, table, wide, lut, tid, misses, unused);
+    __syncthreads();                // the block's wide accumulators are complete
 
     // ---- flush: per aggregate and group, reduce the warp's 32 columns and fold them into the global state
     const int lane = tid & 31;
+    const int G = s_groups;
     {
         u64 z = 0;
         wreduce_sum_carry(misses, z);
@@ -356,34 +414,35 @@ extern "C" __global__ void __launch_bounds__(PG_T, PG_MIN_BLOCKS) pg_lowcard_agg
     for (int ai = 0; ai < a.naggs; ai++) {
         const int op = a.agg_op[ai], kind = a.agg_val_kind[ai];
         for (int g = 0; g < G; g++) {
+            u64* st = a.agg_state[ai] + (i64)g * a.agg_words[ai];
+            if (kind == PGJ_KIND_SUM && tid == 0) {
+                // addends that went to the block's wide accumulator (their rows are counted in the private count words)
+                const u64* w = wide + (g * PG_NSUMS + a.agg_wide_idx[ai]) * 3;
+                if (w[0] | w[1] | w[2]) {
+                    if (op == PGJ_OP_SUM_I64) atomic_add_chain2(st + 1, w[0], w[1]);
+                    else atomic_add_chain3(st + 1, w[0], w[1], w[2]);
+                }
+            }
             const u64* rec = table + (g * PG_REC_WORDS) * PG_T + tid;
             u64 cnt = rec[a.agg_cnt_word[ai] * PG_T], zero = 0;
             wreduce_sum_carry(cnt, zero);
             cnt = __shfl_sync(0xffffffffu, cnt, 0);
-            if (cnt == 0) continue;   // warp-uniform
-            u64* st = a.agg_state[ai] + (i64)g * a.agg_words[ai];
+            if (cnt == 0) continue;   // warp-uniform: none of this warp's rows reached the aggregate in this group
             if (op == PGJ_OP_COUNT) { if (lane == 0) atomicAdd(&st[0], cnt); continue; }
             const u64* col = rec + a.agg_val_word[ai] * PG_T;
-            if (kind == PGJ_KIND_I64 || kind == PGJ_KIND_I32) {
-                u64 s0 = col[0], c0 = 0, s1 = col[PG_T], c1 = 0;
+            if (kind == PGJ_KIND_SUM) {
+                // the thread's signed 64-bit sum, sign-extended and added up over the warp
+                const i64 mine = (i64)col[0];
+                u64 s0 = (u64)mine, c0 = 0;
                 wreduce_sum_carry(s0, c0);
-                wreduce_sum_carry(s1, c1);
+                u64 s1 = (u64)(mine >> 63);     // 0 or all ones
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) s1 += __shfl_down_sync(0xffffffffu, s1, d);
                 if (lane == 0) {
-                    u64 hi = s1 + c0;   // 128-bit signed partial: cannot overflow for < 2^63 rows of 64-bit values
+                    const u64 a1 = s1 + c0;
                     atomicAdd(&st[0], cnt);
-                    if (op == PGJ_OP_SUM_I64) atomic_add_chain2(st + 1, s0, hi);
-                    else atomic_add_chain3(st + 1, s0, hi, (u64)((i64)hi >> 63));
-                }
-            } else if (kind == PGJ_KIND_DEC) {
-                u64 s0 = col[0], c0 = 0, s1 = col[PG_T], c1 = 0, s2 = col[2 * PG_T], c2 = 0;
-                wreduce_sum_carry(s0, c0);
-                wreduce_sum_carry(s1, c1);
-                wreduce_sum_carry(s2, c2);
-                if (lane == 0) {
-                    u64 a1 = s1 + c0;
-                    u64 k1 = c1 + (a1 < s1 ? 1ULL : 0ULL);
-                    atomicAdd(&st[0], cnt);
-                    atomic_add_chain3(st + 1, s0, a1, s2 + k1);
+                    if (op == PGJ_OP_SUM_I64) atomic_add_chain2(st + 1, s0, a1);
+                    else atomic_add_chain3(st + 1, s0, a1, (u64)((i64)a1 >> 63));
                 }
             } else if (kind == PGJ_KIND_F64) {
                 double d = __longlong_as_double((i64)col[0]);

@@ -318,6 +318,24 @@ PG_API int32_t pg_partition_scatter_peers(pg_partitioner* pt, const pg_col* in, 
                                           const int64_t* peer_row_offset);
 PG_API int32_t pg_partition_ids(pg_partitioner* pt, uint8_t* out, int32_t out_mem);
 
+/* pg_partition_positions_noalloc — NO COUNTERPART IN THE REFERENCE; added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The positions pass of pg_partition_create over a precomputed raw-hash channel, without any allocation: it calls no cudaMalloc /
+ * cudaFree / allocating library routine, creates no handle and does not synchronise (results are ready in stream order on the
+ * context's stream).  Every pointer is a DEVICE pointer supplied by the caller:
+ *   raw_hash[n]          BIGINT $hashvalue channel (rawHash of every row)
+ *   out_part_of_row[n]   partition of every row (HashGenerator.getPartition / LocalPartitionGenerator, `mode` as above)
+ *   out_dest[n]          row's position in partition-major order, stable inside a partition (what pg_partition_scatter applies)
+ *   out_counts[nparts]   rows per partition
+ * Its scratch (per-tile histograms) is one fixed array in device memory, about 1 MiB, held by every GPU that loads the library until
+ * exit.  Hence: n <= PG_NOALLOC_MAX_ROWS (larger pages fail with PG_E_INVALID_ARGUMENT - use pg_partition_create), nparts <= 64;
+ * all calls on a device share that array, so calls that OVERLAP on the GPU (different streams or contexts) race - calls on one
+ * stream are ordered and safe; the array keeps the last call's contents and no call depends on them.  The first call on a device
+ * resolves the array's device address (cudaGetSymbolAddress, no allocation): make one call before starting a graph capture. */
+#define PG_NOALLOC_MAX_ROWS 4194304
+PG_API int32_t pg_partition_positions_noalloc(pg_ctx* ctx, const int64_t* raw_hash, int64_t n, int32_t nparts, int32_t mode,
+                                              uint8_t* out_part_of_row, int32_t* out_dest, int64_t* out_counts);
+
 #ifdef __cplusplus
 }
 #endif

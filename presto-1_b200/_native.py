@@ -13,6 +13,7 @@ BIGINT, INTEGER, DATE, DOUBLE, SHORT_DECIMAL, LONG_DECIMAL, VARCHAR, VARBINARY, 
 MEM_HOST, MEM_DEVICE = 0, 1
 AGG_COUNT, AGG_COUNT_COL, AGG_SUM, AGG_AVG, AGG_MIN, AGG_MAX = range(1, 7)
 JOIN_INNER, JOIN_PROBE_OUTER = 0, 1
+NOALLOC_MAX_ROWS = 4194304      # PG_NOALLOC_MAX_ROWS
 
 STATUS_NAMES = {
     1: "NEED_MEMORY", 2: "GENERIC_INSUFFICIENT_RESOURCES", 3: "NUMERIC_VALUE_OUT_OF_RANGE", 4: "INVALID_ARGUMENT",
@@ -110,6 +111,7 @@ _PROTOS = {
     "pg_partition_scatter": (I32, [P, PCOL, PCOLOUT]),
     "pg_partition_scatter_peers": (I32, [P, PCOL, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), PI64]),
     "pg_partition_ids": (I32, [P, P, I32]),
+    "pg_partition_positions_noalloc": (I32, [P, P, I64, I32, I32, P, P, P]),
     "pg_joinbuild_create": (I32, [P, PI32, I32, PI32, I32, I32, I64, C.POINTER(P)]),
     "pg_joinbuild_destroy": (I32, [P]),
     "pg_joinbuild_add_page": (I32, [P, PCOL, I64]),

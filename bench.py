@@ -562,7 +562,8 @@ def gpu_arm(args):
     input_bytes = rows * tpch.Q1_RAW_BYTES_PER_ROW    # > 126 MB L2: every step streams its inputs from HBM
 
     plan = P.PartialFinalAggregation([P.VARCHAR, P.VARCHAR], [0, 1], aggs, ctx, dist, expected_groups=100_000,
-                                     reserve_sms=int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "8")), input_processor=processor)
+                                     reserve_sms=int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "4")), input_processor=processor,
+                                     pipeline=os.environ.get("PRESTOGPU_BENCH_PIPELINE", "1") != "0")
 
     ctx.set_timing(True)
     with ClockSampler(local_rank) as clk:
@@ -627,7 +628,7 @@ def gpu_arm(args):
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int128/int64 (decimal sums), u8 keys", "data": "synthetic (TPC-H-shaped generator, seeded)",
             "config": q1_config(args.sf, rows),
-            "plan": "SINGLE" if world == 1 else "PARTIAL -> NCCL all_gather -> FINAL; the FINAL stage of step i overlaps the PARTIAL stage of step i+1",
+            "plan": "SINGLE" if world == 1 else "PARTIAL -> packed page in device memory -> NCCL all_gather (device to device) -> FINAL on every rank; the FINAL stage of step i overlaps the PARTIAL stage of step i+1",
             "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
             "selfcheck": selfcheck, "result_digest": result_digest(out) if world == 1 else None,
         }

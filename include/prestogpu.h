@@ -249,6 +249,12 @@ PG_API int32_t pg_hashagg_reset(pg_hashagg* op);
 PG_API int32_t pg_hashagg_get_output_packed(pg_hashagg* op, int64_t first, int64_t n, void* buf, int64_t capacity, int64_t* out_bytes,
                                             int64_t* error_group);
 PG_API int32_t pg_hashagg_add_packed(pg_hashagg* op, const void* const* bufs, int32_t nbufs);
+/* The same pages in DEVICE memory, for exchanges that never leave the GPUs (NCCL all-gather of the PARTIAL pages of all ranks):
+ * get_output_packed_device writes the page at device_buf; add_packed_device takes nbufs pages that start `stride` bytes apart
+ * at device_bufs (the all-gather's receive buffer; stride a multiple of 8, every page at most `stride` bytes). */
+PG_API int32_t pg_hashagg_get_output_packed_device(pg_hashagg* op, int64_t first, int64_t n, void* device_buf, int64_t capacity,
+                                                   int64_t* out_bytes, int64_t* error_group);
+PG_API int32_t pg_hashagg_add_packed_device(pg_hashagg* op, const void* device_bufs, int64_t stride, int32_t nbufs);
 
 /* =====================================================================================
  * PageProcessor (filter + projections) — replaces OP/project/PageProcessor.java:54-57,139-330 as ScanFilterAndProjectOperator

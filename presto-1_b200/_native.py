@@ -101,6 +101,8 @@ _PROTOS = {
     "pg_hashagg_reset": (I32, [P]),
     "pg_hashagg_get_output_packed": (I32, [P, I64, I64, P, I64, PI64, PI64]),
     "pg_hashagg_add_packed": (I32, [P, C.POINTER(C.c_void_p), I32]),
+    "pg_hashagg_get_output_packed_device": (I32, [P, I64, I64, P, I64, PI64, PI64]),
+    "pg_hashagg_add_packed_device": (I32, [P, P, I64, I32]),
     "pg_project_create": (I32, [P, C.POINTER(PgExpr), I32, I32, PI32, I32, C.POINTER(P)]),
     "pg_project_destroy": (I32, [P]),
     "pg_project_output_types": (I32, [P, PI32, PI32, PI32, I32, PI32]),

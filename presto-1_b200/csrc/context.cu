@@ -118,11 +118,7 @@ void* in_arena_stage(pg_ctx* ctx, const void* host, int64_t bytes) {
     if (ctx->in_used + need > ctx->in_cap) return nullptr;
     const int64_t off = ctx->in_used;
     ctx->in_used += need;
-    memcpy(ctx->in_pinned + off, host, (size_t)bytes);
-    if (cudaMemcpyAsync((char*)ctx->in_dev + off, ctx->in_pinned + off, (size_t)bytes, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) {
-        cudaGetLastError();
-        return nullptr;
-    }
+    memcpy(ctx->in_pinned + off, host, (size_t)bytes);      // leaves for the device with the next flush_staged_inputs (one copy for all pieces)
     return (char*)ctx->in_dev + off;
 }
 
@@ -183,6 +179,7 @@ int32_t pg_ctx_destroy(pg_ctx* ctx) {
     if (ctx->out_pinned) cudaFreeHost(ctx->out_pinned);
     if (ctx->in_dev) cudaFree(ctx->in_dev);
     if (ctx->in_pinned) cudaFreeHost(ctx->in_pinned);
+    if (ctx->pk_pinned) cudaFreeHost(ctx->pk_pinned);
     for (const pg_kernel_record& r : ctx->records) { cudaEventDestroy(r.start); cudaEventDestroy(r.stop); }
     for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
     pg::jit_cache_free(ctx);

@@ -43,6 +43,10 @@ struct pg_ctx {
     void* in_dev = nullptr;
     char* in_pinned = nullptr;
     int64_t in_cap = 0, in_used = 0;
+    int64_t in_flushed = 0;        // staged bytes [in_flushed, in_used) sit in the pinned arena and leave with ONE copy before the next launch
+    // landing zone for packed pages that arrive in device memory (pg_hashagg_add_packed_device): pinned, grown on demand
+    char* pk_pinned = nullptr;
+    int64_t pk_cap = 0;
     int guard_depth = 0;
     int out_live = 0;              // output-arena pieces handed to an OutStage that has not given them back yet
 };
@@ -76,9 +80,19 @@ struct Error : public std::exception {
 #define PG_CHECK_ARG(cond, ...) do { if (!(cond)) ::pg::fail(PG_E_INVALID_ARGUMENT, __VA_ARGS__); } while (0)
 #define PG_CHECK_STATE(cond, ...) do { if (!(cond)) ::pg::fail(PG_E_ILLEGAL_STATE, __VA_ARGS__); } while (0)
 
+// host inputs staged in the pinned arena since the last flush go to the device with one copy (called before anything that may read them)
+static inline void flush_staged_inputs(pg_ctx* ctx) {
+    if (ctx->in_flushed < ctx->in_used) {
+        cudaMemcpyAsync((char*)ctx->in_dev + ctx->in_flushed, ctx->in_pinned + ctx->in_flushed, (size_t)(ctx->in_used - ctx->in_flushed),
+                        cudaMemcpyHostToDevice, ctx->stream);
+        ctx->in_flushed = ctx->in_used;
+    }
+}
+
 // kernel<<<grid, block, smem, ctx->stream>>>(...) with launch counting and error check
 #define PG_LAUNCH(ctx, kernel, grid, block, smem, ...)                                           \
     do {                                                                                         \
+        ::pg::flush_staged_inputs(ctx);                                                          \
         pg_kernel_record _rec;                                                                   \
         if ((ctx)->timing) {                                                                     \
             _rec.name = #kernel; _rec.start = ::pg::timing_event(ctx); _rec.stop = ::pg::timing_event(ctx); \
@@ -100,6 +114,7 @@ static inline int32_t guard(pg_ctx* ctx, F&& f) {
                 if (c->in_used > 0) {
                     cudaStreamSynchronize(c->stream);   // the previous call's staged copies must have left the pinned buffer
                     c->in_used = 0;
+                    c->in_flushed = 0;
                 }
                 c->out_live = 0;
                 if (c->out_pending.empty()) c->out_used = 0;
@@ -163,6 +178,7 @@ static inline void memset_async(pg_ctx* ctx, void* p, int v, int64_t bytes) {
     if (bytes > 0) PG_CUDA(cudaMemsetAsync(p, v, (size_t)bytes, ctx->stream));
 }
 static inline void copy_async(pg_ctx* ctx, void* dst, const void* src, int64_t bytes, cudaMemcpyKind kind) {
+    if (kind != cudaMemcpyHostToDevice) flush_staged_inputs(ctx);      // the source may be a staged input
     if (bytes > 0) PG_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, kind, ctx->stream));
 }
 void flush_host_outputs(pg_ctx* ctx);   // context.cu

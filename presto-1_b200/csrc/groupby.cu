@@ -75,6 +75,53 @@ struct InsertArgs {
     const uint8_t* arena;
 };
 
+// finds or claims the slot of `row` (claimed = this row created the slot); the body of K1, shared with the small-page kernel
+template <bool BIGINT>
+PG_D int64_t gb_find_or_claim(const InsertArgs& a, const KeyCols& kc, const KeyLayout& L, const DCol& hash_col, int has_hash, int64_t row,
+                              bool& claimed) {
+    // Slot words are read through L1 (plain loads): a key / claim never changes once written, so a cached
+    // non-empty word is always right; a stale cached EMPTY is resolved by the CAS, which returns the live value.
+    if (BIGINT) {
+        const DCol& c = kc.c[0];
+        if (dcol_is_null(c, row)) return a.cap + 1;
+        unsigned long long key = (unsigned long long)((const int64_t*)c.values)[row];
+        if (key == EMPTY_KEY) return a.cap;
+        int64_t p = (int64_t)(fmix64(key) & (uint64_t)a.mask);
+        while (true) {
+            unsigned long long k = a.slots[p].word;
+            if (k == key) break;
+            if (k == EMPTY_KEY) {
+                unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_KEY, key);
+                if (old == EMPTY_KEY) { claimed = true; break; }
+                if (old == key) break;
+            }
+            p = (p + 1) & a.mask;
+        }
+        return p;
+    }
+    int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
+    uint64_t f = fmix64((uint64_t)raw);
+    uint32_t tag = (uint32_t)(f >> 32);
+    unsigned long long mine = ((unsigned long long)tag << 32) | (unsigned long long)(REF_PENDING | (uint32_t)row);
+    int64_t p = (int64_t)(f & (uint64_t)a.mask);
+    while (true) {
+        unsigned long long w = a.slots[p].word;
+        if (w == EMPTY_WORD) {
+            unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_WORD, mine);
+            if (old == EMPTY_WORD) { claimed = true; break; }
+            w = old;
+        }
+        if ((uint32_t)(w >> 32) == tag) {
+            uint32_t ref = (uint32_t)w;
+            bool eq = (ref & REF_PENDING) ? keys_equal_rows(kc, L, row, (int64_t)(ref & ~REF_PENDING))
+                                          : keys_equal_store(kc, L, row, a.key_rows, a.arena, (int64_t)ref);
+            if (eq) break;
+        }
+        p = (p + 1) & a.mask;
+    }
+    return p;
+}
+
 template <bool BIGINT>
 __global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, KeyCols kc, KeyLayout L, DCol hash_col, int has_hash) {
     __shared__ int s_inserted;
@@ -99,52 +146,7 @@ __global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, Key
         bool pending = false;
         int64_t s = -1;
         if (valid) {
-            // Slot words are read through L1 (plain loads): a key / claim never changes once written, so a cached
-            // non-empty word is always right; a stale cached EMPTY is resolved by the CAS, which returns the live value.
-            if (BIGINT) {
-                const DCol& c = kc.c[0];
-                if (dcol_is_null(c, row)) s = a.cap + 1;
-                else {
-                    unsigned long long key = (unsigned long long)((const int64_t*)c.values)[row];
-                    if (key == EMPTY_KEY) s = a.cap;
-                    else {
-                        int64_t p = (int64_t)(fmix64(key) & (uint64_t)a.mask);
-                        while (true) {
-                            unsigned long long k = a.slots[p].word;
-                            if (k == key) break;
-                            if (k == EMPTY_KEY) {
-                                unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_KEY, key);
-                                if (old == EMPTY_KEY) { claimed = true; break; }
-                                if (old == key) break;
-                            }
-                            p = (p + 1) & a.mask;
-                        }
-                        s = p;
-                    }
-                }
-            } else {
-                int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
-                uint64_t f = fmix64((uint64_t)raw);
-                uint32_t tag = (uint32_t)(f >> 32);
-                unsigned long long mine = ((unsigned long long)tag << 32) | (unsigned long long)(REF_PENDING | (uint32_t)row);
-                int64_t p = (int64_t)(f & (uint64_t)a.mask);
-                while (true) {
-                    unsigned long long w = a.slots[p].word;
-                    if (w == EMPTY_WORD) {
-                        unsigned long long old = atomicCAS(&a.slots[p].word, EMPTY_WORD, mine);
-                        if (old == EMPTY_WORD) { claimed = true; break; }
-                        w = old;
-                    }
-                    if ((uint32_t)(w >> 32) == tag) {
-                        uint32_t ref = (uint32_t)w;
-                        bool eq = (ref & REF_PENDING) ? keys_equal_rows(kc, L, row, (int64_t)(ref & ~REF_PENDING))
-                                                      : keys_equal_store(kc, L, row, a.key_rows, a.arena, (int64_t)ref);
-                        if (eq) break;
-                    }
-                    p = (p + 1) & a.mask;
-                }
-                s = p;
-            }
+            s = gb_find_or_claim<BIGINT>(a, kc, L, hash_col, has_hash, row, claimed);
             pending = a.slots[s].gid < 0;   // group ids are only assigned between launches: the cached value is current
             a.row_slot[row] = (int32_t)s;
         }
@@ -219,6 +221,54 @@ struct AssignArgs {
     uint8_t* arena;
 };
 
+// stores the key of new group `gid` (first seen at `row`, slot s; its variable width bytes start at boff) and numbers the slot
+template <bool BIGINT>
+PG_D void gb_assign_row(const AssignArgs& a, const KeyCols& kc, const KeyLayout& L, const DCol& hash_col, int has_hash, int64_t row, int32_t s,
+                        int64_t gid, int64_t boff) {
+    if (BIGINT) {
+        int64_t key = 0;
+        if (s == a.cap) key = (int64_t)EMPTY_KEY;
+        else if (s < a.cap) key = ((const int64_t*)kc.c[0].values)[row];
+        a.values_by_group[gid] = key;
+    } else {
+        uint64_t* out = a.key_rows + gid * L.row_words;
+        uint64_t nullbits = 0;
+        for (int k = 0; k < L.nkeys; k++) {
+            const DCol& c = kc.c[k];
+            uint64_t* w = out + L.word_off[k];
+            if (dcol_is_null(c, row)) {
+                nullbits |= 1ULL << k;
+                w[0] = 0;
+                if (c.type == PG_LONG_DECIMAL) w[1] = 0;
+                if (c.type == PG_VARCHAR || c.type == PG_VARBINARY) w[0] = (uint64_t)boff << 24;
+                continue;
+            }
+            switch (c.type) {
+                case PG_VARCHAR: case PG_VARBINARY: {
+                    int32_t o = c.offsets[row], len = c.offsets[row + 1] - o;
+                    const uint8_t* b = (const uint8_t*)c.values;
+                    for (int32_t t = 0; t < len; t++) a.arena[boff + t] = b[o + t];
+                    w[0] = ((uint64_t)boff << 24) | (uint64_t)(uint32_t)len;
+                    boff += len;
+                    break;
+                }
+                case PG_LONG_DECIMAL: {
+                    const uint64_t* p = (const uint64_t*)c.values;
+                    w[0] = p[2 * row]; w[1] = p[2 * row + 1];
+                    break;
+                }
+                default: w[0] = (uint64_t)dcol_long(c, row);
+            }
+        }
+        out[0] = nullbits;
+        int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
+        a.hash_by_group[gid] = raw;
+        // the slot keeps its tag (= upper half of fmix64(rawHash), what the claim wrote) and now refers to the stored key
+        a.slots[s].word = (fmix64((uint64_t)raw) & 0xFFFFFFFF00000000ULL) | (unsigned long long)(uint32_t)gid;
+    }
+    a.slots[s].gid = (int32_t)gid;
+}
+
 template <bool BIGINT>
 __global__ void __launch_bounds__(SCAN_THREADS) gb_assign_kernel(AssignArgs a, KeyCols kc, KeyLayout L, DCol hash_col, int has_hash,
                                                                  int has_var) {
@@ -237,52 +287,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) gb_assign_kernel(AssignArgs a, K
         }
         Pair64 total;
         Pair64 ex = block_exclusive_scan(v, smem, &total);
-        if (v.a) {
-            int64_t gid = run.a + ex.a;
-            if (BIGINT) {
-                int64_t key = 0;
-                if (s == a.cap) key = (int64_t)EMPTY_KEY;
-                else if (s < a.cap) key = ((const int64_t*)kc.c[0].values)[row];
-                a.values_by_group[gid] = key;
-            } else {
-                uint64_t* out = a.key_rows + gid * L.row_words;
-                int64_t boff = run.b + ex.b;
-                uint64_t nullbits = 0;
-                for (int k = 0; k < L.nkeys; k++) {
-                    const DCol& c = kc.c[k];
-                    uint64_t* w = out + L.word_off[k];
-                    if (dcol_is_null(c, row)) {
-                        nullbits |= 1ULL << k;
-                        w[0] = 0;
-                        if (c.type == PG_LONG_DECIMAL) w[1] = 0;
-                        if (c.type == PG_VARCHAR || c.type == PG_VARBINARY) w[0] = (uint64_t)boff << 24;
-                        continue;
-                    }
-                    switch (c.type) {
-                        case PG_VARCHAR: case PG_VARBINARY: {
-                            int32_t o = c.offsets[row], len = c.offsets[row + 1] - o;
-                            const uint8_t* b = (const uint8_t*)c.values;
-                            for (int32_t t = 0; t < len; t++) a.arena[boff + t] = b[o + t];
-                            w[0] = ((uint64_t)boff << 24) | (uint64_t)(uint32_t)len;
-                            boff += len;
-                            break;
-                        }
-                        case PG_LONG_DECIMAL: {
-                            const uint64_t* p = (const uint64_t*)c.values;
-                            w[0] = p[2 * row]; w[1] = p[2 * row + 1];
-                            break;
-                        }
-                        default: w[0] = (uint64_t)dcol_long(c, row);
-                    }
-                }
-                out[0] = nullbits;
-                int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
-                a.hash_by_group[gid] = raw;
-                unsigned long long tagw = a.slots[s].word & 0xFFFFFFFF00000000ULL;
-                a.slots[s].word = tagw | (unsigned long long)(uint32_t)gid;
-            }
-            a.slots[s].gid = (int32_t)gid;
-        }
+        if (v.a) gb_assign_row<BIGINT>(a, kc, L, hash_col, has_hash, row, s, run.a + ex.a, run.b + ex.b);
         run = run + total;
     }
 }
@@ -297,6 +302,73 @@ __global__ void gb_lookup_ids_kernel(const Slot* slots, const int32_t* row_slot,
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < n; i += stride) out_ids[i] = slots[row_slot[i]].gid;
+}
+
+// ------------------------------------------------------------------ small pages: K1 + K2 + K3 in ONE launch of ONE block
+// Trino pages are small (<= 8192 rows, PageProcessor.java:56); six launches and two read-backs per page cost far more than the
+// work.  One block does the whole getGroupIds: every row finds or claims its slot, the block synchronises, new groups are numbered
+// in row order with block-wide scans, keys are stored, ids are emitted.  The host guarantees that the table (and the arena, for
+// variable width keys) has room for n new groups, so there is no quota / abort protocol; meta->{group_count, arena_bytes,
+// inserted} are what the host reads back afterwards.
+static const int SMALL_THREADS = 1024;
+static const int64_t SMALL_PAGE_ROWS = 16384;
+
+template <bool BIGINT>
+__global__ void __launch_bounds__(SMALL_THREADS) gb_small_page_kernel(InsertArgs a, AssignArgs as, KeyCols kc, KeyLayout L, DCol hash_col, int has_hash,
+                                                                      int has_var, int32_t* row_slot, int32_t* out_ids) {
+    __shared__ Pair64 warp_tot[SMALL_THREADS / 32];
+    __shared__ Pair64 s_run;
+    __shared__ int s_claimed;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t n = a.n;
+    const int64_t base_groups = a.meta->group_count, base_bytes = a.meta->arena_bytes;
+    if (tid == 0) { s_run = Pair64{0, 0}; s_claimed = 0; }
+    __syncthreads();
+    // ---- K1
+    for (int64_t row = tid; row < n; row += SMALL_THREADS) {
+        bool claimed = false;
+        const int64_t s = gb_find_or_claim<BIGINT>(a, kc, L, hash_col, has_hash, row, claimed);
+        row_slot[row] = (int32_t)s;
+        if (__ldcg(&a.slots[s].gid) < 0) atomicMin(&a.slots[s].first_row, (int32_t)row);
+        if (claimed) atomicAdd(&s_claimed, 1);
+    }
+    __syncthreads();
+    // ---- K2: rows in page order, SMALL_THREADS at a time
+    for (int64_t chunk = 0; chunk < n; chunk += SMALL_THREADS) {
+        const int64_t row = chunk + tid;
+        int32_t s = 0;
+        Pair64 v{0, 0};
+        if (row < n) {
+            // first_row was settled with atomics (L2) while this SM's L1 may still hold the slot as it first saw it: read L2
+            s = row_slot[row];
+            const int4 sl = __ldcg((const int4*)&a.slots[s]);
+            if (sl.z < 0 && sl.w == (int32_t)row) {
+                v.a = 1;
+                if (has_var) v.b = row_var_bytes(kc, L, row);
+            }
+        }
+        Pair64 inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            Pair64 o = shfl_up_pair(inc, d);
+            if (lane >= d) inc = inc + o;
+        }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        Pair64 before = s_run;
+        for (int w = 0; w < warp; w++) before = before + warp_tot[w];
+        if (v.a) gb_assign_row<BIGINT>(as, kc, L, hash_col, has_hash, row, s, base_groups + before.a + inc.a - 1, base_bytes + before.b + inc.b - v.b);
+        __syncthreads();
+        if (tid == 0) { Pair64 t = s_run; for (int w = 0; w < SMALL_THREADS / 32; w++) t = t + warp_tot[w]; s_run = t; }
+        __syncthreads();
+    }
+    // ---- K3
+    if (out_ids) for (int64_t row = tid; row < n; row += SMALL_THREADS) out_ids[row] = __ldcg(&a.slots[row_slot[row]].gid);
+    if (tid == 0) {
+        a.meta->group_count = base_groups + s_run.a;
+        a.meta->arena_bytes = base_bytes + s_run.b;
+        a.meta->inserted = s_claimed;
+    }
 }
 
 // ------------------------------------------------------------------ contains (read-only probe)
@@ -542,6 +614,31 @@ static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_co
     gb->tile_sums.grow(ctx, ntiles * (int64_t)sizeof(Pair64), 0);
     GbMeta* meta = gb->meta.as<GbMeta>();
 
+    // ---- small page with room for every row to be a new group: one launch, one read-back
+    {
+        const bool small_on = !(getenv("PRESTOGPU_GB_SMALL") && getenv("PRESTOGPU_GB_SMALL")[0] == '0');
+        const int64_t hint = gb->var_bound_hint;
+        if (small_on && n <= SMALL_PAGE_ROWS && (!gb->has_var || (hint >= 0 && hint <= (64LL << 20)))) {
+            while (gb->max_fill - gb->occupied < n) rebuild_table(gb, gb->cap * 2);
+            if (gb->has_var && gb->arena_used + hint > gb->arena.bytes) gb->arena.grow(ctx, (gb->arena_used + hint) * 2, gb->arena_used);
+            InsertArgs a;
+            a.slots = gb->slots.as<Slot>(); a.cap = gb->cap; a.mask = gb->cap - 1; a.row_slot = gb->row_slot.as<int32_t>();
+            a.meta = meta; a.n = n; a.quota = INT64_MAX / 2; a.key_rows = gb->key_rows.as<uint64_t>(); a.arena = gb->arena.as<uint8_t>();
+            AssignArgs as;
+            as.slots = a.slots; as.cap = gb->cap; as.row_slot = a.row_slot; as.n = n; as.tile_prefix = nullptr; as.meta = meta;
+            as.values_by_group = gb->values_by_group.as<int64_t>(); as.key_rows = gb->key_rows.as<uint64_t>();
+            as.hash_by_group = gb->hash_by_group.as<int64_t>(); as.arena = gb->arena.as<uint8_t>();
+            if (gb->bigint_mode) PG_LAUNCH(ctx, gb_small_page_kernel<true>, 1, SMALL_THREADS, 0, a, as, kc, L, hc, has_hash, 0, a.row_slot, d_out_ids);
+            else PG_LAUNCH(ctx, gb_small_page_kernel<false>, 1, SMALL_THREADS, 0, a, as, kc, L, hc, has_hash, gb->has_var ? 1 : 0, a.row_slot, d_out_ids);
+            int64_t fin[3];
+            read_scalars(ctx, &meta->group_count, 3, fin);
+            gb->groups = fin[0];
+            gb->arena_used = fin[1];
+            gb->occupied += fin[2];
+            return;
+        }
+    }
+
     // ---- K1 with quota / rebuild loop
     const int grid = grid_for(ctx, n, GB_THREADS);
     bool inserted_pending = false, arena_pending = false;
@@ -675,6 +772,18 @@ void import_keys(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int
         PG_CHECK_ARG(!gb->has_hash_channel || gb->bigint_mode, "this GroupByHash was created with a precomputed hash channel");
     }
 }
+// small page: a bound on its variable width key bytes (known for host columns) lets process_chunk take its one-launch path
+struct VarHint {
+    pg_groupby* gb;
+    VarHint(pg_groupby* g, const ImportedKeys& ik, int64_t n) : gb(g) {
+        if (!g->has_var || n > 16384) return;
+        int64_t bound = 0;
+        for (size_t k = 0; k < ik.cols.size() && bound >= 0; k++)
+            if (type_is_var(ik.cols[k].d.type)) bound = ik.cols[k].value_bytes >= 0 ? bound + ik.cols[k].value_bytes : -1;
+        g->var_bound_hint = bound;
+    }
+    ~VarHint() { gb->var_bound_hint = -1; }
+};
 }  // namespace
 
 extern "C" {
@@ -700,6 +809,7 @@ int32_t pg_groupby_get_group_ids(pg_groupby* gb, const pg_col* keys, const pg_co
         import_keys(gb, keys, hash_col, n, ik);
         OutVec<int32_t> ids;
         ids.begin(gb->ctx, out_ids, ids_mem, n);
+        VarHint hint(gb, ik, n);
         groupby_process(gb, ik.kc, ik.has_hash ? &ik.hc : nullptr, n, ids.d);
         ids.finish();
         sync(gb->ctx);
@@ -713,6 +823,7 @@ int32_t pg_groupby_add_page(pg_groupby* gb, const pg_col* keys, const pg_col* ha
         PG_CHECK_ARG(n >= 0, "bad arguments");
         ImportedKeys ik;
         import_keys(gb, keys, hash_col, n, ik);
+        VarHint hint(gb, ik, n);
         groupby_process(gb, ik.kc, ik.has_hash ? &ik.hc : nullptr, n, nullptr);
         sync(gb->ctx);
     });

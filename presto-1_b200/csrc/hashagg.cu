@@ -476,7 +476,16 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     }
     hashagg_sync_gb(op);
     op->ids.grow(ctx, n * 4, 0);
+    if (op->gb->has_var && n <= 16384) {     // small page: a bound on its variable width key bytes lets the GroupByHash take its one-launch path
+        int64_t bound = 0;
+        for (size_t k = 0; k < op->key_channels.size() && bound >= 0; k++) {
+            const ColImport& ci = imp[op->key_channels[k]];
+            if (type_is_var(ci.d.type)) bound = ci.value_bytes >= 0 ? bound + ci.value_bytes : -1;
+        }
+        op->gb->var_bound_hint = bound;
+    }
     groupby_process(op->gb, kc, has_hash ? &hc : nullptr, n, op->ids.as<int32_t>());
+    op->gb->var_bound_hint = -1;
     int64_t groups = op->gb->groups;
     if (op->aggs.empty()) { op->input_rows += n; return; }
     for (pg_agg* a : op->aggs) agg_ensure_capacity(a, groups);
@@ -682,14 +691,15 @@ inline int64_t packed_width(int32_t t) {
 }
 }  // namespace
 
-int32_t pg_hashagg_get_output_packed(pg_hashagg* op, int64_t first, int64_t n, void* buf, int64_t capacity, int64_t* out_bytes,
-                                     int64_t* error_group) {
+static int32_t get_output_packed_impl(pg_hashagg* op, int64_t first, int64_t n, void* buf, int32_t mem, int64_t capacity, int64_t* out_bytes,
+                                      int64_t* error_group) {
     if (!op || !out_bytes) return PG_E_INVALID_ARGUMENT;
     int32_t types[256], ncols = 0;
     int32_t rc = pg_hashagg_output_types(op, types, 256, &ncols);
     if (rc != PG_OK) return rc;
     std::vector<PackedCol> cols(ncols);
-    int64_t pos = align8((int64_t)sizeof(PackedHeader) + (int64_t)ncols * (int64_t)sizeof(PackedCol));
+    const int64_t header_bytes = align8((int64_t)sizeof(PackedHeader) + (int64_t)ncols * (int64_t)sizeof(PackedCol));
+    int64_t pos = header_bytes;
     for (int i = 0; i < ncols; i++) {
         PackedCol& c = cols[i];
         c.type = types[i]; c.has_nulls = 1; c.offsets_bytes = 0;
@@ -708,22 +718,69 @@ int32_t pg_hashagg_get_output_packed(pg_hashagg* op, int64_t first, int64_t n, v
         return guard(op->ctx, [&] { fail(PG_NEED_MEMORY, "packed page needs %lld bytes, the buffer holds %lld", (long long)pos, (long long)capacity); });
     }
     char* base = (char*)buf;
-    PackedHeader* h = (PackedHeader*)base;
+    std::vector<char> hdr((size_t)header_bytes, 0);
+    PackedHeader* h = (PackedHeader*)hdr.data();
     h->total_bytes = pos; h->n = n; h->ncols = ncols; h->magic = PACKED_MAGIC;
-    memcpy(base + sizeof(PackedHeader), cols.data(), (size_t)ncols * sizeof(PackedCol));
+    memcpy(hdr.data() + sizeof(PackedHeader), cols.data(), (size_t)ncols * sizeof(PackedCol));
+    if (mem == PG_MEM_DEVICE) {
+        // zero the page (null flags, padding), then the header; the columns are written in place by the output kernels
+        rc = guard(op->ctx, [&] {
+            memset_async(op->ctx, base, 0, pos);
+            copy_async(op->ctx, base, hdr.data(), header_bytes, cudaMemcpyHostToDevice);
+        });
+        if (rc != PG_OK) return rc;
+    } else memcpy(base, hdr.data(), (size_t)header_bytes);
     std::vector<pg_col_out> outs(ncols);
     for (int i = 0; i < ncols; i++) {
         const PackedCol& c = cols[i];
         pg_col_out& o = outs[i];
         memset(&o, 0, sizeof(o));
-        o.type = c.type; o.mem = PG_MEM_HOST; o.capacity = n;
+        o.type = c.type; o.mem = mem; o.capacity = n;
         o.values = base + c.data_offset;
         o.offsets = c.offsets_bytes ? (int32_t*)(base + c.data_offset + align8(c.values_bytes)) : nullptr;
         o.nulls = (uint8_t*)(base + c.data_offset + align8(c.values_bytes) + align8(c.offsets_bytes));
         o.values_capacity_bytes = packed_is_var(c.type) ? c.values_bytes : 0;
-        memset(o.nulls, 0, (size_t)(n > 0 ? n : 1));
+        if (mem != PG_MEM_DEVICE) memset(o.nulls, 0, (size_t)(n > 0 ? n : 1));
     }
     return pg_hashagg_get_output(op, first, n, outs.data(), error_group);
+}
+
+int32_t pg_hashagg_get_output_packed(pg_hashagg* op, int64_t first, int64_t n, void* buf, int64_t capacity, int64_t* out_bytes,
+                                     int64_t* error_group) {
+    return get_output_packed_impl(op, first, n, buf, PG_MEM_HOST, capacity, out_bytes, error_group);
+}
+
+int32_t pg_hashagg_get_output_packed_device(pg_hashagg* op, int64_t first, int64_t n, void* device_buf, int64_t capacity, int64_t* out_bytes,
+                                            int64_t* error_group) {
+    return get_output_packed_impl(op, first, n, device_buf, PG_MEM_DEVICE, capacity, out_bytes, error_group);
+}
+
+int32_t pg_hashagg_add_packed_device(pg_hashagg* op, const void* device_bufs, int64_t stride, int32_t nbufs) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    pg_ctx* ctx = op->ctx;
+    std::vector<const void*> ptrs;
+    int32_t rc = guard(ctx, [&] {
+        PG_CHECK_ARG(device_bufs && nbufs > 0 && stride >= (int64_t)sizeof(PackedHeader) && stride % 8 == 0, "bad arguments");
+        const int64_t bytes = stride * nbufs;
+        PG_CHECK_ARG(bytes <= (256LL << 20), "packed pages of %lld bytes are too large for this entry point", (long long)bytes);
+        if (ctx->pk_cap < bytes) {
+            if (ctx->pk_pinned) { cudaFreeHost(ctx->pk_pinned); ctx->pk_pinned = nullptr; ctx->pk_cap = 0; }
+            int64_t cap = 1 << 20;
+            while (cap < bytes) cap <<= 1;
+            PG_CUDA(cudaHostAlloc((void**)&ctx->pk_pinned, (size_t)cap, cudaHostAllocDefault));
+            ctx->pk_cap = cap;
+        }
+        // only the bytes each page uses would do, but their count sits in the pages themselves: one copy of everything is cheaper than two trips
+        copy_async(ctx, ctx->pk_pinned, device_bufs, bytes, cudaMemcpyDeviceToHost);
+        sync(ctx);
+        for (int b = 0; b < nbufs; b++) {
+            const PackedHeader* h = (const PackedHeader*)(ctx->pk_pinned + (int64_t)b * stride);
+            PG_CHECK_ARG(h->magic == PACKED_MAGIC && h->total_bytes <= stride, "buffer %d is not a packed page of at most %lld bytes", b, (long long)stride);
+            ptrs.push_back(h);
+        }
+    });
+    if (rc != PG_OK) return rc;
+    return pg_hashagg_add_packed(op, ptrs.data(), nbufs);
 }
 
 int32_t pg_hashagg_add_packed(pg_hashagg* op, const void* const* bufs, int32_t nbufs) {

@@ -134,6 +134,7 @@ void jit_launch(pg_ctx* ctx, JitKernel* k, const char* name, int grid, int block
         PG_CUDA(cudaFuncSetAttribute((const void*)k->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k->max_dyn_smem = (int)smem;
     }
+    flush_staged_inputs(ctx);
     pg_kernel_record rec;
     if (ctx->timing) {
         rec.name = name; rec.start = timing_event(ctx); rec.stop = timing_event(ctx);

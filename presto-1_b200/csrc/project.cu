@@ -664,6 +664,7 @@ int32_t pg_project_process(pg_project* p, const pg_col* cols, int32_t ncols, int
             if (type_is_var(c.type)) {
                 PG_CHECK_ARG(o.offsets != nullptr, "output column %d needs an offsets buffer", (int)k);
                 int32_t last = 0;
+                flush_staged_inputs(ctx);
                 PG_CUDA(cudaMemcpyAsync(&last, c.offsets + m, 4, cudaMemcpyDeviceToHost, ctx->stream));
                 sync(ctx);
                 PG_CHECK_ARG(o.values_capacity_bytes >= last, "output column %d needs %d value bytes", (int)k, last);

@@ -136,6 +136,21 @@ class HashAggregationOperator:
         self._finished = True
         return nbytes.value
 
+    def get_output_packed_device(self, device_ptr, capacity):
+        """get_output_packed into device memory (the send buffer of an all-gather)."""
+        groups = self._stats()[0]
+        nbytes, eg = C.c_int64(), C.c_int64(-1)
+        N.check(self.ctx.handle, N.lib().pg_hashagg_get_output_packed_device(self._h, 0, groups, C.c_void_p(device_ptr), capacity, C.byref(nbytes),
+                                                                             C.byref(eg)))
+        self._next_group = groups
+        self._finished = True
+        return nbytes.value
+
+    def add_packed_device(self, device_ptr, stride, count):
+        """`count` packed pages `stride` bytes apart in device memory (an all-gather's receive buffer) as one input page."""
+        assert self.needs_input(), "Operator is already finishing"
+        N.check(self.ctx.handle, N.lib().pg_hashagg_add_packed_device(self._h, C.c_void_p(device_ptr), stride, count))
+
     def add_packed(self, buf_ptrs):
         """Packed pages (one per producer) as one input page, rows in buffer order."""
         assert self.needs_input(), "Operator is already finishing"

@@ -21,7 +21,7 @@ from .exchange import DevicePartitioner, HashPartitionExchange
 from .join import PagesIndex
 from .operators import FINAL, PARTIAL, SINGLE, AggregatorFactory, HashAggregationOperator
 
-PACKED_CAP = 1 << 16      # bytes reserved per rank for one packed intermediate page (4 groups x 10 columns is < 1 KB)
+PACKED_CAP = 1 << 15      # bytes reserved per rank for one packed intermediate page (64 groups x 10 columns fit; 4 groups are < 1 KB)
 
 
 def final_aggregators(aggregators, first_channel):
@@ -37,16 +37,20 @@ def final_aggregators(aggregators, first_channel):
 class PartialFinalAggregation:
     """PARTIAL -> all-gather -> FINAL for a GROUP BY with few groups, as a two-stage pipeline.
 
-    submit(page) runs the PARTIAL step of one page set on the calling thread; its packed intermediate page (pg_hashagg_get_output_packed)
-    is handed to the second stage, which all-gathers the pages of every rank over NCCL and runs the FINAL step — beside the PARTIAL
-    step of the next submit(), the way consecutive page sets overlap in the reference's pipelined plan.  drain() waits for every
-    submitted page set and returns the newest FINAL output.  Each stage has its own pg_ctx (stream); the FINAL workers use
-    high-priority streams."""
+    submit(page) runs the PARTIAL step of one page set on the calling thread; its intermediate page (a few rows) is written as one
+    packed page into device memory (pg_hashagg_get_output_packed_device) and handed to the second stage, which all-gathers the
+    pages of every rank over NCCL device to device and runs the FINAL step (pg_hashagg_add_packed_device -> addIntermediate) —
+    beside the PARTIAL step of the next submit(), the way consecutive page sets overlap in the reference's pipelined plan.
+    drain() waits for every submitted page set and returns the newest FINAL output.  Each stage has its own pg_ctx (stream); the
+    second stage's streams have high priority and `reserve_sms` multiprocessors are kept out of the first stage's persistent
+    kernels so that its few small kernels are not queued behind them.  pipeline=False runs both stages in sequence on the caller's
+    context (no threads)."""
 
     FINAL_WORKERS = 2
+    SLOTS = 8
 
-    def __init__(self, group_by_types, group_by_channels, aggregators, ctx, dist=None, expected_groups=100_000, reserve_sms=8,
-                 input_processor=None):
+    def __init__(self, group_by_types, group_by_channels, aggregators, ctx, dist=None, expected_groups=100_000, reserve_sms=4,
+                 input_processor=None, packed_bytes=PACKED_CAP, pipeline=True):
         import torch
         self.torch, self.dist, self.ctx = torch, dist, ctx
         self.input_processor = input_processor      # fused ScanFilterAndProject in front of the first stage (PageProcessor)
@@ -58,13 +62,18 @@ class PartialFinalAggregation:
         self.results = {}
         self.err = None
         self._threads = []
+        self.packed_bytes = packed_bytes
+        self.pipeline = pipeline and self.world > 1
         if self.world == 1:
             return
         self.device = torch.cuda.current_device()
-        self.q = queue.Queue(maxsize=3)           # bounded: the pinned send / receive buffers rotate over 8 slots
-        self.fqs = [queue.Queue(maxsize=2) for _ in range(self.FINAL_WORKERS)]
+        self.send = [torch.zeros(packed_bytes, dtype=torch.uint8, device="cuda") for _ in range(self.SLOTS)]
+        self.recv = [torch.zeros(packed_bytes * self.world, dtype=torch.uint8, device="cuda") for _ in range(self.SLOTS)]
         self.fctx, self.comm_ctx = [], None
-        self.send_bufs = [torch.zeros(PACKED_CAP, dtype=torch.uint8).pin_memory() for _ in range(8)]
+        if not self.pipeline:
+            return
+        self.q = queue.Queue(maxsize=3)           # bounded: the send / receive buffers rotate over SLOTS slots
+        self.fqs = [queue.Queue(maxsize=2) for _ in range(self.FINAL_WORKERS)]
         ready = threading.Event()
         t = threading.Thread(target=self._comm_loop, args=(ready,), daemon=True)
         t.start()
@@ -77,7 +86,15 @@ class PartialFinalAggregation:
             ev.wait()
             self._threads.append(t)
         if reserve_sms:
-            ctx.reserve_sms(reserve_sms)          # room for the FINAL stage's small kernels beside the persistent PARTIAL kernel
+            ctx.reserve_sms(reserve_sms)
+
+    def _final(self, ctx, recv):
+        fin = HashAggregationOperator(self.types, list(range(len(self.types))), FINAL, self.fin_aggs, expected_groups=1000, ctx=ctx)
+        fin.add_packed_device(recv.data_ptr(), self.packed_bytes, self.world)
+        fin.finish()
+        out = fin.get_output()
+        fin.close()
+        return out
 
     # ---- stage 1 (calling thread)
     def submit(self, page):
@@ -86,16 +103,20 @@ class PartialFinalAggregation:
                                      input_processor=self.input_processor)
         op.add_input(page)
         op.finish()
-        if self.world == 1:
-            self.results = {self.submitted: op.get_output()}
-            op.close()
-            self.submitted += 1
-            return
-        buf = self.send_bufs[self.submitted % len(self.send_bufs)]
-        op.get_output_packed(buf.data_ptr(), PACKED_CAP)
-        op.close()
-        self.q.put((self.submitted, buf))
+        k = self.submitted
         self.submitted += 1
+        if self.world == 1:
+            self.results = {k: op.get_output()}
+            op.close()
+            return
+        slot = k % self.SLOTS
+        op.get_output_packed_device(self.send[slot].data_ptr(), self.packed_bytes)      # complete (synchronised) when this returns
+        op.close()
+        if self.pipeline:
+            self.q.put((k, slot))
+            return
+        self.dist.all_gather_into_tensor(self.recv[slot], self.send[slot])       # stream-ordered before the FINAL step's reads
+        self.results = {k: self._final(self.ctx, self.recv[slot])}
 
     # ---- stage 2a: one collective per page set, in submit order on every rank
     def _comm_loop(self, ready):
@@ -105,11 +126,7 @@ class PartialFinalAggregation:
         with torch.cuda.stream(stream):
             from .context import GpuContext
             self.comm_ctx = GpuContext(self.device)
-            send = torch.zeros(PACKED_CAP, dtype=torch.uint8, device="cuda")
-            recv = torch.zeros(PACKED_CAP * self.world, dtype=torch.uint8, device="cuda")
-            recv_host = [torch.zeros(PACKED_CAP * self.world, dtype=torch.uint8).pin_memory() for _ in range(8)]
             ready.set()
-            turn = 0
             while True:
                 item = self.q.get()
                 if item is None:
@@ -117,15 +134,10 @@ class PartialFinalAggregation:
                     return
                 try:
                     if self.err is None:
-                        step, send_host = item
-                        rh = recv_host[turn % len(recv_host)]
-                        turn += 1
-                        send.copy_(send_host, non_blocking=True)
-                        self.dist.all_gather_into_tensor(recv, send)
-                        rh.copy_(recv, non_blocking=True)
-                        torch.cuda.current_stream().synchronize()
-                        base = rh.data_ptr()
-                        self.fqs[step % self.FINAL_WORKERS].put((step, [base + r * PACKED_CAP for r in range(self.world)]))
+                        k, slot = item
+                        self.dist.all_gather_into_tensor(self.recv[slot], self.send[slot])
+                        stream.synchronize()
+                        self.fqs[k % self.FINAL_WORKERS].put((k, slot))
                 except BaseException as e:          # surfaced by drain()
                     self.err = e
                 self.q.task_done()
@@ -147,19 +159,15 @@ class PartialFinalAggregation:
                     return
                 try:
                     if self.err is None:
-                        step, ptrs = item
-                        fin = HashAggregationOperator(self.types, list(range(len(self.types))), FINAL, self.fin_aggs, expected_groups=1000, ctx=ctx)
-                        fin.add_packed(ptrs)
-                        fin.finish()
-                        self.results[step] = fin.get_output()
-                        fin.close()
-                        self.results.pop(step - 8, None)
+                        k, slot = item
+                        self.results[k] = self._final(ctx, self.recv[slot])
+                        self.results.pop(k - self.SLOTS, None)
                 except BaseException as e:
                     self.err = e
                 fq.task_done()
 
     def drain(self):
-        if self.world > 1:
+        if self.pipeline:
             self.q.join()
             for fq in self.fqs:
                 fq.join()
@@ -169,12 +177,12 @@ class PartialFinalAggregation:
 
     def launch_count(self):
         """Kernels launched by the second stage's contexts (the first stage's are counted on the caller's ctx)."""
-        if self.world == 1:
+        if not self.pipeline:
             return 0
         return self.comm_ctx.launch_count() + sum(c.launch_count() for c in self.fctx)
 
     def close(self):
-        if self.world == 1:
+        if not self.pipeline:
             return
         self.q.put(None)
         for fq in self.fqs:
@@ -182,6 +190,7 @@ class PartialFinalAggregation:
         for t in self._threads:
             t.join(timeout=10)
         self._threads = []
+        self.pipeline = False
 
 
 class PartitionedAggregation:

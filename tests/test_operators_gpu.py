@@ -416,6 +416,9 @@ def test_packed_pages_carry_partial_output_to_final(pgpu):
     n = page.position_count
     cuts = [0, n // 3, n // 3 + 11, n]
     bufs, pages = [], []
+    import torch
+    STRIDE = 1 << 15
+    dev_pages = torch.zeros(3 * STRIDE, dtype=torch.uint8, device="cuda")
     for lo, hi in zip(cuts[:-1], cuts[1:]):
         blocks = [b.slice(lo, hi) if hasattr(b, "slice") else None for b in page.blocks]
         if any(b is None for b in blocks):
@@ -431,6 +434,13 @@ def test_packed_pages_carry_partial_output_to_final(pgpu):
                 nb = op.get_output_packed(buf.ctypes.data, buf.nbytes)
                 assert 0 < nb <= buf.nbytes and int(buf[:8].view(np.int64)[0]) == nb
                 bufs.append(buf)
+                # the same page written into device memory (slot len(bufs)-1 of an all-gather style receive buffer): same size and
+                # header (bytes behind the used part of a variable width value area are undefined, so contents are compared below
+                # through what a FINAL operator makes of them)
+                op._finished, op._next_group = False, 0
+                slot = dev_pages[(len(bufs) - 1) * STRIDE:]
+                assert op.get_output_packed_device(slot.data_ptr(), STRIDE) == nb
+                assert np.array_equal(slot[:24].cpu().numpy(), buf[:24])
             else:
                 pages += drain(op)
             op.close()
@@ -447,6 +457,10 @@ def test_packed_pages_carry_partial_output_to_final(pgpu):
     f2.finish()
     got, want = rows_of(drain(f1)), rows_of(drain(f2))
     assert got == want and len(got) > 0
+    f3 = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs)
+    f3.add_packed_device(dev_pages.data_ptr(), STRIDE, 3)
+    f3.finish()
+    assert rows_of(drain(f3)) == want
     single = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.SINGLE, aggs)
     single.add_input(page)
     single.finish()

@@ -6,7 +6,7 @@ import torch
 import presto_b200 as P
 from presto_b200 import tpch
 from presto_b200.blocks import Block
-import bench
+from presto_b200.plans import final_aggregators
 
 sf = float(sys.argv[1]) if len(sys.argv) > 1 else 1
 world = int(sys.argv[2]) if len(sys.argv) > 2 else 2
@@ -14,8 +14,9 @@ ctx = P.GpuContext(0)
 cols = tpch.lineitem(sf, seed=42, device="cuda")
 page = tpch.q1_page(cols)
 aggs = tpch.q1_aggregators()
-fin_aggs = bench.final_aggs_for(P, aggs, 2)
-part = bench.run_single_pass(P, page, aggs, P.PARTIAL, ctx)
+fin_aggs = final_aggregators(aggs, 2)
+_op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.PARTIAL, aggs, ctx=ctx)
+_op.add_input(page); _op.finish(); part = _op.get_output(); _op.close()
 blocks = []
 for b in part.blocks:
     hb = b.to_host()
@@ -53,12 +54,6 @@ rep = ctx.kernel_report(reset=True)
 for k, v in sorted(rep.items(), key=lambda kv: -kv[1][0]):
     print("%-44s %8.4f ms/step  %5.1f launches/step" % (k, v[0] / 10, v[1] / 10))
 ctx.set_timing(False)
-# the PARTIAL pass itself, for comparison with SINGLE
-for step, name in ((P.SINGLE, "SINGLE"), (P.PARTIAL, "PARTIAL")):
-    torch.cuda.synchronize(); t = time.perf_counter()
-    for it in range(20):
-        bench.run_single_pass(P, page, aggs, step, ctx)
-    torch.cuda.synchronize(); print("%s pass: %.3f ms" % (name, (time.perf_counter() - t) / 20 * 1e3))
 import cProfile, pstats
 pr = cProfile.Profile(); pr.enable()
 for it in range(50):

@@ -240,8 +240,14 @@ class Env:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         out = None
+        trace = os.environ.get("PRESTOGPU_BENCH_TRACE") == "1"
+        t_prev = time.perf_counter()
         for _ in range(steps):
             out = fn()
+            if trace:
+                t_now = time.perf_counter()
+                print("[trace] rank %d step wall %.3f ms" % (self.rank, (t_now - t_prev) * 1e3), file=sys.stderr, flush=True)
+                t_prev = t_now
         if drain:
             out = drain()
         e1.record()

@@ -322,6 +322,12 @@ PG_API int32_t pg_partition_destroy(pg_partitioner* pt);
 PG_API int32_t pg_partition_scatter(pg_partitioner* pt, const pg_col* in, pg_col_out* out);
 PG_API int32_t pg_partition_scatter_peers(pg_partitioner* pt, const pg_col* in, void* const* peer_values, uint8_t* const* peer_nulls,
                                           const int64_t* peer_row_offset);
+/* The whole page in one launch: every fixed width column (at most 16 per call) is staged tile by tile in shared memory and stored
+ * into the receivers' buffers.  peer_values / peer_nulls hold ncols x nparts pointers ([c * nparts + p]); a column whose
+ * peer_nulls[c * nparts] is NULL travels without a mask.  Stream-ordered: it returns after the launch, and a barrier on the same
+ * stream (as in presto-1_b200/exchange.py) must order the stores before the receivers read. */
+PG_API int32_t pg_partition_scatter_peers_all(pg_partitioner* pt, const pg_col* cols, int32_t ncols, void* const* peer_values,
+                                              uint8_t* const* peer_nulls, const int64_t* peer_row_offset);
 PG_API int32_t pg_partition_ids(pg_partitioner* pt, uint8_t* out, int32_t out_mem);
 
 /* pg_partition_positions_noalloc — NO COUNTERPART IN THE REFERENCE; added for callers that

@@ -112,6 +112,7 @@ _PROTOS = {
     "pg_partition_destroy": (I32, [P]),
     "pg_partition_scatter": (I32, [P, PCOL, PCOLOUT]),
     "pg_partition_scatter_peers": (I32, [P, PCOL, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), PI64]),
+    "pg_partition_scatter_peers_all": (I32, [P, PCOL, I32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), PI64]),
     "pg_partition_ids": (I32, [P, P, I32]),
     "pg_partition_positions_noalloc": (I32, [P, P, I64, I32, I32, P, P, P]),
     "pg_joinbuild_create": (I32, [P, PI32, I32, PI32, I32, I32, I64, C.POINTER(P)]),

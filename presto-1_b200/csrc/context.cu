@@ -173,6 +173,7 @@ int32_t pg_ctx_create(int32_t device, pg_ctx** out) {
 int32_t pg_ctx_destroy(pg_ctx* ctx) {
     if (!ctx) return PG_OK;
     cudaSetDevice(ctx->device);
+    pg::big_cache_clear(ctx);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
     if (ctx->out_dev) cudaFree(ctx->out_dev);
@@ -191,6 +192,7 @@ const char* pg_last_error(pg_ctx* ctx) { return ctx ? ctx->err.c_str() : "null c
 
 int32_t pg_ctx_set_stream(pg_ctx* ctx, void* cuda_stream) {
     if (!ctx) return PG_E_INVALID_ARGUMENT;
+    if (ctx->stream != (cudaStream_t)cuda_stream) { cudaSetDevice(ctx->device); pg::big_cache_clear(ctx); }   // cached blocks are ordered on the old stream
     ctx->stream = (cudaStream_t)cuda_stream;
     return PG_OK;
 }

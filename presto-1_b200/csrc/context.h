@@ -47,6 +47,12 @@ struct pg_ctx {
     // landing zone for packed pages that arrive in device memory (pg_hashagg_add_packed_device): pinned, grown on demand
     char* pk_pinned = nullptr;
     int64_t pk_cap = 0;
+    // large freed device blocks kept for the next request of about the same size (DevBuf): a join table / aggregation state of
+    // several GB is re-created for every page set, and the driver's pool, once other allocations have been carved out of the
+    // freed block, stitches a new one together at 5..10 ms per GB.  All blocks belong to this context's stream.
+    struct big_block { void* p; int64_t bytes; };
+    std::vector<big_block> big_cache;
+    int64_t big_cached_bytes = 0;
     int guard_depth = 0;
     int out_live = 0;              // output-arena pieces handed to an OutStage that has not given them back yet
 };
@@ -136,33 +142,69 @@ static inline int32_t guard(pg_ctx* ctx, F&& f) {
 }
 
 // Stream-ordered device buffer (cudaMallocAsync on the context stream).
+static const int64_t BIG_BLOCK = 64LL << 20;        // blocks from this size on go through the context's cache
+static const size_t BIG_CACHE_ENTRIES = 12;
+static const int64_t BIG_CACHE_BYTES = 48LL << 30;
+static inline void big_cache_drop(pg_ctx* c, size_t i) {
+    cudaFreeAsync(c->big_cache[i].p, c->stream);
+    c->big_cached_bytes -= c->big_cache[i].bytes;
+    c->big_cache.erase(c->big_cache.begin() + (long)i);
+}
+static inline void big_cache_clear(pg_ctx* c) { while (!c->big_cache.empty()) big_cache_drop(c, c->big_cache.size() - 1); }
+
 struct DevBuf {
     pg_ctx* ctx = nullptr;
     void* p = nullptr;
     int64_t bytes = 0;
+    int64_t block = 0;       // size of the underlying block when it came from / goes back to the big-block cache (>= bytes)
     DevBuf() {}
     DevBuf(pg_ctx* c, int64_t nbytes) { alloc(c, nbytes); }
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
-    DevBuf(DevBuf&& o) noexcept { ctx = o.ctx; p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+    DevBuf(DevBuf&& o) noexcept { ctx = o.ctx; p = o.p; bytes = o.bytes; block = o.block; o.p = nullptr; o.bytes = 0; o.block = 0; }
     DevBuf& operator=(DevBuf&& o) noexcept {
-        if (this != &o) { release(); ctx = o.ctx; p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+        if (this != &o) { release(); ctx = o.ctx; p = o.p; bytes = o.bytes; block = o.block; o.p = nullptr; o.bytes = 0; o.block = 0; }
         return *this;
     }
     ~DevBuf() { release(); }
     void alloc(pg_ctx* c, int64_t nbytes) {
         release();
-        ctx = c; bytes = nbytes;
-        if (nbytes > 0) {
-            cudaError_t e = cudaMallocAsync(&p, (size_t)nbytes, c->stream);
-            if (e != cudaSuccess) {
-                p = nullptr; bytes = 0; cudaGetLastError();
-                fail(PG_E_INSUFFICIENT_RESOURCES, "device allocation of %lld bytes failed: %s", (long long)nbytes, cudaGetErrorString(e));
+        ctx = c; bytes = nbytes; block = 0;
+        if (nbytes <= 0) return;
+        if (nbytes >= BIG_BLOCK) {
+            block = nbytes;
+            size_t best = (size_t)-1;        // the smallest cached block that holds the request without wasting more than a quarter
+            for (size_t i = 0; i < c->big_cache.size(); i++) {
+                const int64_t b = c->big_cache[i].bytes;
+                if (b >= nbytes && b <= nbytes + nbytes / 4 && (best == (size_t)-1 || b < c->big_cache[best].bytes)) best = i;
             }
+            if (best != (size_t)-1) {
+                p = c->big_cache[best].p; block = c->big_cache[best].bytes;
+                c->big_cached_bytes -= block;
+                c->big_cache.erase(c->big_cache.begin() + (long)best);
+                return;
+            }
+        }
+        cudaError_t e = cudaMallocAsync(&p, (size_t)nbytes, c->stream);
+        if (e != cudaSuccess && !c->big_cache.empty()) {       // give the cached blocks back and try once more
+            cudaGetLastError();
+            big_cache_clear(c);
+            cudaStreamSynchronize(c->stream);
+            e = cudaMallocAsync(&p, (size_t)nbytes, c->stream);
+        }
+        if (e != cudaSuccess) {
+            p = nullptr; bytes = 0; block = 0; cudaGetLastError();
+            fail(PG_E_INSUFFICIENT_RESOURCES, "device allocation of %lld bytes failed: %s", (long long)nbytes, cudaGetErrorString(e));
         }
     }
     void release() {
-        if (p) { cudaFreeAsync(p, ctx->stream); p = nullptr; bytes = 0; }
+        if (!p) return;
+        if (block >= BIG_BLOCK && block <= BIG_CACHE_BYTES / 2) {
+            ctx->big_cache.push_back(pg_ctx::big_block{p, block});
+            ctx->big_cached_bytes += block;
+            while (ctx->big_cache.size() > BIG_CACHE_ENTRIES || ctx->big_cached_bytes > BIG_CACHE_BYTES) big_cache_drop(ctx, 0);   // oldest first
+        } else cudaFreeAsync(p, ctx->stream);
+        p = nullptr; bytes = 0; block = 0;
     }
     // grow to at least nbytes keeping the first keep_bytes
     void grow(pg_ctx* c, int64_t nbytes, int64_t keep_bytes) {

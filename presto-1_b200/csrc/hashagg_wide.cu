@@ -199,6 +199,207 @@ __global__ void wide_gather_kernel(WideView v, GatherPlan p, const uint32_t* buc
     }
 }
 
+// ---- reordering a page for locality (rows in random key order against a table far larger than the L2).
+// A row's bucket index is ((fmix64(key) >> 32) * cap) >> 32, monotone in the hash, so the top bits of fmix64(key) name a contiguous
+// slice of the table.  The page's columns are rewritten partition-major by those bits (a counting pass and a scattering pass, order
+// inside a partition left to the atomics): the fused kernel then works through one L2-sized slice of the table at a time instead of
+// taking an HBM (and TLB) miss per row.  First-seen order survives because every row keeps its page index (row_ids).
+const int RE_THREADS = 512, RE_ITEMS = 16, RE_TILE = RE_THREADS * RE_ITEMS, RE_MAX_COLS = 72, RE_MAX_P = 1024;
+struct ReorderCols {
+    int32_t ncols, pad;
+    const void* in[RE_MAX_COLS];
+    void* out[RE_MAX_COLS];
+    int32_t width[RE_MAX_COLS];      // 1, 4 or 8 (a 16-byte column is listed as two 8-byte halves with stride 2)
+    int32_t stride[RE_MAX_COLS];     // elements of `width` bytes per row
+    int32_t offset[RE_MAX_COLS];     // element inside the row
+};
+__device__ __forceinline__ int re_part(const long long* keys, const uint8_t* key_nulls, int64_t row, int shift) {
+    if (key_nulls && key_nulls[row]) return 0;
+    return (int)(w_fmix64((unsigned long long)__ldg(keys + row)) >> shift);
+}
+__global__ void __launch_bounds__(RE_THREADS) wide_reorder_hist_kernel(const long long* keys, const uint8_t* key_nulls, int64_t n, int shift, int P,
+                                                                       unsigned long long* hist) {
+    __shared__ unsigned int h[RE_MAX_P];
+    for (int t = threadIdx.x; t < P; t += RE_THREADS) h[t] = 0;
+    __syncthreads();
+    const int64_t ntiles = (n + RE_TILE - 1) / RE_TILE;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t base = tile * RE_TILE;
+#pragma unroll 8
+        for (int j = 0; j < RE_ITEMS; j++) {
+            const int64_t row = base + (int64_t)j * RE_THREADS + threadIdx.x;
+            if (row < n) atomicAdd(&h[re_part(keys, key_nulls, row, shift)], 1u);
+        }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < P; t += RE_THREADS) if (h[t]) atomicAdd(&hist[t], (unsigned long long)h[t]);
+}
+// exclusive prefix of the P partition sizes -> first destination row of every partition (one block of RE_MAX_P threads)
+__global__ void __launch_bounds__(RE_MAX_P) wide_reorder_scan_kernel(const unsigned long long* hist, int P, unsigned long long* cursor) {
+    __shared__ unsigned long long warp_tot[RE_MAX_P / 32];
+    const int t = threadIdx.x, lane = t & 31, wid = t >> 5;
+    const unsigned long long v = t < P ? hist[t] : 0;
+    unsigned long long incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    unsigned long long off = 0;
+    for (int k = 0; k < wid; k++) off += warp_tot[k];
+    if (t < P) cursor[t] = off + incl - v;
+}
+// One tile of RE_TILE rows per block.  The tile's rows are ranked per partition with shared-memory atomics, the tile reserves a
+// run of destination rows in every partition with one global atomic each, and every column then passes through a shared-memory
+// staging area laid out partition-major, so that consecutive threads store consecutive destination rows (runs of
+// RE_TILE / P rows: whole sectors instead of one partial sector per row).
+template <typename T>
+__device__ __forceinline__ void re_move_column(const T* __restrict__ in, T* __restrict__ out, int stride, int offset, int64_t base, int rows,
+                                               const unsigned short* lpos, T* stage, const uint32_t* s_dest) {
+#pragma unroll
+    for (int j = 0; j < RE_ITEMS; j++) {
+        const int i = j * RE_THREADS + threadIdx.x;
+        if (i < rows) stage[lpos[j]] = in[(base + i) * stride + offset];
+    }
+    __syncthreads();
+    for (int l = threadIdx.x; l < rows; l += RE_THREADS) out[(int64_t)s_dest[l] * stride + offset] = stage[l];
+    __syncthreads();
+}
+__global__ void __launch_bounds__(RE_THREADS) wide_reorder_scatter_kernel(ReorderCols cols, const long long* keys, const uint8_t* key_nulls, int64_t n,
+                                                                          int shift, int P, unsigned long long* cursor, uint32_t* row_ids) {
+    extern __shared__ __align__(16) unsigned char re_smem[];
+    unsigned long long* stage = (unsigned long long*)re_smem;                  // RE_TILE x 8 bytes
+    uint32_t* s_dest = (uint32_t*)(re_smem + (size_t)RE_TILE * 8);             // destination row of every staged place
+    unsigned int* cnt = s_dest + RE_TILE;                                      // P: rows of the tile per partition, then its first staged place
+    unsigned int* gfirst = cnt + RE_MAX_P;                                     // P: first destination row reserved for the tile
+    __shared__ unsigned int warp_tot[RE_THREADS / 32];
+    for (int t = threadIdx.x; t < P; t += RE_THREADS) cnt[t] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * RE_TILE;
+    const int rows = (int)((n - base) < RE_TILE ? (n - base) : RE_TILE);
+    uint32_t pr[RE_ITEMS];       // partition << 16 | rank inside the tile's rows of that partition
+#pragma unroll
+    for (int j = 0; j < RE_ITEMS; j++) {
+        const int i = j * RE_THREADS + threadIdx.x;
+        pr[j] = 0;
+        if (i < rows) {
+            const int p = re_part(keys, key_nulls, base + i, shift);
+            pr[j] = ((uint32_t)p << 16) | atomicAdd(&cnt[p], 1u);
+        }
+    }
+    __syncthreads();
+    // exclusive scan of cnt[0..P) (two bins per thread), and the tile's reservation in every partition
+    {
+        const int t0 = threadIdx.x * 2;
+        const unsigned int c0 = t0 < P ? cnt[t0] : 0u, c1 = t0 + 1 < P ? cnt[t0 + 1] : 0u;
+        if (c0) gfirst[t0] = (unsigned int)atomicAdd(&cursor[t0], (unsigned long long)c0);
+        if (c1) gfirst[t0 + 1] = (unsigned int)atomicAdd(&cursor[t0 + 1], (unsigned long long)c1);
+        const unsigned int mine = c0 + c1;
+        unsigned int incl = mine;
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const unsigned int o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+        if (lane == 31) warp_tot[wid] = incl;
+        __syncthreads();
+        unsigned int off = 0;
+        for (int k = 0; k < wid; k++) off += warp_tot[k];
+        if (t0 < P) cnt[t0] = off + incl - mine;
+        if (t0 + 1 < P) cnt[t0 + 1] = off + incl - mine + c0;
+    }
+    __syncthreads();
+    unsigned short lpos[RE_ITEMS];
+    uint32_t* stage32 = (uint32_t*)stage;
+#pragma unroll
+    for (int j = 0; j < RE_ITEMS; j++) {
+        const int i = j * RE_THREADS + threadIdx.x;
+        lpos[j] = 0;
+        if (i < rows) {
+            const uint32_t p = pr[j] >> 16, r = pr[j] & 0xffffu;
+            const uint32_t l = cnt[p] + r;
+            lpos[j] = (unsigned short)l;
+            s_dest[l] = gfirst[p] + r;
+            stage32[l] = (uint32_t)(base + i);
+        }
+    }
+    __syncthreads();
+    for (int l = threadIdx.x; l < rows; l += RE_THREADS) row_ids[s_dest[l]] = stage32[l];
+    __syncthreads();
+    for (int c = 0; c < cols.ncols; c++) {
+        switch (cols.width[c]) {
+            case 1: re_move_column<uint8_t>((const uint8_t*)cols.in[c], (uint8_t*)cols.out[c], cols.stride[c], cols.offset[c], base, rows, lpos, (uint8_t*)stage, s_dest); break;
+            case 4: re_move_column<uint32_t>((const uint32_t*)cols.in[c], (uint32_t*)cols.out[c], cols.stride[c], cols.offset[c], base, rows, lpos, (uint32_t*)stage, s_dest); break;
+            default: re_move_column<unsigned long long>((const unsigned long long*)cols.in[c], (unsigned long long*)cols.out[c], cols.stride[c], cols.offset[c], base, rows, lpos, stage, s_dest);
+        }
+    }
+}
+const size_t RE_SMEM = (size_t)RE_TILE * 8 + (size_t)RE_TILE * 4 + 2 * RE_MAX_P * 4;
+
+struct Reordered {
+    std::vector<DevBuf> bufs;
+    DevBuf row_ids;
+    DCol key;
+    std::vector<DCol> args, masks;
+};
+int in_kind_width(int k) { return k == IN_NONE ? 0 : k == IN_I32 ? 4 : k == IN_DEC128 ? 16 : 8; }
+
+// true when the page was rewritten (out holds the reordered columns and the row ids)
+bool reorder_for_locality(WideTable* w, const DCol& key, const DCol* args_cols, const DCol* masks, int64_t n, Reordered& out) {
+    pg_ctx* ctx = w->ctx;
+    const char* env = getenv("PRESTOGPU_WIDE_REORDER");
+    if (env && env[0] == '0') return false;
+    const int64_t table_bytes = w->cap * (int64_t)w->bucket_words * 8;
+    int64_t min_rows = 4 << 20, slice = 32 << 20;
+    if (const char* e = getenv("PRESTOGPU_WIDE_REORDER_MIN_ROWS")) min_rows = atoll(e);
+    if (const char* e = getenv("PRESTOGPU_WIDE_REORDER_SLICE_MB")) slice = atoll(e) << 20;
+    if (w->range || w->split || n < min_rows || n >= (1LL << 32) || table_bytes < 8 * slice) return false;
+    int logp = 4;
+    while (logp < 10 && (table_bytes >> logp) > slice) logp++;
+    const int P = 1 << logp, shift = 64 - logp;
+    ReorderCols rc;
+    memset(&rc, 0, sizeof(rc));
+    auto add = [&](const void* in, int width) -> void* {
+        if (!in) return nullptr;
+        const int pieces = width == 16 ? 2 : 1;          // a 16-byte column moves as two 8-byte halves
+        PG_CHECK_STATE(rc.ncols + pieces <= RE_MAX_COLS, "too many columns to reorder");
+        out.bufs.emplace_back(ctx, (n + 4) * (int64_t)width);
+        void* o = out.bufs.back().p;
+        for (int h = 0; h < pieces; h++) {
+            rc.in[rc.ncols] = in; rc.out[rc.ncols] = o; rc.width[rc.ncols] = width == 16 ? 8 : width; rc.stride[rc.ncols] = pieces; rc.offset[rc.ncols] = h;
+            rc.ncols++;
+        }
+        return o;
+    };
+    out.bufs.reserve(RE_MAX_COLS);
+    out.key = key;
+    out.key.values = add(key.values, 8);
+    out.key.nulls = (const uint8_t*)add(key.nulls, 1);
+    out.args.assign(args_cols, args_cols + w->aggs.size());
+    out.masks.assign(masks, masks + w->aggs.size());
+    for (size_t i = 0; i < w->aggs.size(); i++) {
+        const int width = in_kind_width(w->aggs[i].in_kind);
+        if (width) out.args[i].values = add(args_cols[i].values, width);
+        out.args[i].nulls = (const uint8_t*)add(args_cols[i].nulls, 1);       // count(column) reads the null mask without the values
+        out.masks[i].values = add(masks[i].values, 1);
+        out.masks[i].nulls = (const uint8_t*)add(masks[i].nulls, 1);
+    }
+    out.row_ids.alloc(ctx, (n + 4) * 4);
+    DevBuf hist(ctx, 2 * RE_MAX_P * 8);
+    memset_async(ctx, hist.p, 0, 2 * RE_MAX_P * 8);
+    unsigned long long* d_hist = hist.as<unsigned long long>();
+    unsigned long long* d_cursor = d_hist + RE_MAX_P;
+    const int64_t ntiles = (n + RE_TILE - 1) / RE_TILE;
+    const int hgrid = (int)std::min<int64_t>(ntiles, (int64_t)ctx->sm_count * 8);
+    PG_LAUNCH(ctx, wide_reorder_hist_kernel, hgrid, RE_THREADS, 0, (const long long*)key.values, key.nulls, n, shift, P, d_hist);
+    PG_LAUNCH(ctx, wide_reorder_scan_kernel, 1, RE_MAX_P, 0, d_hist, P, d_cursor);
+    static bool smem_set = false;
+    if (!smem_set) {
+        PG_CUDA(cudaFuncSetAttribute((const void*)wide_reorder_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RE_SMEM));
+        smem_set = true;
+    }
+    PG_LAUNCH(ctx, wide_reorder_scatter_kernel, (int)ntiles, RE_THREADS, RE_SMEM, rc, (const long long*)key.values, key.nulls, n, shift, P, d_cursor,
+              out.row_ids.as<uint32_t>());
+    return true;
+}
+
 // ---- split mode (the default with a front region; PRESTOGPU_WIDE_SPLIT=0/1 overrides), first kernel: where does every row's state live?
 // wide_locate_kernel reads ONLY the keys, finds or claims the bucket of every run of equal keys (the same warp-uniform rounds as
 // jit/wide_body.cuh) and writes one 32-bit bucket number per row: [0, F) front region, [F, F + cap) table, F + cap the null key,
@@ -554,12 +755,17 @@ WideTable* wide_create(pg_ctx* ctx, const std::vector<pg_agg_spec>& specs, const
     return w;
 }
 
-bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const DCol* masks, int64_t n, int64_t row_base) {
+bool wide_add_page(WideTable* w, const DCol& key_in, const DCol* args_in, const DCol* masks_in, int64_t n, int64_t row_base) {
     pg_ctx* ctx = w->ctx;
     if (n <= 0) return true;
     PG_CHECK_STATE(!w->prepared, "the operator already produced output");
     if (row_base + n >= (1LL << 32))   // limb sums are exact for < 2^32 rows per group
         fail(PG_E_INSUFFICIENT_RESOURCES, "more than 2^32 rows in one aggregation operator instance");
+    Reordered re;
+    const bool reordered = reorder_for_locality(w, key_in, args_in, masks_in, n, re);
+    const DCol& key = reordered ? re.key : key_in;
+    const DCol* args_cols = reordered ? re.args.data() : args_in;
+    const DCol* masks = reordered ? re.masks.data() : masks_in;
     // ---- source
     std::string pre;
     char buf[320];
@@ -574,6 +780,10 @@ bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const D
              key.nulls ? 1 : 0, w->flag_word, vec);
     pre += buf;
     pre += w->range ? "#define PGW_RANGE 1\n" : "#define PGW_RANGE 0\n";
+    // reordered pages: first-seen order from the carried row ids, and tiles handed out in page order (an atomic counter) so that all
+    // resident blocks work inside the same few table slices
+    pre += reordered ? (getenv("PRESTOGPU_WIDE_NOPEEK") ? "#define PGW_ROWIDS 1\n#define PGW_DYNAMIC 1\n#define PGW_PEEK 0\n" : "#define PGW_ROWIDS 1\n#define PGW_DYNAMIC 1\n#define PGW_PEEK 1\n")
+                     : "#define PGW_ROWIDS 0\n#define PGW_DYNAMIC 0\n#define PGW_PEEK 0\n";
     int minb = 3;
     if (const char* e = getenv("PRESTOGPU_WIDE_MINB")) { if (atoi(e) >= 1 && atoi(e) <= 8) minb = atoi(e); }
     snprintf(buf, sizeof(buf), "#define PGW_MINB %d\n#define PGW_PREFETCH %d\n#define PGW_LDCA %d\n", minb, getenv("PRESTOGPU_WIDE_NOPF") ? 0 : 1,
@@ -621,6 +831,7 @@ bool wide_add_page(WideTable* w, const DCol& key, const DCol* args_cols, const D
         a.mask[i] = (const unsigned char*)masks[i].values; a.mask_nulls[i] = masks[i].values ? masks[i].nulls : nullptr;
     }
     a.n = n; a.row_base = row_base;
+    a.row_ids = reordered ? re.row_ids.as<uint32_t>() : nullptr;
     a.counters = w->counters.as<unsigned long long>();
     a.front = w->front.as<unsigned long long>(); a.front_keys = w->front_keys.as<unsigned long long>(); a.k0 = w->k0; a.nseg = (unsigned long long)w->nseg; a.shift = w->shift;
     DevBuf flags[2];               // left-out markers: written by launch i, read as the row filter by launch i + 1

@@ -33,6 +33,9 @@ struct PgwArgs {
     // front region first, then the table and its two extra buckets; >= 0xFFFFFFFE: the row is not handled by this launch
     const unsigned int* bidx;
     unsigned long long front_buckets;
+    // PGW_ROWIDS: the page was reordered for locality (hashagg_wide.cu: reorder_for_locality); row i of the arrays above is row
+    // row_ids[i] of the page the caller handed in, and that index is what first-seen order is built from
+    const unsigned int* row_ids;
 };
 
 #endif

@@ -22,6 +22,15 @@
 #ifndef PGW_LDCA
 #define PGW_LDCA 1
 #endif
+#ifndef PGW_ROWIDS
+#define PGW_ROWIDS 0
+#endif
+#ifndef PGW_DYNAMIC
+#define PGW_DYNAMIC 0
+#endif
+#ifndef PGW_PEEK
+#define PGW_PEEK 0      // read (key, ~first row) of the bucket before any atomic: a hit needs no compare-and-swap, and no atomicMax when
+#endif                  // the stored first row is already the smaller one (both words only ever move one way, so a stale read is safe)
 typedef unsigned long long u64;
 typedef long long i64;
 typedef unsigned int u32;
@@ -185,11 +194,20 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
     bool live[V];
 #pragma unroll
     for (int j = 0; j < V; j++) { first_row[j] = r0 + j; live[j] = valid[j]; }
+#if PGW_ROWIDS
+    {
+        u32 rid[V];
+        if constexpr (V == 1) rid[0] = __ldg(args.row_ids + r0);
+        else { const uint4 t = __ldg((const uint4*)(args.row_ids + r0)); rid[0] = t.x; rid[1] = t.y; rid[2] = t.z; rid[3] = t.w; }
+#pragma unroll
+        for (int j = 0; j < V; j++) first_row[j] = (i64)rid[j];
+    }
+#endif
 #pragma unroll
     for (int j = 1; j < V; j++) {
         if (valid[j] && valid[j - 1] && isnull[j] == isnull[j - 1] && (isnull[j] || key[j] == key[j - 1])) {
             live[j - 1] = false;
-            first_row[j] = first_row[j - 1];
+            first_row[j] = PGW_ROWIDS ? (first_row[j - 1] < first_row[j] ? first_row[j - 1] : first_row[j]) : first_row[j - 1];
 #define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT) \
             PGW_CAT(cn, a)[j] += PGW_CAT(cn, a)[j - 1]; PGW_MERGE_##OP##_##IN(a)
             PGW_AGGS(PG_X)
@@ -213,9 +231,10 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
     u32 idx[V];
     u32 st[V];                       // 0 settled (bucket found, or left out), 1 walking its front chunk, 2 at a free front bucket, 3 probing `table`
     u64 old[V];
+    bool first_known[V];             // PGW_PEEK: the bucket already records a first row at or before this run's
 #pragma unroll
     for (int j = 0; j < V; j++) {
-        bp[j] = nullptr; idx[j] = 0; old[j] = 1; st[j] = 0;
+        bp[j] = nullptr; idx[j] = 0; old[j] = 1; st[j] = 0; first_known[j] = false;
         if (!live[j]) continue;
         if (isnull[j] || key[j] == 0) bp[j] = args.table + (cap + (isnull[j] ? 0 : 1)) * PGW_BUCKET_WORDS;
         else st[j] = 3;
@@ -290,7 +309,14 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
             for (int j = 0; j < V; j++) {
                 if (st[j] != 3) continue;
                 u64* bk = args.table + (i64)idx[j] * PGW_BUCKET_WORDS;
+#if PGW_PEEK
+                const ulonglong2 seen = ld_cg2(bk);
+                old[j] = seen.x;
+                if (seen.x == key[j]) { if (seen.y >= ~(u64)(args.row_base + first_row[j])) first_known[j] = true; }
+                else if (seen.x == 0 && allowed) old[j] = atomicCAS(bk, 0ULL, key[j]);
+#else
                 old[j] = allowed ? atomicCAS(bk, 0ULL, key[j]) : __ldcg(bk);
+#endif
             }
             bool more = false;
 #pragma unroll
@@ -323,7 +349,12 @@ __device__ __forceinline__ void process_rows(const PgwArgs& args, const i64 r0, 
 #endif
         if (b == nullptr) continue;
         u64 flag_bits = 0;
-        if (live[j]) atomicMax(b + 1, ~(u64)(args.row_base + first_row[j]));   // smallest row index wins (stored inverted, zero = never seen)
+#if PGW_PEEK && !PGW_BIDX
+        const bool skip_first = first_known[j];
+#else
+        const bool skip_first = false;
+#endif
+        if (live[j] && !skip_first) atomicMax(b + 1, ~(u64)(args.row_base + first_row[j]));   // smallest row index wins (stored inverted, zero = never seen)
 #define PG_X(a, OP, IN, HASMASK, HASMASKNULLS, HASARGNULLS, CNTMODE, CNTWORD, VALWORD, FLAGBIT)                  \
         if (live[j] && PGW_CAT(cn, a)[j]) { PGW_CNT_##CNTMODE(a, CNTWORD, FLAGBIT) PGW_EMIT_##OP##_##IN(a, VALWORD) }    \
         if (valid[j]) { PGW_SOLO_##OP##_##IN(a, VALWORD) }
@@ -355,6 +386,23 @@ __device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.gl
 extern "C" __global__ void __launch_bounds__(256, PGW_MINB) pg_wide_agg(const PgwArgs args) {
     u64 left_out = 0, claims = 0, fclaims = 0;
     const i64 n = args.n;
+#if PGW_DYNAMIC
+    // tiles of 4 trips are handed out in page order through counters[3] (zeroed by the host before the launch)
+    __shared__ i64 s_tile;
+    const i64 tile_rows = (i64)blockDim.x * PGW_VEC * 4;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = (i64)atomicAdd(args.counters + 3, 1ULL);
+        __syncthreads();
+        const i64 t0 = s_tile * tile_rows;
+        if (t0 >= n) break;
+#pragma unroll 1
+        for (int k = 0; k < 4; k++) {
+            const i64 r0 = t0 + ((i64)k * blockDim.x + threadIdx.x) * PGW_VEC;
+            if (r0 + PGW_VEC <= n) process_rows<PGW_VEC>(args, r0, left_out, claims, fclaims);
+        }
+    }
+#else
     const i64 stride = (i64)gridDim.x * blockDim.x * PGW_VEC;
     for (i64 r0 = ((i64)blockIdx.x * blockDim.x + threadIdx.x) * PGW_VEC; r0 + PGW_VEC <= n; r0 += stride) {
         if (PGW_PREFETCH && PGW_VEC == 4 && r0 + stride + PGW_VEC <= n) {
@@ -367,6 +415,7 @@ extern "C" __global__ void __launch_bounds__(256, PGW_MINB) pg_wide_agg(const Pg
         }
         process_rows<PGW_VEC>(args, r0, left_out, claims, fclaims);
     }
+#endif
     if (PGW_VEC > 1 && blockIdx.x == 0 && threadIdx.x == 0)
         for (i64 r0 = n - n % PGW_VEC; r0 < n; r0++) process_rows<1>(args, r0, left_out, claims, fclaims);
     // ---- per-block totals

@@ -31,6 +31,16 @@ PG_D int partition_of(int64_t raw, int nparts, int mode, unsigned long long magi
     }
     return (int)xxh64_long((int64_t)bit_reverse64((uint64_t)raw)) & (nparts - 1);
 }
+// Lanes of the warp whose row goes to the same partition as this lane's.  Up to 8 partitions: one ballot per partition (cheaper than
+// __match_any_sync); more: __match_any_sync.  p = -1 (row beyond the page) never matches a real partition.
+PG_D unsigned part_peers(int p, int nparts) {
+    if (nparts <= 8) {
+        unsigned mine = 0;
+        for (int q = 0; q < nparts; q++) { const unsigned b = __ballot_sync(0xffffffffu, p == q); if (p == q) mine = b; }
+        return mine;
+    }
+    return __match_any_sync(0xffffffffu, p);
+}
 PG_D int64_t part_row_hash(const KeyCols& kc, int nkeys, const DCol& hash_col, int has_hash, int64_t row) {
     return has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, nkeys, row);
 }
@@ -56,7 +66,38 @@ __global__ void __launch_bounds__(PART_THREADS) part_hist_kernel(KeyCols kc, int
             part_of_row[row] = (uint8_t)p;
         }
         // one shared-memory atomic per distinct partition in the warp, not one per row
-        const unsigned peers = __match_any_sync(0xffffffffu, p);
+        const unsigned peers = part_peers(p, nparts);
+        if (p >= 0 && (peers & ((1u << lane) - 1u)) == 0) atomicAdd(&hist[p], __popc(peers));
+    }
+    __syncthreads();
+    if (threadIdx.x < nparts) counts[(int64_t)threadIdx.x * ntiles + blockIdx.x] = Pair64{hist[threadIdx.x], 0};
+}
+
+// The common case — one BIGINT key without nulls, no precomputed hash channel: all 16 key loads of a thread are issued before the
+// first hash is computed, and no per-row type dispatch.  Same tile / warp / item order and the same outputs as part_hist_kernel.
+__global__ void __launch_bounds__(PART_THREADS) part_hist_bigint_kernel(const int64_t* __restrict__ keys, int64_t n, int nparts, int mode,
+                                                                        uint8_t* __restrict__ part_of_row, Pair64* __restrict__ counts, int64_t ntiles) {
+    __shared__ int hist[MAX_PARTS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < MAX_PARTS) hist[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * PART_TILE;
+    const unsigned long long magic = 0xFFFFFFFFFFFFFFFFULL / (unsigned long long)nparts;
+    int64_t k[PART_ITEMS];
+#pragma unroll
+    for (int j = 0; j < PART_ITEMS; j++) {
+        const int64_t row = part_row_of(base, warp, j, lane);
+        k[j] = row < n ? __ldg(keys + row) : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < PART_ITEMS; j++) {
+        const int64_t row = part_row_of(base, warp, j, lane);
+        int p = -1;
+        if (row < n) {
+            p = partition_of((int64_t)(31ULL * 0ULL + (uint64_t)long_type_hash(k[j])), nparts, mode, magic);     // keys_row_hash with one channel
+            part_of_row[row] = (uint8_t)p;
+        }
+        const unsigned peers = part_peers(p, nparts);
         if (p >= 0 && (peers & ((1u << lane) - 1u)) == 0) atomicAdd(&hist[p], __popc(peers));
     }
     __syncthreads();
@@ -79,7 +120,7 @@ __global__ void __launch_bounds__(PART_THREADS) part_rank_kernel(const uint8_t* 
         const int64_t row = part_row_of(base, warp, j, lane);
         const int p = row < n ? (int)part_of_row[row] : -1;
         mine[j] = p;
-        const unsigned peers = __match_any_sync(0xffffffffu, p);
+        const unsigned peers = part_peers(p, nparts);
         if (p >= 0 && (peers & ((1u << lane) - 1u)) == 0) warp_cnt[warp][p] += __popc(peers);
         __syncwarp();
     }
@@ -93,7 +134,7 @@ __global__ void __launch_bounds__(PART_THREADS) part_rank_kernel(const uint8_t* 
 #pragma unroll
     for (int j = 0; j < PART_ITEMS; j++) {
         const int p = mine[j];
-        const unsigned peers = __match_any_sync(0xffffffffu, p);
+        const unsigned peers = part_peers(p, nparts);
         const int rank_in_warp = __popc(peers & ((1u << lane) - 1u));
         if (p >= 0) {
             dest[part_row_of(base, warp, j, lane)] = warp_cnt[warp][p] + rank_in_warp;
@@ -183,6 +224,118 @@ __global__ void __launch_bounds__(PART_THREADS) part_scatter_staged_kernel(const
     }
 }
 
+// ---- every column of the page in ONE launch, without the dest[] array.
+// A block owns one tile.  It ranks the tile's rows from part_of_row (the same stable order part_rank_kernel produces), so that row i of
+// the tile gets a place lpos inside a partition-major staging area; then, column after column, the values are staged in shared
+// memory and stored with consecutive threads writing consecutive destination rows of one receiver.  Per row the kernel reads
+// 1 + sum(widths) bytes and writes sum(widths): no dest[] round trip (4 B written + 4 B per column read in the per-column form).
+static const int SC_MAX_COLS = 16;
+struct ScatterTable {                       // lives in device memory (too large for kernel parameters at 64 partitions)
+    int32_t ncols, nparts;
+    int64_t part_start[MAX_PARTS];          // first partition-major row of partition p on this rank
+    int64_t peer_row_offset[MAX_PARTS];     // first row this rank writes in receiver p's buffers
+    const void* in[SC_MAX_COLS];
+    const uint8_t* in_nulls[SC_MAX_COLS];
+    int32_t width[SC_MAX_COLS];
+    void* base[SC_MAX_COLS][MAX_PARTS];
+    uint8_t* nulls[SC_MAX_COLS][MAX_PARTS];
+};
+
+template <typename T>
+PG_D void scatter_all_column(const ScatterTable* tab, int c, int64_t base, int rows, int warp, int lane, const unsigned short* lpos, unsigned char* stage,
+                             const uint8_t* s_q, const long long* s_delta) {
+    T* vals = (T*)stage;
+    uint8_t* nl = (uint8_t*)(vals + PART_TILE);
+    const T* in = (const T*)tab->in[c];
+    const uint8_t* in_nulls = tab->in_nulls[c];
+    const bool out_nulls = tab->nulls[c][0] != nullptr;
+#pragma unroll
+    for (int j = 0; j < PART_ITEMS; j++) {
+        const int i = (warp * PART_ITEMS + j) * 32 + lane;
+        if (i < rows) {
+            vals[lpos[j]] = in[base + i];
+            if (out_nulls) nl[lpos[j]] = in_nulls ? in_nulls[base + i] : 0;
+        }
+    }
+    __syncthreads();
+    for (int l = threadIdx.x; l < rows; l += PART_THREADS) {
+        const int q = s_q[l];
+        const long long d = (long long)l + s_delta[q];
+        ((T*)tab->base[c][q])[d] = vals[l];
+        if (out_nulls) tab->nulls[c][q][d] = nl[l];
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(PART_THREADS) part_scatter_all_kernel(const uint8_t* __restrict__ part_of_row, int64_t n, int nparts,
+                                                                        const Pair64* __restrict__ offsets, int64_t ntiles,
+                                                                        const ScatterTable* __restrict__ tab) {
+    extern __shared__ __align__(16) unsigned char stage[];
+    __shared__ long long s_delta[MAX_PARTS];      // destination row in the receiver's buffer = staged place + s_delta[partition]
+    __shared__ int s_start[MAX_PARTS + 1];        // where partition p starts inside the staged tile
+    __shared__ int warp_cnt[PART_THREADS / 32][MAX_PARTS];
+    __shared__ uint8_t s_q[PART_TILE];            // partition of every staged place
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t tile = blockIdx.x, base = tile * PART_TILE;
+    const int rows = (int)((n - base) < PART_TILE ? (n - base) : PART_TILE);
+    if (threadIdx.x < nparts) {
+        const int q = threadIdx.x;
+        const long long f = offsets[(int64_t)q * ntiles + tile].a;
+        const long long nxt = tile + 1 < ntiles ? offsets[(int64_t)q * ntiles + tile + 1].a : (q + 1 < nparts ? offsets[(int64_t)(q + 1) * ntiles].a : n);
+        s_delta[q] = f;
+        s_start[q + 1] = (int)(nxt - f);
+    }
+    for (int q = lane; q < nparts; q += 32) warp_cnt[warp][q] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_start[0] = 0;
+        for (int q = 0; q < nparts; q++) s_start[q + 1] += s_start[q];
+    }
+    int mine[PART_ITEMS];
+#pragma unroll
+    for (int j = 0; j < PART_ITEMS; j++) {
+        const int i = (warp * PART_ITEMS + j) * 32 + lane;
+        const int p = i < rows ? (int)part_of_row[base + i] : -1;
+        mine[j] = p;
+        const unsigned peers = part_peers(p, nparts);
+        if (p >= 0 && (peers & ((1u << lane) - 1u)) == 0) warp_cnt[warp][p] += __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    for (int q = threadIdx.x; q < nparts; q += PART_THREADS) {
+        int run = s_start[q];
+        for (int w = 0; w < PART_THREADS / 32; w++) { const int cnt = warp_cnt[w][q]; warp_cnt[w][q] = run; run += cnt; }
+        s_delta[q] = s_delta[q] - s_start[q] - tab->part_start[q] + tab->peer_row_offset[q];
+    }
+    __syncthreads();
+    unsigned short lpos[PART_ITEMS];
+#pragma unroll
+    for (int j = 0; j < PART_ITEMS; j++) {
+        const int p = mine[j];
+        const unsigned peers = part_peers(p, nparts);
+        const int rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+        lpos[j] = 0;
+        if (p >= 0) {
+            const int l = warp_cnt[warp][p] + rank_in_warp;
+            lpos[j] = (unsigned short)l;
+            s_q[l] = (uint8_t)p;
+        }
+        __syncwarp();
+        if (p >= 0 && rank_in_warp == 0) warp_cnt[warp][p] += __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    const int ncols = tab->ncols;
+    for (int c = 0; c < ncols; c++) {
+        switch (tab->width[c]) {
+            case 1: scatter_all_column<uint8_t>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta); break;
+            case 4: scatter_all_column<int32_t>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta); break;
+            case 8: scatter_all_column<int64_t>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta); break;
+            default: scatter_all_column<int4>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta);
+        }
+    }
+}
+
 }  // namespace pg
 
 using namespace pg;
@@ -192,9 +345,21 @@ struct pg_partitioner {
     int32_t nparts = 0, mode = 0;
     int64_t n = 0;
     DevBuf part_of_row, dest, counts;
+    bool has_dest = false;      // dest[] is only needed by the per-column scatters: computed on first use (ensure_dest)
     int64_t part_counts[MAX_PARTS];
     int64_t part_start[MAX_PARTS];
 };
+
+// dest[row] = place of the row in partition-major order (stable); one more pass over part_of_row
+static void ensure_dest(pg_partitioner* pt) {
+    if (pt->has_dest || pt->n == 0) return;
+    pg_ctx* ctx = pt->ctx;
+    const int64_t ntiles = (pt->n + PART_TILE - 1) / PART_TILE;
+    pt->dest.alloc(ctx, pt->n * 4);
+    PG_LAUNCH(ctx, part_rank_kernel, (int)ntiles, PART_THREADS, 0, pt->part_of_row.as<uint8_t>(), pt->n, pt->nparts, pt->counts.as<Pair64>(), ntiles,
+              pt->dest.as<int32_t>());
+    pt->has_dest = true;
+}
 
 extern "C" {
 
@@ -223,14 +388,15 @@ int32_t pg_partition_create(pg_ctx* ctx, const pg_col* keys, int32_t nkeys, cons
                 else for (int k = 0; k < nkeys; k++) { import_col(ctx, keys[k], n, imp[k]); kc.c[k] = imp[k].d; }
                 int64_t ntiles = (n + PART_TILE - 1) / PART_TILE;
                 pt->part_of_row.alloc(ctx, n);
-                pt->dest.alloc(ctx, n * 4);
                 pt->counts.alloc(ctx, ((int64_t)nparts * ntiles + 1) * (int64_t)sizeof(Pair64));
                 Pair64* counts = pt->counts.as<Pair64>();
-                PG_LAUNCH(ctx, part_hist_kernel, (int)ntiles, PART_THREADS, 0, kc, nkeys, hc, has_hash, n, nparts, mode,
-                          pt->part_of_row.as<uint8_t>(), counts, ntiles);
+                if (!has_hash && nkeys == 1 && kc.c[0].type == PG_BIGINT && !kc.c[0].nulls)
+                    PG_LAUNCH(ctx, part_hist_bigint_kernel, (int)ntiles, PART_THREADS, 0, (const int64_t*)kc.c[0].values, n, nparts, mode,
+                              pt->part_of_row.as<uint8_t>(), counts, ntiles);
+                else
+                    PG_LAUNCH(ctx, part_hist_kernel, (int)ntiles, PART_THREADS, 0, kc, nkeys, hc, has_hash, n, nparts, mode,
+                              pt->part_of_row.as<uint8_t>(), counts, ntiles);
                 scan_tile_totals(ctx, counts, (int64_t)nparts * ntiles, counts + (int64_t)nparts * ntiles);
-                PG_LAUNCH(ctx, part_rank_kernel, (int)ntiles, PART_THREADS, 0, pt->part_of_row.as<uint8_t>(), n, nparts, counts, ntiles,
-                          pt->dest.as<int32_t>());
                 // partition starts = scanned count of each partition's first tile
                 std::vector<int64_t> starts(nparts);
                 for (int p = 0; p < nparts; p++) copy_async(ctx, &ctx->h_scalar[p], &counts[(int64_t)p * ntiles].a, 8, cudaMemcpyDeviceToHost);
@@ -260,6 +426,7 @@ int32_t pg_partition_scatter(pg_partitioner* pt, const pg_col* in, pg_col_out* o
         if (pt->n == 0) return;
         ColImport ci;
         import_col(ctx, *in, pt->n, ci);
+        ensure_dest(pt);
         int w = type_width(in->type);
         int grid = grid_for(ctx, pt->n, 256, 2);
         const int32_t* dest = pt->dest.as<int32_t>();
@@ -287,6 +454,7 @@ int32_t pg_partition_scatter_peers(pg_partitioner* pt, const pg_col* in, void* c
         if (pt->n == 0) return;
         ColImport ci;
         import_col(ctx, *in, pt->n, ci);
+        ensure_dest(pt);
         ScatterPeers sp;
         memset(&sp, 0, sizeof(sp));
         for (int p = 0; p < pt->nparts; p++) {
@@ -333,6 +501,55 @@ int32_t pg_partition_scatter_peers(pg_partitioner* pt, const pg_col* in, void* c
             }
         }
         sync(ctx);
+    });
+}
+
+/* Fused exchange of a whole page: every (fixed width) column is stored into the receivers' buffers by ONE kernel
+ * (part_scatter_all_kernel).  peer_values / peer_nulls: ncols x nparts pointers, column-major ([c * nparts + p]); a column whose
+ * peer_nulls entries are null travels without a mask.  Stream-ordered: returns after the launch (the caller's barrier on the same
+ * stream orders the stores before the receivers' reads). */
+int32_t pg_partition_scatter_peers_all(pg_partitioner* pt, const pg_col* cols, int32_t ncols, void* const* peer_values, uint8_t* const* peer_nulls,
+                                       const int64_t* peer_row_offset) {
+    if (!pt) return PG_E_INVALID_ARGUMENT;
+    return guard(pt->ctx, [&] {
+        pg_ctx* ctx = pt->ctx;
+        PG_CHECK_ARG(cols && peer_values && peer_row_offset && ncols >= 1 && ncols <= SC_MAX_COLS, "between 1 and %d columns per call", SC_MAX_COLS);
+        if (pt->n == 0) return;
+        std::vector<ColImport> imp(ncols);
+        ScatterTable tab;
+        memset(&tab, 0, sizeof(tab));
+        tab.ncols = ncols; tab.nparts = pt->nparts;
+        int maxw = 1;
+        for (int c = 0; c < ncols; c++) {
+            PG_CHECK_ARG(cols[c].n == pt->n, "column %d has %lld rows, the partitioner %lld", c, (long long)cols[c].n, (long long)pt->n);
+            PG_CHECK_ARG(!type_is_var(cols[c].type), "variable width columns cannot be scattered");
+            import_col(ctx, cols[c], pt->n, imp[c]);
+            tab.in[c] = imp[c].d.values; tab.in_nulls[c] = imp[c].d.nulls; tab.width[c] = type_width(cols[c].type);
+            maxw = std::max(maxw, tab.width[c]);
+            const bool with_nulls = peer_nulls && peer_nulls[(size_t)c * pt->nparts] != nullptr;
+            for (int p = 0; p < pt->nparts; p++) {
+                tab.base[c][p] = peer_values[(size_t)c * pt->nparts + p];
+                tab.nulls[c][p] = with_nulls ? peer_nulls[(size_t)c * pt->nparts + p] : nullptr;
+                PG_CHECK_ARG(tab.base[c][p] && (!with_nulls || tab.nulls[c][p]), "column %d: missing receive buffer of partition %d", c, p);
+            }
+        }
+        for (int p = 0; p < pt->nparts; p++) { tab.part_start[p] = pt->part_start[p]; tab.peer_row_offset[p] = peer_row_offset[p]; }
+        DevBuf own_tab;
+        const ScatterTable* d_tab = (const ScatterTable*)in_arena_stage(ctx, &tab, sizeof(tab));     // reaches the device with the launch's flush
+        if (!d_tab) {
+            own_tab.alloc(ctx, sizeof(tab));
+            copy_async(ctx, own_tab.p, &tab, sizeof(tab), cudaMemcpyHostToDevice);
+            d_tab = (const ScatterTable*)own_tab.p;
+        }
+        const int64_t ntiles = (pt->n + PART_TILE - 1) / PART_TILE;
+        const size_t smem = (size_t)PART_TILE * (maxw + 1);
+        static size_t smem_set = 0;
+        if (smem > smem_set) {
+            PG_CUDA(cudaFuncSetAttribute((const void*)part_scatter_all_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(PART_TILE * 17)));
+            smem_set = (size_t)PART_TILE * 17;
+        }
+        PG_LAUNCH(ctx, part_scatter_all_kernel, (int)ntiles, PART_THREADS, smem, pt->part_of_row.as<uint8_t>(), pt->n, pt->nparts,
+                  pt->counts.as<Pair64>(), ntiles, d_tab);
     });
 }
 

@@ -86,6 +86,8 @@ class _PeerBuffers:
 class HashPartitionExchange:
     """exchange(page) -> the rows of every rank whose key hashes to this rank."""
 
+    MAX_COLS_PER_LAUNCH = 16
+
     def __init__(self, partitioner=None, group=None, device=None, peer="auto"):
         import torch.distributed as dist
         self.dist = dist
@@ -101,6 +103,8 @@ class HashPartitionExchange:
         # peer mode: decided once, by everyone together (a rank that cannot set up symmetric memory takes all ranks to NCCL)
         self.peer = None
         self.peer_why = "not requested"
+        import os as _os
+        self.per_column = _os.environ.get("PRESTOGPU_EXCHANGE_PER_COLUMN", "") == "1"     # the one-kernel-per-column form (kept for comparison)
         if peer and self.backend == "nccl" and self.world > 1:
             import os
             import torch
@@ -157,7 +161,7 @@ class HashPartitionExchange:
             offs = (C.c_int64 * W)(*[int(cm[:me, r].sum()) for r in range(W)])   # where my rows start in rank r's buffer
             out_blocks = []
             pending_views = []
-            first = True
+            srcs, pv, pn, handle = [], [], [], None
             for ci, (b, nullable) in enumerate(zip(blocks, nulls_any)):
                 if b.type in (N.VARCHAR, N.VARBINARY):
                     raise N.PrestoGpuError(N.PG_E_INVALID_ARGUMENT, "variable width columns cannot cross the device exchange")
@@ -166,23 +170,33 @@ class HashPartitionExchange:
                 esz = torch.empty(0, dtype=dt).element_size() * k
                 vbuf, vh = self.peer.get((slot, ci, "v"), max(cap_rows, 1) * esz)
                 nbuf, nh = (self.peer.get((slot, ci, "n"), max(cap_rows, 1)) if nullable else (None, None))
-                if first:
-                    vh.barrier()          # stream-ordered: every rank's earlier readers of its receive buffers are done
-                    first = False
-                pv = (C.c_void_p * W)(*[int(vh.buffer_ptrs[r]) for r in range(W)])
-                pn = (C.c_void_p * W)(*[int(nh.buffer_ptrs[r]) for r in range(W)]) if nullable else None
+                handle = vh
+                pv += [int(vh.buffer_ptrs[r]) for r in range(W)]
+                pn += [int(nh.buffer_ptrs[r]) if nullable else None for r in range(W)]
                 src = b
                 if nullable and b.nulls is None:     # someone else's rows have nulls: mine travel with an all-zero mask
                     src = Block(b.type, b.values, torch.zeros(n, dtype=torch.uint8, device=self.device), None, n, b.precision, b.scale)
-                col = src.pg_col()
-                N.check(ctx.handle, N.lib().pg_partition_scatter_peers(h, C.byref(col), pv, pn, offs))
+                srcs.append(src)
                 vals = vbuf[: n_out * esz].view(dt)
                 nulls = nbuf[:n_out] if nullable else None
                 pending_views.append(len(out_blocks))
                 out_blocks.append(Block(b.type, vals, nulls, None, n_out, b.precision, b.scale))
                 self.bytes_sent += (n - int(counts[me])) * esz
-            if not first:
-                vh.barrier()              # every rank's stores have landed before anyone reads its buffer
+            if handle is not None:
+                handle.barrier()          # stream-ordered: every rank's earlier readers of its receive buffers are done
+                if self.per_column:
+                    for ci, src in enumerate(srcs):
+                        col = src.pg_col()
+                        cv = (C.c_void_p * W)(*pv[ci * W:(ci + 1) * W])
+                        cn = (C.c_void_p * W)(*pn[ci * W:(ci + 1) * W]) if pn[ci * W] is not None else None
+                        N.check(ctx.handle, N.lib().pg_partition_scatter_peers(h, C.byref(col), cv, cn, offs))
+                else:
+                    for c0 in range(0, len(srcs), self.MAX_COLS_PER_LAUNCH):      # one launch stores every column of the page
+                        part = srcs[c0:c0 + self.MAX_COLS_PER_LAUNCH]
+                        cv = (C.c_void_p * (W * len(part)))(*pv[c0 * W:(c0 + len(part)) * W])
+                        cn = (C.c_void_p * (W * len(part)))(*pn[c0 * W:(c0 + len(part)) * W])
+                        N.check(ctx.handle, N.lib().pg_partition_scatter_peers_all(h, col_array(part), len(part), cv, cn, offs))
+                handle.barrier()          # every rank's stores have landed before anyone reads its buffer
             if not lease:                 # the caller may hold this page across later exchanges: give it its own memory
                 for i in pending_views:
                     ob = out_blocks[i]

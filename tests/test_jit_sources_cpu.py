@@ -15,16 +15,16 @@ PLAN = ("#define PGW_AGGS(X) X(0, CNT, NONE, 0, 0, 0, C64, 3, 4, 0) X(1, SUMDEC,
         "X(2, SUMF64, F64, 0, 0, 0, FLAG, 0, 6, 1) X(3, SUMDEC, DEC128, 0, 0, 1, C64, 7, 8, 0)\n")
 
 
-@pytest.mark.parametrize("bidx,rng,quota,vec", [(b, r, q, v) for b, r, q, v in itertools.product((0, 1), (0, 1), (0, 1), (4, 1))
-                                                if not (b == 1 and (q == 1 or r == 0 and v == 1))])
-def test_wide_body_compiles_for_sm_100a(tmp_path, bidx, rng, quota, vec):
+@pytest.mark.parametrize("bidx,rng,quota,vec,rowids", [(b, r, q, v, 0) for b, r, q, v in itertools.product((0, 1), (0, 1), (0, 1), (4, 1))
+                                                       if not (b == 1 and (q == 1 or r == 0 and v == 1))] + [(0, 0, 0, 4, 1), (0, 0, 1, 1, 1)])
+def test_wide_body_compiles_for_sm_100a(tmp_path, bidx, rng, quota, vec, rowids):
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         pytest.skip("nvcc not available")
     src = tmp_path / "w.cu"
     src.write_text("#define PGW_BUCKET_WORDS 12\n#define PGW_HASKEYNULL 1\n#define PGW_FLAGWORD 2\n#define PGW_VEC %d\n#define PGW_RANGE %d\n"
-                   "#define PGW_BIDX %d\n#define PGW_HASONLY %d\n#define PGW_QUOTA %d\n#define PGW_FLAGS_UNCONDITIONAL 0\n%s"
-                   "#include \"%s/wide_args.h\"\n#include \"%s/wide_body.cuh\"\n" % (vec, rng, bidx, 0 if bidx else quota, quota, PLAN, JIT, JIT))
+                   "#define PGW_BIDX %d\n#define PGW_HASONLY %d\n#define PGW_QUOTA %d\n#define PGW_FLAGS_UNCONDITIONAL 0\n#define PGW_ROWIDS %d\n#define PGW_DYNAMIC %d\n#define PGW_PEEK %d\n%s"
+                   "#include \"%s/wide_args.h\"\n#include \"%s/wide_body.cuh\"\n" % (vec, rng, bidx, 0 if bidx else quota, quota, rowids, rowids, rowids, PLAN, JIT, JIT))
     r = subprocess.run([nvcc, "-arch=sm_100a", "-std=c++17", "-cubin", "-o", str(tmp_path / "w.cubin"), str(src)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-2000:]
 

@@ -287,10 +287,10 @@ def _assert_rows_equal(got, want):
                 assert x == y
 
 
-@pytest.mark.parametrize("split", ["1", "0"])
+@pytest.mark.parametrize("split,reorder", [("1", False), ("0", False), ("0", True)])
 @pytest.mark.parametrize("expected_groups", [100, 400_000])
 @pytest.mark.parametrize("clustered", [False, True])
-def test_many_groups_bigint_key_matches_oracle_in_first_seen_order(pgpu, monkeypatch, expected_groups, clustered, split):
+def test_many_groups_bigint_key_matches_oracle_in_first_seen_order(pgpu, monkeypatch, expected_groups, clustered, split, reorder):
     """cfg3 shape: GROUP BY one BIGINT key with many groups takes the bucket-resident-state path (hashagg_wide.cu).
     Output order must be the reference's first-seen group-id order, across pages; key 0, the null key, negative values,
     null arguments, a mask, long decimals and table growth (expected_groups=100) are all in play."""
@@ -319,6 +319,11 @@ def test_many_groups_bigint_key_matches_oracle_in_first_seen_order(pgpu, monkeyp
     pages = [page(lo, hi) for lo, hi in bounds]
     monkeypatch.setenv("PRESTOGPU_WIDE", "1")      # clustered input would otherwise stay on the general path
     monkeypatch.setenv("PRESTOGPU_WIDE_SPLIT", split)   # locate + update kernels (default) / one fused kernel
+    if reorder:      # pages rewritten partition-major by hash prefix before the fused kernel (normally only for >= 4 Mi rows, tables >= 128 MB)
+        monkeypatch.setenv("PRESTOGPU_WIDE_REORDER_MIN_ROWS", "5")
+        monkeypatch.setenv("PRESTOGPU_WIDE_REORDER_SLICE_MB", "0")
+    else:
+        monkeypatch.setenv("PRESTOGPU_WIDE_REORDER", "0")
     op = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=expected_groups)
     op.ctx.kernel_report(reset=True)
     op.ctx.set_timing(True)
@@ -329,6 +334,7 @@ def test_many_groups_bigint_key_matches_oracle_in_first_seen_order(pgpu, monkeyp
     seen = op.ctx.kernel_report(reset=True)
     op.ctx.set_timing(False)
     assert "wide_agg_jit" in seen or "wide_update_jit" in seen, "the many-groups path was not taken: %s" % sorted(seen)
+    assert ("wide_reorder_scatter_kernel" in seen) == reorder, sorted(seen)
     got = rows_of(drain(op))
     want = _oracle_rows(P, None, pages, aggs)
     _assert_rows_equal(got, want)

@@ -44,7 +44,7 @@ KERNEL_BYTES = {
     "j_build_fast_kernel": 8 + 16,               # key, slot write (the payload stays where addPage put it)
     "j_build_kernel": 8 + 16,
     "j_probe_dense_kernel": 8 + 16 + 4 + 8,      # key, slot, probe idx out, build position out
-    "j_probe_gather_kernel": 44,                 # fused probe + gather (the whole model)
+    "j_probe_dense_kernel<true>": 44,            # fused probe + gather (the whole model: pg_lookup_join_page)
     "j_gather_fixed_kernel": 8 + 8 + 8,          # build position in, payload gather, payload out
 }
 
@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-workloads", action="store_true", help="headline only (skips the SF100 GROUP BY orderkey / join records)")
+    ap.add_argument("--no-crosscheck", action="store_true", help="skip the small-scale oracle cross-checks (profiling runs)")
     ap.add_argument("--only", default="", help="comma list of workloads to run: groupby,join (default both)")
     return ap.parse_args()
 
@@ -624,7 +625,7 @@ def gpu_arm(args):
     torch.cuda.empty_cache()
     workloads, xchk = None, None
     if not args.no_workloads:
-        xchk = crosschecks(env)
+        xchk = None if args.no_crosscheck else crosschecks(env)
         workloads = wide_workloads(args, env, traffic)
 
     if rank == 0:

@@ -127,6 +127,11 @@ PG_API int32_t pg_groupby_contains(pg_groupby* gb, const pg_col* keys, const pg_
  * out_hash (int64[n], may be NULL) receives the raw-hash channel / getRawHash(groupId) (:85). */
 PG_API int32_t pg_groupby_export_keys(pg_groupby* gb, int64_t first, int64_t n, pg_col_out* out_keys,
                                       int64_t* out_hash, int32_t hash_mem);
+/* UpdateMemory (OP/UpdateMemory.java, consulted by tryRehash: OP/BigintGroupByHash.java:295-334, MultiChannelGroupByHash.java:
+ * 369-420) as a byte limit: once set (> 0), get_group_ids / add_page return PG_NEED_MEMORY — BEFORE consuming any row, the table
+ * unchanged — when the page could force the table to grow past the limit (every row counted as a new group).  The caller gets the
+ * memory (raises the limit) and hands the same page in again: Work.process() returning false, at page granularity. */
+PG_API int32_t pg_groupby_set_memory_limit(pg_groupby* gb, int64_t bytes);
 /* bytes needed for variable-width key `key` over all groups (to size pg_col_out.values) */
 PG_API int32_t pg_groupby_varwidth_bytes(pg_groupby* gb, int32_t key, int64_t* out_bytes);
 /* getGroupCount / getCapacity / getHashCollisions / getEstimatedSize (OP/GroupByHash.java:61-87).
@@ -202,6 +207,16 @@ PG_API int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t 
  * (LookupJoinPageBuilder.appendRow :76-84): gathers build columns; position -1 -> null. */
 PG_API int32_t pg_lookup_gather(pg_lookup* ls, const int64_t* build_pos, int32_t pos_mem, int64_t n, const int32_t* channels,
                                 int32_t nchannels, pg_col_out* out);
+/* LookupJoinOperator's step for one probe page in ONE call: JoinProbe + LookupSource.appendTo of `build_channels`
+ * (OP/LookupJoinOperator.java:333-361, OP/JoinProbe.java:40-116, PagesHashStrategy.appendTo).  out_probe_idx[capacity] (memory kind
+ * out_mem) receives the probe positions; out_build[k] (capacity >= `capacity` rows each; a variable width channel additionally
+ * needs values_capacity_bytes >= the bytes pg_lookup_gather_var_bytes reports, so callers with such channels use the two-step
+ * form) receives build channel build_channels[k] of the matched rows, null for PROBE_OUTER misses.  Unique single-BIGINT-key
+ * build sides with device outputs run one kernel and never materialise 64-bit build positions; every other case runs
+ * pg_lookup_probe + pg_lookup_gather internally.  PG_NEED_MEMORY (nothing consumed, *n_out = rows needed) as in pg_lookup_probe. */
+PG_API int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, const pg_col* hash_col, int64_t n, int32_t join_type,
+                                   const int32_t* build_channels, int32_t nchannels, int32_t* out_probe_idx, int32_t out_mem,
+                                   pg_col_out* out_build, int64_t capacity, int64_t* n_out);
 /* value bytes pg_lookup_gather will write for a variable width build channel */
 PG_API int32_t pg_lookup_gather_var_bytes(pg_lookup* ls, const int64_t* build_pos, int32_t pos_mem, int64_t n, int32_t channel,
                                           int64_t* out_bytes);
@@ -236,6 +251,10 @@ PG_API int32_t pg_hashagg_output_types(pg_hashagg* op, int32_t* types, int32_t c
 /* buildResult() for group ids [first, first+n) */
 PG_API int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_out* out, int64_t* error_group);
 PG_API int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* out_bytes);
+/* The operator's memory yield (HashAggregationOperator.addInput -> unfinishedWork, OP/HashAggregationOperator.java:398-417;
+ * InMemoryHashAggregationBuilder.updateMemoryWithYieldInfo): with a limit set, add_page returns PG_NEED_MEMORY before consuming
+ * anything when the page could grow the operator's table past it; same contract as pg_groupby_set_memory_limit. */
+PG_API int32_t pg_hashagg_set_memory_limit(pg_hashagg* op, int64_t bytes);
 /* partial-aggregation flush: forget all groups (OP/HashAggregationOperator.java:501-517) */
 PG_API int32_t pg_hashagg_reset(pg_hashagg* op);
 /* The output page of group ids [first, first+n) written as ONE self-describing host buffer, and its counterpart that adds several

@@ -10,16 +10,10 @@ package io.trino.gpu;
 import io.trino.operator.Operator;
 import io.trino.operator.OperatorContext;
 import io.trino.spi.Page;
-import io.trino.spi.block.Block;
-import io.trino.spi.block.ByteArrayBlock;
-import io.trino.spi.block.Int128ArrayBlock;
-import io.trino.spi.block.IntArrayBlock;
-import io.trino.spi.block.LongArrayBlock;
-import io.trino.spi.block.VariableWidthBlock;
+import io.trino.spi.type.Type;
 
-import java.util.Optional;
+import java.util.List;
 
-import static io.airlift.slice.Slices.wrappedBuffer;
 import static io.trino.gpu.PrestoGpu.check;
 
 public class GpuHashAggregationOperator
@@ -30,19 +24,43 @@ public class GpuHashAggregationOperator
     private final OperatorContext operatorContext;
     private final long ctx;
     private final long handle;
+    private final List<Type> inputTypes;
+    private final int[] allChannels;
     private final int[] outputTypes;
+    private final boolean partial;
+    private final long maxPartialMemory;
+    private PageArrays unfinished;    // unfinishedWork (HashAggregationOperator.java:398-417): a page the memory limit has not let in yet
+    private long grantedBytes;
     private boolean finishing;
+    private boolean flushing;         // partial aggregation over its memory budget: emit what is there, then reset (:501-517)
     private long outputCursor = -1;   // -1: not producing output yet
     private long groupCount;
 
-    public GpuHashAggregationOperator(OperatorContext operatorContext, long ctx, int[] keyChannels, int[] keyTypes, int hashChannel, int[] aggSpecs, int step, long expectedGroups, int[] outputTypes)
+    public GpuHashAggregationOperator(OperatorContext operatorContext, long ctx, List<Type> inputTypes, int[] keyChannels, int[] keyTypes, int hashChannel,
+            int[] aggSpecs, int step, long expectedGroups, long maxPartialMemory, int[] outputTypes)
     {
         this.operatorContext = operatorContext;
         this.ctx = ctx;
+        this.inputTypes = List.copyOf(inputTypes);
+        this.allChannels = new int[inputTypes.size()];
+        for (int c = 0; c < allChannels.length; c++) {
+            allChannels[c] = c;
+        }
         this.outputTypes = outputTypes;
+        this.partial = step == PrestoGpu.STEP_PARTIAL;
+        this.maxPartialMemory = maxPartialMemory;
         long[] out = new long[1];
         check(ctx, PrestoGpu.hashaggCreate(ctx, keyChannels, keyTypes, hashChannel, aggSpecs, step, expectedGroups, out));
         this.handle = out[0];
+        this.grantedBytes = stats()[2];
+        check(ctx, PrestoGpu.hashaggSetMemoryLimit(handle, grantedBytes));
+    }
+
+    private long[] stats()
+    {
+        long[] s = new long[4];
+        check(ctx, PrestoGpu.hashaggStats(handle, s));
+        return s;
     }
 
     @Override
@@ -54,31 +72,41 @@ public class GpuHashAggregationOperator
     @Override
     public boolean needsInput()
     {
-        return !finishing && outputCursor < 0;   // HashAggregationOperator.java:367-378
+        return !finishing && !flushing && unfinished == null && outputCursor < 0;   // HashAggregationOperator.java:367-378
+    }
+
+    /** unfinishedWork.process(): true when no page is waiting any more.  Memory is asked for where the CPU builder's
+     *  updateMemoryWithYieldInfo would (InMemoryHashAggregationBuilder.java:189-214): a refused reservation leaves the page waiting. */
+    private boolean processUnfinished()
+    {
+        while (unfinished != null) {
+            PageArrays a = unfinished;
+            int status = PrestoGpu.hashaggAddPage(handle, a.types, a.values, a.nulls, a.offsets, a.arrayOffsets, a.positionCount);
+            if (status == PrestoGpu.PG_NEED_MEMORY) {
+                long wanted = grantedBytes * 2;
+                if (!operatorContext.localUserMemoryContext().trySetBytes(wanted)) {
+                    return false;        // the driver yields; getOutput() / the next addInput attempt tries again
+                }
+                grantedBytes = wanted;
+                check(ctx, PrestoGpu.hashaggSetMemoryLimit(handle, grantedBytes));
+                continue;
+            }
+            check(ctx, status);
+            unfinished = null;
+            long[] s = stats();
+            operatorContext.localSystemMemoryContext().setBytes(s[2]);   // device bytes are not JVM heap
+            if (partial && s[2] > maxPartialMemory) {
+                flushing = true;
+            }
+        }
+        return true;
     }
 
     @Override
     public void addInput(Page page)
     {
-        int channels = page.getChannelCount();
-        int[] types = new int[channels];
-        Object[] values = new Object[channels];
-        Object[] nulls = new Object[channels];
-        Object[] offsets = new Object[channels];
-        int[] arrayOffsets = new int[channels];
-        for (int c = 0; c < channels; c++) {
-            // BlockArrays flattens Dictionary/RLE/Lazy blocks (getLoadedBlock + copyPositions) and exposes the backing arrays
-            BlockArrays arrays = BlockArrays.of(page.getBlock(c));
-            types[c] = arrays.typeTag;
-            values[c] = arrays.values;
-            nulls[c] = arrays.valueIsNull;
-            offsets[c] = arrays.offsets;
-            arrayOffsets[c] = arrays.arrayOffset;
-        }
-        check(ctx, PrestoGpu.hashaggAddPage(handle, types, values, nulls, offsets, arrayOffsets, page.getPositionCount()));
-        long[] stats = new long[4];
-        check(ctx, PrestoGpu.hashaggStats(handle, stats));
-        operatorContext.localSystemMemoryContext().setBytes(stats[2]);   // device bytes are not JVM heap
+        unfinished = PageArrays.of(page, allChannels, inputTypes);
+        processUnfinished();
     }
 
     @Override
@@ -90,52 +118,44 @@ public class GpuHashAggregationOperator
     @Override
     public Page getOutput()
     {
-        if (!finishing) {
+        if (!processUnfinished()) {
+            return null;                  // :473-481
+        }
+        if (!finishing && !flushing) {
             return null;
         }
         if (outputCursor < 0) {
-            long[] stats = new long[4];
-            check(ctx, PrestoGpu.hashaggStats(handle, stats));
-            groupCount = stats[0];
+            groupCount = stats()[0];
             outputCursor = 0;
         }
         if (outputCursor >= groupCount) {
+            if (flushing && !finishing) {   // partial flush done: forget the groups and take input again
+                check(ctx, PrestoGpu.hashaggReset(handle));
+                flushing = false;
+                outputCursor = -1;
+            }
             return null;
         }
         int n = (int) Math.min(OUTPUT_PAGE_ROWS, groupCount - outputCursor);
-        OutputArrays out = OutputArrays.allocate(outputTypes, n);      // long[]/int[]/byte[] + boolean[] per channel
+        long[] varBytes = new long[outputTypes.length];
+        for (int c = 0; c < outputTypes.length; c++) {
+            if (outputTypes[c] == PrestoGpu.VARCHAR || outputTypes[c] == PrestoGpu.VARBINARY) {
+                long[] b = new long[1];
+                check(ctx, PrestoGpu.hashaggVarwidthBytes(handle, c, b));
+                varBytes[c] = b[0];
+            }
+        }
+        OutputArrays out = OutputArrays.allocate(outputTypes, n, varBytes);      // long[]/int[]/byte[] + boolean[] per channel
         long[] errorGroup = new long[1];
         check(ctx, PrestoGpu.hashaggGetOutput(handle, outputCursor, n, outputTypes, out.values, out.nulls, out.offsets, out.valueBytes, errorGroup));
         outputCursor += n;
-        Block[] blocks = new Block[outputTypes.length];
-        for (int c = 0; c < blocks.length; c++) {
-            Optional<boolean[]> isNull = Optional.ofNullable((boolean[]) out.nulls[c]);
-            switch (outputTypes[c]) {
-                case PrestoGpu.INTEGER:
-                case PrestoGpu.DATE:
-                    blocks[c] = new IntArrayBlock(n, isNull, (int[]) out.values[c]);
-                    break;
-                case PrestoGpu.LONG_DECIMAL:
-                    blocks[c] = new Int128ArrayBlock(n, isNull, (long[]) out.values[c]);
-                    break;
-                case PrestoGpu.VARCHAR:
-                case PrestoGpu.VARBINARY:
-                    blocks[c] = new VariableWidthBlock(n, wrappedBuffer((byte[]) out.values[c]), (int[]) out.offsets[c], isNull);
-                    break;
-                case PrestoGpu.BOOLEAN:
-                    blocks[c] = new ByteArrayBlock(n, isNull, (byte[]) out.values[c]);
-                    break;
-                default:
-                    blocks[c] = new LongArrayBlock(n, isNull, (long[]) out.values[c]);
-            }
-        }
-        return new Page(n, blocks);
+        return new Page(n, PageArrays.toBlocks(outputTypes, out, n));
     }
 
     @Override
     public boolean isFinished()
     {
-        return finishing && outputCursor >= 0 && outputCursor >= groupCount;
+        return finishing && unfinished == null && outputCursor >= 0 && outputCursor >= groupCount;
     }
 
     @Override

@@ -1,8 +1,10 @@
 /* prestogpu_jni.c — JNI shim between io.trino.gpu.PrestoGpu (integration/java) and libprestogpu.so (include/prestogpu.h).
+ * One wrapper per pg_* entry point (tests/test_boundary_cpu.py checks the list against the header).
  *
- * NOT built in this repository: the image has no JDK (no jni.h).  A maintainer builds it next to the reference with
+ * The image has no JDK: tests/test_boundary_cpu.py compiles this file against tests/jni_stub/jni.h (the JNI types and the
+ * function table entries used here) so that it cannot rot; a maintainer builds it next to the reference with
  *   gcc -shared -fPIC -I$JAVA_HOME/include -I$JAVA_HOME/include/linux -Iinclude \
- *       integration/jni/prestogpu_jni.c -Lpresto-1_b200 -lprestogpu -o libprestogpu_jni.so
+ *       integration/jni/prestogpu_jni.c integration/jni/prestogpu_jni_ops.c -Lpresto-1_b200 -lprestogpu -o libprestogpu_jni.so
  *
  * Conventions
  *  - handles travel as jlong; every native returns the pg status, Java turns non-zero into TrinoException
@@ -10,238 +12,185 @@
  *    PG_E_NUMERIC_OVERFLOW -> NUMERIC_VALUE_OUT_OF_RANGE, PG_E_INVALID_ARGUMENT -> IllegalArgumentException, ...
  *  - a Block crosses as its backing arrays: long[]/int[]/byte[] values, boolean[] valueIsNull (1 byte per element in
  *    HotSpot), int[] offsets, plus arrayOffset and positionCount (LongArrayBlock.java:37-76, VariableWidthBlock.java:38-48).
- *    Arrays are pinned with GetPrimitiveArrayCritical only for the duration of the call; the library copies to the device
- *    before returning (include/prestogpu.h, "ownership").
+ *  - NO array is pinned while the library runs.  Inputs are copied into a thread-local native staging buffer with
+ *    Get<Type>ArrayRegion (a page is <= 1 MiB) and outputs are written by the library into staging and copied back with
+ *    Set<Type>ArrayRegion: GetPrimitiveArrayCritical would hold the garbage collector off for the duration of GPU
+ *    synchronisations inside the call.
  */
-#include <jni.h>
-#include <stdint.h>
-#include <string.h>
-#include "prestogpu.h"
+#include "prestogpu_jni.h"
 
-#define MAX_COLS 64
+/* ---------------------------------------------------------------- staging */
+static __thread pgj_arena tl_in, tl_out;
 
-typedef struct {
-    jarray values, nulls, offsets;
-    void *pv, *pn, *po;
-} pinned_col;
+static int arena_reserve(pgj_arena* a, size_t bytes) {
+    a->used = 0;
+    if (bytes <= a->cap) return 1;
+    size_t cap = a->cap ? a->cap : (1u << 20);
+    while (cap < bytes) cap *= 2;
+    char* p = (char*)realloc(a->p, cap);
+    if (!p) return 0;
+    a->p = p; a->cap = cap;
+    return 1;
+}
+static void* arena_take(pgj_arena* a, size_t bytes) {
+    size_t at = (a->used + 63) & ~(size_t)63;
+    a->used = at + bytes;
+    return a->p + at;
+}
+static size_t padded(size_t bytes) { return (bytes + 63 + 64) & ~(size_t)63; }
 
-/* Java side passes parallel arrays describing the page's channels: types[], values[] (Object[] of primitive arrays),
- * nulls[] (Object[] of boolean[] or null), offsets[] (Object[] of int[] or null), arrayOffsets[]. */
-static int pin_page(JNIEnv* env, jintArray jtypes, jobjectArray jvalues, jobjectArray jnulls, jobjectArray joffsets,
-                    jintArray jarray_offsets, jlong n, pg_col* cols, pinned_col* pins, int* ncols_out) {
-    jsize ncols = (*env)->GetArrayLength(env, jtypes);
-    if (ncols > MAX_COLS) return PG_E_INVALID_ARGUMENT;
-    jint types[MAX_COLS], aoff[MAX_COLS];
+int pgj_type_width(int t) {
+    switch (t) {
+        case PG_INTEGER: case PG_DATE: return 4;
+        case PG_LONG_DECIMAL: return 16;
+        case PG_BOOLEAN: return 1;
+        case PG_VARCHAR: case PG_VARBINARY: return 0;
+        default: return 8;
+    }
+}
+static int is_var(int t) { return t == PG_VARCHAR || t == PG_VARBINARY; }
+
+/* copies `count` elements of `width` bytes starting at element `start` of a primitive array of the matching Java type */
+static void copy_in(JNIEnv* env, jarray arr, int width, jsize start, jsize count, void* dst) {
+    if (count <= 0) return;
+    switch (width) {
+        case 1: (*env)->GetByteArrayRegion(env, (jbyteArray)arr, start, count, (jbyte*)dst); break;
+        case 4: (*env)->GetIntArrayRegion(env, (jintArray)arr, start, count, (jint*)dst); break;
+        case 16: (*env)->GetLongArrayRegion(env, (jlongArray)arr, 2 * start, 2 * count, (jlong*)dst); break;   /* Int128ArrayBlock: long[2n] */
+        default: (*env)->GetLongArrayRegion(env, (jlongArray)arr, start, count, (jlong*)dst);
+    }
+}
+static void copy_out(JNIEnv* env, jarray arr, int width, jsize count, const void* src) {
+    if (count <= 0) return;
+    switch (width) {
+        case 1: (*env)->SetByteArrayRegion(env, (jbyteArray)arr, 0, count, (const jbyte*)src); break;
+        case 4: (*env)->SetIntArrayRegion(env, (jintArray)arr, 0, count, (const jint*)src); break;
+        case 16: (*env)->SetLongArrayRegion(env, (jlongArray)arr, 0, 2 * count, (const jlong*)src); break;
+        default: (*env)->SetLongArrayRegion(env, (jlongArray)arr, 0, count, (const jlong*)src);
+    }
+}
+
+/* A page: parallel arrays types[], values[] (Object[] of primitive arrays), nulls[] (Object[] of boolean[] or null),
+ * offsets[] (Object[] of int[] or null), arrayOffsets[].  Everything is copied into tl_in; cols[] point there. */
+int pgj_page_in(JNIEnv* env, jintArray jtypes, jobjectArray jvalues, jobjectArray jnulls, jobjectArray joffsets, jintArray jarray_offsets,
+                jlong n, pg_col* cols, int* ncols_out) {
+    const jsize ncols = (*env)->GetArrayLength(env, jtypes);
+    *ncols_out = 0;
+    if (ncols > PGJ_MAX_COLS || n < 0 || n > 0x7fffffff) return PG_E_INVALID_ARGUMENT;
+    jint types[PGJ_MAX_COLS], aoff[PGJ_MAX_COLS];
+    jarray av[PGJ_MAX_COLS], an[PGJ_MAX_COLS], ao[PGJ_MAX_COLS];
+    jint first_byte[PGJ_MAX_COLS], end_byte[PGJ_MAX_COLS];
     (*env)->GetIntArrayRegion(env, jtypes, 0, ncols, types);
     (*env)->GetIntArrayRegion(env, jarray_offsets, 0, ncols, aoff);
+    size_t total = 64;
     for (jsize c = 0; c < ncols; c++) {
-        pinned_col* p = &pins[c];
-        memset(p, 0, sizeof(*p));
-        p->values = (jarray)(*env)->GetObjectArrayElement(env, jvalues, c);
-        p->nulls = (jarray)(*env)->GetObjectArrayElement(env, jnulls, c);
-        p->offsets = (jarray)(*env)->GetObjectArrayElement(env, joffsets, c);
+        av[c] = (jarray)(*env)->GetObjectArrayElement(env, jvalues, c);
+        an[c] = jnulls ? (jarray)(*env)->GetObjectArrayElement(env, jnulls, c) : NULL;
+        ao[c] = joffsets ? (jarray)(*env)->GetObjectArrayElement(env, joffsets, c) : NULL;
+        if (!av[c] && n > 0) return PG_E_INVALID_ARGUMENT;
+        first_byte[c] = end_byte[c] = 0;
+        if (is_var(types[c])) {
+            if (!ao[c]) return PG_E_INVALID_ARGUMENT;
+            (*env)->GetIntArrayRegion(env, (jintArray)ao[c], aoff[c], 1, &first_byte[c]);
+            (*env)->GetIntArrayRegion(env, (jintArray)ao[c], aoff[c] + (jsize)n, 1, &end_byte[c]);
+            total += padded((size_t)(end_byte[c] - first_byte[c])) + padded(((size_t)n + 1) * 4);
+        } else total += padded((size_t)n * (size_t)pgj_type_width(types[c]));
+        if (an[c]) total += padded((size_t)n);
     }
-    /* no JNI calls other than Get/ReleasePrimitiveArrayCritical between here and unpin_page */
+    if (!arena_reserve(&tl_in, total)) return PG_E_INSUFFICIENT_RESOURCES;
     for (jsize c = 0; c < ncols; c++) {
-        pinned_col* p = &pins[c];
-        p->pv = p->values ? (*env)->GetPrimitiveArrayCritical(env, p->values, NULL) : NULL;
-        p->pn = p->nulls ? (*env)->GetPrimitiveArrayCritical(env, p->nulls, NULL) : NULL;
-        p->po = p->offsets ? (*env)->GetPrimitiveArrayCritical(env, p->offsets, NULL) : NULL;
         pg_col* col = &cols[c];
         memset(col, 0, sizeof(*col));
-        col->type = types[c];
-        col->mem = PG_MEM_HOST;
-        col->n = n;
-        size_t width = (types[c] == PG_INTEGER || types[c] == PG_DATE) ? 4 : (types[c] == PG_LONG_DECIMAL) ? 16 :
-                       (types[c] == PG_BOOLEAN) ? 1 : 8;
-        if (types[c] == PG_VARCHAR || types[c] == PG_VARBINARY) {
-            col->values = p->pv;                                   /* Slice bytes; offsets are absolute */
-            col->offsets = (const int32_t*)p->po + aoff[c];
+        col->type = types[c]; col->mem = PG_MEM_HOST; col->n = n;
+        if (is_var(types[c])) {
+            const jsize nbytes = end_byte[c] - first_byte[c];
+            void* bytes = arena_take(&tl_in, (size_t)nbytes);
+            int32_t* offs = (int32_t*)arena_take(&tl_in, ((size_t)n + 1) * 4);
+            if (av[c]) copy_in(env, av[c], 1, first_byte[c], nbytes, bytes);       /* only the Slice range this page refers to */
+            (*env)->GetIntArrayRegion(env, (jintArray)ao[c], aoff[c], (jsize)n + 1, (jint*)offs);
+            for (jlong i = 0; i <= n; i++) offs[i] -= first_byte[c];
+            col->values = bytes; col->offsets = offs;
         } else {
-            col->values = (const char*)p->pv + (size_t)aoff[c] * width;
+            const int w = pgj_type_width(types[c]);
+            void* v = arena_take(&tl_in, (size_t)n * (size_t)w);
+            if (av[c]) copy_in(env, av[c], w, aoff[c], (jsize)n, v);
+            col->values = v;
         }
-        col->nulls = p->pn ? (const uint8_t*)p->pn + aoff[c] : NULL;
+        if (an[c]) {
+            void* nl = arena_take(&tl_in, (size_t)n);
+            (*env)->GetBooleanArrayRegion(env, (jbooleanArray)an[c], aoff[c], (jsize)n, (jboolean*)nl);
+            col->nulls = (const uint8_t*)nl;
+        }
     }
     *ncols_out = (int)ncols;
+    return (*env)->ExceptionCheck(env) ? PG_E_INVALID_ARGUMENT : PG_OK;     /* ArrayIndexOutOfBounds from a Region call */
+}
+
+/* Output columns: Java allocates one array set per channel (sized from the *Stats / *VarwidthBytes calls); the library writes
+ * into tl_out and pgj_out_end copies the first `rows` rows back. */
+int pgj_out_begin(JNIEnv* env, jintArray jtypes, jobjectArray jvalues, jobjectArray jnulls, jobjectArray joffsets, jlongArray jvalue_bytes,
+                  jlong capacity, size_t extra, pgj_outs* o) {
+    memset(o, 0, sizeof(*o));
+    const jsize ncols = jtypes ? (*env)->GetArrayLength(env, jtypes) : 0;
+    if (ncols > PGJ_MAX_COLS || capacity < 0) return PG_E_INVALID_ARGUMENT;
+    o->ncols = (int)ncols; o->capacity = capacity;
+    jlong vb[PGJ_MAX_COLS];
+    memset(vb, 0, sizeof(vb));
+    (*env)->GetIntArrayRegion(env, jtypes, 0, ncols, o->types);
+    if (jvalue_bytes) (*env)->GetLongArrayRegion(env, jvalue_bytes, 0, ncols, vb);
+    size_t total = 64 + padded(extra);
+    for (jsize c = 0; c < ncols; c++) {
+        o->values[c] = (jarray)(*env)->GetObjectArrayElement(env, jvalues, c);
+        o->nulls[c] = jnulls ? (jarray)(*env)->GetObjectArrayElement(env, jnulls, c) : NULL;
+        o->offsets[c] = joffsets ? (jarray)(*env)->GetObjectArrayElement(env, joffsets, c) : NULL;
+        if (!o->values[c] || (is_var(o->types[c]) && !o->offsets[c])) return PG_E_INVALID_ARGUMENT;
+        total += is_var(o->types[c]) ? padded((size_t)vb[c]) + padded(((size_t)capacity + 1) * 4) : padded((size_t)capacity * (size_t)pgj_type_width(o->types[c]));
+        if (o->nulls[c]) total += padded((size_t)capacity);
+    }
+    if (!arena_reserve(&tl_out, total)) return PG_E_INSUFFICIENT_RESOURCES;
+    for (jsize c = 0; c < ncols; c++) {
+        pg_col_out* out = &o->cols[c];
+        memset(out, 0, sizeof(*out));
+        out->type = o->types[c]; out->mem = PG_MEM_HOST; out->capacity = capacity;
+        if (is_var(o->types[c])) {
+            out->values = arena_take(&tl_out, (size_t)vb[c]);
+            out->offsets = (int32_t*)arena_take(&tl_out, ((size_t)capacity + 1) * 4);
+            out->values_capacity_bytes = vb[c];
+        } else out->values = arena_take(&tl_out, (size_t)capacity * (size_t)pgj_type_width(o->types[c]));
+        if (o->nulls[c]) out->nulls = (uint8_t*)arena_take(&tl_out, (size_t)capacity);
+    }
     return PG_OK;
 }
 
-static void unpin_page(JNIEnv* env, pinned_col* pins, int ncols) {
-    for (int c = ncols - 1; c >= 0; c--) {
-        if (pins[c].po) (*env)->ReleasePrimitiveArrayCritical(env, pins[c].offsets, pins[c].po, JNI_ABORT);
-        if (pins[c].pn) (*env)->ReleasePrimitiveArrayCritical(env, pins[c].nulls, pins[c].pn, JNI_ABORT);
-        if (pins[c].pv) (*env)->ReleasePrimitiveArrayCritical(env, pins[c].values, pins[c].pv, JNI_ABORT);
+void pgj_out_end(JNIEnv* env, pgj_outs* o, jlong rows) {
+    if (rows > o->capacity) rows = o->capacity;
+    for (int c = 0; c < o->ncols; c++) {
+        const pg_col_out* out = &o->cols[c];
+        if (is_var(o->types[c])) {
+            (*env)->SetIntArrayRegion(env, (jintArray)o->offsets[c], 0, (jsize)rows + 1, (const jint*)out->offsets);
+            copy_out(env, o->values[c], 1, rows > 0 ? (jsize)out->offsets[rows] : 0, out->values);
+        } else copy_out(env, o->values[c], pgj_type_width(o->types[c]), (jsize)rows, out->values);
+        if (o->nulls[c]) (*env)->SetBooleanArrayRegion(env, (jbooleanArray)o->nulls[c], 0, (jsize)rows, (const jboolean*)out->nulls);
     }
 }
 
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_ctxCreate(JNIEnv* env, jclass cls, jint device, jlongArray out) {
-    pg_ctx* ctx = NULL;
-    int32_t rc = pg_ctx_create(device, &ctx);
-    jlong h = (jlong)(intptr_t)ctx;
-    (*env)->SetLongArrayRegion(env, out, 0, 1, &h);
-    return rc;
+/* scratch in tl_out for plain result vectors (group ids, probe positions): after pgj_out_begin(.., extra, ..) reserved `extra`
+ * bytes for them, or after pgj_scratch_reset(total) when the call has no output columns */
+void* pgj_scratch(size_t bytes) {
+    const size_t at = (tl_out.used + 63) & ~(size_t)63;
+    if (at + bytes > tl_out.cap) return NULL;
+    tl_out.used = at + bytes;
+    return tl_out.p + at;
 }
+int pgj_scratch_reset(size_t reserve) { return arena_reserve(&tl_out, padded(reserve) + 256); }
 
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_ctxDestroy(JNIEnv* env, jclass cls, jlong ctx) {
-    return pg_ctx_destroy((pg_ctx*)(intptr_t)ctx);
+void pgj_set_long(JNIEnv* env, jlongArray arr, int i, int64_t v) {
+    if (!arr) return;
+    jlong j = (jlong)v;
+    (*env)->SetLongArrayRegion(env, arr, i, 1, &j);
 }
-
-JNIEXPORT jstring JNICALL Java_io_trino_gpu_PrestoGpu_lastError(JNIEnv* env, jclass cls, jlong ctx) {
-    const char* msg = pg_last_error((pg_ctx*)(intptr_t)ctx);
-    return (*env)->NewStringUTF(env, msg ? msg : "");
-}
-
-/* ---- fused operator: HashAggregationOperator.addInput / getOutput (OP/HashAggregationOperator.java:381-518) ---- */
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggCreate(JNIEnv* env, jclass cls, jlong ctx, jintArray keyChannels,
-        jintArray keyTypes, jint hashChannel, jintArray aggSpecs /* kind,inType,inputChannel,maskChannel per aggregate */,
-        jint step, jlong expectedGroups, jlongArray out) {
-    jsize nkeys = (*env)->GetArrayLength(env, keyChannels);
-    jsize nspec = (*env)->GetArrayLength(env, aggSpecs) / 4;
-    jint kc[MAX_COLS], kt[MAX_COLS], sp[4 * MAX_COLS];
-    if (nkeys > MAX_COLS || nspec > MAX_COLS) return PG_E_INVALID_ARGUMENT;
-    (*env)->GetIntArrayRegion(env, keyChannels, 0, nkeys, kc);
-    (*env)->GetIntArrayRegion(env, keyTypes, 0, nkeys, kt);
-    (*env)->GetIntArrayRegion(env, aggSpecs, 0, nspec * 4, sp);
-    pg_agg_spec specs[MAX_COLS];
-    for (jsize a = 0; a < nspec; a++) {
-        specs[a].kind = sp[4 * a]; specs[a].in_type = sp[4 * a + 1];
-        specs[a].input_channel = sp[4 * a + 2]; specs[a].mask_channel = sp[4 * a + 3];
-    }
-    pg_hashagg* op = NULL;
-    int32_t rc = pg_hashagg_create((pg_ctx*)(intptr_t)ctx, kc, kt, nkeys, hashChannel, specs, nspec, step, expectedGroups, &op);
-    jlong h = (jlong)(intptr_t)op;
-    (*env)->SetLongArrayRegion(env, out, 0, 1, &h);
-    return rc;
-}
-
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggAddPage(JNIEnv* env, jclass cls, jlong op, jintArray types,
-        jobjectArray values, jobjectArray nulls, jobjectArray offsets, jintArray arrayOffsets, jlong positionCount) {
-    pg_col cols[MAX_COLS];
-    pinned_col pins[MAX_COLS];
-    int ncols = 0;
-    int32_t rc = pin_page(env, types, values, nulls, offsets, arrayOffsets, positionCount, cols, pins, &ncols);
-    if (rc == PG_OK) rc = pg_hashagg_add_page((pg_hashagg*)(intptr_t)op, cols, ncols, positionCount);
-    unpin_page(env, pins, ncols);
-    return rc;
-}
-
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggStats(JNIEnv* env, jclass cls, jlong op, jlongArray out4) {
-    int64_t v[4] = {0, 0, 0, 0};
-    int32_t rc = pg_hashagg_stats((pg_hashagg*)(intptr_t)op, &v[0], &v[1], &v[2], &v[3]);
-    (*env)->SetLongArrayRegion(env, out4, 0, 4, (const jlong*)v);
-    return rc;
-}
-
-/* getOutput: Java allocates the output arrays (one per output channel, sized from hashaggStats/hashaggVarwidthBytes)
- * and wraps them into LongArrayBlock/IntArrayBlock/Int128ArrayBlock/VariableWidthBlock afterwards. */
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggGetOutput(JNIEnv* env, jclass cls, jlong op, jlong first, jlong n,
-        jintArray types, jobjectArray values, jobjectArray nulls, jobjectArray offsets, jlongArray valueBytes, jlongArray errorGroup) {
-    jsize ncols = (*env)->GetArrayLength(env, types);
-    if (ncols > MAX_COLS) return PG_E_INVALID_ARGUMENT;
-    jint t[MAX_COLS];
-    jlong vb[MAX_COLS];
-    (*env)->GetIntArrayRegion(env, types, 0, ncols, t);
-    (*env)->GetLongArrayRegion(env, valueBytes, 0, ncols, vb);
-    pg_col_out outs[MAX_COLS];
-    pinned_col pins[MAX_COLS];
-    for (jsize c = 0; c < ncols; c++) {
-        memset(&pins[c], 0, sizeof(pins[c]));
-        pins[c].values = (jarray)(*env)->GetObjectArrayElement(env, values, c);
-        pins[c].nulls = (jarray)(*env)->GetObjectArrayElement(env, nulls, c);
-        pins[c].offsets = (jarray)(*env)->GetObjectArrayElement(env, offsets, c);
-    }
-    for (jsize c = 0; c < ncols; c++) {
-        pins[c].pv = (*env)->GetPrimitiveArrayCritical(env, pins[c].values, NULL);
-        pins[c].pn = pins[c].nulls ? (*env)->GetPrimitiveArrayCritical(env, pins[c].nulls, NULL) : NULL;
-        pins[c].po = pins[c].offsets ? (*env)->GetPrimitiveArrayCritical(env, pins[c].offsets, NULL) : NULL;
-        memset(&outs[c], 0, sizeof(outs[c]));
-        outs[c].type = t[c];
-        outs[c].mem = PG_MEM_HOST;
-        outs[c].capacity = n;
-        outs[c].values = pins[c].pv;
-        outs[c].nulls = (uint8_t*)pins[c].pn;
-        outs[c].offsets = (int32_t*)pins[c].po;
-        outs[c].values_capacity_bytes = vb[c];
-    }
-    int64_t eg = -1;
-    int32_t rc = pg_hashagg_get_output((pg_hashagg*)(intptr_t)op, first, n, outs, &eg);
-    for (int c = ncols - 1; c >= 0; c--) {
-        if (pins[c].po) (*env)->ReleasePrimitiveArrayCritical(env, pins[c].offsets, pins[c].po, 0);
-        if (pins[c].pn) (*env)->ReleasePrimitiveArrayCritical(env, pins[c].nulls, pins[c].pn, 0);
-        (*env)->ReleasePrimitiveArrayCritical(env, pins[c].values, pins[c].pv, 0);
-    }
-    jlong jeg = eg;
-    (*env)->SetLongArrayRegion(env, errorGroup, 0, 1, &jeg);
-    return rc;
-}
-
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggDestroy(JNIEnv* env, jclass cls, jlong op) {
-    return pg_hashagg_destroy((pg_hashagg*)(intptr_t)op);
-}
-
-/* ---- packed pages: PARTIAL output -> FINAL input between processes (the job of PagesSerde in the reference's exchange) ---- */
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggGetOutputPacked(JNIEnv* env, jclass cls, jlong op, jlong first, jlong n,
-        jobject directBuffer, jlongArray outBytes, jlongArray errorGroup) {
-    void* buf = (*env)->GetDirectBufferAddress(env, directBuffer);
-    jlong cap = (*env)->GetDirectBufferCapacity(env, directBuffer);
-    int64_t nbytes = 0, eg = -1;
-    jint rc = pg_hashagg_get_output_packed((pg_hashagg*)(intptr_t)op, first, n, buf, cap, &nbytes, &eg);
-    jlong jb = nbytes, jeg = eg;
-    (*env)->SetLongArrayRegion(env, outBytes, 0, 1, &jb);      /* on PG_NEED_MEMORY: the size a retry needs */
-    (*env)->SetLongArrayRegion(env, errorGroup, 0, 1, &jeg);
-    return rc;
-}
-
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_hashaggAddPacked(JNIEnv* env, jclass cls, jlong op, jobjectArray directBuffers) {
-    jsize nb = (*env)->GetArrayLength(env, directBuffers);
-    const void* ptrs[64];
-    if (nb > 64) return PG_E_INVALID_ARGUMENT;
-    for (jsize i = 0; i < nb; i++) ptrs[i] = (*env)->GetDirectBufferAddress(env, (*env)->GetObjectArrayElement(env, directBuffers, i));
-    return pg_hashagg_add_packed((pg_hashagg*)(intptr_t)op, ptrs, nb);
-}
-
-/* ---- GroupByHash.getGroupIds(Page) (OP/GroupByHash.java:75) ---- */
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_groupbyGetGroupIds(JNIEnv* env, jclass cls, jlong gb, jintArray types,
-        jobjectArray values, jobjectArray nulls, jobjectArray offsets, jintArray arrayOffsets, jboolean lastIsHash,
-        jlong positionCount, jintArray outIds, jlongArray outGroupCount) {
-    pg_col cols[MAX_COLS];
-    pinned_col pins[MAX_COLS];
-    int ncols = 0;
-    int32_t rc = pin_page(env, types, values, nulls, offsets, arrayOffsets, positionCount, cols, pins, &ncols);
-    int64_t groups = 0;
-    if (rc == PG_OK) {
-        jint* ids = (jint*)(*env)->GetPrimitiveArrayCritical(env, outIds, NULL);
-        const pg_col* hash = lastIsHash ? &cols[ncols - 1] : NULL;
-        rc = pg_groupby_get_group_ids((pg_groupby*)(intptr_t)gb, cols, hash, positionCount, (int32_t*)ids, PG_MEM_HOST, &groups);
-        (*env)->ReleasePrimitiveArrayCritical(env, outIds, ids, 0);
-    }
-    unpin_page(env, pins, ncols);
-    jlong g = groups;
-    (*env)->SetLongArrayRegion(env, outGroupCount, 0, 1, &g);
-    return rc;
-}
-
-/* ---- LookupSource: one probe page -> (probe position, build position) pairs (OP/LookupJoinOperator.java:299-378) ---- */
-JNIEXPORT jint JNICALL Java_io_trino_gpu_PrestoGpu_lookupProbe(JNIEnv* env, jclass cls, jlong ls, jintArray types,
-        jobjectArray values, jobjectArray nulls, jobjectArray offsets, jintArray arrayOffsets, jboolean lastIsHash,
-        jlong positionCount, jint joinType, jintArray outProbeIdx, jlongArray outBuildPos, jlongArray nOut) {
-    pg_col cols[MAX_COLS];
-    pinned_col pins[MAX_COLS];
-    int ncols = 0;
-    int32_t rc = pin_page(env, types, values, nulls, offsets, arrayOffsets, positionCount, cols, pins, &ncols);
-    int64_t produced = 0;
-    if (rc == PG_OK) {
-        jsize cap = (*env)->GetArrayLength(env, outProbeIdx);
-        jint* pi = (jint*)(*env)->GetPrimitiveArrayCritical(env, outProbeIdx, NULL);
-        jlong* bp = (jlong*)(*env)->GetPrimitiveArrayCritical(env, outBuildPos, NULL);
-        int nkeys = lastIsHash ? ncols - 1 : ncols;
-        rc = pg_lookup_probe((pg_lookup*)(intptr_t)ls, cols, nkeys, lastIsHash ? &cols[ncols - 1] : NULL, positionCount, joinType,
-                             (int32_t*)pi, (int64_t*)bp, PG_MEM_HOST, cap, &produced);
-        (*env)->ReleasePrimitiveArrayCritical(env, outBuildPos, bp, 0);
-        (*env)->ReleasePrimitiveArrayCritical(env, outProbeIdx, pi, 0);
-    }
-    unpin_page(env, pins, ncols);
-    jlong p = produced;
-    (*env)->SetLongArrayRegion(env, nOut, 0, 1, &p);
-    return rc;   /* PG_NEED_MEMORY: nOut[0] = rows needed; Java grows the arrays and calls again */
+void pgj_set_int(JNIEnv* env, jintArray arr, int i, int32_t v) {
+    if (!arr) return;
+    jint j = (jint)v;
+    (*env)->SetIntArrayRegion(env, arr, i, 1, &j);
 }

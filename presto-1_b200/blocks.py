@@ -230,7 +230,8 @@ def col_array(blocks):
 class OutBlock:
     """Caller-allocated output column (pg_col_out) backed by numpy (host) or torch (device)."""
 
-    def __init__(self, type_, capacity, value_bytes=0, device=False, want_nulls=True):
+    def __init__(self, type_, capacity, value_bytes=0, device=False, want_nulls=True, zero=True):
+        """zero=False (device only): uninitialised memory, for calls that write every row of every array they are given."""
         self.type = type_
         self.capacity = int(capacity)
         self.device = device
@@ -245,9 +246,10 @@ class OutBlock:
         if device:
             import torch
             tdt = {np.int64: torch.int64, np.uint64: torch.int64, np.int32: torch.int32, np.uint8: torch.uint8}[dt]
-            self.values = torch.zeros(nvals, dtype=tdt, device="cuda")
-            self.nulls = torch.zeros(cap, dtype=torch.uint8, device="cuda") if want_nulls else None
-            self.offsets = torch.zeros(cap + 1, dtype=torch.int32, device="cuda") if var else None
+            new = torch.zeros if zero else torch.empty
+            self.values = new(nvals, dtype=tdt, device="cuda")
+            self.nulls = new(cap, dtype=torch.uint8, device="cuda") if want_nulls else None
+            self.offsets = new(cap + 1, dtype=torch.int32, device="cuda") if var else None
         else:
             self.values = np.zeros(nvals, dtype=dt)
             self.nulls = np.zeros(cap, dtype=np.uint8) if want_nulls else None

@@ -591,6 +591,19 @@ void groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys, int32_
     *out = gb;
 }
 
+void groupby_reserve(pg_groupby* gb, int64_t n) {
+    if (gb->memory_limit <= 0 || n <= 0) return;
+    int64_t cap = gb->cap > gb->deferred_cap ? gb->cap : gb->deferred_cap;
+    while (max_fill_075(cap) - gb->occupied < n && cap < (1LL << 30)) cap *= 2;
+    if (cap == gb->cap) return;                       // no growth possible with this page
+    const int64_t per_group = gb->bigint_mode ? 8 : (int64_t)gb->layout.row_words * 8 + 8;
+    const int64_t after = groupby_device_bytes(gb) - gb->slots.bytes - gb->values_by_group.bytes - gb->key_rows.bytes - gb->hash_by_group.bytes +
+                          (cap + 2) * (int64_t)sizeof(Slot) + (max_fill_075(cap) + 2 + 256 * 1024) * per_group;
+    if (after > gb->memory_limit)
+        fail(PG_NEED_MEMORY, "the hash table may have to grow to %lld bytes for this page, the memory limit is %lld; nothing was consumed",
+             (long long)after, (long long)gb->memory_limit);
+}
+
 int64_t groupby_device_bytes(const pg_groupby* gb) {
     return gb->slots.bytes + gb->values_by_group.bytes + gb->key_rows.bytes + gb->hash_by_group.bytes + gb->arena.bytes +
            gb->row_slot.bytes + gb->tile_sums.bytes + gb->meta.bytes;
@@ -810,6 +823,7 @@ int32_t pg_groupby_get_group_ids(pg_groupby* gb, const pg_col* keys, const pg_co
         OutVec<int32_t> ids;
         ids.begin(gb->ctx, out_ids, ids_mem, n);
         VarHint hint(gb, ik, n);
+        groupby_reserve(gb, n);
         groupby_process(gb, ik.kc, ik.has_hash ? &ik.hc : nullptr, n, ids.d);
         ids.finish();
         sync(gb->ctx);
@@ -824,9 +838,16 @@ int32_t pg_groupby_add_page(pg_groupby* gb, const pg_col* keys, const pg_col* ha
         ImportedKeys ik;
         import_keys(gb, keys, hash_col, n, ik);
         VarHint hint(gb, ik, n);
+        groupby_reserve(gb, n);
         groupby_process(gb, ik.kc, ik.has_hash ? &ik.hc : nullptr, n, nullptr);
         sync(gb->ctx);
     });
+}
+
+int32_t pg_groupby_set_memory_limit(pg_groupby* gb, int64_t bytes) {
+    if (!gb || bytes < 0) return PG_E_INVALID_ARGUMENT;
+    gb->memory_limit = bytes;
+    return PG_OK;
 }
 
 int32_t pg_groupby_contains(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n, uint8_t* out, int32_t out_mem) {

@@ -77,6 +77,7 @@ struct pg_groupby {
     int64_t arena_used = 0;
     int64_t var_bound_hint = -1;   // caller's upper bound on the variable width bytes of the next page (-1: unknown, read them back)
     int64_t rehashes = 0;
+    int64_t memory_limit = 0;      // bytes (0 = none): a page that could grow the table past it is refused with PG_NEED_MEMORY
     pg::DevBuf slots, values_by_group, key_rows, hash_by_group, arena, meta;
     // scratch reused across pages
     pg::DevBuf row_slot, tile_sums;
@@ -89,4 +90,8 @@ void groupby_process(pg_groupby* gb, const KeyCols& keys, const DCol* hash_col, 
 void groupby_create(pg_ctx* ctx, const int32_t* key_types, int32_t nkeys, int32_t has_hash_channel, int64_t expected,
                     pg_groupby** out, bool lazy_table = false);
 int64_t groupby_device_bytes(const pg_groupby* gb);
+// The analogue of UpdateMemory.update() returning false inside tryRehash (OP/BigintGroupByHash.java:295-334): called BEFORE any
+// row of a page of n rows is consumed; throws PG_NEED_MEMORY when, with every row a new group, the table would have to grow past
+// memory_limit.  Nothing has changed then, and the caller retries the same page after raising the limit (Work.process() == false).
+void groupby_reserve(pg_groupby* gb, int64_t n);
 }  // namespace pg

@@ -539,8 +539,28 @@ int32_t pg_hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, i
     if (!op) return PG_E_INVALID_ARGUMENT;
     return guard(op->ctx, [&] {
         PG_CHECK_ARG(cols && ncols > 0 && n >= 0, "bad arguments");
+        // memory yield: checked before the first row is consumed, for whichever table this page may grow
+        if (op->gb->memory_limit > 0) {
+            if (op->wide && !op->wide->prepared) {
+                WideTable* w = op->wide;
+                if (w->claimed + n > w->max_fill) {
+                    int64_t cap = w->cap;
+                    while ((int64_t)(cap * 0.75) < w->claimed + n) cap *= 2;
+                    const int64_t after = w->device_bytes() - w->table.bytes + (cap + 2) * (int64_t)w->bucket_words * 8;
+                    if (after > op->gb->memory_limit)
+                        fail(PG_NEED_MEMORY, "the aggregation table may have to grow to %lld bytes for this page, the memory limit is %lld; nothing was consumed",
+                             (long long)after, (long long)op->gb->memory_limit);
+                }
+            } else groupby_reserve(op->gb, n);
+        }
         hashagg_add_page(op, cols, ncols, n);
     });
+}
+
+int32_t pg_hashagg_set_memory_limit(pg_hashagg* op, int64_t bytes) {
+    if (!op || bytes < 0) return PG_E_INVALID_ARGUMENT;
+    op->gb->memory_limit = bytes;
+    return PG_OK;
 }
 
 int32_t pg_hashagg_stats(pg_hashagg* op, int64_t* group_count, int64_t* capacity, int64_t* device_bytes, int64_t* input_rows) {

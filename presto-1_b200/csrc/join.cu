@@ -550,9 +550,33 @@ __global__ void __launch_bounds__(SCAN_THREADS) j_probe_emit_fast_kernel(ProbeAr
 // emitting rows per tile and in total (meta[0]); when the total equals n the output is complete after this one pass and no scan or
 // second pass runs.  (A single-pass version with a decoupled look-back for the tile offsets was slower: 0.82 ms against 0.45 ms,
 // the prefix could not travel through 29 K tiles fast enough.)
+// GATHER: the build channels of the matched row are copied to the output row as well (LookupSource.appendTo fused into the probe:
+// the 64-bit build positions are never written or read back); out_build may then be null.
+static const int JG_MAX_COLS = 8;
+struct GatherTab {
+    int32_t n, pad;
+    const void* src[JG_MAX_COLS];
+    const uint8_t* src_nulls[JG_MAX_COLS];
+    void* out[JG_MAX_COLS];
+    uint8_t* out_nulls[JG_MAX_COLS];
+    int32_t width[JG_MAX_COLS];
+};
+PG_D void gather_row(const GatherTab& g, int64_t row, int cd) {
+    for (int c = 0; c < g.n; c++) {
+        const bool isnull = cd < 0 || (g.src_nulls[c] && g.src_nulls[c][cd]);
+        if (g.out_nulls[c]) g.out_nulls[c][row] = isnull ? 1 : 0;
+        switch (g.width[c]) {
+            case 1: ((uint8_t*)g.out[c])[row] = isnull ? (uint8_t)0 : ((const uint8_t*)g.src[c])[cd]; break;
+            case 4: ((int32_t*)g.out[c])[row] = isnull ? 0 : ((const int32_t*)g.src[c])[cd]; break;
+            case 8: ((int64_t*)g.out[c])[row] = isnull ? 0 : __ldg((const int64_t*)g.src[c] + cd); break;
+            default: ((int4*)g.out[c])[row] = isnull ? make_int4(0, 0, 0, 0) : __ldg((const int4*)g.src[c] + cd);
+        }
+    }
+}
+template <bool GATHER>
 __global__ void __launch_bounds__(SCAN_THREADS) j_probe_dense_kernel(ProbeArgs a, const int64_t* __restrict__ keys, const uint8_t* __restrict__ nulls,
                                                                      Pair64* tile_sums, unsigned long long* total_out,
-                                                                     int32_t* out_probe, int64_t* out_build) {
+                                                                     int32_t* out_probe, int64_t* out_build, GatherTab gt) {
     __shared__ int s_cnt[SCAN_THREADS / 32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
@@ -607,9 +631,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) j_probe_dense_kernel(ProbeArgs a
             if (!((validm >> g) & 1u)) cd = -1;
             if ((inr >> g) & 1u) {
                 const int64_t row = tile_base + (int64_t)(j0 + g) * SCAN_THREADS + threadIdx.x;
-                a.probe_slot[row] = cd;
+                if (!GATHER) a.probe_slot[row] = cd;        // (the fused form never compacts: a page with misses is redone by the two-step path)
                 out_probe[row] = (int32_t)row;
-                out_build[row] = cd;
+                if (out_build) out_build[row] = cd;
+                if (GATHER) gather_row(gt, row, cd);
                 if (cd >= 0 || a.join_type == 1) emitted++;    // PROBE_OUTER: appendNullForBuild (LookupJoinOperator.java:354-361)
             }
         }
@@ -1003,8 +1028,10 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
             OutVec<int32_t> op; OutVec<int64_t> ob;
             op.begin(ctx, out_probe_idx, out_mem, n);
             ob.begin(ctx, out_build_pos, out_mem, n);
-            PG_LAUNCH(ctx, j_probe_dense_kernel, (int)ntiles, SCAN_THREADS, 0, a, (const int64_t*)probe.c[0].values, probe.c[0].nulls, tiles, d_total,
-                      op.d, ob.d);
+            GatherTab none;
+            memset(&none, 0, sizeof(none));
+            PG_LAUNCH(ctx, j_probe_dense_kernel<false>, (int)ntiles, SCAN_THREADS, 0, a, (const int64_t*)probe.c[0].values, probe.c[0].nulls, tiles, d_total,
+                      op.d, ob.d, none);
             int64_t tot;
             read_scalars(ctx, d_total, 1, &tot);
             *n_out = tot;
@@ -1078,6 +1105,72 @@ int32_t pg_lookup_gather(pg_lookup* ls, const int64_t* build_pos, int32_t pos_me
             }
         }
         for (int k = 0; k < nchannels; k++) st[k].finish(vbytes[k]);
+        sync(ctx);
+    });
+}
+
+/* LookupJoinOperator's step for one probe page in one call: JoinProbe + LookupSource.appendTo of `build_channels`
+ * (OP/LookupJoinOperator.java:333-361, OP/JoinProbe.java, PagesHashStrategy.appendTo).  out_probe_idx[capacity] receives the probe
+ * positions, out_build[k] (capacity >= `capacity` rows) the build channels of the matched rows (null for PROBE_OUTER misses).
+ * Unique single-BIGINT-key build sides with device outputs run one kernel (no 64-bit build positions are materialised); every
+ * other case runs pg_lookup_probe + pg_lookup_gather internally.  PG_NEED_MEMORY as in pg_lookup_probe. */
+int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, const pg_col* hash_col, int64_t n, int32_t join_type,
+                            const int32_t* build_channels, int32_t nchannels, int32_t* out_probe_idx, int32_t out_mem, pg_col_out* out_build,
+                            int64_t capacity, int64_t* n_out) {
+    if (!ls) return PG_E_INVALID_ARGUMENT;
+    return guard(ls->ctx, [&] {
+        pg_ctx* ctx = ls->ctx;
+        PG_CHECK_ARG(probe_keys && n_out && n >= 0 && capacity >= 0 && nchannels >= 0 && (nchannels == 0 || (build_channels && out_build)), "bad arguments");
+        PG_CHECK_ARG(nkeys == (int32_t)ls->join_channels.size(), "probe has %d join channels, build has %d", nkeys, (int)ls->join_channels.size());
+        PG_CHECK_ARG(join_type == 0 || join_type == 1, "join type must be INNER (0) or PROBE_OUTER (1)");
+        *n_out = 0;
+        if (n == 0) return;
+        PG_CHECK_ARG(n <= MAX_CHUNK_ROWS, "probe page too large");
+        bool fused = ls->bigint_fast && !ls->has_dups && capacity >= n && out_probe_idx && out_mem == PG_MEM_DEVICE && nchannels <= JG_MAX_COLS &&
+                     (ls->layout.range || ls->cap < (1LL << 30)) && probe_keys[0].type == PG_BIGINT && !getenv("PRESTOGPU_NO_FUSED_PROBE");
+        for (int k = 0; k < nchannels; k++) {
+            const int ch = build_channels[k];
+            PG_CHECK_ARG(ch >= 0 && ch < (int)ls->cols.size(), "build channel %d out of range", ch);
+            PG_CHECK_ARG(out_build[k].type == ls->types[ch], "output %d type mismatch", k);
+            if (type_is_var(ls->types[ch]) || out_build[k].mem != PG_MEM_DEVICE || out_build[k].capacity < n) fused = false;
+            if (join_type == 1 && !out_build[k].nulls) fused = false;      // misses need a null mask
+        }
+        if (fused) {
+            ColImport imp;
+            import_col(ctx, probe_keys[0], n, imp);
+            const int64_t ntiles = num_tiles(n);
+            ProbeArgs a;
+            a.slots = ls->slots.as<JSlot>(); a.cap = ls->cap; a.seg_off = ls->seg_off.as<int32_t>(); a.seg_rows = ls->seg_rows.as<int32_t>();
+            a.n = n; a.join_type = join_type; a.build_empty = ls->rows == 0 ? 1 : 0; a.L = ls->layout;
+            ls->tile_sums.grow(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64), 0);
+            a.probe_slot = nullptr;
+            unsigned long long* d_total = ls->meta.as<unsigned long long>() + 10;
+            memset_async(ctx, d_total, 0, 8);
+            GatherTab gt;
+            memset(&gt, 0, sizeof(gt));
+            gt.n = nchannels;
+            for (int k = 0; k < nchannels; k++) {
+                const DCol src = ls->cols[build_channels[k]].view();
+                gt.src[k] = src.values; gt.src_nulls[k] = src.nulls; gt.out[k] = out_build[k].values; gt.out_nulls[k] = out_build[k].nulls;
+                gt.width[k] = type_width(src.type);
+            }
+            PG_LAUNCH(ctx, j_probe_dense_kernel<true>, (int)ntiles, SCAN_THREADS, 0, a, (const int64_t*)imp.d.values, imp.d.nulls, ls->tile_sums.as<Pair64>(),
+                      d_total, out_probe_idx, (int64_t*)nullptr, gt);
+            int64_t tot;
+            read_scalars(ctx, d_total, 1, &tot);
+            if (tot == n) { *n_out = n; return; }        // every probe row emitted exactly one row: the output is complete
+            // some INNER rows found no match: the compacting path below redoes the page
+        }
+        DevBuf tp(ctx, std::max<int64_t>(capacity, 1) * 4), tb(ctx, std::max<int64_t>(capacity, 1) * 8);
+        int32_t rc = pg_lookup_probe(ls, probe_keys, nkeys, hash_col, n, join_type, tp.as<int32_t>(), tb.as<int64_t>(), PG_MEM_DEVICE, capacity, n_out);
+        if (rc != PG_OK) { const std::string msg = ctx->err; fail(rc, "%s", msg.c_str()); }
+        if (*n_out == 0) return;
+        if (out_probe_idx)
+            copy_async(ctx, out_probe_idx, tp.p, *n_out * 4, out_mem == PG_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost);
+        if (nchannels > 0) {
+            rc = pg_lookup_gather(ls, tb.as<int64_t>(), PG_MEM_DEVICE, *n_out, build_channels, nchannels, out_build);
+            if (rc != PG_OK) { const std::string msg = ctx->err; fail(rc, "%s", msg.c_str()); }
+        }
         sync(ctx);
     });
 }

@@ -31,6 +31,28 @@ class GroupByIdBlock:
         return len(self.ids)
 
 
+class Work:
+    """OP/Work.java: process() -> finished?; get_result() once finished.  A PG_NEED_MEMORY status is the yield."""
+
+    def __init__(self, step):
+        self._step, self._done, self._result = step, False, None
+
+    def process(self):
+        assert not self._done, "process() called on a finished Work"
+        try:
+            self._result = self._step()
+        except N.PrestoGpuError as e:
+            if e.code == N.PG_NEED_MEMORY:
+                return False
+            raise
+        self._done = True
+        return True
+
+    def get_result(self):
+        assert self._done, "get_result() before the Work finished"
+        return self._result
+
+
 class GroupByHash:
     def __init__(self, types, expected_size, has_hash_channel=False, ctx=None):
         self.ctx = ctx or default_context()
@@ -57,6 +79,19 @@ class GroupByHash:
         keys = blocks[:nk]
         hash_block = blocks[nk] if self.has_hash_channel and len(blocks) > nk else None
         return keys, hash_block
+
+    def set_memory_limit(self, nbytes):
+        """UpdateMemory as a byte limit (OP/UpdateMemory.java): with a limit set, the *_work forms below yield instead of growing past it."""
+        N.check(self.ctx.handle, N.lib().pg_groupby_set_memory_limit(self._h, int(nbytes)))
+
+    def add_page_work(self, page):
+        """GroupByHash.addPage(page) as the reference returns it: a Work whose process() is False while the memory limit blocks the
+        page (nothing consumed) and True once the page is in (OP/GroupByHash.java:73, OP/Work.java)."""
+        return Work(lambda: self.add_page(page))
+
+    def get_group_ids_work(self, page, device_ids=None):
+        """GroupByHash.getGroupIds(page) as a Work<GroupByIdBlock> (OP/GroupByHash.java:75)."""
+        return Work(lambda: self.get_group_ids(page, device_ids))
 
     def add_page(self, page):
         keys, hb = self._split(page)

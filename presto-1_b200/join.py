@@ -106,6 +106,39 @@ class LookupSource:
             N.check(self.ctx.handle, rc)
             return op[:n_out.value], ob[:n_out.value]
 
+    def join_and_append(self, probe_keys, channels, hash_block=None, join_type=N.JOIN_INNER, device=None, capacity=None):
+        """One LookupJoinOperator step: (probe positions int32[], build channels `channels` of the matched rows) — JoinProbe and
+        appendTo in one call (pg_lookup_join_page).  Fixed width build channels only (use join_page + append_to otherwise)."""
+        keys = list(probe_keys)
+        n = keys[0].n
+        on_device = keys[0].device if device is None else device
+        hc = hash_block.pg_col() if hash_block is not None else None
+        cap = max(n, 1) if capacity is None else capacity
+        n_out = C.c_int64()
+        chs = (C.c_int32 * max(1, len(channels)))(*channels)
+        for ch in channels:
+            if self.types[ch] in (N.VARCHAR, N.VARBINARY):
+                raise N.PrestoGpuError(N.PG_E_INVALID_ARGUMENT, "join_and_append: variable width build channel %d; use join_page + append_to" % ch)
+        while True:
+            if on_device:
+                import torch
+                op = torch.empty(max(cap, 1), dtype=torch.int32, device="cuda")
+                pp, mem = op.data_ptr(), N.MEM_DEVICE
+            else:
+                op = np.empty(max(cap, 1), dtype=np.int32)
+                pp, mem = op.ctypes.data, N.MEM_HOST
+            outs = [OutBlock(self.types[ch], max(cap, 1), 0, device=on_device, zero=False) for ch in channels]
+            arr = (N.PgColOut * max(1, len(outs)))()
+            for i, o in enumerate(outs):
+                arr[i] = o.pg_col_out()
+            rc = N.lib().pg_lookup_join_page(self._h, col_array(keys), len(keys), C.byref(hc) if hc else None, n, join_type, chs, len(channels),
+                                             pp, mem, arr, cap, C.byref(n_out))
+            if rc == N.PG_NEED_MEMORY:   # nothing consumed: retry with room for every match
+                cap = n_out.value
+                continue
+            N.check(self.ctx.handle, rc)
+            return op[:n_out.value], [o.block(n_out.value) for o in outs]
+
     def append_to(self, build_positions, channels, device=None):
         """appendTo for a vector of build positions: gathers the given build channels (position -1 -> null)."""
         on_device = type(build_positions).__module__.startswith("torch") if device is None else device

@@ -52,17 +52,38 @@ class HashAggregationOperator:
         self._finished = False
         self._next_group = 0
         self._flushing = False
+        self._unfinished = None      # unfinishedWork (:398-417): a page the memory limit has not let in yet
+
+    def set_memory_limit(self, nbytes):
+        """The operator's memory yield: with a limit set, add_input keeps a page that could grow the table past it as unfinished
+        work instead of consuming it (pg_hashagg_set_memory_limit)."""
+        N.check(self.ctx.handle, N.lib().pg_hashagg_set_memory_limit(self._h, int(nbytes)))
 
     # ---- Operator interface
     def needs_input(self):       # HashAggregationOperator.java:367-378
-        return not self._finishing and not self._flushing
+        return not self._finishing and not self._flushing and self._unfinished is None
+
+    def _process_unfinished(self):
+        """unfinishedWork.process(): True when no page is waiting any more."""
+        if self._unfinished is None:
+            return True
+        blocks = self._unfinished
+        rc = N.lib().pg_hashagg_add_page(self._h, col_array(blocks), len(blocks), blocks[0].n)
+        if rc == N.PG_NEED_MEMORY:
+            return False
+        N.check(self.ctx.handle, rc)
+        self._unfinished = None
+        if self.step == PARTIAL and self.get_estimated_size() > self.max_partial_memory:   # builder full -> flush (:208-215, :501-517)
+            self._flushing = True
+        return True
 
     def add_input(self, page):   # :381-440
         assert self.needs_input(), "Operator is already finishing"
-        blocks = page.blocks if isinstance(page, Page) else list(page)
-        N.check(self.ctx.handle, N.lib().pg_hashagg_add_page(self._h, col_array(blocks), len(blocks), blocks[0].n))
-        if self.step == PARTIAL and self.get_estimated_size() > self.max_partial_memory:   # builder full -> flush (:208-215, :501-517)
-            self._flushing = True
+        self._unfinished = page.blocks if isinstance(page, Page) else list(page)
+        self._process_unfinished()
+
+    def has_unfinished_input(self):
+        return self._unfinished is not None
 
     def finish(self):
         self._finishing = True
@@ -97,6 +118,8 @@ class HashAggregationOperator:
         return list(buf[:n.value])
 
     def get_output(self, max_rows=None):   # :469-518
+        if not self._process_unfinished():     # :473-481: the waiting page first; still blocked -> no output
+            return None
         if not (self._finishing or self._flushing) or self._finished:
             return None
         groups = self._stats()[0]

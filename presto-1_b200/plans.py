@@ -236,6 +236,6 @@ class PartitionedHashJoin:
         """Returns (exchanged probe page, probe positions into it, gathered build blocks)."""
         local = self.exchange.exchange(page, probe_join_channels, slot=slot, lease=True) if self.exchange else page
         m = local.position_count
-        pp, bp = self.lookup.join_page([local.blocks[c] for c in probe_join_channels], None, join_type, device=True, capacity=max(m, 1))
-        out = self.lookup.append_to(bp, build_output_channels, device=True)
+        pp, out = self.lookup.join_and_append([local.blocks[c] for c in probe_join_channels], build_output_channels, None, join_type, device=True,
+                                              capacity=max(m, 1))
         return local, pp, out

@@ -182,3 +182,51 @@ def test_large_bigint_growth_and_ids(pgpu):
     assert np.array_equal(ids.ids.cpu().numpy(), want)
     assert ids.get_group_count() == orc.group_count()
     assert gb.get_capacity() == orc.capacity()
+
+
+@pytest.mark.parametrize("kind", ["bigint", "varchar"])
+def test_memory_reservation_yield(pgpu, kind):
+    """TestGroupByHash.testMemoryReservationYield (TestGroupByHash.java:292-371) with UpdateMemory as a byte limit: a page far
+    larger than the table's expected size; the Work blocks (process() == False, nothing consumed, and again False without more
+    memory), memory is granted in steps, and at the end nothing is missing and nothing was inserted twice — for addPage and for
+    getGroupIds."""
+    P = pgpu
+    length = 3_000_000 if kind == "bigint" else 1_200_000
+    if kind == "bigint":
+        values = P.Block.long_array(np.arange(length, dtype=np.int64))
+        types = [P.BIGINT]
+    else:
+        values = P.Block.variable_width(["%d" % i for i in range(length)])
+        types = [P.VARCHAR]
+    page = P.Page(values)
+
+    def drive(make_work, gb):
+        limit = gb.get_estimated_size()          # what the empty table holds: any growth needs a grant
+        gb.set_memory_limit(limit)
+        work = make_work()
+        yields = 0
+        while not work.process():
+            assert gb.get_group_count() == 0     # nothing consumed while blocked
+            assert not work.process()            # blocked again without more memory
+            assert gb.get_group_count() == 0
+            yields += 1
+            limit *= 2
+            gb.set_memory_limit(limit)
+            assert yields < 40
+        return work, yields, limit
+
+    gb = P.GroupByHash(types, 1)
+    work, yields, limit = drive(lambda: gb.add_page_work(page), gb)
+    assert yields >= 1
+    assert gb.get_group_count() == length
+    assert gb.get_estimated_size() <= limit + 64 * length      # the grant covered what the table grew to (+ per-page scratch)
+    gb.close()
+
+    gb = P.GroupByHash(types, 1)
+    work, yields2, _ = drive(lambda: gb.get_group_ids_work(page), gb)
+    assert yields2 == yields
+    ids = work.get_result()
+    assert gb.get_group_count() == length and ids.group_count == length
+    got = np.asarray(ids.ids)
+    assert got.shape[0] == length and np.array_equal(got, np.arange(length, dtype=np.int32))
+    gb.close()

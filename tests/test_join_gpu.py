@@ -261,3 +261,53 @@ def test_bigint_join_range_chunked_table_matches_oracle(pgpu, case, join_type):
     out = ls.append_to(__import__("torch").from_numpy(wb).cuda(), [1])
     sel = wb >= 0
     assert np.array_equal(out[0].to_host().values[sel], pay.view(np.int64)[wb[sel]])
+    # the fused step (pg_lookup_join_page) must give the same probe positions and the same gathered channel, nulls included
+    fp, fout = ls.join_and_append([pk.to_device()], [1, 0], None, join_type)
+    assert np.array_equal(fp.cpu().numpy(), wp), case
+    got = fout[0].to_host()
+    assert np.array_equal(got.values[sel], pay.view(np.int64)[wb[sel]]), case
+    assert np.array_equal(np.asarray(got.nulls) != 0, ~sel), case
+    gk = fout[1].to_host()
+    assert np.array_equal(gk.values[sel], bkeys[wb[sel]]), case
+
+
+@pytest.mark.parametrize("join_type", [0, 1])
+@pytest.mark.parametrize("all_match", [True, False])
+def test_fused_join_step_unique_build_keys(pgpu, join_type, all_match):
+    """pg_lookup_join_page on the foreign-key shape (unique build keys): the one-kernel path when every probe row emits, the
+    compacting fallback when INNER rows miss; host outputs take the two-step path.  Compared with the oracle's probe + appendTo."""
+    P = pgpu
+    rng = np.random.default_rng(91)
+    n, m = 40_000, 130_001
+    i = np.arange(1, n + 1, dtype=np.int64)
+    bkeys = ((i >> 3) << 5) | (i & 7)
+    pay = rng.integers(-10**15, 10**15, n).astype(np.int64)
+    pnulls = (rng.random(n) < 0.05).astype(np.uint8)
+    big = [int(x) * 10**21 * (-1 if x % 2 else 1) for x in rng.integers(1, 10**9, n)]
+    types = [P.BIGINT, P.SHORT_DECIMAL, P.LONG_DECIMAL]
+    blocks = [P.Block.long_array(bkeys), P.Block.long_array(pay, pnulls, P.SHORT_DECIMAL), P.Block.int128_array(big)]
+    idx = P.PagesIndex(types, [0])
+    orc = O.OracleJoin(types, [0])
+    idx.add_page([b.to_device() for b in blocks])
+    orc.add_page(blocks)
+    ls = idx.create_lookup_source()
+    orc.build()
+    pkeys = bkeys[rng.integers(0, n, m)]
+    if not all_match:
+        pkeys[::7] += 8            # keys dbgen never uses
+    pk = P.Block.long_array(pkeys, None if all_match else (rng.random(m) < 0.01).astype(np.uint8))
+    wp, wb = orc.probe([pk], None, join_type)
+    sel = wb >= 0
+    bigv = np.asarray(blocks[2].values).reshape(n, 2)
+    for device in (True, False):
+        fp, fout = ls.join_and_append([pk.to_device() if device else pk], [2, 1], None, join_type, device=device)
+        fp = fp.cpu().numpy() if device else fp
+        assert np.array_equal(fp, wp)
+        g2, g1 = fout[0].to_host(), fout[1].to_host()
+        assert np.array_equal(np.asarray(g2.values).reshape(-1, 2)[sel], bigv[wb[sel]])
+        assert np.array_equal(np.asarray(g2.nulls) != 0, ~sel)
+        want_null = ~sel
+        want_null[sel] = pnulls[wb[sel]] != 0
+        assert np.array_equal(np.asarray(g1.nulls) != 0, want_null)
+        ok = ~want_null
+        assert np.array_equal(np.asarray(g1.values)[ok], pay[wb[ok]])

@@ -471,3 +471,35 @@ def test_packed_pages_carry_partial_output_to_final(pgpu):
     single.add_input(page)
     single.finish()
     assert sorted(got) == sorted(rows_of(drain(single)))
+
+
+def test_operator_yields_on_memory_limit_and_counts_every_row_once(pgpu):
+    """HashAggregationOperator's unfinishedWork (HashAggregationOperator.java:398-417, 473-481): with a memory limit the page that
+    would grow the table is kept, needsInput() is false and getOutput() gives nothing until the memory is granted; then every row
+    counts exactly once (sums bit-exact against the oracle)."""
+    P = pgpu
+    rng = np.random.default_rng(5)
+    n = 2_500_000
+    keys = rng.permutation(n).astype(np.int64) % 1_800_000        # more distinct keys than the starting table's fill limit
+    vals = rng.integers(-10**12, 10**12, n).astype(np.int64)
+    blocks = [P.Block.long_array(keys), P.Block.long_array(vals, None, P.SHORT_DECIMAL)]
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1)]
+    op = P.HashAggregationOperator([P.BIGINT], [0], P.SINGLE, aggs, expected_groups=10)
+    limit = op.get_device_bytes()             # what the empty operator holds: any growth needs a grant
+    op.set_memory_limit(limit)
+    op.add_input(P.Page(*blocks))
+    assert op.has_unfinished_input() and not op.needs_input()
+    assert op.get_group_count() == 0
+    op.finish()
+    assert op.get_output() is None and op.has_unfinished_input()      # still blocked: no output, nothing consumed
+    grants = 0
+    while op.has_unfinished_input():
+        limit *= 2
+        grants += 1
+        op.set_memory_limit(limit)
+        op._process_unfinished()
+        assert grants < 40
+    assert grants >= 1
+    got = rows_of(drain(op))
+    want = _oracle_rows(P, None, [blocks], aggs)
+    _assert_rows_equal(got, want)

@@ -1,4 +1,6 @@
 // context.cu — context lifetime, column import (host Blocks -> device-resident column buffers).
+#include <stdlib.h>
+
 #include "context.h"
 
 namespace pg {
@@ -164,6 +166,13 @@ int32_t pg_ctx_create(int32_t device, pg_ctx** out) {
         PG_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
         uint64_t thresh = UINT64_MAX;
         PG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
+        // L2 fetch granularity on a miss (32 / 64 / 128 bytes; the driver's default is 64).  Hash probes and gathers want one 32-byte
+        // sector per random access; PRESTOGPU_L2_FETCH overrides (0 = leave the device setting alone).
+        int fetch = 0;
+        if (const char* e = getenv("PRESTOGPU_L2_FETCH")) fetch = atoi(e);
+        if (fetch == 32 || fetch == 64 || fetch == 128) {
+            if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)fetch) != cudaSuccess) cudaGetLastError();
+        }
     });
     if (rc != PG_OK) { delete ctx; return rc; }
     *out = ctx;

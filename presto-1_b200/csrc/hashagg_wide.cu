@@ -264,7 +264,7 @@ __device__ __forceinline__ void re_move_column(const T* __restrict__ in, T* __re
     for (int l = threadIdx.x; l < rows; l += RE_THREADS) out[(int64_t)s_dest[l] * stride + offset] = stage[l];
     __syncthreads();
 }
-__global__ void __launch_bounds__(RE_THREADS) wide_reorder_scatter_kernel(ReorderCols cols, const long long* keys, const uint8_t* key_nulls, int64_t n,
+__global__ void __launch_bounds__(RE_THREADS, 2) wide_reorder_scatter_kernel(ReorderCols cols, const long long* keys, const uint8_t* key_nulls, int64_t n,
                                                                           int shift, int P, unsigned long long* cursor, uint32_t* row_ids) {
     extern __shared__ __align__(16) unsigned char re_smem[];
     unsigned long long* stage = (unsigned long long*)re_smem;                  // RE_TILE x 8 bytes

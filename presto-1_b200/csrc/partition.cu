@@ -248,7 +248,8 @@ PG_D void scatter_all_column(const ScatterTable* tab, int c, int64_t base, int r
     uint8_t* nl = (uint8_t*)(vals + PART_TILE);
     const T* in = (const T*)tab->in[c];
     const uint8_t* in_nulls = tab->in_nulls[c];
-    const bool out_nulls = tab->nulls[c][0] != nullptr;
+    bool out_nulls = false;
+    for (int q = 0; q < tab->nparts; q++) out_nulls = out_nulls || tab->nulls[c][q] != nullptr;
 #pragma unroll
     for (int j = 0; j < PART_ITEMS; j++) {
         const int i = (warp * PART_ITEMS + j) * 32 + lane;
@@ -267,7 +268,7 @@ PG_D void scatter_all_column(const ScatterTable* tab, int c, int64_t base, int r
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(PART_THREADS) part_scatter_all_kernel(const uint8_t* __restrict__ part_of_row, int64_t n, int nparts,
+__global__ void __launch_bounds__(PART_THREADS, 4) part_scatter_all_kernel(const uint8_t* __restrict__ part_of_row, int64_t n, int nparts,
                                                                         const Pair64* __restrict__ offsets, int64_t ntiles,
                                                                         const ScatterTable* __restrict__ tab) {
     extern __shared__ __align__(16) unsigned char stage[];
@@ -526,11 +527,12 @@ int32_t pg_partition_scatter_peers_all(pg_partitioner* pt, const pg_col* cols, i
             import_col(ctx, cols[c], pt->n, imp[c]);
             tab.in[c] = imp[c].d.values; tab.in_nulls[c] = imp[c].d.nulls; tab.width[c] = type_width(cols[c].type);
             maxw = std::max(maxw, tab.width[c]);
-            const bool with_nulls = peer_nulls && peer_nulls[(size_t)c * pt->nparts] != nullptr;
+            bool with_nulls = false;        // a column travels with a mask when any receiver gave a mask buffer (empty partitions may pass NULL)
+            for (int p = 0; peer_nulls && p < pt->nparts; p++) with_nulls = with_nulls || peer_nulls[(size_t)c * pt->nparts + p] != nullptr;
             for (int p = 0; p < pt->nparts; p++) {
                 tab.base[c][p] = peer_values[(size_t)c * pt->nparts + p];
                 tab.nulls[c][p] = with_nulls ? peer_nulls[(size_t)c * pt->nparts + p] : nullptr;
-                PG_CHECK_ARG(tab.base[c][p] && (!with_nulls || tab.nulls[c][p]), "column %d: missing receive buffer of partition %d", c, p);
+                PG_CHECK_ARG(pt->part_counts[p] == 0 || (tab.base[c][p] && (!with_nulls || tab.nulls[c][p])), "column %d: missing receive buffer of partition %d", c, p);
             }
         }
         for (int p = 0; p < pt->nparts; p++) { tab.part_start[p] = pt->part_start[p]; tab.peer_row_offset[p] = peer_row_offset[p]; }

@@ -143,7 +143,8 @@ extern "C" int32_t pg_partition_positions_noalloc(pg_ctx* ctx, const int64_t* ra
         Pair64* scratch = scratch_for_device(ctx->device);      // guard() made ctx->device current
         const int64_t ntiles = (n + NA_TILE - 1) / NA_TILE;
         PG_LAUNCH(ctx, na_hist_kernel, (int)ntiles, NA_THREADS, 0, raw_hash, n, nparts, mode, out_part_of_row, scratch, ntiles);
-        scan_tile_totals(ctx, scratch, (int64_t)nparts * ntiles, scratch + (int64_t)nparts * ntiles);
+        // (the single-block scan kernel directly: scan_tile_totals() takes scratch memory from the pool for long inputs)
+        PG_LAUNCH(ctx, scan_tile_totals_kernel, 1, SCAN_THREADS, 0, scratch, (int64_t)nparts * ntiles, scratch + (int64_t)nparts * ntiles);
         PG_LAUNCH(ctx, na_rank_kernel, (int)ntiles, NA_THREADS, 0, out_part_of_row, n, nparts, scratch, ntiles, out_dest, out_counts);
         // asynchronous: the results are ready when the context's stream reaches this point (pg_ctx_synchronize / stream order)
     });

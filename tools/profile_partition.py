@@ -14,6 +14,7 @@ g = torch.Generator(device="cuda").manual_seed(1)
 key = torch.randint(0, 1 << 40, (n,), device="cuda", generator=g)
 cols = [Block(N.BIGINT, key, None, None, n), Block(N.SHORT_DECIMAL, torch.arange(n, device="cuda"), None, None, n),
         Block(N.DOUBLE, torch.arange(n, device="cuda"), None, None, n)]
+ctx.set_timing(True)
 for rep in range(2):
     counts = (C.c_int64 * nparts)()
     h = C.c_void_p()
@@ -26,3 +27,5 @@ for rep in range(2):
     torch.cuda.synchronize()
     N.lib().pg_partition_destroy(h)
 print("rows per partition:", [int(c) for c in counts])
+for k, v in sorted(ctx.kernel_report(reset=True).items(), key=lambda kv: -kv[1][0]):
+    print("%-40s %8.3f ms per launch (%d launches)" % (k, v[0] / v[1], v[1]))

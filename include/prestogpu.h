@@ -245,6 +245,17 @@ PG_API int32_t pg_hashagg_create(pg_ctx* ctx, const int32_t* key_channels, const
 PG_API int32_t pg_hashagg_destroy(pg_hashagg* op);
 /* addInput(Page) */
 PG_API int32_t pg_hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n);
+/* Reference-sized pages.  The reference hands addInput pages of at most ~1 MiB (a few thousand rows: PageBuilder /
+ * ScanFilterAndProjectOperator's merging output, OP/project/MergingPageOutput.java); one kernel pass per such page would be
+ * launch- and synchronisation-bound.  With batching on (rows > 0), host pages smaller than rows / 4 are appended to a pinned
+ * accumulator and enter the kernels as one page of about `rows` rows; page order is kept (first-seen group ids do not change),
+ * and every call that looks at the operator's state (stats, get_output*, varwidth_bytes, add_packed*) first hands the accumulated
+ * rows in.  Under a memory limit the accumulated rows stay accumulated when the flush answers PG_NEED_MEMORY.  rows = 0 turns it
+ * off (the default). */
+PG_API int32_t pg_hashagg_set_page_batching(pg_hashagg* op, int64_t rows);
+/* Feeds a host page of n rows as consecutive pages of page_rows rows, each through the path of one pg_hashagg_add_page call
+ * (a caller that holds many small pages, and bench.py's e2e_pages record). */
+PG_API int32_t pg_hashagg_add_pages(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n, int64_t page_rows);
 PG_API int32_t pg_hashagg_stats(pg_hashagg* op, int64_t* group_count, int64_t* capacity, int64_t* device_bytes, int64_t* input_rows);
 /* buildTypes(): keys..., (hash), then per aggregate its final type or its intermediate columns */
 PG_API int32_t pg_hashagg_output_types(pg_hashagg* op, int32_t* types, int32_t capacity, int32_t* ncols);

@@ -346,6 +346,15 @@ NATIVE(jint, hashaggVarwidthBytes)(JNIEnv* env, jclass cls, jlong op, jint col, 
     return rc;
 }
 NATIVE(jint, hashaggReset)(JNIEnv* env, jclass cls, jlong op) { return pg_hashagg_reset(H(pg_hashagg, op)); }
+NATIVE(jint, hashaggSetPageBatching)(JNIEnv* env, jclass cls, jlong op, jlong rows) { return pg_hashagg_set_page_batching(H(pg_hashagg, op), rows); }
+/* a page held as one large array set, fed as pages of pageRows rows (each through the per-page path) */
+NATIVE(jint, hashaggAddPages)(JNIEnv* env, jclass cls, jlong op, PAGE_PARAMS, jlong pageRows) {
+    pg_col cols[PGJ_MAX_COLS];
+    int ncols = 0;
+    int32_t rc = pgj_page_in(env, PAGE_ARGS, cols, &ncols);
+    if (rc == PG_OK) rc = pg_hashagg_add_pages(H(pg_hashagg, op), cols, ncols, positionCount, pageRows);
+    return rc;
+}
 NATIVE(jint, hashaggSetMemoryLimit)(JNIEnv* env, jclass cls, jlong op, jlong bytes) { return pg_hashagg_set_memory_limit(H(pg_hashagg, op), bytes); }
 NATIVE(jint, hashaggSetInputProcessor)(JNIEnv* env, jclass cls, jlong op, jlong project) { return pg_hashagg_set_input_processor(H(pg_hashagg, op), H(pg_project, project)); }
 /* packed pages: PARTIAL output -> FINAL input between processes (the job of PagesSerde in the reference's exchange) */

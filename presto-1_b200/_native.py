@@ -101,6 +101,8 @@ _PROTOS = {
     "pg_hashagg_varwidth_bytes": (I32, [P, I32, PI64]),
     "pg_hashagg_reset": (I32, [P]),
     "pg_hashagg_set_memory_limit": (I32, [P, I64]),
+    "pg_hashagg_set_page_batching": (I32, [P, I64]),
+    "pg_hashagg_add_pages": (I32, [P, PCOL, I32, I64, I64]),
     "pg_hashagg_get_output_packed": (I32, [P, I64, I64, P, I64, PI64, PI64]),
     "pg_hashagg_add_packed": (I32, [P, C.POINTER(C.c_void_p), I32]),
     "pg_hashagg_get_output_packed_device": (I32, [P, I64, I64, P, I64, PI64, PI64]),

@@ -184,6 +184,7 @@ int32_t pg_ctx_destroy(pg_ctx* ctx) {
     cudaSetDevice(ctx->device);
     pg::big_cache_clear(ctx);
     cudaStreamSynchronize(ctx->stream);
+    pg::page_batch_pool_free(ctx);
     if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
     if (ctx->out_dev) cudaFree(ctx->out_dev);
     if (ctx->out_pinned) cudaFreeHost(ctx->out_pinned);

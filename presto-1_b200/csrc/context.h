@@ -50,6 +50,7 @@ struct pg_ctx {
     // large freed device blocks kept for the next request of about the same size (DevBuf): a join table / aggregation state of
     // several GB is re-created for every page set, and the driver's pool, once other allocations have been carved out of the
     // freed block, stitches a new one together at 5..10 ms per GB.  All blocks belong to this context's stream.
+    std::vector<void*> page_batch_pool;     // pinned page accumulators (hashagg.cu: PageBatch) waiting for their next operator
     struct big_block { void* p; int64_t bytes; };
     std::vector<big_block> big_cache;
     int64_t big_cached_bytes = 0;
@@ -60,6 +61,7 @@ struct pg_ctx {
 namespace pg {
 cudaEvent_t timing_event(pg_ctx* ctx);
 void jit_cache_free(pg_ctx* ctx);
+void page_batch_pool_free(pg_ctx* ctx);     // hashagg.cu
 }
 
 namespace pg {

@@ -30,14 +30,52 @@ struct pg_hashagg {
     struct { pg::DevBuf groups; int64_t count = 0; bool gb_current = true; } lc;
     pg::WideTable* wide = nullptr;   // many-groups path (hashagg_wide.h), chosen on the first page
     int64_t rows_since_reset = 0;    // first-seen order of the wide path is kept by operator-wide row numbers
-    ~pg_hashagg() {
+    // page accumulator (pg_hashagg_set_page_batching): small host pages are appended to pinned buffers and enter the kernels as one
+    // page of `batch_rows` rows; anything that looks at the operator's state flushes first
+    int64_t batch_rows = 0;
+    struct PageBatch* batch = nullptr;
+    ~pg_hashagg();
+};
+
+// One pinned host copy of the channels the operator reads, `cap_rows` rows deep.  Kept by the context between operators
+// (pg_ctx::page_batch_pool): pinning tens of megabytes costs milliseconds.
+struct PageBatch {
+    struct Col {
+        int32_t type = 0;
+        bool used = false, has_nulls = false;
+        char* values = nullptr; int64_t values_cap = 0, values_used = 0;
+        uint8_t* nulls = nullptr;
+        int32_t* offsets = nullptr;
+    };
+    int64_t cap_rows = 0, rows = 0;
+    std::vector<Col> cols;
+    static void* pinned(int64_t bytes) {
+        void* p = nullptr;
+        if (cudaMallocHost(&p, (size_t)(bytes > 0 ? bytes : 8)) != cudaSuccess) { cudaGetLastError(); pg::fail(PG_E_INSUFFICIENT_RESOURCES, "pinned allocation of %lld bytes failed", (long long)bytes); }
+        return p;
+    }
+    void release() {
+        for (Col& c : cols) { if (c.values) cudaFreeHost(c.values); if (c.nulls) cudaFreeHost(c.nulls); if (c.offsets) cudaFreeHost(c.offsets); }
+        cols.clear(); cap_rows = 0; rows = 0;
+    }
+    ~PageBatch() { release(); }
+};
+
+pg_hashagg::~pg_hashagg() {
+    if (batch) { batch->rows = 0; ctx->page_batch_pool.push_back(batch); batch = nullptr; }
+    {
         delete wide;
         for (pg_agg* a : aggs) delete a;
         delete gb;
     }
-};
+}
 
 namespace pg {
+
+void page_batch_pool_free(pg_ctx* ctx) {
+    for (void* b : ctx->page_batch_pool) delete (PageBatch*)b;
+    ctx->page_batch_pool.clear();
+}
 
 static DCol dcol_offset(const DCol& c, int64_t off) {
     DCol r = c;
@@ -505,6 +543,132 @@ static void hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
     sync(ctx);   // staged host columns are released when `imp` goes out of scope
 }
 
+
+// ------------------------------------------------------------------ page accumulator
+static void hashagg_reserve(pg_hashagg* op, int64_t n) {
+    // memory yield: checked before the first row is consumed, for whichever table the rows may grow
+    if (op->gb->memory_limit <= 0) return;
+    if (op->wide && !op->wide->prepared) {
+        WideTable* w = op->wide;
+        if (w->claimed + n > w->max_fill) {
+            int64_t cap = w->cap;
+            while ((int64_t)(cap * 0.75) < w->claimed + n) cap *= 2;
+            const int64_t after = w->device_bytes() - w->table.bytes + (cap + 2) * (int64_t)w->bucket_words * 8;
+            if (after > op->gb->memory_limit)
+                fail(PG_NEED_MEMORY, "the aggregation table may have to grow to %lld bytes for this page, the memory limit is %lld; nothing was consumed",
+                     (long long)after, (long long)op->gb->memory_limit);
+        }
+    } else groupby_reserve(op->gb, n);
+}
+
+static bool channel_is_read(const pg_hashagg* op, int c) {
+    if (op->proc) return c < (int)op->proc->channel_used.size() && op->proc->channel_used[c];
+    if (c == op->hash_channel) return true;
+    for (int k : op->key_channels) if (k == c) return true;
+    for (const pg_agg_spec& s : op->specs) if (s.input_channel == c || s.mask_channel == c) return true;
+    return false;
+}
+
+// true when the page was taken into the accumulator
+static bool batch_append(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n) {
+    if (op->batch_rows <= 0 || n <= 0 || n * 4 > op->batch_rows) return false;
+    for (int c = 0; c < ncols; c++) if (channel_is_read(op, c) && cols[c].mem != PG_MEM_HOST) return false;
+    PageBatch* b = op->batch;
+    if (!b) {
+        pg_ctx* ctx = op->ctx;
+        if (!ctx->page_batch_pool.empty()) { b = (PageBatch*)ctx->page_batch_pool.back(); ctx->page_batch_pool.pop_back(); }
+        else b = new PageBatch();
+        op->batch = b;
+    }
+    // (re)shape the accumulator when it comes from another operator's plan
+    bool same = b->cap_rows >= op->batch_rows && (int)b->cols.size() == ncols;
+    for (int c = 0; same && c < ncols; c++) {
+        const bool used = channel_is_read(op, c);
+        if (b->cols[c].used != used || (used && b->cols[c].type != cols[c].type)) same = false;
+    }
+    if (!same) {
+        PG_CHECK_STATE(b->rows == 0, "page accumulator reshaped while it holds rows");
+        b->release();
+        b->cap_rows = op->batch_rows;
+        b->cols.resize(ncols);
+        for (int c = 0; c < ncols; c++) {
+            PageBatch::Col& bc = b->cols[c];
+            bc.used = channel_is_read(op, c);
+            bc.type = cols[c].type;
+            if (!bc.used) continue;
+            PG_CHECK_ARG(type_valid(bc.type), "unknown column type %d", bc.type);
+            if (type_is_var(bc.type)) {
+                bc.values_cap = b->cap_rows * 16;
+                bc.offsets = (int32_t*)PageBatch::pinned((b->cap_rows + 1) * 4);
+            } else bc.values_cap = b->cap_rows * (int64_t)type_width(bc.type);
+            bc.values = (char*)PageBatch::pinned(bc.values_cap);
+            bc.nulls = (uint8_t*)PageBatch::pinned(b->cap_rows);
+        }
+    }
+    if (b->rows + n > b->cap_rows) return false;           // the caller flushes and tries again
+    for (int c = 0; c < ncols; c++) {
+        PageBatch::Col& bc = b->cols[c];
+        if (!bc.used) continue;
+        const pg_col& in = cols[c];
+        PG_CHECK_ARG(in.type == bc.type && in.n == n, "channel %d: type %d / %lld rows, the accumulated pages have type %d / this page %lld rows", c, in.type,
+                     (long long)in.n, bc.type, (long long)n);
+        if (type_is_var(bc.type)) {
+            PG_CHECK_ARG(in.offsets != nullptr, "variable width channel %d without offsets", c);
+            const int64_t first = in.offsets[0], bytes = (int64_t)in.offsets[n] - first;
+            if (bc.values_used + bytes > bc.values_cap) {
+                int64_t cap = bc.values_cap * 2;
+                while (cap < bc.values_used + bytes) cap *= 2;
+                PG_CHECK_ARG(cap < 0x7fffffffLL, "variable width channel %d exceeds 2 GB per batch", c);
+                char* nv = (char*)PageBatch::pinned(cap);
+                memcpy(nv, bc.values, (size_t)bc.values_used);
+                cudaFreeHost(bc.values);
+                bc.values = nv; bc.values_cap = cap;
+            }
+            if (bytes > 0) memcpy(bc.values + bc.values_used, (const char*)in.values + first, (size_t)bytes);
+            for (int64_t i = 0; i <= n; i++) bc.offsets[b->rows + i] = (int32_t)(bc.values_used + (in.offsets[i] - first));
+            bc.values_used += bytes;
+        } else {
+            const int w = type_width(bc.type);
+            memcpy(bc.values + b->rows * w, in.values, (size_t)(n * w));
+        }
+        if (in.nulls) {
+            if (!bc.has_nulls) { memset(bc.nulls, 0, (size_t)b->rows); bc.has_nulls = true; }
+            memcpy(bc.nulls + b->rows, in.nulls, (size_t)n);
+        } else if (bc.has_nulls) memset(bc.nulls + b->rows, 0, (size_t)n);
+    }
+    b->rows += n;
+    return true;
+}
+
+// hands the accumulated rows to the kernels as one page; on PG_NEED_MEMORY they stay accumulated
+static void batch_flush(pg_hashagg* op) {
+    PageBatch* b = op->batch;
+    if (!b || b->rows == 0) return;
+    std::vector<pg_col> cols(b->cols.size());
+    for (size_t c = 0; c < cols.size(); c++) {
+        const PageBatch::Col& bc = b->cols[c];
+        memset(&cols[c], 0, sizeof(pg_col));
+        cols[c].type = bc.type; cols[c].mem = PG_MEM_HOST; cols[c].n = b->rows;
+        if (!bc.used) continue;
+        cols[c].values = bc.values; cols[c].nulls = bc.has_nulls ? bc.nulls : nullptr; cols[c].offsets = type_is_var(bc.type) ? bc.offsets : nullptr;
+    }
+    hashagg_reserve(op, b->rows);
+    hashagg_add_page(op, cols.data(), (int32_t)cols.size(), b->rows);      // synchronises: the pinned rows have left when it returns
+    b->rows = 0;
+    for (PageBatch::Col& bc : b->cols) { bc.values_used = 0; bc.has_nulls = false; }
+}
+
+static void hashagg_add_page_batched(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n) {
+    if (batch_append(op, cols, ncols, n)) {
+        if (op->batch->rows >= op->batch_rows) batch_flush(op);
+        return;
+    }
+    batch_flush(op);                                   // keeps page order: earlier rows first
+    if (batch_append(op, cols, ncols, n)) return;      // it did not fit before the flush
+    hashagg_reserve(op, n);
+    hashagg_add_page(op, cols, ncols, n);
+}
+
 }  // namespace pg
 
 using namespace pg;
@@ -539,21 +703,35 @@ int32_t pg_hashagg_add_page(pg_hashagg* op, const pg_col* cols, int32_t ncols, i
     if (!op) return PG_E_INVALID_ARGUMENT;
     return guard(op->ctx, [&] {
         PG_CHECK_ARG(cols && ncols > 0 && n >= 0, "bad arguments");
-        // memory yield: checked before the first row is consumed, for whichever table this page may grow
-        if (op->gb->memory_limit > 0) {
-            if (op->wide && !op->wide->prepared) {
-                WideTable* w = op->wide;
-                if (w->claimed + n > w->max_fill) {
-                    int64_t cap = w->cap;
-                    while ((int64_t)(cap * 0.75) < w->claimed + n) cap *= 2;
-                    const int64_t after = w->device_bytes() - w->table.bytes + (cap + 2) * (int64_t)w->bucket_words * 8;
-                    if (after > op->gb->memory_limit)
-                        fail(PG_NEED_MEMORY, "the aggregation table may have to grow to %lld bytes for this page, the memory limit is %lld; nothing was consumed",
-                             (long long)after, (long long)op->gb->memory_limit);
-                }
-            } else groupby_reserve(op->gb, n);
+        hashagg_add_page_batched(op, cols, ncols, n);
+    });
+}
+
+int32_t pg_hashagg_set_page_batching(pg_hashagg* op, int64_t rows) {
+    if (!op || rows < 0) return PG_E_INVALID_ARGUMENT;
+    return guard(op->ctx, [&] {
+        batch_flush(op);
+        op->batch_rows = rows;
+    });
+}
+
+int32_t pg_hashagg_add_pages(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n, int64_t page_rows) {
+    if (!op) return PG_E_INVALID_ARGUMENT;
+    return guard(op->ctx, [&] {
+        PG_CHECK_ARG(cols && ncols > 0 && n >= 0 && page_rows > 0, "bad arguments");
+        std::vector<pg_col> page(ncols);
+        for (int64_t at = 0; at < n; at += page_rows) {
+            const int64_t m = n - at < page_rows ? n - at : page_rows;
+            for (int c = 0; c < ncols; c++) {
+                PG_CHECK_ARG(cols[c].mem == PG_MEM_HOST, "pg_hashagg_add_pages takes host pages");
+                page[c] = cols[c];
+                page[c].n = m;
+                if (page[c].nulls) page[c].nulls += at;
+                if (type_is_var(page[c].type)) { if (page[c].offsets) page[c].offsets += at; }
+                else if (page[c].values) page[c].values = (const char*)page[c].values + at * type_width(page[c].type);
+            }
+            hashagg_add_page_batched(op, page.data(), ncols, m);       // the same path as one pg_hashagg_add_page call per page
         }
-        hashagg_add_page(op, cols, ncols, n);
     });
 }
 
@@ -565,6 +743,10 @@ int32_t pg_hashagg_set_memory_limit(pg_hashagg* op, int64_t bytes) {
 
 int32_t pg_hashagg_stats(pg_hashagg* op, int64_t* group_count, int64_t* capacity, int64_t* device_bytes, int64_t* input_rows) {
     if (!op) return PG_E_INVALID_ARGUMENT;
+    if (op->batch && op->batch->rows > 0) {          // accumulated pages count as consumed input: bring the state up to date first
+        const int32_t rc = guard(op->ctx, [&] { batch_flush(op); });
+        if (rc != PG_OK) return rc;
+    }
     if (op->wide && !op->wide->prepared) {
         // ids do not exist yet; the count and the reference's capacity schedule follow the buckets in use
         op->gb->groups = op->wide->groups();
@@ -630,6 +812,7 @@ int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_o
     if (!op) return PG_E_INVALID_ARGUMENT;
     return guard(op->ctx, [&] {
         pg_ctx* ctx = op->ctx;
+        batch_flush(op);
         if (op->wide) wide_prepare_output(op->wide, op->gb, op->aggs, op->rows_since_reset);
         const int64_t total = hashagg_group_count(op);
         PG_CHECK_ARG(out && first >= 0 && n >= 0 && first + n <= total, "group range outside [0, %lld)", (long long)total);
@@ -687,6 +870,10 @@ int32_t pg_hashagg_get_output(pg_hashagg* op, int64_t first, int64_t n, pg_col_o
 /* value bytes needed for output column `col` (variable width key or VARBINARY intermediate state) */
 int32_t pg_hashagg_varwidth_bytes(pg_hashagg* op, int32_t col, int64_t* out_bytes) {
     if (!op || !out_bytes) return PG_E_INVALID_ARGUMENT;
+    if (op->batch && op->batch->rows > 0) {
+        const int32_t rc = guard(op->ctx, [&] { batch_flush(op); });
+        if (rc != PG_OK) return rc;
+    }
     int nk = (int)op->key_types.size();
     if (col < nk && !op->lc.gb_current) { *out_bytes = 3 * op->lc.count; return PG_OK; }     // packed keys: strings of at most 3 bytes
     if (col < nk) return pg_groupby_varwidth_bytes(op->gb, col, out_bytes);
@@ -805,6 +992,10 @@ int32_t pg_hashagg_add_packed_device(pg_hashagg* op, const void* device_bufs, in
 
 int32_t pg_hashagg_add_packed(pg_hashagg* op, const void* const* bufs, int32_t nbufs) {
     if (!op) return PG_E_INVALID_ARGUMENT;
+    if (op->batch && op->batch->rows > 0) {
+        const int32_t rc = guard(op->ctx, [&] { batch_flush(op); });
+        if (rc != PG_OK) return rc;
+    }
     int32_t ncols = -1;
     int64_t total = 0;
     std::vector<std::vector<char>> values, nulls;
@@ -875,6 +1066,7 @@ int32_t pg_hashagg_set_input_processor(pg_hashagg* op, pg_project* p) {
 int32_t pg_hashagg_reset(pg_hashagg* op) {
     if (!op) return PG_E_INVALID_ARGUMENT;
     return guard(op->ctx, [&] {
+        if (op->batch) { op->batch->rows = 0; for (PageBatch::Col& bc : op->batch->cols) { bc.values_used = 0; bc.has_nulls = false; } }
         for (pg_agg* a : op->aggs) delete a;
         op->aggs.clear();
         delete op->gb; op->gb = nullptr;

@@ -54,6 +54,16 @@ class HashAggregationOperator:
         self._flushing = False
         self._unfinished = None      # unfinishedWork (:398-417): a page the memory limit has not let in yet
 
+    def set_page_batching(self, rows):
+        """Reference-sized pages: small host pages are accumulated and enter the kernels `rows` rows at a time (0 = off)."""
+        N.check(self.ctx.handle, N.lib().pg_hashagg_set_page_batching(self._h, int(rows)))
+
+    def add_pages(self, page, page_rows):
+        """The host page as consecutive pages of page_rows rows, each through the per-page addInput path (pg_hashagg_add_pages)."""
+        assert self.needs_input(), "Operator is already finishing"
+        blocks = page.blocks if isinstance(page, Page) else list(page)
+        N.check(self.ctx.handle, N.lib().pg_hashagg_add_pages(self._h, col_array(blocks), len(blocks), blocks[0].n, int(page_rows)))
+
     def set_memory_limit(self, nbytes):
         """The operator's memory yield: with a limit set, add_input keeps a page that could grow the table past it as unfinished
         work instead of consuming it (pg_hashagg_set_memory_limit)."""

@@ -257,18 +257,20 @@ def test_fused_low_cardinality_page_with_late_and_unpackable_keys(pgpu, key_kind
                 assert x == y
 
 
-def _oracle_rows(P, key_block, agg_pages, aggs, step_final=True):
-    """Oracle result in group-id (= first-seen) order: list of tuples (key, agg0, agg1, ...)."""
-    ogb = O.OracleGroupBy([P.BIGINT], 10_000)
+def _oracle_rows(P, key_block, agg_pages, aggs, step_final=True, key_types=None, key_channels=None):
+    """Oracle result in group-id (= first-seen) order: list of tuples (key..., agg0, agg1, ...)."""
+    key_types = key_types or [P.BIGINT]
+    key_channels = key_channels or [0]
+    ogb = O.OracleGroupBy(key_types, 10_000)
     accs = [O.OracleAccumulator(a.kind, a.in_type) for a in aggs]
     for blocks in agg_pages:
-        ids = ogb.get_group_ids([blocks[0]])
+        ids = ogb.get_group_ids([blocks[c] for c in key_channels])
         g = ogb.group_count()
         for a, oa in zip(aggs, accs):
             oa.add_input(ids, g, blocks[a.input_channel] if a.input_channel >= 0 else None, blocks[a.mask_channel] if a.mask_channel >= 0 else None)
     g = ogb.group_count()
     keys, _ = ogb.export(with_hash=False)
-    cols = [keys[0].to_list()]
+    cols = [k.to_list() for k in keys]
     for oa in accs:
         rc, out, _ = oa.evaluate(0, g, step_final)
         assert rc == 0
@@ -503,3 +505,63 @@ def test_operator_yields_on_memory_limit_and_counts_every_row_once(pgpu):
     got = rows_of(drain(op))
     want = _oracle_rows(P, None, [blocks], aggs)
     _assert_rows_equal(got, want)
+
+
+@pytest.mark.parametrize("shape", ["q1_varchar_keys", "bigint_key_many_groups"])
+def test_reference_sized_pages_through_the_accumulator_equal_one_big_page(pgpu, shape):
+    """pg_hashagg_set_page_batching: 1 000-row host pages (nulls first appearing in a later page, a nullable mask, variable width
+    keys) accumulate and enter the kernels a batch at a time; group ids keep their first-seen order and every aggregate equals
+    the oracle's — also when the stream ends in the middle of a batch and when stats are read half way."""
+    P = pgpu
+    rng = np.random.default_rng(11)
+    n = 57_321
+    if shape == "q1_varchar_keys":
+        flags = np.array(["A", "N", "R"])[rng.integers(0, 3, n)]
+        status = np.array(["F", "O"])[rng.integers(0, 2, n)]
+        keys = [P.Block.variable_width(list(flags)), P.Block.variable_width(list(status))]
+        key_types, key_channels = [P.VARCHAR, P.VARCHAR], [0, 1]
+    else:
+        keys = [P.Block.long_array(rng.integers(0, 20_000, n).astype(np.int64))]
+        key_types, key_channels = [P.BIGINT], [0]
+    nk = len(keys)
+    dec = rng.integers(-10**12, 10**12, n).astype(np.int64)
+    dnull = (rng.random(n) < 0.1).astype(np.uint8)
+    dnull[:20_000] = 0                       # the first pages arrive without a null mask
+    dbl = rng.random(n) * 1e4
+    mask = (rng.random(n) < 0.7).astype(np.uint8)
+    cols = keys + [P.Block.long_array(dec, dnull, P.SHORT_DECIMAL), P.Block.double_array(dbl), P.Block.byte_array(mask)]
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, nk), P.AggregatorFactory(P.AGG_AVG, P.SHORT_DECIMAL, nk, nk + 2),
+            P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, nk + 1), P.AggregatorFactory(P.AGG_MAX, P.SHORT_DECIMAL, nk)]
+
+    def page(lo, hi):
+        out = []
+        for b in cols:
+            if b.type in (P.VARCHAR, P.VARBINARY):
+                out.append(P.Block(b.type, b.values, None, b.offsets[lo:hi + 1], hi - lo))
+            else:
+                nulls = None if b.nulls is None or not b.nulls[lo:hi].any() and hi <= 20_000 else b.nulls[lo:hi]
+                out.append(P.Block(b.type, b.values[lo:hi], nulls, None, hi - lo))
+        return out
+
+    pages = [page(lo, min(lo + 1000, n)) for lo in range(0, n, 1000)]
+    op = P.HashAggregationOperator(key_types, key_channels, P.SINGLE, aggs, expected_groups=100)
+    op.set_page_batching(16_000)
+    op.ctx.kernel_report(reset=True)
+    op.ctx.set_timing(True)
+    for i, pg_ in enumerate(pages):
+        op.add_input(P.Page(*pg_))
+        if i == 30:
+            assert op._stats()[3] == 31_000        # input rows: reading the stats hands the accumulated pages in
+    op.finish()
+    got = rows_of(drain(op))
+    launches = sum(v[1] for v in op.ctx.kernel_report(reset=True).values())
+    op.ctx.set_timing(False)
+    want = _oracle_rows(P, None, [cols], aggs, key_types=key_types, key_channels=key_channels) if shape == "q1_varchar_keys" else _oracle_rows(P, None, [cols], aggs)
+    _assert_rows_equal(got, want)
+    assert launches < 40 * 6, "the pages were not batched: %d kernel launches for %d pages" % (launches, len(pages))
+    # the bulk form of the same thing
+    op2 = P.HashAggregationOperator(key_types, key_channels, P.SINGLE, aggs, expected_groups=100)
+    op2.set_page_batching(16_000)
+    op2.add_pages(P.Page(*cols), 1000)
+    op2.finish()
+    _assert_rows_equal(rows_of(drain(op2)), want)

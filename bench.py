@@ -20,6 +20,7 @@ exists here) on all host threads over the same Q1 input.
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -61,6 +62,10 @@ def parse_args():
     ap.add_argument("--wide-warmup", type=int, default=3)
     ap.add_argument("--cpu-sample-rows", type=int, default=6_000_000)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-e2e-pages", action="store_true")
+    ap.add_argument("--page-rows", type=int, default=8192, help="rows per page of the e2e_pages record (the reference's pages hold a few thousand rows)")
+    ap.add_argument("--page-batch-rows", type=int, default=1 << 20)
+    ap.add_argument("--page-drivers", type=int, default=16)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-workloads", action="store_true", help="headline only (skips the SF100 GROUP BY orderkey / join records)")
     ap.add_argument("--no-crosscheck", action="store_true", help="skip the small-scale oracle cross-checks (profiling runs)")
@@ -70,14 +75,52 @@ def parse_args():
 
 # ------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """Samples SM clocks / throttle reasons during the timed region (B200_PROFILING.md recipe).  In-process NVML (nvidia_ml_py) when
+    it is importable — a query takes microseconds and does not disturb the run; one `nvidia-smi` process per sample (tens of
+    milliseconds of host work and driver locks each: measured to cost 25 % of the 8-GPU Q1 step when every rank did it) otherwise."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, device):
         self.device, self.samples, self._stop, self._t = device, [], threading.Event(), None
+        self.source = None
+
+    def _nvml_handle(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            idx = self.device
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                idx = int(vis.split(",")[self.device])
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(idx)
+        except Exception:
+            return None, None
 
     def _run(self):
+        nv, h = self._nvml_handle()
+        if nv is not None:
+            self.source = "nvml"
+            bits = [(0x8, 0), (0x40, 1), (0x20, 2), (0x4, 3)]      # hw_slowdown, hw_thermal, sw_thermal, sw_power_cap
+            try:
+                mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            except Exception:
+                mx = None
+            while not self._stop.is_set():
+                try:
+                    sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                    try:
+                        r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    except Exception:
+                        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    row = [str(sm), str(mx)] + ["Active" if r & bit else "Not Active" for bit, _ in bits]
+                    self.samples.append(row)
+                except Exception:
+                    pass
+                self._stop.wait(0.005)
+            return
+        self.source = "nvidia-smi"
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
@@ -89,23 +132,24 @@ class ClockSampler:
             self._stop.wait(0.1)
 
     def __enter__(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
+        if self.device is not None:     # None: this rank does not sample (rank 0 prints the line; one sampler per node keeps the host quiet)
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
         return self
 
     def __exit__(self, *a):
         self._stop.set()
-        self._t.join(timeout=6)
+        if self._t is not None:
+            self._t.join(timeout=6)
 
     def summary(self):
         if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock samples (nvml / nvidia-smi unavailable)"]}
         sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
+        reasons = [n for i, n in enumerate(self.NAMES) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
         mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.samples)}
+                "samples": len(self.samples), "source": self.source}
 
 
 def q1_config(sf, rows):
@@ -126,6 +170,77 @@ def result_digest(out):
 
 
 # ------------------------------------------------------------------------------------------- CPU arm (oracle port)
+def slice_host_block(P, b, lo, hi):
+    """Rows [lo, hi) of a host block as a view (no copy)."""
+    from presto_b200.blocks import Block
+    if b.type in (P.VARCHAR, P.VARBINARY):
+        return Block(b.type, b.values, None if b.nulls is None else b.nulls[lo:hi], b.offsets[lo:hi + 1], hi - lo)
+    k = 2 if b.type == P.LONG_DECIMAL else 1
+    return Block(b.type, b.values[k * lo:k * hi], None if b.nulls is None else b.nulls[lo:hi], None, hi - lo, b.precision, b.scale)
+
+
+class PagedDrivers:
+    """The reference's shape of a scan stage: T driver threads, each with its own PARTIAL operator (and context / stream), fed
+    reference-sized host pages one addInput at a time; one FINAL operator merges the drivers' intermediate pages.  The page loop
+    runs in C (pg_hashagg_add_pages: each page goes through pg_hashagg_add_page's path) so that Python's per-call cost is not what
+    is measured; the pinned page accumulator batches the pages (pg_hashagg_set_page_batching)."""
+
+    def __init__(self, P, tpch, torch, device, hpage, nthreads, page_rows, batch_rows):
+        from presto_b200.context import GpuContext
+        from presto_b200.plans import final_aggregators
+        self.P, self.torch, self.page_rows, self.batch_rows, self.T = P, torch, page_rows, batch_rows, nthreads
+        self.aggs = tpch.q1_fused_aggregators()
+        self.fin_aggs = final_aggregators(self.aggs, 2)
+        flt, proj = tpch.q1_expressions()
+        n = hpage.position_count
+        self.slices, self.ctxs, self.procs, self.streams, self.bufs = [], [], [], [], []
+        for t in range(nthreads):
+            lo, hi = n * t // nthreads, n * (t + 1) // nthreads
+            self.slices.append(P.Page(*[slice_host_block(P, b, lo, hi) for b in hpage.blocks], position_count=hi - lo))
+            st = torch.cuda.Stream()
+            with torch.cuda.stream(st):
+                ctx = GpuContext(device)
+            self.streams.append(st)
+            self.ctxs.append(ctx)
+            self.procs.append(P.PageProcessor(flt, proj, ctx=ctx))
+            self.bufs.append(torch.empty(1 << 16, dtype=torch.uint8).pin_memory())
+        self.main_ctx = GpuContext(device)
+        self.err = None
+
+    def _driver(self, t):
+        P = self.P
+        try:
+            self.torch.cuda.set_device(self.ctxs[t].device)
+            op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.PARTIAL, self.aggs, expected_groups=100_000, ctx=self.ctxs[t],
+                                           input_processor=self.procs[t])
+            op.set_page_batching(self.batch_rows)
+            op.add_pages(self.slices[t], self.page_rows)
+            op.finish()
+            op.get_output_packed(self.bufs[t].data_ptr(), self.bufs[t].numel())
+            op.close()
+        except BaseException as e:      # surfaced by step()
+            self.err = e
+
+    def step(self):
+        P = self.P
+        threads = [threading.Thread(target=self._driver, args=(t,)) for t in range(self.T)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        if self.err is not None:
+            raise self.err
+        fin = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, self.fin_aggs, expected_groups=1000, ctx=self.main_ctx)
+        fin.add_packed([b.data_ptr() for b in self.bufs])
+        fin.finish()
+        out = fin.get_output()
+        fin.close()
+        return out
+
+    def launch_count(self):
+        return sum(c.launch_count() for c in self.ctxs) + self.main_ctx.launch_count()
+
+
 def oracle_q1_pass(O, P, blocks, aggs, nthreads, exprs=None):
     """The reference's plan on host cores: `nthreads` drivers each run ScanFilterAndProject (filter + projections), then getGroupIds
     + accumulators (PARTIAL) over a slice of the pages, then one FINAL merge — restated in oracle/ (C++), called through ctypes
@@ -257,7 +372,7 @@ class Env:
         return ms, out, ctx.kernel_report(reset=True), ctx.launch_count() - l0
 
 
-def workload_roofline(env, kern, steps, rows_per_gpu, traffic):
+def workload_roofline(env, kern, steps, rows_per_gpu, traffic, name=None):
     """roofline record of a workload's dominant kernel, from the library's per-launch CUDA events inside the timed region."""
     known = {k: v for k, v in kern.items() if k in KERNEL_BYTES}
     pool = known or kern
@@ -274,7 +389,9 @@ def workload_roofline(env, kern, steps, rows_per_gpu, traffic):
         ach = rows_per_launch * bpr / (launch_ms / 1e3) / 1e9
         rec.update({"algorithmic_bytes_per_row": bpr, "rows_per_launch": int(rows_per_launch), "achieved": round(ach, 1),
                     "frac": round(ach / env.peak, 4)})
-    t = traffic.get(top + "@sf100") if traffic else None
+    t = None
+    if traffic and env.world == 1 and rows_per_gpu > 140_000_000:      # the captures are one-GPU SF100 launches: per-launch traffic at other sizes is not comparable
+        t = traffic.get("%s:%s" % (name, top), traffic.get(top + "@sf100"))
     rec["traffic"] = t
     if t is not None:
         rec["traffic_unit"] = "bytes/launch (ncu dram read+write, SF100 capture on 1 GPU)"
@@ -284,7 +401,7 @@ def workload_roofline(env, kern, steps, rows_per_gpu, traffic):
 def record(env, name, desc, rows_all, ms, brow, kern, steps, rows_per_gpu, traffic, extra=None):
     r = {"workload": desc, "rows": int(rows_all), "ms_per_step": round(ms, 3), "rows_per_s": rows_all / (ms / 1e3),
          "algorithmic_bytes_per_row": brow, "hbm_frac_per_gpu": round(rows_all / env.world * brow / (ms / 1e3) / 1e9 / env.peak, 4),
-         "steps": steps, "roofline": workload_roofline(env, kern, steps, rows_per_gpu, traffic)}
+         "steps": steps, "roofline": workload_roofline(env, kern, steps, rows_per_gpu, traffic, name)}
     if extra:
         r.update(extra)
     return r
@@ -569,11 +686,11 @@ def gpu_arm(args):
     input_bytes = rows * tpch.Q1_RAW_BYTES_PER_ROW    # > 126 MB L2: every step streams its inputs from HBM
 
     plan = P.PartialFinalAggregation([P.VARCHAR, P.VARCHAR], [0, 1], aggs, ctx, dist, expected_groups=100_000,
-                                     reserve_sms=int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "4")), input_processor=processor,
+                                     reserve_sms=int(os.environ.get("PRESTOGPU_BENCH_RESERVE_SMS", "4" if world <= 2 else "8")), input_processor=processor,
                                      pipeline=os.environ.get("PRESTOGPU_BENCH_PIPELINE", "1") != "0")
 
     ctx.set_timing(True)
-    with ClockSampler(local_rank) as clk:
+    with ClockSampler(local_rank if rank == 0 else None) as clk:
         l2 = plan.launch_count()
         ms, out, kernels, launches = env.timed(lambda: plan.submit(page), args.steps, args.warmup, drain=plan.drain)
         launches += plan.launch_count() - l2
@@ -603,6 +720,7 @@ def gpu_arm(args):
         raise SystemExit("bench self-check failed: %s" % json.dumps(selfcheck))
 
     # e2e: host (pinned) buffers through the same operator / C ABI call; H2D copies inside the timed region
+    e2e_pages = None
     e2e = None
     if not args.no_e2e:
         hpage = tpch.page_to_host(page, pinned=True)
@@ -611,6 +729,31 @@ def gpu_arm(args):
         out_bytes = sum(int(np.asarray(b.to_host().values).nbytes) for b in eout.blocks)
         e2e = {"value": total_rows / (ems / 1e3), "unit": "rows/s", "h2d_bytes_per_step": int(input_bytes),
                "d2h_bytes_per_step": int(out_bytes), "ms_per_step": round(ems, 3), "steps": e_steps, "warmup": 3}
+        # the same end-to-end pass with the input arriving as reference-sized pages on several driver threads
+        if not args.no_e2e_pages:
+            nthreads = max(1, min(args.page_drivers, (os.cpu_count() or 8) // max(world, 1)))
+            drivers = PagedDrivers(P, tpch, torch, local_rank, hpage, nthreads, args.page_rows, args.page_batch_rows)
+            for _ in range(2):
+                pout = drivers.step()
+            env.barrier()
+            l0 = drivers.launch_count()
+            t0 = time.perf_counter()
+            for _ in range(e_steps):
+                pout = drivers.step()
+            torch.cuda.synchronize()
+            pms = env.max_over_ranks((time.perf_counter() - t0) * 1e3) / e_steps
+            pcheck = q1_selfcheck(torch, cols, pout, None) if world == 1 else {"sums_bit_exact_vs_torch_int64": None}
+            if world == 1 and not pcheck["sums_bit_exact_vs_torch_int64"]:
+                raise SystemExit("bench self-check failed (e2e_pages): %s" % json.dumps(pcheck))
+            e2e_pages = {"value": total_rows / (pms / 1e3), "unit": "rows/s", "ms_per_step": round(pms, 3), "steps": e_steps, "warmup": 2,
+                         "page_rows": args.page_rows, "pages_per_step": int(math.ceil(rows / args.page_rows)), "driver_threads": nthreads,
+                         "batch_rows": args.page_batch_rows, "h2d_bytes_per_step": int(input_bytes),
+                         "gpu_launches_per_step": (drivers.launch_count() - l0) // e_steps,
+                         "ratio_to_e2e": round((total_rows / (pms / 1e3)) / e2e["value"], 4),
+                         "how": "host pages of page_rows rows, one addInput (pg_hashagg_add_page path, looped in C) per page on each of driver_threads "
+                                "PARTIAL operators; pinned page accumulator; one FINAL merge; wall clock, max over ranks",
+                         "selfcheck": pcheck}
+            del drivers
         del hpage
     plan.close()
 
@@ -636,7 +779,7 @@ def gpu_arm(args):
             "dtype": "int128/int64 (decimal sums), u8 keys", "data": "synthetic (TPC-H-shaped generator, seeded)",
             "config": q1_config(args.sf, rows),
             "plan": "SINGLE" if world == 1 else "PARTIAL -> packed page in device memory -> NCCL all_gather (device to device) -> FINAL on every rank; the FINAL stage of step i overlaps the PARTIAL stage of step i+1",
-            "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
+            "clocks": clk.summary(), "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e, "e2e_pages": e2e_pages,
             "selfcheck": selfcheck, "result_digest": result_digest(out) if world == 1 else None,
         }
         if cpu:

@@ -219,7 +219,8 @@ __global__ void __launch_bounds__(256) j_key_range_kernel(const int64_t* __restr
 // slower), then every lane that saw a free slot claims it with ONE 128-bit compare-and-swap that also sets count = 1 and head = row.
 // Only rows whose key is already there (duplicate build keys) need the separate count / head atomics.  Lanes leaving a
 // data-dependent loop at different iterations are not brought back together by the hardware, hence the __any_sync rounds.
-// meta: [0] duplicate flag (int), [4] slots claimed, [5] rows inserted, [8] set when the hashed region behind a range region is too full
+// meta: [0] duplicate flag (int), [4] slots claimed, [5] rows inserted, [8] set when the hashed region behind a range region is too full,
+//       [9] slots claimed in that hashed region (the host enforces a load factor of 3/4 on it)
 __global__ void __launch_bounds__(J_THREADS) j_build_fast_kernel(JSlot* slots, JLayout L, const int64_t* __restrict__ keys,
                                                                  const uint8_t* __restrict__ nulls, int64_t rows, int32_t* row_slot,
                                                                  unsigned long long* meta) {
@@ -227,7 +228,7 @@ __global__ void __launch_bounds__(J_THREADS) j_build_fast_kernel(JSlot* slots, J
     const int64_t threads = (int64_t)gridDim.x * blockDim.x;
     const int lane = threadIdx.x & 31;
     const unsigned long long EMPTY_HI = 0xFFFFFFFF00000000ULL;          // count 0, head -1
-    unsigned long long claims = 0, inserted = 0;
+    unsigned long long claims = 0, inserted = 0, oclaims = 0;      // oclaims: claims inside the hashed region behind a range region
     bool special_dup = false, failed = false;
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; base - lane < rows; base += threads * R) {
         unsigned long long key[R];
@@ -274,7 +275,7 @@ __global__ void __launch_bounds__(J_THREADS) j_build_fast_kernel(JSlot* slots, J
 #pragma unroll
             for (int k = 0; k < R; k++) {
                 if (st[k] == 2) {
-                    if (olo[k] == EMPTY_KEY) { claims++; inserted++; st[k] = 0; }
+                    if (olo[k] == EMPTY_KEY) { claims++; inserted++; st[k] = 0; if (L.range && p[k] >= L.R) oclaims++; }
                     else if (olo[k] == key[k]) st[k] = 3;
                     else { jl_next(L, h[k], p[k], left[k]); st[k] = 1; }
                 }
@@ -297,10 +298,12 @@ __global__ void __launch_bounds__(J_THREADS) j_build_fast_kernel(JSlot* slots, J
     for (int d = 16; d > 0; d >>= 1) {
         claims += __shfl_down_sync(0xffffffffu, claims, d);
         inserted += __shfl_down_sync(0xffffffffu, inserted, d);
+        oclaims += __shfl_down_sync(0xffffffffu, oclaims, d);
     }
     if (lane == 0) {
         if (claims) atomicAdd(meta + 4, claims);       // words 0..3 of meta belong to the duplicate flag and the segment sort
         if (inserted) atomicAdd(meta + 5, inserted);
+        if (oclaims) atomicAdd(meta + 9, oclaims);
     }
     if (special_dup) *(int*)meta = 1;
     if (failed) meta[8] = 1;
@@ -821,8 +824,11 @@ static void lookup_build(pg_lookup* ls) {
             const DCol& kc = build.c[0];
             PG_LAUNCH(ctx, j_build_fast_kernel, grid_for(ctx, rows, J_THREADS, 4), J_THREADS, 0, ls->slots.as<JSlot>(), L, (const int64_t*)kc.values,
                       kc.nulls, rows, row_slot.as<int32_t>(), ls->meta.as<unsigned long long>());
-            int64_t m[9];
-            read_scalars(ctx, ls->meta.p, 9, m);
+            int64_t m[10];
+            read_scalars(ctx, ls->meta.p, 10, m);
+            // load-factor bound of the hashed region: probing it for an absent key ends at a free slot, so it may never fill up
+            // (a row that needed more than 2048 steps already set m[8]); past 3/4 the plain table is built instead
+            if (L.range && m[9] > (L.omask + 1) / 4 * 3) m[8] = 1;
             lap("build_fast");
             if (trace) fprintf(stderr, "[build] rows %lld slots %lld range %d overflowed %lld\n", (long long)rows, (long long)nslots, L.range, (long long)m[8]);
             if (L.range && m[8] != 0) {
@@ -881,7 +887,7 @@ static void lookup_build(pg_lookup* ls) {
 }
 
 static int64_t lookup_device_bytes(const pg_lookup* ls) {
-    int64_t b = ls->slots.bytes + ls->seg_off.bytes + ls->seg_rows.bytes + ls->probe_slot.bytes + ls->tile_sums.bytes;
+    int64_t b = ls->slots.bytes + ls->seg_off.bytes + ls->seg_rows.bytes;
     for (const ColStore& c : ls->cols) b += c.values.bytes + c.nulls.bytes + c.offsets.bytes;
     return b;
 }
@@ -1019,11 +1025,11 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
         const bool fast_table = ls->bigint_fast && (ls->layout.range || (ls->cap < (1LL << 30) && !getenv("PRESTOGPU_NO_FAST_PROBE")));
         if (fast_table && !ls->has_dups && capacity >= n && out_probe_idx && out_build_pos && !getenv("PRESTOGPU_NO_FUSED_PROBE")) {
             // unique build keys and room for one output row per probe row: resolve, and write the output as if every row emitted
-            ls->probe_slot.grow(ctx, n * 4, 0);
-            ls->tile_sums.grow(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64), 0);
-            Pair64* tiles = ls->tile_sums.as<Pair64>();
-            a.probe_slot = ls->probe_slot.as<int32_t>();
-            unsigned long long* d_total = ls->meta.as<unsigned long long>() + 10;
+            // scratch belongs to the call, not to the lookup source: several probe operators share one source (LookupJoinOperatorFactory)
+            DevBuf probe_slot(ctx, n * 4), tile_sums(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64)), total_buf(ctx, 64);
+            Pair64* tiles = tile_sums.as<Pair64>();
+            a.probe_slot = probe_slot.as<int32_t>();
+            unsigned long long* d_total = total_buf.as<unsigned long long>();
             memset_async(ctx, d_total, 0, 8);
             OutVec<int32_t> op; OutVec<int64_t> ob;
             op.begin(ctx, out_probe_idx, out_mem, n);
@@ -1044,10 +1050,9 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
             sync(ctx);
             return;
         }
-        ls->probe_slot.grow(ctx, n * 4, 0);
-        ls->tile_sums.grow(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64), 0);
-        Pair64* tiles = ls->tile_sums.as<Pair64>();
-        a.probe_slot = ls->probe_slot.as<int32_t>();
+        DevBuf probe_slot(ctx, n * 4), tile_sums(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+        Pair64* tiles = tile_sums.as<Pair64>();
+        a.probe_slot = probe_slot.as<int32_t>();
         const bool fast = fast_table;
         if (fast)
             PG_LAUNCH(ctx, j_probe_count_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, (const int64_t*)probe.c[0].values, probe.c[0].nulls, tiles);
@@ -1142,9 +1147,9 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
             ProbeArgs a;
             a.slots = ls->slots.as<JSlot>(); a.cap = ls->cap; a.seg_off = ls->seg_off.as<int32_t>(); a.seg_rows = ls->seg_rows.as<int32_t>();
             a.n = n; a.join_type = join_type; a.build_empty = ls->rows == 0 ? 1 : 0; a.L = ls->layout;
-            ls->tile_sums.grow(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64), 0);
+            DevBuf tile_sums(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64)), total_buf(ctx, 64);
             a.probe_slot = nullptr;
-            unsigned long long* d_total = ls->meta.as<unsigned long long>() + 10;
+            unsigned long long* d_total = total_buf.as<unsigned long long>();
             memset_async(ctx, d_total, 0, 8);
             GatherTab gt;
             memset(&gt, 0, sizeof(gt));
@@ -1154,7 +1159,7 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
                 gt.src[k] = src.values; gt.src_nulls[k] = src.nulls; gt.out[k] = out_build[k].values; gt.out_nulls[k] = out_build[k].nulls;
                 gt.width[k] = type_width(src.type);
             }
-            PG_LAUNCH(ctx, j_probe_dense_kernel<true>, (int)ntiles, SCAN_THREADS, 0, a, (const int64_t*)imp.d.values, imp.d.nulls, ls->tile_sums.as<Pair64>(),
+            PG_LAUNCH(ctx, j_probe_dense_kernel<true>, (int)ntiles, SCAN_THREADS, 0, a, (const int64_t*)imp.d.values, imp.d.nulls, tile_sums.as<Pair64>(),
                       d_total, out_probe_idx, (int64_t*)nullptr, gt);
             int64_t tot;
             read_scalars(ctx, d_total, 1, &tot);

@@ -83,6 +83,5 @@ struct pg_lookup {
     bool has_dups = false;
     int64_t dup_rows = 0;
     pg::DevBuf slots, seg_off, seg_rows;
-    // probe scratch (reused across pages)
-    pg::DevBuf probe_slot, tile_sums, meta;
+    pg::DevBuf meta;       // build-time counters (probe scratch is allocated per call: probers share the source)
 };

@@ -46,7 +46,7 @@ class PartialFinalAggregation:
     kernels so that its few small kernels are not queued behind them.  pipeline=False runs both stages in sequence on the caller's
     context (no threads)."""
 
-    FINAL_WORKERS = 2
+    FINAL_WORKERS = int(__import__('os').environ.get('PRESTOGPU_FINAL_WORKERS', '2'))
     SLOTS = 8
 
     def __init__(self, group_by_types, group_by_channels, aggregators, ctx, dist=None, expected_groups=100_000, reserve_sms=4,

@@ -75,7 +75,6 @@ def test_decimal_sum_underflow_after_overflow():   # testUnderflowAfterOverflow 
     for _ in range(3):
         s.add(-(TWO ** 126))
     assert (s.ovf.value, s.value()) == (0, -(TWO ** 125))
-    assert s.average() == -(TWO ** 125) // 6 + 0 if False else True   # exact value checked below
 
 
 def test_decimal_combine_overflow_underflow():     # testCombineOverflow / testCombineUnderflow :97-128

@@ -42,6 +42,34 @@ for trial, n in enumerate([0 if rank == 0 else 5, 1000, 300_000 + 17 * rank, 2_0
         ok = ok and same
         if not same:
             print("rank %d trial %d rep %d MISMATCH (%d vs %d rows)" % (rank, trial, rep, pa.position_count, pb.position_count), flush=True)
+# ---- a page returned by exchange N must survive exchange N+1 (same slot): lease=False hands out its own memory; with lease=True the
+# page is a view of the slot's receive buffers and a different slot must be used to keep it
+def same_page(x, y):
+    return x.position_count == y.position_count and all(
+        torch.equal(torch.as_tensor(p.values).view(torch.uint8).cpu(), torch.as_tensor(q.values).view(torch.uint8).cpu()) for p, q in zip(x.blocks, y.blocks))
+
+
+def make(seed, n):
+    r = np.random.default_rng(seed)
+    return P.Page(P.Block.long_array(r.integers(0, 10**9, n).astype(np.int64)), P.Block.long_array(r.integers(-10**9, 10**9, n).astype(np.int64)),
+                  position_count=n).to_device()
+
+
+p1, p2 = make(1000 + rank, 400_000), make(2000 + rank, 350_000 + rank)
+ex = P.HashPartitionExchange(P.DevicePartitioner(ctx), peer="auto")
+ref = P.HashPartitionExchange(P.DevicePartitioner(ctx), peer=False)
+want1, want2 = ref.exchange(p1, [0]), ref.exchange(p2, [0])
+held = ex.exchange(p1, [0])                        # default: a copy
+nxt = ex.exchange(p2, [0])
+torch.cuda.synchronize()
+hold_ok = same_page(held, want1) and same_page(nxt, want2)
+leased = ex.exchange(p1, [0], slot="a", lease=True)
+other = ex.exchange(p2, [0], slot="b", lease=True)  # another slot: `leased` stays valid
+torch.cuda.synchronize()
+hold_ok = hold_ok and same_page(leased, want1) and same_page(other, want2)
+if not hold_ok:
+    print("rank %d: a held page changed under the next exchange" % rank, flush=True)
+ok = ok and hold_ok
 t = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
 if rank == 0:

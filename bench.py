@@ -69,7 +69,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-workloads", action="store_true", help="headline only (skips the SF100 GROUP BY orderkey / join records)")
     ap.add_argument("--no-crosscheck", action="store_true", help="skip the small-scale oracle cross-checks (profiling runs)")
-    ap.add_argument("--only", default="", help="comma list of workloads to run: groupby,join (default both)")
+    ap.add_argument("--only", default="", help="comma list of workloads to run: groupby,join,grid (default all)")
     return ap.parse_args()
 
 
@@ -506,11 +506,68 @@ def wide_workloads(args, env, traffic):
             del want, gv, got, pp, local, ppage
         del od, bpage, join, ls
     ctx.set_timing(False)
+    if world == 1 and (not only or "grid" in only):
+        res["groupby_hash_grid"] = groupby_hash_grid(args, env)
     if exchange:
         res["exchange"] = {"rows_sent_per_rank": exchange.sent_rows, "bytes_sent_per_rank": exchange.bytes_sent,
                            "collective": ("fused partition + peer-memory stores over NVLink (pg_partition_scatter_peers into symmetric receive buffers)"
                                           if exchange.peer is not None else "NCCL all_to_all_single per column (%s)" % exchange.peer_why)}
     return res
+
+
+# ------------------------------------------------------------------------------------------- BenchmarkGroupByHash grid
+def groupby_hash_grid(args, env):
+    """OPT/BenchmarkGroupByHash.java:71-354 (POSITIONS = 10 M, GROUP_COUNT = 3 M, EXPECTED_SIZE = 10 000: the table grows nine times
+    inside the measurement, as in the reference) through the interface-level seam: GroupByHash.addPage and getGroupIds over a
+    device-resident page, BIGINT and VARCHAR channels, with and without a precomputed hash channel.  One rank (the grid does not shard)."""
+    P, torch, ctx = env.P, env.torch, env.ctx
+    from presto_b200.blocks import Block
+    from presto_b200.expressions import Expr, PageProcessor
+    N = P.native
+    positions, groups, expected = 10_000_000, 3_000_000, 10_000
+    g = torch.Generator(device="cuda").manual_seed(99)
+    v = torch.randint(0, groups, (positions,), device="cuda", generator=g)
+    distinct = int(torch.unique(v).numel())
+    vb = v.to(torch.int32).contiguous().view(torch.uint8)               # 4-byte little-endian strings, as createVarcharPages builds them
+    offs = torch.arange(0, 4 * positions + 1, 4, dtype=torch.int32, device="cuda")
+    out = {"what": "OPT/BenchmarkGroupByHash.java: %d positions, %d distinct keys (nextInt(%d)), expectedSize %d; one device page; best of 3 after 2 warm-up runs"
+                   % (positions, distinct, groups, expected), "configs": []}
+    for dtype, channels, hashed in (("BIGINT", 1, False), ("BIGINT", 1, True), ("BIGINT", 5, True), ("BIGINT", 10, False), ("VARCHAR", 1, True), ("VARCHAR", 5, False)):
+        if dtype == "BIGINT":
+            blocks = [Block(N.BIGINT, v, None, None, positions) for _ in range(channels)]
+            types = [N.BIGINT] * channels
+        else:
+            blocks = [Block(N.VARCHAR, vb, None, offs, positions) for _ in range(channels)]
+            types = [N.VARCHAR] * channels
+        if hashed:
+            proc = PageProcessor(None, [Expr.hash_of(*[Expr.input(c, types[c]) for c in range(channels)])], ctx=ctx)
+            blocks = blocks + [proc.process(P.Page(*blocks, position_count=positions), device=True).blocks[0]]
+        page = P.Page(*blocks, position_count=positions)
+        rec = {"data_type": dtype, "channels": channels, "hash_channel": hashed,
+               "class": "BigintGroupByHash" if (dtype == "BIGINT" and channels == 1) else "MultiChannelGroupByHash"}
+        for what in ("add_page", "get_group_ids"):
+            best = None
+            for it in range(5):
+                gb = P.GroupByHash(types, expected, has_hash_channel=hashed, ctx=ctx)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                ids = gb.add_page(page) if what == "add_page" else gb.get_group_ids(page, device_ids=True)
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1)
+                if it >= 2:
+                    best = ms if best is None else min(best, ms)
+                ok = gb.get_group_count() == distinct
+                if what == "get_group_ids":
+                    ok = ok and int(ids.ids.max().item()) == distinct - 1
+                gb.close()
+                if not ok:
+                    raise SystemExit("bench self-check failed (GroupByHash grid %s): group count" % json.dumps(rec))
+            rec[what + "_ms"] = round(best, 3)
+            rec[what + "_rows_per_s"] = positions / (best / 1e3)
+        out["configs"].append(rec)
+    return out
 
 
 # ------------------------------------------------------------------------------------------- cross-checks (small scale factor)
@@ -534,10 +591,16 @@ def crosschecks(env):
         od["orderkey"] = od["orderkey"] + off
         return li, od
 
+    def wide_decimals(quantity, keys):
+        """A decimal(38) column with non-zero high words and both signs: +-quantity x (10^20 + key), sign by row parity."""
+        q, k = quantity.cpu().tolist(), keys.cpu().tolist()
+        return P.Block.int128_array([(qi * (10**20 + ki)) * (1 if i % 2 else -1) for i, (qi, ki) in enumerate(zip(q, k))])
+
     li, od = shard(rank, "cuda")
     n = li["rows"]
     page = P.Page(Block(N.BIGINT, li["orderkey"], None, None, n), Block(N.SHORT_DECIMAL, li["quantity"], None, None, n),
-                  Block(N.DOUBLE, li["extendedprice_double"].view(torch.int64), None, None, n), position_count=n)
+                  Block(N.DOUBLE, li["extendedprice_double"].view(torch.int64), None, None, n), wide_decimals(li["quantity"], li["orderkey"]).to_device(),
+                  position_count=n)
     exchange = P.HashPartitionExchange(P.DevicePartitioner(ctx)) if world > 1 else None
     if exchange is not None:
         # peer-memory exchange against the NCCL all-to-all on the same page, twice (the second call reuses the symmetric buffers)
@@ -554,7 +617,8 @@ def crosschecks(env):
         out["peer_exchange_equals_nccl_all_to_all"] = bool(int(t.item()) == 1) if exchange.peer is not None else "peer mode unavailable: " + exchange.peer_why
         if out["peer_exchange_equals_nccl_all_to_all"] is False:
             raise SystemExit("bench cross-check failed: the peer-memory exchange and the NCCL all-to-all deliver different rows")
-    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2)]
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2),
+            P.AggregatorFactory(P.AGG_SUM, P.LONG_DECIMAL, 3)]
     plan = P.PartitionedAggregation([P.BIGINT], [0], aggs, ctx, dist, expected_groups=n_orders, exchange=exchange)
     g, res = plan.run(page, slot="xchk")
     mine = [b.values.cpu().numpy() for b in res.blocks]
@@ -582,17 +646,26 @@ def crosschecks(env):
         G = ogb.group_count()
         okeys = ogb.export(with_hash=False)[0][0].values
         want = [okeys]
-        for a, col in zip(aggs, (None, P.Block.long_array(qty, None, P.SHORT_DECIMAL), P.Block.double_array(price))):
+        wide = wide_decimals(torch.from_numpy(qty), torch.from_numpy(keys)) if world == 1 else None
+        if world > 1:       # row parity is per shard: build the column shard by shard
+            from presto_b200.blocks import Block as B_
+            parts = [wide_decimals(s[0]["quantity"], s[0]["orderkey"]) for s in shards]
+            wide = B_(N.LONG_DECIMAL, np.concatenate([np.asarray(b.values) for b in parts]), None, None, len(keys))
+        for a, col in zip(aggs, (None, P.Block.long_array(qty, None, P.SHORT_DECIMAL), P.Block.double_array(price), wide)):
             acc = O.OracleAccumulator(a.kind, a.in_type)
             acc.add_input(ids, G, col)
             want.append(np.asarray(acc.evaluate(0, G, True)[1][0].values))
-        got_cols = [np.concatenate([np.asarray(gr[0][c]) for gr in gathered]) for c in range(4)]
+        got_cols = [np.concatenate([np.asarray(gr[0][c]) for gr in gathered]) for c in range(5)]
         og, ow = np.argsort(got_cols[0], kind="stable"), np.argsort(want[0], kind="stable")
         ok = len(got_cols[0]) == G and np.array_equal(got_cols[0][og], want[0][ow]) and np.array_equal(got_cols[1][og], want[1][ow])
         u64 = lambda a: np.ascontiguousarray(a).view(np.uint64)      # noqa: E731
         ok = ok and np.array_equal(u64(got_cols[2]).reshape(-1, 2)[og], u64(want[2]).reshape(-1, 2)[ow])
         gd, wd = u64(got_cols[3]).view(np.float64)[og], u64(want[3]).view(np.float64)[ow]
         ok = ok and bool((np.abs(gd - wd) <= 1e-12 * np.abs(wd)).all())
+        wide_got, wide_want = u64(got_cols[4]).reshape(-1, 2)[og], u64(want[4]).reshape(-1, 2)[ow]
+        ok = ok and np.array_equal(wide_got, wide_want)
+        out["long_decimal_sums_with_high_words_and_negatives"] = bool(np.array_equal(wide_got, wide_want) and (wide_want[:, 1] & np.uint64(0x7fffffffffffffff)).any()
+                                                                   and (wide_want[:, 1] >> np.uint64(63)).any())
         out["groupby_orderkey_equals_oracle"] = bool(ok)
         oj = O.OracleJoin([P.BIGINT, P.DOUBLE], [0])
         for s in shards:

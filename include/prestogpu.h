@@ -123,6 +123,14 @@ PG_API int32_t pg_groupby_add_page(pg_groupby* gb, const pg_col* keys, const pg_
 /* contains(position, page, hashChannels[, rawHash]) for every row of the page (OP/GroupByHash.java:77-83) */
 PG_API int32_t pg_groupby_contains(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n,
                                    uint8_t* out, int32_t out_mem);
+/* MarkDistinctHash.markDistinctRows(page) (OP/MarkDistinctHash.java:52-69, driven by MarkDistinctOperator): adds the page like
+ * getGroupIds and sets out_marks[i] = 1 for the first row of every group this page introduced (ids[i] == nextDistinctId++). */
+PG_API int32_t pg_groupby_mark_distinct(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n, uint8_t* out_marks, int32_t out_mem);
+/* HashSemiJoinOperator (OP/HashSemiJoinOperator.java:176-221) against the ChannelSet this GroupByHash holds (SetBuilderOperator =
+ * pg_groupby_add_page of the build side; ChannelSet.java:32-130): out_values / out_nulls [n] are the appended BOOLEAN column —
+ * NULL probe key: false on an empty set, else NULL; found: true; not found: NULL when the set contains NULL, else false. */
+PG_API int32_t pg_groupby_semi_join(pg_groupby* gb, const pg_col* probe_key, const pg_col* hash_col, int64_t n, int32_t set_contains_null,
+                                    uint8_t* out_values, uint8_t* out_nulls, int32_t out_mem);
 /* appendValuesTo(groupId, pageBuilder, 0) for groupId in [first, first+n) (OP/GroupByHash.java:71);
  * out_hash (int64[n], may be NULL) receives the raw-hash channel / getRawHash(groupId) (:85). */
 PG_API int32_t pg_groupby_export_keys(pg_groupby* gb, int64_t first, int64_t n, pg_col_out* out_keys,
@@ -217,6 +225,13 @@ PG_API int32_t pg_lookup_gather(pg_lookup* ls, const int64_t* build_pos, int32_t
 PG_API int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, const pg_col* hash_col, int64_t n, int32_t join_type,
                                    const int32_t* build_channels, int32_t nchannels, int32_t* out_probe_idx, int32_t out_mem,
                                    pg_col_out* out_build, int64_t capacity, int64_t* n_out);
+/* RIGHT / FULL outer joins (f4).  OuterLookupSource (OP/OuterLookupSource.java:34-205) wraps the lookup source with a tracker of the
+ * build positions that were appended to some output row; after build and probe have finished, LookupOuterOperator
+ * (OP/LookupOuterOperator.java:140-181) emits the positions never visited, ascending, with NULL probe columns.
+ * pg_lookup_track_visited switches the tracker on (before the first probe; the one-kernel join_page form is then not used);
+ * pg_lookup_outer_positions returns the unvisited positions (feed them to pg_lookup_gather). */
+PG_API int32_t pg_lookup_track_visited(pg_lookup* ls);
+PG_API int32_t pg_lookup_outer_positions(pg_lookup* ls, int64_t* out_pos, int32_t out_mem, int64_t capacity, int64_t* n_out);
 /* value bytes pg_lookup_gather will write for a variable width build channel */
 PG_API int32_t pg_lookup_gather_var_bytes(pg_lookup* ls, const int64_t* build_pos, int32_t pos_mem, int64_t n, int32_t channel,
                                           int64_t* out_bytes);

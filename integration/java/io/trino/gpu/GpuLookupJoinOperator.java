@@ -2,8 +2,8 @@
  * LookupJoinOperator on the GPU for INNER and PROBE_OUTER joins (OP/LookupJoinOperator.java:299-378: processProbe / joinCurrentPosition /
  * outerJoinCurrentPosition, output through LookupJoinPageBuilder).  One probe page = one native call that returns the probe positions
  * and the build-side channels of every match in the reference's order (probe order; within a probe row the build rows in
- * positionLinks chain order).  LOOKUP_OUTER / FULL_OUTER need the visited-positions tracker of OP/LookupOuterOperator.java and stay
- * on the CPU operators.  Not compiled in this repository (no JDK); presto-1_b200/operators.py (LookupJoinOperator) is the mirror
+ * positionLinks chain order).  LOOKUP_OUTER / FULL_OUTER: the library has the visited-positions tracker (PrestoGpu.lookupTrackVisited /
+ * lookupOuterPositions, mirrored by operators.LookupOuterOperator in Python); the Java LookupOuterOperator around it is not written.  Not compiled in this repository (no JDK); presto-1_b200/operators.py (LookupJoinOperator) is the mirror
  * the parity tests drive.
  */
 package io.trino.gpu;

@@ -90,6 +90,36 @@ NATIVE(jint, groupbyContains)(JNIEnv* env, jclass cls, jlong gb, PAGE_PARAMS, jb
     }
     return rc;
 }
+/* MarkDistinctHash.markDistinctRows(page) */
+NATIVE(jint, groupbyMarkDistinct)(JNIEnv* env, jclass cls, jlong gb, PAGE_PARAMS, jboolean lastIsHash, jbooleanArray outMarks) {
+    pg_col cols[PGJ_MAX_COLS];
+    int ncols = 0;
+    int32_t rc = pgj_page_in(env, PAGE_ARGS, cols, &ncols);
+    if (rc == PG_OK && (!pgj_scratch_reset((size_t)positionCount) || ncols < 1)) rc = PG_E_INSUFFICIENT_RESOURCES;
+    if (rc == PG_OK) {
+        uint8_t* marks = (uint8_t*)pgj_scratch((size_t)positionCount);
+        rc = pg_groupby_mark_distinct(H(pg_groupby, gb), cols, lastIsHash ? &cols[ncols - 1] : NULL, positionCount, marks, PG_MEM_HOST);
+        if (rc == PG_OK) (*env)->SetBooleanArrayRegion(env, outMarks, 0, (jsize)positionCount, (const jboolean*)marks);
+    }
+    return rc;
+}
+/* HashSemiJoinOperator's output column for one probe page: page = probe join channel [, hash channel] */
+NATIVE(jint, groupbySemiJoin)(JNIEnv* env, jclass cls, jlong gb, PAGE_PARAMS, jboolean lastIsHash, jboolean setContainsNull, jbooleanArray outValues, jbooleanArray outNulls) {
+    pg_col cols[PGJ_MAX_COLS];
+    int ncols = 0;
+    int32_t rc = pgj_page_in(env, PAGE_ARGS, cols, &ncols);
+    if (rc == PG_OK && (!pgj_scratch_reset(2 * (size_t)positionCount + 128) || ncols < 1)) rc = PG_E_INSUFFICIENT_RESOURCES;
+    if (rc == PG_OK) {
+        uint8_t* vals = (uint8_t*)pgj_scratch((size_t)positionCount);
+        uint8_t* nulls = (uint8_t*)pgj_scratch((size_t)positionCount);
+        rc = pg_groupby_semi_join(H(pg_groupby, gb), &cols[0], lastIsHash ? &cols[ncols - 1] : NULL, positionCount, setContainsNull ? 1 : 0, vals, nulls, PG_MEM_HOST);
+        if (rc == PG_OK) {
+            (*env)->SetBooleanArrayRegion(env, outValues, 0, (jsize)positionCount, (const jboolean*)vals);
+            (*env)->SetBooleanArrayRegion(env, outNulls, 0, (jsize)positionCount, (const jboolean*)nulls);
+        }
+    }
+    return rc;
+}
 /* appendValuesTo for groupId in [first, first + n): key columns into the out* arrays, getRawHash into outHash (may be null) */
 NATIVE(jint, groupbyExportKeys)(JNIEnv* env, jclass cls, jlong gb, jlong first, jlong n, OUT_PARAMS, jlongArray outHash) {
     pgj_outs o;
@@ -235,6 +265,18 @@ NATIVE(jint, lookupProbe)(JNIEnv* env, jclass cls, jlong ls, PAGE_PARAMS, jboole
         }
     }
     pgj_set_long(env, nOut, 0, produced);
+    return rc;
+}
+/* OuterLookupSource / LookupOuterOperator: visited-positions tracker and the positions no probe emitted */
+NATIVE(jint, lookupTrackVisited)(JNIEnv* env, jclass cls, jlong ls) { return pg_lookup_track_visited(H(pg_lookup, ls)); }
+NATIVE(jint, lookupOuterPositions)(JNIEnv* env, jclass cls, jlong ls, jlongArray outPositions, jlongArray nOut) {
+    const jsize cap = (*env)->GetArrayLength(env, outPositions);
+    if (!pgj_scratch_reset((size_t)cap * 8)) return PG_E_INSUFFICIENT_RESOURCES;
+    int64_t* pos = (int64_t*)pgj_scratch((size_t)cap * 8);
+    int64_t n = 0;
+    const int32_t rc = pg_lookup_outer_positions(H(pg_lookup, ls), pos, PG_MEM_HOST, cap, &n);
+    if (rc == PG_OK) (*env)->SetLongArrayRegion(env, outPositions, 0, (jsize)n, (const jlong*)pos);
+    pgj_set_long(env, nOut, 0, n);
     return rc;
 }
 /* LookupSource.appendTo for a vector of build positions (-1 -> null) */

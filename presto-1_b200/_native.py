@@ -85,6 +85,8 @@ _PROTOS = {
     "pg_groupby_varwidth_bytes": (I32, [P, I32, PI64]),
     "pg_groupby_stats": (I32, [P, PI64, PI64, PI64, PI64]),
     "pg_groupby_set_memory_limit": (I32, [P, I64]),
+    "pg_groupby_mark_distinct": (I32, [P, PCOL, PCOL, I64, P, I32]),
+    "pg_groupby_semi_join": (I32, [P, PCOL, PCOL, I64, I32, P, P, I32]),
     "pg_agg_create": (I32, [P, I32, I32, C.POINTER(P)]),
     "pg_agg_destroy": (I32, [P]),
     "pg_agg_add_input": (I32, [P, P, I32, I64, PCOL, PCOL, I64]),
@@ -127,6 +129,8 @@ _PROTOS = {
     "pg_lookup_stats": (I32, [P, PI64, PI64, PI64, PI32]),
     "pg_lookup_probe": (I32, [P, PCOL, I32, PCOL, I64, I32, P, P, I32, I64, PI64]),
     "pg_lookup_gather": (I32, [P, P, I32, I64, PI32, I32, PCOLOUT]),
+    "pg_lookup_track_visited": (I32, [P]),
+    "pg_lookup_outer_positions": (I32, [P, P, I32, I64, PI64]),
     "pg_lookup_join_page": (I32, [P, PCOL, I32, PCOL, I64, I32, PI32, I32, P, I32, PCOLOUT, I64, PI64]),
     "pg_lookup_gather_var_bytes": (I32, [P, P, I32, I64, I32, PI64]),
 }

@@ -751,6 +751,35 @@ void groupby_process(pg_groupby* gb, const KeyCols& keys, const DCol* hash_col, 
     while (gb->groups >= max_fill_075(gb->ref_capacity) && gb->ref_capacity < (1LL << 30)) gb->ref_capacity *= 2;
 }
 
+
+// ------------------------------------------------------------------ MarkDistinct / semi join (f4)
+// MarkDistinctHash.markDistinctRows (OP/MarkDistinctHash.java:52-69): a row is marked when its group id equals nextDistinctId, i.e.
+// when it is the first row (in page order) of a group this page introduced.
+__global__ void gb_first_row_of_new_groups_kernel(const int32_t* __restrict__ ids, int64_t n, int64_t base, int32_t* first_row) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) if (ids[i] >= base) atomicMin(&first_row[ids[i] - base], (int32_t)i);
+}
+__global__ void gb_mark_distinct_kernel(const int32_t* __restrict__ ids, int64_t n, int64_t base, const int32_t* __restrict__ first_row, uint8_t* marks) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) marks[i] = (ids[i] >= base && first_row[ids[i] - base] == (int32_t)i) ? 1 : 0;
+}
+// HashSemiJoinOperator's output column (OP/HashSemiJoinOperator.java:190-218): NULL probe key -> false on an empty set, else NULL;
+// found -> true; not found -> NULL when the set holds a NULL, else false.
+__global__ void gb_semi_join_kernel(const uint8_t* __restrict__ found, const uint8_t* __restrict__ probe_nulls, int64_t n, int set_empty, int set_has_null,
+                                    uint8_t* values, uint8_t* nulls) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        uint8_t v = 0, isnull = 0;
+        if (probe_nulls && probe_nulls[i]) isnull = set_empty ? 0 : 1;
+        else if (found[i]) v = 1;
+        else if (set_has_null) isnull = 1;
+        values[i] = v; nulls[i] = isnull;
+    }
+}
+
 }  // namespace pg
 
 // ------------------------------------------------------------------ C ABI
@@ -870,6 +899,64 @@ int32_t pg_groupby_contains(pg_groupby* gb, const pg_col* keys, const pg_col* ha
             PG_LAUNCH(ctx, gb_contains_kernel<false>, grid, 256, 0, gb->slots.as<Slot>(), gb->cap, gb->cap - 1, gb->key_rows.as<uint64_t>(),
                       gb->arena.as<uint8_t>(), ik.kc, gb->layout, hc, ik.has_hash ? 1 : 0, n, o.d);
         o.finish();
+        sync(ctx);
+    });
+}
+
+/* MarkDistinctHash.markDistinctRows(page): getGroupIds + "first row of a group this page introduced" */
+int32_t pg_groupby_mark_distinct(pg_groupby* gb, const pg_col* keys, const pg_col* hash_col, int64_t n, uint8_t* out_marks, int32_t out_mem) {
+    if (!gb) return PG_E_INVALID_ARGUMENT;
+    return guard(gb->ctx, [&] {
+        PG_CHECK_ARG(n >= 0 && (out_marks != nullptr || n == 0), "bad arguments");
+        if (n == 0) return;
+        pg_ctx* ctx = gb->ctx;
+        ImportedKeys ik;
+        import_keys(gb, keys, hash_col, n, ik);
+        const int64_t base = gb->groups;
+        DevBuf ids(ctx, n * 4);
+        VarHint hint(gb, ik, n);
+        groupby_reserve(gb, n);
+        groupby_process(gb, ik.kc, ik.has_hash ? &ik.hc : nullptr, n, ids.as<int32_t>());
+        const int64_t fresh = gb->groups - base;
+        OutVec<uint8_t> o;
+        o.begin(ctx, out_marks, out_mem, n);
+        DevBuf first(ctx, (fresh > 0 ? fresh : 1) * 4);
+        memset_async(ctx, first.p, 0x7f, (fresh > 0 ? fresh : 1) * 4);
+        const int grid = grid_for(ctx, n, 256);
+        if (fresh > 0) PG_LAUNCH(ctx, gb_first_row_of_new_groups_kernel, grid, 256, 0, ids.as<int32_t>(), n, base, first.as<int32_t>());
+        PG_LAUNCH(ctx, gb_mark_distinct_kernel, grid, 256, 0, ids.as<int32_t>(), n, base, first.as<int32_t>(), o.d);
+        o.finish();
+        sync(ctx);
+    });
+}
+
+/* HashSemiJoinOperator: the BOOLEAN semi-join column for one probe page against the set this GroupByHash holds (ChannelSet).
+ * set_contains_null = ChannelSet.containsNull() (the caller asked pg_groupby_contains with a one-row NULL page when the set was built). */
+int32_t pg_groupby_semi_join(pg_groupby* gb, const pg_col* probe_key, const pg_col* hash_col, int64_t n, int32_t set_contains_null, uint8_t* out_values,
+                             uint8_t* out_nulls, int32_t out_mem) {
+    if (!gb) return PG_E_INVALID_ARGUMENT;
+    return guard(gb->ctx, [&] {
+        PG_CHECK_ARG(n >= 0 && ((out_values && out_nulls) || n == 0) && probe_key, "bad arguments");
+        PG_CHECK_ARG(gb->layout.nkeys == 1, "a semi join has one join channel (HashSemiJoinOperator.probeJoinChannel)");
+        if (n == 0) return;
+        pg_ctx* ctx = gb->ctx;
+        ImportedKeys ik;
+        import_keys(gb, probe_key, hash_col, n, ik);
+        DevBuf found(ctx, n);
+        DCol hc; memset(&hc, 0, sizeof(hc));
+        if (ik.has_hash) hc = ik.hc;
+        const int grid = grid_for(ctx, n, 256);
+        if (gb->bigint_mode)
+            PG_LAUNCH(ctx, gb_contains_kernel<true>, grid, 256, 0, gb->slots.as<Slot>(), gb->cap, gb->cap - 1, gb->key_rows.as<uint64_t>(),
+                      gb->arena.as<uint8_t>(), ik.kc, gb->layout, hc, ik.has_hash ? 1 : 0, n, found.as<uint8_t>());
+        else
+            PG_LAUNCH(ctx, gb_contains_kernel<false>, grid, 256, 0, gb->slots.as<Slot>(), gb->cap, gb->cap - 1, gb->key_rows.as<uint64_t>(),
+                      gb->arena.as<uint8_t>(), ik.kc, gb->layout, hc, ik.has_hash ? 1 : 0, n, found.as<uint8_t>());
+        OutVec<uint8_t> ov, on;
+        ov.begin(ctx, out_values, out_mem, n);
+        on.begin(ctx, out_nulls, out_mem, n);
+        PG_LAUNCH(ctx, gb_semi_join_kernel, grid, 256, 0, found.as<uint8_t>(), ik.kc.c[0].nulls, n, gb->groups == 0 ? 1 : 0, set_contains_null ? 1 : 0, ov.d, on.d);
+        ov.finish(); on.finish();
         sync(ctx);
     });
 }

@@ -742,6 +742,45 @@ void gather_device_col(pg_ctx* ctx, const DCol& src, const int64_t* d_pos, int64
                          (uint8_t*)out.nulls);
 }
 
+// ------------------------------------------------------------------ outer side (LookupOuterOperator / OuterLookupSource)
+__global__ void j_mark_visited_kernel(const int64_t* __restrict__ build_pos, int64_t n, unsigned int* visited) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const int64_t p = build_pos[i];
+        if (p >= 0) atomicOr(&visited[p >> 5], 1u << (p & 31));
+    }
+}
+__global__ void __launch_bounds__(SCAN_THREADS) j_outer_count_kernel(const unsigned int* __restrict__ visited, int64_t rows, Pair64* tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    const int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 acc{0, 0};
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        const int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (i < rows && !((visited[i >> 5] >> (i & 31)) & 1u)) acc.a += 1;
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+// positions in ascending order (SharedLookupOuterPositionIterator walks currentPosition upwards): a tile's rows are visited in
+// SCAN_ITEMS rounds of SCAN_THREADS consecutive rows, each round ranked by a block scan
+__global__ void __launch_bounds__(SCAN_THREADS) j_outer_emit_kernel(const unsigned int* __restrict__ visited, int64_t rows, const Pair64* __restrict__ tile_prefix,
+                                                                    int64_t* out_pos, int64_t capacity) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    const int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 run = tile_prefix[blockIdx.x];
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        const int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        Pair64 v{0, 0};
+        if (i < rows && !((visited[i >> 5] >> (i & 31)) & 1u)) v.a = 1;
+        Pair64 total;
+        const Pair64 ex = block_exclusive_scan(v, smem, &total);
+        if (v.a && run.a + ex.a < capacity) out_pos[run.a + ex.a] = i;
+        run = run + total;
+    }
+}
+
 // ------------------------------------------------------------------ host side
 static JoinCols build_join_cols(const std::vector<ColStore>& cols, const std::vector<int32_t>& jch) {
     JoinCols jc;
@@ -1046,6 +1085,7 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
                 scan_tile_totals(ctx, tiles, ntiles, tiles + ntiles);
                 PG_LAUNCH(ctx, j_probe_emit_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
             }
+            if (ls->track_visited) PG_LAUNCH(ctx, j_mark_visited_kernel, grid_for(ctx, tot, 256), 256, 0, ob.d, tot, ls->visited.as<unsigned int>());
             op.finish(tot); ob.finish(tot);
             sync(ctx);
             return;
@@ -1070,6 +1110,7 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
         ob.begin(ctx, out_build_pos, out_mem, tot[0]);
         if (fast) PG_LAUNCH(ctx, j_probe_emit_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
         else PG_LAUNCH(ctx, j_probe_emit_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
+        if (ls->track_visited) PG_LAUNCH(ctx, j_mark_visited_kernel, grid_for(ctx, tot[0], 256), 256, 0, ob.d, tot[0], ls->visited.as<unsigned int>());
         op.finish(); ob.finish();
         sync(ctx);
     });
@@ -1132,7 +1173,8 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
         if (n == 0) return;
         PG_CHECK_ARG(n <= MAX_CHUNK_ROWS, "probe page too large");
         bool fused = ls->bigint_fast && !ls->has_dups && capacity >= n && out_probe_idx && out_mem == PG_MEM_DEVICE && nchannels <= JG_MAX_COLS &&
-                     (ls->layout.range || ls->cap < (1LL << 30)) && probe_keys[0].type == PG_BIGINT && !getenv("PRESTOGPU_NO_FUSED_PROBE");
+                     (ls->layout.range || ls->cap < (1LL << 30)) && probe_keys[0].type == PG_BIGINT && !getenv("PRESTOGPU_NO_FUSED_PROBE") &&
+                     !ls->track_visited;      // (the visited tracker works on the materialised build positions)
         for (int k = 0; k < nchannels; k++) {
             const int ch = build_channels[k];
             PG_CHECK_ARG(ch >= 0 && ch < (int)ls->cols.size(), "build channel %d out of range", ch);
@@ -1176,6 +1218,46 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
             rc = pg_lookup_gather(ls, tb.as<int64_t>(), PG_MEM_DEVICE, *n_out, build_channels, nchannels, out_build);
             if (rc != PG_OK) { const std::string msg = ctx->err; fail(rc, "%s", msg.c_str()); }
         }
+        sync(ctx);
+    });
+}
+
+/* OuterLookupSource: start tracking which build positions a probe emits (RIGHT / FULL joins; OP/OuterLookupSource.java:176-205).
+ * Call before the first probe. */
+int32_t pg_lookup_track_visited(pg_lookup* ls) {
+    if (!ls) return PG_E_INVALID_ARGUMENT;
+    return guard(ls->ctx, [&] {
+        if (ls->track_visited) return;
+        const int64_t words = (ls->rows + 31) / 32 + 1;
+        ls->visited.alloc(ls->ctx, words * 4);
+        memset_async(ls->ctx, ls->visited.p, 0, words * 4);
+        ls->track_visited = true;
+    });
+}
+
+/* OuterPositionIterator (OP/OuterLookupSource.java:118-160): the build positions no probe has emitted, ascending.  *n_out = how many
+ * there are; at most `capacity` are written (PG_NEED_MEMORY when more exist: call again with room for *n_out). */
+int32_t pg_lookup_outer_positions(pg_lookup* ls, int64_t* out_pos, int32_t out_mem, int64_t capacity, int64_t* n_out) {
+    if (!ls || !n_out) return PG_E_INVALID_ARGUMENT;
+    return guard(ls->ctx, [&] {
+        pg_ctx* ctx = ls->ctx;
+        PG_CHECK_STATE(ls->track_visited, "pg_lookup_track_visited was not called on this lookup source");
+        PG_CHECK_ARG(capacity >= 0 && (capacity == 0 || out_pos), "bad arguments");
+        *n_out = 0;
+        if (ls->rows == 0) return;
+        const int64_t ntiles = num_tiles(ls->rows);
+        DevBuf tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+        PG_LAUNCH(ctx, j_outer_count_kernel, (int)ntiles, SCAN_THREADS, 0, ls->visited.as<unsigned int>(), ls->rows, tiles.as<Pair64>());
+        scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, tiles.as<Pair64>() + ntiles);
+        int64_t tot[2];
+        read_scalars(ctx, tiles.as<Pair64>() + ntiles, 2, tot);
+        *n_out = tot[0];
+        if (tot[0] > capacity) fail(PG_NEED_MEMORY, "%lld outer positions, the buffer holds %lld", (long long)tot[0], (long long)capacity);
+        if (tot[0] == 0) return;
+        OutVec<int64_t> o;
+        o.begin(ctx, out_pos, out_mem, tot[0]);
+        PG_LAUNCH(ctx, j_outer_emit_kernel, (int)ntiles, SCAN_THREADS, 0, ls->visited.as<unsigned int>(), ls->rows, tiles.as<Pair64>(), o.d, capacity);
+        o.finish();
         sync(ctx);
     });
 }

@@ -84,4 +84,8 @@ struct pg_lookup {
     int64_t dup_rows = 0;
     pg::DevBuf slots, seg_off, seg_rows;
     pg::DevBuf meta;       // build-time counters (probe scratch is allocated per call: probers share the source)
+    // OuterLookupSource's visited-positions tracker (OP/OuterLookupSource.java:176-205) as a device bitmap over the build rows,
+    // switched on with pg_lookup_track_visited for RIGHT / FULL joins; every emitted build position sets its bit
+    pg::DevBuf visited;
+    bool track_visited = false;
 };

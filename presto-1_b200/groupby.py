@@ -116,6 +116,25 @@ class GroupByHash:
                                                                   N.MEM_DEVICE if on_device else N.MEM_HOST, C.byref(gc)))
         return GroupByIdBlock(gc.value, ids)
 
+    def mark_distinct(self, page):
+        """MarkDistinctHash.markDistinctRows(page) (OP/MarkDistinctHash.java:52-69): numpy bool per row, True for the first row of every
+        group this page introduced."""
+        keys, hb = self._split(page)
+        n = keys[0].n
+        hc = hb.pg_col() if hb is not None else None
+        out = np.zeros(n, dtype=np.uint8)
+        N.check(self.ctx.handle, N.lib().pg_groupby_mark_distinct(self._h, col_array(keys), C.byref(hc) if hc else None, n, out.ctypes.data, N.MEM_HOST))
+        return out.astype(bool)
+
+    def semi_join(self, probe_block, hash_block=None, set_contains_null=False):
+        """The BOOLEAN column HashSemiJoinOperator appends (OP/HashSemiJoinOperator.java:190-218): (values, nulls) numpy arrays."""
+        n = probe_block.n
+        hc = hash_block.pg_col() if hash_block is not None else None
+        vals, nulls = np.zeros(n, dtype=np.uint8), np.zeros(n, dtype=np.uint8)
+        N.check(self.ctx.handle, N.lib().pg_groupby_semi_join(self._h, col_array([probe_block]), C.byref(hc) if hc else None, n, int(bool(set_contains_null)),
+                                                              vals.ctypes.data, nulls.ctypes.data, N.MEM_HOST))
+        return vals, nulls
+
     def contains(self, page):
         """contains(position, page, hashChannels) for every position; returns a numpy bool array."""
         keys, hb = self._split(page)

@@ -139,6 +139,18 @@ class LookupSource:
             N.check(self.ctx.handle, rc)
             return op[:n_out.value], [o.block(n_out.value) for o in outs]
 
+    def track_visited(self):
+        """OuterLookupSource: remember which build positions get emitted (RIGHT / FULL joins); call before the first probe."""
+        N.check(self.ctx.handle, N.lib().pg_lookup_track_visited(self._h))
+
+    def outer_positions(self):
+        """OuterPositionIterator: build positions no probe has emitted, ascending (numpy int64)."""
+        cap = max(1, self._stats()[0])
+        out = np.empty(cap, dtype=np.int64)
+        n_out = C.c_int64()
+        N.check(self.ctx.handle, N.lib().pg_lookup_outer_positions(self._h, out.ctypes.data, N.MEM_HOST, cap, C.byref(n_out)))
+        return out[:n_out.value]
+
     def append_to(self, build_positions, channels, device=None):
         """appendTo for a vector of build positions: gathers the given build channels (position -1 -> null)."""
         on_device = type(build_positions).__module__.startswith("torch") if device is None else device

@@ -305,3 +305,138 @@ def take_positions(block, positions):
     else:
         v = block.values[idx]
     return Block(block.type, np.ascontiguousarray(v), None if block.nulls is None else np.ascontiguousarray(block.nulls[idx]), None, n)
+
+
+# ------------------------------------------------------------------------------------------------ f4: MarkDistinct, SetBuilder, HashSemiJoin
+class MarkDistinctOperator:
+    """OP/MarkDistinctOperator.java:109-140: appends a BOOLEAN channel that is true for the first row of every distinct combination
+    of the mark channels (MarkDistinctHash over a GroupByHash)."""
+
+    def __init__(self, mark_types, mark_channels, hash_channel=None, expected_size=10_000, ctx=None):
+        from .groupby import GroupByHash
+        self.channels, self.hash_channel = list(mark_channels), hash_channel
+        self.hash = GroupByHash(list(mark_types), expected_size, has_hash_channel=hash_channel is not None, ctx=ctx)
+        self._finishing, self._out = False, None
+
+    def needs_input(self):
+        return not self._finishing and self._out is None
+
+    def add_input(self, page):
+        assert self.needs_input()
+        blocks = page.blocks if isinstance(page, Page) else list(page)
+        keys = [blocks[c] for c in self.channels] + ([blocks[self.hash_channel]] if self.hash_channel is not None else [])
+        marks = self.hash.mark_distinct(keys)
+        from .blocks import Block
+        self._out = Page(*(list(blocks) + [Block(N.BOOLEAN, marks.astype(np.uint8), None, None, len(marks))]), position_count=len(marks))
+
+    def get_output(self):
+        out, self._out = self._out, None
+        return out
+
+    def finish(self):
+        self._finishing = True
+
+    def is_finished(self):
+        return self._finishing and self._out is None
+
+
+class SetBuilderOperator:
+    """OP/SetBuilderOperator.java:123-170: collects the build side's join channel into a ChannelSet (a GroupByHash plus 'contains NULL')."""
+
+    def __init__(self, type_, set_channel, hash_channel=None, expected_positions=10_000, ctx=None):
+        from .groupby import GroupByHash
+        self.type, self.channel, self.hash_channel = type_, set_channel, hash_channel
+        self.hash = GroupByHash([type_], expected_positions, has_hash_channel=hash_channel is not None, ctx=ctx)
+        self._finishing = False
+        self.contains_null = False
+
+    def needs_input(self):
+        return not self._finishing
+
+    def add_input(self, page):
+        assert self.needs_input()
+        blocks = page.blocks if isinstance(page, Page) else list(page)
+        keys = [blocks[self.channel]] + ([blocks[self.hash_channel]] if self.hash_channel is not None else [])
+        self.hash.add_page(keys)
+
+    def finish(self):
+        """ChannelSetBuilder.build(): containsNull = hash.contains(0, nullBlockPage) (ChannelSet.java:101-109)."""
+        if self._finishing:
+            return
+        self._finishing = True
+        from .blocks import Block
+        if self.type in (N.VARCHAR, N.VARBINARY):
+            null_row = Block(self.type, np.zeros(1, dtype=np.uint8), np.ones(1, dtype=np.uint8), np.zeros(2, dtype=np.int32), 1)
+        else:
+            from .blocks import _NP_DTYPE
+            k = 2 if self.type == N.LONG_DECIMAL else 1
+            null_row = Block(self.type, np.zeros(k, dtype=np.uint64 if self.type == N.LONG_DECIMAL else _NP_DTYPE[self.type]), np.ones(1, dtype=np.uint8), None, 1)
+        self.contains_null = bool(self.hash.contains([null_row])[0])
+
+    def is_finished(self):
+        return self._finishing
+
+    def size(self):
+        return self.hash.get_group_count()
+
+
+class HashSemiJoinOperator:
+    """OP/HashSemiJoinOperator.java:176-221: appends the BOOLEAN 'probe key IN (set)' channel with SQL three-valued logic."""
+
+    def __init__(self, set_builder, probe_join_channel, probe_hash_channel=None):
+        self.set, self.channel, self.hash_channel = set_builder, probe_join_channel, probe_hash_channel
+        self._finishing, self._out = False, None
+
+    def needs_input(self):
+        return self.set.is_finished() and not self._finishing and self._out is None
+
+    def add_input(self, page):
+        assert self.needs_input()
+        blocks = page.blocks if isinstance(page, Page) else list(page)
+        hb = blocks[self.hash_channel] if self.hash_channel is not None else None
+        vals, nulls = self.set.hash.semi_join(blocks[self.channel], hb, self.set.contains_null)
+        from .blocks import Block
+        self._out = Page(*(list(blocks) + [Block(N.BOOLEAN, vals, nulls if nulls.any() else None, None, len(vals))]), position_count=len(vals))
+
+    def get_output(self):
+        out, self._out = self._out, None
+        return out
+
+    def finish(self):
+        self._finishing = True
+
+    def is_finished(self):
+        return self._finishing and self._out is None
+
+
+class LookupOuterOperator:
+    """OP/LookupOuterOperator.java:140-181: after build and probe have finished, one row per build position that no probe emitted —
+    NULL in the probe output channels, the build output channels from the lookup source.  The lookup source must have been
+    switched to tracking (LookupSource.track_visited) before the first probe, as JoinBridgeManager wraps it in OuterLookupSource
+    for RIGHT / FULL joins."""
+
+    def __init__(self, lookup_source, probe_output_types, build_output_channels, page_rows=8192):
+        self.lookup, self.probe_types, self.build_channels, self.page_rows = lookup_source, list(probe_output_types), list(build_output_channels), page_rows
+        self._positions, self._at = None, 0
+
+    def needs_input(self):
+        return False
+
+    def get_output(self):
+        if self._positions is None:
+            self._positions = self.lookup.outer_positions()
+        if self._at >= len(self._positions):
+            return None
+        pos = self._positions[self._at:self._at + self.page_rows]
+        self._at += len(pos)
+        n = len(pos)
+        nulls = []
+        for t in self.probe_types:
+            o = OutBlock(t, n, 1)
+            b = o.block(n)
+            nulls.append(Block(t, b.values, np.ones(n, dtype=np.uint8), b.offsets, n))
+        build = self.lookup.append_to(pos, self.build_channels, device=False)
+        return Page(*(nulls + build), position_count=n)
+
+    def is_finished(self):
+        return self._positions is not None and self._at >= len(self._positions)

@@ -174,9 +174,12 @@ def slice_host_block(P, b, lo, hi):
     """Rows [lo, hi) of a host block as a view (no copy)."""
     from presto_b200.blocks import Block
     if b.type in (P.VARCHAR, P.VARBINARY):
-        return Block(b.type, b.values, None if b.nulls is None else b.nulls[lo:hi], b.offsets[lo:hi + 1], hi - lo)
-    k = 2 if b.type == P.LONG_DECIMAL else 1
-    return Block(b.type, b.values[k * lo:k * hi], None if b.nulls is None else b.nulls[lo:hi], None, hi - lo, b.precision, b.scale)
+        out = Block(b.type, b.values, None if b.nulls is None else b.nulls[lo:hi], b.offsets[lo:hi + 1], hi - lo)
+    else:
+        k = 2 if b.type == P.LONG_DECIMAL else 1
+        out = Block(b.type, b.values[k * lo:k * hi], None if b.nulls is None else b.nulls[lo:hi], None, hi - lo, b.precision, b.scale)
+    out.pinned = getattr(b, "pinned", False)
+    return out
 
 
 class PagedDrivers:
@@ -185,7 +188,7 @@ class PagedDrivers:
     runs in C (pg_hashagg_add_pages: each page goes through pg_hashagg_add_page's path) so that Python's per-call cost is not what
     is measured; the pinned page accumulator batches the pages (pg_hashagg_set_page_batching)."""
 
-    def __init__(self, P, tpch, torch, device, hpage, nthreads, page_rows, batch_rows):
+    def __init__(self, P, tpch, torch, device, hpage, nthreads, page_rows, batch_rows, zero_copy=True):
         from presto_b200.context import GpuContext
         from presto_b200.plans import final_aggregators
         self.P, self.torch, self.page_rows, self.batch_rows, self.T = P, torch, page_rows, batch_rows, nthreads
@@ -197,6 +200,9 @@ class PagedDrivers:
         for t in range(nthreads):
             lo, hi = n * t // nthreads, n * (t + 1) // nthreads
             self.slices.append(P.Page(*[slice_host_block(P, b, lo, hi) for b in hpage.blocks], position_count=hi - lo))
+            if not zero_copy:       # plain host pages (what a JNI caller has): every page is copied into the pinned accumulator first
+                for b in self.slices[-1].blocks:
+                    b.pinned = False
             st = torch.cuda.Stream()
             with torch.cuda.stream(st):
                 ctx = GpuContext(device)
@@ -805,28 +811,34 @@ def gpu_arm(args):
         # the same end-to-end pass with the input arriving as reference-sized pages on several driver threads
         if not args.no_e2e_pages:
             nthreads = max(1, min(args.page_drivers, (os.cpu_count() or 8) // max(world, 1)))
-            drivers = PagedDrivers(P, tpch, torch, local_rank, hpage, nthreads, args.page_rows, args.page_batch_rows)
-            for _ in range(2):
-                pout = drivers.step()
-            env.barrier()
-            l0 = drivers.launch_count()
-            t0 = time.perf_counter()
-            for _ in range(e_steps):
-                pout = drivers.step()
-            torch.cuda.synchronize()
-            pms = env.max_over_ranks((time.perf_counter() - t0) * 1e3) / e_steps
-            pcheck = q1_selfcheck(torch, cols, pout, None) if world == 1 else {"sums_bit_exact_vs_torch_int64": None}
-            if world == 1 and not pcheck["sums_bit_exact_vs_torch_int64"]:
-                raise SystemExit("bench self-check failed (e2e_pages): %s" % json.dumps(pcheck))
-            e2e_pages = {"value": total_rows / (pms / 1e3), "unit": "rows/s", "ms_per_step": round(pms, 3), "steps": e_steps, "warmup": 2,
-                         "page_rows": args.page_rows, "pages_per_step": int(math.ceil(rows / args.page_rows)), "driver_threads": nthreads,
-                         "batch_rows": args.page_batch_rows, "h2d_bytes_per_step": int(input_bytes),
-                         "gpu_launches_per_step": (drivers.launch_count() - l0) // e_steps,
-                         "ratio_to_e2e": round((total_rows / (pms / 1e3)) / e2e["value"], 4),
-                         "how": "host pages of page_rows rows, one addInput (pg_hashagg_add_page path, looped in C) per page on each of driver_threads "
-                                "PARTIAL operators; pinned page accumulator; one FINAL merge; wall clock, max over ranks",
-                         "selfcheck": pcheck}
-            del drivers
+
+            def paged(zero_copy):
+                drivers = PagedDrivers(P, tpch, torch, local_rank, hpage, nthreads, args.page_rows, args.page_batch_rows, zero_copy=zero_copy)
+                for _ in range(2):
+                    pout = drivers.step()
+                env.barrier()
+                l0 = drivers.launch_count()
+                t0 = time.perf_counter()
+                for _ in range(e_steps):
+                    pout = drivers.step()
+                torch.cuda.synchronize()
+                pms = env.max_over_ranks((time.perf_counter() - t0) * 1e3) / e_steps
+                pcheck = q1_selfcheck(torch, cols, pout, None) if world == 1 else {"sums_bit_exact_vs_torch_int64": None}
+                if world == 1 and not pcheck["sums_bit_exact_vs_torch_int64"]:
+                    raise SystemExit("bench self-check failed (e2e_pages): %s" % json.dumps(pcheck))
+                return {"value": total_rows / (pms / 1e3), "unit": "rows/s", "ms_per_step": round(pms, 3),
+                        "gpu_launches_per_step": (drivers.launch_count() - l0) // e_steps,
+                        "ratio_to_e2e": round((total_rows / (pms / 1e3)) / e2e["value"], 4), "selfcheck": pcheck}
+
+            zc, cp = paged(True), paged(False)
+            e2e_pages = dict(zc)
+            e2e_pages.update({"steps": e_steps, "warmup": 2, "page_rows": args.page_rows, "pages_per_step": int(math.ceil(rows / args.page_rows)),
+                              "driver_threads": nthreads, "batch_rows": args.page_batch_rows, "h2d_bytes_per_step": int(input_bytes),
+                              "pages_in": "caller-pinned host memory (PG_MEM_HOST_PINNED): the accumulator copies each page straight to the device",
+                              "plain_host_pages": dict(cp, pages_in="plain host memory (PG_MEM_HOST, what a JNI caller hands over): each page is first "
+                                                                    "copied into the pinned accumulator"),
+                              "how": "host pages of page_rows rows, one addInput (pg_hashagg_add_page path, looped in C) per page on each of driver_threads "
+                                     "PARTIAL operators; page accumulator; one FINAL merge; wall clock, max over ranks"})
         del hpage
     plan.close()
 

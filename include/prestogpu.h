@@ -55,11 +55,16 @@ enum {
     PG_BOOLEAN = 9        /* ByteArrayBlock, 1 byte                                  */
 };
 
-enum { PG_MEM_HOST = 0, PG_MEM_DEVICE = 1 };
+enum { PG_MEM_HOST = 0, PG_MEM_DEVICE = 1,
+       /* host memory that is page-locked (cudaHostAlloc / cudaHostRegister) AND that the caller keeps valid and unmodified until the
+        * operator has consumed it: accepted wherever PG_MEM_HOST is; the page accumulator of pg_hashagg_add_page then copies such pages
+        * to the device straight from the caller's memory (no intermediate host copy), and they count as consumed after the next call
+        * that reads the operator's state (stats, get_output*, ...), or as soon as pg_ctx_synchronize returns */
+       PG_MEM_HOST_PINNED = 2 };
 
 typedef struct pg_col {
     int32_t type;           /* PG_BIGINT ...                                         */
-    int32_t mem;            /* PG_MEM_HOST | PG_MEM_DEVICE                           */
+    int32_t mem;            /* PG_MEM_HOST | PG_MEM_DEVICE | PG_MEM_HOST_PINNED      */
     int64_t n;              /* positionCount                                         */
     const void* values;     /* element array (bytes for VARCHAR/VARBINARY)           */
     const uint8_t* nulls;   /* 1 byte per row, non-zero == null; NULL == no nulls    */

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "libprestogpu.so")
 PG_OK, PG_NEED_MEMORY, PG_E_INSUFFICIENT_RESOURCES, PG_E_NUMERIC_OVERFLOW = 0, 1, 2, 3
 PG_E_INVALID_ARGUMENT, PG_E_CUDA, PG_E_NCCL, PG_E_INTERNAL, PG_E_ILLEGAL_STATE = 4, 5, 6, 7, 8
 BIGINT, INTEGER, DATE, DOUBLE, SHORT_DECIMAL, LONG_DECIMAL, VARCHAR, VARBINARY, BOOLEAN = range(1, 10)
-MEM_HOST, MEM_DEVICE = 0, 1
+MEM_HOST, MEM_DEVICE, MEM_HOST_PINNED = 0, 1, 2
 AGG_COUNT, AGG_COUNT_COL, AGG_SUM, AGG_AVG, AGG_MIN, AGG_MAX = range(1, 7)
 JOIN_INNER, JOIN_PROBE_OUTER = 0, 1
 NOALLOC_MAX_ROWS = 4194304      # PG_NOALLOC_MAX_ROWS

@@ -44,6 +44,7 @@ class Block:
         self.precision = precision
         self.scale = scale
         self.device = bool(_is_torch(values) and values.is_cuda)
+        self.pinned = False      # host block in page-locked memory that the caller keeps alive until the operator consumed it (PG_MEM_HOST_PINNED)
         if n is None:
             if type_ in (N.VARCHAR, N.VARBINARY):
                 n = len(offsets) - 1
@@ -132,7 +133,7 @@ class Block:
     def pg_col(self):
         c = N.PgCol()
         c.type = self.type
-        c.mem = N.MEM_DEVICE if self.device else N.MEM_HOST
+        c.mem = N.MEM_DEVICE if self.device else (N.MEM_HOST_PINNED if self.pinned else N.MEM_HOST)
         c.n = self.n
         c.values = _ptr(self.values)
         c.nulls = _ptr(self.nulls)

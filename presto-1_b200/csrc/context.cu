@@ -38,7 +38,7 @@ void import_col(pg_ctx* ctx, const pg_col& c, int64_t n, ColImport& out) {
     }
     out.value_bytes = col_value_bytes(ctx, c, n);
     out.host_offsets = type_is_var(c.type) ? c.offsets : nullptr;
-    PG_CHECK_ARG(c.mem == PG_MEM_HOST, "bad mem kind %d", c.mem);
+    PG_CHECK_ARG(c.mem == PG_MEM_HOST || c.mem == PG_MEM_HOST_PINNED, "bad mem kind %d", c.mem);
     // small arrays go through the pinned arena (asynchronous), large ones straight from the caller's memory
     auto stage = [&](DevBuf& own, const void* host, int64_t bytes) -> void* {
         if (void* p = in_arena_stage(ctx, host, bytes)) return p;
@@ -182,9 +182,9 @@ int32_t pg_ctx_create(int32_t device, pg_ctx** out) {
 int32_t pg_ctx_destroy(pg_ctx* ctx) {
     if (!ctx) return PG_OK;
     cudaSetDevice(ctx->device);
+    pg::page_batch_pool_free(ctx);
     pg::big_cache_clear(ctx);
     cudaStreamSynchronize(ctx->stream);
-    pg::page_batch_pool_free(ctx);
     if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
     if (ctx->out_dev) cudaFree(ctx->out_dev);
     if (ctx->out_pinned) cudaFreeHost(ctx->out_pinned);

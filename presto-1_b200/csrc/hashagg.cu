@@ -37,6 +37,22 @@ struct pg_hashagg {
     ~pg_hashagg();
 };
 
+// A piece of a caller-pinned page and where it goes in the device-side accumulator.  The pieces of a whole batch are copied by ONE
+// kernel that reads the host memory directly (page-locked memory is mapped into the device's address space): one cudaMemcpyAsync per
+// page and column made 16 driver threads queue up on the driver's lock (51 000 calls per SF10 pass: 254 ms against 51 ms for one bulk copy).
+struct GatherDesc { const char* src; char* dst; int64_t bytes; };
+static __global__ void __launch_bounds__(256) batch_gather_kernel(const GatherDesc* __restrict__ descs, int ndesc) {
+    for (int d = blockIdx.y; d < ndesc; d += gridDim.y) {
+        const GatherDesc g = descs[d];
+        const uintptr_t mis = (uintptr_t)g.src | (uintptr_t)g.dst | (uintptr_t)g.bytes;
+        const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+        if ((mis & 15) == 0) { for (int64_t i = t; i < g.bytes / 16; i += stride) ((uint4*)g.dst)[i] = ((const uint4*)g.src)[i]; }
+        else if ((mis & 7) == 0) { for (int64_t i = t; i < g.bytes / 8; i += stride) ((unsigned long long*)g.dst)[i] = ((const unsigned long long*)g.src)[i]; }
+        else if ((mis & 3) == 0) { for (int64_t i = t; i < g.bytes / 4; i += stride) ((unsigned int*)g.dst)[i] = ((const unsigned int*)g.src)[i]; }
+        else { for (int64_t i = t; i < g.bytes; i += stride) g.dst[i] = g.src[i]; }
+    }
+}
+
 // One pinned host copy of the channels the operator reads, `cap_rows` rows deep.  Kept by the context between operators
 // (pg_ctx::page_batch_pool): pinning tens of megabytes costs milliseconds.
 struct PageBatch {
@@ -46,8 +62,11 @@ struct PageBatch {
         char* values = nullptr; int64_t values_cap = 0, values_used = 0;
         uint8_t* nulls = nullptr;
         int32_t* offsets = nullptr;
+        pg::DevBuf dvalues, dnulls, doffsets;      // device mode (pages in caller-pinned memory are copied straight to the device)
     };
     int64_t cap_rows = 0, rows = 0;
+    bool device_mode = false;                      // what the rows accumulated so far are: copies in pinned host memory, or device copies
+    std::vector<GatherDesc> descs;                 // device mode: the copies the next flush has to make
     std::vector<Col> cols;
     static void* pinned(int64_t bytes) {
         void* p = nullptr;
@@ -56,13 +75,13 @@ struct PageBatch {
     }
     void release() {
         for (Col& c : cols) { if (c.values) cudaFreeHost(c.values); if (c.nulls) cudaFreeHost(c.nulls); if (c.offsets) cudaFreeHost(c.offsets); }
-        cols.clear(); cap_rows = 0; rows = 0;
+        cols.clear(); descs.clear(); cap_rows = 0; rows = 0; device_mode = false;
     }
     ~PageBatch() { release(); }
 };
 
 pg_hashagg::~pg_hashagg() {
-    if (batch) { batch->rows = 0; ctx->page_batch_pool.push_back(batch); batch = nullptr; }
+    if (batch) { batch->rows = 0; batch->descs.clear(); ctx->page_batch_pool.push_back(batch); batch = nullptr; }
     {
         delete wide;
         for (pg_agg* a : aggs) delete a;
@@ -572,7 +591,12 @@ static bool channel_is_read(const pg_hashagg* op, int c) {
 // true when the page was taken into the accumulator
 static bool batch_append(pg_hashagg* op, const pg_col* cols, int32_t ncols, int64_t n) {
     if (op->batch_rows <= 0 || n <= 0 || n * 4 > op->batch_rows) return false;
-    for (int c = 0; c < ncols; c++) if (channel_is_read(op, c) && cols[c].mem != PG_MEM_HOST) return false;
+    bool pinned = true;        // every channel the operator reads lives in caller-pinned memory: device mode
+    for (int c = 0; c < ncols; c++) {
+        if (!channel_is_read(op, c)) continue;
+        if (cols[c].mem != PG_MEM_HOST && cols[c].mem != PG_MEM_HOST_PINNED) return false;
+        if (cols[c].mem != PG_MEM_HOST_PINNED) pinned = false;
+    }
     PageBatch* b = op->batch;
     if (!b) {
         pg_ctx* ctx = op->ctx;
@@ -606,6 +630,45 @@ static bool batch_append(pg_hashagg* op, const pg_col* cols, int32_t ncols, int6
         }
     }
     if (b->rows + n > b->cap_rows) return false;           // the caller flushes and tries again
+    if (b->rows > 0 && b->device_mode != pinned) return false;      // one kind of copy per batch
+    b->device_mode = pinned;
+    if (pinned) {
+        pg_ctx* ctx = op->ctx;
+        for (int c = 0; c < ncols; c++) {                // room first: a page that does not fit must leave the batch untouched
+            PageBatch::Col& bc = b->cols[c];
+            if (!bc.used || !type_is_var(bc.type)) continue;
+            PG_CHECK_ARG(cols[c].offsets != nullptr, "variable width channel %d without offsets", c);
+            const int64_t bytes = (int64_t)cols[c].offsets[n] - cols[c].offsets[0];
+            if (bc.values_used + bytes > bc.values_cap) return false;
+        }
+        for (int c = 0; c < ncols; c++) {
+            PageBatch::Col& bc = b->cols[c];
+            if (!bc.used) continue;
+            const pg_col& in = cols[c];
+            PG_CHECK_ARG(in.type == bc.type && in.n == n, "channel %d: type %d / %lld rows, the accumulated pages have type %d / this page %lld rows", c, in.type,
+                         (long long)in.n, bc.type, (long long)n);
+            if (!bc.dnulls.p) {
+                bc.dvalues.alloc(ctx, bc.values_cap);
+                bc.dnulls.alloc(ctx, b->cap_rows);
+                if (type_is_var(bc.type)) bc.doffsets.alloc(ctx, (b->cap_rows + 1) * 4);
+            }
+            if (type_is_var(bc.type)) {
+                const int64_t first = in.offsets[0], bytes = (int64_t)in.offsets[n] - first;
+                if (bytes > 0) b->descs.push_back(GatherDesc{(const char*)in.values + first, (char*)bc.dvalues.p + bc.values_used, bytes});
+                for (int64_t i = 0; i <= n; i++) bc.offsets[b->rows + i] = (int32_t)(bc.values_used + (in.offsets[i] - first));     // leave with the flush
+                bc.values_used += bytes;
+            } else {
+                const int w = type_width(bc.type);
+                b->descs.push_back(GatherDesc{(const char*)in.values, (char*)bc.dvalues.p + b->rows * w, n * w});
+            }
+            if (in.nulls) {
+                if (!bc.has_nulls) { memset_async(ctx, bc.dnulls.p, 0, b->rows); bc.has_nulls = true; }
+                b->descs.push_back(GatherDesc{(const char*)in.nulls, (char*)bc.dnulls.p + b->rows, n});
+            } else if (bc.has_nulls) memset_async(ctx, (char*)bc.dnulls.p + b->rows, 0, n);
+        }
+        b->rows += n;
+        return true;
+    }
     for (int c = 0; c < ncols; c++) {
         PageBatch::Col& bc = b->cols[c];
         if (!bc.used) continue;
@@ -644,17 +707,37 @@ static bool batch_append(pg_hashagg* op, const pg_col* cols, int32_t ncols, int6
 static void batch_flush(pg_hashagg* op) {
     PageBatch* b = op->batch;
     if (!b || b->rows == 0) return;
+    DevBuf d_descs;
+    if (b->device_mode && !b->descs.empty()) {
+        pg_ctx* ctx = op->ctx;
+        const int64_t bytes = (int64_t)b->descs.size() * (int64_t)sizeof(GatherDesc);
+        const GatherDesc* dd = (const GatherDesc*)in_arena_stage(ctx, b->descs.data(), bytes);
+        if (!dd) { d_descs.alloc(ctx, bytes); copy_async(ctx, d_descs.p, b->descs.data(), bytes, cudaMemcpyHostToDevice); dd = (const GatherDesc*)d_descs.p; }
+        const int nd = (int)b->descs.size();
+        dim3 grid(8, nd < 16384 ? nd : 16384);
+        PG_LAUNCH(ctx, batch_gather_kernel, grid, 256, 0, dd, nd);
+    }
     std::vector<pg_col> cols(b->cols.size());
     for (size_t c = 0; c < cols.size(); c++) {
         const PageBatch::Col& bc = b->cols[c];
         memset(&cols[c], 0, sizeof(pg_col));
         cols[c].type = bc.type; cols[c].mem = PG_MEM_HOST; cols[c].n = b->rows;
         if (!bc.used) continue;
+        if (b->device_mode) {
+            cols[c].mem = PG_MEM_DEVICE;
+            cols[c].values = bc.dvalues.p; cols[c].nulls = bc.has_nulls ? (const uint8_t*)bc.dnulls.p : nullptr;
+            if (type_is_var(bc.type)) {
+                copy_async(op->ctx, bc.doffsets.p, bc.offsets, (b->rows + 1) * 4, cudaMemcpyHostToDevice);
+                cols[c].offsets = (const int32_t*)bc.doffsets.p;
+            }
+            continue;
+        }
         cols[c].values = bc.values; cols[c].nulls = bc.has_nulls ? bc.nulls : nullptr; cols[c].offsets = type_is_var(bc.type) ? bc.offsets : nullptr;
     }
     hashagg_reserve(op, b->rows);
     hashagg_add_page(op, cols.data(), (int32_t)cols.size(), b->rows);      // synchronises: the pinned rows have left when it returns
     b->rows = 0;
+    b->descs.clear();
     for (PageBatch::Col& bc : b->cols) { bc.values_used = 0; bc.has_nulls = false; }
 }
 
@@ -723,7 +806,7 @@ int32_t pg_hashagg_add_pages(pg_hashagg* op, const pg_col* cols, int32_t ncols, 
         for (int64_t at = 0; at < n; at += page_rows) {
             const int64_t m = n - at < page_rows ? n - at : page_rows;
             for (int c = 0; c < ncols; c++) {
-                PG_CHECK_ARG(cols[c].mem == PG_MEM_HOST, "pg_hashagg_add_pages takes host pages");
+                PG_CHECK_ARG(cols[c].mem == PG_MEM_HOST || cols[c].mem == PG_MEM_HOST_PINNED, "pg_hashagg_add_pages takes host pages");
                 page[c] = cols[c];
                 page[c].n = m;
                 if (page[c].nulls) page[c].nulls += at;
@@ -1066,7 +1149,7 @@ int32_t pg_hashagg_set_input_processor(pg_hashagg* op, pg_project* p) {
 int32_t pg_hashagg_reset(pg_hashagg* op) {
     if (!op) return PG_E_INVALID_ARGUMENT;
     return guard(op->ctx, [&] {
-        if (op->batch) { op->batch->rows = 0; for (PageBatch::Col& bc : op->batch->cols) { bc.values_used = 0; bc.has_nulls = false; } }
+        if (op->batch) { op->batch->rows = 0; op->batch->descs.clear(); for (PageBatch::Col& bc : op->batch->cols) { bc.values_used = 0; bc.has_nulls = false; } }
         for (pg_agg* a : op->aggs) delete a;
         op->aggs.clear();
         delete op->gb; op->gb = nullptr;

@@ -195,5 +195,8 @@ def page_to_host(page, pinned=True):
         if pinned:
             c = c.pin_memory()
         return c.numpy()
-    return Page(*[Block(b.type, h(b.values), h(b.nulls), h(b.offsets), b.n, b.precision, b.scale) for b in page.blocks],
-                position_count=page.position_count)
+    out = Page(*[Block(b.type, h(b.values), h(b.nulls), h(b.offsets), b.n, b.precision, b.scale) for b in page.blocks],
+               position_count=page.position_count)
+    for b in out.blocks:
+        b.pinned = bool(pinned)      # the numpy arrays view page-locked torch storage that lives as long as they do
+    return out

@@ -565,3 +565,51 @@ def test_reference_sized_pages_through_the_accumulator_equal_one_big_page(pgpu, 
     op2.add_pages(P.Page(*cols), 1000)
     op2.finish()
     _assert_rows_equal(rows_of(drain(op2)), want)
+
+
+def test_caller_pinned_pages_go_to_the_device_without_a_host_copy(pgpu):
+    """PG_MEM_HOST_PINNED pages through the accumulator's device mode (variable width keys with re-based offsets, a null mask that
+    first appears mid-stream, a batch boundary inside the stream, plain host pages mixed in) give the oracle's rows."""
+    import torch
+    P = pgpu
+    rng = np.random.default_rng(13)
+    n = 41_003
+    flags = np.array(["A", "NN", "R"])[rng.integers(0, 3, n)]
+    keyb = P.Block.variable_width(list(flags))
+    dec = rng.integers(-10**12, 10**12, n).astype(np.int64)
+    dnull = (rng.random(n) < 0.1).astype(np.uint8)
+    dnull[:15_000] = 0
+    dbl = rng.random(n) * 1e3
+    cols = [keyb, P.Block.long_array(dec, dnull, P.SHORT_DECIMAL), P.Block.double_array(dbl)]
+    aggs = [P.AggregatorFactory(P.AGG_COUNT), P.AggregatorFactory(P.AGG_SUM, P.SHORT_DECIMAL, 1), P.AggregatorFactory(P.AGG_SUM, P.DOUBLE, 2),
+            P.AggregatorFactory(P.AGG_COUNT_COL, P.SHORT_DECIMAL, 1)]
+
+    def pin(a):
+        return None if a is None else torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+
+    pinned = [P.Block(b.type, pin(b.values), pin(b.nulls), pin(b.offsets), b.n) for b in cols]
+    keep = pinned        # the pinned arrays stay alive until the operator has been drained (the PG_MEM_HOST_PINNED promise)
+
+    def page(src, lo, hi, is_pinned):
+        out = []
+        for b in src:
+            if b.type in (P.VARCHAR, P.VARBINARY):
+                nb = P.Block(b.type, b.values, None, b.offsets[lo:hi + 1], hi - lo)
+            else:
+                nulls = None if (b.nulls is None or hi <= 15_000) else b.nulls[lo:hi]
+                nb = P.Block(b.type, b.values[lo:hi], nulls, None, hi - lo)
+            nb.pinned = is_pinned
+            out.append(nb)
+        return out
+
+    op = P.HashAggregationOperator([P.VARCHAR], [0], P.SINGLE, aggs, expected_groups=100)
+    op.set_page_batching(12_000)
+    for i, lo in enumerate(range(0, n, 1500)):
+        hi = min(lo + 1500, n)
+        plain = i in (9, 10)                    # two plain host pages in the middle: the accumulator switches modes
+        op.add_input(P.Page(*page(cols if plain else pinned, lo, hi, not plain)))
+    op.finish()
+    got = rows_of(drain(op))
+    want = _oracle_rows(P, None, [cols], aggs, key_types=[P.VARCHAR], key_channels=[0])
+    _assert_rows_equal(got, want)
+    assert keep

@@ -15,7 +15,9 @@ key = torch.randint(0, 1 << 40, (n,), device="cuda", generator=g)
 cols = [Block(N.BIGINT, key, None, None, n), Block(N.SHORT_DECIMAL, torch.arange(n, device="cuda"), None, None, n),
         Block(N.DOUBLE, torch.arange(n, device="cuda"), None, None, n)]
 ctx.set_timing(True)
-for rep in range(2):
+for rep in range(int(os.environ.get("REPS", "2"))):
+    if rep == 1:
+        ctx.kernel_report(reset=True)
     counts = (C.c_int64 * nparts)()
     h = C.c_void_p()
     N.check(ctx.handle, N.lib().pg_partition_create(ctx.handle, col_array(cols[:1]), 1, None, n, nparts, 0, counts, C.byref(h)))

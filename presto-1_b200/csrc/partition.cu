@@ -6,6 +6,9 @@
 // (3) stable ranking: dest[row] = offset[partition][tile] + rank of the row among the tile's rows of that partition.
 // Columns are then scattered with out[dest[row]] = in[row]; rows keep their relative order inside a partition.
 // The scatter can target local memory (NCCL all-to-all follows) or peer GPUs' receive buffers directly (P2P over NVLink).
+#include <algorithm>
+#include <vector>
+
 #include "groupby_dev.cuh"
 #include "scan.cuh"
 
@@ -241,42 +244,55 @@ struct ScatterTable {                       // lives in device memory (too large
     uint8_t* nulls[SC_MAX_COLS][MAX_PARTS];
 };
 
-template <typename T>
-PG_D void scatter_all_column(const ScatterTable* tab, int c, int64_t base, int rows, int warp, int lane, const unsigned short* lpos, unsigned char* stage,
+template <typename T, int THREADS>
+PG_D void scatter_all_column(const ScatterTable* tab, int c, int64_t base, int rows, int warp, int lane, const unsigned short* s_l, unsigned char* stage,
                              const uint8_t* s_q, const long long* s_delta) {
+    constexpr int ITEMS = PART_TILE / THREADS;
     T* vals = (T*)stage;
     uint8_t* nl = (uint8_t*)(vals + PART_TILE);
     const T* in = (const T*)tab->in[c];
     const uint8_t* in_nulls = tab->in_nulls[c];
     bool out_nulls = false;
     for (int q = 0; q < tab->nparts; q++) out_nulls = out_nulls || tab->nulls[c][q] != nullptr;
+    T v[ITEMS];
 #pragma unroll
-    for (int j = 0; j < PART_ITEMS; j++) {
-        const int i = (warp * PART_ITEMS + j) * 32 + lane;
+    for (int j = 0; j < ITEMS; j++) {            // all loads of the thread are issued before the first store to shared memory
+        const int i = (warp * ITEMS + j) * 32 + lane;
+        if (i < rows) v[j] = in[base + i];
+    }
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+        const int i = (warp * ITEMS + j) * 32 + lane;
         if (i < rows) {
-            vals[lpos[j]] = in[base + i];
-            if (out_nulls) nl[lpos[j]] = in_nulls ? in_nulls[base + i] : 0;
+            const int l = s_l[i];
+            vals[l] = v[j];
+            if (out_nulls) nl[l] = in_nulls ? in_nulls[base + i] : 0;
         }
     }
     __syncthreads();
-    for (int l = threadIdx.x; l < rows; l += PART_THREADS) {
+    for (int l = threadIdx.x; l < rows; l += THREADS) {
         const int q = s_q[l];
         const long long d = (long long)l + s_delta[q];
-        ((T*)tab->base[c][q])[d] = vals[l];
+        ((T*)tab->base[c][q])[d] = vals[l];       // (the table's pointers stay in L1; copying them to shared memory per column was slower)
         if (out_nulls) tab->nulls[c][q][d] = nl[l];
     }
     __syncthreads();
 }
 
-template <int MINB>
-__global__ void __launch_bounds__(PART_THREADS, MINB) part_scatter_all_kernel(const uint8_t* __restrict__ part_of_row, int64_t n, int nparts,
-                                                                        const Pair64* __restrict__ offsets, int64_t ntiles,
-                                                                        const ScatterTable* __restrict__ tab) {
+// THREADS threads share the 4096 rows of a tile: warp w owns the PART_TILE / (THREADS / 32) consecutive rows starting at
+// w * that many and visits them 32 at a time, so ranks follow row order whatever THREADS is (the histogram's tiles are the same
+// 4096 rows; only their division among warps differs, which a stable rank does not see).
+template <int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) part_scatter_all_kernel(const uint8_t* __restrict__ part_of_row, int64_t n, int nparts,
+                                                                         const Pair64* __restrict__ offsets, int64_t ntiles,
+                                                                         const ScatterTable* __restrict__ tab) {
+    constexpr int ITEMS = PART_TILE / THREADS;
     extern __shared__ __align__(16) unsigned char stage[];
     __shared__ long long s_delta[MAX_PARTS];      // destination row in the receiver's buffer = staged place + s_delta[partition]
     __shared__ int s_start[MAX_PARTS + 1];        // where partition p starts inside the staged tile
-    __shared__ int warp_cnt[PART_THREADS / 32][MAX_PARTS];
+    __shared__ int warp_cnt[THREADS / 32][MAX_PARTS];
     __shared__ uint8_t s_q[PART_TILE];            // partition of every staged place
+    __shared__ unsigned short s_l[PART_TILE];     // staged place of every row of the tile (kept here, not in registers: every column pass reads it)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t tile = blockIdx.x, base = tile * PART_TILE;
     const int rows = (int)((n - base) < PART_TILE ? (n - base) : PART_TILE);
@@ -293,33 +309,34 @@ __global__ void __launch_bounds__(PART_THREADS, MINB) part_scatter_all_kernel(co
         s_start[0] = 0;
         for (int q = 0; q < nparts; q++) s_start[q + 1] += s_start[q];
     }
-    int mine[PART_ITEMS];
+    int mine[ITEMS];
 #pragma unroll
-    for (int j = 0; j < PART_ITEMS; j++) {
-        const int i = (warp * PART_ITEMS + j) * 32 + lane;
-        const int p = i < rows ? (int)part_of_row[base + i] : -1;
-        mine[j] = p;
+    for (int j = 0; j < ITEMS; j++) {
+        const int i = (warp * ITEMS + j) * 32 + lane;
+        mine[j] = i < rows ? (int)part_of_row[base + i] : -1;
+    }
+#pragma unroll
+    for (int j = 0; j < ITEMS; j++) {
+        const int p = mine[j];
         const unsigned peers = part_peers(p, nparts);
         if (p >= 0 && (peers & ((1u << lane) - 1u)) == 0) warp_cnt[warp][p] += __popc(peers);
         __syncwarp();
     }
     __syncthreads();
-    for (int q = threadIdx.x; q < nparts; q += PART_THREADS) {
+    for (int q = threadIdx.x; q < nparts; q += THREADS) {
         int run = s_start[q];
-        for (int w = 0; w < PART_THREADS / 32; w++) { const int cnt = warp_cnt[w][q]; warp_cnt[w][q] = run; run += cnt; }
+        for (int w = 0; w < THREADS / 32; w++) { const int cnt = warp_cnt[w][q]; warp_cnt[w][q] = run; run += cnt; }
         s_delta[q] = s_delta[q] - s_start[q] - tab->part_start[q] + tab->peer_row_offset[q];
     }
     __syncthreads();
-    unsigned short lpos[PART_ITEMS];
 #pragma unroll
-    for (int j = 0; j < PART_ITEMS; j++) {
+    for (int j = 0; j < ITEMS; j++) {
         const int p = mine[j];
         const unsigned peers = part_peers(p, nparts);
         const int rank_in_warp = __popc(peers & ((1u << lane) - 1u));
-        lpos[j] = 0;
         if (p >= 0) {
             const int l = warp_cnt[warp][p] + rank_in_warp;
-            lpos[j] = (unsigned short)l;
+            s_l[(warp * ITEMS + j) * 32 + lane] = (unsigned short)l;
             s_q[l] = (uint8_t)p;
         }
         __syncwarp();
@@ -330,10 +347,10 @@ __global__ void __launch_bounds__(PART_THREADS, MINB) part_scatter_all_kernel(co
     const int ncols = tab->ncols;
     for (int c = 0; c < ncols; c++) {
         switch (tab->width[c]) {
-            case 1: scatter_all_column<uint8_t>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta); break;
-            case 4: scatter_all_column<int32_t>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta); break;
-            case 8: scatter_all_column<int64_t>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta); break;
-            default: scatter_all_column<int4>(tab, c, base, rows, warp, lane, lpos, stage, s_q, s_delta);
+            case 1: scatter_all_column<uint8_t, THREADS>(tab, c, base, rows, warp, lane, s_l, stage, s_q, s_delta); break;
+            case 4: scatter_all_column<int32_t, THREADS>(tab, c, base, rows, warp, lane, s_l, stage, s_q, s_delta); break;
+            case 8: scatter_all_column<int64_t, THREADS>(tab, c, base, rows, warp, lane, s_l, stage, s_q, s_delta); break;
+            default: scatter_all_column<int4, THREADS>(tab, c, base, rows, warp, lane, s_l, stage, s_q, s_delta);
         }
     }
 }
@@ -546,24 +563,31 @@ int32_t pg_partition_scatter_peers_all(pg_partitioner* pt, const pg_col* cols, i
         }
         const int64_t ntiles = (pt->n + PART_TILE - 1) / PART_TILE;
         const size_t smem = (size_t)PART_TILE * (maxw + 1);
-        static bool smem_set = false;
-        if (!smem_set) {
-            PG_CUDA(cudaFuncSetAttribute((const void*)part_scatter_all_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(PART_TILE * 17)));
-            PG_CUDA(cudaFuncSetAttribute((const void*)part_scatter_all_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(PART_TILE * 17)));
-            PG_CUDA(cudaFuncSetAttribute((const void*)part_scatter_all_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(PART_TILE * 17)));
-            smem_set = true;
-        }
-        // register budget: <4> = 64 registers (spills the per-row places), <3> = 80, <2> = 128 (no spills, half the resident warps);
-        // 300 M rows x 3 columns into 8 local buffers, steady state: 6.6 / 8.2 / 11.3 ms — the kernel waits between its block-wide
-        // phases, resident warps are what it needs
-        int minb = 4;
-        if (const char* e = getenv("PRESTOGPU_SCATTER_MINB")) minb = atoi(e);
-        if (minb >= 4)
-            PG_LAUNCH(ctx, part_scatter_all_kernel<4>, (int)ntiles, PART_THREADS, smem, pt->part_of_row.as<uint8_t>(), pt->n, pt->nparts, pt->counts.as<Pair64>(), ntiles, d_tab);
-        else if (minb == 3)
-            PG_LAUNCH(ctx, part_scatter_all_kernel<3>, (int)ntiles, PART_THREADS, smem, pt->part_of_row.as<uint8_t>(), pt->n, pt->nparts, pt->counts.as<Pair64>(), ntiles, d_tab);
-        else
-            PG_LAUNCH(ctx, part_scatter_all_kernel<2>, (int)ntiles, PART_THREADS, smem, pt->part_of_row.as<uint8_t>(), pt->n, pt->nparts, pt->counts.as<Pair64>(), ntiles, d_tab);
+        // thread layout / register budget, 300 M rows x 3 columns into 8 local buffers, steady state: 256 threads x 16 rows per thread with
+        // the rows' places in registers 6.6 ms at 64 registers (spills), 11.3 ms at 128 (two blocks per SM); places in shared memory and
+        // 512 threads x 8 rows: 5.1 ms at 64 registers, 4.2 ms at 40 (three blocks = 75 % of the warp slots), 4.5 ms at 32.  The kernel
+        // waits between its block-wide phases: resident warps are what it needs.  PRESTOGPU_SCATTER_SHAPE: 0 256x4, 1 512x2, 2 1024x1,
+        // 3 512x3 (default), 4 512x4, 5 1024x2, 6 256x6
+        int shape = 3;
+        if (const char* e = getenv("PRESTOGPU_SCATTER_SHAPE")) shape = atoi(e);
+#define PG_SCATTER_ALL(T, M)                                                                                                          \
+        do {                                                                                                                           \
+            static bool prepared = false;                                                                                              \
+            if (!prepared) {                                                                                                           \
+                PG_CUDA(cudaFuncSetAttribute((const void*)part_scatter_all_kernel<T, M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(PART_TILE * 17))); \
+                prepared = true;                                                                                                       \
+            }                                                                                                                          \
+            auto part_scatter_all_kernel_ = part_scatter_all_kernel<T, M>;                                                             \
+            PG_LAUNCH(ctx, part_scatter_all_kernel_, (int)ntiles, T, smem, pt->part_of_row.as<uint8_t>(), pt->n, pt->nparts, pt->counts.as<Pair64>(), ntiles, d_tab); \
+        } while (0)
+        if (shape == 0) PG_SCATTER_ALL(256, 4);
+        else if (shape == 2) PG_SCATTER_ALL(1024, 1);
+        else if (shape == 3) PG_SCATTER_ALL(512, 3);
+        else if (shape == 4) PG_SCATTER_ALL(512, 4);
+        else if (shape == 5) PG_SCATTER_ALL(1024, 2);
+        else if (shape == 6) PG_SCATTER_ALL(256, 6);
+        else PG_SCATTER_ALL(512, 2);
+#undef PG_SCATTER_ALL
     });
 }
 

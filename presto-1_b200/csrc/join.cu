@@ -1,8 +1,6 @@
 // join.cu — join build (PagesIndex + PagesHash + ArrayPositionLinks) and probe (JoinProbe + LookupJoinOperator emit).
 #include <stdlib.h>
 
-#include <chrono>
-
 #include "join.h"
 #include "project.h"
 
@@ -801,15 +799,7 @@ static int64_t overflow_slots(int64_t rows) {
 static void lookup_build(pg_lookup* ls) {
     pg_ctx* ctx = ls->ctx;
     int64_t rows = ls->rows;
-    const bool trace = getenv("PRESTOGPU_TRACE_BUILD") != nullptr;
-    auto t_last = std::chrono::steady_clock::now();
-    auto lap = [&](const char* what) {
-        if (!trace) return;
-        cudaStreamSynchronize(ctx->stream);
-        auto now = std::chrono::steady_clock::now();
-        fprintf(stderr, "[build] %-12s %.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
-        t_last = now;
-    };
+
     JoinCols build = build_join_cols(ls->cols, ls->join_channels);
     ls->bigint_fast = build.bigint_fast != 0;
     int64_t plain_cap = array_size_075(rows > 0 ? rows : 1);   // PagesHash.java:63
@@ -842,10 +832,8 @@ static void lookup_build(pg_lookup* ls) {
             }
         }
     }
-    lap("key range");
     DevBuf row_slot;
     if (rows > 0) row_slot.alloc(ctx, rows * 4);
-    lap("row_slot");
     DCol hc; memset(&hc, 0, sizeof(hc));
     int has_hash = 0;
     if (ls->hash_channel >= 0 && !ls->bigint_fast) { hc = ls->cols[ls->hash_channel].view(); has_hash = 1; }
@@ -854,11 +842,9 @@ static void lookup_build(pg_lookup* ls) {
         ls->cap = L.total;
         const int64_t nslots = ls->cap + 1;
         ls->slots.alloc(ctx, nslots * (int64_t)sizeof(JSlot));
-        lap("slots alloc");
-        PG_LAUNCH(ctx, j_init_slots_kernel, grid_for(ctx, nslots, 256, 4), 256, 0, ls->slots.as<JSlot>(), nslots,
+            PG_LAUNCH(ctx, j_init_slots_kernel, grid_for(ctx, nslots, 256, 4), 256, 0, ls->slots.as<JSlot>(), nslots,
                   ls->bigint_fast ? EMPTY_KEY : EMPTY_WORD);
-        lap("init");
-        if (rows == 0) return;
+            if (rows == 0) return;
         if (fast) {
             const DCol& kc = build.c[0];
             PG_LAUNCH(ctx, j_build_fast_kernel, grid_for(ctx, rows, J_THREADS, 4), J_THREADS, 0, ls->slots.as<JSlot>(), L, (const int64_t*)kc.values,
@@ -868,9 +854,7 @@ static void lookup_build(pg_lookup* ls) {
             // load-factor bound of the hashed region: probing it for an absent key ends at a free slot, so it may never fill up
             // (a row that needed more than 2048 steps already set m[8]); past 3/4 the plain table is built instead
             if (L.range && m[9] > (L.omask + 1) / 4 * 3) m[8] = 1;
-            lap("build_fast");
-            if (trace) fprintf(stderr, "[build] rows %lld slots %lld range %d overflowed %lld\n", (long long)rows, (long long)nslots, L.range, (long long)m[8]);
-            if (L.range && m[8] != 0) {
+                    if (L.range && m[8] != 0) {
                 // the keys are spread too unevenly for the range region (its hashed overflow filled up): build the plain table instead
                 memset(&L, 0, sizeof(L));
                 L.omask = plain_cap - 1; L.total = plain_cap;
@@ -889,11 +873,9 @@ static void lookup_build(pg_lookup* ls) {
         break;
     }
     const int64_t nslots = ls->cap + 1;
-    lap("after loop");
     if (!ls->has_dups) {         // JoinHashSupplier.java:72: positionLinks == Optional.empty()
         row_slot.release();
-        lap("free row_slot");
-        return;
+            return;
     }
     // CSR segments for repeated keys
     int64_t ntiles = num_tiles(nslots);
@@ -986,11 +968,7 @@ int32_t pg_joinbuild_add_page(pg_joinbuild* b, const pg_col* cols, int64_t n) {
 
 int32_t pg_joinbuild_finish(pg_joinbuild* b, pg_lookup** out) {
     if (!b || !out) return PG_E_INVALID_ARGUMENT;
-    const bool trace = getenv("PRESTOGPU_TRACE_BUILD") != nullptr;
-    auto t0 = std::chrono::steady_clock::now();
-    auto since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
-    int32_t rc = guard(b->ctx, [&] {
-        if (trace) fprintf(stderr, "[finish] in guard %.3f\n", since());
+    return guard(b->ctx, [&] {
         pg_lookup* ls = new pg_lookup();
         try {
             ls->ctx = b->ctx; ls->types = b->types; ls->join_channels = b->join_channels; ls->hash_channel = b->hash_channel;
@@ -999,16 +977,11 @@ int32_t pg_joinbuild_finish(pg_joinbuild* b, pg_lookup** out) {
             b->cols.clear(); b->cols.resize(b->types.size());
             for (size_t k = 0; k < b->types.size(); k++) b->cols[k].type = b->types[k];
             b->rows = 0;
-            if (trace) fprintf(stderr, "[finish] before build %.3f\n", since());
             lookup_build(ls);
-            if (trace) fprintf(stderr, "[finish] after build %.3f\n", since());
             sync(ls->ctx);
-            if (trace) fprintf(stderr, "[finish] after sync %.3f\n", since());
         } catch (...) { delete ls; throw; }
         *out = ls;
     });
-    if (trace) fprintf(stderr, "[finish] done %.3f\n", since());
-    return rc;
 }
 
 int32_t pg_lookup_destroy(pg_lookup* ls) {

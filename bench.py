@@ -69,7 +69,7 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-workloads", action="store_true", help="headline only (skips the SF100 GROUP BY orderkey / join records)")
     ap.add_argument("--no-crosscheck", action="store_true", help="skip the small-scale oracle cross-checks (profiling runs)")
-    ap.add_argument("--only", default="", help="comma list of workloads to run: groupby,join,grid (default all)")
+    ap.add_argument("--only", default="", help="comma list of workloads to run: groupby,join,q3,grid (default all)")
     return ap.parse_args()
 
 
@@ -511,6 +511,10 @@ def wide_workloads(args, env, traffic):
                                {"matches": n_all, "selfcheck": check})
             del want, gv, got, pp, local, ppage
         del od, bpage, join, ls
+    if not only or "q3" in only:
+        del li, lis
+        torch.cuda.empty_cache()
+        res["q3_join_aggregation"] = q3_shape(args, env, exchange)
     ctx.set_timing(False)
     if world == 1 and (not only or "grid" in only):
         res["groupby_hash_grid"] = groupby_hash_grid(args, env)
@@ -519,6 +523,87 @@ def wide_workloads(args, env, traffic):
                            "collective": ("fused partition + peer-memory stores over NVLink (pg_partition_scatter_peers into symmetric receive buffers)"
                                           if exchange.peer is not None else "NCCL all_to_all_single per column (%s)" % exchange.peer_why)}
     return res
+
+
+# ------------------------------------------------------------------------------------------- cfg5: TPC-H Q3 shape
+def q3_shape(args, env, exchange):
+    """BASELINE.json configs[4]: customer (mktsegment = 'BUILDING') JOIN orders (orderdate < 1995-03-15) ON custkey JOIN lineitem
+    (shipdate > 1995-03-15) ON orderkey, GROUP BY (l_orderkey, o_orderdate, o_shippriority), sum(extendedprice * (1 - discount));
+    1 % NULL o_custkey and l_orderkey.  Filters and the revenue projection are PageProcessors, both joins are
+    PartitionedHashJoin (hash exchange on the join key at N > 1), the aggregation is the general (multi-channel) path on each rank's
+    join output — its group key starts with the exchanged orderkey, so no further exchange is needed.  SF = --wide-sf in total."""
+    P, tpch, torch, ctx, world, rank = env.P, env.tpch, env.torch, env.ctx, env.world, env.rank
+    from presto_b200.blocks import Block
+    from presto_b200.expressions import Expr as E, PageProcessor
+    from presto_b200.operators import take_positions
+    N = P.native
+    sf = args.wide_sf / world
+    cutoff = 9204                                                 # 1995-03-15
+    cu = tpch.customer(sf, seed=42 + rank, device="cuda")
+    od = tpch.orders(sf, seed=42 + rank, device="cuda")
+    li = tpch.lineitem(sf, seed=42 + rank, device="cuda", need=("keys", "raw"))
+    n_c, n_o, n_l = cu["rows"], int(od["orderkey"].numel()), li["rows"]
+    okey_off = rank * tpch.order_key(torch.tensor(n_o, dtype=torch.int64)).item()
+    ckey_off = rank * n_c                                         # disjoint customer / order key ranges per rank
+    od["orderkey"] += okey_off; li["orderkey"] += okey_off
+    cu["custkey"] += ckey_off; od["custkey"] = (od["custkey"] - 1) % n_c + 1 + ckey_off
+    o_null = tpch.null_mask(n_o, 43 + rank, 1, 100, "cuda")
+    l_null = tpch.null_mask(n_l, 43 + rank, 2, 100, "cuda")
+    cpage = P.Page(Block(N.BIGINT, cu["custkey"], None, None, n_c), Block(N.VARCHAR, cu["mktsegment_bytes"], None, cu["mktsegment_offsets"], n_c), position_count=n_c)
+    opage = P.Page(Block(N.BIGINT, od["custkey"], o_null, None, n_o), Block(N.BIGINT, od["orderkey"], None, None, n_o),
+                   Block(N.DATE, od["orderdate"], None, None, n_o), Block(N.INTEGER, od["shippriority"], None, None, n_o), position_count=n_o)
+    lpage = P.Page(Block(N.BIGINT, li["orderkey"], l_null, None, n_l), Block(N.SHORT_DECIMAL, li["extendedprice"], None, None, n_l, 12, 2),
+                   Block(N.SHORT_DECIMAL, li["discount"], None, None, n_l, 12, 2), Block(N.DATE, li["shipdate"], None, None, n_l), position_count=n_l)
+    seg_filter = PageProcessor(E.input(1, N.VARCHAR).eq(E.varchar("BUILDING")), [E.input(0, N.BIGINT)], ctx=ctx)
+    ord_filter = PageProcessor(E.input(2, N.DATE) < E.date(cutoff), [E.input(0, N.BIGINT), E.input(1, N.BIGINT), E.input(2, N.DATE), E.input(3, N.INTEGER)], ctx=ctx)
+    li_filter = PageProcessor(E.input(3, N.DATE) > E.date(cutoff),
+                              [E.input(0, N.BIGINT), E.input(1, N.SHORT_DECIMAL, 12, 2) * (E.decimal(1, 1, 0) - E.input(2, N.SHORT_DECIMAL, 12, 2))], ctx=ctx)
+    aggs = [P.AggregatorFactory(P.AGG_SUM, P.LONG_DECIMAL, 3)]
+    join1 = P.PartitionedHashJoin([P.BIGINT], [0], ctx, env.dist, exchange=exchange)
+    join2 = P.PartitionedHashJoin([P.BIGINT, P.DATE, P.INTEGER], [0], ctx, env.dist, exchange=exchange)
+
+    def step():
+        building = seg_filter.process(cpage, device=True)                                     # custkey of the segment's customers
+        orders_f = ord_filter.process(opage, device=True)                                     # custkey, orderkey, orderdate, shippriority
+        join1.build(building, slot="q3_b1")
+        local_o, pp, _ = join1.probe(orders_f, [0], [], slot="q3_p1")
+        surviving = P.Page(*[take_positions(local_o.blocks[c], pp) for c in (1, 2, 3)], position_count=len(pp))
+        join2.build(surviving, slot="q3_b2")
+        items = li_filter.process(lpage, device=True)                                         # orderkey, revenue decimal(25,4)
+        local_l, pp2, gathered = join2.probe(items, [0], [1, 2], slot="q3_p2")
+        joined = P.Page(take_positions(local_l.blocks[0], pp2), gathered[0], gathered[1], take_positions(local_l.blocks[1], pp2), position_count=len(pp2))
+        op = P.HashAggregationOperator([P.BIGINT, P.DATE, P.INTEGER], [0, 1, 2], P.SINGLE, aggs, expected_groups=max(len(pp) , 1000), ctx=ctx, device_output=True)
+        op.add_input(joined)
+        op.finish()
+        g = op.get_group_count()
+        out = op.get_output(max_rows=max(g, 1))
+        op.close()
+        return g, out, len(pp), len(pp2), joined
+
+    ms, (groups, out, n_surv, n_joined, joined), kern, _ = env.timed(step, args.wide_steps, args.wide_warmup)
+    # self-check with torch on the same columns (independent of the library): which orders survive, which lineitems join, what they add up to
+    if world == 1:
+        cust_ok = torch.zeros(n_c + 2, dtype=torch.bool, device="cuda")
+        cust_ok[cu["custkey"][cu["segment_code"] == 1]] = True
+        o_ok = (od["orderdate"] < cutoff) & (o_null == 0) & cust_ok[od["custkey"].clamp(0, n_c + 1)]
+        l_ok = (li["shipdate"] > cutoff) & (l_null == 0)
+        order_pos = torch.searchsorted(od["orderkey"], li["orderkey"]).clamp(max=n_o - 1)
+        l_join = l_ok & o_ok[order_pos] & (od["orderkey"][order_pos] == li["orderkey"])
+        rev = (li["extendedprice"] * (100 - li["discount"]))[l_join]
+        want_groups = int(torch.unique(li["orderkey"][l_join]).numel())
+        got_rev = out.blocks[3].values.view(-1, 2)[:, 0]              # sums are far below 2^63
+        check = {"surviving_orders": n_surv == int(o_ok.sum().item()), "joined_lineitems": n_joined == int(l_join.sum().item()),
+                 "groups": groups == want_groups, "revenue_sum_bit_exact": int(got_rev.sum().item()) == int(rev.sum().item())}
+    else:
+        check = {"groups_positive": env.total(groups) > 0}
+    if not all(check.values()):
+        raise SystemExit("bench self-check failed (Q3 shape): %s" % json.dumps(check))
+    rows_in = env.total(n_c + n_o + n_l)
+    return {"workload": "TPC-H Q3 shape (cfg5): customer[mktsegment='BUILDING'] JOIN orders[orderdate<1995-03-15] JOIN lineitem[shipdate>1995-03-15], "
+                        "GROUP BY (l_orderkey, o_orderdate, o_shippriority) sum(extendedprice*(1-discount)); 1 % NULL join keys; filters, two hash "
+                        "joins, composite-key aggregation", "input_rows": int(rows_in), "ms_per_step": round(ms, 3), "rows_per_s": rows_in / (ms / 1e3),
+            "surviving_orders": env.total(n_surv), "joined_lineitems": env.total(n_joined), "groups": env.total(groups), "steps": args.wide_steps,
+            "kernels_ms_per_step": {k: round(v[0] / args.wide_steps, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:10]}, "selfcheck": check}
 
 
 # ------------------------------------------------------------------------------------------- BenchmarkGroupByHash grid

@@ -184,7 +184,7 @@ class PageProcessor:
             if t in (N.VARCHAR, N.VARBINARY):
                 src = blocks[e.channel]
                 vb = int(src.values.numel() if src.device else len(src.values))
-            outs.append(OutBlock(t, n, vb, device=on_device))
+            outs.append(OutBlock(t, n, vb, device=on_device, zero=not on_device))     # (the kernels write every selected row of every array)
         arr = (N.PgColOut * max(1, len(outs)))()
         for i, o in enumerate(outs):
             arr[i] = o.pg_col_out()

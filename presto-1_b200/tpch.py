@@ -63,6 +63,31 @@ def orders(sf, seed=42, device="cuda", rows=None):
     return {"orderkey": okey, "custkey": custkey, "totalprice": totalprice, "orderdate": orderdate, "shippriority": shipprio}
 
 
+SEGMENTS = ("AUTOMOBILE", "BUILDING", "FURNITURE", "MACHINERY", "HOUSEHOLD")
+
+
+def customer(sf, seed=42, device="cuda"):
+    """customer: c_custkey (1..150 000 x SF), c_mktsegment (one of the five TPC-H segments, a VARCHAR column: bytes + offsets)."""
+    n = max(2, int(150_000 * sf))
+    idx = torch.arange(n, device=device, dtype=torch.int64)
+    seg = _randint(seed + 2, 1, idx, 0, len(SEGMENTS))
+    lens = torch.tensor([len(x) for x in SEGMENTS], device=device, dtype=torch.int64)
+    text = torch.tensor(list("".join(SEGMENTS).encode()), device=device, dtype=torch.uint8)
+    starts = torch.cumsum(lens, 0) - lens
+    offsets = torch.zeros(n + 1, device=device, dtype=torch.int64)
+    torch.cumsum(lens[seg], 0, out=offsets[1:])
+    row_of_byte = torch.repeat_interleave(idx, lens[seg])
+    within = torch.arange(int(offsets[-1].item()), device=device, dtype=torch.int64) - offsets[:-1][row_of_byte]
+    data = text[starts[seg][row_of_byte] + within]
+    return {"rows": n, "custkey": idx + 1, "segment_code": seg, "mktsegment_bytes": data, "mktsegment_offsets": offsets.to(torch.int32)}
+
+
+def null_mask(n, seed, stream, one_in, device):
+    """uint8 mask with about one row in `one_in` set (the same rows on CPU and CUDA)."""
+    idx = torch.arange(n, device=device, dtype=torch.int64)
+    return (_randint(seed, stream, idx, 0, one_in) == 0).to(torch.uint8)
+
+
 def shuffle_order(n, seed, device):
     """A seeded permutation of range(n), identical on CPU and CUDA (stable argsort of hashed row numbers)."""
     return torch.argsort(_mix(seed, 99, torch.arange(n, device=device, dtype=torch.int64)), stable=True)

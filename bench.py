@@ -556,8 +556,11 @@ def q3_shape(args, env, exchange):
                    Block(N.SHORT_DECIMAL, li["discount"], None, None, n_l, 12, 2), Block(N.DATE, li["shipdate"], None, None, n_l), position_count=n_l)
     seg_filter = PageProcessor(E.input(1, N.VARCHAR).eq(E.varchar("BUILDING")), [E.input(0, N.BIGINT)], ctx=ctx)
     ord_filter = PageProcessor(E.input(2, N.DATE) < E.date(cutoff), [E.input(0, N.BIGINT), E.input(1, N.BIGINT), E.input(2, N.DATE), E.input(3, N.INTEGER)], ctx=ctx)
-    li_filter = PageProcessor(E.input(3, N.DATE) > E.date(cutoff),
-                              [E.input(0, N.BIGINT), E.input(1, N.SHORT_DECIMAL, 12, 2) * (E.decimal(1, 1, 0) - E.input(2, N.SHORT_DECIMAL, 12, 2))], ctx=ctx)
+    li_filter = PageProcessor(E.input(3, N.DATE) > E.date(cutoff), [E.input(0, N.BIGINT), E.input(1, N.SHORT_DECIMAL, 12, 2), E.input(2, N.SHORT_DECIMAL, 12, 2)], ctx=ctx)
+    # the revenue expression sits above the joins, as in the reference's plan (a ProjectNode right below the aggregation): it is the
+    # aggregation's input processor and is evaluated for the joined rows only
+    revenue = PageProcessor(None, [E.input(0, N.BIGINT), E.input(1, N.DATE), E.input(2, N.INTEGER),
+                                   E.input(3, N.SHORT_DECIMAL, 12, 2) * (E.decimal(1, 1, 0) - E.input(4, N.SHORT_DECIMAL, 12, 2))], ctx=ctx)
     aggs = [P.AggregatorFactory(P.AGG_SUM, P.LONG_DECIMAL, 3)]
     join1 = P.PartitionedHashJoin([P.BIGINT], [0], ctx, env.dist, exchange=exchange)
     join2 = P.PartitionedHashJoin([P.BIGINT, P.DATE, P.INTEGER], [0], ctx, env.dist, exchange=exchange)
@@ -569,10 +572,14 @@ def q3_shape(args, env, exchange):
         local_o, pp, _ = join1.probe(orders_f, [0], [], slot="q3_p1")
         surviving = P.Page(*[take_positions(local_o.blocks[c], pp) for c in (1, 2, 3)], position_count=len(pp))
         join2.build(surviving, slot="q3_b2")
-        items = li_filter.process(lpage, device=True)                                         # orderkey, revenue decimal(25,4)
+        items = li_filter.process(lpage, device=True)                                         # orderkey, extendedprice, discount
         local_l, pp2, gathered = join2.probe(items, [0], [1, 2], slot="q3_p2")
-        joined = P.Page(take_positions(local_l.blocks[0], pp2), gathered[0], gathered[1], take_positions(local_l.blocks[1], pp2), position_count=len(pp2))
-        op = P.HashAggregationOperator([P.BIGINT, P.DATE, P.INTEGER], [0, 1, 2], P.SINGLE, aggs, expected_groups=max(len(pp) , 1000), ctx=ctx, device_output=True)
+        joined = P.Page(take_positions(local_l.blocks[0], pp2), gathered[0], gathered[1], take_positions(local_l.blocks[1], pp2),
+                        take_positions(local_l.blocks[2], pp2), position_count=len(pp2))
+        for b in joined.blocks[3:]:
+            b.precision, b.scale = 12, 2
+        op = P.HashAggregationOperator([P.BIGINT, P.DATE, P.INTEGER], [0, 1, 2], P.SINGLE, aggs, expected_groups=max(len(pp), 1000), ctx=ctx, device_output=True,
+                                       input_processor=revenue)
         op.add_input(joined)
         op.finish()
         g = op.get_group_count()

@@ -213,6 +213,40 @@ __global__ void __launch_bounds__(SCAN_THREADS) proj_select_kernel(const PNode* 
     if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
     if (err) atomicOr(d_err, err);
 }
+// pass 1, common case: the filter is one comparison of a fixed width input column with a constant of the same type (a date or key
+// range).  No interpreter: 4 or 8 bytes read per row instead of a walk over the node array with 24-byte values in local memory
+// (600 M rows: 10 ms interpreted).  cmp: PG_EXPR_LT .. PG_EXPR_NE; a NULL input never passes.
+template <typename T>
+__global__ void __launch_bounds__(SCAN_THREADS) proj_select_cmp_kernel(const T* __restrict__ values, const uint8_t* __restrict__ nulls, T constant, int cmp,
+                                                                       int64_t n, const unsigned int* __restrict__ only_bits, uint8_t* __restrict__ flags,
+                                                                       Pair64* __restrict__ tile_sums) {
+    __shared__ Pair64 smem[SCAN_THREADS / 32 + 1];
+    const int64_t tile_base = (int64_t)blockIdx.x * SCAN_TILE;
+    Pair64 acc{0, 0};
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        const int64_t i = tile_base + (int64_t)j * SCAN_THREADS + threadIdx.x;
+        if (i >= n) continue;
+        bool pass = only_bits == nullptr || ((only_bits[i >> 5] >> (i & 31)) & 1u);
+        if (pass) {
+            const T v = values[i];
+            switch (cmp) {
+                case PG_EXPR_LT: pass = v < constant; break;
+                case PG_EXPR_LE: pass = v <= constant; break;
+                case PG_EXPR_GT: pass = v > constant; break;
+                case PG_EXPR_GE: pass = v >= constant; break;
+                case PG_EXPR_EQ: pass = v == constant; break;
+                default: pass = v != constant;
+            }
+            if (nulls && nulls[i]) pass = false;
+        }
+        flags[i] = pass ? 1 : 0;
+        acc.a += pass ? 1 : 0;
+    }
+    Pair64 total;
+    block_exclusive_scan(acc, smem, &total);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
 // pass 2: selected row numbers in page order
 __global__ void __launch_bounds__(SCAN_THREADS) proj_positions_kernel(const uint8_t* __restrict__ flags, int64_t n, const Pair64* __restrict__ tile_prefix,
                                                                       int64_t* __restrict__ sel) {
@@ -404,6 +438,28 @@ void project_materialize(pg_project* p, const DCol* in, int ncols, int64_t n, co
     if (selecting && n > 0) {
         const int64_t ntiles = num_tiles(n);
         DevBuf flags(ctx, n), tiles(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64));
+        // the filter as "input column <cmp> constant" over integer-like values of one width (exact for BIGINT, INTEGER, DATE and for
+        // short decimals of equal scale; doubles and everything else go through the interpreter)
+        int simple = 0;
+        const PNode* fa = nullptr; const PNode* fb = nullptr;
+        if (p->filter >= 0) {
+            const PNode& f = p->nodes[p->filter];
+            if (f.op >= PG_EXPR_LT && f.op <= PG_EXPR_NE && f.a0 >= 0 && f.a1 >= 0) {
+                fa = &p->nodes[f.a0]; fb = &p->nodes[f.a1];
+                const bool ints = fa->type == fb->type && (fa->type == PG_BIGINT || fa->type == PG_INTEGER || fa->type == PG_DATE ||
+                                                           (fa->type == PG_SHORT_DECIMAL && fa->scale == fb->scale));
+                if (ints && fa->op == PG_EXPR_INPUT && fb->op == PG_EXPR_CONST && !fb->is_null) simple = f.op;
+            }
+        }
+        if (simple && !getenv("PRESTOGPU_PROJECT_INTERPRET")) {
+            const DCol& c = in[fa->channel];
+            if (type_width(fa->type) == 4)
+                PG_LAUNCH(ctx, proj_select_cmp_kernel<int32_t>, (int)ntiles, SCAN_THREADS, 0, (const int32_t*)c.values, c.nulls, (int32_t)fb->lo, simple, n, only_bits,
+                          flags.as<uint8_t>(), tiles.as<Pair64>());
+            else
+                PG_LAUNCH(ctx, proj_select_cmp_kernel<int64_t>, (int)ntiles, SCAN_THREADS, 0, (const int64_t*)c.values, c.nulls, (int64_t)fb->lo, simple, n, only_bits,
+                          flags.as<uint8_t>(), tiles.as<Pair64>());
+        } else
         PG_LAUNCH(ctx, proj_select_kernel, (int)ntiles, SCAN_THREADS, 0, d_nodes, n_nodes, p->filter, pc, d_bytes, n, only_bits, flags.as<uint8_t>(),
                   tiles.as<Pair64>(), err.as<unsigned int>());
         scan_tile_totals(ctx, tiles.as<Pair64>(), ntiles, tiles.as<Pair64>() + ntiles);

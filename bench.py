@@ -565,19 +565,36 @@ def q3_shape(args, env, exchange):
     join1 = P.PartitionedHashJoin([P.BIGINT], [0], ctx, env.dist, exchange=exchange)
     join2 = P.PartitionedHashJoin([P.BIGINT, P.DATE, P.INTEGER], [0], ctx, env.dist, exchange=exchange)
 
+    stages = None                                                                             # filled by the untimed breakdown pass below
+
+    def mark(name, t0):
+        if stages is None:
+            return t0
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        stages[name] = round(stages.get(name, 0.0) + (t1 - t0) * 1e3, 3)
+        return t1
+
     def step():
+        t = time.perf_counter()
         building = seg_filter.process(cpage, device=True)                                     # custkey of the segment's customers
         orders_f = ord_filter.process(opage, device=True)                                     # custkey, orderkey, orderdate, shippriority
+        t = mark("filter_customer_orders", t)
         join1.build(building, slot="q3_b1")
+        t = mark("join1_build", t)
         local_o, pp, _ = join1.probe(orders_f, [0], [], slot="q3_p1")
         surviving = P.Page(*[take_positions(local_o.blocks[c], pp) for c in (1, 2, 3)], position_count=len(pp))
+        t = mark("join1_probe", t)
         join2.build(surviving, slot="q3_b2")
+        t = mark("join2_build", t)
         items = li_filter.process(lpage, device=True)                                         # orderkey, extendedprice, discount
+        t = mark("filter_lineitem", t)
         local_l, pp2, gathered = join2.probe(items, [0], [1, 2], slot="q3_p2")
         joined = P.Page(take_positions(local_l.blocks[0], pp2), gathered[0], gathered[1], take_positions(local_l.blocks[1], pp2),
                         take_positions(local_l.blocks[2], pp2), position_count=len(pp2))
         for b in joined.blocks[3:]:
             b.precision, b.scale = 12, 2
+        t = mark("join2_probe", t)
         op = P.HashAggregationOperator([P.BIGINT, P.DATE, P.INTEGER], [0, 1, 2], P.SINGLE, aggs, expected_groups=max(len(pp), 1000), ctx=ctx, device_output=True,
                                        input_processor=revenue)
         op.add_input(joined)
@@ -585,9 +602,21 @@ def q3_shape(args, env, exchange):
         g = op.get_group_count()
         out = op.get_output(max_rows=max(g, 1))
         op.close()
+        mark("aggregation", t)
         return g, out, len(pp), len(pp2), joined
 
     ms, (groups, out, n_surv, n_joined, joined), kern, _ = env.timed(step, args.wide_steps, args.wide_warmup)
+    stages = {}                                                   # one more pass, untimed, synchronised after every stage
+    torch.cuda.synchronize()
+    if os.environ.get("PRESTOGPU_Q3_CPROFILE") == "1":
+        import cProfile, pstats
+        prof = cProfile.Profile()
+        prof.runcall(step)
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("tottime").print_stats(22)
+    else:
+        step()
+    stage_ms, stages = stages, None
+    ctx.kernel_report(reset=True)
     # self-check with torch on the same columns (independent of the library): which orders survive, which lineitems join, what they add up to
     if world == 1:
         cust_ok = torch.zeros(n_c + 2, dtype=torch.bool, device="cuda")
@@ -610,7 +639,8 @@ def q3_shape(args, env, exchange):
                         "GROUP BY (l_orderkey, o_orderdate, o_shippriority) sum(extendedprice*(1-discount)); 1 % NULL join keys; filters, two hash "
                         "joins, composite-key aggregation", "input_rows": int(rows_in), "ms_per_step": round(ms, 3), "rows_per_s": rows_in / (ms / 1e3),
             "surviving_orders": env.total(n_surv), "joined_lineitems": env.total(n_joined), "groups": env.total(groups), "steps": args.wide_steps,
-            "kernels_ms_per_step": {k: round(v[0] / args.wide_steps, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:10]}, "selfcheck": check}
+            "kernels_ms_per_step": {k: round(v[0] / args.wide_steps, 3) for k, v in sorted(kern.items(), key=lambda kv: -kv[1][0])[:10]},
+            "stages_ms_untimed_pass": stage_ms, "selfcheck": check}
 
 
 # ------------------------------------------------------------------------------------------- BenchmarkGroupByHash grid

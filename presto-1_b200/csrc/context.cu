@@ -168,6 +168,9 @@ int32_t pg_ctx_create(int32_t device, pg_ctx** out) {
         PG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thresh));
         // L2 fetch granularity on a miss (32 / 64 / 128 bytes; the driver's default is 64).  Hash probes and gathers want one 32-byte
         // sector per random access; PRESTOGPU_L2_FETCH overrides (0 = leave the device setting alone).
+        // blocks of 64 MB and more are kept by the context when freed (context.h: DevBuf) instead of going back to the pool
+        if (const char* e = getenv("PRESTOGPU_BIG_CACHE_ENTRIES")) ctx->big_cache_entries = (size_t)std::max(0, atoi(e));
+        if (const char* e = getenv("PRESTOGPU_BIG_CACHE_GB")) ctx->big_cache_bytes = (int64_t)std::max(0, atoi(e)) << 30;
         int fetch = 0;
         if (const char* e = getenv("PRESTOGPU_L2_FETCH")) fetch = atoi(e);
         if (fetch == 32 || fetch == 64 || fetch == 128) {

@@ -54,6 +54,8 @@ struct pg_ctx {
     struct big_block { void* p; int64_t bytes; };
     std::vector<big_block> big_cache;
     int64_t big_cached_bytes = 0;
+    size_t big_cache_entries = 32;              // PRESTOGPU_BIG_CACHE_ENTRIES
+    int64_t big_cache_bytes = 64LL << 30;       // PRESTOGPU_BIG_CACHE_GB
     int guard_depth = 0;
     int out_live = 0;              // output-arena pieces handed to an OutStage that has not given them back yet
 };
@@ -145,8 +147,6 @@ static inline int32_t guard(pg_ctx* ctx, F&& f) {
 
 // Stream-ordered device buffer (cudaMallocAsync on the context stream).
 static const int64_t BIG_BLOCK = 64LL << 20;        // blocks from this size on go through the context's cache
-static const size_t BIG_CACHE_ENTRIES = 12;
-static const int64_t BIG_CACHE_BYTES = 48LL << 30;
 static inline void big_cache_drop(pg_ctx* c, size_t i) {
     cudaFreeAsync(c->big_cache[i].p, c->stream);
     c->big_cached_bytes -= c->big_cache[i].bytes;
@@ -201,10 +201,10 @@ struct DevBuf {
     }
     void release() {
         if (!p) return;
-        if (block >= BIG_BLOCK && block <= BIG_CACHE_BYTES / 2) {
+        if (block >= BIG_BLOCK && block <= ctx->big_cache_bytes / 2) {
             ctx->big_cache.push_back(pg_ctx::big_block{p, block});
             ctx->big_cached_bytes += block;
-            while (ctx->big_cache.size() > BIG_CACHE_ENTRIES || ctx->big_cached_bytes > BIG_CACHE_BYTES) big_cache_drop(ctx, 0);   // oldest first
+            while (ctx->big_cache.size() > ctx->big_cache_entries || ctx->big_cached_bytes > ctx->big_cache_bytes) big_cache_drop(ctx, 0);   // oldest first
         } else cudaFreeAsync(p, ctx->stream);
         p = nullptr; bytes = 0; block = 0;
     }

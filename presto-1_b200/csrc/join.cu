@@ -740,6 +740,10 @@ void gather_device_col(pg_ctx* ctx, const DCol& src, const int64_t* d_pos, int64
                          (uint8_t*)out.nulls);
 }
 
+void gather_device_col_into(pg_ctx* ctx, const DCol& src, const int64_t* d_pos, int64_t n, void* values, uint8_t* nulls) {
+    if (n > 0) PG_LAUNCH(ctx, j_gather_fixed_kernel, grid_for(ctx, n, 256), 256, 0, src, d_pos, n, values, nulls);
+}
+
 // ------------------------------------------------------------------ outer side (LookupOuterOperator / OuterLookupSource)
 __global__ void j_mark_visited_kernel(const int64_t* __restrict__ build_pos, int64_t n, unsigned int* visited) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1155,9 +1159,27 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
             if (type_is_var(ls->types[ch]) || out_build[k].mem != PG_MEM_DEVICE || out_build[k].capacity < n) fused = false;
             if (join_type == 1 && !out_build[k].nulls) fused = false;      // misses need a null mask
         }
+        ColImport imp;
+        if (fused) import_col(ctx, probe_keys[0], n, imp);
+        if (fused && join_type == 0 && n >= 64 * (int64_t)SCAN_TILE && !getenv("PRESTOGPU_NO_PROBE_SAMPLE")) {
+            // an INNER probe with misses has to compact its output, which the one-kernel path cannot do: look at three small samples of
+            // the page first (start, middle, end) and go straight to the compacting path when any of their rows finds no match
+            const int64_t srows = 2 * (int64_t)SCAN_TILE;
+            DevBuf scodes(ctx, srows * 4), stiles(ctx, 6 * (int64_t)sizeof(Pair64));
+            ProbeArgs sa;
+            sa.slots = ls->slots.as<JSlot>(); sa.cap = ls->cap; sa.seg_off = ls->seg_off.as<int32_t>(); sa.seg_rows = ls->seg_rows.as<int32_t>();
+            sa.n = srows; sa.join_type = 0; sa.build_empty = ls->rows == 0 ? 1 : 0; sa.L = ls->layout; sa.probe_slot = scodes.as<int32_t>();
+            const int64_t at[3] = {0, (n / 2) & ~(int64_t)31, (n - srows) & ~(int64_t)31};
+            for (int r = 0; r < 3; r++)
+                PG_LAUNCH(ctx, j_probe_count_fast_kernel, 2, SCAN_THREADS, 0, sa, (const int64_t*)imp.d.values + at[r],
+                          imp.d.nulls ? imp.d.nulls + at[r] : nullptr, stiles.as<Pair64>() + 2 * r);
+            int64_t got[12];
+            read_scalars(ctx, stiles.p, 12, got);
+            int64_t matched = 0;
+            for (int r = 0; r < 6; r++) matched += got[2 * r];
+            if (matched < 3 * srows) fused = false;
+        }
         if (fused) {
-            ColImport imp;
-            import_col(ctx, probe_keys[0], n, imp);
             const int64_t ntiles = num_tiles(n);
             ProbeArgs a;
             a.slots = ls->slots.as<JSlot>(); a.cap = ls->cap; a.seg_off = ls->seg_off.as<int32_t>(); a.seg_rows = ls->seg_rows.as<int32_t>();

@@ -415,11 +415,12 @@ static void project_build(pg_project* p, const pg_expr* in, int32_t n, int32_t f
 }
 
 void project_materialize(pg_project* p, const DCol* in, int ncols, int64_t n, const unsigned int* only_bits, const std::vector<char>* want,
-                         ProjectedPage& out) {
+                         ProjectedPage& out, const pg_col_out* direct) {
     pg_ctx* ctx = p->ctx;
     PG_CHECK_ARG(p->max_channel < ncols, "the page has %d channels, the processor reads channel %d", ncols, p->max_channel);
     const int np = (int)p->proj.size();
     out.cols.assign(np, DCol{0, 0, nullptr, nullptr, nullptr});
+    out.in_place.assign(np, 0);
     out.n = 0;
     ProjCols pc; memset(&pc, 0, sizeof(pc));
     for (int c = 0; c <= p->max_channel; c++) if (p->channel_used[c]) pc.c[c] = in[c];
@@ -476,8 +477,17 @@ void project_materialize(pg_project* p, const DCol* in, int ncols, int64_t n, co
         if (want && !(*want)[k]) continue;
         const PNode& e = p->nodes[p->proj[k]];
         DCol& oc = out.cols[k];
+        // `direct`: the caller's own device buffers; fixed-width columns are produced there instead of in a buffer of ours
+        const bool into = direct && direct[k].mem == PG_MEM_DEVICE && direct[k].values && direct[k].type == e.type && !type_is_var(e.type) &&
+                          direct[k].capacity >= m;
         if (e.op == PG_EXPR_INPUT) {
             if (identity) { oc = in[e.channel]; continue; }
+            if (into) {
+                gather_device_col_into(ctx, in[e.channel], sel.as<int64_t>(), m, direct[k].values, direct[k].nulls);
+                oc.type = e.type; oc.values = direct[k].values; oc.nulls = direct[k].nulls; oc.offsets = nullptr;
+                out.in_place[k] = 1;
+                continue;
+            }
             out.bufs.emplace_back(); out.bufs.emplace_back(); out.bufs.emplace_back();
             const size_t b = out.bufs.size();
             gather_device_col(ctx, in[e.channel], sel.as<int64_t>(), m, out.bufs[b - 3], out.bufs[b - 2], out.bufs[b - 1], oc);
@@ -488,10 +498,14 @@ void project_materialize(pg_project* p, const DCol* in, int ncols, int64_t n, co
                       err.as<unsigned int>());
             po.count = 0;
         }
-        out.bufs.emplace_back(ctx, m * (int64_t)type_width(e.type));
-        void* v = out.bufs.back().p;
-        out.bufs.emplace_back(ctx, m);
-        uint8_t* nl = (uint8_t*)out.bufs.back().p;
+        void* v; uint8_t* nl;
+        if (into && direct[k].nulls) { v = direct[k].values; nl = direct[k].nulls; out.in_place[k] = 1; }
+        else {
+            out.bufs.emplace_back(ctx, m * (int64_t)type_width(e.type));
+            v = out.bufs.back().p;
+            out.bufs.emplace_back(ctx, m);
+            nl = (uint8_t*)out.bufs.back().p;
+        }
         oc.type = e.type; oc.values = v; oc.nulls = nl; oc.offsets = nullptr;
         po.values[po.count] = v; po.nulls[po.count] = nl; po.node[po.count] = p->proj[k]; po.count++;
     }
@@ -512,7 +526,7 @@ void project_materialize(pg_project* p, const DCol* in, int ncols, int64_t n, co
             else if (q.op == PG_EXPR_CONST) nullable = q.is_null != 0;
             else if (q.op != PG_EXPR_IS_NULL) { if (q.a0 >= 0) stack.push_back(q.a0); if (q.a1 >= 0) stack.push_back(q.a1); }
         }
-        if (!nullable) out.cols[k].nulls = nullptr;
+        if (!nullable && !out.in_place[k]) out.cols[k].nulls = nullptr;      // (a caller's mask was written by the kernel: all zero)
     }
 }
 
@@ -707,11 +721,12 @@ int32_t pg_project_process(pg_project* p, const pg_col* cols, int32_t ncols, int
             in[c] = imp[c].d;
         }
         ProjectedPage page;
-        project_materialize(p, in.data(), ncols, n, nullptr, nullptr, page);
+        project_materialize(p, in.data(), ncols, n, nullptr, nullptr, page, out);
         const int64_t m = page.n;
         *n_out = m;
-        // copy the projected columns into the caller's buffers
+        // copy the projected columns into the caller's buffers (those not produced there already)
         for (size_t k = 0; k < p->proj.size() && m > 0; k++) {
+            if (page.in_place[k]) continue;
             const DCol& c = page.cols[k];
             pg_col_out& o = out[k];
             PG_CHECK_ARG(o.type == c.type && o.capacity >= m, "output column %d: type %d / capacity %lld do not fit type %d / %lld rows", (int)k, o.type,

@@ -34,6 +34,7 @@ struct ProjectedPage {
     int64_t n = 0;
     std::vector<DCol> cols;
     std::vector<DevBuf> bufs;
+    std::vector<char> in_place;     // column k was written into the caller's buffer (project_materialize's `direct`)
 };
 
 }  // namespace pg
@@ -53,9 +54,10 @@ namespace pg {
 // only_bits (optional): bitmap over the n input rows; rows whose bit is 0 are treated as rejected (used for the rows a fused
 // kernel left to the general path).  want (optional): which projections to materialise (others stay DCol{} with values null).
 void project_materialize(pg_project* p, const DCol* in, int ncols, int64_t n, const unsigned int* only_bits, const std::vector<char>* want,
-                         ProjectedPage& out);
+                         ProjectedPage& out, const pg_col_out* direct = nullptr);
 // gather rows `pos` of a device column into fresh device buffers (join.cu kernels); returns the value bytes written
 void gather_device_col(pg_ctx* ctx, const DCol& src, const int64_t* d_pos, int64_t n, DevBuf& values, DevBuf& nulls, DevBuf& offsets, DCol& out);
+void gather_device_col_into(pg_ctx* ctx, const DCol& src, const int64_t* d_pos, int64_t n, void* values, uint8_t* nulls);   // fixed width only
 
 // ---- code generation for the specialised kernels
 struct ProjCode {

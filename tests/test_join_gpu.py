@@ -311,3 +311,32 @@ def test_fused_join_step_unique_build_keys(pgpu, join_type, all_match):
         assert np.array_equal(np.asarray(g1.nulls) != 0, want_null)
         ok = ~want_null
         assert np.array_equal(np.asarray(g1.values)[ok], pay[wb[ok]])
+
+
+@pytest.mark.parametrize("misses", ["sampled", "unsampled", "none"])
+def test_fused_join_step_samples_large_pages(pgpu, misses):
+    """Large INNER probe pages are sampled (start, middle, end) before the one-kernel path is tried: misses inside a sample go straight to
+    the compacting path, misses elsewhere are caught by the kernel's own count.  Either way the output equals the oracle's."""
+    P = pgpu
+    rng = np.random.default_rng(17)
+    n, m = 50_000, 300_000
+    bkeys = np.arange(1, n + 1, dtype=np.int64) * 3
+    pay = rng.integers(-10**12, 10**12, n).astype(np.int64)
+    types = [P.BIGINT, P.BIGINT]
+    blocks = [P.Block.long_array(bkeys), P.Block.long_array(pay)]
+    idx = P.PagesIndex(types, [0])
+    orc = O.OracleJoin(types, [0])
+    idx.add_page([b.to_device() for b in blocks])
+    orc.add_page(blocks)
+    ls = idx.create_lookup_source()
+    orc.build()
+    pkeys = bkeys[rng.integers(0, n, m)]
+    if misses == "sampled":
+        pkeys[::11] += 1
+    elif misses == "unsampled":
+        pkeys[20_000:30_000:3] += 1
+    pk = P.Block.long_array(pkeys)
+    wp, wb = orc.probe([pk], None, 0)
+    fp, fout = ls.join_and_append([pk.to_device()], [1], None, 0)
+    assert np.array_equal(fp.cpu().numpy(), wp)
+    assert np.array_equal(np.asarray(fout[0].to_host().values), pay[wb])

@@ -12,7 +12,7 @@ from .groupby import GroupByHash, GroupByIdBlock
 from .accumulators import GroupedAccumulator, final_type, intermediate_types
 from .join import LookupSource, PagesIndex
 from .operators import (FINAL, INTERMEDIATE, PARTIAL, SINGLE, AggregatorFactory, HashAggregationOperator, HashBuilderOperator,
-                        HashSemiJoinOperator, LookupJoinOperator, LookupOuterOperator, MarkDistinctOperator, SetBuilderOperator, take_positions)
+                        DistinctLimitOperator, HashSemiJoinOperator, LookupJoinOperator, LookupOuterOperator, MarkDistinctOperator, SetBuilderOperator, take_positions)
 JOIN_INNER, JOIN_PROBE_OUTER = native.JOIN_INNER, native.JOIN_PROBE_OUTER
 from .exchange import DevicePartitioner, HashPartitionExchange
 from .plans import PartialFinalAggregation, PartitionedAggregation, PartitionedHashJoin, final_aggregators

@@ -340,6 +340,48 @@ class MarkDistinctOperator:
         return self._finishing and self._out is None
 
 
+class DistinctLimitOperator:
+    """OP/DistinctLimitOperator.java:115-220: passes through the first row of every new distinct combination of the distinct channels
+    (plus the precomputed hash channel) until `limit` rows have been produced.  The first-row test is the one MarkDistinct uses
+    (group id == nextDistinctId over the page's GroupByIdBlock; pg_groupby_mark_distinct)."""
+
+    def __init__(self, distinct_types, distinct_channels, limit, hash_channel=None, ctx=None):
+        from .groupby import GroupByHash
+        if limit < 0:
+            raise ValueError("limit must be at least zero")                                   # DistinctLimitOperator.java:120
+        self.channels, self.hash_channel = list(distinct_channels), hash_channel
+        self.output_channels = self.channels + ([hash_channel] if hash_channel is not None else [])
+        self.hash = GroupByHash(list(distinct_types), min(limit, 10_000), has_hash_channel=hash_channel is not None, ctx=ctx)
+        self.remaining_limit = limit
+        self._finishing, self._page, self._marks = False, None, None
+
+    def needs_input(self):
+        return not self._finishing and self.remaining_limit > 0 and self._page is None
+
+    def add_input(self, page):
+        assert self.needs_input()
+        blocks = page.blocks if isinstance(page, Page) else list(page)
+        keys = [blocks[c] for c in self.channels] + ([blocks[self.hash_channel]] if self.hash_channel is not None else [])
+        self._marks = self.hash.mark_distinct(keys)
+        self._page = blocks
+
+    def get_output(self):
+        if self._page is None:
+            return None
+        positions = np.flatnonzero(self._marks)[:self.remaining_limit]                         # stop at the row that exhausts the limit
+        self.remaining_limit -= len(positions)
+        blocks, self._page, self._marks = self._page, None, None
+        if len(positions) == 0:
+            return None
+        return Page(*[take_positions(blocks[c], positions) for c in self.output_channels], position_count=len(positions))
+
+    def finish(self):
+        self._finishing = True
+
+    def is_finished(self):
+        return self._page is None and (self._finishing or self.remaining_limit == 0)
+
+
 class SetBuilderOperator:
     """OP/SetBuilderOperator.java:123-170: collects the build side's join channel into a ChannelSet (a GroupByHash plus 'contains NULL')."""
 

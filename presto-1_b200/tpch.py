@@ -4,6 +4,8 @@ It follows dbgen's value domains for the columns the configs touch (SURVEY.md §
 order, quantity 1-50, retail-price formula, discount 0.00-0.10, tax 0.00-0.08, ship/receipt date offsets, returnflag /
 linestatus derived from the dates.  It is NOT bit-identical to io.trino.tpch:tpch (an un-vendored dependency of the
 reference); the GPU path and the oracle always consume the same generated buffers, so parity does not depend on that.
+What it is held to instead: the column statistics the reference ships for the TPC-H connector (row counts, min / max, distinct
+counts per column at SF 0.01 and SF 1; tests/golden/tpch_stats.json, checked by tests/test_tpch_stats_cpu.py).
 Money columns are unscaled integer cents (short decimal); derived products are long decimals (Int128, sign-magnitude).
 """
 import numpy as np
@@ -20,8 +22,10 @@ LINES_PER_ORDER_MEAN = 4
 
 
 def order_key(i):
-    """dbgen sparse keys: 8 used out of every 32."""
-    return (i // 8) * 32 + (i % 8) + 1
+    """dbgen's sparse order keys (mk_sparse): the 1-based order number keeps its low 3 bits and the rest moves up by two bits, so 8 of
+    every 32 values are used and order number 1 500 000 x SF gets key 6 000 000 x SF (the o_orderkey max of the reference's statistics
+    files).  `i` is the 0-based order index."""
+    return (((i + 1) >> 3) << 5) | ((i + 1) & 7)
 
 
 _M64 = (1 << 64) - 1
@@ -57,6 +61,7 @@ def orders(sf, seed=42, device="cuda", rows=None):
     idx = torch.arange(n, device=device, dtype=torch.int64)
     okey = order_key(idx)
     custkey = _randint(seed, 1, idx, 1, max(2, int(150_000 * sf)) + 1)
+    custkey = torch.where(custkey % 3 == 0, custkey - 1, custkey)             # dbgen: a third of the customers never order (custkey % 3 != 0)
     totalprice = _randint(seed, 2, idx, 85_771, 55_528_517).double() * 0.01   # a product, not a quotient: torch CUDA turns x / c into x * (1 / c), the CPU build does not
     orderdate = _randint(seed, 3, idx, STARTDATE, ENDDATE_ORDER + 1).to(torch.int32)
     shipprio = torch.zeros(n, device=device, dtype=torch.int32)
@@ -94,7 +99,7 @@ def shuffle_order(n, seed, device):
 
 
 def lineitem(sf, seed=42, device="cuda", orders_count=None, need=("q1",), shuffle=False):
-    """lineitem columns.  need: subset of {"q1", "keys", "double", "raw"} selecting which columns are materialised.
+    """lineitem columns.  need: subset of {"q1", "keys", "double", "raw", "stats"} selecting which columns are materialised.
     "q1" adds the derived long-decimal columns and the filter mask (the materialised Q1 page); "raw" only the raw columns
     (shipdate, discount, tax, returnflag, linestatus) a fused filter + projection reads."""
     n_orders = int(1_500_000 * sf) if orders_count is None else int(orders_count)
@@ -111,10 +116,17 @@ def lineitem(sf, seed=42, device="cuda", orders_count=None, need=("q1",), shuffl
         del perm
     if "keys" in need or "join" in need:
         out["orderkey"] = order_key(order_idx)
+    if "stats" in need:                                          # l_linenumber: 1.. within the order (needs the unshuffled row identity)
+        first = torch.cumsum(_randint(seed + 1, 1, oidx, 1, 8), 0)
+        first = torch.cat([first.new_zeros(1), first[:-1]])
+        out["linenumber"] = (idx - first[order_idx] + 1).to(torch.int32)
+        del first
     s = seed + 1
     qty = _randint(s, 2, idx, 1, 51)
     partkey = _randint(s, 3, idx, 1, max(2, int(200_000 * sf)) + 1)
     retail = 90_000 + (torch.div(partkey, 10, rounding_mode="floor") % 20_001) + 100 * (partkey % 1000)
+    if "stats" in need:
+        out["partkey"] = partkey
     out["quantity"] = qty * 100                                  # decimal(12,2)
     out["extendedprice"] = qty * retail                          # decimal(12,2) cents
     del partkey, retail, qty

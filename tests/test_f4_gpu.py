@@ -158,3 +158,66 @@ def test_lookup_outer_emits_exactly_the_unvisited_build_rows(pgpu, dups):
         assert np.array_equal(np.asarray(out.blocks[3].to_host().values), pay[pos])
         rows += k
     assert rows == len(want) and op.is_finished()
+
+
+def _sequence_page(P, length, start, hash_enabled):
+    v = P.Block.long_array(np.arange(start, start + length, dtype=np.int64))
+    return P.Page(*([v] + ([P.Block.long_array(O.hash_rows([v]))] if hash_enabled else [])))
+
+
+@pytest.mark.parametrize("hash_enabled", [False, True])
+@pytest.mark.parametrize("pages,limit,want", [(((3, 1), (5, 2)), 5, [1, 2, 3, 4, 5]),        # testDistinctLimit
+                                              (((3, 1), (3, 2)), 3, [1, 2, 3]),              # testDistinctLimitWithPageAlignment
+                                              (((3, 1), (3, 2)), 5, [1, 2, 3, 4])])          # testDistinctLimitValuesLessThanLimit
+def test_distinct_limit_reference_rows(pgpu, hash_enabled, pages, limit, want):
+    """TestDistinctLimitOperator.java:92-156, driven the way assertOperatorEquals drives an operator."""
+    P = pgpu
+    op = P.DistinctLimitOperator([P.BIGINT], [0], limit, hash_channel=1 if hash_enabled else None)
+    got = []
+    for length, start in pages:
+        if not op.needs_input():
+            break
+        op.add_input(_sequence_page(P, length, start, hash_enabled))
+        out = op.get_output()
+        if out is not None:
+            assert len(out.blocks) == (2 if hash_enabled else 1)           # the hash channel is passed through
+            got += out.blocks[0].to_host().values.tolist()
+    op.finish()
+    assert op.is_finished() and op.get_output() is None
+    assert got == want
+
+
+def test_distinct_limit_random_pages_match_oracle(pgpu):
+    """First row of every new group in page order, cut at the limit, with nulls and repeats; checked against the oracle's group ids."""
+    P = pgpu
+    rng = np.random.default_rng(5)
+    limit = 7_500
+    op = P.DistinctLimitOperator([P.BIGINT, P.VARCHAR], [1, 0], limit)
+    ogb = O.OracleGroupBy([P.BIGINT, P.VARCHAR], 100)
+    next_id, produced = 0, 0
+    while op.needs_input():
+        n = int(rng.integers(1, 4000))
+        strings = ["s%d" % x for x in rng.integers(0, 60, n)]
+        s = P.Block.variable_width(strings)
+        b = P.Block.long_array(rng.integers(0, 400, n).astype(np.int64), (rng.random(n) < 0.03).astype(np.uint8))
+        ids = ogb.get_group_ids([b, s])
+        want = []
+        for i in range(n):
+            if ids[i] == next_id and produced + len(want) < limit:
+                want.append(i)
+                next_id += 1
+        op.add_input(P.Page(s, b))
+        out = op.get_output()
+        produced += len(want)
+        if not want:
+            assert out is None
+            continue
+        hb = b.to_host()
+        gb, gs = out.blocks[0].to_host(), out.blocks[1].to_host()
+        assert np.array_equal(np.asarray(gb.nulls) != 0, np.asarray(hb.nulls)[want] != 0)
+        assert np.array_equal(gb.values[np.asarray(gb.nulls) == 0], hb.values[want][np.asarray(hb.nulls)[want] == 0])
+        got_strings = [bytes(gs.values[gs.offsets[i]:gs.offsets[i + 1]]).decode() for i in range(gs.n)]
+        assert got_strings == [strings[i] for i in want]
+        if produced > 20_000:
+            break
+    assert produced == limit and op.is_finished()

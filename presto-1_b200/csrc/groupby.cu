@@ -122,44 +122,114 @@ PG_D int64_t gb_find_or_claim(const InsertArgs& a, const KeyCols& kc, const KeyL
     return p;
 }
 
+// K1.  Four rows per thread, and every probe round is warp-uniform: all lanes load the slot words of their probing rows first (four
+// independent loads in flight per lane), then compare / claim, and the warp leaves the loop together (__any_sync) - lanes that leave a
+// data-dependent loop at different iterations are not brought back together by the hardware, which left the one-row-per-lane loop
+// running at a few active lanes per instruction on long probe sequences.
 template <bool BIGINT>
 __global__ void __launch_bounds__(GB_THREADS) gb_insert_kernel(InsertArgs a, KeyCols kc, KeyLayout L, DCol hash_col, int has_hash) {
     __shared__ int s_inserted;
     __shared__ int s_stop;
     if (threadIdx.x == 0) { s_inserted = 0; s_stop = 0; }
     __syncthreads();
+    constexpr int R = 4;
     const int lane = threadIdx.x & 31;
-    int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * R;
     int iter = 0;
-    for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < a.n; base += stride, iter++) {
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x * R; base < a.n; base += stride, iter++) {
         // warp-uniform stop test (no block barrier inside the loop: warps of a block run independently)
         int stop = 0;
         if (lane == 0) {
             stop = *((volatile int*)&s_stop);
-            if (!stop && (iter & 7) == 7) stop = *((volatile int32_t*)&a.meta->abort);
+            if (!stop && (iter & 1) == 1) stop = *((volatile int32_t*)&a.meta->abort);
         }
         stop = __shfl_sync(0xffffffffu, stop, 0);
         if (stop) break;
-        int64_t row = base + threadIdx.x;
-        bool valid = row < a.n;
-        bool claimed = false;
-        bool pending = false;
-        int64_t s = -1;
-        if (valid) {
-            s = gb_find_or_claim<BIGINT>(a, kc, L, hash_col, has_hash, row, claimed);
-            pending = a.slots[s].gid < 0;   // group ids are only assigned between launches: the cached value is current
-            a.row_slot[row] = (int32_t)s;
+        int64_t p[R];
+        unsigned long long want[R];      // BIGINT: the key; otherwise the claim word {tag, PENDING | row}
+        bool probing[R], claimed[R];
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const int64_t row = base + (int64_t)k * blockDim.x + threadIdx.x;
+            probing[k] = false; claimed[k] = false; p[k] = -1; want[k] = 0;
+            if (row >= a.n) continue;
+            if (BIGINT) {
+                const DCol& c = kc.c[0];
+                if (dcol_is_null(c, row)) { p[k] = a.cap + 1; continue; }
+                want[k] = (unsigned long long)((const int64_t*)c.values)[row];
+                if (want[k] == EMPTY_KEY) { p[k] = a.cap; continue; }
+                p[k] = (int64_t)(fmix64(want[k]) & (uint64_t)a.mask);
+            } else {
+                const int64_t raw = has_hash ? ((const int64_t*)hash_col.values)[row] : keys_row_hash(kc, L.nkeys, row);
+                const uint64_t f = fmix64((uint64_t)raw);
+                want[k] = ((unsigned long long)(uint32_t)(f >> 32) << 32) | (unsigned long long)(REF_PENDING | (uint32_t)row);
+                p[k] = (int64_t)(f & (uint64_t)a.mask);
+            }
+            probing[k] = true;
         }
-        // rows of still-unnumbered slots compete for first_row; lanes of a warp that share a slot send one atomic
-        unsigned pend = __ballot_sync(0xffffffffu, pending);
-        if (pend) {
-            unsigned peers = __match_any_sync(0xffffffffu, pending ? s : (int64_t)(-1 - lane));
-            if (pending && (__ffs(peers) - 1) == lane) atomicMin(&a.slots[s].first_row, (int32_t)row);
+        while (true) {
+            // Slot words are read through L1 (plain loads): a key / claim never changes once written, so a cached non-empty word is
+            // always right; a stale cached EMPTY is resolved by the CAS, which returns the live value.
+            unsigned long long w[R];
+#pragma unroll
+            for (int k = 0; k < R; k++) if (probing[k]) w[k] = a.slots[p[k]].word;
+            bool more = false;
+#pragma unroll
+            for (int k = 0; k < R; k++) {
+                if (!probing[k]) continue;
+                if (BIGINT) {
+                    if (w[k] == want[k]) probing[k] = false;
+                    else {
+                        if (w[k] == EMPTY_KEY) {
+                            const unsigned long long old = atomicCAS(&a.slots[p[k]].word, EMPTY_KEY, want[k]);
+                            if (old == EMPTY_KEY) { claimed[k] = true; probing[k] = false; }
+                            else if (old == want[k]) probing[k] = false;
+                        }
+                        if (probing[k]) p[k] = (p[k] + 1) & a.mask;
+                    }
+                } else {
+                    if (w[k] == EMPTY_WORD) {
+                        const unsigned long long old = atomicCAS(&a.slots[p[k]].word, EMPTY_WORD, want[k]);
+                        if (old == EMPTY_WORD) { claimed[k] = true; probing[k] = false; }
+                        else w[k] = old;
+                    }
+                    if (probing[k] && (uint32_t)(w[k] >> 32) == (uint32_t)(want[k] >> 32)) {
+                        const int64_t row = base + (int64_t)k * blockDim.x + threadIdx.x;
+                        const uint32_t ref = (uint32_t)w[k];
+                        const bool eq = (ref & REF_PENDING) ? keys_equal_rows(kc, L, row, (int64_t)(ref & ~REF_PENDING))
+                                                            : keys_equal_store(kc, L, row, a.key_rows, a.arena, (int64_t)ref);
+                        if (eq) probing[k] = false;
+                    }
+                    if (probing[k]) p[k] = (p[k] + 1) & a.mask;
+                }
+                more |= probing[k];
+            }
+            if (!__any_sync(0xffffffffu, more)) break;
         }
-        unsigned b = __ballot_sync(0xffffffffu, claimed);
-        if (lane == 0 && b) {
-            int before = atomicAdd(&s_inserted, __popc(b));
-            if ((int64_t)before + __popc(b) >= a.quota) *((volatile int*)&s_stop) = 1;
+        int nclaimed = 0;
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const int64_t row = base + (int64_t)k * blockDim.x + threadIdx.x;
+            const bool valid = row < a.n;
+            const int64_t s = p[k];
+            bool pending = false;
+            if (valid) {
+                pending = a.slots[s].gid < 0;   // group ids are only assigned between launches: the cached value is current
+                a.row_slot[row] = (int32_t)s;
+            }
+            // rows of still-unnumbered slots compete for first_row; lanes of a warp that share a slot send one atomic
+            const unsigned pend = __ballot_sync(0xffffffffu, pending);
+            if (pend) {
+                const unsigned peers = __match_any_sync(0xffffffffu, pending ? s : (int64_t)(-1 - lane));
+                if (pending && (__ffs(peers) - 1) == lane) atomicMin(&a.slots[s].first_row, (int32_t)row);
+            }
+            nclaimed += claimed[k] ? 1 : 0;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) nclaimed += __shfl_down_sync(0xffffffffu, nclaimed, d);
+        if (lane == 0 && nclaimed) {
+            const int before = atomicAdd(&s_inserted, nclaimed);
+            if ((int64_t)before + nclaimed >= a.quota) *((volatile int*)&s_stop) = 1;
         }
     }
     __syncthreads();
@@ -653,14 +723,14 @@ static void process_chunk(pg_groupby* gb, const KeyCols& kc, const DCol* hash_co
     }
 
     // ---- K1 with quota / rebuild loop
-    const int grid = grid_for(ctx, n, GB_THREADS);
+    const int grid = grid_for(ctx, n, GB_THREADS, 4);       // (gb_insert_kernel: four rows per thread)
     bool inserted_pending = false, arena_pending = false;
     while (true) {
         int64_t room = gb->max_fill - gb->occupied;
         int64_t quota;
         if (room >= n) quota = INT64_MAX / 2;
         else {
-            quota = room / grid - GB_THREADS;
+            quota = room / grid - 4 * GB_THREADS;       // a block may overshoot by the rows its warps had in flight when it stopped
             if (quota < 32) { rebuild_table(gb, gb->cap * 2); continue; }
         }
         memset_async(ctx, &meta->inserted, 0, 8);

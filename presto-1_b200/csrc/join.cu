@@ -1039,7 +1039,7 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
         a.probe_slot = nullptr; a.n = n; a.join_type = join_type; a.build_empty = ls->rows == 0 ? 1 : 0;
         a.L = ls->layout;
         const bool fast_table = ls->bigint_fast && (ls->layout.range || (ls->cap < (1LL << 30) && !getenv("PRESTOGPU_NO_FAST_PROBE")));
-        if (fast_table && !ls->has_dups && capacity >= n && out_probe_idx && out_build_pos && !getenv("PRESTOGPU_NO_FUSED_PROBE")) {
+        if (fast_table && !ls->has_dups && capacity >= n && out_probe_idx && out_build_pos && !ls->sparse_probe_hint && !getenv("PRESTOGPU_NO_FUSED_PROBE")) {
             // unique build keys and room for one output row per probe row: resolve, and write the output as if every row emitted
             // scratch belongs to the call, not to the lookup source: several probe operators share one source (LookupJoinOperatorFactory)
             DevBuf probe_slot(ctx, n * 4), tile_sums(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64)), total_buf(ctx, 64);
@@ -1160,6 +1160,7 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
             if (join_type == 1 && !out_build[k].nulls) fused = false;      // misses need a null mask
         }
         ColImport imp;
+        bool sparse_hint = false;
         if (fused) import_col(ctx, probe_keys[0], n, imp);
         if (fused && join_type == 0 && n >= 64 * (int64_t)SCAN_TILE && !getenv("PRESTOGPU_NO_PROBE_SAMPLE")) {
             // an INNER probe with misses has to compact its output, which the one-kernel path cannot do: look at three small samples of
@@ -1178,6 +1179,8 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
             int64_t matched = 0;
             for (int r = 0; r < 6; r++) matched += got[2 * r];
             if (matched < 3 * srows) fused = false;
+            // with many misses even the two-step path should not write an output row per probe row first: count, then emit
+            sparse_hint = matched < 3 * srows / 4 * 3;
         }
         if (fused) {
             const int64_t ntiles = num_tiles(n);
@@ -1204,7 +1207,9 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
             // some INNER rows found no match: the compacting path below redoes the page
         }
         DevBuf tp(ctx, std::max<int64_t>(capacity, 1) * 4), tb(ctx, std::max<int64_t>(capacity, 1) * 8);
+        ls->sparse_probe_hint = sparse_hint;         // (a context is driven by one thread: the hint cannot leak into another call)
         int32_t rc = pg_lookup_probe(ls, probe_keys, nkeys, hash_col, n, join_type, tp.as<int32_t>(), tb.as<int64_t>(), PG_MEM_DEVICE, capacity, n_out);
+        ls->sparse_probe_hint = false;
         if (rc != PG_OK) { const std::string msg = ctx->err; fail(rc, "%s", msg.c_str()); }
         if (*n_out == 0) return;
         if (out_probe_idx)

@@ -266,6 +266,68 @@ __global__ void __launch_bounds__(SCAN_THREADS) proj_positions_kernel(const uint
     for (int j = 0; j < SCAN_ITEMS; j++) if (f[j]) sel[dst++] = first + j;
 }
 
+// pass 2 for a filter whose projections only pass fixed-width channels through (the usual ScanFilterAndProject shape): the selected rows
+// of every such channel move straight to their place in the output, no list of row numbers in between
+struct CompactTab {
+    const void* src[PROJ_MAX_OUTPUTS]; const uint8_t* src_nulls[PROJ_MAX_OUTPUTS];
+    void* dst[PROJ_MAX_OUTPUTS]; uint8_t* dst_nulls[PROJ_MAX_OUTPUTS];
+    int32_t width[PROJ_MAX_OUTPUTS]; int32_t count;
+};
+// One warp owns 32 * SCAN_ITEMS consecutive rows and walks them 32 at a time, so that loads are coalesced and the selected rows of each
+// group of 32 land next to each other (ballot + popc give the place; page order is kept).
+template <typename T>
+PG_D void compact_column(const T* __restrict__ src, T* __restrict__ dst, const unsigned (&b)[SCAN_ITEMS], int64_t wbase, int64_t d, int lane) {
+    // the loads of a batch are issued before its first store: several requests in flight per lane instead of one
+    constexpr int BATCH = sizeof(T) > 8 ? 4 : SCAN_ITEMS;
+    const T* s0 = src + wbase + lane;
+    T* d0 = dst + d;
+#pragma unroll
+    for (int j0 = 0; j0 < SCAN_ITEMS; j0 += BATCH) {
+        T v[BATCH];
+#pragma unroll
+        for (int j = 0; j < BATCH; j++) if ((b[j0 + j] >> lane) & 1u) v[j] = s0[(j0 + j) * 32];
+#pragma unroll
+        for (int j = 0; j < BATCH; j++) {
+            if ((b[j0 + j] >> lane) & 1u) d0[__popc(b[j0 + j] & ((1u << lane) - 1u))] = v[j];
+            d0 += __popc(b[j0 + j]);
+        }
+    }
+}
+template <typename T>      // one launch moves the channels of one width (CompactTab.width is all sizeof(T))
+__global__ void __launch_bounds__(SCAN_THREADS, 3) proj_compact_kernel(const uint8_t* __restrict__ flags, int64_t n, const Pair64* __restrict__ tile_prefix,
+                                                                       CompactTab t) {
+    __shared__ int s_warp[SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t wbase = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)warp * (32 * SCAN_ITEMS);
+    unsigned b[SCAN_ITEMS];
+    int mine = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        const int64_t row = wbase + j * 32 + lane;
+        b[j] = __ballot_sync(0xffffffffu, row < n && flags[row] != 0);
+        mine += __popc(b[j]);
+    }
+    if (lane == 0) s_warp[warp] = mine;
+    __syncthreads();
+    int64_t d = tile_prefix[blockIdx.x].a;
+    for (int w = 0; w < warp; w++) d += s_warp[w];
+    if (mine == 0) return;
+    for (int c = 0; c < t.count; c++) {
+        compact_column((const T*)t.src[c], (T*)t.dst[c], b, wbase, d, lane);
+        if (t.dst_nulls[c]) {
+            if (t.src_nulls[c]) compact_column(t.src_nulls[c], t.dst_nulls[c], b, wbase, d, lane);
+            else {
+                int64_t q = d;
+#pragma unroll
+                for (int j = 0; j < SCAN_ITEMS; j++) {
+                    if ((b[j] >> lane) & 1u) t.dst_nulls[c][q + __popc(b[j] & ((1u << lane) - 1u))] = 0;
+                    q += __popc(b[j]);
+                }
+            }
+        }
+    }
+}
+
 struct ProjOut { void* values[PROJ_MAX_OUTPUTS]; uint8_t* nulls[PROJ_MAX_OUTPUTS]; int32_t node[PROJ_MAX_OUTPUTS]; int32_t count; };
 
 // computed projections over the selected rows (sel == nullptr: every row)
@@ -467,6 +529,51 @@ void project_materialize(pg_project* p, const DCol* in, int ncols, int64_t n, co
         int64_t tot[2];
         read_scalars(ctx, tiles.as<Pair64>() + ntiles, 2, tot);
         m = tot[0];
+        bool compactable = m > 0 && m < n && !getenv("PRESTOGPU_PROJECT_NO_COMPACT");
+        for (int k = 0; k < np && compactable; k++) {
+            if (want && !(*want)[k]) continue;
+            const PNode& e = p->nodes[p->proj[k]];
+            if (e.op != PG_EXPR_INPUT || type_is_var(e.type)) compactable = false;
+        }
+        if (compactable) {
+            out.n = m;
+            for (int width : {1, 4, 8, 16}) {
+            CompactTab ct; memset(&ct, 0, sizeof(ct));
+            auto flush = [&] {
+                if (ct.count > 0) {
+                    if (width == 1) PG_LAUNCH(ctx, proj_compact_kernel<uint8_t>, (int)ntiles, SCAN_THREADS, 0, flags.as<uint8_t>(), n, tiles.as<Pair64>(), ct);
+                    else if (width == 4) PG_LAUNCH(ctx, proj_compact_kernel<int32_t>, (int)ntiles, SCAN_THREADS, 0, flags.as<uint8_t>(), n, tiles.as<Pair64>(), ct);
+                    else if (width == 8) PG_LAUNCH(ctx, proj_compact_kernel<int64_t>, (int)ntiles, SCAN_THREADS, 0, flags.as<uint8_t>(), n, tiles.as<Pair64>(), ct);
+                    else PG_LAUNCH(ctx, proj_compact_kernel<int4>, (int)ntiles, SCAN_THREADS, 0, flags.as<uint8_t>(), n, tiles.as<Pair64>(), ct);
+                }
+                ct.count = 0;
+            };
+            for (int k = 0; k < np; k++) {
+                if (want && !(*want)[k]) continue;
+                const PNode& e = p->nodes[p->proj[k]];
+                if (type_width(e.type) != width) continue;
+                const DCol& src = in[e.channel];
+                DCol& oc = out.cols[k];
+                const bool into = direct && direct[k].mem == PG_MEM_DEVICE && direct[k].values && direct[k].type == e.type && direct[k].capacity >= m;
+                oc.type = e.type; oc.pad = 0; oc.offsets = nullptr;
+                if (into) { oc.values = direct[k].values; oc.nulls = direct[k].nulls; out.in_place[k] = 1; }
+                else {
+                    out.bufs.emplace_back(ctx, m * (int64_t)type_width(e.type));
+                    oc.values = out.bufs.back().p;
+                    oc.nulls = nullptr;
+                    if (src.nulls) { out.bufs.emplace_back(ctx, m); oc.nulls = (uint8_t*)out.bufs.back().p; }
+                }
+                if (ct.count == PROJ_MAX_OUTPUTS) flush();
+                const int c = ct.count++;
+                ct.src[c] = src.values; ct.src_nulls[c] = src.nulls; ct.dst[c] = (void*)oc.values; ct.dst_nulls[c] = (uint8_t*)oc.nulls; ct.width[c] = type_width(e.type);
+            }
+            flush();
+            }
+            int64_t e = 0;
+            read_scalars(ctx, err.p, 1, &e);
+            if (e & 1) fail(PG_E_NUMERIC_OVERFLOW, "Decimal overflow / numeric value out of range in a filter or projection expression");
+            return;
+        }
         sel.alloc(ctx, (m > 0 ? m : 1) * 8);
         if (m > 0 && m < n) PG_LAUNCH(ctx, proj_positions_kernel, (int)ntiles, SCAN_THREADS, 0, flags.as<uint8_t>(), n, tiles.as<Pair64>(), sel.as<int64_t>());
     }

@@ -76,6 +76,8 @@ def processors():
         ("bigint_double_arith", None, [big + big, big - E.bigint(7), big * E.bigint(3), dbl * dbl, dbl + E.double(1.5), i32 + i32, i32 * E.integer(2)]),
         ("casts_and_hash", big.ne(E.bigint(0)), [i32.cast(P.BIGINT), big.cast(P.DOUBLE), i32.cast(P.LONG_DECIMAL, 20, 3), price.cast(P.LONG_DECIMAL, 20, 6),
                                                E.hash_of(big, date, seg), E.hash_of(wide, dbl, flag, price)]),
+        ("filter_passthrough_fixed", date < E.date(9500), [big, date, price, wide, dbl, i32, flag, big]),    # one compaction kernel, widths 1 / 4 / 8 / 16
+        ("filter_passthrough_simple_cmp", i32 >= E.integer(0), [flag, wide]),
         ("reject_all", date > E.date(20000), [big, seg]),
         ("null_const", E.const(None, P.BOOLEAN) | (date >= E.date(0)), [big + E.const(None, P.BIGINT), seg]),
     ]

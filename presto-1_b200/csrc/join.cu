@@ -562,15 +562,34 @@ struct GatherTab {
     uint8_t* out_nulls[JG_MAX_COLS];
     int32_t width[JG_MAX_COLS];
 };
-PG_D void gather_row(const GatherTab& g, int64_t row, int cd) {
-    for (int c = 0; c < g.n; c++) {
-        const bool isnull = cd < 0 || (g.src_nulls[c] && g.src_nulls[c][cd]);
-        if (g.out_nulls[c]) g.out_nulls[c][row] = isnull ? 1 : 0;
-        switch (g.width[c]) {
-            case 1: ((uint8_t*)g.out[c])[row] = isnull ? (uint8_t)0 : ((const uint8_t*)g.src[c])[cd]; break;
-            case 4: ((int32_t*)g.out[c])[row] = isnull ? 0 : ((const int32_t*)g.src[c])[cd]; break;
-            case 8: ((int64_t*)g.out[c])[row] = isnull ? 0 : __ldg((const int64_t*)g.src[c] + cd); break;
-            default: ((int4*)g.out[c])[row] = isnull ? make_int4(0, 0, 0, 0) : __ldg((const int4*)g.src[c] + cd);
+// LookupSource.appendTo for G rows of one lane, channel by channel: the (random) loads of all G rows are issued before the first store, so a lane
+// has G requests in flight instead of one - what a shuffled probe side is bound by
+template <int G, typename T>
+PG_D void gather_rows_col(const T* __restrict__ src, const uint8_t* __restrict__ src_nulls, T* __restrict__ out, uint8_t* __restrict__ out_nulls,
+                          const int64_t (&row)[G], const int (&cd)[G], unsigned inr, T zero) {
+    T v[G];
+    uint8_t nl[G];
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        const bool hit = ((inr >> g) & 1u) && cd[g] >= 0;
+        v[g] = hit ? __ldg(src + cd[g]) : zero;
+        nl[g] = hit ? (src_nulls ? __ldg(src_nulls + cd[g]) : (uint8_t)0) : (uint8_t)1;
+    }
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        if (!((inr >> g) & 1u)) continue;
+        out[row[g]] = nl[g] ? zero : v[g];
+        if (out_nulls) out_nulls[row[g]] = nl[g] ? 1 : 0;
+    }
+}
+template <int G>
+PG_D void gather_rows(const GatherTab& t, const int64_t (&row)[G], const int (&cd)[G], unsigned inr) {
+    for (int c = 0; c < t.n; c++) {
+        switch (t.width[c]) {
+            case 1: gather_rows_col<G>((const uint8_t*)t.src[c], t.src_nulls[c], (uint8_t*)t.out[c], t.out_nulls[c], row, cd, inr, (uint8_t)0); break;
+            case 4: gather_rows_col<G>((const int32_t*)t.src[c], t.src_nulls[c], (int32_t*)t.out[c], t.out_nulls[c], row, cd, inr, (int32_t)0); break;
+            case 8: gather_rows_col<G>((const int64_t*)t.src[c], t.src_nulls[c], (int64_t*)t.out[c], t.out_nulls[c], row, cd, inr, (int64_t)0); break;
+            default: gather_rows_col<G>((const int4*)t.src[c], t.src_nulls[c], (int4*)t.out[c], t.out_nulls[c], row, cd, inr, make_int4(0, 0, 0, 0));
         }
     }
 }
@@ -626,19 +645,23 @@ __global__ void __launch_bounds__(SCAN_THREADS) j_probe_dense_kernel(ProbeArgs a
             }
             if (!__any_sync(0xffffffffu, probing != 0)) break;
         }
+        int64_t rows[G];
+        int cds[G];
 #pragma unroll
         for (int g = 0; g < G; g++) {
             int cd = __shfl_sync(0xffffffffu, code[g], leader[g]);
             if (!((validm >> g) & 1u)) cd = -1;
+            cds[g] = cd;
+            rows[g] = tile_base + (int64_t)(j0 + g) * SCAN_THREADS + threadIdx.x;
             if ((inr >> g) & 1u) {
-                const int64_t row = tile_base + (int64_t)(j0 + g) * SCAN_THREADS + threadIdx.x;
+                const int64_t row = rows[g];
                 if (!GATHER) a.probe_slot[row] = cd;        // (the fused form never compacts: a page with misses is redone by the two-step path)
                 out_probe[row] = (int32_t)row;
                 if (out_build) out_build[row] = cd;
-                if (GATHER) gather_row(gt, row, cd);
                 if (cd >= 0 || a.join_type == 1) emitted++;    // PROBE_OUTER: appendNullForBuild (LookupJoinOperator.java:354-361)
             }
         }
+        if (GATHER) gather_rows<G>(gt, rows, cds, inr);
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) emitted += __shfl_down_sync(0xffffffffu, emitted, d);

@@ -1025,6 +1025,9 @@ int32_t pg_lookup_stats(pg_lookup* ls, int64_t* rows, int64_t* hash_size, int64_
     return PG_OK;
 }
 
+// set by pg_lookup_join_page around its internal pg_lookup_probe call: the page's samples had many misses (count, then emit)
+static thread_local bool t_sparse_probe_hint = false;
+
 int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, const pg_col* hash_col, int64_t n, int32_t join_type,
                         int32_t* out_probe_idx, int64_t* out_build_pos, int32_t out_mem, int64_t capacity, int64_t* n_out) {
     if (!ls) return PG_E_INVALID_ARGUMENT;
@@ -1062,7 +1065,7 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
         a.probe_slot = nullptr; a.n = n; a.join_type = join_type; a.build_empty = ls->rows == 0 ? 1 : 0;
         a.L = ls->layout;
         const bool fast_table = ls->bigint_fast && (ls->layout.range || (ls->cap < (1LL << 30) && !getenv("PRESTOGPU_NO_FAST_PROBE")));
-        if (fast_table && !ls->has_dups && capacity >= n && out_probe_idx && out_build_pos && !ls->sparse_probe_hint && !getenv("PRESTOGPU_NO_FUSED_PROBE")) {
+        if (fast_table && !ls->has_dups && capacity >= n && out_probe_idx && out_build_pos && !t_sparse_probe_hint && !getenv("PRESTOGPU_NO_FUSED_PROBE")) {
             // unique build keys and room for one output row per probe row: resolve, and write the output as if every row emitted
             // scratch belongs to the call, not to the lookup source: several probe operators share one source (LookupJoinOperatorFactory)
             DevBuf probe_slot(ctx, n * 4), tile_sums(ctx, (ntiles + 1) * (int64_t)sizeof(Pair64)), total_buf(ctx, 64);
@@ -1230,9 +1233,9 @@ int32_t pg_lookup_join_page(pg_lookup* ls, const pg_col* probe_keys, int32_t nke
             // some INNER rows found no match: the compacting path below redoes the page
         }
         DevBuf tp(ctx, std::max<int64_t>(capacity, 1) * 4), tb(ctx, std::max<int64_t>(capacity, 1) * 8);
-        ls->sparse_probe_hint = sparse_hint;         // (a context is driven by one thread: the hint cannot leak into another call)
+        t_sparse_probe_hint = sparse_hint;           // per thread, not per lookup source: probers share the source
         int32_t rc = pg_lookup_probe(ls, probe_keys, nkeys, hash_col, n, join_type, tp.as<int32_t>(), tb.as<int64_t>(), PG_MEM_DEVICE, capacity, n_out);
-        ls->sparse_probe_hint = false;
+        t_sparse_probe_hint = false;
         if (rc != PG_OK) { const std::string msg = ctx->err; fail(rc, "%s", msg.c_str()); }
         if (*n_out == 0) return;
         if (out_probe_idx)

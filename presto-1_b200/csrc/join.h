@@ -88,5 +88,4 @@ struct pg_lookup {
     // switched on with pg_lookup_track_visited for RIGHT / FULL joins; every emitted build position sets its bit
     pg::DevBuf visited;
     bool track_visited = false;
-    bool sparse_probe_hint = false;   // set by pg_lookup_join_page around its internal pg_lookup_probe call: the page's samples had many misses
 };

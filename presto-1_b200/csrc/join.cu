@@ -543,6 +543,38 @@ __global__ void __launch_bounds__(SCAN_THREADS) j_probe_emit_fast_kernel(ProbeAr
     }
 }
 
+// the same for unique build keys (every probe row emits at most one row): a warp owns 32 * SCAN_ITEMS consecutive rows, ballot + popc
+// place the emitting rows, and the block needs one exchange of warp totals instead of a block-wide scan per item
+__global__ void __launch_bounds__(SCAN_THREADS) j_probe_emit_unique_kernel(ProbeArgs a, const Pair64* tile_prefix, int32_t* out_probe,
+                                                                           int64_t* out_build) {
+    __shared__ int s_warp[SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t wbase = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)warp * (32 * SCAN_ITEMS);
+    int code[SCAN_ITEMS];
+    unsigned b[SCAN_ITEMS];
+    int mine = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        const int64_t row = wbase + j * 32 + lane;
+        code[j] = row < a.n ? a.probe_slot[row] : -1;
+        b[j] = __ballot_sync(0xffffffffu, row < a.n && (code[j] >= 0 || a.join_type == 1));   // PROBE_OUTER: a miss emits (row, -1)
+        mine += __popc(b[j]);
+    }
+    if (lane == 0) s_warp[warp] = mine;
+    __syncthreads();
+    int64_t d = tile_prefix[blockIdx.x].a;
+    for (int w = 0; w < warp; w++) d += s_warp[w];
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; j++) {
+        if ((b[j] >> lane) & 1u) {
+            const int64_t o = d + __popc(b[j] & ((1u << lane) - 1u));
+            out_probe[o] = (int32_t)(wbase + j * 32 + lane);
+            out_build[o] = code[j] >= 0 ? code[j] : -1;
+        }
+        d += __popc(b[j]);
+    }
+}
+
 // ---- single BIGINT key, build keys unique (no position links), caller's buffers hold at least n rows.  Every probe row yields at
 // most one output row, and in the common foreign-key join (lineitem -> orders) and in every PROBE_OUTER join each row yields exactly
 // one: the output is then the identity on the probe side.  This kernel resolves the rows (four items of a thread together: keys
@@ -1086,7 +1118,7 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
             if (tot == 0) return;
             if (tot < n) {   // some rows do not emit: compact with the per-row codes the kernel stored
                 scan_tile_totals(ctx, tiles, ntiles, tiles + ntiles);
-                PG_LAUNCH(ctx, j_probe_emit_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
+                PG_LAUNCH(ctx, j_probe_emit_unique_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
             }
             if (ls->track_visited) PG_LAUNCH(ctx, j_mark_visited_kernel, grid_for(ctx, tot, 256), 256, 0, ob.d, tot, ls->visited.as<unsigned int>());
             op.finish(tot); ob.finish(tot);
@@ -1111,7 +1143,8 @@ int32_t pg_lookup_probe(pg_lookup* ls, const pg_col* probe_keys, int32_t nkeys, 
         OutVec<int32_t> op; OutVec<int64_t> ob;
         op.begin(ctx, out_probe_idx, out_mem, tot[0]);
         ob.begin(ctx, out_build_pos, out_mem, tot[0]);
-        if (fast) PG_LAUNCH(ctx, j_probe_emit_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
+        if (fast && !ls->has_dups) PG_LAUNCH(ctx, j_probe_emit_unique_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
+        else if (fast) PG_LAUNCH(ctx, j_probe_emit_fast_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
         else PG_LAUNCH(ctx, j_probe_emit_kernel, (int)ntiles, SCAN_THREADS, 0, a, tiles, op.d, ob.d);
         if (ls->track_visited) PG_LAUNCH(ctx, j_mark_visited_kernel, grid_for(ctx, tot[0], 256), 256, 0, ob.d, tot[0], ls->visited.as<unsigned int>());
         op.finish(); ob.finish();

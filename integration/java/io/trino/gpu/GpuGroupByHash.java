@@ -191,6 +191,29 @@ public class GpuGroupByHash
         return windowHash[groupId - windowFirst];
     }
 
+    /**
+     * MarkDistinctHash.markDistinctRows (OP/MarkDistinctHash.java:52-69): the page is added, and marks[i] is true for the first row of
+     * every group the page introduced.  Used by GpuMarkDistinctOperator and GpuDistinctLimitOperator.
+     */
+    boolean[] markDistinct(Page page)
+    {
+        PageArrays a = keyArrays(page);
+        boolean[] marks = new boolean[page.getPositionCount()];
+        check(ctx, PrestoGpu.groupbyMarkDistinct(handle, a.types, a.values, a.nulls, a.offsets, a.arrayOffsets, a.positionCount, inputHashChannel.isPresent(), marks));
+        windowFirst = -1;
+        return marks;
+    }
+
+    /**
+     * The BOOLEAN channel HashSemiJoinOperator appends (OP/HashSemiJoinOperator.java:190-218) for the probe channel of `page`:
+     * values[i] / isNull[i] under SQL's three-valued IN.  `this` is the ChannelSet's hash (built by GpuSetBuilderOperator).
+     */
+    void semiJoin(Page page, boolean setContainsNull, boolean[] values, boolean[] isNull)
+    {
+        PageArrays a = keyArrays(page);
+        check(ctx, PrestoGpu.groupbySemiJoin(handle, a.types, a.values, a.nulls, a.offsets, a.arrayOffsets, a.positionCount, inputHashChannel.isPresent(), setContainsNull, values, isNull));
+    }
+
     private long[] stats()
     {
         long[] s = new long[4];

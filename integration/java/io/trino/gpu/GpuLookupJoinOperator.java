@@ -3,7 +3,7 @@
  * outerJoinCurrentPosition, output through LookupJoinPageBuilder).  One probe page = one native call that returns the probe positions
  * and the build-side channels of every match in the reference's order (probe order; within a probe row the build rows in
  * positionLinks chain order).  LOOKUP_OUTER / FULL_OUTER: the library has the visited-positions tracker (PrestoGpu.lookupTrackVisited /
- * lookupOuterPositions, mirrored by operators.LookupOuterOperator in Python); the Java LookupOuterOperator around it is not written.  Not compiled in this repository (no JDK); presto-1_b200/operators.py (LookupJoinOperator) is the mirror
+ * lookupOuterPositions) and GpuLookupOuterOperator emits the unmatched build rows once the probes are done.  Not compiled in this repository (no JDK); presto-1_b200/operators.py (LookupJoinOperator) is the mirror
  * the parity tests drive.
  */
 package io.trino.gpu;

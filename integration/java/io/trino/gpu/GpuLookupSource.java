@@ -128,6 +128,45 @@ public final class GpuLookupSource
         }
     }
 
+    /** OuterLookupSource (OP/OuterLookupSource.java:176-205): from now on every emitted build position is recorded.  Call before the first probe. */
+    public void trackVisitedPositions()
+    {
+        check(ctx, PrestoGpu.lookupTrackVisited(handle));
+    }
+
+    /**
+     * OuterPositionIterator (OP/OuterLookupSource.java:118-160) in one piece: the build rows no probe has matched, ascending, with
+     * the requested build channels materialised (LookupSource.appendTo for each of them).
+     */
+    public Page unvisitedRows(int[] buildOutputChannels)
+    {
+        long[] count = new long[1];
+        long[] positions = new long[0];
+        int status = PrestoGpu.lookupOuterPositions(handle, positions, count);
+        if (status == PrestoGpu.PG_NEED_MEMORY) {
+            positions = new long[(int) count[0]];
+            status = PrestoGpu.lookupOuterPositions(handle, positions, count);
+        }
+        check(ctx, status);
+        int n = (int) count[0];
+        if (n == 0) {
+            return null;
+        }
+        int[] outTags = new int[buildOutputChannels.length];
+        long[] varBytes = new long[outTags.length];
+        for (int i = 0; i < outTags.length; i++) {
+            outTags[i] = PageArrays.typeTag(buildTypes.get(buildOutputChannels[i]));
+            if (outTags[i] == PrestoGpu.VARCHAR || outTags[i] == PrestoGpu.VARBINARY) {
+                long[] b = new long[1];
+                check(ctx, PrestoGpu.lookupGatherVarBytes(handle, positions, n, buildOutputChannels[i], b));
+                varBytes[i] = b[0];
+            }
+        }
+        OutputArrays out = OutputArrays.allocate(outTags, n, varBytes);
+        check(ctx, PrestoGpu.lookupGather(handle, positions, n, buildOutputChannels, outTags, out.values, out.nulls, out.offsets, out.valueBytes));
+        return new Page(n, PageArrays.toBlocks(outTags, out, n));
+    }
+
     /** The probe-side channels of the output: every output row repeats probe row probePositions[i]. */
     static Block[] selectProbeRows(Page probe, int[] probeOutputChannels, JoinedPage joined)
     {

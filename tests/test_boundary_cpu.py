@@ -84,7 +84,8 @@ def test_java_sources_only_call_declared_natives_and_classes_exist():
     constants = set(re.findall(r"public static final int (\w+)", java))
     want_classes = ["GpuHashAggregationOperator", "GpuHashAggregationOperatorFactory", "GpuHashBuilderOperator", "GpuHashBuilderOperatorFactory",
                     "GpuLookupJoinOperator", "GpuLookupJoinOperatorFactory", "GpuGroupByHash", "GpuGroupedAccumulator", "GpuLookupSource", "BlockFields",
-                    "BlockArrays", "PageArrays", "OutputArrays", "PrestoGpu"]
+                    "BlockArrays", "PageArrays", "OutputArrays", "PrestoGpu",
+                    "GpuMarkDistinctOperator", "GpuDistinctLimitOperator", "GpuSetBuilderOperator", "GpuHashSemiJoinOperator", "GpuLookupOuterOperator"]
     for c in want_classes:
         path = os.path.join(JAVA, c + ".java")
         assert os.path.exists(path), c

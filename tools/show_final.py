@@ -10,4 +10,8 @@ print("  e2e %.3f G rows/s" % (r["e2e"]["value"] / 1e9), "pages ratio", (r.get("
 for k, v in r["workloads"].items():
     if isinstance(v, dict) and "ms_per_step" in v:
         print("  %-28s %8.3f ms %7.2f G rows/s  frac %s" % (k, v["ms_per_step"], v["rows_per_s"] / 1e9, v.get("hbm_frac_per_gpu")))
+q = r["workloads"].get("q3_join_aggregation")
+if q:
+    print("  q3 stages", q.get("stages_ms_untimed_pass"))
+    print("  q3 kernels", q.get("kernels_ms_per_step"))
 print("  crosscheck", {k: v for k, v in r.get("crosscheck", {}).items() if isinstance(v, bool)})

@@ -16,4 +16,5 @@ from .operators import (FINAL, INTERMEDIATE, PARTIAL, SINGLE, AggregatorFactory,
 JOIN_INNER, JOIN_PROBE_OUTER = native.JOIN_INNER, native.JOIN_PROBE_OUTER
 from .exchange import DevicePartitioner, HashPartitionExchange
 from .plans import PartialFinalAggregation, PartitionedAggregation, PartitionedHashJoin, final_aggregators
+from . import pages_serde
 from .expressions import Expr, PageProcessor, ScanFilterAndProjectOperator

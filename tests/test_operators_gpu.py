@@ -475,6 +475,49 @@ def test_packed_pages_carry_partial_output_to_final(pgpu):
     assert sorted(got) == sorted(rows_of(drain(single)))
 
 
+def test_partial_output_travels_as_serialized_pages(pgpu):
+    """f3: PARTIAL output pages (VARCHAR keys, decimal sum / avg states as VARBINARY, counts, with nulls in an argument) written in
+    the reference's PagesSerde framing (presto-1_b200/pages_serde.py), read back and fed to a FINAL operator: the same rows as feeding the
+    pages directly, and as one SINGLE step."""
+    P = pgpu
+    from presto_b200 import pages_serde, tpch
+    cols = tpch.lineitem(40_000 / 5_998_605.2, seed=12, device="cuda")
+    page = tpch.page_to_host(tpch.q1_page(cols), pinned=False)
+    aggs = tpch.q1_aggregators()
+    n = page.position_count
+    wire, direct = [], []
+    for lo, hi in ((0, n // 2), (n // 2, n)):
+        op = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.PARTIAL, aggs, max_partial_memory=1 << 40)
+        op.add_input(P.Page(*[b.slice(lo, hi) for b in page.blocks], position_count=hi - lo))
+        op.finish()
+        out = drain(op)
+        op.close()
+        direct += out
+        wire.append(pages_serde.write_pages(out))
+    inter_types = [P.VARCHAR, P.VARCHAR]
+    fin_aggs, ch = [], 2
+    for a in aggs:
+        fin_aggs.append(P.AggregatorFactory(a.kind, a.in_type, ch))
+        inter_types += list(P.intermediate_types(a.kind, a.in_type))
+        ch += len(P.intermediate_types(a.kind, a.in_type))
+    assert [b.type for b in direct[0].blocks] == inter_types
+    f1 = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs)
+    for buf in wire:
+        for pg in pages_serde.read_pages(buf, inter_types):
+            f1.add_input(pg)
+    f1.finish()
+    f2 = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.FINAL, fin_aggs)
+    for pg in direct:
+        f2.add_input(pg)
+    f2.finish()
+    got, want = rows_of(drain(f1)), rows_of(drain(f2))
+    assert got == want and len(got) == 4
+    single = P.HashAggregationOperator([P.VARCHAR, P.VARCHAR], [0, 1], P.SINGLE, aggs)
+    single.add_input(page)
+    single.finish()
+    assert sorted(got) == sorted(rows_of(drain(single)))
+
+
 def test_operator_yields_on_memory_limit_and_counts_every_row_once(pgpu):
     """HashAggregationOperator's unfinishedWork (HashAggregationOperator.java:398-417, 473-481): with a memory limit the page that
     would grow the table is kept, needsInput() is false and getOutput() gives nothing until the memory is granted; then every row

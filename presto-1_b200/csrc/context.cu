@@ -1,9 +1,40 @@
 // context.cu — context lifetime, column import (host Blocks -> device-resident column buffers).
 #include <stdlib.h>
 
+#include <algorithm>
+
 #include "context.h"
 
 namespace pg {
+
+// 256-bit stores (STG.E.ENL2.256): one instruction moves 32 bytes per lane, and the store path of an SM is bound by instructions, not bytes
+__device__ __forceinline__ void st256(void* p, unsigned long long a, unsigned long long b) {
+    asm volatile("st.global.v4.b64 [%0], {%1, %2, %3, %4};" ::"l"(p), "l"(a), "l"(b), "l"(a), "l"(b) : "memory");
+}
+__global__ void __launch_bounds__(256) fill16_kernel(unsigned long long* body, int64_t n32, unsigned long long* head, unsigned long long* tail,
+                                                     unsigned long long lo, unsigned long long hi) {
+    const int64_t base = (int64_t)blockIdx.x * 1024 + threadIdx.x;     // a block fills 32 KB in a row
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int64_t u = base + k * 256;
+        if (u < n32) st256(body + 4 * u, lo, hi);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (head) { head[0] = lo; head[1] = hi; }
+        if (tail) { tail[0] = lo; tail[1] = hi; }
+    }
+}
+void fill16_async(pg_ctx* ctx, void* p, unsigned long long lo, unsigned long long hi, int64_t bytes) {
+    if (bytes <= 0) return;
+    PG_CHECK_STATE((((uintptr_t)p | (uintptr_t)bytes) & 15) == 0, "fill16: pointer and size must be multiples of 16");
+    unsigned long long* q = (unsigned long long*)p;
+    unsigned long long* head = nullptr;
+    if ((uintptr_t)q & 31) { head = q; q += 2; bytes -= 16; }
+    const int64_t n32 = bytes / 32;
+    unsigned long long* tail = (bytes & 31) ? q + 4 * n32 : nullptr;
+    const int64_t blocks = std::max<int64_t>(1, (n32 + 1023) / 1024);
+    PG_LAUNCH(ctx, fill16_kernel, (int)blocks, 256, 0, q, n32, head, tail, lo, hi);
+}
 
 int64_t col_value_bytes(pg_ctx* ctx, const pg_col& c, int64_t n) {
     if (!type_is_var(c.type)) return n * type_width(c.type);

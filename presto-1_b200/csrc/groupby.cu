@@ -7,17 +7,6 @@ namespace pg {
 static const int GB_THREADS = 256;
 
 // ------------------------------------------------------------------ table init / rebuild
-__global__ void gb_init_slots_kernel(Slot* slots, int64_t nslots, unsigned long long empty) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; i < nslots; i += stride) {
-        // one 16-byte store per slot
-        int4 v;
-        v.x = (int)(empty & 0xffffffffu); v.y = (int)(empty >> 32); v.z = -1; v.w = 0x7fffffff;
-        ((int4*)slots)[i] = v;
-    }
-}
-
 // re-insert every assigned group into a fresh table (BigintGroupByHash.tryRehash :287-303 walks valuesByGroupId
 // the same way; MultiChannelGroupByHash.tryRehash :384-404 walks the old slots)
 __global__ void gb_rebuild_bigint_kernel(Slot* slots, int64_t mask, const int64_t* values_by_group, int64_t groups,
@@ -582,8 +571,8 @@ static const int64_t MIN_PHYS_CAP = 1LL << 20;
 static void alloc_table(pg_groupby* gb, int64_t cap, DevBuf& slots) {
     pg_ctx* ctx = gb->ctx;
     slots.alloc(ctx, (cap + 2) * (int64_t)sizeof(Slot));
-    int grid = grid_for(ctx, cap + 2, 256, 4);
-    PG_LAUNCH(ctx, gb_init_slots_kernel, grid, 256, 0, slots.as<Slot>(), cap + 2, gb->bigint_mode ? EMPTY_KEY : EMPTY_WORD);
+    // every slot = {word: empty marker, gid -1, first_row INT_MAX}
+    fill16_async(ctx, slots.p, gb->bigint_mode ? EMPTY_KEY : EMPTY_WORD, 0x7FFFFFFFFFFFFFFFULL, (cap + 2) * (int64_t)sizeof(Slot));
 }
 
 static void ensure_group_storage(pg_groupby* gb) {

@@ -96,16 +96,6 @@ PG_D bool jrows_equal(const JoinCols& a, int64_t i, const JoinCols& b, int64_t j
     return true;
 }
 
-__global__ void j_init_slots_kernel(JSlot* slots, int64_t nslots, unsigned long long empty) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (; i < nslots; i += stride) {
-        int4 v;
-        v.x = (int)(empty & 0xffffffffu); v.y = (int)(empty >> 32); v.z = 0; v.w = -1;
-        ((int4*)slots)[i] = v;
-    }
-}
-
 // find (probe side) or claim (build side) the slot of row i.  Returns -1 when absent (FIND only).
 template <bool CLAIM>
 PG_D int64_t j_locate(JSlot* slots, int64_t cap, int64_t mask, const JoinCols& build, const JoinCols& rowcols, int64_t i,
@@ -901,8 +891,10 @@ static void lookup_build(pg_lookup* ls) {
         ls->cap = L.total;
         const int64_t nslots = ls->cap + 1;
         ls->slots.alloc(ctx, nslots * (int64_t)sizeof(JSlot));
-            PG_LAUNCH(ctx, j_init_slots_kernel, grid_for(ctx, nslots, 256, 4), 256, 0, ls->slots.as<JSlot>(), nslots,
-                  ls->bigint_fast ? EMPTY_KEY : EMPTY_WORD);
+        {   // every slot = {word: empty marker, count 0, head -1}
+            const unsigned long long empty = ls->bigint_fast ? EMPTY_KEY : EMPTY_WORD;
+            fill16_async(ctx, ls->slots.p, empty, 0xFFFFFFFF00000000ULL, nslots * (int64_t)sizeof(JSlot));
+        }
             if (rows == 0) return;
         if (fast) {
             const DCol& kc = build.c[0];

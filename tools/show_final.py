@@ -5,7 +5,7 @@ import sys
 r = json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
 print("N", r["n_gpus"], "Q1 %.1f G rows/s" % (r["value"] / 1e9), "%.3f ms" % r["ms_per_step"], "plan", r.get("plan"), "kernel frac", r["roofline"].get("frac"),
       "launches", r["gpu_launches"], "clocks", r["clocks"].get("sm_mhz"), r["clocks"].get("reasons"))
-print("  e2e %.3f G rows/s" % (r["e2e"]["value"] / 1e9), "pages ratio", (r.get("e2e_pages") or {}).get("ratio_to_e2e"),
+print("  e2e %.3f G rows/s" % ((r.get("e2e") or {"value": 0})["value"] / 1e9), "pages ratio", (r.get("e2e_pages") or {}).get("ratio_to_e2e"),
       "plain", ((r.get("e2e_pages") or {}).get("plain_host_pages") or {}).get("ratio_to_e2e"))
 for k, v in r["workloads"].items():
     if isinstance(v, dict) and "ms_per_step" in v:
